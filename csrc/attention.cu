@@ -1,0 +1,834 @@
+// attention.cu — flash attention forward + backward on tcgen05 / TMEM / TMA (sm_100a).
+//
+// Layout: q [B, S, Hq, D], k/v [B, S, Hk, D] addressed through 4-D tensor maps
+// {D, H, S, B} with arbitrary row pitch, so q/k/v may be views into one fused QKV buffer.
+// Causal and full attention, GQA (Hq % Hk == 0), D in {64, 128}.
+//
+// Three kernels share one skeleton (warp 0 = TMA, warp 1 = one-thread MMA issuer,
+// warps 2..5 = 128 "row" threads that own one TMEM lane each):
+//   fwd    : S = Q K^T -> online softmax in registers -> P (bf16, swizzled smem) -> O += P V
+//   bwd_dq : S, dP = dO V^T -> dS -> dQ += dS K                       (one CTA per 128 queries)
+//   bwd_dkv: S^T = K Q^T, dP^T = V dO^T -> P^T, dS^T -> dV += P^T dO, dK += dS^T Q
+//                                                                      (one CTA per 128 keys)
+// The reference has no attention kernel for this architecture: training uses external
+// flash-attn (deepspeed/sequence/fpdt_layer.py:14-20) and the inference wrapper rejects
+// anything but sm_8x/sm_90 (deepspeed/inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.cpp:29-31).
+#include "sxb_common.cuh"
+
+namespace sxb {
+namespace attn {
+
+constexpr int kThreads = 192;
+constexpr int BQ = 128;   // rows owned by the 128 row-threads (queries in fwd/dq, keys in dkv)
+constexpr int BC = 64;    // inner block (keys in fwd/dq, queries in dkv)
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+struct Params {
+  int B, S, Hq, Hk, D;
+  int causal;
+  float scale;          // softmax scale (1/sqrt(D))
+  void* out;            // fwd: O [B,S,Hq,D] ; dq: dQ ; dkv: dK
+  void* out2;           // dkv: dV
+  long long out_stride; // row pitch (elements) of out / out2
+  long long out2_stride;
+  float* lse;           // [B, Hq, S] natural-log LSE (fwd writes, bwd reads)
+  const float* delta;   // [B, Hq, S] rowsum(dO * O) (bwd)
+};
+
+// Write one row-thread's 64 bf16 values (128 B) into a [128 x 128B] K-major SW128 tile.
+__device__ __forceinline__ void store_row_sw128(uint8_t* tile, int row, const float (&v)[64]) {
+  uint8_t* dst = tile + row * 128;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    uint4 o;
+    o.x = pack_bf16(v[c * 8 + 0], v[c * 8 + 1]);
+    o.y = pack_bf16(v[c * 8 + 2], v[c * 8 + 3]);
+    o.z = pack_bf16(v[c * 8 + 4], v[c * 8 + 5]);
+    o.w = pack_bf16(v[c * 8 + 6], v[c * 8 + 7]);
+    *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = o;
+  }
+}
+
+__device__ __forceinline__ void ld_row64(uint32_t taddr, float (&v)[64]) {
+  uint32_t a[32], b[32];
+  tmem_ld_32x32(taddr, a);
+  tmem_ld_32x32(taddr + 32, b);
+  tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    v[i] = __uint_as_float(a[i]);
+    v[32 + i] = __uint_as_float(b[i]);
+  }
+}
+
+// K-major operand whose K extent is D (Q, K, V, dO tiles): `rows` rows, D/64 halves of
+// [rows x 128B]; k-step kk covers d in [16kk, 16kk+16).
+__device__ __forceinline__ uint64_t desc_kmajor_d(uint32_t base, int rows, int kk) {
+  return make_smem_desc(base + (kk >> 2) * (rows * 128) + (kk & 3) * 32, 16, 1024, 2);
+}
+// K-major operand with a single 128B-wide tile (P / dS tiles): k-step kk covers 16 columns.
+__device__ __forceinline__ uint64_t desc_kmajor_1(uint32_t base, int kk) {
+  return make_smem_desc(base + kk * 32, 16, 1024, 2);
+}
+// MN-major operand: tile stored as [krows x D] (D contiguous) in D/64 halves of
+// [krows x 128B]; k-step kk covers krows [16kk, 16kk+16).
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, int krows, int kk) {
+  return make_smem_desc(base + kk * 2048, krows * 128, 1024, 2);
+}
+
+// ============================================================================ forward
+template <int D>
+struct FwdSmem {
+  static constexpr int kQ = BQ * D * 2;
+  static constexpr int kKV = BC * D * 2;
+  static constexpr int kStages = 2;
+  static constexpr int kP = BQ * BC * 2;
+  static constexpr int oQ = 0;
+  static constexpr int oK = oQ + kQ;
+  static constexpr int oV = oK + kStages * kKV;
+  static constexpr int oP = oV + kStages * kKV;
+  static constexpr int oBar = oP + kP;
+  static constexpr int kTotal = oBar + 128 + 1024;
+};
+
+template <int D>
+__global__ void __launch_bounds__(kThreads, 2)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, const Params p) {
+  using L = FwdSmem<D>;
+  constexpr int NH = D / 64;  // 128-byte halves along D
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
+  uint64_t* q_full = bars + 0;
+  uint64_t* k_full = bars + 1;    // [2]
+  uint64_t* v_full = bars + 3;    // [2]
+  uint64_t* kv_empty = bars + 5;  // [2]
+  uint64_t* s_full = bars + 7;    // [2]
+  uint64_t* p_full = bars + 9;
+  uint64_t* o_done = bars + 10;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qt = gridDim.x - 1 - blockIdx.x;  // heavy (late) causal tiles first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int hk = h / (p.Hq / p.Hk);
+  const int q0 = qt * BQ;
+  const int kv_len = p.causal ? min(p.S, q0 + BQ) : p.S;
+  const int nblk = (kv_len + BC - 1) / BC;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(q_full, 1);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&k_full[i], 1); mbar_init(&v_full[i], 1); mbar_init(&kv_empty[i], 1);
+        mbar_init(&s_full[i], 1);
+      }
+      mbar_init(p_full, 128);
+      mbar_init(o_done, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 256);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem;          // 2 x 64 columns
+  const uint32_t tO = tmem + 128;    // D columns
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(q_full, L::kQ);
+      for (int hh = 0; hh < NH; ++hh)
+        tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, q0, b);
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
+        mbar_expect_tx(&k_full[st], L::kKV);
+        for (int hh = 0; hh < NH; ++hh)
+          tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &k_full[st], hh * 64, hk,
+                      j * BC, b);
+        mbar_expect_tx(&v_full[st], L::kKV);
+        for (int hh = 0; hh < NH; ++hh)
+          tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &v_full[st], hh * 64, hk,
+                      j * BC, b);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
+      const uint32_t idesc_o = make_idesc(BQ, D, 1, 1, 0, 1);
+      const uint32_t sQ = smem_u32(smem + L::oQ);
+      const uint32_t sP = smem_u32(smem + L::oP);
+      auto issue_qk = [&](int j) {
+        const int st = j & 1;
+        mbar_wait(&k_full[st], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t sK = smem_u32(smem + L::oK + st * L::kKV);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16(tS + (j & 1) * BC, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, BC, kk),
+                   idesc_s, kk != 0);
+        umma_commit(&s_full[j & 1]);
+      };
+      mbar_wait(q_full, 0);
+      issue_qk(0);
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        if (j + 1 < nblk) issue_qk(j + 1);
+        mbar_wait(p_full, j & 1);
+        mbar_wait(&v_full[st], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t sV = smem_u32(smem + L::oV + st * L::kKV);
+#pragma unroll
+        for (int kk = 0; kk < BC / 16; ++kk)
+          umma_f16(tO, desc_kmajor_1(sP, kk), desc_mnmajor(sV, BC, kk), idesc_o,
+                   (j | kk) != 0);
+        umma_commit(&kv_empty[st]);
+        umma_commit(o_done);
+      }
+    }
+  } else {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const uint32_t lane_off = uint32_t(quad * 32) << 16;
+    const int qpos = q0 + row;
+    const float sc = p.scale * kLog2e;
+    float m_run = -INFINITY, l_run = 0.f;
+    uint8_t* sP = smem + L::oP;
+    for (int j = 0; j < nblk; ++j) {
+      mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+      tc_fence_after();
+      float s[64];
+      ld_row64(tS + (j & 1) * BC + lane_off, s);
+      const int k0 = j * BC;
+      const bool need_mask = (p.causal && (k0 + BC - 1 > q0)) || (k0 + BC > p.S);
+      float mx = -INFINITY;
+      if (need_mask) {
+#pragma unroll
+        for (int c = 0; c < 64; ++c) {
+          const int kp = k0 + c;
+          const bool ok = (kp < p.S) && (!p.causal || kp <= qpos);
+          s[c] = ok ? s[c] * sc : -INFINITY;
+          mx = fmaxf(mx, s[c]);
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 64; ++c) {
+          s[c] *= sc;
+          mx = fmaxf(mx, s[c]);
+        }
+      }
+      // Lazy rescale: keep the running max stale unless it grew by more than 2^8.
+      float m_new = m_run;
+      const bool grow = mx > m_run + 8.f;
+      const bool any_grow = __any_sync(0xffffffffu, grow) != 0;
+      if (any_grow) m_new = fmaxf(m_run, mx);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      float rs = 0.f;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) {
+        s[c] = fast_exp2(s[c] - m_use);
+        rs += s[c];
+      }
+      if (j > 0) {
+        mbar_wait(o_done, (j - 1) & 1);
+        tc_fence_after();
+        if (any_grow) {
+          const float alpha = (m_run == -INFINITY) ? 0.f : fast_exp2(m_run - m_use);
+          l_run *= alpha;
+#pragma unroll 1
+          for (int c = 0; c < D / 32; ++c) {
+            uint32_t o[32];
+            tmem_ld_32x32(tO + lane_off + c * 32, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st_32x32(tO + lane_off + c * 32, o);
+          }
+          tmem_st_wait();
+        }
+      }
+      m_run = m_new;
+      l_run += rs;
+      store_row_sw128(sP, row, s);
+      fence_async_smem();
+      tc_fence_before();
+      mbar_arrive(p_full);
+    }
+    mbar_wait(o_done, (nblk - 1) & 1);
+    tc_fence_after();
+    const float inv_l = (l_run > 0.f) ? 1.f / l_run : 0.f;
+    if (qpos < p.S) {
+      __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
+                            ((long long)b * p.S + qpos) * p.out_stride + (long long)h * D;
+#pragma unroll 1
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32(tO + lane_off + c * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint4 w;
+          w.x = pack_bf16(__uint_as_float(o[i * 8 + 0]) * inv_l, __uint_as_float(o[i * 8 + 1]) * inv_l);
+          w.y = pack_bf16(__uint_as_float(o[i * 8 + 2]) * inv_l, __uint_as_float(o[i * 8 + 3]) * inv_l);
+          w.z = pack_bf16(__uint_as_float(o[i * 8 + 4]) * inv_l, __uint_as_float(o[i * 8 + 5]) * inv_l);
+          w.w = pack_bf16(__uint_as_float(o[i * 8 + 6]) * inv_l, __uint_as_float(o[i * 8 + 7]) * inv_l);
+          *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = w;
+        }
+      }
+      if (p.lse)
+        p.lse[((long long)b * p.Hq + h) * p.S + qpos] =
+            (l_run > 0.f) ? (m_run + log2f(l_run)) * kLn2 : -INFINITY;
+    } else {
+      // keep the warp-collective tcgen05.ld pattern uniform
+#pragma unroll 1
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32(tO + lane_off + c * 32, o);
+        tmem_ld_wait();
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 256);
+  }
+}
+
+// ===================================================================== backward: dQ
+// One CTA per (128-query tile, head, batch); loops over 64-key blocks.
+template <int D>
+struct DqSmem {
+  static constexpr int kQ = BQ * D * 2;      // Q and dO tiles
+  static constexpr int kKV = BC * D * 2;
+  static constexpr int kStages = 2;
+  static constexpr int kDS = BQ * BC * 2;
+  static constexpr int oQ = 0;
+  static constexpr int oDO = oQ + kQ;
+  static constexpr int oK = oDO + kQ;
+  static constexpr int oV = oK + kStages * kKV;
+  static constexpr int oDS = oV + kStages * kKV;
+  static constexpr int oBar = oDS + kDS;
+  static constexpr int kTotal = oBar + 128 + 1024;
+};
+
+template <int D>
+__global__ void __launch_bounds__(kThreads, 1)
+attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                   const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
+                   const Params p) {
+  using L = DqSmem<D>;
+  constexpr int NH = D / 64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
+  uint64_t* q_full = bars + 0;
+  uint64_t* kv_full = bars + 1;   // [2]
+  uint64_t* kv_empty = bars + 3;  // [2]
+  uint64_t* s_full = bars + 5;    // S and dP ready
+  uint64_t* ds_full = bars + 6;   // dS written (128 arrivals)
+  uint64_t* dq_done = bars + 7;   // dQ MMA of block j finished
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qt = gridDim.x - 1 - blockIdx.x;
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int hk = h / (p.Hq / p.Hk);
+  const int q0 = qt * BQ;
+  const int kv_len = p.causal ? min(p.S, q0 + BQ) : p.S;
+  const int nblk = (kv_len + BC - 1) / BC;
+
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(q_full, 1);
+      for (int i = 0; i < 2; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1); }
+      mbar_init(s_full, 1);
+      mbar_init(ds_full, 128);
+      mbar_init(dq_done, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 256);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tDP = tmem + 64, tDQ = tmem + 128;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(q_full, 2 * L::kQ);
+      for (int hh = 0; hh < NH; ++hh) {
+        tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, q0, b);
+        tma_load_4d(smem + L::oDO + hh * (BQ * 128), &tmDO, q_full, hh * 64, h, q0, b);
+      }
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
+        mbar_expect_tx(&kv_full[st], 2 * L::kKV);
+        for (int hh = 0; hh < NH; ++hh) {
+          tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &kv_full[st], hh * 64, hk,
+                      j * BC, b);
+          tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &kv_full[st], hh * 64, hk,
+                      j * BC, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
+      const uint32_t idesc_dq = make_idesc(BQ, D, 1, 1, 0, 1);
+      const uint32_t sQ = smem_u32(smem + L::oQ), sDO = smem_u32(smem + L::oDO);
+      const uint32_t sDS = smem_u32(smem + L::oDS);
+      mbar_wait(q_full, 0);
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        mbar_wait(&kv_full[st], (j >> 1) & 1);
+        // S / dP TMEM columns were last read by the row threads before ds_full(j-1), which
+        // this thread waited on in the previous iteration.
+        tc_fence_after();
+        const uint32_t sK = smem_u32(smem + L::oK + st * L::kKV);
+        const uint32_t sV = smem_u32(smem + L::oV + st * L::kKV);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16(tS, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, BC, kk), idesc_s, kk != 0);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16(tDP, desc_kmajor_d(sDO, BQ, kk), desc_kmajor_d(sV, BC, kk), idesc_s, kk != 0);
+        umma_commit(s_full);
+        mbar_wait(ds_full, j & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < BC / 16; ++kk)
+          umma_f16(tDQ, desc_kmajor_1(sDS, kk), desc_mnmajor(sK, BC, kk), idesc_dq,
+                   (j | kk) != 0);
+        umma_commit(&kv_empty[st]);
+        umma_commit(dq_done);
+      }
+    }
+  } else {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const uint32_t lane_off = uint32_t(quad * 32) << 16;
+    const int qpos = q0 + row;
+    const float sc = p.scale * kLog2e;
+    const long long stat_idx = ((long long)b * p.Hq + h) * p.S + min(qpos, p.S - 1);
+    const float lse2 = p.lse[stat_idx] * kLog2e;
+    const float dlt = p.delta[stat_idx];
+    uint8_t* sDS = smem + L::oDS;
+    for (int j = 0; j < nblk; ++j) {
+      mbar_wait(s_full, j & 1);
+      tc_fence_after();
+      float s[64], dp[64];
+      ld_row64(tS + lane_off, s);
+      ld_row64(tDP + lane_off, dp);
+      const int k0 = j * BC;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) {
+        const int kp = k0 + c;
+        const bool ok = (kp < p.S) && (!p.causal || kp <= qpos) && (qpos < p.S);
+        const float pr = ok ? fast_exp2(s[c] * sc - lse2) : 0.f;
+        s[c] = pr * (dp[c] - dlt) * p.scale;
+      }
+      if (j > 0) mbar_wait(dq_done, (j - 1) & 1);  // previous dQ MMA no longer reads sDS
+      store_row_sw128(sDS, row, s);
+      fence_async_smem();
+      tc_fence_before();
+      mbar_arrive(ds_full);
+    }
+    mbar_wait(dq_done, (nblk - 1) & 1);
+    tc_fence_after();
+    __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
+                          ((long long)b * p.S + min(qpos, p.S - 1)) * p.out_stride + (long long)h * D;
+#pragma unroll 1
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t o[32];
+      tmem_ld_32x32(tDQ + lane_off + c * 32, o);
+      tmem_ld_wait();
+      if (qpos < p.S) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint4 w;
+          w.x = pack_bf16(__uint_as_float(o[i * 8 + 0]), __uint_as_float(o[i * 8 + 1]));
+          w.y = pack_bf16(__uint_as_float(o[i * 8 + 2]), __uint_as_float(o[i * 8 + 3]));
+          w.z = pack_bf16(__uint_as_float(o[i * 8 + 4]), __uint_as_float(o[i * 8 + 5]));
+          w.w = pack_bf16(__uint_as_float(o[i * 8 + 6]), __uint_as_float(o[i * 8 + 7]));
+          *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = w;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 256);
+  }
+}
+
+// ================================================================== backward: dK, dV
+// One CTA per (128-key tile, kv head, batch); loops over the q heads of the GQA group
+// and over 64-query blocks.  Row threads own KEY rows (transposed formulation).
+template <int D>
+struct DkvSmem {
+  static constexpr int kKV = BQ * D * 2;   // K and V tiles (128 keys)
+  static constexpr int kQ = BC * D * 2;    // Q_i / dO_i tiles (64 queries)
+  static constexpr int kStages = 2;
+  static constexpr int kPT = BQ * BC * 2;  // P^T / dS^T tiles
+  static constexpr int oK = 0;
+  static constexpr int oV = oK + kKV;
+  static constexpr int oQ = oV + kKV;
+  static constexpr int oDO = oQ + kStages * kQ;
+  static constexpr int oPT = oDO + kStages * kQ;
+  static constexpr int oDST = oPT + kPT;
+  static constexpr int oStat = oDST + kPT;               // [stages][2][64] floats
+  static constexpr int oBar = oStat + kStages * 2 * BC * 4;
+  static constexpr int kTotal = oBar + 128 + 1024;
+};
+
+template <int D>
+__global__ void __launch_bounds__(kThreads, 1)
+attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                    const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
+                    const Params p) {
+  using L = DkvSmem<D>;
+  constexpr int NH = D / 64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
+  uint64_t* kv_full = bars + 0;
+  uint64_t* q_full = bars + 1;    // [2]
+  uint64_t* q_empty = bars + 3;   // [2]
+  uint64_t* s_full = bars + 5;
+  uint64_t* pt_full = bars + 6;   // 128 arrivals
+  uint64_t* acc_done = bars + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kt = blockIdx.x;
+  const int hk = blockIdx.y, b = blockIdx.z;
+  const int group = p.Hq / p.Hk;
+  const int n0 = kt * BQ;
+  const int nq_blocks = (p.S + BC - 1) / BC;
+  const int i_start = p.causal ? (n0 / BC) : 0;
+  const int per_head = nq_blocks - i_start;
+  const int niter = per_head * group;
+
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(kv_full, 1);
+      for (int i = 0; i < 2; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
+      mbar_init(s_full, 1);
+      mbar_init(pt_full, 128);
+      mbar_init(acc_done, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tST = tmem, tDPT = tmem + 64, tDV = tmem + 128, tDK = tmem + 256;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(kv_full, 2 * L::kKV);
+      for (int hh = 0; hh < NH; ++hh) {
+        tma_load_4d(smem + L::oK + hh * (BQ * 128), &tmK, kv_full, hh * 64, hk, n0, b);
+        tma_load_4d(smem + L::oV + hh * (BQ * 128), &tmV, kv_full, hh * 64, hk, n0, b);
+      }
+      for (int it = 0; it < niter; ++it) {
+        const int st = it & 1;
+        const int h = hk * group + it / per_head;
+        const int qi = i_start + it % per_head;
+        mbar_wait(&q_empty[st], ((it >> 1) & 1) ^ 1);
+        mbar_expect_tx(&q_full[st], 2 * L::kQ);
+        for (int hh = 0; hh < NH; ++hh) {
+          tma_load_4d(smem + L::oQ + st * L::kQ + hh * (BC * 128), &tmQ, &q_full[st], hh * 64, h,
+                      qi * BC, b);
+          tma_load_4d(smem + L::oDO + st * L::kQ + hh * (BC * 128), &tmDO, &q_full[st], hh * 64, h,
+                      qi * BC, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
+      const uint32_t idesc_acc = make_idesc(BQ, D, 1, 1, 0, 1);
+      const uint32_t sK = smem_u32(smem + L::oK), sV = smem_u32(smem + L::oV);
+      const uint32_t sPT = smem_u32(smem + L::oPT), sDST = smem_u32(smem + L::oDST);
+      mbar_wait(kv_full, 0);
+      for (int it = 0; it < niter; ++it) {
+        const int st = it & 1;
+        mbar_wait(&q_full[st], (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t sQ = smem_u32(smem + L::oQ + st * L::kQ);
+        const uint32_t sDO = smem_u32(smem + L::oDO + st * L::kQ);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16(tST, desc_kmajor_d(sK, BQ, kk), desc_kmajor_d(sQ, BC, kk), idesc_s, kk != 0);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16(tDPT, desc_kmajor_d(sV, BQ, kk), desc_kmajor_d(sDO, BC, kk), idesc_s, kk != 0);
+        umma_commit(s_full);
+        mbar_wait(pt_full, it & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < BC / 16; ++kk)
+          umma_f16(tDV, desc_kmajor_1(sPT, kk), desc_mnmajor(sDO, BC, kk), idesc_acc,
+                   (it | kk) != 0);
+#pragma unroll
+        for (int kk = 0; kk < BC / 16; ++kk)
+          umma_f16(tDK, desc_kmajor_1(sDST, kk), desc_mnmajor(sQ, BC, kk), idesc_acc,
+                   (it | kk) != 0);
+        umma_commit(&q_empty[st]);
+        umma_commit(acc_done);
+      }
+    }
+  } else {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const int et = threadIdx.x - 64;
+    const uint32_t lane_off = uint32_t(quad * 32) << 16;
+    const int kpos = n0 + row;
+    const float sc = p.scale * kLog2e;
+    float* stat = reinterpret_cast<float*>(smem + L::oStat);
+    uint8_t* sPT = smem + L::oPT;
+    uint8_t* sDST = smem + L::oDST;
+    for (int it = 0; it < niter; ++it) {
+      const int st = it & 1;
+      const int h = hk * group + it / per_head;
+      const int qi = i_start + it % per_head;
+      const int qb = qi * BC;
+      // stage per-query statistics for this block (64 lse + 64 delta)
+      {
+        const int c = et & 63;
+        const int qq = min(qb + c, p.S - 1);
+        const long long si = ((long long)b * p.Hq + h) * p.S + qq;
+        stat[st * 128 + et] = (et < 64) ? p.lse[si] * kLog2e : p.delta[si];
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      mbar_wait(s_full, it & 1);
+      tc_fence_after();
+      float s[64], dp[64];
+      ld_row64(tST + lane_off, s);
+      ld_row64(tDPT + lane_off, dp);
+      const float* lse2 = stat + st * 128;
+      const float* dlt = lse2 + 64;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) {
+        const int qp = qb + c;
+        const bool ok = (qp < p.S) && (kpos < p.S) && (!p.causal || kpos <= qp);
+        const float pr = ok ? fast_exp2(s[c] * sc - lse2[c]) : 0.f;
+        s[c] = pr;                                    // P^T
+        dp[c] = pr * (dp[c] - dlt[c]) * p.scale;      // dS^T (already scaled)
+      }
+      if (it > 0) mbar_wait(acc_done, (it - 1) & 1);
+      store_row_sw128(sPT, row, s);
+      store_row_sw128(sDST, row, dp);
+      fence_async_smem();
+      tc_fence_before();
+      mbar_arrive(pt_full);
+    }
+    if (niter > 0) {
+      mbar_wait(acc_done, (niter - 1) & 1);
+      tc_fence_after();
+    }
+    const long long orow_idx = (long long)b * p.S + min(kpos, p.S - 1);
+    __nv_bfloat16* dk_row = reinterpret_cast<__nv_bfloat16*>(p.out) + orow_idx * p.out_stride + (long long)hk * D;
+    __nv_bfloat16* dv_row = reinterpret_cast<__nv_bfloat16*>(p.out2) + orow_idx * p.out2_stride + (long long)hk * D;
+#pragma unroll 1
+    for (int c = 0; c < 2 * (D / 32); ++c) {
+      const bool is_dv = c < D / 32;
+      const int cc = is_dv ? c : c - D / 32;
+      uint32_t o[32];
+      if (niter > 0) {
+        tmem_ld_32x32((is_dv ? tDV : tDK) + lane_off + cc * 32, o);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = 0u;
+      }
+      if (kpos < p.S) {
+        __nv_bfloat16* dst = (is_dv ? dv_row : dk_row) + cc * 32;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint4 w;
+          w.x = pack_bf16(__uint_as_float(o[i * 8 + 0]), __uint_as_float(o[i * 8 + 1]));
+          w.y = pack_bf16(__uint_as_float(o[i * 8 + 2]), __uint_as_float(o[i * 8 + 3]));
+          w.z = pack_bf16(__uint_as_float(o[i * 8 + 4]), __uint_as_float(o[i * 8 + 5]));
+          w.w = pack_bf16(__uint_as_float(o[i * 8 + 6]), __uint_as_float(o[i * 8 + 7]));
+          *reinterpret_cast<uint4*>(dst + i * 8) = w;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+// delta[b,h,s] = sum_d dO[b,s,h,d] * O[b,s,h,d]   (one warp per (token, head))
+__global__ void __launch_bounds__(256)
+attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                  float* __restrict__ delta, int B, int S, int H, int D, long long o_stride,
+                  long long do_stride) {
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const long long total = (long long)B * S * H;
+  if (w >= total) return;
+  const int h = (int)(w % H);
+  const long long t = w / H;  // b*S + s
+  const __nv_bfloat16* op = o + t * o_stride + (long long)h * D;
+  const __nv_bfloat16* dp = d_o + t * do_stride + (long long)h * D;
+  float acc = 0.f;
+  for (int d = lane * 2; d < D; d += 64) {
+    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(op + d);
+    const __nv_bfloat162 g = *reinterpret_cast<const __nv_bfloat162*>(dp + d);
+    acc += __low2float(a) * __low2float(g) + __high2float(a) * __high2float(g);
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) {
+    const long long bb = t / S, s = t % S;
+    delta[(bb * H + h) * S + s] = acc;
+  }
+}
+
+static int make_qkv_map(CUtensorMap* m, const void* ptr, int B, int S, int H, int D,
+                        long long row_stride, int box_rows) {
+  unsigned long long dims[4] = {(unsigned long long)D, (unsigned long long)H,
+                                (unsigned long long)S, (unsigned long long)B};
+  unsigned long long strides[3] = {(unsigned long long)D * 2, (unsigned long long)row_stride * 2,
+                                   (unsigned long long)row_stride * 2 * (unsigned long long)S};
+  unsigned int box[4] = {64, 1, (unsigned int)box_rows, 1};
+  return encode_tensor_map(m, kBF16, 4, ptr, dims, strides, box, 128);
+}
+
+template <typename K>
+static int set_smem(K kernel, int bytes) {
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  return e == cudaSuccess ? SXB_OK : (int)e;
+}
+
+}  // namespace attn
+}  // namespace sxb
+
+using namespace sxb;
+using namespace sxb::attn;
+
+static bool attn_args_ok(int B, int S, int Hq, int Hk, int D, long long qs, long long ks,
+                         long long vs) {
+  if (B <= 0 || S <= 0 || Hq <= 0 || Hk <= 0 || Hq % Hk) return false;
+  if (D != 64 && D != 128) return false;
+  if ((qs % 8) || (ks % 8) || (vs % 8)) return false;
+  return true;
+}
+
+// bf16 flash attention forward.  q/k/v/out: [B, S, H, D] with row pitches (elements) q_stride...
+// lse: [B, Hq, S] fp32 (may be NULL).
+SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out, void* lse, int B,
+                         int S, int Hq, int Hk, int D, long long q_stride, long long k_stride,
+                         long long v_stride, long long o_stride, int causal, float scale,
+                         void* stream) {
+  if (!attn_args_ok(B, S, Hq, Hk, D, q_stride, k_stride, v_stride) || (o_stride % 8))
+    return SXB_ERR_UNSUPPORTED;
+  CUtensorMap tq, tk, tv;
+  int rc;
+  if ((rc = make_qkv_map(&tq, q, B, S, Hq, D, q_stride, BQ))) return rc;
+  if ((rc = make_qkv_map(&tk, k, B, S, Hk, D, k_stride, BC))) return rc;
+  if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BC))) return rc;
+  Params p{};
+  p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
+  p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
+  dim3 grid((S + BQ - 1) / BQ, Hq, B);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (D == 128) {
+    if ((rc = set_smem(attn_fwd_kernel<128>, FwdSmem<128>::kTotal))) return rc;
+    attn_fwd_kernel<128><<<grid, kThreads, FwdSmem<128>::kTotal, s>>>(tq, tk, tv, p);
+  } else {
+    if ((rc = set_smem(attn_fwd_kernel<64>, FwdSmem<64>::kTotal))) return rc;
+    attn_fwd_kernel<64><<<grid, kThreads, FwdSmem<64>::kTotal, s>>>(tq, tk, tv, p);
+  }
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+// Backward.  delta: [B, Hq, S] fp32 scratch written here; dq/dk/dv: [B, S, H, D] bf16.
+SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void* out,
+                         const void* d_out, const void* lse, void* delta, void* dq, void* dk,
+                         void* dv, int B, int S, int Hq, int Hk, int D, long long q_stride,
+                         long long k_stride, long long v_stride, long long o_stride,
+                         long long do_stride, long long dq_stride, long long dk_stride,
+                         long long dv_stride, int causal, float scale, void* stream) {
+  if (!attn_args_ok(B, S, Hq, Hk, D, q_stride, k_stride, v_stride) || (o_stride % 8) ||
+      (do_stride % 8) || (dq_stride % 8) || (dk_stride % 8) || (dv_stride % 8))
+    return SXB_ERR_UNSUPPORTED;
+  cudaStream_t s = (cudaStream_t)stream;
+  {
+    const long long warps = (long long)B * S * Hq;
+    const long long blocks = (warps * 32 + 255) / 256;
+    attn_delta_kernel<<<(unsigned)blocks, 256, 0, s>>>((const __nv_bfloat16*)out,
+                                                       (const __nv_bfloat16*)d_out, (float*)delta,
+                                                       B, S, Hq, D, o_stride, do_stride);
+    SXB_CHECK_LAUNCH();
+  }
+  int rc;
+  Params p{};
+  p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
+  p.lse = (float*)const_cast<void*>(lse); p.delta = (const float*)delta;
+  // ---- dQ
+  {
+    CUtensorMap tq, tk, tv, tdo;
+    if ((rc = make_qkv_map(&tq, q, B, S, Hq, D, q_stride, BQ))) return rc;
+    if ((rc = make_qkv_map(&tdo, d_out, B, S, Hq, D, do_stride, BQ))) return rc;
+    if ((rc = make_qkv_map(&tk, k, B, S, Hk, D, k_stride, BC))) return rc;
+    if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BC))) return rc;
+    p.out = dq; p.out_stride = dq_stride;
+    dim3 grid((S + BQ - 1) / BQ, Hq, B);
+    if (D == 128) {
+      if ((rc = set_smem(attn_bwd_dq_kernel<128>, DqSmem<128>::kTotal))) return rc;
+      attn_bwd_dq_kernel<128><<<grid, kThreads, DqSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
+    } else {
+      if ((rc = set_smem(attn_bwd_dq_kernel<64>, DqSmem<64>::kTotal))) return rc;
+      attn_bwd_dq_kernel<64><<<grid, kThreads, DqSmem<64>::kTotal, s>>>(tq, tk, tv, tdo, p);
+    }
+    SXB_CHECK_LAUNCH();
+  }
+  // ---- dK, dV
+  {
+    CUtensorMap tq, tk, tv, tdo;
+    if ((rc = make_qkv_map(&tq, q, B, S, Hq, D, q_stride, BC))) return rc;
+    if ((rc = make_qkv_map(&tdo, d_out, B, S, Hq, D, do_stride, BC))) return rc;
+    if ((rc = make_qkv_map(&tk, k, B, S, Hk, D, k_stride, BQ))) return rc;
+    if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BQ))) return rc;
+    p.out = dk; p.out_stride = dk_stride; p.out2 = dv; p.out2_stride = dv_stride;
+    dim3 grid((S + BQ - 1) / BQ, Hk, B);
+    if (D == 128) {
+      if ((rc = set_smem(attn_bwd_dkv_kernel<128>, DkvSmem<128>::kTotal))) return rc;
+      attn_bwd_dkv_kernel<128><<<grid, kThreads, DkvSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
+    } else {
+      if ((rc = set_smem(attn_bwd_dkv_kernel<64>, DkvSmem<64>::kTotal))) return rc;
+      attn_bwd_dkv_kernel<64><<<grid, kThreads, DkvSmem<64>::kTotal, s>>>(tq, tk, tv, tdo, p);
+    }
+    SXB_CHECK_LAUNCH();
+  }
+  return SXB_OK;
+}

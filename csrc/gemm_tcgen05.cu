@@ -1,0 +1,413 @@
+// gemm_tcgen05.cu — persistent, warp-specialised bf16 GEMM for sm_100a.
+//
+//   C[M,N] (+)= op(A) * op(B)         fp32 accumulation in TMEM
+//
+//   layout NT : A[M,K] row-major, B[N,K] row-major   (forward  y = x W^T)
+//   layout NN : A[M,K] row-major, B[K,N] row-major   (dgrad    dx = dy W)
+//   layout TN : A[K,M] row-major, B[K,N] row-major   (wgrad    dW = dy^T x)
+//
+// Structure (one CTA per SM, 192 threads):
+//   warp 0      TMA producer  : cp.async.bulk.tensor -> 128B-swizzled smem ring
+//   warp 1      MMA issuer    : one thread issues tcgen05.mma (128 x BN x 16),
+//                               accumulators double-buffered in TMEM
+//   warps 2..5  epilogue      : tcgen05.ld -> bf16 -> swizzled smem -> TMA store
+//                               (or direct global read-modify-write when
+//                               accumulating / writing fp32)
+// Replaces the cuBLAS calls behind F.linear that the reference relies on
+// (reference: deepspeed/inference/v2/kernels/core_ops/blas_kernels/blas_utils.h:31-41,
+// and every nn.Linear in the training path).
+#include "sxb_common.cuh"
+
+namespace sxb {
+namespace gemm {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = one 128B swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kThreads = 192;
+constexpr int kEpiThreads = 128;
+constexpr int kStageC = 128 * 64 * 2;  // one 128x64 bf16 staging tile (16 KB)
+
+enum Layout : int { NT = 0, NN = 1, TN = 2 };
+
+template <int BN, int STAGES>
+struct SmemPlan {
+  static constexpr int kA = BM * BK * 2;
+  static constexpr int kB = BN * BK * 2;
+  static constexpr int kStage = kA + kB;
+  static constexpr int kRing = kStage * STAGES;
+  static constexpr int kCOff = kRing;
+  static constexpr int kBarOff = kCOff + 2 * kStageC;
+  static constexpr int kTotal = kBarOff + 256 + 1024;  // + alignment slack
+};
+
+struct Params {
+  int M, N, K;
+  int layout;
+  int c_dtype;     // kBF16 or kF32
+  int accumulate;  // C += result
+  int direct;      // 1 = epilogue writes global memory directly (no TMA store)
+  void* C;
+  int ldc;
+  float alpha;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmC, const Params p) {
+  using Plan = SmemPlan<BN, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Plan::kBarOff);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const bool a_mn = (p.layout == TN);
+  const bool b_mn = (p.layout != NT);
+
+  const int tiles_m = (p.M + BM - 1) / BM;
+  const int tiles_n = (p.N + BN - 1) / BN;
+  const int num_tiles = tiles_m * tiles_n;
+  const int num_kb = (p.K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < STAGES; ++s) {
+        mbar_init(&full_bar[s], 1);
+        mbar_init(&empty_bar[s], 1);
+      }
+      for (int s = 0; s < 2; ++s) {
+        mbar_init(&tfull_bar[s], 1);
+        mbar_init(&tempty_bar[s], kEpiThreads);
+      }
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 2 * BN);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  auto tile_coord = [&](int t, int& tm, int& tn) {
+    constexpr int GROUP = 8;
+    const int group_sz = GROUP * tiles_n;
+    const int g = t / group_sz;
+    const int first_m = g * GROUP;
+    const int gm = min(tiles_m - first_m, GROUP);
+    const int r = t - g * group_sz;
+    tm = first_m + (r % gm);
+    tn = r / gm;
+  };
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        int tm, tn;
+        tile_coord(t, tm, tn);
+        const int m0 = tm * BM, n0 = tn * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Plan::kStage;
+          uint8_t* sb = sa + Plan::kA;
+          mbar_expect_tx(&full_bar[stage], Plan::kStage);
+          const int k0 = kb * BK;
+          if (!a_mn) {
+            tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d(sa + j * (64 * BK * 2), &tmA, &full_bar[stage], m0 + j * 64, k0);
+          }
+          if (!b_mn) {
+            tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sb + j * (64 * BK * 2), &tmB, &full_bar[stage], n0 + j * 64, k0);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // -------------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(BM, BN, 1, 1, a_mn ? 1u : 0u, b_mn ? 1u : 0u);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * Plan::kStage);
+          const uint32_t sb = sa + Plan::kA;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // K-major: 16 elements = 32 B inside the swizzled 128 B row.
+            // MN-major: 16 k-rows of 128 B = 2048 B (two 8-row swizzle atoms).
+            const uint64_t adesc = a_mn ? make_smem_desc(sa + k * 2048, 64 * BK * 2, 1024, 2)
+                                        : make_smem_desc(sa + k * 32, 16, 1024, 2);
+            const uint64_t bdesc = b_mn ? make_smem_desc(sb + k * 2048, 64 * BK * 2, 1024, 2)
+                                        : make_smem_desc(sb + k * 32, 16, 1024, 2);
+            umma_f16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tfull_bar[acc]);
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ---------------------------------------------------------------- epilogue
+    const int et = threadIdx.x - 64;       // 0..127
+    const int quad = warp & 3;             // TMEM lane quadrant this warp may read
+    const int row = quad * 32 + lane;      // row of the 128-row tile owned by this thread
+    const bool use_tma = !p.direct;
+    uint8_t* stage_c = smem + Plan::kCOff;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int buf = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      int tm, tn;
+      tile_coord(t, tm, tn);
+      const int m0 = tm * BM, n0 = tn * BN;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + acc * BN + (uint32_t(quad * 32) << 16);
+#pragma unroll 1
+      for (int c = 0; c < BN / 64; ++c) {
+        uint32_t v0[32], v1[32];
+        tmem_ld_32x32(t_row + c * 64, v0);
+        tmem_ld_32x32(t_row + c * 64 + 32, v1);
+        tmem_ld_wait();
+        if (c == BN / 64 - 1) {
+          tc_fence_before();
+          mbar_arrive(&tempty_bar[acc]);
+        }
+        if (use_tma) {
+          if (et == 0) tma_store_wait_read<1>();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          uint8_t* dst = stage_c + buf * kStageC + row * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t* s = (j < 4) ? &v0[j * 8] : &v1[(j - 4) * 8];
+            uint4 o;
+            o.x = pack_bf16(__uint_as_float(s[0]), __uint_as_float(s[1]));
+            o.y = pack_bf16(__uint_as_float(s[2]), __uint_as_float(s[3]));
+            o.z = pack_bf16(__uint_as_float(s[4]), __uint_as_float(s[5]));
+            o.w = pack_bf16(__uint_as_float(s[6]), __uint_as_float(s[7]));
+            *reinterpret_cast<uint4*>(dst + ((j ^ (row & 7)) << 4)) = o;
+          }
+          fence_async_smem();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (et == 0) {
+            tma_store_2d(&tmC, stage_c + buf * kStageC, n0 + c * 64, m0);
+            tma_store_commit();
+          }
+          buf ^= 1;
+        } else {
+          const int gr = m0 + row;
+          if (gr < p.M) {
+            const int gc0 = n0 + c * 64;
+            if (p.c_dtype == kBF16) {
+              __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)gr * p.ldc;
+#pragma unroll
+              for (int j = 0; j < 64; ++j) {
+                const int gc = gc0 + j;
+                if (gc < p.N) {
+                  float r = p.alpha * __uint_as_float(j < 32 ? v0[j] : v1[j - 32]);
+                  if (p.accumulate) r += __bfloat162float(crow[gc]);
+                  crow[gc] = __float2bfloat16_rn(r);
+                }
+              }
+            } else {
+              float* crow = reinterpret_cast<float*>(p.C) + (size_t)gr * p.ldc;
+              if (gc0 + 64 <= p.N && (p.ldc & 3) == 0) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const uint32_t* s = (j < 8) ? &v0[j * 4] : &v1[(j - 8) * 4];
+                  float4 r = make_float4(p.alpha * __uint_as_float(s[0]),
+                                         p.alpha * __uint_as_float(s[1]),
+                                         p.alpha * __uint_as_float(s[2]),
+                                         p.alpha * __uint_as_float(s[3]));
+                  float4* dp = reinterpret_cast<float4*>(crow + gc0 + j * 4);
+                  if (p.accumulate) {
+                    float4 o = *dp;
+                    r.x += o.x; r.y += o.y; r.z += o.z; r.w += o.w;
+                  }
+                  *dp = r;
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 64; ++j) {
+                  const int gc = gc0 + j;
+                  if (gc < p.N) {
+                    float r = p.alpha * __uint_as_float(j < 32 ? v0[j] : v1[j - 32]);
+                    if (p.accumulate) r += crow[gc];
+                    crow[gc] = r;
+                  }
+                }
+              }
+            }
+          }
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+    if (use_tma && et == 0) tma_store_wait<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// 2-D bf16 tensor map over a row-major [rows, cols] matrix with row pitch `ld` elements;
+// box = [box_rows, box_cols] with box_cols * 2 == 128 bytes (128B swizzle).
+static int make_map_2d(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
+                       uint32_t box_rows, uint32_t box_cols, CUtensorMapDataType dt, int esize) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return SXB_ERR_DRIVER;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * (uint64_t)esize};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? SXB_OK : SXB_ERR_DRIVER;
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+  if (!g_num_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+template <int BN, int STAGES>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
+                  const Params& p, int max_ctas, cudaStream_t stream) {
+  using Plan = SmemPlan<BN, STAGES>;
+  static bool configured = false;
+  auto kfn = gemm_kernel<BN, STAGES>;
+  if (!configured) {
+    cudaError_t e =
+        cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
+  int grid = num_sms();
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (tiles < grid) grid = tiles;
+  kfn<<<grid, kThreads, Plan::kTotal, stream>>>(ta, tb, tc, p);
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+}  // namespace gemm
+}  // namespace sxb
+
+using namespace sxb;
+using namespace sxb::gemm;
+
+// C[M,N] (+)= alpha * op(A) op(B).  A/B are bf16; C is bf16 or fp32 (c_dtype).
+// lda/ldb/ldc are row pitches in elements of the *stored* matrices.
+// max_ctas: 0 = all SMs; otherwise leaves SMs free for a concurrent comm kernel.
+SXB_API int sxb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int layout,
+                          int lda, int ldb, int ldc, int c_dtype, int accumulate, float alpha,
+                          int max_ctas, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return SXB_OK;
+  if (layout < 0 || layout > 2) return SXB_ERR_BAD_ARG;
+  if (c_dtype != kBF16 && c_dtype != kF32) return SXB_ERR_BAD_ARG;
+  if ((lda % 8) || (ldb % 8) || (reinterpret_cast<uintptr_t>(A) & 15) ||
+      (reinterpret_cast<uintptr_t>(B) & 15))
+    return SXB_ERR_UNSUPPORTED;
+  const bool tma_c =
+      (c_dtype == kBF16) && !accumulate && alpha == 1.0f && (ldc % 8 == 0) &&
+      ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+  Params p;
+  p.M = M; p.N = N; p.K = K; p.layout = layout; p.c_dtype = c_dtype;
+  p.accumulate = accumulate ? 1 : 0; p.direct = tma_c ? 0 : 1; p.C = C; p.ldc = ldc;
+  p.alpha = alpha;
+  const int BNsel = (N > 128) ? 256 : 128;
+  CUtensorMap ta, tb, tc;
+  int rc;
+  const CUtensorMapDataType BF = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  if (layout == TN) rc = make_map_2d(&ta, A, K, M, lda, BK, 64, BF, 2);
+  else rc = make_map_2d(&ta, A, M, K, lda, BM, BK, BF, 2);
+  if (rc) return rc;
+  if (layout == NT) rc = make_map_2d(&tb, B, N, K, ldb, BNsel, BK, BF, 2);
+  else rc = make_map_2d(&tb, B, K, N, ldb, BK, 64, BF, 2);
+  if (rc) return rc;
+  if (tma_c) {
+    rc = make_map_2d(&tc, C, M, N, ldc, BM, 64, BF, 2);
+    if (rc) return rc;
+  } else {
+    tc = ta;  // never dereferenced by the direct epilogue
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (BNsel == 256) return launch<256, 4>(ta, tb, tc, p, max_ctas, s);
+  return launch<128, 6>(ta, tb, tc, p, max_ctas, s);
+}
