@@ -150,7 +150,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, q0, b);
       for (int j = 0; j < nblk; ++j) {
         const int st = j & 1;
-        mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
+        if (!mbar_wait_to(&kv_empty[st], ((j >> 1) & 1) ^ 1, 21)) goto done;
         mbar_expect_tx(&k_full[st], L::kKV);
         for (int hh = 0; hh < NH; ++hh)
           tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &k_full[st], hh * 64, hk,
@@ -167,9 +167,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const uint32_t idesc_o = make_idesc(BQ, D, 1, 1, 0, 1);
       const uint32_t sQ = smem_u32(smem + L::oQ);
       const uint32_t sP = smem_u32(smem + L::oP);
-      auto issue_qk = [&](int j) {
+      auto issue_qk = [&](int j) -> bool {
         const int st = j & 1;
-        mbar_wait(&k_full[st], (j >> 1) & 1);
+        if (!mbar_wait_to(&k_full[st], (j >> 1) & 1, 11, j)) return false;
         tc_fence_after();
         const uint32_t sK = smem_u32(smem + L::oK + st * L::kKV);
 #pragma unroll
@@ -177,14 +177,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           umma_f16(tS + (j & 1) * BC, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, BC, kk),
                    idesc_s, kk != 0);
         umma_commit(&s_full[j & 1]);
+        return true;
       };
-      mbar_wait(q_full, 0);
-      issue_qk(0);
+      if (!mbar_wait_to(q_full, 0, 10)) goto done;
+      if (!issue_qk(0)) goto done;
       for (int j = 0; j < nblk; ++j) {
         const int st = j & 1;
-        if (j + 1 < nblk) issue_qk(j + 1);
-        mbar_wait(p_full, j & 1);
-        mbar_wait(&v_full[st], (j >> 1) & 1);
+        if (j + 1 < nblk && !issue_qk(j + 1)) goto done;
+        if (!mbar_wait_to(p_full, j & 1, 22)) goto done;
+        if (!mbar_wait_to(&v_full[st], (j >> 1) & 1, 23)) goto done;
         tc_fence_after();
         const uint32_t sV = smem_u32(smem + L::oV + st * L::kKV);
 #pragma unroll
@@ -204,7 +205,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     float m_run = -INFINITY, l_run = 0.f;
     uint8_t* sP = smem + L::oP;
     for (int j = 0; j < nblk; ++j) {
-      mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+      if (!mbar_wait_to(&s_full[j & 1], (j >> 1) & 1, 24)) goto done;
       tc_fence_after();
       float s[64];
       ld_row64(tS + (j & 1) * BC + lane_off, s);
@@ -239,7 +240,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         rs += s[c];
       }
       if (j > 0) {
-        mbar_wait(o_done, (j - 1) & 1);
+        if (!mbar_wait_to(o_done, (j - 1) & 1, 25)) goto done;
         tc_fence_after();
         if (any_grow) {
           const float alpha = (m_run == -INFINITY) ? 0.f : fast_exp2(m_run - m_use);
@@ -263,7 +264,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tc_fence_before();
       mbar_arrive(p_full);
     }
-    mbar_wait(o_done, (nblk - 1) & 1);
+    if (!mbar_wait_to(o_done, (nblk - 1) & 1, 26)) goto done;
     tc_fence_after();
     const float inv_l = (l_run > 0.f) ? 1.f / l_run : 0.f;
     if (qpos < p.S) {
@@ -297,6 +298,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
     }
   }
+done:
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -376,7 +378,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
       for (int j = 0; j < nblk; ++j) {
         const int st = j & 1;
-        mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
+        if (!mbar_wait_to(&kv_empty[st], ((j >> 1) & 1) ^ 1, 27)) goto done;
         mbar_expect_tx(&kv_full[st], 2 * L::kKV);
         for (int hh = 0; hh < NH; ++hh) {
           tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &kv_full[st], hh * 64, hk,
@@ -392,10 +394,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       const uint32_t idesc_dq = make_idesc(BQ, D, 1, 1, 0, 1);
       const uint32_t sQ = smem_u32(smem + L::oQ), sDO = smem_u32(smem + L::oDO);
       const uint32_t sDS = smem_u32(smem + L::oDS);
-      mbar_wait(q_full, 0);
+      if (!mbar_wait_to(q_full, 0, 28)) goto done;
       for (int j = 0; j < nblk; ++j) {
         const int st = j & 1;
-        mbar_wait(&kv_full[st], (j >> 1) & 1);
+        if (!mbar_wait_to(&kv_full[st], (j >> 1) & 1, 29)) goto done;
         // S / dP TMEM columns were last read by the row threads before ds_full(j-1), which
         // this thread waited on in the previous iteration.
         tc_fence_after();
@@ -408,7 +410,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tDP, desc_kmajor_d(sDO, BQ, kk), desc_kmajor_d(sV, BC, kk), idesc_s, kk != 0);
         umma_commit(s_full);
-        mbar_wait(ds_full, j & 1);
+        if (!mbar_wait_to(ds_full, j & 1, 30)) goto done;
         tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
@@ -429,7 +431,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const float dlt = p.delta[stat_idx];
     uint8_t* sDS = smem + L::oDS;
     for (int j = 0; j < nblk; ++j) {
-      mbar_wait(s_full, j & 1);
+      if (!mbar_wait_to(s_full, j & 1, 31)) goto done;
       tc_fence_after();
       float s[64], dp[64];
       ld_row64(tS + lane_off, s);
@@ -442,13 +444,13 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const float pr = ok ? fast_exp2(s[c] * sc - lse2) : 0.f;
         s[c] = pr * (dp[c] - dlt) * p.scale;
       }
-      if (j > 0) mbar_wait(dq_done, (j - 1) & 1);  // previous dQ MMA no longer reads sDS
+      if (j > 0) if (!mbar_wait_to(dq_done, (j - 1) & 1, 32)) goto done;  // previous dQ MMA no longer reads sDS
       store_row_sw128(sDS, row, s);
       fence_async_smem();
       tc_fence_before();
       mbar_arrive(ds_full);
     }
-    mbar_wait(dq_done, (nblk - 1) & 1);
+    if (!mbar_wait_to(dq_done, (nblk - 1) & 1, 33)) goto done;
     tc_fence_after();
     __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
                           ((long long)b * p.S + min(qpos, p.S - 1)) * p.out_stride + (long long)h * D;
@@ -470,6 +472,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
     }
   }
+done:
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -556,7 +559,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         const int st = it & 1;
         const int h = hk * group + it / per_head;
         const int qi = i_start + it % per_head;
-        mbar_wait(&q_empty[st], ((it >> 1) & 1) ^ 1);
+        if (!mbar_wait_to(&q_empty[st], ((it >> 1) & 1) ^ 1, 34)) goto done;
         mbar_expect_tx(&q_full[st], 2 * L::kQ);
         for (int hh = 0; hh < NH; ++hh) {
           tma_load_4d(smem + L::oQ + st * L::kQ + hh * (BC * 128), &tmQ, &q_full[st], hh * 64, h,
@@ -572,10 +575,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const uint32_t idesc_acc = make_idesc(BQ, D, 1, 1, 0, 1);
       const uint32_t sK = smem_u32(smem + L::oK), sV = smem_u32(smem + L::oV);
       const uint32_t sPT = smem_u32(smem + L::oPT), sDST = smem_u32(smem + L::oDST);
-      mbar_wait(kv_full, 0);
+      if (!mbar_wait_to(kv_full, 0, 35)) goto done;
       for (int it = 0; it < niter; ++it) {
         const int st = it & 1;
-        mbar_wait(&q_full[st], (it >> 1) & 1);
+        if (!mbar_wait_to(&q_full[st], (it >> 1) & 1, 36)) goto done;
         tc_fence_after();
         const uint32_t sQ = smem_u32(smem + L::oQ + st * L::kQ);
         const uint32_t sDO = smem_u32(smem + L::oDO + st * L::kQ);
@@ -586,7 +589,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tDPT, desc_kmajor_d(sV, BQ, kk), desc_kmajor_d(sDO, BC, kk), idesc_s, kk != 0);
         umma_commit(s_full);
-        mbar_wait(pt_full, it & 1);
+        if (!mbar_wait_to(pt_full, it & 1, 37)) goto done;
         tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
@@ -623,7 +626,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         stat[st * 128 + et] = (et < 64) ? p.lse[si] * kLog2e : p.delta[si];
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      mbar_wait(s_full, it & 1);
+      if (!mbar_wait_to(s_full, it & 1, 38)) goto done;
       tc_fence_after();
       float s[64], dp[64];
       ld_row64(tST + lane_off, s);
@@ -638,7 +641,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         s[c] = pr;                                    // P^T
         dp[c] = pr * (dp[c] - dlt[c]) * p.scale;      // dS^T (already scaled)
       }
-      if (it > 0) mbar_wait(acc_done, (it - 1) & 1);
+      if (it > 0) if (!mbar_wait_to(acc_done, (it - 1) & 1, 39)) goto done;
       store_row_sw128(sPT, row, s);
       store_row_sw128(sDST, row, dp);
       fence_async_smem();
@@ -646,7 +649,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       mbar_arrive(pt_full);
     }
     if (niter > 0) {
-      mbar_wait(acc_done, (niter - 1) & 1);
+      if (!mbar_wait_to(acc_done, (niter - 1) & 1, 40)) goto done;
       tc_fence_after();
     }
     const long long orow_idx = (long long)b * p.S + min(kpos, p.S - 1);
@@ -678,6 +681,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
     }
   }
+done:
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -733,6 +737,8 @@ static int set_smem(K kernel, int bytes) {
 
 using namespace sxb;
 using namespace sxb::attn;
+
+SXB_DEFINE_HANG_ACCESSOR(sxb_attn_hang_info)
 
 static bool attn_args_ok(int B, int S, int Hq, int Hk, int D, long long qs, long long ks,
                          long long vs) {

@@ -122,7 +122,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         tile_coord(t, tm, tn);
         const int m0 = tm * BM, n0 = tn * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (!mbar_wait_to(&empty_bar[stage], phase ^ 1, 1, kb)) goto done;
           uint8_t* sa = smem + stage * Plan::kStage;
           uint8_t* sb = sa + Plan::kA;
           mbar_expect_tx(&full_bar[stage], Plan::kStage);
@@ -157,11 +157,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        if (!mbar_wait_to(&tempty_bar[acc], acc_phase ^ 1, 2, t)) goto done;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
+          if (!mbar_wait_to(&full_bar[stage], phase, 3, kb)) goto done;
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * Plan::kStage);
           const uint32_t sb = sa + Plan::kA;
@@ -202,7 +202,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       int tm, tn;
       tile_coord(t, tm, tn);
       const int m0 = tm * BM, n0 = tn * BN;
-      mbar_wait(&tfull_bar[acc], acc_phase);
+      if (!mbar_wait_to(&tfull_bar[acc], acc_phase, 4, t)) goto done;
       tc_fence_after();
       const uint32_t t_row = tmem_base + acc * BN + (uint32_t(quad * 32) << 16);
 #pragma unroll 1
@@ -291,6 +291,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (use_tma && et == 0) tma_store_wait<0>();
   }
 
+done:
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -371,6 +372,8 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
 
 using namespace sxb;
 using namespace sxb::gemm;
+
+SXB_DEFINE_HANG_ACCESSOR(sxb_gemm_hang_info)
 
 // C[M,N] (+)= alpha * op(A) op(B).  A/B are bf16; C is bf16 or fp32 (c_dtype).
 // lda/ldb/ldc are row pitches in elements of the *stored* matrices.

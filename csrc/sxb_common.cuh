@@ -369,3 +369,51 @@ int encode_tensor_map(CUtensorMap* m, int dtype_code, int rank, const void* ptr,
                       const unsigned long long* dims, const unsigned long long* strides_bytes,
                       const unsigned int* box, int swizzle_bytes);
 }  // namespace sxb
+
+// ---- appended: bounded mbarrier wait + hang diagnostics -----------------------------------
+// A protocol bug must never wedge the GPU: every pipeline wait gives up after ~2 s, records
+// who waited on what, raises a per-library abort flag that all other waiters observe, and the
+// kernel drains normally (its output is then garbage and the host can read the record).
+namespace sxb {
+static __device__ unsigned int g_sxb_hang[8];  // [0]=flag [1]=tag [2..4]=blockIdx [5]=threadIdx.x [6]=parity [7]=aux
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+static __device__ __noinline__ bool mbar_wait_slow(uint64_t* bar, uint32_t parity, uint32_t tag, uint32_t aux) {
+  const unsigned long long t0 = global_ns();
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if ((++spins & 0x3F) == 0) {
+      if (*reinterpret_cast<volatile unsigned int*>(&g_sxb_hang[0]) != 0) return false;
+      if (global_ns() - t0 > 2000000000ull) {
+        if (atomicCAS(&g_sxb_hang[0], 0u, 1u) == 0u) {
+          g_sxb_hang[1] = tag; g_sxb_hang[2] = blockIdx.x; g_sxb_hang[3] = blockIdx.y;
+          g_sxb_hang[4] = blockIdx.z; g_sxb_hang[5] = threadIdx.x; g_sxb_hang[6] = parity;
+          g_sxb_hang[7] = aux;
+          __threadfence();
+        }
+        return false;
+      }
+    }
+  }
+  return true;
+}
+// Returns false when the wait was abandoned (caller must leave its role loop).
+__device__ __forceinline__ bool mbar_wait_to(uint64_t* bar, uint32_t parity, uint32_t tag, uint32_t aux = 0) {
+  if (mbar_try_wait(bar, parity)) return true;
+  return mbar_wait_slow(bar, parity, tag, aux);
+}
+}  // namespace sxb
+
+// Host accessor: copies the 8-word record into `out` and clears it.  One per translation unit.
+#define SXB_DEFINE_HANG_ACCESSOR(fn_name)                                                    \
+  SXB_API int fn_name(unsigned int* out) {                                                   \
+    cudaError_t e = cudaMemcpyFromSymbol(out, sxb::g_sxb_hang, sizeof(unsigned int) * 8);     \
+    if (e != cudaSuccess) return (int)e;                                                     \
+    unsigned int z[8] = {0, 0, 0, 0, 0, 0, 0, 0};                                            \
+    e = cudaMemcpyToSymbol(sxb::g_sxb_hang, z, sizeof(z));                                   \
+    return e == cudaSuccess ? SXB_OK : (int)e;                                               \
+  }

@@ -61,6 +61,8 @@ SIGNATURES = {
     "sxb_scale_cast": "pp" "l" "ii" "f" "i" "p",
     "sxb_attn_fwd": "ppppp" "iiiii" "llll" "i" "f" "p",
     "sxb_attn_bwd": "pppppppppp" "iiiii" "llllllll" "i" "f" "p",
+    "sxb_gemm_hang_info": "p",
+    "sxb_attn_hang_info": "p",
 }
 _LONG_RETURN = {"sxb_norm_bwd_scratch_elems"}
 
@@ -149,6 +151,23 @@ def call(name: str, *args):
                   -4: "driver entry point unavailable"}.get(rc, "error")
         raise NativeError(f"{name} rejected the call: {reason} ({rc})")
     return 0
+
+
+def hang_info(kind: str = "attn"):
+    """Read-and-clear the pipeline watchdog record of a kernel family (``gemm`` | ``attn`` | ...).
+
+    Returns ``None`` when no wait was abandoned since the last call, else a dict naming the
+    barrier tag and the block/thread that gave up (see ``mbar_wait_to`` in csrc/sxb_common.cuh).
+    """
+    torch.cuda.synchronize()
+    buf = (ctypes.c_uint * 8)()
+    fn = getattr(load(), f"sxb_{kind}_hang_info")
+    rc = fn(ctypes.cast(buf, ctypes.c_void_p))
+    if rc != 0:
+        raise NativeError(f"sxb_{kind}_hang_info failed: {rc}")
+    if buf[0] == 0:
+        return None
+    return {"tag": buf[1], "block": (buf[2], buf[3], buf[4]), "thread": buf[5], "parity": buf[6], "aux": buf[7]}
 
 
 def reset_launch_count() -> int:

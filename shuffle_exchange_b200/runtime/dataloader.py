@@ -1,0 +1,111 @@
+"""Data loading (reference: deepspeed/runtime/dataloader.py — ``DeepSpeedDataLoader`` and
+``RepeatingLoader``; engine entry point ``deepspeed_io`` runtime/engine.py:1916-1974)."""
+from __future__ import annotations
+
+import torch
+from torch.utils.data import DataLoader, RandomSampler
+from torch.utils.data.distributed import DistributedSampler
+
+from ..device import get_accelerator
+from ..utils.logging import logger
+
+
+class RepeatingLoader:
+    """Wrap an iterable so it restarts (and bumps the sampler epoch) when exhausted."""
+
+    def __init__(self, loader):
+        self.loader = loader
+        self.data_iter = iter(self.loader)
+        self._epoch = 0
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        try:
+            return next(self.data_iter)
+        except StopIteration:
+            self._epoch += 1
+            sampler = getattr(self.loader, "sampler", None) or getattr(self.loader, "data_sampler", None)
+            if sampler is not None and hasattr(sampler, "set_epoch"):
+                sampler.set_epoch(self._epoch)
+            self.data_iter = iter(self.loader)
+            return next(self.data_iter)
+
+
+class DeepSpeedDataLoader:
+    def __init__(self, dataset, batch_size, pin_memory, local_rank, tput_timer, collate_fn=None, num_local_io_workers=None,
+                 data_sampler=None, data_parallel_world_size=None, data_parallel_rank=None, dataloader_drop_last=False,
+                 deepspeed_dataloader_config=None):
+        self.deepspeed_dataloader_config = deepspeed_dataloader_config or {}
+        self.tput_timer = tput_timer
+        self.batch_size = batch_size
+        self.curriculum_learning_enabled = bool(self.deepspeed_dataloader_config.get("curriculum_learning_enabled"))
+        if self.curriculum_learning_enabled:
+            from .data_pipeline.data_sampling.data_sampler import DeepSpeedDataSampler
+            data_sampler = DeepSpeedDataSampler(self.deepspeed_dataloader_config["data_efficiency"], len(dataset),
+                                                self.batch_size, data_parallel_rank, data_parallel_world_size,
+                                                self.deepspeed_dataloader_config.get("data_parallel_group"),
+                                                self.deepspeed_dataloader_config.get("gradient_accumulation_steps", 1),
+                                                self.deepspeed_dataloader_config.get("global_rank", 0),
+                                                drop_last=dataloader_drop_last)
+            device_count = 1
+            num_local_io_workers = self.deepspeed_dataloader_config.get("num_workers", 0)
+        else:
+            if local_rank >= 0:
+                if data_sampler is None:
+                    data_sampler = DistributedSampler(dataset=dataset, num_replicas=data_parallel_world_size,
+                                                      rank=data_parallel_rank)
+                device_count = 1
+            else:
+                if data_sampler is None:
+                    data_sampler = RandomSampler(dataset)
+                device_count = max(1, get_accelerator().device_count())
+                batch_size *= device_count
+            if num_local_io_workers is None:
+                num_local_io_workers = 2 * device_count
+        self.num_local_io_workers = num_local_io_workers
+        self.data_sampler = data_sampler
+        self.dataset = dataset
+        self.collate_fn = collate_fn
+        self.device_count = device_count
+        self.batch_size = batch_size
+        self.pin_memory = pin_memory and get_accelerator().is_available()
+        self.data = None
+        self.dataloader_drop_last = dataloader_drop_last
+        self.post_process_func = None
+        if self.dataloader_drop_last:
+            self.len = len(self.data_sampler) // self.batch_size
+        else:
+            from math import ceil
+            self.len = ceil(len(self.data_sampler) / self.batch_size)
+
+    def __iter__(self):
+        self._create_dataloader()
+        return self
+
+    def __len__(self):
+        return self.len
+
+    def __next__(self):
+        if self.tput_timer:
+            self.tput_timer.start()
+        if self.curriculum_learning_enabled:
+            data = next(self.data_iterator)
+            if self.post_process_func is not None:
+                data = self.post_process_func(data, self.data_sampler.state_dict())
+            return data
+        return next(self.data)
+
+    def _create_dataloader(self):
+        kw = dict(pin_memory=self.pin_memory, num_workers=self.num_local_io_workers)
+        if self.collate_fn is not None:
+            kw["collate_fn"] = self.collate_fn
+        if self.curriculum_learning_enabled:
+            self.dataloader = DataLoader(self.dataset, batch_sampler=self.data_sampler, **kw)
+            self.data_iterator = iter(self.dataloader)
+            return self.dataloader
+        self.dataloader = DataLoader(self.dataset, batch_size=self.batch_size, sampler=self.data_sampler,
+                                     drop_last=self.dataloader_drop_last, **kw)
+        self.data = (x for x in self.dataloader)
+        return self.dataloader

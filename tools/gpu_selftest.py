@@ -147,7 +147,7 @@ def _():
         (y.float() * gy.float()).sum().add((h.float() * gh.float()).sum()).backward()
         xr, rr, wr = (t.detach().float().requires_grad_() for t in (x, r, w))
         hr = xr + rr
-        hr_q = hr.to(torch.bfloat16).float() + (hr - hr.detach())  # straight-through the bf16 rounding
+        hr_q = hr + (hr.to(torch.bfloat16).float() - hr).detach()  # straight-through the bf16 rounding
         yr = hr_q * torch.rsqrt(hr_q.pow(2).mean(-1, keepdim=True) + 1e-5) * wr
         ((yr * gy.float()).sum() + (hr * gh.float()).sum()).backward()
         errs[H] = {"y": _rel_err(y, yr), "dx": _rel_err(x.grad, xr.grad), "dr": _rel_err(r.grad, rr.grad),
@@ -278,9 +278,7 @@ def _():
         n.call("sxb_adam_flat", p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), lp.data_ptr(), N4,
                n.BF16, n.BF16, 1e-2, 0.9, 0.95, 1e-8, 0.1, step, 1, 1, 1.0, None, None, n.stream_ptr())
     torch.cuda.synchronize()
-    ms = _time(lambda: n.call("sxb_adam_flat", p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(),
-                              lp.data_ptr(), N4, n.BF16, n.BF16, 1e-2, 0.9, 0.95, 1e-8, 0.1, 4, 1, 1, 1.0,
-                              None, None, n.stream_ptr()))
+    err = max(_rel_err(p, pr.detach()), _rel_err(lp, pr.detach()))
     big = 1 << 28
     P = torch.randn(big, device="cuda"); G = torch.randn(big, device="cuda").to(torch.bfloat16)
     Mm = torch.zeros(big, device="cuda"); Vv = torch.zeros(big, device="cuda")
@@ -289,7 +287,7 @@ def _():
                                   LP.data_ptr(), big, n.BF16, n.BF16, 1e-2, 0.9, 0.95, 1e-8, 0.1, 4, 1, 1,
                                   1.0, None, None, n.stream_ptr()), iters=5)
     gbs = big * (4 * 3 * 2 + 2 + 2) / ms_big / 1e6
-    return {"err": max(_rel_err(p, pr.detach()), _rel_err(lp, pr.detach())), "adam_268M_ms": ms_big,
+    return {"err": err, "adam_268M_ms": ms_big,
             "adam_GBps": gbs}
 
 
@@ -302,7 +300,11 @@ def _attn_case(B, S, Hq, Hk, D, causal, bwd=True):
     q = qkv[..., : Hq * D].view(B, S, Hq, D)
     k = qkv[..., Hq * D: (Hq + Hk) * D].view(B, S, Hk, D)
     v = qkv[..., (Hq + Hk) * D:].view(B, S, Hk, D)
+    from shuffle_exchange_b200.native import lib as n
     out = F.flash_attention(q, k, v, causal)
+    hi = n.hang_info("attn")
+    if hi is not None:
+        return {"hang_fwd": hi}
     qr = qkv.detach().float().requires_grad_()
     q2 = qr[..., : Hq * D].view(B, S, Hq, D)
     k2 = qr[..., Hq * D: (Hq + Hk) * D].view(B, S, Hk, D)
@@ -312,6 +314,9 @@ def _attn_case(B, S, Hq, Hk, D, causal, bwd=True):
     if bwd:
         g = torch.randn_like(out)
         out.backward(g)
+        hi = n.hang_info("attn")
+        if hi is not None:
+            return {"hang_bwd": hi}
         ref.backward(g.float())
         dq, dqr = qkv.grad[..., : Hq * D], qr.grad[..., : Hq * D]
         dk, dkr = qkv.grad[..., Hq * D: (Hq + Hk) * D], qr.grad[..., Hq * D: (Hq + Hk) * D]
@@ -320,30 +325,30 @@ def _attn_case(B, S, Hq, Hk, D, causal, bwd=True):
     return res
 
 
-@check("attn_fwd_small")
-def _():
-    r = _attn_case(1, 128, 1, 1, 128, False, bwd=False)
-    return {"err": max(r.values()), "detail": r}
+def _attn_sweep(cfgs, bwd):
+    out = {}
+    worst = 0.0
+    for cfg in cfgs:
+        r = _attn_case(*cfg, bwd=bwd)
+        out[str(cfg)] = r
+        for v in r.values():
+            worst = max(worst, v if isinstance(v, float) else 1e9)
+    return {"err": worst, "detail": out}
+
+
+_ATTN_CFGS = [(1, 128, 1, 1, 128, False), (1, 256, 1, 1, 128, True), (2, 256, 1, 1, 128, True),
+              (1, 512, 4, 2, 128, True), (2, 512, 4, 2, 128, True), (1, 1024, 2, 1, 128, False),
+              (1, 300, 2, 1, 128, True), (1, 128, 1, 1, 64, False), (1, 384, 2, 2, 64, True)]
 
 
 @check("attn_fwd")
 def _():
-    rs = [_attn_case(2, 512, 4, 2, 128, True, bwd=False), _attn_case(1, 384, 2, 2, 64, True, bwd=False),
-          _attn_case(1, 300, 2, 1, 128, True, bwd=False), _attn_case(1, 1024, 2, 1, 128, False, bwd=False)]
-    return {"err": max(v for r in rs for v in r.values()), "detail": rs}
-
-
-@check("attn_bwd_small")
-def _():
-    r = _attn_case(1, 128, 1, 1, 128, False)
-    return {"err": max(r.values()), "detail": r}
+    return _attn_sweep(_ATTN_CFGS, False)
 
 
 @check("attn_bwd")
 def _():
-    rs = [_attn_case(2, 512, 4, 2, 128, True), _attn_case(1, 384, 2, 2, 64, True),
-          _attn_case(1, 300, 2, 1, 128, True)]
-    return {"err": max(v for r in rs for v in r.values()), "detail": rs}
+    return _attn_sweep(_ATTN_CFGS, True)
 
 
 @check("attn_perf")
@@ -370,6 +375,64 @@ def _():
             "bwd_tflops": 2.5 * flops / ms_b / 1e9, "sdpa_fwd_ms": ms_sf, "sdpa_bwd_ms": ms_sb}
 
 
+@check("llama_tiny")
+def _():
+    import torch
+    from shuffle_exchange_b200.models.llama import LlamaForCausalLM, llama_config, reference_forward
+    from shuffle_exchange_b200.native import lib as n
+    torch.manual_seed(0)
+    out = {}
+    for name, kw in (("d64", {}), ("d128", dict(hidden_size=512, num_attention_heads=4, num_key_value_heads=2))):
+        cfg = llama_config("llama-tiny", **kw)
+        m = LlamaForCausalLM(cfg).to("cuda", torch.bfloat16).train()
+        ids = torch.randint(0, cfg.vocab_size, (2, 256), device="cuda")
+        loss = m(ids, labels=ids)
+        loss.backward()
+        hi = n.hang_info("attn") or n.hang_info("gemm")
+        if hi:
+            return {"ok": False, "hang": hi}
+        mr = LlamaForCausalLM(cfg).to("cuda", torch.float32)
+        mr.load_state_dict({k: v.float() for k, v in m.state_dict().items()})
+        mr.cfg.activation_checkpointing = False
+        # autograd through the fp32 oracle
+        params = {k: v.detach().clone().requires_grad_() for k, v in mr.state_dict().items()}
+        mr.load_state_dict(params, strict=True)
+        for k, v in mr.named_parameters():
+            v.requires_grad_()
+        import torch.nn.functional as TF
+        from shuffle_exchange_b200.ops import functional as F
+        # run the composite (CPU-path) implementation on GPU tensors by calling the reference pieces
+        lref = reference_forward(mr, ids, ids)
+        out[name] = {"loss": loss.item(), "ref": lref.item(), "rel": abs(loss.item() - lref.item()) / abs(lref.item())}
+    return {"err": max(v["rel"] for v in out.values()), "detail": out}
+
+
+@check("llama_layer_perf")
+def _():
+    import torch
+    from shuffle_exchange_b200.models.llama import LlamaDecoderLayer, llama_config
+    from shuffle_exchange_b200.ops import functional as F
+    cfg = llama_config("llama3-8b")
+    layer = LlamaDecoderLayer(cfg, 0, device="cuda", dtype=torch.bfloat16)
+    layer.reset_parameters(0.02)
+    B, S = 1, 8192
+    h = torch.randn(B, S, cfg.hidden_size, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+    res = torch.randn(B, S, cfg.hidden_size, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+    pos = torch.arange(S, device="cuda").repeat(B)
+    cos, sin = F.rope_tables(S, cfg.head_dim, cfg.rope_theta, "cuda")
+
+    def fwd():
+        with torch.no_grad():
+            return layer(h, res, pos, cos, sin)
+
+    def fwdbwd():
+        o, r = layer(h, res, pos, cos, sin)
+        (o.float().mean() + r.float().mean()).backward()
+    ms_f = _time(fwd, iters=5)
+    ms_fb = _time(fwdbwd, iters=5)
+    return {"fwd_ms": ms_f, "fwd_bwd_ms": ms_fb, "est_step_ms_32_layers_recompute": 32 * (ms_f + ms_fb)}
+
+
 def main():
     if len(sys.argv) >= 3 and sys.argv[1] == "--one":
         name = sys.argv[2]
@@ -390,7 +453,7 @@ def main():
         t0 = time.time()
         try:
             r = subprocess.run([sys.executable, __file__, "--one", name], capture_output=True, text=True,
-                               timeout=180)
+                               timeout=120)
             line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")]
             if line:
                 results[name] = json.loads(line[-1][7:])
