@@ -211,34 +211,34 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       ld_row64(tS + (j & 1) * BC + lane_off, s);
       const int k0 = j * BC;
       const bool need_mask = (p.causal && (k0 + BC - 1 > q0)) || (k0 + BC > p.S);
-      float mx = -INFINITY;
+      // row max on raw scores (scale > 0 commutes with max); 4 independent chains
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
       if (need_mask) {
 #pragma unroll
         for (int c = 0; c < 64; ++c) {
           const int kp = k0 + c;
           const bool ok = (kp < p.S) && (!p.causal || kp <= qpos);
-          s[c] = ok ? s[c] * sc : -INFINITY;
-          mx = fmaxf(mx, s[c]);
+          s[c] = ok ? s[c] : -INFINITY;
+          mx4[c & 3] = fmaxf(mx4[c & 3], s[c]);
         }
       } else {
 #pragma unroll
-        for (int c = 0; c < 64; ++c) {
-          s[c] *= sc;
-          mx = fmaxf(mx, s[c]);
-        }
+        for (int c = 0; c < 64; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], s[c]);
       }
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sc;
       // Lazy rescale: keep the running max stale unless it grew by more than 2^8.
       float m_new = m_run;
       const bool grow = mx > m_run + 8.f;
       const bool any_grow = __any_sync(0xffffffffu, grow) != 0;
       if (any_grow) m_new = fmaxf(m_run, mx);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      float rs = 0.f;
+      float rs4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int c = 0; c < 64; ++c) {
-        s[c] = fast_exp2(s[c] - m_use);
-        rs += s[c];
+        s[c] = fast_exp2(fmaf(s[c], sc, -m_use));
+        rs4[c & 3] += s[c];
       }
+      const float rs = (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
       if (j > 0) {
         if (!mbar_wait_to(o_done, (j - 1) & 1, 25)) goto done;
         tc_fence_after();
@@ -267,35 +267,32 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (!mbar_wait_to(o_done, (nblk - 1) & 1, 26)) goto done;
     tc_fence_after();
     const float inv_l = (l_run > 0.f) ? 1.f / l_run : 0.f;
-    if (qpos < p.S) {
+    {
+      // tcgen05.ld is warp-collective (.sync.aligned): every lane issues it, only the global
+      // stores are predicated on the row being inside the sequence.
+      const bool valid = qpos < p.S;
       __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                            ((long long)b * p.S + qpos) * p.out_stride + (long long)h * D;
+                            ((long long)b * p.S + (valid ? qpos : 0)) * p.out_stride + (long long)h * D;
 #pragma unroll 1
       for (int c = 0; c < D / 32; ++c) {
         uint32_t o[32];
         tmem_ld_32x32(tO + lane_off + c * 32, o);
         tmem_ld_wait();
+        if (valid) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          uint4 w;
-          w.x = pack_bf16(__uint_as_float(o[i * 8 + 0]) * inv_l, __uint_as_float(o[i * 8 + 1]) * inv_l);
-          w.y = pack_bf16(__uint_as_float(o[i * 8 + 2]) * inv_l, __uint_as_float(o[i * 8 + 3]) * inv_l);
-          w.z = pack_bf16(__uint_as_float(o[i * 8 + 4]) * inv_l, __uint_as_float(o[i * 8 + 5]) * inv_l);
-          w.w = pack_bf16(__uint_as_float(o[i * 8 + 6]) * inv_l, __uint_as_float(o[i * 8 + 7]) * inv_l);
-          *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = w;
+          for (int i = 0; i < 4; ++i) {
+            uint4 w;
+            w.x = pack_bf16(__uint_as_float(o[i * 8 + 0]) * inv_l, __uint_as_float(o[i * 8 + 1]) * inv_l);
+            w.y = pack_bf16(__uint_as_float(o[i * 8 + 2]) * inv_l, __uint_as_float(o[i * 8 + 3]) * inv_l);
+            w.z = pack_bf16(__uint_as_float(o[i * 8 + 4]) * inv_l, __uint_as_float(o[i * 8 + 5]) * inv_l);
+            w.w = pack_bf16(__uint_as_float(o[i * 8 + 6]) * inv_l, __uint_as_float(o[i * 8 + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = w;
+          }
         }
       }
-      if (p.lse)
+      if (valid && p.lse)
         p.lse[((long long)b * p.Hq + h) * p.S + qpos] =
             (l_run > 0.f) ? (m_run + log2f(l_run)) * kLn2 : -INFINITY;
-    } else {
-      // keep the warp-collective tcgen05.ld pattern uniform
-#pragma unroll 1
-      for (int c = 0; c < D / 32; ++c) {
-        uint32_t o[32];
-        tmem_ld_32x32(tO + lane_off + c * 32, o);
-        tmem_ld_wait();
-      }
     }
   }
 done:

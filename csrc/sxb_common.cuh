@@ -384,9 +384,8 @@ __device__ __forceinline__ unsigned long long global_ns() {
 }
 static __device__ __noinline__ bool mbar_wait_slow(uint64_t* bar, uint32_t parity, uint32_t tag, uint32_t aux) {
   const unsigned long long t0 = global_ns();
-  uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 0x3F) == 0) {
+    {
       if (*reinterpret_cast<volatile unsigned int*>(&g_sxb_hang[0]) != 0) return false;
       if (global_ns() - t0 > 2000000000ull) {
         if (atomicCAS(&g_sxb_hang[0], 0u, 1u) == 0u) {

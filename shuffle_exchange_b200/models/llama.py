@@ -107,7 +107,7 @@ class LlamaDecoderLayer(nn.Module):
         x, residual = F.rms_norm(h, self.input_layernorm, eps, residual)
         qkv = F.linear(x, self.wqkv)
         C = qkv.shape[-1]
-        qkv = F.rope(qkv.view(B * S, C), positions, cos, sin, self.n_q + self.n_kv, self.d).view(B, S, C)
+        qkv = F.rope(qkv, positions, cos, sin, self.n_q + self.n_kv, self.d)
         q = qkv[..., : self.n_q * self.d].view(B, S, self.n_q, self.d)
         k = qkv[..., self.n_q * self.d: (self.n_q + self.n_kv) * self.d].view(B, S, self.n_kv, self.d)
         v = qkv[..., (self.n_q + self.n_kv) * self.d:].view(B, S, self.n_kv, self.d)

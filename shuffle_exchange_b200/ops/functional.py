@@ -99,13 +99,16 @@ class _Linear(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias):
         x2 = x.reshape(-1, x.shape[-1])
-        y = gemm(x2, weight, GEMM_NT)
+        # allocate with the final shape so the returned tensor is not a view (in-place consumers
+        # such as RoPE may then modify it)
+        y = torch.empty((*x.shape[:-1], weight.shape[0]), dtype=x.dtype, device=x.device)
+        gemm(x2, weight, GEMM_NT, out=y.view(-1, weight.shape[0]))
         if bias is not None:
-            y = y + bias
+            y.add_(bias)
         ctx.save_for_backward(x2, weight)
         ctx.has_bias = bias is not None
         ctx.xshape = x.shape
-        return y.view(*x.shape[:-1], weight.shape[0])
+        return y
 
     @staticmethod
     def backward(ctx, dy):
@@ -313,8 +316,9 @@ class _Rope(torch.autograd.Function):
     def forward(ctx, x, positions, cos, sin, n_heads, head_dim):
         # x: [T, C] contiguous; rotates in place on a clone-free basis (x is marked dirty)
         ctx.mark_dirty(x)
-        _n.call("sxb_rope", x.data_ptr(), _n.ptr(positions), cos.data_ptr(), sin.data_ptr(), x.shape[0],
-                n_heads, head_dim, x.stride(0), 0, _n.dtype_code(x.dtype), _n.stream_ptr())
+        C = x.shape[-1]
+        _n.call("sxb_rope", x.data_ptr(), _n.ptr(positions), cos.data_ptr(), sin.data_ptr(), x.numel() // C,
+                n_heads, head_dim, C, 0, _n.dtype_code(x.dtype), _n.stream_ptr())
         ctx.save_for_backward(positions, cos, sin)
         ctx.nh, ctx.hd = n_heads, head_dim
         return x
@@ -323,18 +327,23 @@ class _Rope(torch.autograd.Function):
     def backward(ctx, dx):
         positions, cos, sin = ctx.saved_tensors
         dx = dx.clone(memory_format=torch.contiguous_format)  # never rotate autograd's buffer in place
-        _n.call("sxb_rope", dx.data_ptr(), _n.ptr(positions), cos.data_ptr(), sin.data_ptr(), dx.shape[0],
-                ctx.nh, ctx.hd, dx.stride(0), 1, _n.dtype_code(dx.dtype), _n.stream_ptr())
+        C = dx.shape[-1]
+        _n.call("sxb_rope", dx.data_ptr(), _n.ptr(positions), cos.data_ptr(), sin.data_ptr(), dx.numel() // C,
+                ctx.nh, ctx.hd, C, 1, _n.dtype_code(dx.dtype), _n.stream_ptr())
         return dx, None, None, None, None, None
 
 
 def rope(x: torch.Tensor, positions: Optional[torch.Tensor], cos: torch.Tensor, sin: torch.Tensor,
          n_heads: int, head_dim: int) -> torch.Tensor:
-    """Rotate the first ``n_heads`` heads of every row of ``x`` ([T, C]); in place on CUDA."""
+    """Rotate the first ``n_heads`` heads of every row of ``x`` ([..., C], contiguous); in place on CUDA."""
     if x.is_cuda:
+        if not x.is_contiguous():
+            x = x.contiguous()
         return _Rope.apply(x, positions, cos, sin, n_heads, head_dim)
-    pos = positions if positions is not None else torch.arange(x.shape[0])
-    return rope_ref(x, pos, cos, sin, n_heads, head_dim)
+    shape = x.shape
+    x2 = x.reshape(-1, shape[-1])
+    pos = positions if positions is not None else torch.arange(x2.shape[0])
+    return rope_ref(x2, pos, cos, sin, n_heads, head_dim).view(shape)
 
 
 # ------------------------------------------------------------------- gated activations

@@ -1,0 +1,215 @@
+"""Safe access to full fp32 parameters / gradients / optimizer state under any sharding.
+
+User-visible functions of the reference (deepspeed/utils/tensor_fragment.py:134-371):
+``safe_get/set_full_fp32_param``, ``safe_get/set_full_grad``, ``safe_get/set_full_optimizer_state``,
+``safe_get/set_local_fp32_param``, ``safe_get/set_local_grad``, ``safe_get/set_local_optimizer_state``,
+``safe_update_full_grad_vectorized``.  The reference keeps a per-parameter ``_hp_mapping`` fragment
+record (:19-70, :373-481); with FlatGroup storage a parameter's master fragment is simply the
+intersection of its range with this rank's partition, so the mapping is two integers and all
+functions reduce to "scatter my fragment into a zero buffer, all-reduce over the sharding group".
+All functions are collective over the group that shards the parameter.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+
+from ..comm import comm as dist
+
+
+@dataclass
+class _Link:
+    group: object        # FlatGroup
+    index: int           # position of the parameter inside the group
+    optimizer: object    # owning sharded optimizer
+
+
+def link_group_params(fg, optimizer):
+    for i, p in enumerate(fg.params):
+        p._sxb_link = _Link(fg, i, optimizer)
+        p._hp_mapping = p._sxb_link    # name the reference uses; truthiness is what callers test
+
+
+def _link(param) -> Optional[_Link]:
+    return getattr(param, "_sxb_link", None)
+
+
+def _assemble(param, source: torch.Tensor, dtype=torch.float32) -> torch.Tensor:
+    """Full tensor of ``param`` from a per-rank shard-shaped ``source`` (collective)."""
+    lk = _link(param)
+    fg = lk.group
+    shape = fg.shapes[lk.index]
+    n = fg.numels[lk.index]
+    dev = fg.device
+    full = torch.zeros(n, dtype=dtype, device=dev)
+    r = fg.shard_range_of_param(lk.index)
+    if r is not None and source is not None:
+        p_off, s_off, cnt = r
+        full[p_off: p_off + cnt] = source[s_off: s_off + cnt].to(device=dev, dtype=dtype)
+    if fg.world > 1:
+        dist.all_reduce(full, group=fg.pg)
+    return full.view(shape)
+
+
+def _scatter_into(param, value: torch.Tensor, target: torch.Tensor):
+    lk = _link(param)
+    fg = lk.group
+    r = fg.shard_range_of_param(lk.index)
+    if r is None:
+        return
+    p_off, s_off, cnt = r
+    flat = value.reshape(-1)
+    target[s_off: s_off + cnt].copy_(flat[p_off: p_off + cnt].to(device=target.device, dtype=target.dtype))
+
+
+# ------------------------------------------------------------------------------------ full API
+def safe_get_full_fp32_param(param):
+    """fp32 master value of ``param`` (assembled across ranks), or None if it has no master copy."""
+    lk = _link(param)
+    if lk is None:
+        return param.detach().float() if param.numel() > 0 else None
+    return _assemble(param, lk.group.hp_param.data)
+
+
+def safe_set_full_fp32_param(param, value):
+    lk = _link(param)
+    if lk is None:
+        param.data.copy_(value.to(param.dtype))
+        return
+    fg = lk.group
+    _scatter_into(param, value, fg.hp_param.data)
+    _scatter_into(param, value, fg.lp_shard)
+    if fg.flat_lp is not None:
+        off = fg.offsets[lk.index]
+        fg.flat_lp[off: off + fg.numels[lk.index]].copy_(value.reshape(-1).to(fg.flat_lp.dtype))
+
+
+def safe_get_full_optimizer_state(param, optim_state_key):
+    lk = _link(param)
+    if lk is None:
+        return None
+    st = lk.optimizer._optimizer_state_for(lk.group)
+    if optim_state_key not in st or not torch.is_tensor(st[optim_state_key]):
+        return None
+    return _assemble(param, st[optim_state_key])
+
+
+def safe_set_full_optimizer_state(param, value, optim_state_key):
+    lk = _link(param)
+    if lk is None:
+        return
+    st = lk.optimizer._optimizer_state_for(lk.group)
+    if optim_state_key not in st:
+        st[optim_state_key] = torch.zeros_like(lk.group.hp_param.data)
+    _scatter_into(param, value, st[optim_state_key])
+
+
+def safe_get_full_grad(param):
+    """Gradient of ``param`` as the optimizer will see it (after reduction) — fp32."""
+    if param.grad is not None:
+        return param.grad.float()
+    lk = _link(param)
+    if lk is None:
+        return None
+    fg = lk.group
+    if fg.grad_shard is not None:
+        return _assemble(param, fg.grad_shard)
+    if fg.flat_grad is not None:
+        off = fg.offsets[lk.index]
+        return fg.flat_grad[off: off + fg.numels[lk.index]].float().view(fg.shapes[lk.index])
+    return None
+
+
+def safe_set_full_grad(param, value):
+    lk = _link(param)
+    if lk is None:
+        param.grad = value.to(param.dtype)
+        return
+    fg = lk.group
+    if fg.grad_shard is not None:
+        _scatter_into(param, value, fg.grad_shard)
+    if fg.flat_grad is not None:
+        off = fg.offsets[lk.index]
+        fg.flat_grad[off: off + fg.numels[lk.index]].copy_(value.reshape(-1).to(fg.flat_grad.dtype))
+
+
+def safe_update_full_grad_vectorized(param_list: List[torch.nn.Parameter], update_func):
+    """``update_func(full_grad, param) -> new_full_grad`` applied to each parameter's gradient."""
+    for p in param_list:
+        g = safe_get_full_grad(p)
+        if g is None:
+            continue
+        safe_set_full_grad(p, update_func(g, p))
+
+
+# ----------------------------------------------------------------------------------- local API
+def _local_view(param, source):
+    lk = _link(param)
+    r = lk.group.shard_range_of_param(lk.index)
+    if r is None or source is None:
+        return None
+    _, s_off, cnt = r
+    return source[s_off: s_off + cnt]
+
+
+def safe_get_local_fp32_param(param):
+    lk = _link(param)
+    return None if lk is None else _local_view(param, lk.group.hp_param.data)
+
+
+def safe_set_local_fp32_param(param, value):
+    v = safe_get_local_fp32_param(param)
+    if v is not None:
+        v.copy_(value.reshape(-1).to(v.dtype))
+        lv = _local_view(param, _link(param).group.lp_shard)
+        lv.copy_(value.reshape(-1).to(lv.dtype))
+
+
+def safe_get_local_grad(param):
+    lk = _link(param)
+    if lk is None or lk.group.grad_shard is None:
+        return None
+    v = _local_view(param, lk.group.grad_shard)
+    return None if v is None else v.float()
+
+
+def safe_set_local_grad(param, value):
+    lk = _link(param)
+    if lk is None or lk.group.grad_shard is None:
+        return
+    v = _local_view(param, lk.group.grad_shard)
+    if v is not None:
+        v.copy_(value.reshape(-1).to(v.dtype))
+
+
+def safe_get_local_optimizer_state(param, optim_state_key):
+    lk = _link(param)
+    if lk is None:
+        return None
+    st = lk.optimizer._optimizer_state_for(lk.group)
+    return _local_view(param, st.get(optim_state_key))
+
+
+def safe_set_local_optimizer_state(param, value, optim_state_key):
+    v = safe_get_local_optimizer_state(param, optim_state_key)
+    if v is not None:
+        v.copy_(value.reshape(-1).to(v.dtype))
+
+
+# reference-name aliases used by checkpoint tooling
+def get_hp_fragment_mapping(param):
+    return _link(param)
+
+
+def get_full_hp_param(self, optim_state_key=None):
+    if optim_state_key is None:
+        return safe_get_full_fp32_param(self)
+    return safe_get_full_optimizer_state(self, optim_state_key)
+
+
+def set_full_hp_param(self, value, optim_state_key=None):
+    if optim_state_key is None:
+        return safe_set_full_fp32_param(self, value)
+    return safe_set_full_optimizer_state(self, value, optim_state_key)

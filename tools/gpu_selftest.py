@@ -329,7 +329,9 @@ def _attn_sweep(cfgs, bwd):
     out = {}
     worst = 0.0
     for cfg in cfgs:
+        print("CFG", cfg, flush=True)
         r = _attn_case(*cfg, bwd=bwd)
+        print("  ->", r, flush=True)
         out[str(cfg)] = r
         for v in r.values():
             worst = max(worst, v if isinstance(v, float) else 1e9)
@@ -341,14 +343,20 @@ _ATTN_CFGS = [(1, 128, 1, 1, 128, False), (1, 256, 1, 1, 128, True), (2, 256, 1,
               (1, 300, 2, 1, 128, True), (1, 128, 1, 1, 64, False), (1, 384, 2, 2, 64, True)]
 
 
-@check("attn_fwd")
-def _():
-    return _attn_sweep(_ATTN_CFGS, False)
+def _mk_attn_check(cfg, bwd):
+    def f():
+        r = _attn_case(*cfg, bwd=bwd)
+        worst = max((v if isinstance(v, float) else 1e9) for v in r.values())
+        return {"err": worst, "detail": r}
+    return f
 
 
-@check("attn_bwd")
-def _():
-    return _attn_sweep(_ATTN_CFGS, True)
+for _cfg in _ATTN_CFGS:
+    _tag = "x".join(str(int(v)) for v in _cfg)
+    CHECKS[f"attn_fwd_{_tag}"] = _mk_attn_check(_cfg, False)
+for _cfg in _ATTN_CFGS:
+    _tag = "x".join(str(int(v)) for v in _cfg)
+    CHECKS[f"attn_bwd_{_tag}"] = _mk_attn_check(_cfg, True)
 
 
 @check("attn_perf")
@@ -436,6 +444,8 @@ def _():
 def main():
     if len(sys.argv) >= 3 and sys.argv[1] == "--one":
         name = sys.argv[2]
+        import faulthandler
+        faulthandler.dump_traceback_later(45, exit=False)
         import torch  # noqa
         try:
             res = CHECKS[name]()
@@ -453,7 +463,7 @@ def main():
         t0 = time.time()
         try:
             r = subprocess.run([sys.executable, __file__, "--one", name], capture_output=True, text=True,
-                               timeout=120)
+                               timeout=60)
             line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")]
             if line:
                 results[name] = json.loads(line[-1][7:])
@@ -462,8 +472,10 @@ def main():
                                  "tail": (r.stdout + r.stderr)[-800:]}
             if not results[name].get("ok"):
                 results[name]["tail"] = (r.stdout + r.stderr)[-1500:]
-        except subprocess.TimeoutExpired:
-            results[name] = {"ok": False, "error": "timeout (hang?)"}
+        except subprocess.TimeoutExpired as e:
+            def _s(b):
+                return (b.decode(errors="replace") if isinstance(b, bytes) else (b or ""))[-1800:]
+            results[name] = {"ok": False, "error": "timeout (hang?)", "stdout": _s(e.stdout), "stderr": _s(e.stderr)}
         results[name]["secs"] = round(time.time() - t0, 1)
         err = results[name].get("err")
         tol = 2e-2
