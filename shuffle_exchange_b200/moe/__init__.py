@@ -1,0 +1,1 @@
+from .layer import MoE  # noqa: F401

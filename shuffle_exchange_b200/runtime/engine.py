@@ -1,0 +1,1086 @@
+"""DeepSpeedEngine — the training engine returned by :func:`shuffle_exchange_b200.initialize`.
+
+API and behaviour follow the reference engine (deepspeed/runtime/engine.py, 4089 lines: init order
+:216-411, optimizer selection :1368-1569 / :1687-1838, ``forward/backward/step`` :2103/:2270/:2404,
+non-ZeRO gradient all-reduce :2616-2824, checkpoint save/load :2826-3959, config accessors :633-1089)
+with the device abstraction, op-builder and hook archaeology removed: one CUDA device helper, one
+native library, and sharded optimizers built on :class:`FlatGroup`.
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+import re
+from collections import OrderedDict, defaultdict
+from typing import Callable, Dict, Iterable, Optional
+
+import torch
+import torch.nn as nn
+from torch.optim import Optimizer
+from torch.optim.lr_scheduler import _LRScheduler
+
+from .. import comm as dist
+from ..device import get_accelerator
+from ..monitor.monitor import MonitorMaster
+from ..utils import groups
+from ..utils.logging import log_dist, logger
+from ..utils.timer import (BACKWARD_GLOBAL_TIMER, BACKWARD_INNER_GLOBAL_TIMER, BACKWARD_INNER_MICRO_TIMER,
+                           BACKWARD_MICRO_TIMER, BACKWARD_REDUCE_GLOBAL_TIMER, BACKWARD_REDUCE_MICRO_TIMER,
+                           FORWARD_GLOBAL_TIMER, FORWARD_MICRO_TIMER, STEP_GLOBAL_TIMER, STEP_MICRO_TIMER, NoopTimer,
+                           SynchronizedWallClockTimer, ThroughputTimer)
+from ..version import __version__
+from . import lr_schedules
+from .config import (ADAGRAD_OPTIMIZER, ADAM_OPTIMIZER, ADAMW_OPTIMIZER, DEEPSPEED_OPTIMIZERS, LAMB_OPTIMIZER,
+                     LION_OPTIMIZER, MUADAM_OPTIMIZER, MUADAMW_OPTIMIZER, MUSGD_OPTIMIZER, ONEBIT_ADAM_OPTIMIZER,
+                     ONEBIT_LAMB_OPTIMIZER, SGD_OPTIMIZER, TORCH_ADAM_PARAM, ADAM_W_MODE, ADAM_W_MODE_DEFAULT,
+                     ZERO_ONE_ADAM_OPTIMIZER, DeepSpeedConfig)
+from .dataloader import DeepSpeedDataLoader
+from .zero.config import ZeroStageEnum
+
+MEMORY_OPT_ALLREDUCE_SIZE = 500000000
+DeepSpeedOptimizerCallable = Callable[[Iterable], Optimizer]
+DeepSpeedSchedulerCallable = Callable[[Optimizer], _LRScheduler]
+
+
+class EngineTimers:
+    """Names of the wall-clock timers the engine drives (reference: engine.py:160-192)."""
+
+    def __init__(self, enable_micro_timers, enable_global_timers):
+        self.forward_timers = []
+        self.backward_timers = []
+        self.backward_inner_timers = []
+        self.backward_reduce_timers = []
+        self.step_timers = []
+        self.global_timers = []
+        self.micro_timers = []
+        if enable_micro_timers:
+            self.forward_timers += [FORWARD_MICRO_TIMER]
+            self.backward_timers += [BACKWARD_MICRO_TIMER]
+            self.backward_inner_timers += [BACKWARD_INNER_MICRO_TIMER]
+            self.backward_reduce_timers += [BACKWARD_REDUCE_MICRO_TIMER]
+            self.step_timers += [STEP_MICRO_TIMER]
+            self.micro_timers += [FORWARD_MICRO_TIMER, BACKWARD_MICRO_TIMER, BACKWARD_INNER_MICRO_TIMER,
+                                  BACKWARD_REDUCE_MICRO_TIMER, STEP_MICRO_TIMER]
+        if enable_global_timers:
+            self.forward_timers += [FORWARD_GLOBAL_TIMER]
+            self.backward_timers += [BACKWARD_GLOBAL_TIMER]
+            self.backward_inner_timers += [BACKWARD_INNER_GLOBAL_TIMER]
+            self.backward_reduce_timers += [BACKWARD_REDUCE_GLOBAL_TIMER]
+            self.step_timers += [STEP_GLOBAL_TIMER]
+            self.global_timers += [FORWARD_GLOBAL_TIMER, BACKWARD_GLOBAL_TIMER, BACKWARD_INNER_GLOBAL_TIMER,
+                                   BACKWARD_REDUCE_GLOBAL_TIMER, STEP_GLOBAL_TIMER]
+
+
+def _cfg_accessor(path, attr=None):
+    def get(self):
+        obj = self._config
+        for part in path.split("."):
+            obj = getattr(obj, part)
+        return obj
+    return get
+
+
+class DeepSpeedEngine(nn.Module):
+    def __init__(self, args=None, model=None, optimizer=None, model_parameters=None, training_data=None,
+                 lr_scheduler=None, mpu=None, dist_init_required=None, collate_fn=None, config=None,
+                 config_class=None, mesh_device=None, dont_change_device=False,
+                 rings=8, shuffle_step=50, method="RR", slice_count=2):
+        super().__init__()
+        self.dont_change_device = dont_change_device
+        self.client_optimizer = optimizer
+        self.client_lr_scheduler = lr_scheduler
+        self.training_data = training_data
+        self.collate_fn = collate_fn
+        self.mpu = mpu
+        self.mesh_device = mesh_device
+        self.all_to_all_group = None
+        self.data_parallel_group = None
+        self.global_steps = 0
+        self.global_samples = 0
+        self.micro_steps = 0
+        self.skipped_steps = 0
+        self.gradient_average = True
+        self.warn_unscaled_loss = True
+        self.config = config
+        self._config = config_class
+        self.loaded_checkpoint_mp_world_size = None
+        self.loaded_checkpoint_dp_world_size = None
+        self.enable_backward_allreduce = True
+        self.inside_no_sync_ctxt = False
+        self.progressive_layer_drop = None
+        self.eigenvalue = None
+        self.block_eigenvalue = None
+        self.gas_boundary_ctr = 0
+        self.dist_backend = get_accelerator().communication_backend_name()
+        self.has_moe_layers = False
+        self.num_experts = []
+        self.gate_modules = []
+        self.moe_layers = []
+        self._step_applied = False
+        self._global_grad_norm = None
+        self.use_ds_comm = False
+        self.checkpoint_engine = None
+        self._is_gradient_accumulation_boundary = None
+        self.scale_wrt_gas = None
+        self.losses = None
+        self._rings, self._shuffle_step, self._method, self._slice_count = rings, shuffle_step, method, slice_count
+
+        self._do_args_sanity_check(args)
+        self._configure_with_arguments(args, mpu)
+        self._do_sanity_check()
+        if mpu is not None:
+            groups.mpu = mpu
+        if mesh_device is not None:
+            groups.mesh_device = mesh_device
+        self._set_distributed_vars(args)
+        dist.configure(self._config)
+        self.monitor = MonitorMaster(self._config.monitor_config)
+        self.pipeline_parallelism = isinstance(model, _pipeline_module_type())
+
+        self._configure_distributed_model(model)
+        self.param_names = {p: n for n, p in self.module.named_parameters()}
+
+        self.wall_clock_breakdown_ = self._config.wall_clock_breakdown
+        self.timers = SynchronizedWallClockTimer() if self.wall_clock_breakdown_ else NoopTimer()
+        self.engine_timers = EngineTimers(enable_micro_timers=self.wall_clock_breakdown_,
+                                          enable_global_timers=self.wall_clock_breakdown_ or self.flops_profiler_enabled())
+        self.tput_timer = ThroughputTimer(self._config.timers_config.throughput, batch_size=self.train_batch_size(),
+                                          steps_per_output=self.steps_per_print(),
+                                          monitor_memory=False)
+        if self.flops_profiler_enabled():
+            from ..profiling.flops_profiler import FlopsProfiler
+            self.flops_profiler = FlopsProfiler(self.module, self, self._config.flops_profiler_config.recompute_fwd_factor)
+
+        if training_data is not None:
+            self.training_dataloader = self.deepspeed_io(training_data)
+        else:
+            self.training_dataloader = None
+
+        self.optimizer = None
+        self.basic_optimizer = None
+        self.lr_scheduler = None
+        has_optimizer = bool(optimizer is not None or self.optimizer_name())
+        if has_optimizer or model_parameters is not None and self.optimizer_name():
+            self._configure_optimizer(optimizer, model_parameters)
+            self._configure_lr_scheduler(lr_scheduler)
+            self._report_progress(0)
+        elif self.zero_optimization():
+            self.optimizer = self._configure_zero_optimizer(optimizer=None)
+        self._configure_checkpointing()
+
+        if self.pld_enabled():
+            from .progressive_layer_drop import ProgressiveLayerDrop
+            self.progressive_layer_drop = ProgressiveLayerDrop(**self.pld_params())
+        if self.curriculum_enabled_legacy():
+            from .data_pipeline.curriculum_scheduler import CurriculumScheduler
+            self.curriculum_scheduler_legacy = CurriculumScheduler(self.curriculum_params_legacy())
+        if self.eigenvalue_enabled():
+            from .eigenvalue import Eigenvalue
+            c = self._config.eigenvalue_config
+            self.eigenvalue = Eigenvalue(verbose=c.verbose, max_iter=c.max_iter, tol=c.tol, stability=c.stability,
+                                         gas_boundary_resolution=c.gas_boundary_resolution, layer_name=c.layer_name,
+                                         layer_num=c.layer_num)
+        if self.global_rank == 0 and self._config.dump_state:
+            self._config.print("DeepSpeedEngine configuration")
+        self.unflatten = torch._utils._unflatten_dense_tensors
+        self.flatten = torch._utils._flatten_dense_tensors
+
+    # =========================================================================== construction
+    def _do_args_sanity_check(self, args):
+        if args is None:
+            return
+        if hasattr(args, "deepscale_config") and args.deepscale_config is not None:
+            logger.warning("************ --deepscale_config is deprecated, please use --deepspeed_config ************")
+            if hasattr(args, "deepspeed_config"):
+                assert args.deepspeed_config is None, "Not sure how to proceed, we were given both a deepscale_config and deepspeed_config"
+            args.deepspeed_config = args.deepscale_config
+            args.deepscale_config = None
+        if hasattr(args, "local_rank") and args.local_rank is not None and "LOCAL_RANK" in os.environ:
+            env_local = int(os.environ["LOCAL_RANK"])
+            if isinstance(args.local_rank, int) and args.local_rank >= 0:
+                assert env_local == args.local_rank, (f"Mismatch in local rank setting, args.local_rank={args.local_rank} "
+                                                      f"but env['LOCAL_RANK']={env_local}.")
+
+    def _configure_with_arguments(self, args, mpu):
+        if "OMPI_COMM_WORLD_LOCAL_RANK" in os.environ:
+            os.environ.setdefault("LOCAL_RANK", os.environ["OMPI_COMM_WORLD_LOCAL_RANK"])
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if self._config is None:
+            cfg = self.config
+            if cfg is None and args is not None and getattr(args, "deepspeed_config", None) is not None:
+                cfg = args.deepspeed_config
+            assert cfg is not None, "DeepSpeed requires --deepspeed_config to specify configuration file"
+            self._config = DeepSpeedConfig(cfg, mpu, mesh_device=self.mesh_device)
+
+    def _do_sanity_check(self):
+        if self.fp16_enabled() and self.bfloat16_enabled():
+            raise ValueError("fp16 and bf16 cannot both be enabled")
+
+    def _set_distributed_vars(self, args):
+        acc = get_accelerator()
+        if acc.is_available():
+            self.device = torch.device(acc.device_name(self.local_rank % max(1, acc.device_count())))
+            if not self.dont_change_device:
+                acc.set_device(self.device.index)
+        else:
+            self.device = torch.device("cpu")
+        self.world_size = dist.get_world_size()
+        self.global_rank = dist.get_rank()
+
+    def _configure_distributed_model(self, model):
+        self._set_client_model(model)
+        is_zero_init = any(hasattr(p, "ds_id") for p in self.module.parameters())
+        target = None
+        if self.fp16_enabled():
+            target = torch.float16
+        elif self.bfloat16_enabled():
+            target = torch.bfloat16
+        if target is not None and not self.torch_autocast_enabled():
+            for p in self.module.parameters():
+                if p.is_floating_point() and p.dtype != target and not getattr(p, "_sxb_keep_dtype", False):
+                    p.data = p.data.to(target)
+            for b in self.module.buffers():
+                if b.is_floating_point() and b.dtype != target and not getattr(b, "_sxb_keep_dtype", False):
+                    b.data = b.data.to(target)
+        if not self.dont_change_device:
+            self.module.to(self.device)
+        # MoE discovery (reference :1311-1328)
+        from ..moe.layer import MoE
+        for _, m in self.module.named_modules():
+            if isinstance(m, MoE):
+                self.has_moe_layers = True
+                self.num_experts.append(m.num_experts)
+                self.moe_layers.append(m)
+        if self.has_moe_layers:
+            for m in self.moe_layers:
+                m.set_deepspeed_parallelism(self._config.use_data_before_expert_parallel_)
+        self.data_parallel_group = groups._get_data_parallel_group()
+        self.dp_world_size = groups._get_data_parallel_world_size()
+        self.seq_data_parallel_group = groups._get_sequence_data_parallel_group()
+        self.seq_dp_world_size = groups._get_sequence_data_parallel_world_size()
+        self.mp_world_size = groups.get_model_parallel_world_size()
+        self.expert_parallel_group = groups._get_expert_parallel_group_dict()
+        self.expert_data_parallel_group = groups._get_expert_data_parallel_group_dict()
+        self.sequence_parallel_size = groups._get_sequence_parallel_world_size()
+        if self.sequence_parallel_size > 1:
+            self.communication_data_type = self._config.seq_parallel_communication_data_type
+            self.seq_parallel_group = groups._get_sequence_parallel_group()
+        if not (self.amp_enabled() or is_zero_init):
+            self._broadcast_model()
+
+    def _set_client_model(self, model):
+        modules = self.__dict__.get("_modules")
+        modules["module"] = model
+        self.__dict__["module"] = model
+
+    def _broadcast_model(self):
+        if self.world_size == 1 or not dist.is_initialized():
+            return
+
+        def is_replicated(p):
+            return not (hasattr(p, "ds_status") and getattr(p, "ds_tensor", None) is not None and p.numel() == 0)
+
+        for n, p in self.module.named_parameters():
+            if hasattr(p, "allreduce") and not p.allreduce:      # expert parameter
+                if torch.is_tensor(p) and is_replicated(p):
+                    dist.broadcast(p.data, groups._get_expert_parallel_src_rank(p.group_name) if False else
+                                   dist.get_global_rank(self.expert_data_parallel_group[p.group_name], 0),
+                                   group=self.expert_data_parallel_group[p.group_name])
+            elif torch.is_tensor(p) and is_replicated(p):
+                dist.broadcast(p.data, groups._get_broadcast_src_rank(), group=self.seq_data_parallel_group)
+
+    # ============================================================================ data loading
+    def deepspeed_io(self, dataset, batch_size=None, route="train", pin_memory=True, data_sampler=None, collate_fn=None,
+                     num_local_io_workers=None):
+        if not (isinstance(dataset, torch.utils.data.Dataset)):
+            raise ValueError("Training data must be a torch Dataset")
+        if batch_size is None:
+            batch_size = self.train_micro_batch_size_per_gpu()
+        if collate_fn is None:
+            collate_fn = self.collate_fn
+        tput = self.tput_timer if route == "train" else None
+        if self.mpu is not None:
+            dp_world, dp_rank = self.mpu.get_data_parallel_world_size(), self.mpu.get_data_parallel_rank()
+        else:
+            dp_world, dp_rank = self.dp_world_size, groups._get_data_parallel_rank()
+        cfg = {}
+        if self.curriculum_learning_enabled():
+            cfg = {"curriculum_learning_enabled": True, "data_efficiency": self._config.data_efficiency_config,
+                   "data_parallel_group": self.data_parallel_group,
+                   "gradient_accumulation_steps": self.gradient_accumulation_steps(), "global_rank": self.global_rank}
+        return DeepSpeedDataLoader(dataset=dataset, batch_size=batch_size, pin_memory=pin_memory,
+                                   collate_fn=collate_fn, local_rank=self.local_rank, tput_timer=tput,
+                                   num_local_io_workers=num_local_io_workers, data_sampler=data_sampler,
+                                   data_parallel_world_size=dp_world, data_parallel_rank=dp_rank,
+                                   dataloader_drop_last=self.dataloader_drop_last(), deepspeed_dataloader_config=cfg)
+
+    # ================================================================================ optimizer
+    def _configure_optimizer(self, client_optimizer, model_parameters):
+        if client_optimizer is None:
+            if model_parameters is None:
+                model_parameters = list(self.module.parameters())
+            basic_optimizer = self._configure_basic_optimizer(model_parameters)
+            log_dist(f"Using configured optimizer = {self.optimizer_name()}", ranks=[0])
+        elif isinstance(client_optimizer, Optimizer):
+            basic_optimizer = client_optimizer
+            log_dist("Using client Optimizer as basic optimizer", ranks=[0])
+        else:
+            basic_optimizer = client_optimizer(model_parameters if model_parameters is not None
+                                               else self.module.parameters())
+            log_dist("Using client callable to create basic optimizer", ranks=[0])
+        if not isinstance(model_parameters, list) and model_parameters is not None and client_optimizer is not None:
+            pass
+        # drop frozen params from the groups (they have no optimizer state)
+        for g in basic_optimizer.param_groups:
+            g["params"] = [p for p in g["params"] if p.requires_grad]
+        self.basic_optimizer = basic_optimizer
+        self._do_optimizer_sanity_check(basic_optimizer)
+        log_dist(f"Basic Optimizer = {type(basic_optimizer).__name__}", ranks=[0])
+        if self.zero_optimization():
+            if self.has_moe_layers:
+                from ..moe.utils import configure_moe_param_groups
+                basic_optimizer.param_groups[:] = configure_moe_param_groups(basic_optimizer.param_groups)
+            self.optimizer = self._configure_zero_optimizer(basic_optimizer)
+        elif self.bfloat16_enabled():
+            self.optimizer = self._configure_bf16_optimizer(basic_optimizer)
+        elif self.fp16_enabled():
+            self.optimizer = self._configure_fp16_optimizer(basic_optimizer)
+        else:
+            self.optimizer = basic_optimizer
+        log_dist(f"Final Optimizer = {type(self.optimizer).__name__}", ranks=[0])
+
+    def _do_optimizer_sanity_check(self, basic_optimizer):
+        if self.zero_optimization() and not self.zero_allow_untested_optimizer():
+            from ..ops.adam import DeepSpeedCPUAdam, FusedAdam
+            from ..ops.lamb import FusedLamb
+            from ..ops.lion import FusedLion
+            ok = (torch.optim.Adam, torch.optim.AdamW, torch.optim.SGD, torch.optim.Adagrad, FusedAdam, DeepSpeedCPUAdam,
+                  FusedLamb, FusedLion)
+            if not isinstance(basic_optimizer, ok):
+                assert self.zero_allow_untested_optimizer(), (
+                    'You are using an untested ZeRO Optimizer. Please add <"zero_allow_untested_optimizer": true> in '
+                    "the configuration file to use it.")
+
+    def _configure_basic_optimizer(self, model_parameters):
+        params = dict(self.optimizer_params() or {})
+        name = self.optimizer_name()
+        if "max_grad_norm" in params:
+            params.pop("max_grad_norm")
+        cpu_offload = self.zero_cpu_offload()
+        on_gpu = get_accelerator().is_available() and not cpu_offload
+        if name in (ADAM_OPTIMIZER, ADAMW_OPTIMIZER):
+            torch_adam = params.pop(TORCH_ADAM_PARAM, False)
+            adam_w_mode = params.pop(ADAM_W_MODE, ADAM_W_MODE_DEFAULT)
+            effective_w = name == ADAMW_OPTIMIZER or adam_w_mode
+            if torch_adam:
+                cls = torch.optim.AdamW if effective_w else torch.optim.Adam
+                return cls(model_parameters, **params)
+            if cpu_offload:
+                from ..ops.adam import DeepSpeedCPUAdam
+                return DeepSpeedCPUAdam(model_parameters, **params, adamw_mode=effective_w)
+            from ..ops.adam import FusedAdam
+            return FusedAdam(model_parameters, **params, adam_w_mode=effective_w)
+        if name == ADAGRAD_OPTIMIZER:
+            if cpu_offload:
+                from ..ops.adagrad import DeepSpeedCPUAdagrad
+                return DeepSpeedCPUAdagrad(model_parameters, **params)
+            return torch.optim.Adagrad(model_parameters, **params)
+        if name == LAMB_OPTIMIZER:
+            from ..ops.lamb import FusedLamb
+            return FusedLamb(model_parameters, **params)
+        if name == ONEBIT_ADAM_OPTIMIZER:
+            from .fp16.onebit.adam import OnebitAdam
+            return OnebitAdam(model_parameters, self, **params)
+        if name == ZERO_ONE_ADAM_OPTIMIZER:
+            from .fp16.onebit.zoadam import ZeroOneAdam
+            return ZeroOneAdam(model_parameters, self, **params)
+        if name == ONEBIT_LAMB_OPTIMIZER:
+            from .fp16.onebit.lamb import OnebitLamb
+            return OnebitLamb(model_parameters, self, **params)
+        if name == LION_OPTIMIZER:
+            if cpu_offload:
+                from ..ops.lion import DeepSpeedCPULion
+                return DeepSpeedCPULion(model_parameters, **params)
+            from ..ops.lion import FusedLion
+            return FusedLion(model_parameters, **params)
+        if name in (MUADAM_OPTIMIZER, MUADAMW_OPTIMIZER, MUSGD_OPTIMIZER):
+            try:
+                import mup
+            except ImportError as e:
+                raise ImportError("Install mup to use the Mu* optimizers") from e
+            return {MUADAM_OPTIMIZER: mup.MuAdam, MUADAMW_OPTIMIZER: mup.MuAdamW, MUSGD_OPTIMIZER: mup.MuSGD}[name](
+                model_parameters, **params)
+        if name == SGD_OPTIMIZER:
+            return torch.optim.SGD(model_parameters, **params)
+        return getattr(torch.optim, name)(model_parameters, **params)
+
+    def _loss_scale_args(self):
+        return dict(static_loss_scale=self.loss_scale() if self.loss_scale() else 1.0,
+                    dynamic_loss_scale=self.fp16_enabled() and self.loss_scale() == 0,
+                    dynamic_loss_args=self.dynamic_loss_scale_args())
+
+    def _configure_zero_optimizer(self, optimizer):
+        zc = self._config.zero_config
+        stage = self.zero_optimization_stage()
+        timers = self.timers if self.wall_clock_breakdown() else NoopTimer()
+        ra = zc.replica_averaging
+        if ra is not None:
+            method, rings, shuffle_step, slice_count, seed, fused = (ra.method, ra.rings, ra.shuffle_step,
+                                                                     ra.slice_count, ra.seed, ra.fused)
+        else:
+            method, rings, shuffle_step, slice_count, seed, fused = (self._method, self._rings, self._shuffle_step,
+                                                                     self._slice_count, 1234, None)
+        lp_dtype = torch.float16 if self.fp16_enabled() else (torch.bfloat16 if self.bfloat16_enabled() else torch.float32)
+        common = dict(timers=timers, clip_grad=self.gradient_clipping(), mpu=self.mpu,
+                      dp_process_group=self.seq_data_parallel_group,
+                      gradient_accumulation_steps=self.gradient_accumulation_steps(),
+                      gradient_predivide_factor=self.gradient_predivide_factor(),
+                      postscale_gradients=self.postscale_gradients(),
+                      communication_data_type=self.communication_data_type or lp_dtype,
+                      gradient_accumulation_dtype=self._grad_accum_dtype(lp_dtype),
+                      check_grad_overflow=(True if self.fp16_enabled() else self._config.bfloat16_check_grad_overflow),
+                      dtype=lp_dtype, **self._loss_scale_args())
+        if stage <= ZeroStageEnum.gradients:
+            from .zero.stage_1_and_2 import DeepSpeedZeroOptimizer
+            assert optimizer is not None, "ZeRO stage 1/2 needs an optimizer"
+            use_avg = self.world_size > 1 and slice_count < self.seq_dp_world_size
+            return DeepSpeedZeroOptimizer(
+                optimizer, param_names=self.param_names, contiguous_gradients=zc.contiguous_gradients,
+                reduce_bucket_size=zc.reduce_bucket_size, allgather_bucket_size=zc.allgather_bucket_size,
+                expert_parallel_group=self.expert_parallel_group if self.has_moe_layers else None,
+                expert_data_parallel_group=self.expert_data_parallel_group if self.has_moe_layers else None,
+                reduce_scatter=zc.reduce_scatter, overlap_comm=bool(zc.overlap_comm),
+                offload_optimizer_config=zc.offload_optimizer, ignore_unused_parameters=zc.ignore_unused_parameters,
+                partition_grads=stage == ZeroStageEnum.gradients, round_robin_gradients=zc.round_robin_gradients,
+                has_moe_layers=self.has_moe_layers, elastic_checkpoint=zc.elastic_checkpoint,
+                method=method, rings=rings, shuffle_step=shuffle_step, slice_count=slice_count, seed=seed,
+                replica_averaging=use_avg, fused_replica_averaging=fused, **common)
+        from .zero.stage3 import DeepSpeedZeroOptimizer_Stage3
+        assert not self.has_moe_layers, "MoE not supported with Stage 3"
+        if optimizer is None:
+            optimizer = _DummyOptim(list(self.module.parameters()))
+        if zc.mics_shard_size > 0:
+            from .zero.mics import MiCS_Optimizer
+            cls = MiCS_Optimizer
+        else:
+            cls = DeepSpeedZeroOptimizer_Stage3
+        return cls(self.module, optimizer, param_names=self.param_names, ds_config=self._config,
+                   contiguous_gradients=zc.contiguous_gradients, reduce_bucket_size=zc.reduce_bucket_size,
+                   prefetch_bucket_size=zc.prefetch_bucket_size, max_reuse_distance=zc.max_reuse_distance,
+                   max_live_parameters=zc.max_live_parameters,
+                   param_persistence_threshold=zc.param_persistence_threshold,
+                   model_persistence_threshold=zc.model_persistence_threshold, reduce_scatter=zc.reduce_scatter,
+                   overlap_comm=bool(zc.overlap_comm), offload_optimizer_config=zc.offload_optimizer,
+                   offload_param_config=zc.offload_param, sub_group_size=zc.sub_group_size,
+                   elastic_checkpoint=zc.elastic_checkpoint, aio_config=self._config.aio_config,
+                   zero_hpz_partition_size=zc.zero_hpz_partition_size, zero_quantized_weights=zc.zero_quantized_weights,
+                   zero_quantized_nontrainable_weights=zc.zero_quantized_nontrainable_weights,
+                   zeropp_loco_param=zc.zeropp_loco_param, fused_step=zc.fused_step, **common)
+
+    def _grad_accum_dtype(self, lp_dtype):
+        name = self._config.grad_accum_dtype
+        if name is None:
+            return lp_dtype if self.gradient_accumulation_steps() == 1 else torch.float32 if lp_dtype == torch.bfloat16 else lp_dtype
+        return {"fp32": torch.float32, "fp16": torch.float16, "bf16": torch.bfloat16}[name]
+
+    def _configure_bf16_optimizer(self, optimizer):
+        from .bf16_optimizer import BF16_Optimizer
+        timers = self.timers if self.wall_clock_breakdown() else NoopTimer()
+        return BF16_Optimizer(optimizer, self.param_names, mpu=self.mpu, clip_grad=self.gradient_clipping(),
+                              allgather_bucket_size=self._config.zero_config.allgather_bucket_size,
+                              dp_process_group=self.seq_data_parallel_group, timers=timers,
+                              grad_acc_dtype=self._grad_accum_dtype(torch.bfloat16),
+                              immediate_grad_update=self._config.bfloat16_immediate_grad_update,
+                              check_grad_overflow=self._config.bfloat16_check_grad_overflow,
+                              gradient_accumulation_steps=self.gradient_accumulation_steps())
+
+    def _configure_fp16_optimizer(self, optimizer):
+        from .fp16.fused_optimizer import FP16_Optimizer
+        timers = self.timers if self.wall_clock_breakdown() else NoopTimer()
+        return FP16_Optimizer(optimizer, deepspeed=self, mpu=self.mpu, clip_grad=self.gradient_clipping(),
+                              timers=timers, dp_process_group=self.seq_data_parallel_group,
+                              has_moe_layers=self.has_moe_layers, **self._loss_scale_args())
+
+    def _configure_lr_scheduler(self, client_lr_scheduler=None):
+        sched = None
+        if client_lr_scheduler is not None:
+            if isinstance(client_lr_scheduler, Callable) and not hasattr(client_lr_scheduler, "step"):
+                sched = client_lr_scheduler(self.basic_optimizer)
+            else:
+                sched = client_lr_scheduler
+            log_dist("Using client LR scheduler", ranks=[0])
+        elif self.scheduler_name() is not None:
+            name = self.scheduler_name()
+            if hasattr(lr_schedules, name):
+                cls = getattr(lr_schedules, name)
+            else:
+                assert hasattr(torch.optim.lr_scheduler, name), f"DeepSpeed does not recognize LR scheduler {name}"
+                cls = getattr(torch.optim.lr_scheduler, name)
+            sched = cls(self.basic_optimizer, **(self.scheduler_params() or {}))
+            log_dist(f"Using configured LR scheduler = {name}", ranks=[0])
+        self.lr_scheduler = sched
+
+    def _configure_checkpointing(self):
+        from .checkpoint_engine.utils import create_checkpoint_engine
+        self.checkpoint_engine = create_checkpoint_engine(self._config, groups, self.zero_optimization_stage(),
+                                                          self.has_moe_layers, self.optimizer)
+        dp_rank = groups._get_sequence_data_parallel_rank()
+        rank = self.local_rank if self.use_node_local_storage() else dp_rank
+        self.save_non_zero_checkpoint = (rank == 0) or (self.zero_optimization_partition_weights()
+                                                        and self.is_first_weights_partition_group())
+        if self.zero_optimization() or self.bfloat16_enabled():
+            self.save_zero_checkpoint = True       # every rank owns a distinct optimizer partition
+
+    def is_first_weights_partition_group(self):
+        return True if self.mics_shard_size() < 0 or self.global_rank < self.mics_shard_size() else False
+
+    # ================================================================================= training
+    def train(self, mode=True):
+        self.warn_unscaled_loss = True
+        self.module.train(mode)
+        return self
+
+    def eval(self):
+        self.warn_unscaled_loss = True
+        self.module.train(False)
+        return self
+
+    def is_gradient_accumulation_boundary(self):
+        if self._is_gradient_accumulation_boundary is None:
+            return (self.micro_steps + 1) % self.gradient_accumulation_steps() == 0
+        return self._is_gradient_accumulation_boundary
+
+    def set_gradient_accumulation_boundary(self, is_boundary):
+        self._is_gradient_accumulation_boundary = is_boundary
+        if hasattr(self.optimizer, "set_gradient_accumulation_boundary"):
+            self.optimizer.set_gradient_accumulation_boundary(is_boundary)
+
+    def no_sync(self):
+        from contextlib import contextmanager
+
+        @contextmanager
+        def ctx():
+            assert not self.zero_optimization_partition_gradients(), \
+                f"no_sync context manager is incompatible with gradient partitioning logic of ZeRO stage {self.zero_optimization_stage()}"
+            assert not self.inside_no_sync_ctxt, "no_sync context manager reentry is unsupported"
+            self.inside_no_sync_ctxt = True
+            try:
+                yield
+            finally:
+                self.inside_no_sync_ctxt = False
+        return ctx()
+
+    def forward(self, *inputs, **kwargs):
+        if self.flops_profiler_enabled() and self.global_steps == self.flops_profiler_profile_step() and self.global_rank == 0:
+            self.flops_profiler.start_profile(ignore_list=None)
+        if self.module.training and self.progressive_layer_drop is not None:
+            kwargs.update(self.progressive_layer_drop.get_state())
+        if self.module.training and self.curriculum_enabled_legacy():
+            self.curriculum_scheduler_legacy.update_difficulty(self.global_steps + 1)
+            if self.curriculum_params_legacy().get("curriculum_type") == "seqlen":
+                kwargs.update({"curriculum_seqlen": self.curriculum_scheduler_legacy.get_current_difficulty()})
+        if self.training_dataloader is None:
+            self.tput_timer.start()
+        self._start_timers(self.engine_timers.forward_timers)
+        if hasattr(self.optimizer, "set_gradient_accumulation_boundary"):
+            self.optimizer.set_gradient_accumulation_boundary(self.is_gradient_accumulation_boundary())
+        if self.fp16_auto_cast():
+            inputs = tuple(t.half() if torch.is_tensor(t) and t.is_floating_point() else t for t in inputs)
+        if self.torch_autocast_enabled():
+            with torch.autocast(device_type=self.device.type, dtype=self._config.torch_autocast_dtype):
+                loss = self.module(*inputs, **kwargs)
+        else:
+            loss = self.module(*inputs, **kwargs)
+        self._stop_timers(self.engine_timers.forward_timers)
+        if self.flops_profiler_enabled() and self.global_steps == self.flops_profiler_profile_step() and self.global_rank == 0:
+            self.flops_profiler.stop_profile()
+        return loss
+
+    def _scale_loss_by_gas(self, loss):
+        if torch.is_tensor(loss):
+            return loss / self.gradient_accumulation_steps()
+        if isinstance(loss, (tuple, list)) and torch.is_tensor(loss[0]):
+            return type(loss)(l / self.gradient_accumulation_steps() for l in loss)
+        if self.warn_unscaled_loss:
+            logger.warning(f"DeepSpeed unable to scale loss because of type: {type(loss)}")
+            self.warn_unscaled_loss = False
+        return loss
+
+    def allreduce_gradients(self, bucket_size=MEMORY_OPT_ALLREDUCE_SIZE):
+        """Data-parallel gradient reduction at the accumulation boundary."""
+        if self.is_gradient_accumulation_boundary() is False and not self.zero_optimization_partition_gradients():
+            return
+        if hasattr(self.optimizer, "overlapping_partition_gradients_reduce_epilogue") and (
+                self.zero_optimization() or self.bfloat16_enabled() or self.fp16_enabled() and hasattr(self.optimizer, "groups")):
+            self.optimizer.overlapping_partition_gradients_reduce_epilogue()
+        elif self.is_gradient_accumulation_boundary():
+            self.buffered_allreduce_fallback(elements_per_buffer=bucket_size)
+
+    def backward(self, loss, retain_graph=False, scale_wrt_gas=True):
+        assert self.optimizer is not None, "must provide optimizer during init in order to use backward"
+        if not self.inside_no_sync_ctxt:
+            self._start_timers(self.engine_timers.backward_timers)
+        do_scale = self.gradient_accumulation_steps() > 1 and scale_wrt_gas
+        if do_scale:
+            loss = self._scale_loss_by_gas(loss.float())
+        if self.monitor.enabled and self.is_gradient_accumulation_boundary():
+            self._loss_for_monitor = loss.detach()
+        self._start_timers(self.engine_timers.backward_inner_timers)
+        if hasattr(self.optimizer, "set_gradient_accumulation_boundary"):
+            self.optimizer.set_gradient_accumulation_boundary(self.is_gradient_accumulation_boundary())
+        if hasattr(self.optimizer, "backward") and not isinstance(self.optimizer, Optimizer):
+            self.optimizer.backward(loss, retain_graph=retain_graph)
+        elif self.amp_enabled():
+            raise NotImplementedError("apex amp is not available in this build; use bf16/fp16 sections")
+        else:
+            loss.backward(retain_graph=retain_graph)
+        self._stop_timers(self.engine_timers.backward_inner_timers)
+        self._start_timers(self.engine_timers.backward_reduce_timers)
+        if self.enable_backward_allreduce and not self.inside_no_sync_ctxt:
+            self.allreduce_gradients()
+        self._stop_timers(self.engine_timers.backward_reduce_timers)
+        if not self.inside_no_sync_ctxt:
+            self._stop_timers(self.engine_timers.backward_timers)
+        return loss
+
+    def zero_grad(self):
+        for p in self.module.parameters():
+            p.grad = None
+
+    def clip_fp32_gradients(self):
+        from .utils import clip_grad_norm_
+        clip_grad_norm_(parameters=self.module.parameters(), max_norm=self.gradient_clipping(), mpu=self.mpu)
+
+    def _take_model_step(self, lr_kwargs, block_eigenvalue=None):
+        if self.gradient_clipping() > 0.0 and isinstance(self.optimizer, Optimizer):
+            self.clip_fp32_gradients()
+        self.optimizer.step()
+        if hasattr(self.optimizer, "_global_grad_norm"):
+            self._global_grad_norm = self.optimizer._global_grad_norm
+        overflow = bool(getattr(self.optimizer, "overflow", False))
+        if isinstance(self.optimizer, Optimizer):
+            self.optimizer.zero_grad(set_to_none=True)
+        else:
+            self.optimizer.zero_grad()
+        self._step_applied = not overflow
+        if overflow:
+            self.skipped_steps += 1
+        else:
+            if self.lr_scheduler is not None:
+                try:
+                    self.lr_scheduler.step(**(lr_kwargs or {}))
+                except TypeError:
+                    self.lr_scheduler.step()
+        if self.steps_per_print() is not None and self.global_steps % self.steps_per_print() == 0 and self.global_rank == 0 \
+                and self.global_steps > 0:
+            self._report_progress(self.global_steps + 1)
+        self.losses = None
+        self.global_steps += 1
+        self.global_samples += self.train_batch_size()
+
+    def step(self, lr_kwargs=None):
+        assert self.optimizer is not None and not isinstance(self.optimizer, _DummyOptim), \
+            "must provide optimizer during init in order to use step"
+        self._start_timers(self.engine_timers.step_timers)
+        report = False
+        self._step_applied = False
+        if self.is_gradient_accumulation_boundary():
+            self.gas_boundary_ctr += 1
+            if self.eigenvalue_enabled() and self.gas_boundary_ctr % self.eigenvalue_gas_boundary_resolution() == 0 \
+                    and self.quantizer is not None:
+                self.block_eigenvalue = self.eigenvalue.compute_eigenvalue(self.module, self.device)
+            if self.progressive_layer_drop:
+                self.progressive_layer_drop.update_state(self.global_steps)
+            self._take_model_step(lr_kwargs)
+            report = True
+            if getattr(self, "_decoupled_commit_pending", False):
+                self._commit_decoupled_checkpoint()
+        self.tput_timer.stop(global_step=self.is_gradient_accumulation_boundary(), report_speed=report)
+        self._stop_timers(self.engine_timers.step_timers)
+        if self.monitor.enabled and self.is_gradient_accumulation_boundary() and self.global_rank == 0:
+            ev = [("Train/Samples/lr", self.get_lr()[0], self.global_samples)]
+            if getattr(self, "_loss_for_monitor", None) is not None:
+                ev.append(("Train/Samples/train_loss", float(self._loss_for_monitor), self.global_samples))
+            if self.fp16_enabled() and hasattr(self.optimizer, "cur_scale"):
+                ev.append(("Train/Samples/loss_scale", self.optimizer.cur_scale, self.global_samples))
+            self.monitor.write_events(ev)
+        if self.wall_clock_breakdown() and self.is_gradient_accumulation_boundary():
+            if self.global_steps % self.steps_per_print() == 0:
+                self.timers.log(self.engine_timers.global_timers if self.engine_timers.global_timers
+                                else self.engine_timers.micro_timers, memory_breakdown=self.memory_breakdown())
+        self.micro_steps += 1
+
+    def was_step_applied(self) -> bool:
+        return self._step_applied
+
+    def _start_timers(self, names):
+        for n in names:
+            self.timers(n).start()
+
+    def _stop_timers(self, names):
+        record = self.global_rank == 0
+        for n in names:
+            self.timers(n).stop(record=record)
+
+    def _report_progress(self, step):
+        lr = self.get_lr()
+        mom = self.get_mom()
+        log_dist(f"step={step}, skipped={self.skipped_steps}, lr={lr}, mom={mom}", ranks=[0])
+
+    # ------------------------------------------------------------------ non-ZeRO DP all-reduce
+    def allreduce_bucket(self, bucket, dp_group, dp_world_size=None):
+        tensor = self.flatten(bucket)
+        dp_world_size = dp_world_size or dist.get_world_size(dp_group)
+        comm_dtype = self.communication_data_type
+        t = tensor.to(comm_dtype) if comm_dtype is not None and comm_dtype != tensor.dtype else tensor
+        if self.postscale_gradients():
+            if self.gradient_predivide_factor() != 1.0:
+                t.mul_(1.0 / self.gradient_predivide_factor())
+            dist.all_reduce(t, group=dp_group)
+            if self.gradient_average and self.gradient_predivide_factor() != dp_world_size:
+                t.mul_(self.gradient_predivide_factor() / dp_world_size)
+        else:
+            t.mul_(1.0 / dp_world_size)
+            dist.all_reduce(t, group=dp_group)
+        if t is not tensor:
+            tensor.copy_(t)
+        return tensor
+
+    def allreduce_and_copy(self, small_bucket, dp_group, dp_world_size=None):
+        allreduced = self.allreduce_bucket(small_bucket, dp_group, dp_world_size)
+        for buf, synced in zip(small_bucket, self.unflatten(allreduced, small_bucket)):
+            buf.copy_(synced)
+
+    def allreduce_no_retain(self, bucket, dp_group, numel_per_bucket=500000000, dp_world_size=None):
+        small, numel = [], 0
+        for t in bucket:
+            small.append(t)
+            numel += t.numel()
+            if numel > numel_per_bucket:
+                self.allreduce_and_copy(small, dp_group, dp_world_size)
+                small, numel = [], 0
+        if small:
+            self.allreduce_and_copy(small, dp_group, dp_world_size)
+
+    def _get_gradients_for_reduction(self):
+        non_expert, expert = [], defaultdict(list)
+        for name, p in self.module.named_parameters():
+            if not p.requires_grad:
+                continue
+            if p.grad is None:
+                p.grad = torch.zeros(p.size(), dtype=p.dtype, device=p.device)
+            g = p.grad.data
+            if hasattr(p, "allreduce") and not p.allreduce:
+                expert[p.group_name].append(g)
+            else:
+                non_expert.append(g)
+        return non_expert, expert
+
+    def buffered_allreduce_fallback(self, grads=None, elements_per_buffer=500000000):
+        if grads is None:
+            non_expert, expert = self._get_gradients_for_reduction()
+        else:
+            non_expert, expert = grads, {}
+        if dist.get_world_size(self.seq_data_parallel_group) > 1 and dist.is_initialized():
+            by_dtype = defaultdict(list)
+            for g in non_expert:
+                if g.is_sparse:
+                    self._sparse_allreduce(g)
+                else:
+                    by_dtype[g.dtype].append(g)
+            for _, bucket in by_dtype.items():
+                self.allreduce_no_retain(bucket, self.seq_data_parallel_group, elements_per_buffer)
+        for gname, gl in expert.items():
+            grp = self.expert_data_parallel_group[gname]
+            # expert grads are summed over expert-DP but averaged by the FULL dp size (reference :2713-2734)
+            by_dtype = defaultdict(list)
+            for g in gl:
+                by_dtype[g.dtype].append(g)
+            for _, bucket in by_dtype.items():
+                self.allreduce_no_retain(bucket, grp, elements_per_buffer, dp_world_size=self.seq_dp_world_size)
+
+    def _sparse_allreduce(self, g):
+        from .sparse_tensor import sparse_allreduce
+        sparse_allreduce(g, self.seq_data_parallel_group, self.postscale_gradients(), self.gradient_predivide_factor())
+
+    # =============================================================================== accessors
+    def get_lr(self):
+        return [g["lr"] for g in self.optimizer.param_groups] if self.optimizer is not None else []
+
+    def get_type(self):
+        return [g.get("type") for g in self.optimizer.param_groups]
+
+    def get_mom(self):
+        if self.optimizer is None:
+            return []
+        if self.optimizer_name() in (SGD_OPTIMIZER, "rmsprop"):
+            return [g.get("momentum") for g in self.optimizer.param_groups]
+        return [g.get("betas") for g in self.optimizer.param_groups]
+
+    def get_global_grad_norm(self):
+        return self._global_grad_norm
+
+    def get_batch_info(self):
+        return self.train_batch_size(), self.train_micro_batch_size_per_gpu(), self.gradient_accumulation_steps()
+
+    def set_train_batch_size(self, train_batch_size):
+        if train_batch_size % (self.train_micro_batch_size_per_gpu() * self.dp_world_size) != 0:
+            raise ValueError("Train batch size must be divisible by micro-batch data parallelism")
+        self._config.gradient_accumulation_steps = train_batch_size // (self.train_micro_batch_size_per_gpu() * self.dp_world_size)
+        self._config.train_batch_size = train_batch_size
+
+    def set_train_micro_batch_size(self, micro_batch_size):
+        self._config.train_batch_size = micro_batch_size * self._config.gradient_accumulation_steps * self.dp_world_size
+        self._config.train_micro_batch_size_per_gpu = micro_batch_size
+
+    def train_batch_size(self): return self._config.train_batch_size
+    def train_micro_batch_size_per_gpu(self): return self._config.train_micro_batch_size_per_gpu
+    def gradient_accumulation_steps(self): return self._config.gradient_accumulation_steps
+    def steps_per_print(self): return self._config.steps_per_print
+    def optimizer_name(self): return self.client_optimizer.__class__.__name__ if self.client_optimizer else self._config.optimizer_name
+    def optimizer_params(self): return self._config.optimizer_params
+    def optimizer_legacy_fusion(self): return self._config.optimizer_legacy_fusion
+    def scheduler_name(self): return self._config.scheduler_name
+    def scheduler_params(self): return self._config.scheduler_params
+    def zero_optimization(self): return self._config.zero_enabled
+    def zero_optimization_stage(self): return self._config.zero_optimization_stage
+    def zero_allow_untested_optimizer(self): return self._config.zero_allow_untested_optimizer
+    def zero_force_ds_cpu_optimizer(self): return self._config.zero_force_ds_cpu_optimizer
+    def zero_reduce_scatter(self): return self._config.zero_config.reduce_scatter
+    def zero_overlap_comm(self): return self._config.zero_config.overlap_comm
+    def zero_offload_optimizer(self): return self._config.zero_config.offload_optimizer
+    def zero_offload_param(self): return self._config.zero_config.offload_param
+    def zero_use_cpu_optimizer(self): return self.zero_cpu_offload()
+    def zero_cpu_offload(self):
+        oc = self._config.zero_config.offload_optimizer
+        return oc is not None and str(oc.device).endswith("cpu")
+    def zero_partial_offload(self): return getattr(self._config.zero_config.offload_optimizer, "ratio", 1.0)
+    def zero_sub_group_size(self): return self._config.zero_config.sub_group_size
+    def zero_reduce_bucket_size(self): return self._config.zero_config.reduce_bucket_size
+    def zero_multi_rank_bucket_allreduce(self): return self._config.zero_config.use_multi_rank_bucket_allreduce
+    def zero_allgather_bucket_size(self): return self._config.zero_config.allgather_bucket_size
+    def zero_optimization_partition_gradients(self): return self.zero_optimization_stage() >= ZeroStageEnum.gradients
+    def zero_optimization_partition_weights(self): return self.zero_optimization_stage() >= ZeroStageEnum.weights
+    def zero_contiguous_gradients(self): return self._config.zero_config.contiguous_gradients
+    def zero_load_from_fp32_weights(self): return self._config.zero_config.load_from_fp32_weights
+    def zero_elastic_checkpoint(self): return self._config.zero_config.elastic_checkpoint
+    def zero_has_nvme_offload(self):
+        zc = self._config.zero_config
+        return any(o is not None and str(o.device).endswith("nvme") for o in (zc.offload_optimizer, zc.offload_param))
+    def zero_max_live_parameters(self): return self._config.zero_config.max_live_parameters
+    def zero_max_reuse_distance(self): return self._config.zero_config.max_reuse_distance
+    def zero_prefetch_bucket_size(self): return self._config.zero_config.prefetch_bucket_size
+    def zero_param_persistence_threshold(self): return self._config.zero_config.param_persistence_threshold
+    def zero_model_persistence_threshold(self): return self._config.zero_config.model_persistence_threshold
+    def zero_gather_16bit_weights_on_model_save(self): return self._config.zero_config.gather_16bit_weights_on_model_save
+    def zero_grad_hooks(self): return True
+    def zero_legacy_stage1(self): return self._config.zero_config.legacy_stage1
+    def zero_ignore_unused_parameters(self): return self._config.zero_config.ignore_unused_parameters
+    def zero_round_robin_gradients(self): return self._config.zero_config.round_robin_gradients
+    def zero_hpz_partition_size(self): return self._config.zero_config.zero_hpz_partition_size
+    def zero_quantized_weights(self): return self._config.zero_config.zero_quantized_weights
+    def zero_quantized_nontrainable_weights(self): return self._config.zero_config.zero_quantized_nontrainable_weights
+    def zero_quantized_gradients(self): return self._config.zero_config.zero_quantized_gradients
+    def zeropp_loco_param(self): return self._config.zero_config.zeropp_loco_param
+    def mics_shard_size(self): return self._config.mics_shard_size
+    def fp16_enabled(self): return self._config.fp16_enabled
+    def bfloat16_enabled(self): return self._config.bfloat16_enabled
+    def fp16_master_weights_and_gradients(self): return self._config.fp16_master_weights_and_gradients
+    def amp_enabled(self): return self._config.amp_enabled
+    def amp_params(self): return self._config.amp_params
+    def fp16_auto_cast(self): return self._config.fp16_auto_cast
+    def torch_autocast_enabled(self): return self._config.torch_autocast_enabled
+    def loss_scale(self): return self._config.loss_scale
+    def initial_dynamic_scale(self): return self._config.initial_dynamic_scale
+    def dynamic_loss_scale(self): return self._config.loss_scale == 0
+    def dynamic_loss_scale_args(self): return self._config.dynamic_loss_scale_args
+    def gradient_clipping(self): return self._config.gradient_clipping
+    def gradient_predivide_factor(self): return self._config.gradient_predivide_factor
+    def postscale_gradients(self): return not self._config.prescale_gradients
+    def sparse_gradients_enabled(self): return self._config.sparse_gradients_enabled
+    def dump_state(self): return self._config.dump_state
+    def wall_clock_breakdown(self): return self._config.wall_clock_breakdown
+    def memory_breakdown(self): return self._config.memory_breakdown
+    def flops_profiler_enabled(self): return self._config.flops_profiler_config.enabled
+    def flops_profiler_recompute_fwd_factor(self): return self._config.flops_profiler_config.recompute_fwd_factor
+    def flops_profiler_profile_step(self): return max(1, self._config.flops_profiler_config.profile_step)
+    def flops_profiler_module_depth(self): return self._config.flops_profiler_config.module_depth
+    def flops_profiler_top_modules(self): return self._config.flops_profiler_config.top_modules
+    def flops_profiler_detailed(self): return self._config.flops_profiler_config.detailed
+    def flops_profiler_output_file(self): return self._config.flops_profiler_config.output_file
+    def tensorboard_enabled(self): return self._config.monitor_config.tensorboard.enabled
+    def tensorboard_output_path(self): return self._config.monitor_config.tensorboard.output_path
+    def tensorboard_job_name(self): return self._config.monitor_config.tensorboard.job_name
+    def pld_enabled(self): return self._config.pld_enabled
+    def pld_params(self): return self._config.pld_params
+    def pld_theta(self): return self.pld_params()["theta"]
+    def pld_gamma(self): return self.pld_params()["gamma"]
+    def eigenvalue_enabled(self): return self._config.eigenvalue_enabled
+    def eigenvalue_verbose(self): return self._config.eigenvalue_verbose
+    def eigenvalue_max_iter(self): return self._config.eigenvalue_max_iter
+    def eigenvalue_tol(self): return self._config.eigenvalue_tol
+    def eigenvalue_stability(self): return self._config.eigenvalue_stability
+    def eigenvalue_gas_boundary_resolution(self): return self._config.eigenvalue_gas_boundary_resolution
+    def eigenvalue_layer_name(self): return self._config.eigenvalue_layer_name
+    def eigenvalue_layer_num(self): return self._config.eigenvalue_layer_num
+    def curriculum_enabled_legacy(self): return self._config.curriculum_enabled_legacy
+    def curriculum_params_legacy(self): return self._config.curriculum_params_legacy
+    def data_efficiency_enabled(self): return self._config.data_efficiency_enabled
+    def data_efficiency_config(self): return self._config.data_efficiency_config
+    def data_sampling_enabled(self): return self._config.data_efficiency_config.get("data_sampling", {}).get("enabled", False)
+    def data_sampling_config(self): return self._config.data_efficiency_config.get("data_sampling", {})
+    def curriculum_learning_enabled(self):
+        return self.data_sampling_config().get("curriculum_learning", {}).get("enabled", False)
+    def curriculum_learning_config(self): return self.data_sampling_config().get("curriculum_learning", {})
+    def random_ltd_enabled(self):
+        return self._config.data_efficiency_config.get("data_routing", {}).get("random_ltd", {}).get("enabled", False)
+    def random_ltd_config(self): return self._config.data_efficiency_config.get("data_routing", {}).get("random_ltd", {})
+    def checkpoint_tag_validation_enabled(self): return self._config.checkpoint_tag_validation_enabled
+    def checkpoint_tag_validation_fail(self): return self._config.checkpoint_tag_validation_fail
+    def load_universal_checkpoint(self): return self._config.load_universal_checkpoint
+    def use_node_local_storage(self): return self._config.use_node_local_storage
+    def elasticity_enabled(self): return self._config.elasticity_enabled
+    def is_elastic_model_parallel_supported(self): return self.elasticity_enabled()
+    def dataloader_drop_last(self): return self._config.dataloader_drop_last
+    def aio_config(self): return self._config.aio_config
+    def graph_harvesting(self): return self._config.graph_harvesting
+    def swap_tensor_config(self): return self._config.zero_config.offload_optimizer
+    def autotuning_enabled(self): return self._config.autotuning_config.get("enabled", False)
+    def autotuning_metric(self): return self._config.autotuning_config.get("metric", "throughput")
+    def get_data_types(self):
+        model_dtype = torch.float16 if self.fp16_enabled() else (torch.bfloat16 if self.bfloat16_enabled() else torch.float32)
+        return model_dtype, self._grad_accum_dtype(model_dtype)
+
+    @property
+    def communication_data_type(self):
+        res = self.__dict__.get("_communication_data_type", None)
+        if res is not None:
+            return res
+        if self._config.communication_data_type is not None:
+            return self._config.communication_data_type
+        if self.fp16_enabled():
+            return torch.float16
+        if self.bfloat16_enabled():
+            return torch.bfloat16
+        return torch.float32
+
+    @communication_data_type.setter
+    def communication_data_type(self, value):
+        self.__dict__["_communication_data_type"] = value
+
+    quantizer = None
+
+    def __getattr__(self, name):
+        """Forward missing attributes to the wrapped module (reference: engine.py:618-631)."""
+        _d = self.__dict__
+        _module = _d.get("module")
+        try:
+            return super().__getattr__(name)
+        except AttributeError:
+            if _module is not None and hasattr(_module, name):
+                return getattr(_module, name)
+            raise
+
+    def destroy(self):
+        if self.optimizer is not None and hasattr(self.optimizer, "destroy"):
+            self.optimizer.destroy()
+        if self.checkpoint_engine is not None and hasattr(self.checkpoint_engine, "cleanup"):
+            self.checkpoint_engine.cleanup()
+
+    def empty_partition_cache(self):
+        if hasattr(self.optimizer, "empty_partition_cache"):
+            self.optimizer.empty_partition_cache()
+            get_accelerator().empty_cache()
+
+    def compile(self, backend=None, compile_kwargs=None, schedule=None):
+        """``torch.compile`` is deliberately not the hot path on B200 (hand-written kernels + CUDA
+        graphs are); kept for API compatibility — compiles the wrapped module's forward."""
+        self.module.compile(backend=backend or "inductor", **(compile_kwargs or {}))
+        self._is_compiled = True
+
+    @property
+    def is_compiled(self):
+        return getattr(self, "_is_compiled", False)
+
+    def offload_states(self, include=None, device="cpu", pin_memory=True, non_blocking=False):
+        from .zero.offload_states import offload_optimizer_states
+        offload_optimizer_states(self.optimizer, include, device, pin_memory, non_blocking)
+
+    def reload_states(self, non_blocking=False):
+        from .zero.offload_states import reload_optimizer_states
+        reload_optimizer_states(self.optimizer, non_blocking)
+
+    # ============================================================================== checkpointing
+    def module_state_dict(self, destination=None, prefix="", keep_vars=False, exclude_frozen_parameters=False):
+        gathered = self._gather_for_state_dict()
+        try:
+            sd = self.module.state_dict(destination=destination, prefix=prefix, keep_vars=keep_vars)
+            sd = OrderedDict((k, v.detach().clone() if gathered and torch.is_tensor(v) else v) for k, v in sd.items())
+        finally:
+            self._release_after_state_dict(gathered)
+        if exclude_frozen_parameters:
+            frozen = {n for n, p in self.module.named_parameters() if not p.requires_grad}
+            for n in frozen:
+                sd.pop(prefix + n, None)
+        return sd
+
+    def _gather_for_state_dict(self):
+        if self.zero_optimization_partition_weights() and hasattr(self.optimizer, "gather_all"):
+            self.optimizer.gather_all()
+            return True
+        return False
+
+    def _release_after_state_dict(self, gathered):
+        if gathered:
+            self.optimizer.release_all()
+
+    def load_module_state_dict(self, checkpoint, strict=True, custom_load_fn=None, fetch_z3_params=False):
+        sd = checkpoint["module"] if isinstance(checkpoint, dict) and "module" in checkpoint else checkpoint
+        if custom_load_fn:
+            custom_load_fn(src=sd, dst=self.module)
+            return
+        gathered = self._gather_for_state_dict()
+        try:
+            self.module.load_state_dict(sd, strict=strict)
+            if gathered:
+                self._scatter_module_into_shards()
+        finally:
+            self._release_after_state_dict(gathered)
+
+    def _scatter_module_into_shards(self):
+        """After loading full weights into gathered ZeRO-3 units, refresh lp/fp32 shards from them."""
+        for fg in self.optimizer.groups:
+            if fg.flat_lp is None:
+                continue
+            sl = fg.flat_lp[fg.rank * fg.part: (fg.rank + 1) * fg.part]
+            if fg.lp_shard.data_ptr() != sl.data_ptr():
+                fg.lp_shard.copy_(sl)
+            fg.hp_param.data.copy_(fg.lp_shard.to(fg.hp_param.device))
+
+    from .checkpointing import (_checkpoint_tag_validation, _get_ckpt_name, _get_zero_ckpt_name, load_checkpoint,  # noqa: E402
+                                save_16bit_model, save_checkpoint, _save_zero_checkpoint, _load_zero_checkpoint,
+                                _get_all_zero_checkpoints, _zero3_consolidated_16bit_state_dict, _get_zero_ckpt_prefix,
+                                _get_expert_ckpt_name, _get_optimizer_ckpt_name, _save_moe_checkpoint,
+                                _commit_decoupled_checkpoint, _copy_recovery_script, _get_rank_zero_ckpt_name)
+    save_fp16_model = save_16bit_model
+
+
+class _DummyOptim(Optimizer):
+    """Placeholder when ZeRO-3 is requested without an optimizer (inference / eval under sharding)."""
+
+    def __init__(self, params):
+        super().__init__([{"params": list(params)}], {})
+
+    def step(self, closure=None):
+        return None
+
+
+DummyOptim = _DummyOptim
+
+
+def _pipeline_module_type():
+    try:
+        from .pipe.module import PipelineModule
+        return PipelineModule
+    except Exception:
+        return ()

@@ -148,7 +148,8 @@ class FlatGroup:
         for i, p in enumerate(self.params):
             if self.trainable[i]:
                 p._sxb_main_grad = self.grad_view(i)
-                p._sxb_grad_written = False
+                if not hasattr(p, "_sxb_grad_written"):
+                    p._sxb_grad_written = False
 
     def detach_main_grads(self):
         for p in self.params:

@@ -52,7 +52,7 @@ class DeepSpeedZeroOptimizer(ShardedOptimizerBase):
                  round_robin_gradients=False, has_moe_layers=False, fp16_master_weights_and_gradients=False,
                  elastic_checkpoint=False, check_grad_overflow=None, dtype=None,
                  method="RR", rings=4, shuffle_step=1, slice_count=2, seed=1234, replica_averaging=True,
-                 fused_replica_averaging=None):
+                 fused_replica_averaging=None, shard_optimizer=True):
         first = next(p for g in init_optimizer.param_groups for p in g["params"])
         lp_dtype = dtype or first.dtype
         super().__init__(init_optimizer, timers=timers, dtype=lp_dtype, static_loss_scale=static_loss_scale,
@@ -89,8 +89,11 @@ class DeepSpeedZeroOptimizer(ShardedOptimizerBase):
                                             slice_count=slice_count, seed=seed, fused=fused_replica_averaging)
             self.dp_process_group = self.averager.slice_pg
         self.method, self.rings, self.shuffle_step, self.slice_count = method, rings, shuffle_step, slice_count
-        self.partition_count_value = dist.get_world_size(self.dp_process_group) if dist.is_initialized() else 1
-        self.partition_rank = dist.get_rank(self.dp_process_group) if dist.is_initialized() else 0
+        if shard_optimizer and dist.is_initialized():
+            self.partition_count_value = dist.get_world_size(self.dp_process_group)
+            self.partition_rank = dist.get_rank(self.dp_process_group)
+        else:
+            self.partition_count_value, self.partition_rank = 1, 0
 
         # ---- flat groups ------------------------------------------------------------------------
         self.bit16_groups: List[List[torch.nn.Parameter]] = []
