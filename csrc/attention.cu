@@ -105,11 +105,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint64_t* q_full = bars + 0;
   uint64_t* k_full = bars + 1;    // [2]
   uint64_t* v_full = bars + 3;    // [2]
-  uint64_t* kv_empty = bars + 5;  // [2]
-  uint64_t* s_full = bars + 7;    // [2]
-  uint64_t* p_full = bars + 9;
-  uint64_t* o_done = bars + 10;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  uint64_t* k_empty = bars + 5;   // [2]  released as soon as S = Q K^T of that block finished
+  uint64_t* v_empty = bars + 7;   // [2]  released when O += P V finished
+  uint64_t* s_full = bars + 9;    // [2]
+  uint64_t* p_full = bars + 11;
+  uint64_t* o_done = bars + 12;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = gridDim.x - 1 - blockIdx.x;  // heavy (late) causal tiles first
@@ -126,8 +127,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (lane == 0) {
       mbar_init(q_full, 1);
       for (int i = 0; i < 2; ++i) {
-        mbar_init(&k_full[i], 1); mbar_init(&v_full[i], 1); mbar_init(&kv_empty[i], 1);
-        mbar_init(&s_full[i], 1);
+        mbar_init(&k_full[i], 1); mbar_init(&v_full[i], 1); mbar_init(&k_empty[i], 1);
+        mbar_init(&v_empty[i], 1); mbar_init(&s_full[i], 1);
       }
       mbar_init(p_full, 128);
       mbar_init(o_done, 1);
@@ -148,17 +149,32 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_expect_tx(q_full, L::kQ);
       for (int hh = 0; hh < NH; ++hh)
         tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, q0, b);
-      for (int j = 0; j < nblk; ++j) {
-        const int st = j & 1;
-        if (!mbar_wait_to(&kv_empty[st], ((j >> 1) & 1) ^ 1, 21)) goto done;
-        mbar_expect_tx(&k_full[st], L::kKV);
-        for (int hh = 0; hh < NH; ++hh)
-          tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &k_full[st], hh * 64, hk,
-                      j * BC, b);
-        mbar_expect_tx(&v_full[st], L::kKV);
-        for (int hh = 0; hh < NH; ++hh)
-          tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &v_full[st], hh * 64, hk,
-                      j * BC, b);
+      // K and V rings advance independently (polling state machine): a K slot is recycled right
+      // after its QK^T, so the next-but-one K tile is in flight ~2 iterations before it is needed.
+      int jk = 0, jv = 0;
+      unsigned long long t0 = global_ns();
+      while (jk < nblk || jv < nblk) {
+        bool progressed = false;
+        if (jk < nblk && mbar_try_wait(&k_empty[jk & 1], ((jk >> 1) & 1) ^ 1)) {
+          const int st = jk & 1;
+          mbar_expect_tx(&k_full[st], L::kKV);
+          for (int hh = 0; hh < NH; ++hh)
+            tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &k_full[st], hh * 64, hk,
+                        jk * BC, b);
+          ++jk;
+          progressed = true;
+        }
+        if (jv < nblk && mbar_try_wait(&v_empty[jv & 1], ((jv >> 1) & 1) ^ 1)) {
+          const int st = jv & 1;
+          mbar_expect_tx(&v_full[st], L::kKV);
+          for (int hh = 0; hh < NH; ++hh)
+            tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &v_full[st], hh * 64, hk,
+                        jv * BC, b);
+          ++jv;
+          progressed = true;
+        }
+        if (progressed) t0 = global_ns();
+        else if (hang_should_abort(t0, 21, jk * 1000 + jv)) goto done;
       }
     }
   } else if (warp == 1) {
@@ -177,6 +193,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           umma_f16(tS + (j & 1) * BC, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, BC, kk),
                    idesc_s, kk != 0);
         umma_commit(&s_full[j & 1]);
+        umma_commit(&k_empty[st]);
         return true;
       };
       if (!mbar_wait_to(q_full, 0, 10)) goto done;
@@ -192,7 +209,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int kk = 0; kk < BC / 16; ++kk)
           umma_f16(tO, desc_kmajor_1(sP, kk), desc_mnmajor(sV, BC, kk), idesc_o,
                    (j | kk) != 0);
-        umma_commit(&kv_empty[st]);
+        umma_commit(&v_empty[st]);
         umma_commit(o_done);
       }
     }
@@ -305,12 +322,14 @@ done:
 }
 
 // ===================================================================== backward: dQ
-// One CTA per (128-query tile, head, batch); loops over 64-key blocks.
+// One CTA per (128-query tile, head, batch); loops over 64-key blocks.  S / dP accumulators are
+// double-buffered in TMEM so the tensor core computes block j+1 while the row threads turn block j
+// into dS; K/V tiles ride a 3-deep TMA ring.
 template <int D>
 struct DqSmem {
   static constexpr int kQ = BQ * D * 2;      // Q and dO tiles
   static constexpr int kKV = BC * D * 2;
-  static constexpr int kStages = 2;
+  static constexpr int kStages = 3;
   static constexpr int kDS = BQ * BC * 2;
   static constexpr int oQ = 0;
   static constexpr int oDO = oQ + kQ;
@@ -328,17 +347,18 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                    const Params p) {
   using L = DqSmem<D>;
   constexpr int NH = D / 64;
+  constexpr int NS = L::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
   uint64_t* q_full = bars + 0;
-  uint64_t* kv_full = bars + 1;   // [2]
-  uint64_t* kv_empty = bars + 3;  // [2]
-  uint64_t* s_full = bars + 5;    // S and dP ready
-  uint64_t* ds_full = bars + 6;   // dS written (128 arrivals)
-  uint64_t* dq_done = bars + 7;   // dQ MMA of block j finished
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* kv_full = bars + 1;   // [3]
+  uint64_t* kv_empty = bars + 4;  // [3]
+  uint64_t* s_full = bars + 7;    // [2] S and dP of buffer b ready
+  uint64_t* ds_full = bars + 9;   // dS written (128 arrivals)
+  uint64_t* dq_done = bars + 10;  // dQ MMA of block j finished
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = gridDim.x - 1 - blockIdx.x;
@@ -351,20 +371,22 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   if (warp == 1) {
     if (lane == 0) {
       mbar_init(q_full, 1);
-      for (int i = 0; i < 2; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1); }
-      mbar_init(s_full, 1);
+      for (int i = 0; i < NS; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1); }
+      mbar_init(&s_full[0], 1);
+      mbar_init(&s_full[1], 1);
       mbar_init(ds_full, 128);
       mbar_init(dq_done, 1);
       mbar_fence_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_slot, 256);
+    tmem_alloc(tmem_slot, 512);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t tS = tmem, tDP = tmem + 64, tDQ = tmem + 128;
+  // buffer b: S at 128*b, dP at 128*b + 64 ; dQ at 256
+  const uint32_t tDQ = tmem + 256;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -374,8 +396,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         tma_load_4d(smem + L::oDO + hh * (BQ * 128), &tmDO, q_full, hh * 64, h, q0, b);
       }
       for (int j = 0; j < nblk; ++j) {
-        const int st = j & 1;
-        if (!mbar_wait_to(&kv_empty[st], ((j >> 1) & 1) ^ 1, 27)) goto done;
+        const int st = j % NS;
+        if (!mbar_wait_to(&kv_empty[st], ((j / NS) & 1) ^ 1, 27, j)) goto done;
         mbar_expect_tx(&kv_full[st], 2 * L::kKV);
         for (int hh = 0; hh < NH; ++hh) {
           tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &kv_full[st], hh * 64, hk,
@@ -391,24 +413,31 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       const uint32_t idesc_dq = make_idesc(BQ, D, 1, 1, 0, 1);
       const uint32_t sQ = smem_u32(smem + L::oQ), sDO = smem_u32(smem + L::oDO);
       const uint32_t sDS = smem_u32(smem + L::oDS);
-      if (!mbar_wait_to(q_full, 0, 28)) goto done;
-      for (int j = 0; j < nblk; ++j) {
-        const int st = j & 1;
-        if (!mbar_wait_to(&kv_full[st], (j >> 1) & 1, 29)) goto done;
-        // S / dP TMEM columns were last read by the row threads before ds_full(j-1), which
-        // this thread waited on in the previous iteration.
+      auto issue_sdp = [&](int j) -> bool {
+        const int st = j % NS;
+        if (!mbar_wait_to(&kv_full[st], (j / NS) & 1, 29, j)) return false;
         tc_fence_after();
         const uint32_t sK = smem_u32(smem + L::oK + st * L::kKV);
         const uint32_t sV = smem_u32(smem + L::oV + st * L::kKV);
+        const uint32_t tS = tmem + (j & 1) * 128, tDP = tS + 64;
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tS, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, BC, kk), idesc_s, kk != 0);
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tDP, desc_kmajor_d(sDO, BQ, kk), desc_kmajor_d(sV, BC, kk), idesc_s, kk != 0);
-        umma_commit(s_full);
-        if (!mbar_wait_to(ds_full, j & 1, 30)) goto done;
+        umma_commit(&s_full[j & 1]);
+        return true;
+      };
+      if (!mbar_wait_to(q_full, 0, 28)) goto done;
+      if (!issue_sdp(0)) goto done;
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j % NS;
+        // buffer (j+1)&1 was last read for block j-1, whose ds_full this thread already waited on
+        if (j + 1 < nblk && !issue_sdp(j + 1)) goto done;
+        if (!mbar_wait_to(ds_full, j & 1, 30, j)) goto done;
         tc_fence_after();
+        const uint32_t sK = smem_u32(smem + L::oK + st * L::kKV);
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
           umma_f16(tDQ, desc_kmajor_1(sDS, kk), desc_mnmajor(sK, BC, kk), idesc_dq,
@@ -428,20 +457,30 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const float dlt = p.delta[stat_idx];
     uint8_t* sDS = smem + L::oDS;
     for (int j = 0; j < nblk; ++j) {
-      if (!mbar_wait_to(s_full, j & 1, 31)) goto done;
+      if (!mbar_wait_to(&s_full[j & 1], (j >> 1) & 1, 31, j)) goto done;
       tc_fence_after();
       float s[64], dp[64];
-      ld_row64(tS + lane_off, s);
-      ld_row64(tDP + lane_off, dp);
+      const uint32_t tS = tmem + (j & 1) * 128 + lane_off;
+      ld_row64(tS, s);
+      ld_row64(tS + 64, dp);
       const int k0 = j * BC;
+      const bool need_mask = (p.causal && (k0 + BC - 1 > q0)) || (k0 + BC > p.S) || (q0 + BQ > p.S);
+      if (need_mask) {
 #pragma unroll
-      for (int c = 0; c < 64; ++c) {
-        const int kp = k0 + c;
-        const bool ok = (kp < p.S) && (!p.causal || kp <= qpos) && (qpos < p.S);
-        const float pr = ok ? fast_exp2(s[c] * sc - lse2) : 0.f;
-        s[c] = pr * (dp[c] - dlt) * p.scale;
+        for (int c = 0; c < 64; ++c) {
+          const int kp = k0 + c;
+          const bool ok = (kp < p.S) && (!p.causal || kp <= qpos) && (qpos < p.S);
+          const float pr = ok ? fast_exp2(fmaf(s[c], sc, -lse2)) : 0.f;
+          s[c] = pr * (dp[c] - dlt) * p.scale;
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 64; ++c) {
+          const float pr = fast_exp2(fmaf(s[c], sc, -lse2));
+          s[c] = pr * (dp[c] - dlt) * p.scale;
+        }
       }
-      if (j > 0) if (!mbar_wait_to(dq_done, (j - 1) & 1, 32)) goto done;  // previous dQ MMA no longer reads sDS
+      if (j > 0) if (!mbar_wait_to(dq_done, (j - 1) & 1, 32, j)) goto done;  // dQ(j-1) no longer reads sDS
       store_row_sw128(sDS, row, s);
       fence_async_smem();
       tc_fence_before();
@@ -474,18 +513,20 @@ done:
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem, 256);
+    tmem_dealloc(tmem, 512);
   }
 }
 
 // ================================================================== backward: dK, dV
-// One CTA per (128-key tile, kv head, batch); loops over the q heads of the GQA group
-// and over 64-query blocks.  Row threads own KEY rows (transposed formulation).
+// One CTA per (128-key tile, kv head, batch); loops over the q heads of the GQA group and over
+// 64-query blocks.  Row threads own KEY rows (transposed formulation).  S^T / dP^T are
+// double-buffered in TMEM, Q/dO tiles ride a 3-deep TMA ring, per-query statistics are prefetched
+// one iteration ahead.
 template <int D>
 struct DkvSmem {
   static constexpr int kKV = BQ * D * 2;   // K and V tiles (128 keys)
   static constexpr int kQ = BC * D * 2;    // Q_i / dO_i tiles (64 queries)
-  static constexpr int kStages = 2;
+  static constexpr int kStages = 3;
   static constexpr int kPT = BQ * BC * 2;  // P^T / dS^T tiles
   static constexpr int oK = 0;
   static constexpr int oV = oK + kKV;
@@ -505,17 +546,18 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                     const Params p) {
   using L = DkvSmem<D>;
   constexpr int NH = D / 64;
+  constexpr int NS = L::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
   uint64_t* kv_full = bars + 0;
-  uint64_t* q_full = bars + 1;    // [2]
-  uint64_t* q_empty = bars + 3;   // [2]
-  uint64_t* s_full = bars + 5;
-  uint64_t* pt_full = bars + 6;   // 128 arrivals
-  uint64_t* acc_done = bars + 7;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* q_full = bars + 1;    // [3]
+  uint64_t* q_empty = bars + 4;   // [3]
+  uint64_t* s_full = bars + 7;    // [2]
+  uint64_t* pt_full = bars + 9;   // 128 arrivals
+  uint64_t* acc_done = bars + 10;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kt = blockIdx.x;
@@ -530,8 +572,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   if (warp == 1) {
     if (lane == 0) {
       mbar_init(kv_full, 1);
-      for (int i = 0; i < 2; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
-      mbar_init(s_full, 1);
+      for (int i = 0; i < NS; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
+      mbar_init(&s_full[0], 1);
+      mbar_init(&s_full[1], 1);
       mbar_init(pt_full, 128);
       mbar_init(acc_done, 1);
       mbar_fence_init();
@@ -543,7 +586,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t tST = tmem, tDPT = tmem + 64, tDV = tmem + 128, tDK = tmem + 256;
+  // buffer b: S^T at 128*b, dP^T at 128*b + 64 ; dV at 256 ; dK at 384
+  const uint32_t tDV = tmem + 256, tDK = tmem + 384;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -553,10 +597,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tma_load_4d(smem + L::oV + hh * (BQ * 128), &tmV, kv_full, hh * 64, hk, n0, b);
       }
       for (int it = 0; it < niter; ++it) {
-        const int st = it & 1;
+        const int st = it % NS;
         const int h = hk * group + it / per_head;
         const int qi = i_start + it % per_head;
-        if (!mbar_wait_to(&q_empty[st], ((it >> 1) & 1) ^ 1, 34)) goto done;
+        if (!mbar_wait_to(&q_empty[st], ((it / NS) & 1) ^ 1, 34, it)) goto done;
         mbar_expect_tx(&q_full[st], 2 * L::kQ);
         for (int hh = 0; hh < NH; ++hh) {
           tma_load_4d(smem + L::oQ + st * L::kQ + hh * (BC * 128), &tmQ, &q_full[st], hh * 64, h,
@@ -572,22 +616,31 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const uint32_t idesc_acc = make_idesc(BQ, D, 1, 1, 0, 1);
       const uint32_t sK = smem_u32(smem + L::oK), sV = smem_u32(smem + L::oV);
       const uint32_t sPT = smem_u32(smem + L::oPT), sDST = smem_u32(smem + L::oDST);
-      if (!mbar_wait_to(kv_full, 0, 35)) goto done;
-      for (int it = 0; it < niter; ++it) {
-        const int st = it & 1;
-        if (!mbar_wait_to(&q_full[st], (it >> 1) & 1, 36)) goto done;
+      auto issue_first = [&](int it) -> bool {
+        const int st = it % NS;
+        if (!mbar_wait_to(&q_full[st], (it / NS) & 1, 36, it)) return false;
         tc_fence_after();
         const uint32_t sQ = smem_u32(smem + L::oQ + st * L::kQ);
         const uint32_t sDO = smem_u32(smem + L::oDO + st * L::kQ);
+        const uint32_t tST = tmem + (it & 1) * 128, tDPT = tST + 64;
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tST, desc_kmajor_d(sK, BQ, kk), desc_kmajor_d(sQ, BC, kk), idesc_s, kk != 0);
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tDPT, desc_kmajor_d(sV, BQ, kk), desc_kmajor_d(sDO, BC, kk), idesc_s, kk != 0);
-        umma_commit(s_full);
-        if (!mbar_wait_to(pt_full, it & 1, 37)) goto done;
+        umma_commit(&s_full[it & 1]);
+        return true;
+      };
+      if (!mbar_wait_to(kv_full, 0, 35)) goto done;
+      if (niter > 0 && !issue_first(0)) goto done;
+      for (int it = 0; it < niter; ++it) {
+        const int st = it % NS;
+        if (it + 1 < niter && !issue_first(it + 1)) goto done;
+        if (!mbar_wait_to(pt_full, it & 1, 37, it)) goto done;
         tc_fence_after();
+        const uint32_t sQ = smem_u32(smem + L::oQ + st * L::kQ);
+        const uint32_t sDO = smem_u32(smem + L::oDO + st * L::kQ);
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
           umma_f16(tDV, desc_kmajor_1(sPT, kk), desc_mnmajor(sDO, BC, kk), idesc_acc,
@@ -610,35 +663,47 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     float* stat = reinterpret_cast<float*>(smem + L::oStat);
     uint8_t* sPT = smem + L::oPT;
     uint8_t* sDST = smem + L::oDST;
-    for (int it = 0; it < niter; ++it) {
-      const int st = it & 1;
+    auto load_stat = [&](int it) -> float {
       const int h = hk * group + it / per_head;
-      const int qi = i_start + it % per_head;
-      const int qb = qi * BC;
-      // stage per-query statistics for this block (64 lse + 64 delta)
-      {
-        const int c = et & 63;
-        const int qq = min(qb + c, p.S - 1);
-        const long long si = ((long long)b * p.Hq + h) * p.S + qq;
-        stat[st * 128 + et] = (et < 64) ? p.lse[si] * kLog2e : p.delta[si];
-      }
+      const int qb = (i_start + it % per_head) * BC;
+      const int qq = min(qb + (et & 63), p.S - 1);
+      const long long si = ((long long)b * p.Hq + h) * p.S + qq;
+      return (et < 64) ? p.lse[si] * kLog2e : p.delta[si];
+    };
+    float nxt = (niter > 0) ? load_stat(0) : 0.f;
+    for (int it = 0; it < niter; ++it) {
+      const int st = it % NS;
+      const int qb = (i_start + it % per_head) * BC;
+      stat[st * 128 + et] = nxt;
+      if (it + 1 < niter) nxt = load_stat(it + 1);     // prefetch: consumed next iteration
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (!mbar_wait_to(s_full, it & 1, 38)) goto done;
+      if (!mbar_wait_to(&s_full[it & 1], (it >> 1) & 1, 38, it)) goto done;
       tc_fence_after();
       float s[64], dp[64];
-      ld_row64(tST + lane_off, s);
-      ld_row64(tDPT + lane_off, dp);
+      const uint32_t tST = tmem + (it & 1) * 128 + lane_off;
+      ld_row64(tST, s);
+      ld_row64(tST + 64, dp);
       const float* lse2 = stat + st * 128;
       const float* dlt = lse2 + 64;
+      const bool need_mask = (p.causal && (n0 + BQ - 1 > qb)) || (qb + BC > p.S) || (n0 + BQ > p.S);
+      if (need_mask) {
 #pragma unroll
-      for (int c = 0; c < 64; ++c) {
-        const int qp = qb + c;
-        const bool ok = (qp < p.S) && (kpos < p.S) && (!p.causal || kpos <= qp);
-        const float pr = ok ? fast_exp2(s[c] * sc - lse2[c]) : 0.f;
-        s[c] = pr;                                    // P^T
-        dp[c] = pr * (dp[c] - dlt[c]) * p.scale;      // dS^T (already scaled)
+        for (int c = 0; c < 64; ++c) {
+          const int qp = qb + c;
+          const bool ok = (qp < p.S) && (kpos < p.S) && (!p.causal || kpos <= qp);
+          const float pr = ok ? fast_exp2(fmaf(s[c], sc, -lse2[c])) : 0.f;
+          s[c] = pr;                                    // P^T
+          dp[c] = pr * (dp[c] - dlt[c]) * p.scale;      // dS^T (already scaled)
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 64; ++c) {
+          const float pr = fast_exp2(fmaf(s[c], sc, -lse2[c]));
+          s[c] = pr;
+          dp[c] = pr * (dp[c] - dlt[c]) * p.scale;
+        }
       }
-      if (it > 0) if (!mbar_wait_to(acc_done, (it - 1) & 1, 39)) goto done;
+      if (it > 0) if (!mbar_wait_to(acc_done, (it - 1) & 1, 39, it)) goto done;
       store_row_sw128(sPT, row, s);
       store_row_sw128(sDST, row, dp);
       fence_async_smem();

@@ -416,3 +416,21 @@ __device__ __forceinline__ bool mbar_wait_to(uint64_t* bar, uint32_t parity, uin
     e = cudaMemcpyToSymbol(sxb::g_sxb_hang, z, sizeof(z));                                   \
     return e == cudaSuccess ? SXB_OK : (int)e;                                               \
   }
+
+// ---- appended: watchdog helper for polling state machines ------------------------------------
+namespace sxb {
+// Returns true when the caller should abandon its loop: either another waiter already raised the
+// abort flag or `t0` is more than ~2 s in the past (then this thread records the hang).
+__device__ __forceinline__ bool hang_should_abort(unsigned long long t0, uint32_t tag, uint32_t aux) {
+  if (*reinterpret_cast<volatile unsigned int*>(&g_sxb_hang[0]) != 0) return true;
+  if (global_ns() - t0 > 2000000000ull) {
+    if (atomicCAS(&g_sxb_hang[0], 0u, 1u) == 0u) {
+      g_sxb_hang[1] = tag; g_sxb_hang[2] = blockIdx.x; g_sxb_hang[3] = blockIdx.y;
+      g_sxb_hang[4] = blockIdx.z; g_sxb_hang[5] = threadIdx.x; g_sxb_hang[6] = 0; g_sxb_hang[7] = aux;
+      __threadfence();
+    }
+    return true;
+  }
+  return false;
+}
+}  // namespace sxb

@@ -1,0 +1,115 @@
+"""ZeRO-1/2/3 on CPU/gloo: sharded training must match an unsharded fp32-master AdamW run."""
+import copy
+
+import pytest
+import torch
+
+from conftest import run_dist
+
+
+def _cfg(stage, gas=1, clip=0.0, extra=None):
+    c = {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": gas, "steps_per_print": 10 ** 9,
+         "bf16": {"enabled": True}, "gradient_clipping": clip,
+         "optimizer": {"type": "AdamW", "params": {"lr": 5e-3, "betas": [0.9, 0.95], "weight_decay": 0.05}},
+         "zero_optimization": {"stage": stage}}
+    if extra:
+        c["zero_optimization"].update(extra)
+    return c
+
+
+def _reference_run(model, batches, gas, clip, steps):
+    """Plain PyTorch: bf16 forward weights, fp32 master, AdamW, mean gradient over all micro-batches."""
+    master = [p.detach().float().clone().requires_grad_() for p in model.parameters()]
+    opt = torch.optim.AdamW(master, lr=5e-3, betas=(0.9, 0.95), weight_decay=0.05)
+    it = iter(batches)
+    for _ in range(steps):
+        for p, m in zip(model.parameters(), master):
+            p.data = m.detach().to(torch.bfloat16)
+        model.zero_grad()
+        group = [next(it) for _ in range(gas)]
+        n = sum(len(g) for g in group)
+        for micro in group:
+            for ids in micro:                      # one entry per data-parallel rank
+                (model(ids, labels=ids) / n).backward()
+        for p, m in zip(model.parameters(), master):
+            m.grad = p.grad.float()
+        if clip > 0:
+            torch.nn.utils.clip_grad_norm_(master, clip)
+        opt.step()
+    return [m.detach() for m in master]
+
+
+def _worker(rank, world, stage, gas, clip):
+    import shuffle_exchange_b200 as ds
+    from shuffle_exchange_b200.models import GPT2LMHeadModel, gpt2_config
+    from shuffle_exchange_b200.utils.tensor_fragment import safe_get_full_fp32_param
+    torch.manual_seed(0)
+    model = GPT2LMHeadModel(gpt2_config("gpt2-tiny"))
+    ref_model = copy.deepcopy(model).to(torch.bfloat16)
+    steps = 3
+    g = torch.Generator().manual_seed(5)
+    batches = [[torch.randint(0, 512, (2, 16), generator=g) for _ in range(world)] for _ in range(steps * gas)]
+    engine, opt, _, _ = ds.initialize(model=model, config=_cfg(stage, gas, clip), model_parameters=model.parameters(),
+                                      slice_count=world)
+    for micro in batches:
+        loss = engine(micro[rank], labels=micro[rank])
+        engine.backward(loss)
+        engine.step()
+    want = _reference_run(ref_model, batches, gas, clip, steps)
+    for (n, p), w in zip(engine.module.named_parameters(), want):
+        got = safe_get_full_fp32_param(p)
+        err = (got.cpu() - w).abs().max().item()
+        assert err < 2e-3, (stage, n, err)
+
+
+@pytest.mark.parametrize("stage,gas,clip", [(1, 2, 1.0), (2, 2, 0.0), (3, 1, 0.0), (3, 2, 0.5)])
+def test_zero_matches_unsharded(stage, gas, clip):
+    run_dist(_worker, 2, (stage, gas, clip))
+
+
+def _fragment_worker(rank, world):
+    import shuffle_exchange_b200 as ds
+    from shuffle_exchange_b200.models import GPT2LMHeadModel, gpt2_config
+    from shuffle_exchange_b200.utils import tensor_fragment as tf
+    torch.manual_seed(0)
+    model = GPT2LMHeadModel(gpt2_config("gpt2-tiny"))
+    want = {n: p.detach().to(torch.bfloat16).float().clone() for n, p in model.named_parameters()}
+    engine, opt, _, _ = ds.initialize(model=model, config=_cfg(3), model_parameters=model.parameters())
+    for n, p in engine.module.named_parameters():
+        assert torch.equal(tf.safe_get_full_fp32_param(p).cpu(), want[n]), n
+    p = next(engine.module.parameters())
+    tf.safe_set_full_fp32_param(p, torch.full_like(want["wte"], 0.25))
+    assert torch.all(tf.safe_get_full_fp32_param(p) == 0.25)
+    ids = torch.randint(0, 512, (2, 16))
+    engine.backward(engine(ids, labels=ids))
+    engine.step()
+    assert tf.safe_get_full_optimizer_state(p, "exp_avg").shape == want["wte"].shape
+    with ds.zero.GatheredParameters(list(engine.module.parameters()), modifier_rank=0):
+        if rank == 0:
+            engine.module.ln_f_w.data.fill_(3.0)
+    assert torch.all(tf.safe_get_full_fp32_param(engine.module.ln_f_w) == 3.0)
+
+
+def test_fragment_api_and_gathered_parameters():
+    run_dist(_fragment_worker, 2)
+
+
+def _zero_init_worker(rank, world):
+    import shuffle_exchange_b200 as ds
+    from shuffle_exchange_b200.models import GPT2LMHeadModel, gpt2_config
+    with ds.zero.Init(dtype=torch.bfloat16):
+        model = GPT2LMHeadModel(gpt2_config("gpt2-tiny"))
+    assert all(p.numel() == 0 and p.ds_tensor is not None for p in model.parameters())
+    engine, _, _, _ = ds.initialize(model=model, config=_cfg(3), model_parameters=model.parameters())
+    ids = torch.randint(0, 512, (2, 16))
+    l0 = None
+    for _ in range(4):
+        loss = engine(ids, labels=ids)
+        engine.backward(loss)
+        engine.step()
+        l0 = l0 or loss.item()
+    assert loss.item() < l0
+
+
+def test_zero_init_context():
+    run_dist(_zero_init_worker, 2)

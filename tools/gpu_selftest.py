@@ -441,6 +441,115 @@ def _():
     return {"fwd_ms": ms_f, "fwd_bwd_ms": ms_fb, "est_step_ms_32_layers_recompute": 32 * (ms_f + ms_fb)}
 
 
+@check("attn_long_vs_sdpa")
+def _():
+    import torch
+    from shuffle_exchange_b200.native import lib as n
+    from shuffle_exchange_b200.ops import functional as F
+    torch.manual_seed(0)
+    out = {}
+    for (B, S, Hq, Hk, D) in [(1, 8192, 4, 2, 128), (2, 4096, 4, 1, 64)]:
+        qkv = torch.randn(B, S, (Hq + 2 * Hk) * D, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+        q = qkv[..., : Hq * D].view(B, S, Hq, D)
+        k = qkv[..., Hq * D: (Hq + Hk) * D].view(B, S, Hk, D)
+        v = qkv[..., (Hq + Hk) * D:].view(B, S, Hk, D)
+        o = F.flash_attention(q, k, v, True)
+        g = torch.randn_like(o)
+        (dqkv,) = torch.autograd.grad(o, qkv, g)
+        hi = n.hang_info("attn")
+        if hi:
+            return {"ok": False, "hang": hi}
+        q2, k2, v2 = (t.detach().float().transpose(1, 2).contiguous().requires_grad_() for t in (q, k, v))
+        o2 = torch.nn.functional.scaled_dot_product_attention(q2, k2, v2, is_causal=True, enable_gqa=True)
+        o2.backward(g.float().transpose(1, 2))
+        ref = torch.cat([q2.grad.transpose(1, 2).reshape(B, S, -1), k2.grad.transpose(1, 2).reshape(B, S, -1),
+                         v2.grad.transpose(1, 2).reshape(B, S, -1)], -1)
+        out[f"{B}x{S}x{Hq}x{Hk}x{D}"] = {"fwd": _rel_err(o, o2.transpose(1, 2)), "bwd": _rel_err(dqkv, ref)}
+    return {"err": max(v for d in out.values() for v in d.values()), "detail": out}
+
+
+@check("llama_train_parity")
+def _():
+    """5 optimizer steps through the engine (bf16, ZeRO-3, fused AdamW in backward) vs the fp32
+    PyTorch oracle with torch.optim.AdamW: loss curves must track."""
+    import os
+    import torch
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT="29577", RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    import shuffle_exchange_b200 as sxb
+    from shuffle_exchange_b200.models.llama import LlamaForCausalLM, llama_config, reference_forward
+    torch.manual_seed(0)
+    cfg = llama_config("llama-tiny", hidden_size=512, num_attention_heads=4, num_key_value_heads=2)
+    model = LlamaForCausalLM(cfg, device="cuda", dtype=torch.bfloat16)
+    ref = LlamaForCausalLM(cfg, device="cuda", dtype=torch.float32)
+    ref.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
+    ref.cfg.activation_checkpointing = False
+    hp = dict(lr=2e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    engine, _, _, _ = sxb.initialize(model=model, model_parameters=model.parameters(), config={
+        "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "steps_per_print": 1 << 30,
+        "optimizer": {"type": "AdamW", "params": dict(lr=hp["lr"], betas=list(hp["betas"]), eps=hp["eps"],
+                                                        weight_decay=hp["weight_decay"])},
+        "zero_optimization": {"stage": 3}})
+    params = list(ref.parameters())
+    opt = torch.optim.AdamW(params, **hp)
+    g = torch.Generator(device="cpu").manual_seed(1)
+    ours, theirs = [], []
+    for step in range(6):
+        ids = torch.randint(0, cfg.vocab_size, (2, 256), generator=g).cuda()
+        loss = engine(ids, labels=ids)
+        engine.backward(loss)
+        engine.step()
+        ours.append(float(loss))
+        opt.zero_grad()
+        # differentiable oracle: run reference_forward on live parameters
+        sd_live = dict(ref.named_parameters())
+        lref = _oracle_loss(ref, ids)
+        lref.backward()
+        opt.step()
+        theirs.append(float(lref))
+    err = max(abs(a - b) / abs(b) for a, b in zip(ours, theirs))
+    return {"err": err, "ours": ours, "oracle": theirs}
+
+
+def _oracle_loss(model, ids):
+    """fp32 autograd version of models.llama.reference_forward (same math, live parameters)."""
+    import torch
+    from shuffle_exchange_b200.ops import functional as F
+    cfg = model.cfg
+    P = dict(model.named_parameters())
+    B, S = ids.shape
+    d, nq, nk, f = cfg.head_dim, cfg.num_attention_heads, cfg.num_key_value_heads, cfg.intermediate_size
+    h = P["model.embed_tokens"][ids]
+    inv = 1.0 / (cfg.rope_theta ** (torch.arange(0, d, 2, dtype=torch.float64, device=h.device) / d))
+    ang = torch.outer(torch.arange(S, dtype=torch.float64, device=h.device), inv)
+    cos, sin = ang.cos().float(), ang.sin().float()
+
+    def rms(x, w):
+        return x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + cfg.rms_norm_eps) * w
+
+    def rot(x):
+        a, b = x[..., : d // 2], x[..., d // 2:]
+        c, s = cos[None, :, None, :], sin[None, :, None, :]
+        return torch.cat([a * c - b * s, b * c + a * s], -1)
+
+    for i in range(cfg.num_hidden_layers):
+        p = f"model.layers.{i}."
+        x = rms(h, P[p + "input_layernorm"])
+        qkv = x @ P[p + "wqkv"].t()
+        q = rot(qkv[..., : nq * d].view(B, S, nq, d))
+        k = rot(qkv[..., nq * d: (nq + nk) * d].view(B, S, nk, d))
+        v = qkv[..., (nq + nk) * d:].view(B, S, nk, d)
+        o = F.attention_ref(q, k, v, True)
+        h = h + o.reshape(B, S, nq * d) @ P[p + "wo"].t()
+        x = rms(h, P[p + "post_attention_layernorm"])
+        gu = x @ P[p + "w_gate_up"].t()
+        h = h + (torch.nn.functional.silu(gu[..., :f]) * gu[..., f:]) @ P[p + "w_down"].t()
+    x = rms(h, P["model.norm"])
+    logits = x @ P["lm_head"].t()
+    tgt = torch.full_like(ids, -100)
+    tgt[:, :-1] = ids[:, 1:]
+    return torch.nn.functional.cross_entropy(logits.view(-1, logits.shape[-1]), tgt.view(-1), ignore_index=-100)
+
+
 def main():
     if len(sys.argv) >= 3 and sys.argv[1] == "--one":
         name = sys.argv[2]
