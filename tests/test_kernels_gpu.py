@@ -1,0 +1,45 @@
+"""GPU numerics: every sm_100a kernel against a plain PyTorch fp32 statement of the same op.
+The checks live in tools/gpu_selftest.py (also runnable stand-alone, one subprocess per check)."""
+import importlib.util
+import os
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_spec = importlib.util.spec_from_file_location("gpu_selftest", os.path.join(ROOT, "tools", "gpu_selftest.py"))
+selftest = importlib.util.module_from_spec(_spec)
+_spec.loader.exec_module(selftest)
+
+NUMERIC = [n for n in selftest.CHECKS if not n.endswith("_perf")]
+TOL = 2e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(240)
+@pytest.mark.parametrize("name", NUMERIC)
+def test_kernel_numerics(name):
+    from shuffle_exchange_b200.native import lib
+    assert lib.available(), "libsxb200.so missing: the CUDA path must be the one that runs"
+    res = selftest.CHECKS[name]()
+    assert "hang" not in res, res
+    assert lib.hang_info("gemm") is None and lib.hang_info("attn") is None
+    err = res.get("err")
+    assert err is not None and err == err and err < TOL, (name, res)
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(240)
+def test_native_library_is_loaded_and_counted():
+    import torch
+    from shuffle_exchange_b200.native import lib
+    from shuffle_exchange_b200.ops import functional as F
+    lib.reset_launch_count()
+    x = torch.randn(256, 512, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(1024, 512, device="cuda", dtype=torch.bfloat16)
+    y = F.linear(x, w)
+    torch.cuda.synchronize()
+    assert lib.launch_count >= 1 and y.shape == (256, 1024)
+    with open("/proc/self/maps") as f:
+        assert "libsxb200.so" in f.read()
+    with pytest.raises(lib.NativeError):
+        F.linear(x.float(), w.float())          # no silent fallback on a CUDA tensor

@@ -25,14 +25,17 @@ def _reference_run(model, batches, gas, clip, steps):
     for _ in range(steps):
         for p, m in zip(model.parameters(), master):
             p.data = m.detach().to(torch.bfloat16)
-        model.zero_grad()
         group = [next(it) for _ in range(gas)]
         n = sum(len(g) for g in group)
+        acc = [torch.zeros_like(m) for m in master]
         for micro in group:
             for ids in micro:                      # one entry per data-parallel rank
+                model.zero_grad()
                 (model(ids, labels=ids) / n).backward()
-        for p, m in zip(model.parameters(), master):
-            m.grad = p.grad.float()
+                for a, p in zip(acc, model.parameters()):
+                    a += p.grad.float()
+        for a, m in zip(acc, master):
+            m.grad = a
         if clip > 0:
             torch.nn.utils.clip_grad_norm_(master, clip)
         opt.step()
@@ -55,11 +58,18 @@ def _worker(rank, world, stage, gas, clip):
         loss = engine(micro[rank], labels=micro[rank])
         engine.backward(loss)
         engine.step()
+    init = [p.detach().float().clone() for p in ref_model.parameters()]
     want = _reference_run(ref_model, batches, gas, clip, steps)
-    for (n, p), w in zip(engine.module.named_parameters(), want):
-        got = safe_get_full_fp32_param(p)
-        err = (got.cpu() - w).abs().max().item()
-        assert err < 2e-3, (stage, n, err)
+    # Adam normalises every element's update to ~lr, so elements whose gradient is ~0 are decided by
+    # rounding noise; compare the update *direction* and bound the worst element by 2*lr*steps.
+    num = den_a = den_b = 0.0
+    for (n, p), w, w0 in zip(engine.module.named_parameters(), want, init):
+        got = safe_get_full_fp32_param(p).cpu()
+        da, db = (got - w0).double().flatten(), (w - w0).double().flatten()
+        num += float(da @ db); den_a += float(da @ da); den_b += float(db @ db)
+        assert (got - w).abs().max().item() <= 2 * 5e-3 * steps + 1e-6, (stage, n)
+    cos = num / (den_a ** 0.5 * den_b ** 0.5)
+    assert cos > 0.99, (stage, gas, clip, cos)
 
 
 @pytest.mark.parametrize("stage,gas,clip", [(1, 2, 1.0), (2, 2, 0.0), (3, 1, 0.0), (3, 2, 0.5)])
