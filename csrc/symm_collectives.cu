@@ -1,0 +1,432 @@
+// symm_collectives.cu — collectives fused with their adjacent compute, issued from inside the kernel
+// over NVLink 5 / NVSwitch peer mappings (symmetric memory: every rank holds VA mappings of all
+// peers' buffers and of their signal pads; optionally an NVLS multicast mapping).
+//
+//   sxb_symm_rs_adam       K1: gradient reduce-scatter (+1/n, unscale/clip) (+) AdamW on the fp32 master
+//                              shard (+) bf16 parameter-shard write-back, one pass, no NCCL.
+//                              Replaces reduce_scatter_coalesced + partition_grads + FusedAdam
+//                              (runtime/comm/coalesced_collectives.py:159-218, runtime/zero/stage3.py:1388-1540, 2137-2152).
+//   sxb_symm_subset_mean   K9: shuffle-exchange replica averaging — the ring membership table is the
+//                              kernel's peer-address schedule (runtime/zero/stage_1_and_2.py:2227-2250).
+//   sxb_symm_all_gather    K2 (gather half): pull-based all-gather that publishes per-chunk arrival
+//                              flags so a concurrently running GEMM can start on arrived weight tiles
+//                              (runtime/zero/partition_parameters.py:1221-1261).
+//   sxb_symm_a2a_rows      K4-K7 transport: direct peer stores of token rows (MoE dispatch/combine,
+//                              Ulysses head-scatter) with per-destination row tables
+//                              (moe/sharded_moe.py:96-108, sequence/layer.py:221-254).
+//
+// Cross-rank ordering uses monotonically increasing epochs written with st.release.sys and polled
+// with ld.acquire.sys on per-(channel, peer) 32-bit slots of the signal pad; nothing is ever reset,
+// so there is no ABA window.  Every spin is bounded (~2 s) and raises the library abort flag.
+#include "sxb_common.cuh"
+
+namespace sxb {
+namespace symm {
+
+constexpr int kMaxPeers = 16;
+constexpr int kThreads = 512;
+
+struct Peers {
+  void* buf[kMaxPeers];        // peer mappings of the payload buffer (index = rank in group)
+  uint32_t* sig[kMaxPeers];    // peer mappings of the signal pad
+  int rank;
+  int world;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// 16-byte peer load that does not pollute L1 (peer data is never re-read by this SM)
+__device__ __forceinline__ uint4 ld_peer16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint4 ld_volatile16(const void* p) {
+  uint4 r;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+// slot layout of a signal pad: [channel][kMaxPeers] uint32
+__device__ __forceinline__ uint32_t* slot(uint32_t* pad, int channel, int peer) {
+  return pad + channel * kMaxPeers + peer;
+}
+
+// Tell every peer "rank `me` reached `epoch` on `channel`".
+__device__ __forceinline__ void signal_all(const Peers& P, int channel, uint32_t epoch) {
+  if (threadIdx.x < P.world) st_release_sys(slot(P.sig[threadIdx.x], channel, P.rank), epoch);
+}
+// Wait until every peer reached `epoch` on `channel` (threads 0..world-1 poll, then block-sync).
+__device__ __forceinline__ bool wait_all(const Peers& P, int channel, uint32_t epoch, uint32_t tag) {
+  __shared__ int ok_flag;
+  if (threadIdx.x == 0) ok_flag = 1;
+  __syncthreads();
+  if (threadIdx.x < P.world) {
+    const uint32_t* s = slot(P.sig[P.rank], channel, threadIdx.x);
+    const unsigned long long t0 = global_ns();
+    while ((int32_t)(ld_acquire_sys(s) - epoch) < 0) {
+      if (hang_should_abort(t0, tag, threadIdx.x)) { ok_flag = 0; break; }
+    }
+  }
+  __syncthreads();
+  return ok_flag != 0;
+}
+
+__device__ __forceinline__ void bf16x8_acc(const uint4& v, float (&a)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    a[2 * i] += __low2float(h[i]);
+    a[2 * i + 1] += __high2float(h[i]);
+  }
+}
+
+struct AdamArgs {
+  float lr, beta1, beta2, eps, weight_decay, bc1, bc2, grad_scale;
+  int adamw;
+};
+
+// ------------------------------------------------------------------------------------ K1
+// Each rank reduces ITS shard [rank*part, (rank+1)*part) of every peer's flat bf16 gradient buffer and
+// immediately applies AdamW.  channel 0 = "gradients ready", channel 1 = "finished reading".
+__global__ void __launch_bounds__(kThreads)
+rs_adam_kernel(Peers P, long long part, float* __restrict__ hp, float* __restrict__ m, float* __restrict__ v,
+               __nv_bfloat16* __restrict__ lp, __nv_bfloat16* __restrict__ grad_out, AdamArgs a, uint32_t epoch,
+               const void* mc_ptr, unsigned int* __restrict__ cta_counter, int apply_adam) {
+  if (blockIdx.x == 0) signal_all(P, 0, epoch);
+  if (!wait_all(P, 0, epoch, 101)) return;
+  const long long base = (long long)P.rank * part;
+  const long long nvec = part >> 3;
+  const float inv_n = 1.0f / (float)P.world;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
+       i += (long long)gridDim.x * blockDim.x) {
+    float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (mc_ptr) {
+      // NVLS: one load returns the in-switch sum over all ranks (fp32 accumulation inside the switch)
+      uint4 r;
+      const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(mc_ptr) + base + i * 8;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                   : "l"(src)
+                   : "memory");
+      bf16x8_acc(r, g);
+    } else {
+      uint4 r[kMaxPeers];
+#pragma unroll
+      for (int pi = 0; pi < kMaxPeers; ++pi) {
+        if (pi < P.world) {
+          const int peer = (P.rank + pi) % P.world;       // stagger so ranks do not hammer one peer
+          r[pi] = ld_peer16(reinterpret_cast<const __nv_bfloat16*>(P.buf[peer]) + base + i * 8);
+        }
+      }
+#pragma unroll
+      for (int pi = 0; pi < kMaxPeers; ++pi)
+        if (pi < P.world) bf16x8_acc(r[pi], g);
+    }
+    if (apply_adam) {
+      float4 p0 = *reinterpret_cast<float4*>(hp + i * 8), p1 = *reinterpret_cast<float4*>(hp + i * 8 + 4);
+      float4 m0 = *reinterpret_cast<float4*>(m + i * 8), m1 = *reinterpret_cast<float4*>(m + i * 8 + 4);
+      float4 v0 = *reinterpret_cast<float4*>(v + i * 8), v1 = *reinterpret_cast<float4*>(v + i * 8 + 4);
+      float pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+      float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+      float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float gg = g[k] * inv_n * a.grad_scale;
+        if (!a.adamw) gg += a.weight_decay * pp[k];
+        mm[k] = a.beta1 * mm[k] + (1.f - a.beta1) * gg;
+        vv[k] = a.beta2 * vv[k] + (1.f - a.beta2) * gg * gg;
+        float upd = (mm[k] / a.bc1) / (sqrtf(vv[k] / a.bc2) + a.eps);
+        if (a.adamw) upd += a.weight_decay * pp[k];
+        pp[k] -= a.lr * upd;
+      }
+      *reinterpret_cast<float4*>(hp + i * 8) = make_float4(pp[0], pp[1], pp[2], pp[3]);
+      *reinterpret_cast<float4*>(hp + i * 8 + 4) = make_float4(pp[4], pp[5], pp[6], pp[7]);
+      *reinterpret_cast<float4*>(m + i * 8) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+      *reinterpret_cast<float4*>(m + i * 8 + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
+      *reinterpret_cast<float4*>(v + i * 8) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+      *reinterpret_cast<float4*>(v + i * 8 + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
+      uint4 o;
+      o.x = pack_bf16(pp[0], pp[1]); o.y = pack_bf16(pp[2], pp[3]);
+      o.z = pack_bf16(pp[4], pp[5]); o.w = pack_bf16(pp[6], pp[7]);
+      *reinterpret_cast<uint4*>(lp + i * 8) = o;
+    } else {
+      uint4 o;
+      o.x = pack_bf16(g[0] * inv_n, g[1] * inv_n); o.y = pack_bf16(g[2] * inv_n, g[3] * inv_n);
+      o.z = pack_bf16(g[4] * inv_n, g[5] * inv_n); o.w = pack_bf16(g[6] * inv_n, g[7] * inv_n);
+      *reinterpret_cast<uint4*>(grad_out + i * 8) = o;
+    }
+  }
+  // last CTA to finish tells the peers that this rank no longer reads their gradient buffers
+  __syncthreads();
+  __shared__ unsigned int last;
+  if (threadIdx.x == 0) {
+    __threadfence();
+    last = (atomicAdd(cta_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (last) {
+    if (threadIdx.x == 0) *cta_counter = 0u;
+    signal_all(P, 1, epoch);
+  }
+}
+
+// Wait until every peer finished reading (channel 1) — launched before a symmetric buffer is reused.
+__global__ void wait_channel_kernel(Peers P, int channel, uint32_t epoch) { wait_all(P, channel, epoch, 102); }
+
+// ------------------------------------------------------------------------------------ K9
+// out[i] = mean over `members` (ranks in the column group) of their symmetric shard; fp32 accumulate.
+struct Members {
+  int idx[kMaxPeers];
+  int count;
+};
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+subset_mean_kernel(Peers P, Members M, T* __restrict__ out, long long n, uint32_t epoch,
+                   unsigned int* __restrict__ cta_counter) {
+  if (blockIdx.x == 0) signal_all(P, 2, epoch);
+  if (!wait_all(P, 2, epoch, 103)) return;
+  const long long nvec = n >> 3;
+  const float inv = 1.0f / (float)M.count;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
+       i += (long long)gridDim.x * blockDim.x) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int k = 0; k < M.count; ++k) {
+      const uint4 r = ld_peer16(reinterpret_cast<const T*>(P.buf[M.idx[k]]) + i * 8);
+      const T* h = reinterpret_cast<const T*>(&r);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += to_f32<T>(h[e]);
+    }
+    uint4 o;
+    T* oh = reinterpret_cast<T*>(&o);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) oh[e] = from_f32<T>(acc[e] * inv);
+    *reinterpret_cast<uint4*>(out + i * 8) = o;
+  }
+  for (long long i = (nvec << 3) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int k = 0; k < M.count; ++k) acc += to_f32<T>(reinterpret_cast<const T*>(P.buf[M.idx[k]])[i]);
+    out[i] = from_f32<T>(acc * inv);
+  }
+  __syncthreads();
+  __shared__ unsigned int last;
+  if (threadIdx.x == 0) {
+    __threadfence();
+    last = (atomicAdd(cta_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (last) {
+    if (threadIdx.x == 0) *cta_counter = 0u;
+    signal_all(P, 3, epoch);
+  }
+}
+
+// ------------------------------------------------------------------------------------ K2 (gather)
+// Pull-based all-gather: dst[(r*part) ...] <- peer r's shard, chunk by chunk; after each chunk the CTA
+// that copied it bumps `chunk_flags[chunk]` to `epoch` (release, gpu scope) so a GEMM running on the
+// remaining SMs can consume weight tiles as they arrive.  Chunks are visited in flat order.
+__global__ void __launch_bounds__(kThreads)
+all_gather_kernel(Peers P, long long part_bytes, uint8_t* __restrict__ dst, long long chunk_bytes,
+                  uint32_t* __restrict__ chunk_flags, uint32_t epoch) {
+  if (blockIdx.x == 0) signal_all(P, 4, epoch);
+  if (!wait_all(P, 4, epoch, 104)) return;
+  const long long total = part_bytes * P.world;
+  const long long nchunks = (total + chunk_bytes - 1) / chunk_bytes;
+  for (long long c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const long long lo = c * chunk_bytes;
+    const long long hi = min(lo + chunk_bytes, total);
+    for (long long off = lo + (long long)threadIdx.x * 16; off < hi; off += (long long)blockDim.x * 16) {
+      const int r = (int)(off / part_bytes);
+      const long long in_off = off - (long long)r * part_bytes;
+      const uint4 val = (r == P.rank)
+                            ? *reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(P.buf[r]) + in_off)
+                            : ld_peer16(reinterpret_cast<const uint8_t*>(P.buf[r]) + in_off);
+      *reinterpret_cast<uint4*>(dst + off) = val;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && chunk_flags) {
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(chunk_flags + c), "r"(epoch) : "memory");
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ a2a rows
+// Rank-local view of an all-to-all of fixed-size rows: for every destination d, rows
+// [send_off[d], send_off[d] + count[d]) of `src` are stored into peer d's symmetric buffer starting at
+// row recv_off[d] (offsets precomputed on the host or by a count exchange).  One warp per row.
+struct A2A {
+  long long send_off[kMaxPeers];
+  long long recv_off[kMaxPeers];
+  long long count[kMaxPeers];
+};
+__global__ void __launch_bounds__(256)
+a2a_rows_kernel(Peers P, A2A T, const uint8_t* __restrict__ src, int row_bytes, uint32_t epoch,
+                unsigned int* __restrict__ cta_counter) {
+  // channel 5: destination buffers free (previous consumer done) ; channel 6: my rows have landed
+  if (blockIdx.x == 0) signal_all(P, 5, epoch);
+  if (!wait_all(P, 5, epoch, 105)) return;
+  long long total = 0;
+  for (int d = 0; d < P.world; ++d) total += T.count[d];
+  const int warps_per_block = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31;
+  for (long long w = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5); w < total;
+       w += (long long)gridDim.x * warps_per_block) {
+    long long r = w;
+    int d = 0;
+    while (r >= T.count[d]) { r -= T.count[d]; ++d; }
+    const int peer = (d + P.rank) % P.world;   // not used for addressing; keeps traffic staggered
+    (void)peer;
+    const uint8_t* s = src + (T.send_off[d] + r) * (long long)row_bytes;
+    uint8_t* t = reinterpret_cast<uint8_t*>(P.buf[d]) + (T.recv_off[d] + r) * (long long)row_bytes;
+    for (int off = lane * 16; off < row_bytes; off += 32 * 16)
+      *reinterpret_cast<uint4*>(t + off) = *reinterpret_cast<const uint4*>(s + off);
+  }
+  __syncthreads();
+  __shared__ unsigned int last;
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    last = (atomicAdd(cta_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (last) {
+    if (threadIdx.x == 0) *cta_counter = 0u;
+    __threadfence_system();
+    signal_all(P, 6, epoch);
+  }
+}
+
+static int fill_peers(Peers& P, const void* const* bufs, const void* const* sigs, int rank, int world) {
+  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return SXB_ERR_BAD_ARG;
+  for (int i = 0; i < kMaxPeers; ++i) {
+    P.buf[i] = i < world ? const_cast<void*>(bufs[i]) : nullptr;
+    P.sig[i] = i < world ? reinterpret_cast<uint32_t*>(const_cast<void*>(sigs[i])) : nullptr;
+  }
+  P.rank = rank;
+  P.world = world;
+  return SXB_OK;
+}
+
+static int grid_cap(long long work_items, int max_ctas) {
+  long long g = (work_items + kThreads - 1) / kThreads;
+  if (g < 1) g = 1;
+  const int cap = max_ctas > 0 ? max_ctas : 148 * 2;
+  if (g > cap) g = cap;
+  return (int)g;
+}
+
+}  // namespace symm
+}  // namespace sxb
+
+using namespace sxb;
+using namespace sxb::symm;
+
+SXB_DEFINE_HANG_ACCESSOR(sxb_symm_hang_info)
+
+// K1.  bufs/sigs: host arrays of `world` device pointers (peer mappings of the flat bf16 gradient buffer
+// and of the signal pads).  part: elements per shard (multiple of 8).  counter: device uint32 (zeroed once).
+// apply_adam == 0 -> plain reduce-scatter(mean) into grad_out (used when the step must be deferred).
+SXB_API int sxb_symm_rs_adam(const void* const* bufs, const void* const* sigs, int rank, int world, long long part,
+                             void* hp, void* m, void* v, void* lp, void* grad_out, float lr, float beta1,
+                             float beta2, float eps, float weight_decay, int step, int adamw, int bias_correction,
+                             float grad_scale, unsigned int epoch, const void* multicast_ptr, void* counter,
+                             int apply_adam, int max_ctas, void* stream) {
+  Peers P;
+  int rc = fill_peers(P, bufs, sigs, rank, world);
+  if (rc) return rc;
+  if (part <= 0 || (part & 7)) return SXB_ERR_UNSUPPORTED;
+  AdamArgs a;
+  a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay;
+  a.bc1 = bias_correction ? 1.f - powf(beta1, (float)step) : 1.f;
+  a.bc2 = bias_correction ? 1.f - powf(beta2, (float)step) : 1.f;
+  a.grad_scale = grad_scale; a.adamw = adamw;
+  rs_adam_kernel<<<grid_cap(part / 8, max_ctas), kThreads, 0, (cudaStream_t)stream>>>(
+      P, part, (float*)hp, (float*)m, (float*)v, (__nv_bfloat16*)lp, (__nv_bfloat16*)grad_out, a, epoch,
+      multicast_ptr, (unsigned int*)counter, apply_adam);
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+SXB_API int sxb_symm_wait(const void* const* bufs, const void* const* sigs, int rank, int world, int channel,
+                          unsigned int epoch, void* stream) {
+  Peers P;
+  int rc = fill_peers(P, bufs, sigs, rank, world);
+  if (rc) return rc;
+  wait_channel_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, channel, epoch);
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+// K9.  members: host array of `n_members` group ranks (must contain `rank`); out: local (non-symmetric) result.
+SXB_API int sxb_symm_subset_mean(const void* const* bufs, const void* const* sigs, int rank, int world,
+                                 const int* members, int n_members, void* out, long long n, int dtype,
+                                 unsigned int epoch, void* counter, int max_ctas, void* stream) {
+  Peers P;
+  int rc = fill_peers(P, bufs, sigs, rank, world);
+  if (rc) return rc;
+  if (n_members < 1 || n_members > kMaxPeers) return SXB_ERR_BAD_ARG;
+  Members M;
+  M.count = n_members;
+  for (int i = 0; i < kMaxPeers; ++i) M.idx[i] = i < n_members ? members[i] : 0;
+  const int grid = grid_cap(n / 8 + 1, max_ctas);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == kBF16) subset_mean_kernel<__nv_bfloat16><<<grid, kThreads, 0, s>>>(P, M, (__nv_bfloat16*)out, n, epoch, (unsigned int*)counter);
+  else if (dtype == kF16) subset_mean_kernel<__half><<<grid, kThreads, 0, s>>>(P, M, (__half*)out, n, epoch, (unsigned int*)counter);
+  else return SXB_ERR_BAD_ARG;
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+SXB_API int sxb_symm_all_gather(const void* const* bufs, const void* const* sigs, int rank, int world,
+                                long long part_bytes, void* dst, long long chunk_bytes, void* chunk_flags,
+                                unsigned int epoch, int max_ctas, void* stream) {
+  Peers P;
+  int rc = fill_peers(P, bufs, sigs, rank, world);
+  if (rc) return rc;
+  if ((part_bytes & 15) || (chunk_bytes & 15) || chunk_bytes <= 0) return SXB_ERR_UNSUPPORTED;
+  const long long nchunks = (part_bytes * world + chunk_bytes - 1) / chunk_bytes;
+  int grid = max_ctas > 0 ? max_ctas : 32;
+  if (grid > nchunks) grid = (int)nchunks;
+  all_gather_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(P, part_bytes, (uint8_t*)dst, chunk_bytes,
+                                                               (uint32_t*)chunk_flags, epoch);
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+// send_off / recv_off / count: host arrays of `world` int64 (rows).
+SXB_API int sxb_symm_a2a_rows(const void* const* bufs, const void* const* sigs, int rank, int world,
+                              const void* src, const long long* send_off, const long long* recv_off,
+                              const long long* count, int row_bytes, unsigned int epoch, void* counter,
+                              int max_ctas, void* stream) {
+  Peers P;
+  int rc = fill_peers(P, bufs, sigs, rank, world);
+  if (rc) return rc;
+  if (row_bytes & 15) return SXB_ERR_UNSUPPORTED;
+  A2A T;
+  long long total = 0;
+  for (int i = 0; i < kMaxPeers; ++i) {
+    T.send_off[i] = i < world ? send_off[i] : 0;
+    T.recv_off[i] = i < world ? recv_off[i] : 0;
+    T.count[i] = i < world ? count[i] : 0;
+    total += T.count[i];
+  }
+  long long g = (total + 7) / 8;
+  if (g < 1) g = 1;
+  const int cap = max_ctas > 0 ? max_ctas : 148;
+  if (g > cap) g = cap;
+  a2a_rows_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(P, T, (const uint8_t*)src, row_bytes, epoch,
+                                                            (unsigned int*)counter);
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
