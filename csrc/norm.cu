@@ -308,3 +308,62 @@ SXB_API int sxb_layernorm_bwd(const void* dy, const void* x, const void* w, cons
   return norm_bwd<true>(dy, x, w, mean, rstd, dres, dx, dw, db, scratch, rows, H, dtype,
                         accumulate_dw, (cudaStream_t)stream);
 }
+
+// ------------------------------------------------------------------------------------------------
+// RMSNorm backward for callers that must not allocate.
+//
+// Same computation as sxb_rmsnorm_bwd, but the per-CTA weight-gradient partials live in a scratch
+// array that is part of the library image instead of a buffer handed in by the caller.  It is meant
+// for code that runs when device memory can no longer be asked for: a training job whose memory plan
+// has already handed every remaining byte to its parameter / optimizer pools (the 8B single-GPU
+// configuration runs within a few GB of the 180 GB limit), a serving process that gave the whole device
+// to its KV-cache pool at start-up, or a recovery path that is running precisely because an allocation
+// just failed.  Such callers still own their inputs and outputs; only the scratch is ours.
+//
+// Limit: rows are unlimited, H <= SXB_NOALLOC_NORM_MAX_H (8192); the array holds 296 x 8192 floats
+// (about 9.3 MiB) on every GPU that loads the library, for the life of the process.
+// Sharing: there is ONE array per device.  Every call overwrites the part it uses before reading it
+// (each CTA stores its full partial row, the reduction reads only rows written by this launch), so
+// nothing needs to start at zero and stale contents of earlier calls are harmless.  Two calls that
+// overlap on the GPU (different streams, or concurrent host threads on one device) race on the array
+// and must be serialised by the caller.
+// Set-up: the first call on each device resolves the array's device address with
+// cudaGetSymbolAddress while that device is current and caches it; make that first call before any
+// stream capture begins.  Later calls do no runtime queries at all.
+constexpr int SXB_NOALLOC_NORM_MAX_H = 8192;
+constexpr int kNoAllocMaxGrid = 148 * 2;
+constexpr long long kNoAllocScratchElems = (long long)kNoAllocMaxGrid * SXB_NOALLOC_NORM_MAX_H;
+static __device__ __align__(256) float g_noalloc_norm_scratch[kNoAllocScratchElems];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_noalloc_ptr[kMaxDevices] = {nullptr};
+}  // namespace
+
+SXB_API int sxb_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w, const void* rstd,
+                                    const void* dres, void* dx, void* dw, long long rows, int H, int dtype,
+                                    int accumulate_dw, void* stream) {
+  if (rows <= 0) return SXB_OK;
+  if (!norm_ok(H)) return SXB_ERR_UNSUPPORTED;
+  if (H > SXB_NOALLOC_NORM_MAX_H) return SXB_ERR_TOO_LARGE;   // scratch is sized for H <= 8192
+  if (sxb_norm_bwd_scratch_elems(rows, H, 0) > kNoAllocScratchElems) return SXB_ERR_TOO_LARGE;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return SXB_ERR_UNSUPPORTED;
+  float* scratch = g_noalloc_ptr[dev];
+  if (scratch == nullptr) {
+    // In host code `g_noalloc_norm_scratch` is only a handle; the device address has to be asked for,
+    // once per device, with that device current.
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_norm_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return SXB_ERR_DRIVER;
+    scratch = static_cast<float*>(p);
+    g_noalloc_ptr[dev] = scratch;
+  }
+  return norm_bwd<false>(dy, x, w, nullptr, rstd, dres, dx, dw, nullptr, scratch, rows, H, dtype,
+                         accumulate_dw, (cudaStream_t)stream);
+}
+
+SXB_API int sxb_rmsnorm_bwd_noalloc_max_h() { return SXB_NOALLOC_NORM_MAX_H; }

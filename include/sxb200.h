@@ -54,6 +54,18 @@ int sxb_rmsnorm_fwd(const void* x, const void* res, const void* w, void* y, void
                     long long rows, int H, float eps, int dtype, void* stream);
 int sxb_rmsnorm_bwd(const void* dy, const void* x, const void* w, const void* rstd, const void* dres, void* dx,
                     void* dw, void* scratch, long long rows, int H, int dtype, int accumulate_dw, void* stream);
+/* RMSNorm backward for callers that cannot allocate device memory when they need it (a trainer whose
+ * memory plan already owns the whole GPU, a server that gave the device to its KV-cache pool, a
+ * recovery path running because an allocation failed).  No counterpart in the reference: the reference
+ * always allocates through torch.  Identical to sxb_rmsnorm_bwd except that the weight-gradient
+ * partials live in a ~9.3 MiB scratch array inside the library image (held by every GPU that loads
+ * the library).  Limit: H <= sxb_rmsnorm_bwd_noalloc_max_h() (8192), otherwise returns -3.  One array
+ * per device, shared by all calls: calls that overlap on the GPU race and must be serialised by the
+ * caller; nothing needs zeroing between calls.  The first call on a device looks up the array's device
+ * address (cudaGetSymbolAddress) — make it before any stream capture.  Never calls cudaMalloc/cudaFree. */
+int sxb_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w, const void* rstd, const void* dres,
+                            void* dx, void* dw, long long rows, int H, int dtype, int accumulate_dw, void* stream);
+int sxb_rmsnorm_bwd_noalloc_max_h(void);
 int sxb_layernorm_fwd(const void* x, const void* res, const void* w, const void* b, void* y, void* res_out,
                       void* mean, void* rstd, long long rows, int H, float eps, int dtype, void* stream);
 int sxb_layernorm_bwd(const void* dy, const void* x, const void* w, const void* mean, const void* rstd,
