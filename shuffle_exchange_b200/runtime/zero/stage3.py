@@ -354,7 +354,21 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
 
     def _pre_backward_unit(self, u: Unit):
         self._fetch(u)
+        self._attach_unit(u)
         self._prefetch_after(u, forward=False)
+
+    def _attach_unit(self, u: Unit):
+        """Allocate the unit's flat gradient buffer and point its parameters' main-grad views at it —
+        done lazily, right before the unit's backward, so only ~one unit of gradients is alive."""
+        if getattr(u, "attached", False):
+            return
+        u.attached = True
+        for fg in u.groups:
+            if (fg.grad_shard is not None and fg.flat_grad is not None
+                    and fg.grad_shard.data_ptr() == fg.flat_grad.data_ptr()):
+                fg.grad_shard = fg.grad_shard.clone()   # un-alias before the buffer is overwritten
+            fg.attach_main_grads()
+            fg.mark_grads_unwritten()
 
     # ---------------------------------------------------------------------------------- backward
     def set_gradient_accumulation_boundary(self, is_boundary: bool):
@@ -368,12 +382,11 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             u.grads_ready = 0
             u.reduced = False
             u.stepped = False
+            u.attached = False
             for fg in u.groups:
-                if (fg.grad_shard is not None and fg.flat_grad is not None
-                        and fg.grad_shard.data_ptr() == fg.flat_grad.data_ptr()):
-                    fg.grad_shard = fg.grad_shard.clone()   # un-alias before the buffer is overwritten
-                fg.attach_main_grads()
                 fg.mark_grads_unwritten()
+            if u is self.root_unit or u.module is self.module:
+                self._attach_unit(u)       # no module-level backward hook for the root unit
 
     def _post_backward(self):
         # units whose gradients never (all) arrived — unused parameters — are flushed here
