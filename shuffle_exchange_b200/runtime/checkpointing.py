@@ -113,6 +113,7 @@ def save_checkpoint(self, save_dir, tag=None, client_state={}, save_latest=True,
     self.checkpoint_engine.create(tag)
     self._checkpoint_tag_validation(tag)
     os.makedirs(os.path.join(save_dir, tag), exist_ok=True)
+    self._curr_ckpt_path = os.path.join(save_dir, tag)
     if dist.is_initialized():
         dist.barrier()
     if self.has_moe_layers:
@@ -282,6 +283,7 @@ def load_checkpoint(self, load_dir, tag=None, load_module_strict=True, load_opti
         from ..checkpoint.universal_checkpoint import load_universal_into_engine
         return load_universal_into_engine(self, load_dir, tag, load_optimizer_states, load_lr_scheduler_states)
     path = self._get_ckpt_name(load_dir, tag)
+    self._curr_ckpt_path = os.path.join(load_dir, str(tag))
     if not os.path.exists(path):
         alt = os.path.join(load_dir, str(tag), f"mp_rank_{_mp_rank(self):02d}_model_states.pt")
         if os.path.exists(alt):
