@@ -38,6 +38,7 @@ def parse():
     ap.add_argument("--mbs", type=int, default=1)
     ap.add_argument("--layers", type=int, default=0, help="debug only: override layer count (result is then INVALID)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-fused", action="store_true", help="NCCL baseline path for the ZeRO-3 collectives")
     return ap.parse_args()
 
 
@@ -129,7 +130,16 @@ def ds_config(args, world):
         "zero_optimization": {"stage": 3, "overlap_comm": True, "contiguous_gradients": True,
                               "stage3_param_persistence_threshold": 100000},
         "gradient_clipping": 0.0,
-    }
+    } if not getattr(args, "no_fused", False) else _with_nccl_collectives(args)
+
+
+def _with_nccl_collectives(args):
+    import copy
+    a = copy.copy(args)
+    a.no_fused = False
+    c = ds_config(a, 0)
+    c["zero_optimization"]["fused_collectives"] = False
+    return c
 
 
 def run_ours(args):
@@ -215,6 +225,7 @@ def run_ours(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
             "config": {"model": args.model + ("" if not args.layers else f"-DEBUG-{args.layers}-layers"),
                        "global_batch": B * world, "seq_len": S, "parallelism": f"zero3-dp{world}",
+                       "collectives": ("nccl" if args.no_fused or world == 1 else "fused symmetric-memory kernels"),
                        "activation_checkpointing": "per-layer", "optimizer": "AdamW fp32 master",
                        "l2_policy": "inputs (16 GB weights + activations) larger than L2; no explicit flush",
                        "params": cfg.num_parameters()},

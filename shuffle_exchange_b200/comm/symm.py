@@ -40,7 +40,8 @@ def available(group=None) -> bool:
     if not torch.cuda.is_available():
         return False
     try:
-        import torch.distributed._symmetric_memory  # noqa: F401
+        import importlib
+        importlib.import_module("torch.distributed._symmetric_memory")
         return torch.distributed.is_initialized() and torch.distributed.get_backend(group) == "nccl"
     except Exception:
         return False

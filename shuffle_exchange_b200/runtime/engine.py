@@ -475,7 +475,8 @@ class DeepSpeedEngine(nn.Module):
                    elastic_checkpoint=zc.elastic_checkpoint, aio_config=self._config.aio_config,
                    zero_hpz_partition_size=zc.zero_hpz_partition_size, zero_quantized_weights=zc.zero_quantized_weights,
                    zero_quantized_nontrainable_weights=zc.zero_quantized_nontrainable_weights,
-                   zeropp_loco_param=zc.zeropp_loco_param, fused_step=zc.fused_step, **common)
+                   zeropp_loco_param=zc.zeropp_loco_param, fused_step=zc.fused_step,
+                   fused_collectives=zc.fused_collectives, **common)
 
     def _grad_accum_dtype(self, lp_dtype):
         name = self._config.grad_accum_dtype

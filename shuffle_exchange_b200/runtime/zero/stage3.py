@@ -100,7 +100,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                  gradient_accumulation_steps=1, elastic_checkpoint=False, aio_config=None, all2all_process_group=None,
                  zero_hpz_partition_size=1, zero_quantized_weights=False, zero_quantized_nontrainable_weights=False,
                  zero_module_granularity_threshold=0, zeropp_loco_param=None, log_trace_cache_warnings=False,
-                 check_grad_overflow=None, dtype=None, fused_step=True, unit_modules=None):
+                 check_grad_overflow=None, dtype=None, fused_step=True, unit_modules=None, fused_collectives=None):
         first = next(p for g in init_optimizer.param_groups for p in g["params"])
         lp_dtype = dtype or (first.dtype if first.dtype != torch.float32 or getattr(first, "ds_tensor", None) is None
                              else first.ds_tensor.dtype)
@@ -140,7 +140,10 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         self._in_backward = False
         self._hooks = []
 
+        self.fused = None
         self._build_units(unit_modules)
+        from .fused_collectives import maybe_create
+        self.fused = maybe_create(self, dp_process_group, fused_collectives)
         self._install_hooks()
         from ...utils.tensor_fragment import link_group_params
         for fg in self.groups:
@@ -279,15 +282,21 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             self.allgather_stream.wait_stream(get_accelerator().current_stream())
             with get_accelerator().stream(self.allgather_stream):
                 for fg in u.groups:
-                    fg.gather_params()
+                    self._gather_fg(fg)
                 ev = get_accelerator().Event()
                 ev.record(self.allgather_stream)
             u.fetch_event = ev
         else:
             for fg in u.groups:
-                fg.gather_params()
+                self._gather_fg(fg)
             u.available = True
         self._live_numel += u.numel
+
+    def _gather_fg(self, fg: FlatGroup):
+        if self.fused is not None and getattr(fg, "_symm_shard", None) is not None:
+            self.fused.gather(fg)
+        else:
+            fg.gather_params()
 
     def _wait_unit(self, u: Unit):
         if u.fetch_event is not None:
@@ -363,6 +372,13 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         if getattr(u, "attached", False):
             return
         u.attached = True
+        if self.fused is not None:
+            ev = getattr(self, "_arena_free_events", [None, None])[self.fused._slot]
+            if ev is not None:
+                get_accelerator().current_stream().wait_event(ev)   # my own reduce of this arena's last occupant
+            u._arena_slot = self.fused._slot
+            self.fused.attach_unit_grads(u)
+            return
         for fg in u.groups:
             if (fg.grad_shard is not None and fg.flat_grad is not None
                     and fg.grad_shard.data_ptr() == fg.flat_grad.data_ptr()):
@@ -411,6 +427,25 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         stream = self.reduce_stream
         if stream is not None:
             stream.wait_stream(get_accelerator().current_stream())
+        if self.fused is not None:
+            if not getattr(u, "attached", False):
+                self._attach_unit(u)
+            with get_accelerator().stream(stream):
+                for fg in u.groups:
+                    if self.fused.reduce_and_step(fg, fuse, accumulate):
+                        u.stepped = True
+                    fg.flat_grad = None
+                    fg.detach_main_grads()
+                ev = get_accelerator().Event()
+                ev.record(stream if stream is not None else get_accelerator().current_stream())
+            if not hasattr(self, "_arena_free_events"):
+                self._arena_free_events = [None, None]
+            self._arena_free_events[u._arena_slot] = ev
+            if stream is not None:
+                self._pending_reduce.append(u)
+            if not u.persistent and not force:
+                self._release(u)
+            return
         with get_accelerator().stream(stream):
             for fg in u.groups:
                 if fg.flat_grad is None:
