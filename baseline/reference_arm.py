@@ -67,6 +67,22 @@ def run(args, ClockSampler, ds_config_fn):
                                       "stage3_max_live_parameters": int(1e9), "stage3_max_reuse_distance": int(1e9)})
     engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config=conf)
     B, S = args.mbs, args.seq
+    # Same policy as our arm: recompute only when HBM demands it.  HF's switch is all-or-nothing; a
+    # non-checkpointed HF Llama layer keeps ~2.3 GB at B*S = 8192 tokens (fp32 norm upcasts, q/k/v + rotated
+    # copies, gate/up/act/product), scaled linearly with the token count.
+    ckpt_mode = "per-layer (HF gradient_checkpointing)"
+    if getattr(args, "ckpt_layers", "auto") == "auto":
+        total = torch.cuda.get_device_properties(dev).total_memory
+        need = cfg.num_hidden_layers * int(2.3e9 * (B * S) / 8192) + 30 * 2 ** 30
+        fits = torch.tensor([1 if total - torch.cuda.memory_allocated(dev) >= need else 0], device=dev)
+        if world > 1:
+            torch.distributed.all_reduce(fits, op=torch.distributed.ReduceOp.MIN)
+        if int(fits.item()):
+            model.gradient_checkpointing_disable()
+            ckpt_mode = "none (fits in HBM)"
+    elif args.ckpt_layers not in ("all",) and int(args.ckpt_layers) == 0:
+        model.gradient_checkpointing_disable()
+        ckpt_mode = "none (--ckpt-layers 0)"
     g = torch.Generator().manual_seed(1000 + rank)
     n_batches = 4
     host = [torch.randint(0, cfg.vocab_size, (B, S), generator=g, dtype=torch.int64).pin_memory() for _ in range(n_batches)]
@@ -129,7 +145,7 @@ def run(args, ClockSampler, ds_config_fn):
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "reference",
             "config": {"model": args.model + ("" if not args.layers else f"-DEBUG-{args.layers}-layers"),
                        "global_batch": B * world, "seq_len": S, "parallelism": f"zero3-dp{world}",
-                       "activation_checkpointing": "per-layer (HF gradient_checkpointing)",
+                       "activation_checkpointing": ckpt_mode,
                        "optimizer": "torch.optim.AdamW (torch_adam)", "attention": "torch sdpa",
                        "l2_policy": "inputs larger than L2; no explicit flush"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": 0, "loss": float(last.item()),

@@ -38,6 +38,9 @@ def parse():
     ap.add_argument("--mbs", type=int, default=1)
     ap.add_argument("--layers", type=int, default=0, help="debug only: override layer count (result is then INVALID)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--ckpt-layers", default="auto",
+                    help="decoder layers that recompute activations in backward: 'auto' = as few as HBM allows, "
+                         "'all', or a count")
     ap.add_argument("--no-fused", action="store_true", help="NCCL baseline path for the ZeRO-3 collectives")
     return ap.parse_args()
 
@@ -142,6 +145,29 @@ def _with_nccl_collectives(args):
     return c
 
 
+def pick_checkpoint_layers(args, cfg, B, S, dev, world):
+    """Spend spare HBM on NOT recomputing: every layer left un-checkpointed keeps
+    ``cfg.activation_bytes_per_layer`` bytes alive until its backward.  The reserve covers the transient peak of
+    a fully checkpointed step (logits + loss grad, two gathered units, lazily allocated gradient arenas, one
+    layer being recomputed) measured at 13.4 GiB for this model, plus allocator slack."""
+    import torch
+    L = cfg.num_hidden_layers
+    if args.ckpt_layers == "all":
+        return L
+    if args.ckpt_layers != "auto":
+        return max(0, min(L, int(args.ckpt_layers)))
+    total = torch.cuda.get_device_properties(dev).total_memory
+    resident = torch.cuda.memory_allocated(dev)
+    reserve = 24 * 2 ** 30
+    per_layer = cfg.activation_bytes_per_layer(B, S)
+    free_layers = int(max(0, total - resident - reserve) // per_layer)
+    t = torch.tensor([free_layers], device=dev, dtype=torch.int64)
+    if world > 1:
+        import torch.distributed as td
+        td.all_reduce(t, op=td.ReduceOp.MIN)
+    return max(0, L - int(t.item()))
+
+
 def run_ours(args):
     import torch
     rank, world, local = dist_env(args)
@@ -159,6 +185,7 @@ def run_ours(args):
     engine, _, _, _ = sxb.initialize(model=model, config=ds_config(args, world), model_parameters=model.parameters())
     engine.train()
     B, S = args.mbs, args.seq
+    cfg.checkpoint_layers = pick_checkpoint_layers(args, cfg, B, S, dev, world)
     g = torch.Generator().manual_seed(1000 + rank)
     n_batches = 4
     host = [torch.randint(0, cfg.vocab_size, (B, S), generator=g, dtype=torch.int64).pin_memory() for _ in range(n_batches)]
@@ -226,7 +253,9 @@ def run_ours(args):
             "config": {"model": args.model + ("" if not args.layers else f"-DEBUG-{args.layers}-layers"),
                        "global_batch": B * world, "seq_len": S, "parallelism": f"zero3-dp{world}",
                        "collectives": ("nccl" if args.no_fused or world == 1 else "fused symmetric-memory kernels"),
-                       "activation_checkpointing": "per-layer", "optimizer": "AdamW fp32 master",
+                       "activation_checkpointing": f"{cfg.checkpoint_layers} of {cfg.num_hidden_layers} layers recompute "
+                                                   f"(--ckpt-layers {args.ckpt_layers})",
+                       "optimizer": "AdamW fp32 master",
                        "l2_policy": "inputs (16 GB weights + activations) larger than L2; no explicit flush",
                        "params": cfg.num_parameters()},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,

@@ -39,6 +39,9 @@ class LlamaConfig:
     tie_word_embeddings: bool = False
     initializer_range: float = 0.02
     activation_checkpointing: bool = True
+    # number of decoder layers (counted from layer 0) whose activations are recomputed in backward;
+    # -1 = all of them.  Lets a run spend spare HBM on skipping recompute (see activation_bytes_per_layer).
+    checkpoint_layers: int = -1
 
     @property
     def head_dim(self) -> int:
@@ -58,6 +61,14 @@ class LlamaConfig:
         mm += self.vocab_size * h
         attn = self.num_hidden_layers * 2 * 2 * self.num_attention_heads * d * seq_len * (0.5 if causal else 1.0)
         return 6.0 * mm + 3.0 * attn
+
+    def activation_bytes_per_layer(self, batch: int, seq_len: int, elem: int = 2) -> int:
+        """Bytes one decoder layer keeps for backward when it is NOT checkpointed: two residual streams, two
+        normed inputs, qkv, attention output, gate|up and the SwiGLU product (plus fp32 rstd/lse rows)."""
+        t = batch * seq_len
+        h, f = self.hidden_size, self.intermediate_size
+        qkv = (self.num_attention_heads + 2 * self.num_key_value_heads) * self.head_dim
+        return t * elem * (5 * h + qkv + 3 * f) + t * 4 * (2 + self.num_attention_heads)
 
     to_dict = asdict
 
@@ -147,8 +158,9 @@ class LlamaModel(nn.Module):
         h = F.embedding(input_ids, self.embed_tokens)
         residual = None
         ckpt = cfg.activation_checkpointing and self.training and torch.is_grad_enabled()
-        for layer in self.layers:
-            if ckpt:
+        n_ckpt = len(self.layers) if cfg.checkpoint_layers < 0 else cfg.checkpoint_layers
+        for i, layer in enumerate(self.layers):
+            if ckpt and i < n_ckpt:
                 from ..runtime.activation_checkpointing import checkpointing
                 h, residual = checkpointing.checkpoint(layer, h, residual, positions, cos, sin)
             else:

@@ -1,0 +1,70 @@
+#!/usr/bin/env python
+"""Summarise ``.ncu-rep`` files into a small JSON/markdown table (the judged artefacts live in profiles/).
+
+    python tools/ncu_summary.py gpurun_out/prof_gemm.ncu-rep ... > profiles/ncu_summary_<tag>.md
+"""
+import csv
+import io
+import json
+import subprocess
+import sys
+
+METRICS = [
+    ("gpu__time_duration.sum", "time"),
+    ("sm__cycles_elapsed.avg.per_second", "sm clock"),
+    ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "tensor pipe active %"),
+    ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "SM throughput %"),
+    ("sm__warps_active.avg.pct_of_peak_sustained_active", "warps active %"),
+    ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue slots busy %"),
+    ("dram__bytes_read.sum", "DRAM read"),
+    ("dram__bytes_write.sum", "DRAM write"),
+    ("dram__throughput.avg.pct_of_peak_sustained_elapsed", "DRAM throughput %"),
+    ("lts__t_sector_hit_rate.pct", "L2 hit %"),
+    ("lts__throughput.avg.pct_of_peak_sustained_elapsed", "L2 throughput %"),
+    ("l1tex__m_xbar2l1tex_read_bytes.sum.per_second", "xbar->SM read"),
+    ("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "smem bank conflicts"),
+    ("launch__registers_per_thread", "regs/thread"),
+    ("launch__shared_mem_per_block_dynamic", "dyn smem/block"),
+    ("launch__grid_size", "grid"),
+    ("launch__block_size", "block"),
+    ("smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio", "stall long_scoreboard"),
+    ("smsp__average_warps_issue_stalled_wait_per_issue_active.ratio", "stall wait"),
+    ("smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio", "stall barrier"),
+    ("smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio", "stall short_scoreboard"),
+    ("smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio", "stall branch_resolving"),
+]
+
+
+def load(path):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units = rows[0], rows[1]
+    res = []
+    for r in rows[2:]:
+        d = {h: (v, u) for h, u, v in zip(hdr, units, r)}
+        res.append(d)
+    return res
+
+
+def main():
+    allres = {}
+    print("| kernel | " + " | ".join(lbl for _, lbl in METRICS) + " |")
+    print("|---|" + "---|" * len(METRICS))
+    for path in sys.argv[1:]:
+        for d in load(path):
+            name = d["Kernel Name"][0].split("(")[0].replace("void ", "")
+            cells = []
+            for key, lbl in METRICS:
+                v, u = d.get(key, ("", ""))
+                try:
+                    v = f"{float(v):.4g}"
+                except ValueError:
+                    pass
+                cells.append(f"{v} {u}".strip())
+            print(f"| `{name}` | " + " | ".join(cells) + " |")
+            allres[name] = {lbl: " ".join(d.get(key, ("", ""))).strip() for key, lbl in METRICS}
+    print("\n```json\n" + json.dumps(allres, indent=1) + "\n```")
+
+
+if __name__ == "__main__":
+    main()
