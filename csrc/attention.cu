@@ -152,7 +152,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       // K and V rings advance independently (polling state machine): a K slot is recycled right
       // after its QK^T, so the next-but-one K tile is in flight ~2 iterations before it is needed.
       int jk = 0, jv = 0;
-      unsigned long long t0 = global_ns();
+      unsigned long long t0 = 0;
+      long long c_next = 0;
       while (jk < nblk || jv < nblk) {
         bool progressed = false;
         if (jk < nblk && mbar_try_wait(&k_empty[jk & 1], ((jk >> 1) & 1) ^ 1)) {
@@ -173,8 +174,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           ++jv;
           progressed = true;
         }
-        if (progressed) t0 = global_ns();
-        else if (hang_should_abort(t0, 21, jk * 1000 + jv)) goto done;
+        if (progressed) { t0 = 0; c_next = 0; }
+        else if (hang_should_abort(t0, 21, jk * 1000 + jv, &c_next)) goto done;
       }
     }
   } else if (warp == 1) {

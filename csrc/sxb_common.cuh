@@ -201,6 +201,74 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                : "memory");
 }
 
+// ------------------------------------------------------- CTA-pair (cta_group::2) variants
+// In a 2-CTA cluster the 32-bit shared address of the odd CTA differs from the even (leader)
+// CTA's by bit 24; clearing it names the leader's copy of the same smem offset.
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_arrive() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  cluster_arrive();
+  cluster_wait();
+}
+// Arrive on the LEADER CTA's copy of `bar` (callable from either CTA of the pair).
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerBitMask)
+               : "memory");
+}
+// TMA load into THIS CTA's smem whose completion bytes are credited to the leader CTA's barrier.
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* m, uint64_t* bar,
+                                                 int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)),
+      "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_slot, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(smem_slot)),
+               "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish_pair() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols)
+               : "memory");
+}
+// D[tmem of both CTAs] (+)= A * B with M = 256 split over the pair; issued by ONE thread of the leader.
+__device__ __forceinline__ void umma_f16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                              uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Arrive on the same-offset mbarrier in every CTA of `cta_mask` once this thread's MMAs finish.
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar, uint16_t cta_mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
+      "[%0], %1;" ::"r"(smem_u32(bar)),
+      "h"(cta_mask)
+      : "memory");
+}
+
 // 32 lanes x 32 consecutive fp32 columns: thread t gets row (warp%4)*32+t.
 __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
@@ -382,25 +450,32 @@ __device__ __forceinline__ unsigned long long global_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+// The expensive part of the watchdog (a volatile global load + globaltimer read, ~700 cycles of L2
+// round trip) runs at most once every ~64k SM cycles; between checks the waiter only re-polls the
+// mbarrier, so a wait that is satisfied late still wakes up within one try_wait period.
+static __device__ __noinline__ bool hang_record(uint32_t tag, uint32_t parity, uint32_t aux) {
+  if (atomicCAS(&g_sxb_hang[0], 0u, 1u) == 0u) {
+    g_sxb_hang[1] = tag; g_sxb_hang[2] = blockIdx.x; g_sxb_hang[3] = blockIdx.y;
+    g_sxb_hang[4] = blockIdx.z; g_sxb_hang[5] = threadIdx.x; g_sxb_hang[6] = parity;
+    g_sxb_hang[7] = aux;
+    __threadfence();
+  }
+  return false;
+}
 static __device__ __noinline__ bool mbar_wait_slow(uint64_t* bar, uint32_t parity, uint32_t tag, uint32_t aux) {
-  const unsigned long long t0 = global_ns();
+  unsigned long long t0 = 0;
+  long long c_next = clock64() + 65536;
   while (!mbar_try_wait(bar, parity)) {
-    {
+    if (clock64() - c_next > 0) {
+      c_next = clock64() + 65536;
       if (*reinterpret_cast<volatile unsigned int*>(&g_sxb_hang[0]) != 0) return false;
-      if (global_ns() - t0 > 2000000000ull) {
-        if (atomicCAS(&g_sxb_hang[0], 0u, 1u) == 0u) {
-          g_sxb_hang[1] = tag; g_sxb_hang[2] = blockIdx.x; g_sxb_hang[3] = blockIdx.y;
-          g_sxb_hang[4] = blockIdx.z; g_sxb_hang[5] = threadIdx.x; g_sxb_hang[6] = parity;
-          g_sxb_hang[7] = aux;
-          __threadfence();
-        }
-        return false;
-      }
+      const unsigned long long now = global_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 2000000000ull) return hang_record(tag, parity, aux);
     }
   }
   return true;
 }
-// Returns false when the wait was abandoned (caller must leave its role loop).
 __device__ __forceinline__ bool mbar_wait_to(uint64_t* bar, uint32_t parity, uint32_t tag, uint32_t aux = 0) {
   if (mbar_try_wait(bar, parity)) return true;
   return mbar_wait_slow(bar, parity, tag, aux);
@@ -421,16 +496,21 @@ __device__ __forceinline__ bool mbar_wait_to(uint64_t* bar, uint32_t parity, uin
 namespace sxb {
 // Returns true when the caller should abandon its loop: either another waiter already raised the
 // abort flag or `t0` is more than ~2 s in the past (then this thread records the hang).
-__device__ __forceinline__ bool hang_should_abort(unsigned long long t0, uint32_t tag, uint32_t aux) {
-  if (*reinterpret_cast<volatile unsigned int*>(&g_sxb_hang[0]) != 0) return true;
-  if (global_ns() - t0 > 2000000000ull) {
-    if (atomicCAS(&g_sxb_hang[0], 0u, 1u) == 0u) {
-      g_sxb_hang[1] = tag; g_sxb_hang[2] = blockIdx.x; g_sxb_hang[3] = blockIdx.y;
-      g_sxb_hang[4] = blockIdx.z; g_sxb_hang[5] = threadIdx.x; g_sxb_hang[6] = 0; g_sxb_hang[7] = aux;
-      __threadfence();
-    }
-    return true;
+// Poll-loop companion of mbar_wait_to: `c_next` is a clock64 deadline owned by the caller (initialise to 0);
+// `t0` is the globaltimer value at the last progress (0 = unknown).  Cheap unless the deadline passed.
+__device__ __forceinline__ bool hang_should_abort(unsigned long long& t0, uint32_t tag, uint32_t aux,
+                                                  long long* c_next = nullptr) {
+  static_assert(sizeof(long long) == 8, "");
+  if (c_next) {
+    const long long c = clock64();
+    if (*c_next == 0) { *c_next = c + 65536; return false; }
+    if (c - *c_next <= 0) return false;
+    *c_next = c + 65536;
   }
+  if (*reinterpret_cast<volatile unsigned int*>(&g_sxb_hang[0]) != 0) return true;
+  const unsigned long long now = global_ns();
+  if (t0 == 0) { t0 = now; return false; }
+  if (now - t0 > 2000000000ull) { hang_record(tag, 0, aux); return true; }
   return false;
 }
 }  // namespace sxb

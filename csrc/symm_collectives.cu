@@ -73,9 +73,10 @@ __device__ __forceinline__ bool wait_all(const Peers& P, int channel, uint32_t e
   __syncthreads();
   if (threadIdx.x < P.world) {
     const uint32_t* s = slot(P.sig[P.rank], channel, threadIdx.x);
-    const unsigned long long t0 = global_ns();
+    unsigned long long t0 = 0;
+    long long c_next = 0;
     while ((int32_t)(ld_acquire_sys(s) - epoch) < 0) {
-      if (hang_should_abort(t0, tag, threadIdx.x)) { ok_flag = 0; break; }
+      if (hang_should_abort(t0, tag, threadIdx.x, &c_next)) { ok_flag = 0; break; }
     }
   }
   __syncthreads();

@@ -21,6 +21,9 @@ int sxb_abi_version(void);
 int sxb_device_info(int* sm_count, int* cc_major, int* cc_minor, long long* total_mem);
 /* pipeline watchdog records (8 x uint32, host pointer): see csrc/sxb_common.cuh mbar_wait_to */
 int sxb_gemm_hang_info(unsigned int* out_host);
+/* Kernel selection for sxb_gemm_bf16: 0 = auto (CTA-pair cta_group::2 kernel, 256x256 tiles, for large
+ * problems; single-CTA 128x256 kernel otherwise), 1 = force single-CTA, 2 = force CTA-pair. */
+int sxb_gemm_set_mode(int mode);
 int sxb_attn_hang_info(unsigned int* out_host);
 
 /* ---- tcgen05 GEMM: C[M,N] (+)= alpha * op(A) op(B); layout 0 NT, 1 NN, 2 TN.

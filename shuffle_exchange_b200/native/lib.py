@@ -62,6 +62,7 @@ SIGNATURES = {
     "sxb_attn_fwd": "ppppp" "iiiii" "llll" "i" "f" "p",
     "sxb_attn_bwd": "pppppppppp" "iiiii" "llllllll" "i" "f" "p",
     "sxb_gemm_hang_info": "p",
+    "sxb_gemm_set_mode": "i",
     "sxb_attn_hang_info": "p",
 }
 _LONG_RETURN = {"sxb_norm_bwd_scratch_elems"}

@@ -132,6 +132,64 @@ def _():
     return res
 
 
+def _with_gemm_mode(mode, fn):
+    from shuffle_exchange_b200.native import lib
+    lib.call("sxb_gemm_set_mode", mode)
+    try:
+        return fn()
+    finally:
+        lib.call("sxb_gemm_set_mode", 0)
+
+
+@check("gemm_pair")
+def _():
+    """CTA-pair (cta_group::2) kernel forced on: every layout, ragged edges, fp32 accumulate."""
+    import torch
+    from shuffle_exchange_b200.native import lib
+
+    def run():
+        errs = {"nt": _gemm_case(0, 1024, 4096, 4096), "nn": _gemm_case(1, 1024, 4096, 1024),
+                "tn": _gemm_case(2, 4096, 1024, 2048), "nt_small": _gemm_case(0, 256, 256, 64),
+                "tails": max(_gemm_case(0, 200, 328, 136), _gemm_case(1, 200, 328, 136), _gemm_case(2, 200, 328, 136)),
+                "acc": max(_gemm_case(2, 512, 768, 1024, out_dtype=torch.float32, accumulate=True),
+                           _gemm_case(0, 512, 768, 1024, accumulate=True)),
+                "many_tiles": _gemm_case(0, 8192, 6144, 512)}
+        return errs
+    errs = _with_gemm_mode(2, run)
+    return {"err": max(errs.values()), "cases": errs, "watchdog": lib.hang_info("gemm")}
+
+
+@check("gemm_pair_perf")
+def _():
+    import torch
+    from shuffle_exchange_b200.ops import functional as F
+    res = {}
+    shapes = [(0, 8192, 8192, 8192), (0, 8192, 6144, 4096), (0, 8192, 28672, 4096), (0, 8192, 4096, 14336),
+              (0, 8192, 4096, 4096), (1, 8192, 4096, 28672), (1, 8192, 14336, 4096), (2, 28672, 4096, 8192),
+              (2, 4096, 14336, 8192), (0, 8192, 128256, 4096)]
+    for (layout, M, N, K) in shapes:
+        if layout == 0:
+            a = torch.randn(M, K, device="cuda", dtype=torch.bfloat16); b = torch.randn(N, K, device="cuda", dtype=torch.bfloat16)
+        elif layout == 1:
+            a = torch.randn(M, K, device="cuda", dtype=torch.bfloat16); b = torch.randn(K, N, device="cuda", dtype=torch.bfloat16)
+        else:
+            a = torch.randn(K, M, device="cuda", dtype=torch.bfloat16); b = torch.randn(K, N, device="cuda", dtype=torch.bfloat16)
+        out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+        fl = 2 * M * N * K / 1e9
+        ms1 = _with_gemm_mode(1, lambda: _time(lambda: F.gemm(a, b, layout, out=out)))
+        ms2 = _with_gemm_mode(2, lambda: _time(lambda: F.gemm(a, b, layout, out=out)))
+        if layout == 0:
+            msr = _time(lambda: torch.matmul(a, b.t(), out=out))
+        elif layout == 1:
+            msr = _time(lambda: torch.matmul(a, b, out=out))
+        else:
+            msr = _time(lambda: torch.matmul(a.t(), b, out=out))
+        res[f"{'NT NN TN'.split()[layout]}_{M}x{N}x{K}"] = {"single_tflops": fl / ms1, "pair_tflops": fl / ms2,
+                                                             "cublas_tflops": fl / msr}
+        del a, b, out
+    return res
+
+
 @check("rmsnorm")
 def _():
     import torch
