@@ -144,75 +144,99 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   const uint32_t tS = tmem;          // 2 x 64 columns
   const uint32_t tO = tmem + 128;    // D columns
 
+  // Producer / MMA warps run whole-warp in uniform control flow; only the asynchronous instruction is
+  // predicated on one elected lane (keeps operands in uniform registers: no R2UR waterfall per MMA).
   if (warp == 0) {
-    if (lane == 0) {
+    const bool elected = elect_one();
+    if (elected) {
       mbar_expect_tx(q_full, L::kQ);
       for (int hh = 0; hh < NH; ++hh)
         tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, q0, b);
-      // K and V rings advance independently (polling state machine): a K slot is recycled right
-      // after its QK^T, so the next-but-one K tile is in flight ~2 iterations before it is needed.
-      int jk = 0, jv = 0;
-      unsigned long long t0 = 0;
-      long long c_next = 0;
-      while (jk < nblk || jv < nblk) {
-        bool progressed = false;
-        if (jk < nblk && mbar_try_wait(&k_empty[jk & 1], ((jk >> 1) & 1) ^ 1)) {
-          const int st = jk & 1;
+    }
+    __syncwarp();
+    // K and V rings advance independently (polling state machine): a K slot is recycled right
+    // after its QK^T, so the next-but-one K tile is in flight ~2 iterations before it is needed.
+    int jk = 0, jv = 0;
+    unsigned long long t0 = 0;
+    long long c_next = 0;
+    while (jk < nblk || jv < nblk) {
+      bool progressed = false;
+      const bool k_ok = jk < nblk &&
+          __shfl_sync(0xffffffffu, (int)mbar_try_wait(&k_empty[jk & 1], ((jk >> 1) & 1) ^ 1), 0);
+      if (k_ok) {
+        const int st = jk & 1;
+        if (elected) {
           mbar_expect_tx(&k_full[st], L::kKV);
           for (int hh = 0; hh < NH; ++hh)
             tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &k_full[st], hh * 64, hk,
                         jk * BC, b);
-          ++jk;
-          progressed = true;
         }
-        if (jv < nblk && mbar_try_wait(&v_empty[jv & 1], ((jv >> 1) & 1) ^ 1)) {
-          const int st = jv & 1;
+        __syncwarp();
+        ++jk;
+        progressed = true;
+      }
+      const bool v_ok = jv < nblk &&
+          __shfl_sync(0xffffffffu, (int)mbar_try_wait(&v_empty[jv & 1], ((jv >> 1) & 1) ^ 1), 0);
+      if (v_ok) {
+        const int st = jv & 1;
+        if (elected) {
           mbar_expect_tx(&v_full[st], L::kKV);
           for (int hh = 0; hh < NH; ++hh)
             tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &v_full[st], hh * 64, hk,
                         jv * BC, b);
-          ++jv;
-          progressed = true;
         }
-        if (progressed) { t0 = 0; c_next = 0; }
-        else if (hang_should_abort(t0, 21, jk * 1000 + jv, &c_next)) goto done;
+        __syncwarp();
+        ++jv;
+        progressed = true;
+      }
+      if (progressed) { t0 = 0; c_next = 0; }
+      else {
+        const bool abort_ = hang_should_abort(t0, 21, jk * 1000 + jv, &c_next);
+        if (__any_sync(0xffffffffu, abort_)) goto done;
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
-      const uint32_t idesc_o = make_idesc(BQ, D, 1, 1, 0, 1);
-      const uint32_t sQ = smem_u32(smem + L::oQ);
-      const uint32_t sP = smem_u32(smem + L::oP);
-      auto issue_qk = [&](int j) -> bool {
-        const int st = j & 1;
-        if (!mbar_wait_to(&k_full[st], (j >> 1) & 1, 11, j)) return false;
-        tc_fence_after();
-        const uint32_t sK = smem_u32(smem + L::oK + st * L::kKV);
+    const bool elected = elect_one();
+    const uint32_t sbase = __shfl_sync(0xffffffffu, smem_u32(smem), 0);
+    const uint32_t tS_u = __shfl_sync(0xffffffffu, tS, 0);
+    const uint32_t tO_u = tS_u + 128;
+    const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
+    const uint32_t idesc_o = make_idesc(BQ, D, 1, 1, 0, 1);
+    const uint32_t sQ = sbase + L::oQ;
+    const uint32_t sP = sbase + L::oP;
+    auto issue_qk = [&](int j) -> bool {
+      const int st = j & 1;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&k_full[st], (j >> 1) & 1, 11, j))) return false;
+      tc_fence_after();
+      const uint32_t sK = sbase + L::oK + st * L::kKV;
+      if (elected) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
-          umma_f16(tS + (j & 1) * BC, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, BC, kk),
+          umma_f16(tS_u + (j & 1) * BC, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, BC, kk),
                    idesc_s, kk != 0);
         umma_commit(&s_full[j & 1]);
         umma_commit(&k_empty[st]);
-        return true;
-      };
-      if (!mbar_wait_to(q_full, 0, 10)) goto done;
-      if (!issue_qk(0)) goto done;
-      for (int j = 0; j < nblk; ++j) {
-        const int st = j & 1;
-        if (j + 1 < nblk && !issue_qk(j + 1)) goto done;
-        if (!mbar_wait_to(p_full, j & 1, 22)) goto done;
-        if (!mbar_wait_to(&v_full[st], (j >> 1) & 1, 23)) goto done;
-        tc_fence_after();
-        const uint32_t sV = smem_u32(smem + L::oV + st * L::kKV);
+      }
+      __syncwarp();
+      return true;
+    };
+    if (!__all_sync(0xffffffffu, mbar_wait_to(q_full, 0, 10))) goto done;
+    if (!issue_qk(0)) goto done;
+    for (int j = 0; j < nblk; ++j) {
+      const int st = j & 1;
+      if (j + 1 < nblk && !issue_qk(j + 1)) goto done;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(p_full, j & 1, 22))) goto done;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&v_full[st], (j >> 1) & 1, 23))) goto done;
+      tc_fence_after();
+      const uint32_t sV = sbase + L::oV + st * L::kKV;
+      if (elected) {
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
-          umma_f16(tO, desc_kmajor_1(sP, kk), desc_mnmajor(sV, BC, kk), idesc_o,
-                   (j | kk) != 0);
+          umma_f16(tO_u, desc_kmajor_1(sP, kk), desc_mnmajor(sV, BC, kk), idesc_o, (j | kk) != 0);
         umma_commit(&v_empty[st]);
         umma_commit(o_done);
       }
+      __syncwarp();
     }
   } else {
     const int quad = warp & 3;
@@ -390,15 +414,19 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   const uint32_t tDQ = tmem + 256;
 
   if (warp == 0) {
-    if (lane == 0) {
+    const bool elected = elect_one();
+    if (elected) {
       mbar_expect_tx(q_full, 2 * L::kQ);
       for (int hh = 0; hh < NH; ++hh) {
         tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, q0, b);
         tma_load_4d(smem + L::oDO + hh * (BQ * 128), &tmDO, q_full, hh * 64, h, q0, b);
       }
-      for (int j = 0; j < nblk; ++j) {
-        const int st = j % NS;
-        if (!mbar_wait_to(&kv_empty[st], ((j / NS) & 1) ^ 1, 27, j)) goto done;
+    }
+    __syncwarp();
+    for (int j = 0; j < nblk; ++j) {
+      const int st = j % NS;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&kv_empty[st], ((j / NS) & 1) ^ 1, 27, j))) goto done;
+      if (elected) {
         mbar_expect_tx(&kv_full[st], 2 * L::kKV);
         for (int hh = 0; hh < NH; ++hh) {
           tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &kv_full[st], hh * 64, hk,
@@ -407,20 +435,25 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                       j * BC, b);
         }
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
-      const uint32_t idesc_dq = make_idesc(BQ, D, 1, 1, 0, 1);
-      const uint32_t sQ = smem_u32(smem + L::oQ), sDO = smem_u32(smem + L::oDO);
-      const uint32_t sDS = smem_u32(smem + L::oDS);
-      auto issue_sdp = [&](int j) -> bool {
-        const int st = j % NS;
-        if (!mbar_wait_to(&kv_full[st], (j / NS) & 1, 29, j)) return false;
-        tc_fence_after();
-        const uint32_t sK = smem_u32(smem + L::oK + st * L::kKV);
-        const uint32_t sV = smem_u32(smem + L::oV + st * L::kKV);
-        const uint32_t tS = tmem + (j & 1) * 128, tDP = tS + 64;
+    const bool elected = elect_one();
+    const uint32_t sbase = __shfl_sync(0xffffffffu, smem_u32(smem), 0);
+    const uint32_t tm_u = __shfl_sync(0xffffffffu, tmem, 0);
+    const uint32_t tDQ_u = tm_u + 256;
+    const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
+    const uint32_t idesc_dq = make_idesc(BQ, D, 1, 1, 0, 1);
+    const uint32_t sQ = sbase + L::oQ, sDO = sbase + L::oDO;
+    const uint32_t sDS = sbase + L::oDS;
+    auto issue_sdp = [&](int j) -> bool {
+      const int st = j % NS;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&kv_full[st], (j / NS) & 1, 29, j))) return false;
+      tc_fence_after();
+      const uint32_t sK = sbase + L::oK + st * L::kKV;
+      const uint32_t sV = sbase + L::oV + st * L::kKV;
+      const uint32_t tS = tm_u + (j & 1) * 128, tDP = tS + 64;
+      if (elected) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tS, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, BC, kk), idesc_s, kk != 0);
@@ -428,24 +461,27 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tDP, desc_kmajor_d(sDO, BQ, kk), desc_kmajor_d(sV, BC, kk), idesc_s, kk != 0);
         umma_commit(&s_full[j & 1]);
-        return true;
-      };
-      if (!mbar_wait_to(q_full, 0, 28)) goto done;
-      if (!issue_sdp(0)) goto done;
-      for (int j = 0; j < nblk; ++j) {
-        const int st = j % NS;
-        // buffer (j+1)&1 was last read for block j-1, whose ds_full this thread already waited on
-        if (j + 1 < nblk && !issue_sdp(j + 1)) goto done;
-        if (!mbar_wait_to(ds_full, j & 1, 30, j)) goto done;
-        tc_fence_after();
-        const uint32_t sK = smem_u32(smem + L::oK + st * L::kKV);
+      }
+      __syncwarp();
+      return true;
+    };
+    if (!__all_sync(0xffffffffu, mbar_wait_to(q_full, 0, 28))) goto done;
+    if (!issue_sdp(0)) goto done;
+    for (int j = 0; j < nblk; ++j) {
+      const int st = j % NS;
+      // buffer (j+1)&1 was last read for block j-1, whose ds_full this warp already waited on
+      if (j + 1 < nblk && !issue_sdp(j + 1)) goto done;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(ds_full, j & 1, 30, j))) goto done;
+      tc_fence_after();
+      const uint32_t sK = sbase + L::oK + st * L::kKV;
+      if (elected) {
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
-          umma_f16(tDQ, desc_kmajor_1(sDS, kk), desc_mnmajor(sK, BC, kk), idesc_dq,
-                   (j | kk) != 0);
+          umma_f16(tDQ_u, desc_kmajor_1(sDS, kk), desc_mnmajor(sK, BC, kk), idesc_dq, (j | kk) != 0);
         umma_commit(&kv_empty[st]);
         umma_commit(dq_done);
       }
+      __syncwarp();
     }
   } else {
     const int quad = warp & 3;
@@ -591,17 +627,21 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const uint32_t tDV = tmem + 256, tDK = tmem + 384;
 
   if (warp == 0) {
-    if (lane == 0) {
+    const bool elected = elect_one();
+    if (elected) {
       mbar_expect_tx(kv_full, 2 * L::kKV);
       for (int hh = 0; hh < NH; ++hh) {
         tma_load_4d(smem + L::oK + hh * (BQ * 128), &tmK, kv_full, hh * 64, hk, n0, b);
         tma_load_4d(smem + L::oV + hh * (BQ * 128), &tmV, kv_full, hh * 64, hk, n0, b);
       }
-      for (int it = 0; it < niter; ++it) {
-        const int st = it % NS;
-        const int h = hk * group + it / per_head;
-        const int qi = i_start + it % per_head;
-        if (!mbar_wait_to(&q_empty[st], ((it / NS) & 1) ^ 1, 34, it)) goto done;
+    }
+    __syncwarp();
+    for (int it = 0; it < niter; ++it) {
+      const int st = it % NS;
+      const int h = hk * group + it / per_head;
+      const int qi = i_start + it % per_head;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&q_empty[st], ((it / NS) & 1) ^ 1, 34, it))) goto done;
+      if (elected) {
         mbar_expect_tx(&q_full[st], 2 * L::kQ);
         for (int hh = 0; hh < NH; ++hh) {
           tma_load_4d(smem + L::oQ + st * L::kQ + hh * (BC * 128), &tmQ, &q_full[st], hh * 64, h,
@@ -610,20 +650,25 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                       qi * BC, b);
         }
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
-      const uint32_t idesc_acc = make_idesc(BQ, D, 1, 1, 0, 1);
-      const uint32_t sK = smem_u32(smem + L::oK), sV = smem_u32(smem + L::oV);
-      const uint32_t sPT = smem_u32(smem + L::oPT), sDST = smem_u32(smem + L::oDST);
-      auto issue_first = [&](int it) -> bool {
-        const int st = it % NS;
-        if (!mbar_wait_to(&q_full[st], (it / NS) & 1, 36, it)) return false;
-        tc_fence_after();
-        const uint32_t sQ = smem_u32(smem + L::oQ + st * L::kQ);
-        const uint32_t sDO = smem_u32(smem + L::oDO + st * L::kQ);
-        const uint32_t tST = tmem + (it & 1) * 128, tDPT = tST + 64;
+    const bool elected = elect_one();
+    const uint32_t sbase = __shfl_sync(0xffffffffu, smem_u32(smem), 0);
+    const uint32_t tm_u = __shfl_sync(0xffffffffu, tmem, 0);
+    const uint32_t tDV_u = tm_u + 256, tDK_u = tm_u + 384;
+    const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
+    const uint32_t idesc_acc = make_idesc(BQ, D, 1, 1, 0, 1);
+    const uint32_t sK = sbase + L::oK, sV = sbase + L::oV;
+    const uint32_t sPT = sbase + L::oPT, sDST = sbase + L::oDST;
+    auto issue_first = [&](int it) -> bool {
+      const int st = it % NS;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&q_full[st], (it / NS) & 1, 36, it))) return false;
+      tc_fence_after();
+      const uint32_t sQ = sbase + L::oQ + st * L::kQ;
+      const uint32_t sDO = sbase + L::oDO + st * L::kQ;
+      const uint32_t tST = tm_u + (it & 1) * 128, tDPT = tST + 64;
+      if (elected) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tST, desc_kmajor_d(sK, BQ, kk), desc_kmajor_d(sQ, BC, kk), idesc_s, kk != 0);
@@ -631,28 +676,30 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tDPT, desc_kmajor_d(sV, BQ, kk), desc_kmajor_d(sDO, BC, kk), idesc_s, kk != 0);
         umma_commit(&s_full[it & 1]);
-        return true;
-      };
-      if (!mbar_wait_to(kv_full, 0, 35)) goto done;
-      if (niter > 0 && !issue_first(0)) goto done;
-      for (int it = 0; it < niter; ++it) {
-        const int st = it % NS;
-        if (it + 1 < niter && !issue_first(it + 1)) goto done;
-        if (!mbar_wait_to(pt_full, it & 1, 37, it)) goto done;
-        tc_fence_after();
-        const uint32_t sQ = smem_u32(smem + L::oQ + st * L::kQ);
-        const uint32_t sDO = smem_u32(smem + L::oDO + st * L::kQ);
+      }
+      __syncwarp();
+      return true;
+    };
+    if (!__all_sync(0xffffffffu, mbar_wait_to(kv_full, 0, 35))) goto done;
+    if (niter > 0 && !issue_first(0)) goto done;
+    for (int it = 0; it < niter; ++it) {
+      const int st = it % NS;
+      if (it + 1 < niter && !issue_first(it + 1)) goto done;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(pt_full, it & 1, 37, it))) goto done;
+      tc_fence_after();
+      const uint32_t sQ = sbase + L::oQ + st * L::kQ;
+      const uint32_t sDO = sbase + L::oDO + st * L::kQ;
+      if (elected) {
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
-          umma_f16(tDV, desc_kmajor_1(sPT, kk), desc_mnmajor(sDO, BC, kk), idesc_acc,
-                   (it | kk) != 0);
+          umma_f16(tDV_u, desc_kmajor_1(sPT, kk), desc_mnmajor(sDO, BC, kk), idesc_acc, (it | kk) != 0);
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
-          umma_f16(tDK, desc_kmajor_1(sDST, kk), desc_mnmajor(sQ, BC, kk), idesc_acc,
-                   (it | kk) != 0);
+          umma_f16(tDK_u, desc_kmajor_1(sDST, kk), desc_mnmajor(sQ, BC, kk), idesc_acc, (it | kk) != 0);
         umma_commit(&q_empty[st]);
         umma_commit(acc_done);
       }
+      __syncwarp();
     }
   } else {
     const int quad = warp & 3;

@@ -112,17 +112,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tn = r / gm;
   };
 
+  // Whole-warp uniform role loops; the async instruction is predicated on one elected lane (see the
+  // CTA-pair kernel below for why).
+  const uint32_t sbase = __shfl_sync(0xffffffffu, smem_u32(smem), 0);
+  const uint32_t tbase = __shfl_sync(0xffffffffu, tmem_base, 0);
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        int tm, tn;
-        tile_coord(t, tm, tn);
-        const int m0 = tm * BM, n0 = tn * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          if (!mbar_wait_to(&empty_bar[stage], phase ^ 1, 1, kb)) goto done;
+    const bool elected = elect_one();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      int tm, tn;
+      tile_coord(t, tm, tn);
+      const int m0 = tm * BM, n0 = tn * BN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        if (!__all_sync(0xffffffffu, mbar_wait_to(&empty_bar[stage], phase ^ 1, 1, kb))) goto done;
+        if (elected) {
           uint8_t* sa = smem + stage * Plan::kStage;
           uint8_t* sb = sa + Plan::kA;
           mbar_expect_tx(&full_bar[stage], Plan::kStage);
@@ -141,51 +146,56 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             for (int j = 0; j < BN / 64; ++j)
               tma_load_2d(sb + j * (64 * BK * 2), &tmB, &full_bar[stage], n0 + j * 64, k0);
           }
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1;
-          }
+        }
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
         }
       }
     }
   } else if (warp == 1) {
     // -------------------------------------------------------------- MMA issuer
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc(BM, BN, 1, 1, a_mn ? 1u : 0u, b_mn ? 1u : 0u);
-      int stage = 0;
-      uint32_t phase = 0;
-      int acc = 0;
-      uint32_t acc_phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        if (!mbar_wait_to(&tempty_bar[acc], acc_phase ^ 1, 2, t)) goto done;
+    const bool elected = elect_one();
+    const uint32_t idesc = make_idesc(BM, BN, 1, 1, a_mn ? 1u : 0u, b_mn ? 1u : 0u);
+    constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    const uint32_t a_lo0 = ((sbase >> 4) & 0x3FFFu) | ((a_mn ? (64u * BK * 2) >> 4 : 1u) << 16);
+    const uint32_t b_lo0 = (((sbase + Plan::kA) >> 4) & 0x3FFFu) | ((b_mn ? (64u * BK * 2) >> 4 : 1u) << 16);
+    const uint32_t a_kstep = a_mn ? (2048u >> 4) : (32u >> 4);
+    const uint32_t b_kstep = b_mn ? (2048u >> 4) : (32u >> 4);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&tempty_bar[acc], acc_phase ^ 1, 2, t))) goto done;
+      tc_fence_after();
+      const uint32_t d_tmem = tbase + acc * BN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        if (!__all_sync(0xffffffffu, mbar_wait_to(&full_bar[stage], phase, 3, kb))) goto done;
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          if (!mbar_wait_to(&full_bar[stage], phase, 3, kb)) goto done;
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * Plan::kStage);
-          const uint32_t sb = sa + Plan::kA;
+        const uint32_t a_lo = a_lo0 + stage * (Plan::kStage >> 4);
+        const uint32_t b_lo = b_lo0 + stage * (Plan::kStage >> 4);
+        if (elected) {
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
-            // K-major: 16 elements = 32 B inside the swizzled 128 B row.
-            // MN-major: 16 k-rows of 128 B = 2048 B (two 8-row swizzle atoms).
-            const uint64_t adesc = a_mn ? make_smem_desc(sa + k * 2048, 64 * BK * 2, 1024, 2)
-                                        : make_smem_desc(sa + k * 32, 16, 1024, 2);
-            const uint64_t bdesc = b_mn ? make_smem_desc(sb + k * 2048, 64 * BK * 2, 1024, 2)
-                                        : make_smem_desc(sb + k * 32, 16, 1024, 2);
+            const uint64_t adesc = (uint64_t(kDescHi) << 32) | (a_lo + k * a_kstep);
+            const uint64_t bdesc = (uint64_t(kDescHi) << 32) | (b_lo + k * b_kstep);
             umma_f16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0);
           }
           umma_commit(&empty_bar[stage]);
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1;
-          }
         }
-        umma_commit(&tfull_bar[acc]);
-        if (++acc == 2) {
-          acc = 0;
-          acc_phase ^= 1;
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
         }
+      }
+      if (elected) umma_commit(&tfull_bar[acc]);
+      __syncwarp();
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
       }
     }
   } else {
