@@ -19,6 +19,7 @@ namespace sxb {
 namespace attn {
 
 constexpr int kThreads = 192;
+constexpr int kBwdThreads = 320;  // TMA warp + MMA warp + 8 row-warps
 constexpr int BQ = 128;   // rows owned by the 128 row-threads (queries in fwd/dq, keys in dkv)
 constexpr int BC = 64;    // inner block (keys in fwd/dq, queries in dkv)
 constexpr float kLog2e = 1.4426950408889634f;
@@ -47,6 +48,32 @@ __device__ __forceinline__ void store_row_sw128(uint8_t* tile, int row, const fl
     o.z = pack_bf16(v[c * 8 + 4], v[c * 8 + 5]);
     o.w = pack_bf16(v[c * 8 + 6], v[c * 8 + 7]);
     *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = o;
+  }
+}
+
+// Half-row variants for the backward kernels, where TWO warps share each TMEM lane quadrant and split
+// the 64 columns of a block between them (8 row-warps per CTA -> 2 per scheduler instead of 1).
+__device__ __forceinline__ void store_half_sw128(uint8_t* tile, int row, int half, const float (&v)[32]) {
+  uint8_t* dst = tile + row * 128;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    uint4 o;
+    o.x = pack_bf16(v[c * 8 + 0], v[c * 8 + 1]);
+    o.y = pack_bf16(v[c * 8 + 2], v[c * 8 + 3]);
+    o.z = pack_bf16(v[c * 8 + 4], v[c * 8 + 5]);
+    o.w = pack_bf16(v[c * 8 + 6], v[c * 8 + 7]);
+    *reinterpret_cast<uint4*>(dst + (((half * 4 + c) ^ (row & 7)) << 4)) = o;
+  }
+}
+__device__ __forceinline__ void ld_row32x2(uint32_t taddr_a, uint32_t taddr_b, float (&a)[32], float (&b)[32]) {
+  uint32_t x[32], y[32];
+  tmem_ld_32x32(taddr_a, x);
+  tmem_ld_32x32(taddr_b, y);
+  tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    a[i] = __uint_as_float(x[i]);
+    b[i] = __uint_as_float(y[i]);
   }
 }
 
@@ -110,7 +137,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint64_t* s_full = bars + 9;    // [2]
   uint64_t* p_full = bars + 11;
   uint64_t* o_done = bars + 12;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint64_t* s_free = bars + 13;   // [2]  row warps have copied S(j) out of TMEM (one arrive per warp)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = gridDim.x - 1 - blockIdx.x;  // heavy (late) causal tiles first
@@ -132,6 +160,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       mbar_init(p_full, 128);
       mbar_init(o_done, 1);
+      mbar_init(&s_free[0], 4);
+      mbar_init(&s_free[1], 4);
       mbar_fence_init();
     }
     __syncwarp();
@@ -222,6 +252,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     };
     if (!__all_sync(0xffffffffu, mbar_wait_to(q_full, 0, 10))) goto done;
     if (!issue_qk(0)) goto done;
+    // Measured: issuing S(j+2) as soon as the row warps have copied S(j) out of TMEM (an "early
+    // release" of the S buffer) is SLOWER (0.98-1.24 ms vs 0.83 ms at S=8192) than keeping S one block
+    // ahead, so QK(j+1) is issued right behind PV(j-1).
     for (int j = 0; j < nblk; ++j) {
       const int st = j & 1;
       if (j + 1 < nblk && !issue_qk(j + 1)) goto done;
@@ -354,7 +387,7 @@ template <int D>
 struct DqSmem {
   static constexpr int kQ = BQ * D * 2;      // Q and dO tiles
   static constexpr int kKV = BC * D * 2;
-  static constexpr int kStages = 3;
+  static constexpr int kStages = 4;
   static constexpr int kDS = BQ * BC * 2;
   static constexpr int oQ = 0;
   static constexpr int oDO = oQ + kQ;
@@ -366,7 +399,7 @@ struct DqSmem {
 };
 
 template <int D>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
                    const Params p) {
@@ -378,12 +411,13 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                                              ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
   uint64_t* q_full = bars + 0;
-  uint64_t* kv_full = bars + 1;   // [3]
-  uint64_t* kv_empty = bars + 4;  // [3]
-  uint64_t* s_full = bars + 7;    // [2] S and dP of buffer b ready
-  uint64_t* ds_full = bars + 9;   // dS written (128 arrivals)
-  uint64_t* dq_done = bars + 10;  // dQ MMA of block j finished
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  uint64_t* kv_full = bars + 1;   // [4]
+  uint64_t* kv_empty = bars + 5;  // [4]
+  uint64_t* s_full = bars + 9;    // [2] S and dP of buffer b ready
+  uint64_t* ds_full = bars + 11;  // dS written (256 arrivals)
+  uint64_t* dq_done = bars + 12;  // dQ MMA of block j finished
+  uint64_t* s_free = bars + 13;   // [2] row warps copied S/dP of buffer b out of TMEM (one arrive per warp)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = gridDim.x - 1 - blockIdx.x;
@@ -399,8 +433,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       for (int i = 0; i < NS; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1); }
       mbar_init(&s_full[0], 1);
       mbar_init(&s_full[1], 1);
-      mbar_init(ds_full, 128);
+      mbar_init(ds_full, 256);
       mbar_init(dq_done, 1);
+      mbar_init(&s_free[0], 8);
+      mbar_init(&s_free[1], 8);
       mbar_fence_init();
     }
     __syncwarp();
@@ -484,7 +520,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       __syncwarp();
     }
   } else {
-    const int quad = warp & 3;
+    const int quad = warp & 3;                 // TMEM lane quadrant (hardware: warp id mod 4)
+    const int half = (warp - 2) >> 2;          // which 32 of the block's 64 key columns
     const int row = quad * 32 + lane;
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
     const int qpos = q0 + row;
@@ -496,15 +533,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     for (int j = 0; j < nblk; ++j) {
       if (!mbar_wait_to(&s_full[j & 1], (j >> 1) & 1, 31, j)) goto done;
       tc_fence_after();
-      float s[64], dp[64];
-      const uint32_t tS = tmem + (j & 1) * 128 + lane_off;
-      ld_row64(tS, s);
-      ld_row64(tS + 64, dp);
-      const int k0 = j * BC;
-      const bool need_mask = (p.causal && (k0 + BC - 1 > q0)) || (k0 + BC > p.S) || (q0 + BQ > p.S);
+      float s[32], dp[32];
+      const uint32_t tS = tmem + (j & 1) * 128 + lane_off + half * 32;
+      ld_row32x2(tS, tS + 64, s, dp);
+      const int k0 = j * BC + half * 32;
+      const bool need_mask = (p.causal && (k0 + 31 > q0)) || (k0 + 32 > p.S) || (q0 + BQ > p.S);
       if (need_mask) {
 #pragma unroll
-        for (int c = 0; c < 64; ++c) {
+        for (int c = 0; c < 32; ++c) {
           const int kp = k0 + c;
           const bool ok = (kp < p.S) && (!p.causal || kp <= qpos) && (qpos < p.S);
           const float pr = ok ? fast_exp2(fmaf(s[c], sc, -lse2)) : 0.f;
@@ -512,13 +548,13 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         }
       } else {
 #pragma unroll
-        for (int c = 0; c < 64; ++c) {
+        for (int c = 0; c < 32; ++c) {
           const float pr = fast_exp2(fmaf(s[c], sc, -lse2));
           s[c] = pr * (dp[c] - dlt) * p.scale;
         }
       }
       if (j > 0) if (!mbar_wait_to(dq_done, (j - 1) & 1, 32, j)) goto done;  // dQ(j-1) no longer reads sDS
-      store_row_sw128(sDS, row, s);
+      store_half_sw128(sDS, row, half, s);
       fence_async_smem();
       tc_fence_before();
       mbar_arrive(ds_full);
@@ -528,7 +564,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
                           ((long long)b * p.S + min(qpos, p.S - 1)) * p.out_stride + (long long)h * D;
 #pragma unroll 1
-    for (int c = 0; c < D / 32; ++c) {
+    for (int c = half * (D / 64); c < (half + 1) * (D / 64); ++c) {
       uint32_t o[32];
       tmem_ld_32x32(tDQ + lane_off + c * 32, o);
       tmem_ld_wait();
@@ -577,7 +613,7 @@ struct DkvSmem {
 };
 
 template <int D>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
                     const Params p) {
@@ -592,9 +628,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint64_t* q_full = bars + 1;    // [3]
   uint64_t* q_empty = bars + 4;   // [3]
   uint64_t* s_full = bars + 7;    // [2]
-  uint64_t* pt_full = bars + 9;   // 128 arrivals
+  uint64_t* pt_full = bars + 9;   // 256 arrivals
   uint64_t* acc_done = bars + 10;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  uint64_t* s_free = bars + 11;   // [2] one arrive per row warp
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kt = blockIdx.x;
@@ -612,8 +649,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       for (int i = 0; i < NS; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
       mbar_init(&s_full[0], 1);
       mbar_init(&s_full[1], 1);
-      mbar_init(pt_full, 128);
+      mbar_init(pt_full, 256);
       mbar_init(acc_done, 1);
+      mbar_init(&s_free[0], 8);
+      mbar_init(&s_free[1], 8);
       mbar_fence_init();
     }
     __syncwarp();
@@ -703,8 +742,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     }
   } else {
     const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;          // which 32 of the block's 64 query columns
     const int row = quad * 32 + lane;
-    const int et = threadIdx.x - 64;
+    const int et = threadIdx.x - 64;           // 0..255
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
     const int kpos = n0 + row;
     const float sc = p.scale * kLog2e;
@@ -718,25 +758,26 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const long long si = ((long long)b * p.Hq + h) * p.S + qq;
       return (et < 64) ? p.lse[si] * kLog2e : p.delta[si];
     };
-    float nxt = (niter > 0) ? load_stat(0) : 0.f;
+    float nxt = (niter > 0 && et < 128) ? load_stat(0) : 0.f;
     for (int it = 0; it < niter; ++it) {
       const int st = it % NS;
-      const int qb = (i_start + it % per_head) * BC;
-      stat[st * 128 + et] = nxt;
-      if (it + 1 < niter) nxt = load_stat(it + 1);     // prefetch: consumed next iteration
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const int qb = (i_start + it % per_head) * BC + half * 32;
+      if (et < 128) {
+        stat[st * 128 + et] = nxt;
+        if (it + 1 < niter) nxt = load_stat(it + 1);   // prefetch: consumed next iteration
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       if (!mbar_wait_to(&s_full[it & 1], (it >> 1) & 1, 38, it)) goto done;
       tc_fence_after();
-      float s[64], dp[64];
-      const uint32_t tST = tmem + (it & 1) * 128 + lane_off;
-      ld_row64(tST, s);
-      ld_row64(tST + 64, dp);
-      const float* lse2 = stat + st * 128;
+      float s[32], dp[32];
+      const uint32_t tST = tmem + (it & 1) * 128 + lane_off + half * 32;
+      ld_row32x2(tST, tST + 64, s, dp);
+      const float* lse2 = stat + st * 128 + half * 32;
       const float* dlt = lse2 + 64;
-      const bool need_mask = (p.causal && (n0 + BQ - 1 > qb)) || (qb + BC > p.S) || (n0 + BQ > p.S);
+      const bool need_mask = (p.causal && (n0 + BQ - 1 > qb)) || (qb + 32 > p.S) || (n0 + BQ > p.S);
       if (need_mask) {
 #pragma unroll
-        for (int c = 0; c < 64; ++c) {
+        for (int c = 0; c < 32; ++c) {
           const int qp = qb + c;
           const bool ok = (qp < p.S) && (kpos < p.S) && (!p.causal || kpos <= qp);
           const float pr = ok ? fast_exp2(fmaf(s[c], sc, -lse2[c])) : 0.f;
@@ -745,15 +786,15 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
       } else {
 #pragma unroll
-        for (int c = 0; c < 64; ++c) {
+        for (int c = 0; c < 32; ++c) {
           const float pr = fast_exp2(fmaf(s[c], sc, -lse2[c]));
           s[c] = pr;
           dp[c] = pr * (dp[c] - dlt[c]) * p.scale;
         }
       }
       if (it > 0) if (!mbar_wait_to(acc_done, (it - 1) & 1, 39, it)) goto done;
-      store_row_sw128(sPT, row, s);
-      store_row_sw128(sDST, row, dp);
+      store_half_sw128(sPT, row, half, s);
+      store_half_sw128(sDST, row, half, dp);
       fence_async_smem();
       tc_fence_before();
       mbar_arrive(pt_full);
@@ -762,23 +803,25 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (!mbar_wait_to(acc_done, (niter - 1) & 1, 40)) goto done;
       tc_fence_after();
     }
+    // half 0 drains dV, half 1 drains dK
     const long long orow_idx = (long long)b * p.S + min(kpos, p.S - 1);
-    __nv_bfloat16* dk_row = reinterpret_cast<__nv_bfloat16*>(p.out) + orow_idx * p.out_stride + (long long)hk * D;
-    __nv_bfloat16* dv_row = reinterpret_cast<__nv_bfloat16*>(p.out2) + orow_idx * p.out2_stride + (long long)hk * D;
+    const bool is_dv = (half == 0);
+    __nv_bfloat16* dst_row = is_dv
+        ? reinterpret_cast<__nv_bfloat16*>(p.out2) + orow_idx * p.out2_stride + (long long)hk * D
+        : reinterpret_cast<__nv_bfloat16*>(p.out) + orow_idx * p.out_stride + (long long)hk * D;
+    const uint32_t t_acc = (is_dv ? tDV : tDK) + lane_off;
 #pragma unroll 1
-    for (int c = 0; c < 2 * (D / 32); ++c) {
-      const bool is_dv = c < D / 32;
-      const int cc = is_dv ? c : c - D / 32;
+    for (int cc = 0; cc < D / 32; ++cc) {
       uint32_t o[32];
       if (niter > 0) {
-        tmem_ld_32x32((is_dv ? tDV : tDK) + lane_off + cc * 32, o);
+        tmem_ld_32x32(t_acc + cc * 32, o);
         tmem_ld_wait();
       } else {
 #pragma unroll
         for (int i = 0; i < 32; ++i) o[i] = 0u;
       }
       if (kpos < p.S) {
-        __nv_bfloat16* dst = (is_dv ? dv_row : dk_row) + cc * 32;
+        __nv_bfloat16* dst = dst_row + cc * 32;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           uint4 w;
@@ -921,10 +964,10 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     dim3 grid((S + BQ - 1) / BQ, Hq, B);
     if (D == 128) {
       if ((rc = set_smem(attn_bwd_dq_kernel<128>, DqSmem<128>::kTotal))) return rc;
-      attn_bwd_dq_kernel<128><<<grid, kThreads, DqSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
+      attn_bwd_dq_kernel<128><<<grid, kBwdThreads, DqSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
     } else {
       if ((rc = set_smem(attn_bwd_dq_kernel<64>, DqSmem<64>::kTotal))) return rc;
-      attn_bwd_dq_kernel<64><<<grid, kThreads, DqSmem<64>::kTotal, s>>>(tq, tk, tv, tdo, p);
+      attn_bwd_dq_kernel<64><<<grid, kBwdThreads, DqSmem<64>::kTotal, s>>>(tq, tk, tv, tdo, p);
     }
     SXB_CHECK_LAUNCH();
   }
@@ -939,10 +982,10 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     dim3 grid((S + BQ - 1) / BQ, Hk, B);
     if (D == 128) {
       if ((rc = set_smem(attn_bwd_dkv_kernel<128>, DkvSmem<128>::kTotal))) return rc;
-      attn_bwd_dkv_kernel<128><<<grid, kThreads, DkvSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
+      attn_bwd_dkv_kernel<128><<<grid, kBwdThreads, DkvSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
     } else {
       if ((rc = set_smem(attn_bwd_dkv_kernel<64>, DkvSmem<64>::kTotal))) return rc;
-      attn_bwd_dkv_kernel<64><<<grid, kThreads, DkvSmem<64>::kTotal, s>>>(tq, tk, tv, tdo, p);
+      attn_bwd_dkv_kernel<64><<<grid, kBwdThreads, DkvSmem<64>::kTotal, s>>>(tq, tk, tv, tdo, p);
     }
     SXB_CHECK_LAUNCH();
   }
