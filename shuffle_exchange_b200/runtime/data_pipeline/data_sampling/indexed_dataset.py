@@ -1,0 +1,219 @@
+"""Memory-mapped indexed dataset (Megatron ``MMIDIDX`` on-disk format) used by the data-efficiency pipeline for
+both token data and the per-sample metric / cluster index files.
+
+Reference: ``data_sampling/indexed_dataset.py:369-627`` (``MMapIndexedDataset`` + ``MMapIndexedDatasetBuilder``).
+File layout kept byte-compatible so existing ``.bin/.idx`` pairs load:
+
+    .idx : b"MMIDIDX\\0\\0" | <Q version=1> | <B dtype code> | <Q n_items> | <Q n_docs>
+           | int32 sizes[n_items] | int64 byte pointers[n_items] | int64 doc_idx[n_docs]
+    .bin : the items back to back
+
+The legacy (non-mmap) ``IndexedDataset`` variants of the reference are not reproduced; ``make_dataset`` accepts only
+``mmap`` (``infer_dataset_impl`` reports other files as unsupported).
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import struct
+
+import numpy as np
+import torch
+
+_MAGIC = b"MMIDIDX\x00\x00"
+_DTYPES = {1: np.uint8, 2: np.int8, 3: np.int16, 4: np.int32, 5: np.int64, 6: np.float64, 7: np.float32,
+           8: np.uint16, 9: np.uint32, 10: np.uint64}
+
+
+def code(dtype) -> int:
+    for k, v in _DTYPES.items():
+        if v == dtype:
+            return k
+    raise ValueError(dtype)
+
+
+def index_file_path(prefix_path: str) -> str:
+    return prefix_path + ".idx"
+
+
+def data_file_path(prefix_path: str) -> str:
+    return prefix_path + ".bin"
+
+
+def get_available_dataset_impl():
+    return ["mmap"]
+
+
+def infer_dataset_impl(path):
+    if not MMapIndexedDataset.exists(path):
+        return None
+    with open(index_file_path(path), "rb") as f:
+        return "mmap" if f.read(9) == _MAGIC else None
+
+
+def dataset_exists(path, impl="mmap"):
+    return MMapIndexedDataset.exists(path)
+
+
+def make_builder(out_file, impl="mmap", vocab_size=None):
+    dtype = np.uint16 if vocab_size is not None and vocab_size < 65500 else np.int32
+    return MMapIndexedDatasetBuilder(out_file, dtype=dtype)
+
+
+def make_dataset(path, impl="mmap", skip_warmup=False):
+    if not MMapIndexedDataset.exists(path):
+        print(f"Dataset does not exist: {path}")
+        return None
+    if impl == "infer":
+        impl = infer_dataset_impl(path)
+    if impl != "mmap":
+        raise ValueError(f"dataset implementation '{impl}' is not supported (mmap only)")
+    return MMapIndexedDataset(path, skip_warmup)
+
+
+class _Index:
+    def __init__(self, path: str):
+        with open(path, "rb") as f:
+            if f.read(9) != _MAGIC:
+                raise ValueError(f"{path} is not an MMIDIDX index file")
+            (version,) = struct.unpack("<Q", f.read(8))
+            assert version == 1
+            (dcode,) = struct.unpack("<B", f.read(1))
+            self.dtype = _DTYPES[dcode]
+            (self.n,) = struct.unpack("<Q", f.read(8))
+            (self.n_docs,) = struct.unpack("<Q", f.read(8))
+            offset = f.tell()
+        self._mm = np.memmap(path, mode="r", order="C")
+        buf = memoryview(self._mm)
+        self.sizes = np.frombuffer(buf, dtype=np.int32, count=self.n, offset=offset)
+        self.pointers = np.frombuffer(buf, dtype=np.int64, count=self.n, offset=offset + self.sizes.nbytes)
+        self.doc_idx = np.frombuffer(buf, dtype=np.int64, count=self.n_docs,
+                                     offset=offset + self.sizes.nbytes + self.pointers.nbytes)
+
+    @staticmethod
+    def write(path: str, dtype, sizes, doc_idx):
+        sizes = np.asarray(sizes, dtype=np.int32)
+        itemsize = np.dtype(dtype).itemsize
+        pointers = np.zeros(len(sizes), dtype=np.int64)
+        if len(sizes) > 1:
+            np.cumsum(sizes[:-1].astype(np.int64) * itemsize, out=pointers[1:])
+        with open(path, "wb") as f:
+            f.write(_MAGIC)
+            f.write(struct.pack("<Q", 1))
+            f.write(struct.pack("<B", code(dtype)))
+            f.write(struct.pack("<Q", len(sizes)))
+            f.write(struct.pack("<Q", len(doc_idx)))
+            f.write(sizes.tobytes(order="C"))
+            f.write(pointers.tobytes(order="C"))
+            f.write(np.asarray(doc_idx, dtype=np.int64).tobytes(order="C"))
+
+
+class MMapIndexedDataset(torch.utils.data.Dataset):
+    def __init__(self, path, skip_warmup=False):
+        super().__init__()
+        self._path = None
+        self._do_init(path, skip_warmup)
+
+    def __getstate__(self):
+        return self._path
+
+    def __setstate__(self, state):
+        self._do_init(state, skip_warmup=True)
+
+    def _do_init(self, path, skip_warmup):
+        self._path = path
+        self._index = _Index(index_file_path(path))
+        if not skip_warmup:
+            with open(data_file_path(path), "rb") as f:      # touch the pages once
+                while f.read(100 * 1024 * 1024):
+                    pass
+        self._bin = np.memmap(data_file_path(path), mode="r", order="C")
+        self._buf = memoryview(self._bin)
+
+    def __len__(self):
+        return self._index.n
+
+    def __getitem__(self, idx):
+        if isinstance(idx, (int, np.integer)):
+            ptr, size = self._index.pointers[idx], self._index.sizes[idx]
+            return np.frombuffer(self._buf, dtype=self._index.dtype, count=size, offset=ptr)
+        if isinstance(idx, slice):
+            start, stop, step = idx.indices(len(self))
+            if step != 1:
+                raise ValueError("Slices into indexed_dataset must be contiguous")
+            ptr = self._index.pointers[start]
+            sizes = self._index.sizes[idx]
+            flat = np.frombuffer(self._buf, dtype=self._index.dtype, count=int(sum(sizes)), offset=ptr)
+            return np.split(flat, np.cumsum(sizes)[:-1])
+        raise TypeError(f"bad index {idx!r}")
+
+    def get(self, idx, offset=0, length=None):
+        ptr, size = self._index.pointers[idx], self._index.sizes[idx]
+        length = size - offset if length is None else length
+        ptr += offset * np.dtype(self._index.dtype).itemsize
+        return np.frombuffer(self._buf, dtype=self._index.dtype, count=length, offset=ptr)
+
+    @property
+    def sizes(self):
+        return self._index.sizes
+
+    def size(self, index):
+        return self._index.sizes[index]
+
+    @property
+    def doc_idx(self):
+        return self._index.doc_idx
+
+    def get_doc_idx(self):
+        return self._index.doc_idx
+
+    def set_doc_idx(self, doc_idx_):
+        self._index.doc_idx = doc_idx_
+
+    @property
+    def supports_prefetch(self):
+        return False
+
+    @property
+    def dtype(self):
+        return self._index.dtype
+
+    @staticmethod
+    def exists(path):
+        return os.path.exists(index_file_path(path)) and os.path.exists(data_file_path(path))
+
+
+class MMapIndexedDatasetBuilder:
+    def __init__(self, out_file, dtype=np.int64):
+        self._data_file = open(out_file, "wb")
+        self._dtype = dtype
+        self._sizes = []
+        self._doc_idx = [0]
+
+    def add_item(self, tensor):
+        self.add_item_numpy(np.asarray(tensor.numpy() if torch.is_tensor(tensor) else tensor))
+
+    def add_items(self, arr_list):
+        for a in arr_list:
+            self.add_item_numpy(np.asarray(a))
+
+    def add_item_numpy(self, np_array):
+        arr = np_array.astype(self._dtype, copy=False)
+        self._data_file.write(arr.tobytes(order="C"))
+        self._sizes.append(arr.size)
+
+    def end_document(self):
+        self._doc_idx.append(len(self._sizes))
+
+    def merge_file_(self, another_file):
+        index = _Index(index_file_path(another_file))
+        assert index.dtype == self._dtype
+        total = len(self._sizes)
+        self._sizes.extend(int(s) for s in index.sizes)
+        self._doc_idx.extend(int(d) + total for d in index.doc_idx[1:])
+        with open(data_file_path(another_file), "rb") as f:
+            shutil.copyfileobj(f, self._data_file)
+
+    def finalize(self, index_file):
+        self._data_file.close()
+        _Index.write(index_file, self._dtype, self._sizes, self._doc_idx)
