@@ -240,8 +240,11 @@ subset_mean_kernel(Peers P, Members M, T* __restrict__ out, long long n, uint32_
 __global__ void __launch_bounds__(kThreads)
 all_gather_kernel(Peers P, long long part_bytes, uint8_t* __restrict__ dst, long long chunk_bytes,
                   uint32_t* __restrict__ chunk_flags, uint32_t epoch) {
-  if (blockIdx.x == 0) signal_all(P, 4, epoch);
-  if (!wait_all(P, 4, epoch, 104)) return;
+  // epoch == 0: barrier-free pull (the caller established shard readiness once per step with sxb_symm_barrier)
+  if (epoch != 0) {
+    if (blockIdx.x == 0) signal_all(P, 4, epoch);
+    if (!wait_all(P, 4, epoch, 104)) return;
+  }
   const long long total = part_bytes * P.world;
   const long long nchunks = (total + chunk_bytes - 1) / chunk_bytes;
   for (long long c = blockIdx.x; c < nchunks; c += gridDim.x) {
@@ -367,6 +370,21 @@ SXB_API int sxb_symm_rs_adam(const void* const* bufs, const void* const* sigs, i
   rs_adam_kernel<<<grid_cap(part / 8, max_ctas), kThreads, 0, (cudaStream_t)stream>>>(
       P, part, (float*)hp, (float*)m, (float*)v, (__nv_bfloat16*)lp, (__nv_bfloat16*)grad_out, a, epoch,
       multicast_ptr, (unsigned int*)counter, apply_adam);
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+// Full barrier on `channel`: tell every peer "I reached `epoch`", then wait until all of them did.
+__global__ void barrier_channel_kernel(sxb::symm::Peers P, int channel, uint32_t epoch) {
+  sxb::symm::signal_all(P, channel, epoch);
+  sxb::symm::wait_all(P, channel, epoch, 110);
+}
+SXB_API int sxb_symm_barrier(const void* const* bufs, const void* const* sigs, int rank, int world, int channel,
+                             unsigned int epoch, void* stream) {
+  Peers P;
+  int rc = fill_peers(P, bufs, sigs, rank, world);
+  if (rc) return rc;
+  barrier_channel_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, channel, epoch);
   SXB_CHECK_LAUNCH();
   return SXB_OK;
 }

@@ -27,6 +27,7 @@ from ..native import lib as _n
 _n.register({
     "sxb_symm_rs_adam": "ppiil" "ppppp" "fffff" "iii" "f" "i" "pp" "ii" "p",
     "sxb_symm_wait": "ppiiiip",
+    "sxb_symm_barrier": "ppiiiip",
     "sxb_symm_subset_mean": "ppiipiplii" "pip",
     "sxb_symm_all_gather": "ppiilplpiip",
     "sxb_symm_a2a_rows": "ppiippppiipip",
@@ -66,6 +67,16 @@ class SymmBuffer:
     def next_epoch(self, ch: int) -> int:
         self.epochs[ch] += 1
         return self.epochs[ch]
+
+    def peer_tensor(self, rank: int) -> torch.Tensor:
+        """The whole buffer of ``rank`` as a tensor on THIS device's address space (NVLink peer mapping); copying
+        from it with ``Tensor.copy_`` is a ``cudaMemcpyAsync`` served by the copy engines — no SMs involved."""
+        cache = self.__dict__.setdefault("_peer_tensors", {})
+        t = cache.get(rank)
+        if t is None:
+            t = cache[rank] = (self.tensor if rank == self.rank else
+                               self.handle.get_buffer(rank, tuple(self.tensor.shape), self.tensor.dtype))
+        return t
 
     @property
     def bufs(self):
@@ -141,9 +152,18 @@ class SymmGroup:
                 _n.dtype_code(out.dtype), int(epoch), self._ctr(1), int(max_ctas), _n.stream_ptr())
 
     # ------------------------------------------------------------------------------------- K2
+    def barrier(self, buf: SymmBuffer, channel: int = CH_AG_READY):
+        """Stream-ordered barrier among all ranks of the group on ``buf``'s signal pad."""
+        epoch = buf.next_epoch(channel)
+        _n.call("sxb_symm_barrier", buf.bufs, buf.sigs, self.rank, self.world, int(channel), int(epoch),
+                _n.stream_ptr())
+        return epoch
+
     def all_gather(self, shard: SymmBuffer, part_numel: int, dst: torch.Tensor, chunk_bytes: int = 1 << 20,
-                   chunk_flags: Optional[torch.Tensor] = None, max_ctas: int = 32):
-        epoch = shard.next_epoch(CH_AG_READY)
+                   chunk_flags: Optional[torch.Tensor] = None, max_ctas: int = 32, barrier: bool = True):
+        """``barrier=False``: pure pull, no cross-rank handshake (the shards were declared ready by an earlier
+        :meth:`barrier` and do not change until the next one)."""
+        epoch = shard.next_epoch(CH_AG_READY) if barrier else 0
         es = dst.element_size()
         _n.call("sxb_symm_all_gather", shard.bufs, shard.sigs, self.rank, self.world, int(part_numel * es),
                 dst.data_ptr(), int(chunk_bytes), _n.ptr(chunk_flags), int(epoch), int(max_ctas), _n.stream_ptr())

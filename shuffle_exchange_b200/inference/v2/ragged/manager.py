@@ -1,0 +1,69 @@
+"""Sequence / KV-cache state manager (reference: ``inference/v2/ragged/ragged_manager.py:19-206``)."""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, Optional
+
+import torch
+
+from .kv_cache import BlockedKVCache, KVCacheConfig
+from .sequence_descriptor import DSSequenceDescriptor
+
+
+@dataclass
+class DSStateManagerConfig:
+    max_tracked_sequences: int = 2048
+    max_ragged_batch_size: int = 768
+    max_ragged_sequence_count: int = 512
+    max_context: int = 8192
+    memory_config_fraction: float = 0.8
+    num_kv_blocks: Optional[int] = None
+    offload: bool = False
+
+
+class DSStateManager:
+    def __init__(self, config: DSStateManagerConfig, kv_config: KVCacheConfig, device=None) -> None:
+        self._config, self._kv_config = config, kv_config
+        self._seqs: Dict[int, DSSequenceDescriptor] = {}
+        self._kv_cache = BlockedKVCache(kv_config, num_blocks=config.num_kv_blocks,
+                                        memory_fraction=config.memory_config_fraction, device=device)
+        self.max_blocks_per_seq = (config.max_context + kv_config.block_size - 1) // kv_config.block_size
+
+    def get_sequence(self, uid: int) -> Optional[DSSequenceDescriptor]:
+        return self._seqs.get(uid)
+
+    def get_or_create_sequence(self, uid: int) -> DSSequenceDescriptor:
+        seq = self._seqs.get(uid)
+        if seq is None:
+            if len(self._seqs) >= self._config.max_tracked_sequences:
+                raise RuntimeError(f"Unable to create tracking slot for sequence {uid}: too many tracked sequences")
+            seq = self._seqs[uid] = DSSequenceDescriptor(uid, self.max_blocks_per_seq)
+        return seq
+
+    def flush_sequence(self, uid: int) -> None:
+        seq = self._seqs.pop(uid, None)
+        if seq is None:
+            return
+        self._kv_cache.free(seq.kv_blocks())
+
+    def allocate_blocks(self, n_blocks: int) -> torch.Tensor:
+        return self._kv_cache.reserve(n_blocks)
+
+    def get_cache(self, layer: int) -> torch.Tensor:
+        return self._kv_cache.get_cache(layer)
+
+    @property
+    def free_blocks(self) -> int:
+        return self._kv_cache.free_blocks
+
+    @property
+    def kv_block_size(self) -> int:
+        return self._kv_config.block_size
+
+    @property
+    def n_tracked_sequences(self) -> int:
+        return len(self._seqs)
+
+    @property
+    def tracked_sequences(self):
+        return self._seqs

@@ -1,0 +1,56 @@
+"""Per-sequence bookkeeping (reference: ``inference/v2/ragged/sequence_descriptor.py:58-280``): tokens already in the
+cache, tokens in flight in the current forward, and the KV block ids the sequence owns."""
+from __future__ import annotations
+
+from typing import List
+
+import torch
+
+
+class DSSequenceDescriptor:
+    def __init__(self, tracking_id: int, max_blocks: int) -> None:
+        self._tracking_id = tracking_id
+        self._seen_tokens = 0
+        self._in_flight_tokens = 0
+        self._blocks = torch.zeros(max_blocks, dtype=torch.int32)
+        self._n_blocks = 0
+
+    @property
+    def tracking_id(self) -> int:
+        return self._tracking_id
+
+    @property
+    def seen_tokens(self) -> int:
+        return self._seen_tokens
+
+    @property
+    def in_flight_tokens(self) -> int:
+        return self._in_flight_tokens
+
+    @property
+    def cur_allocated_blocks(self) -> int:
+        return self._n_blocks
+
+    @property
+    def max_context(self) -> int:
+        return self._blocks.numel()
+
+    def kv_blocks(self) -> torch.Tensor:
+        return self._blocks[: self._n_blocks]
+
+    def all_block_ids(self) -> torch.Tensor:
+        return self.kv_blocks()
+
+    def extend_kv_cache(self, new_ids: torch.Tensor) -> None:
+        n = new_ids.numel()
+        if self._n_blocks + n > self._blocks.numel():
+            raise ValueError("sequence exceeds the maximum number of KV blocks")
+        self._blocks[self._n_blocks: self._n_blocks + n] = new_ids
+        self._n_blocks += n
+
+    def pre_forward(self, num_tokens: int) -> None:
+        self._in_flight_tokens = num_tokens
+
+    def post_forward(self) -> None:
+        self._seen_tokens += self._in_flight_tokens
+        self._in_flight_tokens = 0

@@ -70,19 +70,45 @@ class FusedZ3Comm:
             fg.lp_shard = view.tensor
             fg._symm_shard = view
             off += fg.part
-        # ---- two rotating gradient arenas sized for the largest unit ----------------------------------
+        # ---- rotating gradient arenas sized for the largest unit ----------------------------------------
+        # Unit i writes its gradients into arena i % N and may only start once EVERY peer has finished reducing
+        # the arena's previous occupant (unit i - N).  With N = 2 that couples the compute streams of all ranks
+        # one unit apart (measured: 98 ms of exposed waiting per step at 8 GPUs); N = 4 leaves three units of slack.
         biggest = max(sum(fg.total for fg in u.groups) for u in optimizer.units)
-        self.grad_arenas = [symm.SymmBuffer(biggest, dtype, group) for _ in range(2)]
+        self.n_arenas = 4 if len(optimizer.units) > 4 else 2
+        self.grad_arenas = [symm.SymmBuffer(biggest, dtype, group) for _ in range(self.n_arenas)]
         self._slot = 0
+        self._shards_dirty = True        # a step rewrote shards since the last cross-rank barrier
+        import os
+        self.gather_mode = os.environ.get("SXB_Z3_GATHER", "ce")   # "ce" (copy engines) | "sm" (pull kernel)
         self.use_multicast = bool(self.grad_arenas[0].multicast_ptr)
         logger.info(f"[rank {self.rank}] ZeRO-3 fused collectives: shard arena {total_part * 2 / 2**20:.0f} MiB, "
-                    f"2 x {biggest * 2 / 2**20:.0f} MiB gradient arenas, NVLS multicast={self.use_multicast}")
+                    f"{self.n_arenas} x {biggest * 2 / 2**20:.0f} MiB gradient arenas, NVLS multicast={self.use_multicast}")
 
     # ----------------------------------------------------------------------------------- params
+    def shards_ready_barrier(self):
+        """ONE cross-rank barrier per optimizer step (on the current stream): after it, every peer's updated shards
+        are visible and stay unchanged until the next step, so all gathers of the step are barrier-free pulls.
+        (A peer rewrites its shard of unit u only after every rank finished the backward of u — the gradient
+        reduction of u cannot complete earlier — hence no gather of this step can still be reading it.)"""
+        if self._shards_dirty:
+            self.sg.barrier(self.shards)
+            self._shards_dirty = False
+
     def gather(self, fg):
         """Full flat buffer of ``fg`` from the peers' shards (kernel-driven, on the current stream)."""
         flat = fg.allocate_full()
-        self.sg.all_gather(fg._symm_shard, fg.part, flat, chunk_bytes=1 << 20, chunk_flags=None, max_ctas=48)
+        if self.gather_mode == "ce":
+            # copy-engine pull: world-1 peer-to-peer DMA copies + one local copy; leaves every SM to the GEMMs that
+            # run concurrently on the compute stream (the SM pull kernel below costs them issue slots and L2)
+            view = fg._symm_shard
+            for i in range(self.world):
+                r = (self.rank + 1 + i) % self.world          # start with the next rank: spreads load over links
+                src = self.shards.peer_tensor(r)[view.offset: view.offset + fg.part]
+                flat[r * fg.part: (r + 1) * fg.part].copy_(src, non_blocking=True)
+        else:
+            self.sg.all_gather(fg._symm_shard, fg.part, flat, chunk_bytes=1 << 20, chunk_flags=None, max_ctas=48,
+                               barrier=False)
         fg._bind_params()
 
     # ------------------------------------------------------------------------------------ grads
@@ -90,7 +116,7 @@ class FusedZ3Comm:
         """Give the unit a zeroed slice of the next gradient arena (after every peer finished reading
         that arena's previous occupant) and point the parameters' main-grad views into it."""
         arena = self.grad_arenas[self._slot]
-        self._slot ^= 1
+        self._slot = (self._slot + 1) % self.n_arenas
         self.sg.wait_readers(arena, symm.CH_GRADS_READ)
         off = 0
         for fg in unit.groups:
@@ -110,6 +136,7 @@ class FusedZ3Comm:
         if fuse_step and not accumulate:
             st = opt.optimizer.flat_state(fg.hp_param)
             st["step"] += 1
+            self._shards_dirty = True
             self.sg.rs_adam(view, fg.part, fg.hp_param.data, st["exp_avg"], st["exp_avg_sq"], fg.lp_shard,
                             fg.param_group, st["step"], adamw=bool(getattr(opt.optimizer, "adam_w_mode", 1)),
                             grad_scale=grad_scale, use_multicast=self.use_multicast)

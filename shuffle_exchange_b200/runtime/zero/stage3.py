@@ -278,6 +278,16 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
     def _gather_unit(self, u: Unit, async_on_side_stream: bool):
         if u.available or u.fetch_event is not None:
             return
+        if self.fused is not None and self.fused._shards_dirty:
+            # first gather after an optimizer step: wait for my own shard updates, then one cross-rank barrier
+            side = self.allgather_stream if self.allgather_stream is not None else get_accelerator().current_stream()
+            if self.reduce_stream is not None:
+                side.wait_stream(self.reduce_stream)
+            side.wait_stream(get_accelerator().current_stream())
+            with get_accelerator().stream(side):
+                self.fused.shards_ready_barrier()
+            if side is not get_accelerator().current_stream() and not async_on_side_stream:
+                get_accelerator().current_stream().wait_stream(side)
         if async_on_side_stream and self.allgather_stream is not None:
             self.allgather_stream.wait_stream(get_accelerator().current_stream())
             with get_accelerator().stream(self.allgather_stream):
@@ -373,7 +383,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             return
         u.attached = True
         if self.fused is not None:
-            ev = getattr(self, "_arena_free_events", [None, None])[self.fused._slot]
+            ev = getattr(self, "_arena_free_events", [None] * self.fused.n_arenas)[self.fused._slot]
             if ev is not None:
                 get_accelerator().current_stream().wait_event(ev)   # my own reduce of this arena's last occupant
             u._arena_slot = self.fused._slot
@@ -439,7 +449,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                 ev = get_accelerator().Event()
                 ev.record(stream if stream is not None else get_accelerator().current_stream())
             if not hasattr(self, "_arena_free_events"):
-                self._arena_free_events = [None, None]
+                self._arena_free_events = [None] * self.fused.n_arenas
             self._arena_free_events[u._arena_slot] = ev
             if stream is not None:
                 self._pending_reduce.append(u)
@@ -501,6 +511,8 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         self._finish_step()
 
     def _finish_step(self):
+        if self.fused is not None:
+            self.fused._shards_dirty = True
         for fg in self.groups:
             fg.micro_steps_accumulated = 0
             fg.grad_shard = None
