@@ -96,7 +96,7 @@ quantize_int_kernel(const T* __restrict__ in, uint8_t* __restrict__ q, float* __
   const T* src = in + g * group_size;
   const long long go = swizzle_group(g, groups, nodes, devs);
   float v[PASSES * 8];
-  float lo = INFINITY, hi = -INFINITY;
+  float lo = INFINITY, hi = -INFINITY, am = 0.f;   // threads without a slice contribute the identities
   SXB_FOR_SLICES(ps, base) {
     float t[8];
     load8<T>(src + base, t);
@@ -105,12 +105,13 @@ quantize_int_kernel(const T* __restrict__ in, uint8_t* __restrict__ q, float* __
       v[ps * 8 + i] = t[i];
       lo = fminf(lo, t[i]);
       hi = fmaxf(hi, t[i]);
+      am = fmaxf(am, fabsf(t[i]));
     }
   }
   constexpr int QMAX = (1 << (BITS - 1)) - 1;  // 127 / 7
   float scale, offset = 0.f;
   if (SYM) {
-    const float amax = block_max(fmaxf(fabsf(lo), fabsf(hi)), red);
+    const float amax = block_max(am, red);
     scale = amax > 0.f ? amax / QMAX : 1.f;
     if (threadIdx.x == 0) scales[go] = scale;
   } else {
@@ -208,15 +209,19 @@ quantized_reduction_kernel(const uint8_t* __restrict__ q_in, const float* __rest
       for (int i = 0; i < 8; ++i) acc[ps * 8 + i] += t[i];
     }
   }
-  float lo = INFINITY, hi = -INFINITY;
+  float lo = INFINITY, hi = -INFINITY, am = 0.f;
   SXB_FOR_SLICES(ps, base) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { lo = fminf(lo, acc[ps * 8 + i]); hi = fmaxf(hi, acc[ps * 8 + i]); }
+    for (int i = 0; i < 8; ++i) {
+      lo = fminf(lo, acc[ps * 8 + i]);
+      hi = fmaxf(hi, acc[ps * 8 + i]);
+      am = fmaxf(am, fabsf(acc[ps * 8 + i]));
+    }
   }
   constexpr int QMAX = (1 << (BITS - 1)) - 1;
   float scale, offset = 0.f;
   if (SYM) {
-    const float amax = block_max(fmaxf(fabsf(lo), fabsf(hi)), red);
+    const float amax = block_max(am, red);
     scale = amax > 0.f ? amax / QMAX : 1.f;
     if (threadIdx.x == 0) s_out[g] = scale;
   } else {

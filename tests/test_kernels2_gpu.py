@@ -39,9 +39,11 @@ def test_swizzle_and_quantized_reduction():
     qc, sc = quantize(x, 32, 4, True, nodes=2, devs=4)
     assert torch.allclose(sg.cpu(), sc, rtol=1e-5)
     rq, rs = quantized_reduction(qg, sg, 32, 8, 4, True, 4)
-    ref = dequantize(qc, sc, 32, 4, True, torch.float32).view(4, 8, 512).sum(0)
+    assert (qg.cpu() != qc).float().mean().item() < 5e-3                 # same swizzled layout, same codes (up to ties)
+    # reference built from the GPU's own first-hop codes so that only the reduce + requantise step is under test
+    ref = dequantize(qg, sg, 32, 4, True, torch.float32).cpu().view(4, 8, 512).sum(0)
     got = dequantize(rq, rs, 8, 4, True, torch.float32).cpu()
-    assert (got - ref).abs().max().item() <= 0.51 * rs.max().item() + 1e-5
+    assert ((got - ref).abs().amax(dim=1) <= 0.51 * rs.cpu() + 1e-5).all()
 
 
 @pytest.mark.parametrize("q_bits", [8, 6, 4, 12])
