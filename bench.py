@@ -145,7 +145,7 @@ def _with_nccl_collectives(args):
     return c
 
 
-def pick_checkpoint_layers(args, cfg, B, S, dev, world):
+def pick_checkpoint_layers(args, cfg, B, S, dev, world, extra_reserve=0):
     """Spend spare HBM on NOT recomputing: every layer left un-checkpointed keeps
     ``cfg.activation_bytes_per_layer`` bytes alive until its backward.  The reserve covers the transient peak of
     a fully checkpointed step (logits + loss grad, two gathered units, lazily allocated gradient arenas, one
@@ -158,7 +158,7 @@ def pick_checkpoint_layers(args, cfg, B, S, dev, world):
         return max(0, min(L, int(args.ckpt_layers)))
     total = torch.cuda.get_device_properties(dev).total_memory
     resident = torch.cuda.memory_allocated(dev)
-    reserve = 24 * 2 ** 30
+    reserve = 24 * 2 ** 30 + int(extra_reserve)
     per_layer = cfg.activation_bytes_per_layer(B, S)
     free_layers = int(max(0, total - resident - reserve) // per_layer)
     t = torch.tensor([free_layers], device=dev, dtype=torch.int64)
@@ -177,15 +177,42 @@ def run_ours(args):
     from shuffle_exchange_b200.models.llama import LlamaForCausalLM, llama_config
     from shuffle_exchange_b200.native import lib as nlib
 
-    cfg = llama_config(args.model, max_position_embeddings=max(args.seq, 8192))
-    if args.layers:
-        cfg.num_hidden_layers = args.layers
-    torch.manual_seed(1234)
-    model = LlamaForCausalLM(cfg, device=dev, dtype=torch.bfloat16)
-    engine, _, _, _ = sxb.initialize(model=model, config=ds_config(args, world), model_parameters=model.parameters())
+    is_moe = args.model.startswith("mixtral")
+    if is_moe:
+        # Second half of the headline metric: Mixtral with expert parallelism over all GPUs of the box
+        # (experts sharded 1/N per rank, ZeRO-2 for the dense part: the reference asserts MoE + ZeRO-3 unsupported,
+        # runtime/engine.py:1760).  The full 8x7B model needs >= 8 GPUs of 180 GB for training state.
+        from shuffle_exchange_b200.models.mixtral import MixtralForCausalLM, mixtral_config
+        cfg = mixtral_config(args.model, max_position_embeddings=max(args.seq, 8192), ep_size=world)
+        if args.layers:
+            cfg.num_hidden_layers = args.layers
+        per_rank = cfg.num_parameters() - cfg.num_hidden_layers * (cfg.num_local_experts - cfg.num_local_experts // world) * 3 * cfg.hidden_size * cfg.intermediate_size
+        need = per_rank * 4 + (per_rank - 1.7e9) * 12 + 1.7e9 * 12 / world
+        total = torch.cuda.get_device_properties(dev).total_memory
+        if need > 0.92 * total and not args.layers:
+            if rank == 0:
+                print(json.dumps({"impl": "ours", "metric": "tokens/sec/box Mixtral-8x7B EP", "n_gpus": world,
+                                  "unavailable": f"training state of {args.model} with EP={world} needs ~{need / 2**30:.0f} GiB "
+                                                 f"per GPU (> {total / 2**30:.0f} GiB); run with --gpus 8"}))
+            return
+        torch.manual_seed(1234)
+        model = MixtralForCausalLM(cfg, device=dev, dtype=torch.bfloat16)
+        conf = ds_config(args, world)
+        conf["zero_optimization"] = {"stage": 2, "overlap_comm": True, "contiguous_gradients": True,
+                                     "reduce_bucket_size": int(5e8)}
+    else:
+        cfg = llama_config(args.model, max_position_embeddings=max(args.seq, 8192))
+        if args.layers:
+            cfg.num_hidden_layers = args.layers
+        torch.manual_seed(1234)
+        model = LlamaForCausalLM(cfg, device=dev, dtype=torch.bfloat16)
+        conf = ds_config(args, world)
+    engine, _, _, _ = sxb.initialize(model=model, config=conf, model_parameters=model.parameters())
     engine.train()
     B, S = args.mbs, args.seq
-    cfg.checkpoint_layers = pick_checkpoint_layers(args, cfg, B, S, dev, world)
+    # ZeRO-2 keeps a full-size low-precision gradient buffer that is allocated lazily in the first backward
+    extra = sum(p.numel() for p in model.parameters()) * 2 if is_moe else 0
+    cfg.checkpoint_layers = pick_checkpoint_layers(args, cfg, B, S, dev, world, extra)
     g = torch.Generator().manual_seed(1000 + rank)
     n_batches = 4
     host = [torch.randint(0, cfg.vocab_size, (B, S), generator=g, dtype=torch.int64).pin_memory() for _ in range(n_batches)]
@@ -247,12 +274,14 @@ def run_ours(args):
     if rank == 0:
         flops = cfg.flops_per_token(S) * tokens_per_step / world
         out = {
-            "metric": "tokens/sec/box Llama-3-8B ZeRO-3", "value": value, "unit": "tokens/s", "n_gpus": world,
+            "metric": ("tokens/sec/box Mixtral-8x7B EP" if is_moe else "tokens/sec/box Llama-3-8B ZeRO-3"),
+            "value": value, "unit": "tokens/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
             "config": {"model": args.model + ("" if not args.layers else f"-DEBUG-{args.layers}-layers"),
-                       "global_batch": B * world, "seq_len": S, "parallelism": f"zero3-dp{world}",
-                       "collectives": ("nccl" if args.no_fused or world == 1 else "fused symmetric-memory kernels"),
+                       "global_batch": B * world, "seq_len": S, "parallelism": (f"ep{world}-zero2-dp{world}" if is_moe else f"zero3-dp{world}"),
+                       "collectives": ("nccl all-to-all of routed rows + ZeRO-2 gradient reduce" if is_moe else
+                                       "nccl" if args.no_fused or world == 1 else "fused symmetric-memory kernels"),
                        "activation_checkpointing": f"{cfg.checkpoint_layers} of {cfg.num_hidden_layers} layers recompute "
                                                    f"(--ckpt-layers {args.ckpt_layers})",
                        "optimizer": "AdamW fp32 master",

@@ -34,6 +34,15 @@ class MixtralConfig(LlamaConfig):
         per_layer = attn + self.num_local_experts * 3 * h * f + self.num_local_experts * h + 2 * h
         return self.num_hidden_layers * per_layer + 2 * v * h + h
 
+    def activation_bytes_per_layer(self, batch: int, seq_len: int, elem: int = 2) -> int:
+        """Dense part as in Llama (residuals, normed inputs, qkv, attention output) plus the routed rows: dispatched
+        copy, gate|up, SwiGLU product and expert output for ``k`` rows per token (worst case all on this rank's
+        experts under expert parallelism: tokens arrive from every rank, ~k*t rows on average)."""
+        t = batch * seq_len
+        h, f, k = self.hidden_size, self.intermediate_size, self.num_experts_per_tok
+        qkv = (self.num_attention_heads + 2 * self.num_key_value_heads) * self.head_dim
+        return t * elem * (5 * h + qkv) + t * k * elem * (3 * h + 3 * f) + t * 4 * (2 + self.num_attention_heads)
+
     def flops_per_token(self, seq_len: int, causal: bool = True) -> float:
         h, f, d = self.hidden_size, self.intermediate_size, self.head_dim
         attn_mm = h * (self.num_attention_heads + 2 * self.num_key_value_heads) * d + h * h

@@ -112,7 +112,8 @@ class DroplessMoE(MoE):
         shape = hidden_states.shape
         x = hidden_states.reshape(-1, shape[-1])
         T = x.shape[0]
-        logits = F.linear(x, self.wg)
+        # router: [T, H] x [E, H]^T with E << 128 — a plain library GEMM (cuBLAS); not worth a tensor-core tile
+        logits = torch.nn.functional.linear(x, self.wg)
         scores, assign, offsets, counts = moe_ops.top_k_gating(logits.detach(), self.k, renormalize=True)
         # the scores must carry gradient to the router: recompute them differentiably from the logits
         probs = torch.softmax(logits.float(), dim=-1)

@@ -43,6 +43,10 @@ def _torch_act(x, code):
 # ----------------------------------------------------------------------------- GEMM
 GEMM_NT, GEMM_NN, GEMM_TN = 0, 1, 2
 
+# Set by profiling.flops_profiler while a profile is running: callable(kind: str, flops: float).  The native ops
+# are invisible to torch's dispatcher, so they report their own work.
+flop_sink = None
+
 
 def gemm(a: torch.Tensor, b: torch.Tensor, layout: int = GEMM_NT, out: Optional[torch.Tensor] = None,
          accumulate: bool = False, alpha: float = 1.0, out_dtype: Optional[torch.dtype] = None,
@@ -63,6 +67,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, layout: int = GEMM_NT, out: Optional[
     if out is None:
         out = torch.empty((M, N), dtype=out_dtype or a.dtype, device=a.device)
         accumulate = False
+    if flop_sink is not None:
+        flop_sink("gemm", 2.0 * M * N * K)
     if not a.is_cuda:
         fa, fb = a.float(), b.float()
         r = fa @ fb.t() if layout == GEMM_NT else (fa @ fb if layout == GEMM_NN else fa.t() @ fb)
@@ -516,6 +522,8 @@ class _FlashAttn(torch.autograd.Function):
         Hk = k.shape[2]
         out = torch.empty((B, S, Hq, D), dtype=q.dtype, device=q.device)
         lse = torch.empty((B, Hq, S), dtype=torch.float32, device=q.device)
+        if flop_sink is not None:
+            flop_sink("attention", 4.0 * B * Hq * S * S * D * (0.5 if causal else 1.0))
         _n.call("sxb_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), lse.data_ptr(),
                 B, S, Hq, Hk, D, q.stride(1), k.stride(1), v.stride(1), out.stride(1), int(causal),
                 float(scale), _n.stream_ptr())
