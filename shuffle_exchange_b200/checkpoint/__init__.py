@@ -1,0 +1,5 @@
+from .deepspeed_checkpoint import DeepSpeedCheckpoint
+from .reshape_utils import get_files, get_files_with_prefix, get_zero_files, merge_state, partition_data
+from .universal_checkpoint import enable_universal_checkpoint, load_hp_checkpoint_state
+from .utils import (clone_tensors_for_torch_save, get_layer_ckpt_name_for_rank, get_model_ckpt_name_for_rank,
+                    get_zero_ckpt_name_for_rank)
