@@ -106,6 +106,8 @@ class DroplessMoE(MoE):
             if hi > lo:
                 pieces.append(self.experts[e](rows[lo:hi]))
             lo = hi
+        if len(pieces) == 1:
+            return pieces[0]                   # one local expert (EP = number of experts): no concatenation copy
         return torch.cat(pieces) if pieces else out
 
     def forward(self, hidden_states: torch.Tensor, used_token: Optional[torch.Tensor] = None):
