@@ -1,0 +1,4 @@
+from .base_file_writer import BaseFileWriter
+from .fast_file_writer import FastFileWriter, FastFileWriterConfig
+from .mock_file_writer import MockFileWriter
+from .py_file_writer import PyFileWriter

@@ -1,0 +1,84 @@
+"""Checkpointing decoupled from the training loop: ``save`` snapshots the state dict into host memory (pinned, async D2H)
+and returns; a background writer drains the queue to storage; ``commit`` of checkpoint *k* only waits for the snapshot,
+durability is awaited at the NEXT ``create``/``cleanup`` (reference:
+``runtime/checkpoint_engine/decoupled_checkpoint_engine.py:30-260``, which uses a separate process fed through a
+multiprocessing queue; a daemon thread suffices here because the writer spends its time in IO syscalls and native
+serialisation, both of which release the GIL)."""
+from __future__ import annotations
+
+import queue
+import threading
+
+import torch
+
+from ...utils.logging import log_dist, logger
+from .fast_checkpoint_engine import FastCheckpointEngine
+
+
+def _snapshot(obj):
+    """Deep copy with every tensor moved to (pinned) host memory."""
+    if torch.is_tensor(obj):
+        if obj.device.type == "cpu":
+            return obj.detach().clone()
+        host = torch.empty(obj.shape, dtype=obj.dtype, device="cpu", pin_memory=True)
+        host.copy_(obj.detach(), non_blocking=True)
+        return host
+    if isinstance(obj, dict):
+        return type(obj)((k, _snapshot(v)) for k, v in obj.items())
+    if isinstance(obj, (list, tuple)):
+        return type(obj)(_snapshot(v) for v in obj)
+    return obj
+
+
+class DecoupledCheckpointEngine(FastCheckpointEngine):
+    def __init__(self, config_params, dp_writer_config=None, optimize_dp_state=True):
+        super().__init__(config_params, dp_writer_config, optimize_dp_state)
+        self._q: "queue.Queue" = queue.Queue()
+        self._errors = []
+        self._thread = threading.Thread(target=self._drain, name="sxb-ckpt-writer", daemon=True)
+        self._thread.start()
+        self._pending_tag = None
+
+    def is_decoupled(self):
+        return True
+
+    def _drain(self):
+        while True:
+            item = self._q.get()
+            if item is None:
+                self._q.task_done()
+                return
+            state, path = item
+            try:
+                FastCheckpointEngine.save(self, state, path)
+            except Exception as e:  # pragma: no cover
+                self._errors.append(e)
+                logger.error(f"background checkpoint write of {path} failed: {e}")
+            finally:
+                self._q.task_done()
+
+    def create(self, info):
+        self._wait_durable()               # at most one checkpoint in flight
+        log_dist(f"[Decoupled] Checkpoint {info} is about to be saved!", ranks=[0])
+        self._pending_tag = info
+
+    def save(self, state_dict, path: str):
+        snap = _snapshot(state_dict)
+        if torch.cuda.is_available():
+            torch.cuda.current_stream().synchronize()       # D2H copies of the snapshot are complete
+        self._q.put((snap, path))
+
+    def commit(self, info):
+        log_dist(f"[Decoupled] Checkpoint {info} handed to the background writer", ranks=[0])
+        return True
+
+    def _wait_durable(self):
+        self._q.join()
+        if self._errors:
+            e = self._errors.pop()
+            raise RuntimeError(f"a background checkpoint write failed: {e}")
+
+    def cleanup(self):
+        self._wait_durable()
+        self._q.put(None)
+        self._thread.join(timeout=60)
