@@ -10,6 +10,7 @@ from __future__ import annotations
 
 import os
 import time
+import warnings
 from dataclasses import dataclass
 from typing import Optional
 
@@ -18,6 +19,8 @@ import torch
 from ..ops.aio import aio_handle
 from .base_file_writer import BaseFileWriter
 from .constants import *  # noqa: F401,F403
+
+warnings.filterwarnings("ignore", message="The given buffer is not writable")   # read-only views of torch.save's bytes
 
 FASTIO_STAT_KEYS = [AIO_WRITE_SEC_KEY, AIO_WRITE_BYTES_KEY, AIO_SPEED_KEY, SLOW_WRITE_BYTES_KEY, SLOW_WRITE_SEC_KEY,
                     AIO_FILL_BUFFER_COUNT_KEY, AIO_FILL_BUFFER_SEC_KEY, AIO_FILL_BUFFER_SPEED_KEY]
