@@ -1,0 +1,49 @@
+"""Column-parallel linear whose backward overlaps the input-gradient all-reduce with the weight-gradient GEMM
+(reference: ``runtime/domino/async_linear.py:18-93``).  The all-reduce handle is parked in ``handle_dic`` under the
+micro-batch key so that the Domino layer can wait for it as late as possible."""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from ... import comm as dist
+
+
+class DominoAsyncColumnParallelLinearImpl(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, inp, weight, bias, handle_dic, h_id, group):
+        ctx.save_for_backward(inp, weight)
+        ctx.use_bias = bias is not None
+        ctx.handle_dic, ctx.h_id, ctx.group = handle_dic, h_id, group
+        out = torch.matmul(inp, weight.t())
+        return out + bias if bias is not None else out
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        inp, weight = ctx.saved_tensors
+        grad_input = grad_output.matmul(weight)
+        handle = None
+        if ctx.group is not None and dist.is_initialized() and dist.get_world_size(group=ctx.group) > 1:
+            handle = dist.all_reduce(grad_input, group=ctx.group, async_op=True)
+            if ctx.handle_dic is not None:
+                ctx.handle_dic[ctx.h_id] = handle
+        g2 = grad_output.reshape(-1, grad_output.shape[-1])
+        grad_weight = g2.t().matmul(inp.reshape(-1, inp.shape[-1]))
+        grad_bias = g2.sum(dim=0) if ctx.use_bias else None
+        if handle is not None and ctx.handle_dic is None:
+            handle.wait()
+        return grad_input, grad_weight, grad_bias, None, None, None
+
+
+class DominoAsyncColumnParallelLinear(nn.Module):
+    def __init__(self, input_size, output_size, _tp_group, config=None, init_method=nn.init.xavier_normal_, bias=True):
+        super().__init__()
+        self.tp_group = _tp_group
+        tp = dist.get_world_size(group=_tp_group) if (_tp_group is not None and dist.is_initialized()) else 1
+        assert output_size % tp == 0
+        self.weight = nn.Parameter(torch.empty(output_size // tp, input_size))
+        init_method(self.weight)
+        self.bias = nn.Parameter(torch.zeros(output_size // tp)) if bias else None
+
+    def forward(self, inp, handle_dic=None, h_id=None):
+        return DominoAsyncColumnParallelLinearImpl.apply(inp, self.weight, self.bias, handle_dic, h_id, self.tp_group)

@@ -1,0 +1,123 @@
+"""Domino: tensor parallelism that hides its all-reduces by splitting every batch into two micro-batches and
+interleaving them — while micro-batch 0's row-parallel output is being all-reduced, micro-batch 1 computes
+(reference: ``runtime/domino/transformer.py:250-409``, https://arxiv.org/abs/2409.15241).
+
+``DominoTransformerLayer`` is a pre-LN decoder layer with column-parallel QKV / up projections and row-parallel
+output / down projections over ``tp_group``; collectives are issued asynchronously and waited for just before their
+result is needed.  On one rank (or without a group) it is an ordinary transformer layer.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as TF
+
+from ... import comm as dist
+from .async_linear import DominoAsyncColumnParallelLinear
+
+
+class DominoUtil:
+    """Shared dictionary of in-flight all-reduce handles keyed by a batch id."""
+    HANDLE_DIC = {"0": None, "1": None, "2": None, "3": None}
+
+
+def _tp(group):
+    return dist.get_world_size(group=group) if (group is not None and dist.is_initialized()) else 1
+
+
+class _AsyncReduce:
+    def __init__(self, t, group):
+        self.t = t
+        self.h = dist.all_reduce(t, group=group, async_op=True) if _tp(group) > 1 else None
+
+    def wait(self):
+        if self.h is not None:
+            self.h.wait()
+        return self.t
+
+
+class _RowParallel(torch.autograd.Function):
+    """y = x W^T summed over the group, asynchronously; backward is identity on the reduction."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        ctx.save_for_backward(x, weight)
+        return torch.matmul(x, weight.t())
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        g2 = g.reshape(-1, g.shape[-1])
+        return g.matmul(w), g2.t().matmul(x.reshape(-1, x.shape[-1]))
+
+
+class DominoTransformerLayer(nn.Module):
+    def __init__(self, hidden_size: int, num_heads: int, ffn_hidden_size: Optional[int] = None, tp_group=None,
+                 layernorm_epsilon: float = 1e-5, attention_dropout: float = 0.0, hidden_dropout: float = 0.0):
+        super().__init__()
+        self.tp_group = tp_group
+        tp = _tp(tp_group)
+        assert num_heads % tp == 0
+        self.h, self.heads_local, self.hd = hidden_size, num_heads // tp, hidden_size // num_heads
+        ffn = ffn_hidden_size or 4 * hidden_size
+        self.input_layernorm = nn.LayerNorm(hidden_size, eps=layernorm_epsilon)
+        self.post_attention_layernorm = nn.LayerNorm(hidden_size, eps=layernorm_epsilon)
+        self.query_key_value = DominoAsyncColumnParallelLinear(hidden_size, 3 * hidden_size, tp_group)
+        self.dense = nn.Parameter(torch.empty(hidden_size, hidden_size // tp))
+        self.dense_bias = nn.Parameter(torch.zeros(hidden_size))
+        self.dense_h_to_4h = DominoAsyncColumnParallelLinear(hidden_size, ffn, tp_group)
+        self.dense_4h_to_h = nn.Parameter(torch.empty(hidden_size, ffn // tp))
+        self.mlp_bias = nn.Parameter(torch.zeros(hidden_size))
+        nn.init.xavier_normal_(self.dense)
+        nn.init.xavier_normal_(self.dense_4h_to_h)
+        self.attn_p, self.hidden_p = attention_dropout, hidden_dropout
+
+    def _attn_partial(self, x, key):
+        B, S, _ = x.shape
+        qkv = self.query_key_value(x, DominoUtil.HANDLE_DIC, key).view(B, S, 3, self.heads_local, self.hd)
+        q, k, v = (t.transpose(1, 2) for t in qkv.unbind(dim=2))
+        ctx = TF.scaled_dot_product_attention(q, k, v, is_causal=True, dropout_p=self.attn_p if self.training else 0.0)
+        return _RowParallel.apply(ctx.transpose(1, 2).reshape(B, S, self.heads_local * self.hd), self.dense)
+
+    def _mlp_partial(self, x, key):
+        return _RowParallel.apply(TF.gelu(self.dense_h_to_4h(x, DominoUtil.HANDLE_DIC, key)), self.dense_4h_to_h)
+
+    def forward(self, hidden_states, attention_mask=None, rotary_pos_emb=None):
+        """``hidden_states`` [B, S, H]; the batch is cut into two halves that ping-pong between compute and
+        communication."""
+        B = hidden_states.shape[0]
+        halves = hidden_states.chunk(2, dim=0) if B >= 2 else (hidden_states,)
+        # ---- attention: issue half 0's reduce, compute half 1 meanwhile
+        parts = []
+        for i, h in enumerate(halves):
+            parts.append(_AsyncReduce(self._attn_partial(self.input_layernorm(h), str(i)), self.tp_group))
+        attn_out = []
+        for h, p in zip(halves, parts):
+            o = p.wait() + self.dense_bias
+            attn_out.append(h + TF.dropout(o, self.hidden_p, self.training))
+        # ---- MLP, same interleave
+        parts = []
+        for i, h in enumerate(attn_out):
+            parts.append(_AsyncReduce(self._mlp_partial(self.post_attention_layernorm(h), str(2 + i)), self.tp_group))
+        outs = []
+        for h, p in zip(attn_out, parts):
+            o = p.wait() + self.mlp_bias
+            outs.append(h + TF.dropout(o, self.hidden_p, self.training))
+        return torch.cat(outs, dim=0) if len(outs) > 1 else outs[0]
+
+
+class DominoTransformer(nn.Module):
+    def __init__(self, num_layers: int, hidden_size: int, num_heads: int, ffn_hidden_size: Optional[int] = None,
+                 tp_group=None, post_layer_norm: bool = True, **kw):
+        super().__init__()
+        self.layers = nn.ModuleList([DominoTransformerLayer(hidden_size, num_heads, ffn_hidden_size, tp_group, **kw)
+                                     for _ in range(num_layers)])
+        self.final_layernorm = nn.LayerNorm(hidden_size) if post_layer_norm else None
+
+    def forward(self, hidden_states, attention_mask=None, rotary_pos_emb=None):
+        for layer in self.layers:
+            hidden_states = layer(hidden_states, attention_mask, rotary_pos_emb)
+        return self.final_layernorm(hidden_states) if self.final_layernorm is not None else hidden_states
