@@ -1,0 +1,277 @@
+"""``InferenceEngine`` (v1): wrap a PyTorch model for tensor-parallel, low-precision inference.
+
+Reference: ``deepspeed/inference/engine.py:40-625``.  Kept: config handling, TP group creation (or adoption of an
+``mpu``), dtype conversion, AutoTP sharding (``replace_with_kernel_inject`` selects the fused path, which in this
+framework is the ragged v2 engine — see ``inference/v2``), sharded checkpoint loading, optional CUDA-graph capture of
+the forward, ``forward`` / ``generate`` delegation, model-time profiling.
+"""
+from __future__ import annotations
+
+import os
+import time
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from .. import comm as dist
+from ..utils.logging import log_dist, logger
+from .config import DeepSpeedInferenceConfig
+
+INFERENCE_MODEL_TIMER = "model-forward-inference"
+
+
+class InferenceEngine(nn.Module):
+    inference_mp_group = None
+    inference_ep_group = None
+    expert_mp_group = None
+
+    def __init__(self, model, config: DeepSpeedInferenceConfig):
+        super().__init__()
+        self.module = model
+        self._config = config
+        self._get_model_config_generate(config)
+        if hasattr(self.module, "generate"):
+            self.generate = self._generate
+        if hasattr(self.module, "config"):
+            self.config = self.module.config
+        self.injection_dict = config.injection_policy
+        self.mp_group = config.tensor_parallel.tp_group
+        self.mpu = config.tensor_parallel.mpu
+        self.quantize_merge_count = 1
+        self.quantization_scales = None
+        self.ep_group = None
+        self.expert_mp_group = None
+        self.cuda_graph_created = False
+        self.checkpoint_engine = None
+        self._model_times = []
+        self.model_profile_enabled = False
+        self.use_cuda_events = torch.cuda.is_available()
+        self._cuda_graphs = None
+        self.local_cuda_graph = False
+        if config.enable_cuda_graph and not torch.cuda.is_available():
+            raise ValueError("enable_cuda_graph needs a CUDA device")
+        if config.tensor_parallel.tp_size > 1:
+            self._create_model_parallel_group(config)
+            config.tensor_parallel.tp_group = self.mp_group
+        if isinstance(self.module, nn.Module):
+            moe, _ = self._has_moe()
+            if moe and dist.is_initialized() and dist.get_world_size() > 1:
+                self._create_ep_parallel_group(config.moe.moe_experts if hasattr(config.moe, "moe_experts") else [1])
+        self._convert_dtype(config)
+        if config.tensor_parallel.tp_size > 1:
+            self._apply_injection_policy(config)
+        if config.checkpoint is not None:
+            self._load_checkpoint(config.checkpoint)
+        dev = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+        if not config.keep_module_on_host:
+            self.module.to(dev)
+        if config.tensor_parallel.tp_size > 1:
+            # identical sampling across the TP group
+            seed = torch.tensor([torch.initial_seed() % (2 ** 31)], dtype=torch.int64, device=dev)
+            dist.broadcast(seed, src=dist.get_global_rank(self.mp_group, 0) if self.mp_group is not None else 0,
+                           group=self.mp_group)
+            torch.manual_seed(int(seed.item()))
+        self.module.eval()
+
+    # ------------------------------------------------------------------------------ profiling
+    def profile_model_time(self, use_cuda_events=True):
+        if not self.model_profile_enabled and not self._config.enable_cuda_graph:
+            self.module.register_forward_pre_hook(self._pre_forward_hook)
+            self.module.register_forward_hook(self._post_forward_hook)
+        self.model_profile_enabled = True
+        self.use_cuda_events = use_cuda_events and torch.cuda.is_available()
+        if self.use_cuda_events:
+            self._t0, self._t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def _pre_forward_hook(self, module, *inputs, **kwargs):
+        if self.use_cuda_events:
+            self._t0.record()
+        else:
+            self._start = time.time()
+
+    def _post_forward_hook(self, module, input, output):
+        if self.use_cuda_events:
+            self._t1.record()
+            torch.cuda.synchronize()
+            self._model_times.append(self._t0.elapsed_time(self._t1))
+        else:
+            self._model_times.append((time.time() - self._start) * 1e3)
+
+    def model_times(self):
+        assert self.model_profile_enabled, "model profiling is not enabled"
+        times, self._model_times = self._model_times, []
+        if self._config.enable_cuda_graph and not times:
+            raise ValueError("Model times are empty and cuda graph is enabled. If this is a GPT-style model this combo is not supported.")
+        return times
+
+    # ---------------------------------------------------------------------------------- groups
+    def _get_model_config_generate(self, config):
+        self.config = getattr(self.module, "config", None) if config.config is None else config.config
+
+    def _create_model_parallel_group(self, config):
+        if InferenceEngine.inference_mp_group is None:
+            if not dist.is_initialized():
+                dist.init_distributed()
+            local_rank = int(os.getenv("LOCAL_RANK", "0"))
+            if torch.cuda.is_available():
+                torch.cuda.set_device(local_rank)
+            if config.tensor_parallel.mpu is not None:
+                mpu = config.tensor_parallel.mpu
+                self.mp_group = mpu.get_model_parallel_group() if hasattr(mpu, "get_model_parallel_group") else mpu.get_tensor_model_parallel_group()
+            else:
+                tp, world, rank = config.tensor_parallel.tp_size, dist.get_world_size(), dist.get_rank()
+                assert world % tp == 0, f"world size {world} is not divisible by tp_size {tp}"
+                for start in range(0, world, tp):
+                    g = dist.new_group(list(range(start, start + tp)))
+                    if start <= rank < start + tp:
+                        self.mp_group = g
+            InferenceEngine.inference_mp_group = self.mp_group
+        else:
+            self.mp_group = InferenceEngine.inference_mp_group
+
+    def _create_ep_parallel_group(self, moe_experts):
+        self.ep_group, self.expert_mp_group = {}, {}
+        world, rank = dist.get_world_size(), dist.get_rank()
+        moe_experts = moe_experts if isinstance(moe_experts, list) else [moe_experts]
+        for e in moe_experts:
+            size = min(e, world)
+            for start in range(0, world, size):
+                g = dist.new_group(list(range(start, start + size)))
+                if start <= rank < start + size:
+                    self.ep_group[e] = g
+            self.expert_mp_group[e] = None
+
+    def _has_moe(self):
+        from ..moe.layer import MoE
+        n = [m.num_experts for m in self.module.modules() if isinstance(m, MoE)]
+        return bool(n), n
+
+    # ------------------------------------------------------------------------ dtype / injection
+    def _convert_dtype(self, config):
+        if not isinstance(self.module, nn.Module):
+            return
+        if config.dtype == torch.float16:
+            self.module.half()
+        elif config.dtype == torch.bfloat16:
+            self.module.bfloat16()
+        elif config.dtype == torch.float32:
+            self.module.float()
+
+    def _apply_injection_policy(self, config, client_module=None):
+        from ..module_inject import replace_transformer_layer
+        checkpoint = None
+        if isinstance(self.module, nn.Module):
+            if config.injection_policy:
+                for cls, names in config.injection_policy.items():
+                    config.injection_policy_tuple = tuple(names) if isinstance(names, (list, tuple)) else (names,)
+                    replace_transformer_layer(cls, self.module, checkpoint, config, self.config)
+            else:
+                replace_transformer_layer(None, self.module, checkpoint, config, self.config)
+
+    # ------------------------------------------------------------------------------ checkpoints
+    def _load_checkpoint(self, load_dir, load_module_strict=True, tag=None):
+        """``load_dir``: a folder with ``*.pt`` / ``*.bin`` / safetensors shards, or a JSON descriptor
+        ``{"type": ..., "checkpoints": [...], "version": ...}`` (reference :433-506)."""
+        import glob
+        import json
+        files = []
+        if isinstance(load_dir, dict):
+            files = load_dir.get("checkpoints", [])
+            base = load_dir.get("base_dir", self._config.base_dir)
+            files = [os.path.join(base, f) for f in files]
+        elif os.path.isfile(load_dir) and load_dir.endswith(".json"):
+            with open(load_dir) as f:
+                d = json.load(f)
+            base = d.get("base_dir", os.path.dirname(load_dir))
+            files = [os.path.join(base, f) for f in d["checkpoints"]]
+        else:
+            for pat in ("*.safetensors", "pytorch_model*.bin", "*.pt"):
+                files = sorted(glob.glob(os.path.join(load_dir, pat)))
+                if files:
+                    break
+        sd = {}
+        for f in files:
+            if f.endswith(".safetensors"):
+                from safetensors.torch import load_file
+                sd.update(load_file(f))
+            else:
+                part = torch.load(f, map_location="cpu", weights_only=False)
+                sd.update(part.get("module", part.get("model", part)) if isinstance(part, dict) else part)
+        if not sd:
+            raise ValueError(f"no checkpoint files found for {load_dir}")
+        own = self.module.state_dict()
+        tp_rank = dist.get_rank(group=self.mp_group) if self.mp_group is not None else 0
+        tp = self._config.tensor_parallel.tp_size
+        fixed = {}
+        for k, v in sd.items():
+            if k not in own:
+                continue
+            tgt = own[k]
+            if v.shape == tgt.shape:
+                fixed[k] = v
+                continue
+            for dim in range(v.dim()):          # full tensor -> this rank's TP slice
+                if v.shape[dim] == tgt.shape[dim] * tp:
+                    fixed[k] = v.chunk(tp, dim=dim)[tp_rank]
+                    break
+        missing = self.module.load_state_dict(fixed, strict=False)
+        if load_module_strict and missing.missing_keys:
+            logger.warning(f"checkpoint is missing {len(missing.missing_keys)} keys, e.g. {missing.missing_keys[:3]}")
+
+    # ------------------------------------------------------------------------------ CUDA graphs
+    def _create_cuda_graph(self, *inputs, **kwargs):
+        stream = torch.cuda.Stream()
+        stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                self.module(*inputs, **kwargs)
+        torch.cuda.current_stream().wait_stream(stream)
+        self._cuda_graphs = torch.cuda.CUDAGraph()
+        self.static_inputs, self.static_kwargs = inputs, kwargs
+        with torch.cuda.graph(self._cuda_graphs):
+            self.static_output = self.module(*self.static_inputs, **self.static_kwargs)
+        self.cuda_graph_created = True
+
+    def _graph_replay(self, *inputs, **kwargs):
+        for i, t in enumerate(inputs):
+            if torch.is_tensor(t):
+                self.static_inputs[i].copy_(t)
+        for k, t in kwargs.items():
+            if torch.is_tensor(t):
+                self.static_kwargs[k].copy_(t)
+        self._cuda_graphs.replay()
+        return self.static_output
+
+    # ------------------------------------------------------------------------------------ calls
+    def forward(self, *inputs, **kwargs):
+        start = None
+        if self.model_profile_enabled and self._config.enable_cuda_graph:
+            torch.cuda.synchronize()
+            start = time.time()
+        if self._config.enable_cuda_graph and not self.local_cuda_graph:
+            if self.cuda_graph_created:
+                outputs = self._graph_replay(*inputs, **kwargs)
+            else:
+                self._create_cuda_graph(*inputs, **kwargs)
+                outputs = self._graph_replay(*inputs, **kwargs)
+        else:
+            outputs = self.module(*inputs, **kwargs)
+        if start is not None:
+            torch.cuda.synchronize()
+            self._model_times.append((time.time() - start) * 1e3)
+        return outputs
+
+    def _generate(self, *inputs, **kwargs):
+        num_beams = kwargs.get("num_beams", 1)
+        if "generation_config" in kwargs:
+            num_beams = getattr(kwargs["generation_config"], "num_beams", num_beams)
+        if num_beams > 1:
+            raise NotImplementedError("DeepSpeed does not support `num_beams` > 1, if this is important to you please "
+                                      "add your request to: https://github.com/deepspeedai/DeepSpeed/issues/2506")
+        if "input_ids" in kwargs and self._config.max_out_tokens:
+            n = kwargs["input_ids"].shape[-1]
+            if n > self._config.max_out_tokens:
+                raise RuntimeError(f"Input with size {n} exceeds maximum length of {self._config.max_out_tokens}. "
+                                   "Please increase `max_tokens` in the DeepSpeed Inference Config.")
+        return self.module.generate(*inputs, **kwargs)
