@@ -1,0 +1,60 @@
+"""Validated view of the ``elasticity`` block (reference: ``deepspeed/elasticity/config.py:10-110``)."""
+import json
+
+from .constants import *  # noqa: F401,F403
+
+
+class ElasticityError(Exception):
+    """Base exception of the elasticity module."""
+
+
+class ElasticityConfigError(ElasticityError):
+    """The elasticity configuration is missing, disabled or inconsistent."""
+
+
+class ElasticityIncompatibleWorldSize(ElasticityError):
+    """The current world size is not among the GPU counts the elastic batch size supports."""
+
+
+class ElasticityConfig:
+    def __init__(self, param_dict):
+        self.enabled = param_dict.get(ENABLED, ENABLED_DEFAULT)
+        if self.enabled:
+            for key in (MAX_ACCEPTABLE_BATCH_SIZE, MICRO_BATCHES):
+                if key not in param_dict:
+                    raise ElasticityConfigError(f"Elasticity config missing {key}")
+        self.max_acceptable_batch_size = param_dict.get(MAX_ACCEPTABLE_BATCH_SIZE, MAX_ACCEPTABLE_BATCH_SIZE_DEFAULT)
+        self.micro_batches = param_dict.get(MICRO_BATCHES, MICRO_BATCHES_DEFAULT)
+        if not isinstance(self.micro_batches, list):
+            raise ElasticityConfigError(f"Elasticity expected value of {MICRO_BATCHES} to be a list of micro batches, "
+                                        f"instead is: {type(self.micro_batches)}, containing: {self.micro_batches}")
+        if not all(isinstance(m, int) for m in self.micro_batches):
+            raise ElasticityConfigError(f"Elasticity expected {MICRO_BATCHES} to only contain a list of integers, "
+                                        f"instead contains: f{self.micro_batches}")
+        if not all(m > 0 for m in self.micro_batches):
+            raise ElasticityConfigError(f"Elasticity expected {MICRO_BATCHES} to only contain positive integers, "
+                                        f"instead contains: f{self.micro_batches}")
+        self.min_gpus = param_dict.get(MIN_GPUS, MIN_GPUS_DEFAULT)
+        self.max_gpus = param_dict.get(MAX_GPUS, MAX_GPUS_DEFAULT)
+        if self.min_gpus < 1 or self.max_gpus < 1:
+            raise ElasticityConfigError(f"Elasticity min/max gpus must be > 0, given min_gpus: {self.min_gpus}, max_gpus: {self.max_gpus}")
+        if self.max_gpus < self.min_gpus:
+            raise ElasticityConfigError(f"Elasticity min_gpus cannot be greater than max_gpus, given min_gpus: {self.min_gpus}, max_gpus: {self.max_gpus}")
+        self.model_parallel_size = param_dict.get(MODEL_PARALLEL_SIZE, MODEL_PARALLEL_SIZE_DEFAULT)
+        if self.model_parallel_size < 1:
+            raise ElasticityConfigError(f"Model-Parallel size cannot be less than 1, given model-parallel size: {self.model_parallel_size}")
+        self.num_gpus_per_node = param_dict.get(NUM_GPUS_PER_NODE, NUM_GPUS_PER_NODE_DEFAULT)
+        if self.num_gpus_per_node < 1:
+            raise ElasticityConfigError(f"Number of GPUs per node cannot be less than 1, given number of GPUs per node: {self.num_gpus_per_node}")
+        self.min_time = param_dict.get(MIN_TIME, MIN_TIME_DEFAULT)
+        if self.min_time < 0:
+            raise ElasticityConfigError(f"Elasticity min time needs to be >= 0: given {self.min_time}")
+        self.version = param_dict.get(VERSION, VERSION_DEFAULT)
+        self.prefer_larger_batch_size = param_dict.get(PREFER_LARGER_BATCH, PREFER_LARGER_BATCH_DEFAULT)
+        self.ignore_non_elastic_batch_info = param_dict.get(IGNORE_NON_ELASTIC_BATCH_INFO, IGNORE_NON_ELASTIC_BATCH_INFO_DEFAULT)
+
+    def repr(self):
+        return self.__dict__
+
+    def __repr__(self):
+        return json.dumps(self.__dict__, sort_keys=True, indent=4)
