@@ -1,0 +1,3 @@
+from .compress import init_compression, redundancy_clean, student_initialization
+from .helper import convert_conv1d_to_linear
+from .scheduler import compression_scheduler
