@@ -1,0 +1,2 @@
+from .autotuner import Autotuner
+from .config import DeepSpeedAutotuningConfig
