@@ -28,6 +28,7 @@ constexpr float kLn2 = 0.6931471805599453f;
 struct Params {
   int B, S, Hq, Hk, D;
   int causal;
+  int debug;            // profiling aid (env SXB_ATTN_DEBUG): 1 = row warps skip the exp/dS math, 2 = also skip LDTM
   float scale;          // softmax scale (1/sqrt(D))
   void* out;            // fwd: O [B,S,Hq,D] ; dq: dQ ; dkv: dK
   void* out2;           // dkv: dV
@@ -649,7 +650,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       for (int i = 0; i < NS; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
       mbar_init(&s_full[0], 1);
       mbar_init(&s_full[1], 1);
-      mbar_init(pt_full, 256);
+      mbar_init(pt_full, 8);       // one arrival per row warp
       mbar_init(acc_done, 1);
       mbar_init(&s_free[0], 8);
       mbar_init(&s_free[1], 8);
@@ -723,18 +724,25 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     if (niter > 0 && !issue_first(0)) goto done;
     for (int it = 0; it < niter; ++it) {
       const int st = it % NS;
+      // S^T/dP^T(it+1) overwrite the TMEM buffer that held P^T/dS^T(it-1): safe without a barrier because the
+      // dV/dK MMAs that read them were issued earlier by this same thread and the tensor pipe runs in order.
       if (it + 1 < niter && !issue_first(it + 1)) goto done;
       if (!__all_sync(0xffffffffu, mbar_wait_to(pt_full, it & 1, 37, it))) goto done;
       tc_fence_after();
       const uint32_t sQ = sbase + L::oQ + st * L::kQ;
       const uint32_t sDO = sbase + L::oDO + st * L::kQ;
+      // P^T (bf16, packed 2 per column) lives in the first 16 columns of each half of the S^T buffer, dS^T
+      // likewise inside the dP^T buffer: k-step kk (16 queries) = 8 columns.
+      const uint32_t tPT = tm_u + (it & 1) * 128, tDST = tPT + 64;
       if (elected) {
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
-          umma_f16(tDV_u, desc_kmajor_1(sPT, kk), desc_mnmajor(sDO, BC, kk), idesc_acc, (it | kk) != 0);
+          umma_f16_ts(tDV_u, tPT + (kk >> 1) * 32 + (kk & 1) * 8, desc_mnmajor(sDO, BC, kk), idesc_acc,
+                      (it | kk) != 0);
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
-          umma_f16(tDK_u, desc_kmajor_1(sDST, kk), desc_mnmajor(sQ, BC, kk), idesc_acc, (it | kk) != 0);
+          umma_f16_ts(tDK_u, tDST + (kk >> 1) * 32 + (kk & 1) * 8, desc_mnmajor(sQ, BC, kk), idesc_acc,
+                      (it | kk) != 0);
         umma_commit(&q_empty[st]);
         umma_commit(acc_done);
       }
@@ -771,11 +779,18 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       tc_fence_after();
       float s[32], dp[32];
       const uint32_t tST = tmem + (it & 1) * 128 + lane_off + half * 32;
-      ld_row32x2(tST, tST + 64, s, dp);
+      if (p.debug < 2) {
+        ld_row32x2(tST, tST + 64, s, dp);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) { s[c] = 0.f; dp[c] = 0.f; }
+      }
       const float* lse2 = stat + st * 128 + half * 32;
       const float* dlt = lse2 + 64;
       const bool need_mask = (p.causal && (n0 + BQ - 1 > qb)) || (qb + 32 > p.S) || (n0 + BQ > p.S);
-      if (need_mask) {
+      if (p.debug >= 1) {
+        // math skipped
+      } else if (need_mask) {
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
           const int qp = qb + c;
@@ -792,12 +807,22 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           dp[c] = pr * (dp[c] - dlt[c]) * p.scale;
         }
       }
-      if (it > 0) if (!mbar_wait_to(acc_done, (it - 1) & 1, 39, it)) goto done;
-      store_half_sw128(sPT, row, half, s);
-      store_half_sw128(sDST, row, half, dp);
-      fence_async_smem();
+      {
+        // bf16-pack this thread's 32 values of P^T and of dS^T and park them in TMEM, over the first half of the
+        // very columns they were computed from (own lanes, own column range: no cross-warp hazard)
+        uint32_t pk[16], dk[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          pk[c] = pack_bf16(s[2 * c], s[2 * c + 1]);
+          dk[c] = pack_bf16(dp[2 * c], dp[2 * c + 1]);
+        }
+        tmem_st_32x16(tST, pk);
+        tmem_st_32x16(tST + 64, dk);
+        tmem_st_wait();
+      }
       tc_fence_before();
-      mbar_arrive(pt_full);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pt_full);
     }
     if (niter > 0) {
       if (!mbar_wait_to(acc_done, (niter - 1) & 1, 40)) goto done;
@@ -953,6 +978,11 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
   Params p{};
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.lse = (float*)const_cast<void*>(lse); p.delta = (const float*)delta;
+  {
+    static int dbg = -1;
+    if (dbg < 0) { const char* e = getenv("SXB_ATTN_DEBUG"); dbg = e ? atoi(e) : 0; }
+    p.debug = dbg;
+  }
   // ---- dQ
   {
     CUtensorMap tq, tk, tv, tdo;
