@@ -142,8 +142,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qt = gridDim.x - 1 - blockIdx.x;  // heavy (late) causal tiles first
-  const int h = blockIdx.y, b = blockIdx.z;
+  // tile index is the SLOWEST grid dimension: CTAs are handed out in linear block order, so every (head, batch)
+  // of the heaviest causal tile starts before any lighter tile (longest-first packing over the 148 SMs)
+  const int qt = gridDim.z - 1 - blockIdx.z;
+  const int h = blockIdx.x, b = blockIdx.y;
   const int hk = h / (p.Hq / p.Hk);
   const int q0 = qt * BQ;
   const int kv_len = p.causal ? min(p.S, q0 + BQ) : p.S;
@@ -421,8 +423,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qt = gridDim.x - 1 - blockIdx.x;
-  const int h = blockIdx.y, b = blockIdx.z;
+  const int qt = gridDim.z - 1 - blockIdx.z;   // heaviest causal tiles first across all heads
+  const int h = blockIdx.x, b = blockIdx.y;
   const int hk = h / (p.Hq / p.Hk);
   const int q0 = qt * BQ;
   const int kv_len = p.causal ? min(p.S, q0 + BQ) : p.S;
@@ -635,8 +637,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int kt = blockIdx.x;
-  const int hk = blockIdx.y, b = blockIdx.z;
+  const int kt = blockIdx.z;                   // key tile 0 sees every query block: heaviest first
+  const int hk = blockIdx.x, b = blockIdx.y;
   const int group = p.Hq / p.Hk;
   const int n0 = kt * BQ;
   const int nq_blocks = (p.S + BC - 1) / BC;
@@ -942,7 +944,7 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
   Params p{};
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
-  dim3 grid((S + BQ - 1) / BQ, Hq, B);
+  dim3 grid(Hq, B, (S + BQ - 1) / BQ);
   cudaStream_t s = (cudaStream_t)stream;
   if (D == 128) {
     if ((rc = set_smem(attn_fwd_kernel<128>, FwdSmem<128>::kTotal))) return rc;
@@ -991,7 +993,7 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     if ((rc = make_qkv_map(&tk, k, B, S, Hk, D, k_stride, BC))) return rc;
     if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BC))) return rc;
     p.out = dq; p.out_stride = dq_stride;
-    dim3 grid((S + BQ - 1) / BQ, Hq, B);
+    dim3 grid(Hq, B, (S + BQ - 1) / BQ);
     if (D == 128) {
       if ((rc = set_smem(attn_bwd_dq_kernel<128>, DqSmem<128>::kTotal))) return rc;
       attn_bwd_dq_kernel<128><<<grid, kBwdThreads, DqSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
@@ -1009,7 +1011,7 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     if ((rc = make_qkv_map(&tk, k, B, S, Hk, D, k_stride, BQ))) return rc;
     if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BQ))) return rc;
     p.out = dk; p.out_stride = dk_stride; p.out2 = dv; p.out2_stride = dv_stride;
-    dim3 grid((S + BQ - 1) / BQ, Hk, B);
+    dim3 grid(Hk, B, (S + BQ - 1) / BQ);
     if (D == 128) {
       if ((rc = set_smem(attn_bwd_dkv_kernel<128>, DkvSmem<128>::kTotal))) return rc;
       attn_bwd_dkv_kernel<128><<<grid, kBwdThreads, DkvSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
