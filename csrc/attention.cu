@@ -78,6 +78,12 @@ __device__ __forceinline__ void ld_row32x2(uint32_t taddr_a, uint32_t taddr_b, f
   }
 }
 
+__device__ __forceinline__ float4 lds128(uint32_t saddr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+  return v;
+}
+
 __device__ __forceinline__ void ld_row64(uint32_t taddr, float (&v)[64]) {
   uint32_t a[32], b[32];
   tmem_ld_32x32(taddr, a);
@@ -120,7 +126,10 @@ struct FwdSmem {
   static constexpr int kTotal = oBar + 128 + 1024;
 };
 
-template <int D>
+// MC = 2: launched as 2-CTA clusters over adjacent q heads of one GQA group.  Both CTAs walk the same K/V blocks, so
+// each loads one 64-wide half of every K/V tile and multicasts it into both CTAs' rings: L2 -> SM traffic (the
+// measured limiter of this kernel: 5.4 TB/s of the ~6.9 TB/s L2 can deliver) is halved.
+template <int D, int MC>
 __global__ void __launch_bounds__(kThreads, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const Params p) {
@@ -158,8 +167,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (lane == 0) {
       mbar_init(q_full, 1);
       for (int i = 0; i < 2; ++i) {
-        mbar_init(&k_full[i], 1); mbar_init(&v_full[i], 1); mbar_init(&k_empty[i], 1);
-        mbar_init(&v_empty[i], 1); mbar_init(&s_full[i], 1);
+        mbar_init(&k_full[i], 1); mbar_init(&v_full[i], 1); mbar_init(&k_empty[i], MC);
+        mbar_init(&v_empty[i], MC); mbar_init(&s_full[i], 1);
       }
       mbar_init(p_full, 128);
       mbar_init(o_done, 1);
@@ -171,8 +180,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     tmem_alloc(tmem_slot, 256);
   }
   tc_fence_before();
-  __syncthreads();
+  if (MC > 1) cluster_sync_all();   // peer barriers exist before any multicast byte or remote arrive lands
+  else __syncthreads();
   tc_fence_after();
+  const uint32_t crank = (MC > 1) ? cluster_ctarank() : 0;
   const uint32_t tmem = *tmem_slot;
   const uint32_t tS = tmem;          // 2 x 64 columns
   const uint32_t tO = tmem + 128;    // D columns
@@ -200,9 +211,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int st = jk & 1;
         if (elected) {
           mbar_expect_tx(&k_full[st], L::kKV);
-          for (int hh = 0; hh < NH; ++hh)
-            tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &k_full[st], hh * 64, hk,
-                        jk * BC, b);
+          if (MC > 1) {
+            tma_load_4d_mc(smem + L::oK + st * L::kKV + crank * (BC * 128), &tmK, &k_full[st], crank * 64, hk,
+                           jk * BC, b, 3);
+          } else {
+            for (int hh = 0; hh < NH; ++hh)
+              tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &k_full[st], hh * 64, hk,
+                          jk * BC, b);
+          }
         }
         __syncwarp();
         ++jk;
@@ -214,9 +230,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int st = jv & 1;
         if (elected) {
           mbar_expect_tx(&v_full[st], L::kKV);
-          for (int hh = 0; hh < NH; ++hh)
-            tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &v_full[st], hh * 64, hk,
-                        jv * BC, b);
+          if (MC > 1) {
+            tma_load_4d_mc(smem + L::oV + st * L::kKV + crank * (BC * 128), &tmV, &v_full[st], crank * 64, hk,
+                           jv * BC, b, 3);
+          } else {
+            for (int hh = 0; hh < NH; ++hh)
+              tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &v_full[st], hh * 64, hk,
+                          jv * BC, b);
+          }
         }
         __syncwarp();
         ++jv;
@@ -248,7 +269,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           umma_f16(tS_u + (j & 1) * BC, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, BC, kk),
                    idesc_s, kk != 0);
         umma_commit(&s_full[j & 1]);
-        umma_commit(&k_empty[st]);
+        if (MC > 1) umma_commit_mc(&k_empty[st], 3);
+        else umma_commit(&k_empty[st]);
       }
       __syncwarp();
       return true;
@@ -269,7 +291,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
           umma_f16(tO_u, desc_kmajor_1(sP, kk), desc_mnmajor(sV, BC, kk), idesc_o, (j | kk) != 0);
-        umma_commit(&v_empty[st]);
+        if (MC > 1) umma_commit_mc(&v_empty[st], 3);
+        else umma_commit(&v_empty[st]);
         umma_commit(o_done);
       }
       __syncwarp();
@@ -375,7 +398,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   }
 done:
   tc_fence_before();
-  __syncthreads();
+  if (MC > 1) cluster_sync_all();   // neither CTA leaves while the peer can still write its ring or barriers
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem, 256);
@@ -401,7 +425,7 @@ struct DqSmem {
   static constexpr int kTotal = oBar + 128 + 1024;
 };
 
-template <int D>
+template <int D, int MC>   // MC = 2: K/V ring filled by multicast from a 2-CTA cluster over a q-head pair (see forward)
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
@@ -433,7 +457,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   if (warp == 1) {
     if (lane == 0) {
       mbar_init(q_full, 1);
-      for (int i = 0; i < NS; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1); }
+      for (int i = 0; i < NS; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], MC); }
       mbar_init(&s_full[0], 1);
       mbar_init(&s_full[1], 1);
       mbar_init(ds_full, 256);
@@ -446,8 +470,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     tmem_alloc(tmem_slot, 512);
   }
   tc_fence_before();
-  __syncthreads();
+  if (MC > 1) cluster_sync_all();
+  else __syncthreads();
   tc_fence_after();
+  const uint32_t crank = (MC > 1) ? cluster_ctarank() : 0;
   const uint32_t tmem = *tmem_slot;
   // buffer b: S at 128*b, dP at 128*b + 64 ; dQ at 256
   const uint32_t tDQ = tmem + 256;
@@ -467,11 +493,18 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       if (!__all_sync(0xffffffffu, mbar_wait_to(&kv_empty[st], ((j / NS) & 1) ^ 1, 27, j))) goto done;
       if (elected) {
         mbar_expect_tx(&kv_full[st], 2 * L::kKV);
-        for (int hh = 0; hh < NH; ++hh) {
-          tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &kv_full[st], hh * 64, hk,
-                      j * BC, b);
-          tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &kv_full[st], hh * 64, hk,
-                      j * BC, b);
+        if (MC > 1) {
+          tma_load_4d_mc(smem + L::oK + st * L::kKV + crank * (BC * 128), &tmK, &kv_full[st], crank * 64, hk,
+                         j * BC, b, 3);
+          tma_load_4d_mc(smem + L::oV + st * L::kKV + crank * (BC * 128), &tmV, &kv_full[st], crank * 64, hk,
+                         j * BC, b, 3);
+        } else {
+          for (int hh = 0; hh < NH; ++hh) {
+            tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &kv_full[st], hh * 64, hk,
+                        j * BC, b);
+            tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &kv_full[st], hh * 64, hk,
+                        j * BC, b);
+          }
         }
       }
       __syncwarp();
@@ -517,7 +550,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
           umma_f16(tDQ_u, desc_kmajor_1(sDS, kk), desc_mnmajor(sK, BC, kk), idesc_dq, (j | kk) != 0);
-        umma_commit(&kv_empty[st]);
+        if (MC > 1) umma_commit_mc(&kv_empty[st], 3);
+        else umma_commit(&kv_empty[st]);
         umma_commit(dq_done);
       }
       __syncwarp();
@@ -586,7 +620,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   }
 done:
   tc_fence_before();
-  __syncthreads();
+  if (MC > 1) cluster_sync_all();
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem, 512);
@@ -596,23 +631,20 @@ done:
 // ================================================================== backward: dK, dV
 // One CTA per (128-key tile, kv head, batch); loops over the q heads of the GQA group and over
 // 64-query blocks.  Row threads own KEY rows (transposed formulation).  S^T / dP^T are
-// double-buffered in TMEM, Q/dO tiles ride a 3-deep TMA ring, per-query statistics are prefetched
+// double-buffered in TMEM, Q/dO tiles ride a 4-deep TMA ring, per-query statistics are prefetched
 // one iteration ahead.
 template <int D>
 struct DkvSmem {
   static constexpr int kKV = BQ * D * 2;   // K and V tiles (128 keys)
   static constexpr int kQ = BC * D * 2;    // Q_i / dO_i tiles (64 queries)
-  static constexpr int kStages = 3;
-  static constexpr int kPT = BQ * BC * 2;  // P^T / dS^T tiles
+  static constexpr int kStages = 4;         // P^T / dS^T live in TMEM, so the ring takes the smem they used
   static constexpr int oK = 0;
   static constexpr int oV = oK + kKV;
   static constexpr int oQ = oV + kKV;
   static constexpr int oDO = oQ + kStages * kQ;
-  static constexpr int oPT = oDO + kStages * kQ;
-  static constexpr int oDST = oPT + kPT;
-  static constexpr int oStat = oDST + kPT;               // [stages][2][64] floats
+  static constexpr int oStat = oDO + kStages * kQ;       // [stages][2][64] floats
   static constexpr int oBar = oStat + kStages * 2 * BC * 4;
-  static constexpr int kTotal = oBar + 128 + 1024;
+  static constexpr int kTotal = oBar + 256 + 1024;
 };
 
 template <int D>
@@ -628,13 +660,15 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                                              ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
   uint64_t* kv_full = bars + 0;
-  uint64_t* q_full = bars + 1;    // [3]
-  uint64_t* q_empty = bars + 4;   // [3]
-  uint64_t* s_full = bars + 7;    // [2]
-  uint64_t* pt_full = bars + 9;   // 256 arrivals
-  uint64_t* acc_done = bars + 10;
-  uint64_t* s_free = bars + 11;   // [2] one arrive per row warp
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint64_t* q_full = bars + 1;    // [NS]
+  uint64_t* q_empty = bars + 5;   // [NS]
+  uint64_t* s_full = bars + 9;    // [2] S^T(it) in TMEM
+  uint64_t* dp_full = bars + 11;  // [2] dP^T(it) in TMEM
+  uint64_t* p_full = bars + 13;   // P^T packed into TMEM (one arrival per row warp)
+  uint64_t* ds_full = bars + 14;  // dS^T packed into TMEM
+  uint64_t* acc_done = bars + 15;
+  uint64_t* stat_full = bars + 16;  // [NS] lse / delta of the stage's 64 queries staged in smem
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kt = blockIdx.z;                   // key tile 0 sees every query block: heaviest first
@@ -650,12 +684,11 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     if (lane == 0) {
       mbar_init(kv_full, 1);
       for (int i = 0; i < NS; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
-      mbar_init(&s_full[0], 1);
-      mbar_init(&s_full[1], 1);
-      mbar_init(pt_full, 8);       // one arrival per row warp
+      for (int i = 0; i < NS; ++i) mbar_init(&stat_full[i], 1);
+      for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&dp_full[i], 1); }
+      mbar_init(p_full, 8);        // one arrival per row warp
+      mbar_init(ds_full, 8);
       mbar_init(acc_done, 1);
-      mbar_init(&s_free[0], 8);
-      mbar_init(&s_free[1], 8);
       mbar_fence_init();
     }
     __syncwarp();
@@ -678,11 +711,26 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
     }
     __syncwarp();
+    // The otherwise idle lanes of this warp stage the per-query statistics of each block (-lse*log2e and delta, 64
+    // floats each) next to the Q/dO tiles: loaded one iteration ahead, written once the ring slot is free.
+    float* stat = reinterpret_cast<float*>(smem + L::oStat);
+    int st = 0, hrel = 0, qrel = 0;
+    uint32_t ph = 1;
+    auto stat_load = [&](int hh, int qr, float (&v)[4]) {
+      const int qb = (i_start + qr) * BC;
+      const long long base = ((long long)b * p.Hq + hk * group + hh) * p.S;
+      const int q0i = min(qb + lane, p.S - 1), q1i = min(qb + 32 + lane, p.S - 1);
+      v[0] = -p.lse[base + q0i] * kLog2e;
+      v[1] = -p.lse[base + q1i] * kLog2e;
+      v[2] = p.delta[base + q0i];
+      v[3] = p.delta[base + q1i];
+    };
+    float nxt[4] = {0.f, 0.f, 0.f, 0.f};
+    if (niter > 0) stat_load(0, 0, nxt);
     for (int it = 0; it < niter; ++it) {
-      const int st = it % NS;
-      const int h = hk * group + it / per_head;
-      const int qi = i_start + it % per_head;
-      if (!__all_sync(0xffffffffu, mbar_wait_to(&q_empty[st], ((it / NS) & 1) ^ 1, 34, it))) goto done;
+      const int h = hk * group + hrel;
+      const int qi = i_start + qrel;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&q_empty[st], ph, 34, it))) goto done;
       if (elected) {
         mbar_expect_tx(&q_full[st], 2 * L::kQ);
         for (int hh = 0; hh < NH; ++hh) {
@@ -692,7 +740,16 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                       qi * BC, b);
         }
       }
+      float* sp = stat + st * 128;
+      sp[lane] = nxt[0];
+      sp[32 + lane] = nxt[1];
+      sp[64 + lane] = nxt[2];
+      sp[96 + lane] = nxt[3];
       __syncwarp();
+      if (lane == 0) mbar_arrive(&stat_full[st]);
+      if (++qrel == per_head) { qrel = 0; ++hrel; }
+      if (++st == NS) { st = 0; ph ^= 1; }
+      if (it + 1 < niter) stat_load(hrel, qrel, nxt);
     }
   } else if (warp == 1) {
     const bool elected = elect_one();
@@ -702,7 +759,6 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
     const uint32_t idesc_acc = make_idesc(BQ, D, 1, 1, 0, 1);
     const uint32_t sK = sbase + L::oK, sV = sbase + L::oV;
-    const uint32_t sPT = sbase + L::oPT, sDST = sbase + L::oDST;
     auto issue_first = [&](int it) -> bool {
       const int st = it % NS;
       if (!__all_sync(0xffffffffu, mbar_wait_to(&q_full[st], (it / NS) & 1, 36, it))) return false;
@@ -714,10 +770,11 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tST, desc_kmajor_d(sK, BQ, kk), desc_kmajor_d(sQ, BC, kk), idesc_s, kk != 0);
+        umma_commit(&s_full[it & 1]);
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16(tDPT, desc_kmajor_d(sV, BQ, kk), desc_kmajor_d(sDO, BC, kk), idesc_s, kk != 0);
-        umma_commit(&s_full[it & 1]);
+        umma_commit(&dp_full[it & 1]);
       }
       __syncwarp();
       return true;
@@ -729,7 +786,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       // S^T/dP^T(it+1) overwrite the TMEM buffer that held P^T/dS^T(it-1): safe without a barrier because the
       // dV/dK MMAs that read them were issued earlier by this same thread and the tensor pipe runs in order.
       if (it + 1 < niter && !issue_first(it + 1)) goto done;
-      if (!__all_sync(0xffffffffu, mbar_wait_to(pt_full, it & 1, 37, it))) goto done;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(p_full, it & 1, 37, it))) goto done;
       tc_fence_after();
       const uint32_t sQ = sbase + L::oQ + st * L::kQ;
       const uint32_t sDO = sbase + L::oDO + st * L::kQ;
@@ -741,6 +798,11 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int kk = 0; kk < BC / 16; ++kk)
           umma_f16_ts(tDV_u, tPT + (kk >> 1) * 32 + (kk & 1) * 8, desc_mnmajor(sDO, BC, kk), idesc_acc,
                       (it | kk) != 0);
+      }
+      __syncwarp();
+      if (!__all_sync(0xffffffffu, mbar_wait_to(ds_full, it & 1, 39, it))) goto done;
+      tc_fence_after();
+      if (elected) {
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
           umma_f16_ts(tDK_u, tDST + (kk >> 1) * 32 + (kk & 1) * 8, desc_mnmajor(sQ, BC, kk), idesc_acc,
@@ -754,77 +816,79 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const int quad = warp & 3;
     const int half = (warp - 2) >> 2;          // which 32 of the block's 64 query columns
     const int row = quad * 32 + lane;
-    const int et = threadIdx.x - 64;           // 0..255
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
     const int kpos = n0 + row;
     const float sc = p.scale * kLog2e;
-    float* stat = reinterpret_cast<float*>(smem + L::oStat);
-    uint8_t* sPT = smem + L::oPT;
-    uint8_t* sDST = smem + L::oDST;
-    auto load_stat = [&](int it) -> float {
-      const int h = hk * group + it / per_head;
-      const int qb = (i_start + it % per_head) * BC;
-      const int qq = min(qb + (et & 63), p.S - 1);
-      const long long si = ((long long)b * p.Hq + h) * p.S + qq;
-      return (et < 64) ? p.lse[si] * kLog2e : p.delta[si];
-    };
-    float nxt = (niter > 0 && et < 128) ? load_stat(0) : 0.f;
+    const uint32_t stat_u = smem_u32(smem + L::oStat) + half * 128;   // this warp's 32 of the 64 queries
+    int st = 0, qrel = 0;
+    uint32_t ph = 0;
     for (int it = 0; it < niter; ++it) {
-      const int st = it % NS;
-      const int qb = (i_start + it % per_head) * BC + half * 32;
-      if (et < 128) {
-        stat[st * 128 + et] = nxt;
-        if (it + 1 < niter) nxt = load_stat(it + 1);   // prefetch: consumed next iteration
-      }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (!mbar_wait_to(&s_full[it & 1], (it >> 1) & 1, 38, it)) goto done;
-      tc_fence_after();
-      float s[32], dp[32];
+      const int qb = (i_start + qrel) * BC + half * 32;
       const uint32_t tST = tmem + (it & 1) * 128 + lane_off + half * 32;
-      if (p.debug < 2) {
-        ld_row32x2(tST, tST + 64, s, dp);
-      } else {
-#pragma unroll
-        for (int c = 0; c < 32; ++c) { s[c] = 0.f; dp[c] = 0.f; }
-      }
-      const float* lse2 = stat + st * 128 + half * 32;
-      const float* dlt = lse2 + 64;
+      const uint32_t sstat = stat_u + st * 512;
       const bool need_mask = (p.causal && (n0 + BQ - 1 > qb)) || (qb + 32 > p.S) || (n0 + BQ > p.S);
-      if (p.debug >= 1) {
-        // math skipped
-      } else if (need_mask) {
+      if (!mbar_wait_to(&stat_full[st], ph, 41, it)) goto done;
+      if (!mbar_wait_to(&s_full[it & 1], (it >> 1) & 1, 38, it)) goto done;
+      // Measured: starting on S^T while the dP^T MMAs of the same buffer are still in flight corrupts results
+      // (tcgen05.st into a TMEM buffer the tensor core is accumulating into), so wait for both.
+      if (!mbar_wait_to(&dp_full[it & 1], (it >> 1) & 1, 42, it)) goto done;
+      tc_fence_after();
+      float s[32];
+      {
+        uint32_t x[32];
+        tmem_ld_32x32(tST, x);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) {
+          const float4 nl = lds128(sstat + c4 * 16);          // -lse * log2e, warp-broadcast
+          s[c4 * 4 + 0] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 0]), sc, nl.x));
+          s[c4 * 4 + 1] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 1]), sc, nl.y));
+          s[c4 * 4 + 2] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 2]), sc, nl.z));
+          s[c4 * 4 + 3] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 3]), sc, nl.w));
+        }
+      }
+      if (need_mask) {
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
           const int qp = qb + c;
           const bool ok = (qp < p.S) && (kpos < p.S) && (!p.causal || kpos <= qp);
-          const float pr = ok ? fast_exp2(fmaf(s[c], sc, -lse2[c])) : 0.f;
-          s[c] = pr;                                    // P^T
-          dp[c] = pr * (dp[c] - dlt[c]) * p.scale;      // dS^T (already scaled)
-        }
-      } else {
-#pragma unroll
-        for (int c = 0; c < 32; ++c) {
-          const float pr = fast_exp2(fmaf(s[c], sc, -lse2[c]));
-          s[c] = pr;
-          dp[c] = pr * (dp[c] - dlt[c]) * p.scale;
+          s[c] = ok ? s[c] : 0.f;
         }
       }
       {
-        // bf16-pack this thread's 32 values of P^T and of dS^T and park them in TMEM, over the first half of the
-        // very columns they were computed from (own lanes, own column range: no cross-warp hazard)
-        uint32_t pk[16], dk[16];
+        // bf16-pack this thread's 32 values of P^T and park them in TMEM over the first half of the very columns
+        // they were computed from (own lanes, own column range: no cross-warp hazard)
+        uint32_t pk[16];
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
-          pk[c] = pack_bf16(s[2 * c], s[2 * c + 1]);
-          dk[c] = pack_bf16(dp[2 * c], dp[2 * c + 1]);
-        }
+        for (int c = 0; c < 16; ++c) pk[c] = pack_bf16(s[2 * c], s[2 * c + 1]);
         tmem_st_32x16(tST, pk);
+        tmem_st_wait();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full);                      // dV += P^T dO can start
+      {
+        uint32_t x[32], dk[16];
+        tmem_ld_32x32(tST + 64, x);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) {
+          const float4 dl = lds128(sstat + 256 + c4 * 16);     // delta
+          const float d0 = s[c4 * 4 + 0] * p.scale * (__uint_as_float(x[c4 * 4 + 0]) - dl.x);
+          const float d1 = s[c4 * 4 + 1] * p.scale * (__uint_as_float(x[c4 * 4 + 1]) - dl.y);
+          const float d2 = s[c4 * 4 + 2] * p.scale * (__uint_as_float(x[c4 * 4 + 2]) - dl.z);
+          const float d3 = s[c4 * 4 + 3] * p.scale * (__uint_as_float(x[c4 * 4 + 3]) - dl.w);
+          dk[c4 * 2 + 0] = pack_bf16(d0, d1);
+          dk[c4 * 2 + 1] = pack_bf16(d2, d3);
+        }
         tmem_st_32x16(tST + 64, dk);
         tmem_st_wait();
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(pt_full);
+      if (lane == 0) mbar_arrive(ds_full);
+      if (++qrel == per_head) qrel = 0;
+      if (++st == NS) { st = 0; ph ^= 1; }
     }
     if (niter > 0) {
       if (!mbar_wait_to(acc_done, (niter - 1) & 1, 40)) goto done;
@@ -912,6 +976,32 @@ static int set_smem(K kernel, int bytes) {
   return e == cudaSuccess ? SXB_OK : (int)e;
 }
 
+// Launch `kernel` as 2x1x1 thread-block clusters (grid.x even).
+template <typename K, typename... Args>
+static int launch_cluster2(K kernel, dim3 grid, int threads, int smem_bytes, cudaStream_t s, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(threads);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, args...);
+  return e == cudaSuccess ? SXB_OK : (int)e;
+}
+
+// Head-pair multicast needs D = 128 (two 64-wide halves to split) and an even GQA group (pair shares its K/V head).
+// SXB_ATTN_MC=0 forces the single-CTA kernels (A/B measurements).
+static bool use_multicast(int Hq, int Hk, int D) {
+  static const int env = [] { const char* e = getenv("SXB_ATTN_MC"); return e ? atoi(e) : 1; }();
+  return env != 0 && D == 128 && Hk > 0 && ((Hq / Hk) % 2 == 0) && (Hq % 2 == 0);
+}
+
 }  // namespace attn
 }  // namespace sxb
 
@@ -946,12 +1036,16 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
   p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
   dim3 grid(Hq, B, (S + BQ - 1) / BQ);
   cudaStream_t s = (cudaStream_t)stream;
-  if (D == 128) {
-    if ((rc = set_smem(attn_fwd_kernel<128>, FwdSmem<128>::kTotal))) return rc;
-    attn_fwd_kernel<128><<<grid, kThreads, FwdSmem<128>::kTotal, s>>>(tq, tk, tv, p);
+  if (use_multicast(Hq, Hk, D)) {
+    if ((rc = set_smem(attn_fwd_kernel<128, 2>, FwdSmem<128>::kTotal))) return rc;
+    if ((rc = launch_cluster2(attn_fwd_kernel<128, 2>, grid, kThreads, FwdSmem<128>::kTotal, s, tq, tk, tv, p)))
+      return rc;
+  } else if (D == 128) {
+    if ((rc = set_smem(attn_fwd_kernel<128, 1>, FwdSmem<128>::kTotal))) return rc;
+    attn_fwd_kernel<128, 1><<<grid, kThreads, FwdSmem<128>::kTotal, s>>>(tq, tk, tv, p);
   } else {
-    if ((rc = set_smem(attn_fwd_kernel<64>, FwdSmem<64>::kTotal))) return rc;
-    attn_fwd_kernel<64><<<grid, kThreads, FwdSmem<64>::kTotal, s>>>(tq, tk, tv, p);
+    if ((rc = set_smem(attn_fwd_kernel<64, 1>, FwdSmem<64>::kTotal))) return rc;
+    attn_fwd_kernel<64, 1><<<grid, kThreads, FwdSmem<64>::kTotal, s>>>(tq, tk, tv, p);
   }
   SXB_CHECK_LAUNCH();
   return SXB_OK;
@@ -994,12 +1088,17 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BC))) return rc;
     p.out = dq; p.out_stride = dq_stride;
     dim3 grid(Hq, B, (S + BQ - 1) / BQ);
-    if (D == 128) {
-      if ((rc = set_smem(attn_bwd_dq_kernel<128>, DqSmem<128>::kTotal))) return rc;
-      attn_bwd_dq_kernel<128><<<grid, kBwdThreads, DqSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
+    if (use_multicast(Hq, Hk, D)) {
+      if ((rc = set_smem(attn_bwd_dq_kernel<128, 2>, DqSmem<128>::kTotal))) return rc;
+      if ((rc = launch_cluster2(attn_bwd_dq_kernel<128, 2>, grid, kBwdThreads, DqSmem<128>::kTotal, s, tq, tk, tv,
+                                tdo, p)))
+        return rc;
+    } else if (D == 128) {
+      if ((rc = set_smem(attn_bwd_dq_kernel<128, 1>, DqSmem<128>::kTotal))) return rc;
+      attn_bwd_dq_kernel<128, 1><<<grid, kBwdThreads, DqSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
     } else {
-      if ((rc = set_smem(attn_bwd_dq_kernel<64>, DqSmem<64>::kTotal))) return rc;
-      attn_bwd_dq_kernel<64><<<grid, kBwdThreads, DqSmem<64>::kTotal, s>>>(tq, tk, tv, tdo, p);
+      if ((rc = set_smem(attn_bwd_dq_kernel<64, 1>, DqSmem<64>::kTotal))) return rc;
+      attn_bwd_dq_kernel<64, 1><<<grid, kBwdThreads, DqSmem<64>::kTotal, s>>>(tq, tk, tv, tdo, p);
     }
     SXB_CHECK_LAUNCH();
   }

@@ -4,7 +4,7 @@
 //   sxb_bias_dropout_residual   out = residual + dropout(x + bias)            (+ 1-byte keep mask)
 //   sxb_dropout_bwd             dx  = dy * keep / (1 - p)
 //   sxb_biased_softmax_fwd/bwd  softmax(scale * s + bias1 + bias2) over the last dim of [B, H, Sq, Sk], both biases
-//                               with arbitrary broadcast strides, optional dropout of the probabilities
+//                               with arbitrary broadcast strides
 //   sxb_bsr_softmax_fwd/bwd     softmax over the non-zero blocks of one block-row of a block-sparse score matrix,
 //                               with relative-position bias, key-padding mask and attention mask (add or mul mode)
 //
@@ -95,12 +95,12 @@ struct BiasDesc {
   long long sb, sh, sq, sk;  // element strides (0 = broadcast)
 };
 
-// One CTA per score row.  Pass 1: online max/sum, pass 2: normalise (+dropout) and store.
+// One CTA per score row.  Pass 1: online max/sum, pass 2: normalise and store (dropout of the probabilities, when
+// wanted, is the bias_dropout_residual kernel with no bias and no residual).
 template <typename T>
 __global__ void __launch_bounds__(256)
-biased_softmax_fwd_kernel(const T* __restrict__ s, T* __restrict__ out, uint8_t* __restrict__ keep, BiasDesc b1,
-                          BiasDesc b2, int H, int Sq, int Sk, float scale, float p, unsigned long long seed,
-                          unsigned long long offset) {
+biased_softmax_fwd_kernel(const T* __restrict__ s, T* __restrict__ out, BiasDesc b1, BiasDesc b2, int H, int Sq,
+                          int Sk, float scale) {
   __shared__ float red[64];
   const long long row = blockIdx.x;
   const int q = (int)(row % Sq);
@@ -130,85 +130,231 @@ biased_softmax_fwd_kernel(const T* __restrict__ s, T* __restrict__ out, uint8_t*
   sum = (mx > -INFINITY) ? sum * __expf(mx - gmx) : 0.f;
   const float gsum = block_sum(sum, red + 32);
   const float inv_sum = gsum > 0.f ? 1.f / gsum : 0.f;
-  const Philox rng(seed);
-  const float inv_keep = p < 1.f ? 1.f / (1.f - p) : 0.f;
   T* orow = out + row * Sk;
   for (int k = threadIdx.x; k < Sk; k += blockDim.x) {
     const float v = val(k);
-    float pr = (v > -INFINITY) ? __expf(v - gmx) * inv_sum : 0.f;
-    if (p > 0.f) {
-      const unsigned long long idx = (unsigned long long)row * Sk + k;
-      const uint4 u = rng(idx >> 2, offset);
-      const uint32_t rr = (idx & 3) == 0 ? u.x : (idx & 3) == 1 ? u.y : (idx & 3) == 2 ? u.z : u.w;
-      const bool kp = u01(rr) >= p;
-      if (keep) keep[idx] = kp ? 1 : 0;
-      pr = kp ? pr * inv_keep : 0.f;
-    }
+    const float pr = (v > -INFINITY) ? __expf(v - gmx) * inv_sum : 0.f;
     orow[k] = from_f32<T>(pr);
   }
 }
 
-// dS = scale * P * (dP - sum_k dP*P); with dropout, ``y`` holds the dropped probabilities and
-// dP_eff = dy * keep / (1-p), P = y * (1-p) on kept entries (dropped entries carry no gradient).  Optional
-// dbias (same shape as the scores, un-scaled) for the Evoformer pair bias.
+// dS = scale * P * (dP - sum_k dP*P).  Optional dbias (same shape as the scores, un-scaled) for additive biases.
 template <typename T>
 __global__ void __launch_bounds__(256)
-biased_softmax_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, const uint8_t* __restrict__ keep,
-                          T* __restrict__ ds, T* __restrict__ dbias, int Sk, float scale, float p) {
+biased_softmax_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ ds,
+                          T* __restrict__ dbias, int Sk, float scale) {
   __shared__ float red[32];
   const long long row = blockIdx.x;
   const T* yr = y + row * Sk;
   const T* dr = dy + row * Sk;
-  const uint8_t* kr = keep ? keep + row * Sk : nullptr;
-  const float keep_scale = 1.f - p;
   float dot = 0.f;
-  for (int k = threadIdx.x; k < Sk; k += blockDim.x) {
-    // P*dP_eff = (y*(1-p)) * (dy/(1-p)) = y*dy on kept entries; dropped entries have y == 0
-    dot += to_f32<T>(yr[k]) * to_f32<T>(dr[k]);
-  }
+  for (int k = threadIdx.x; k < Sk; k += blockDim.x) dot += to_f32<T>(yr[k]) * to_f32<T>(dr[k]);
   dot = block_sum(dot, red);
   for (int k = threadIdx.x; k < Sk; k += blockDim.x) {
-    float pr = to_f32<T>(yr[k]), g = to_f32<T>(dr[k]);
-    float v;
-    if (kr) {
-      // dropped entries: P unknown from y (it is 0 there) — recover nothing, their dP_eff is 0 so
-      // dS = -P * dot; we need P: callers keep the un-dropped probabilities when p > 0 (see Python).
-      const bool kp = kr[k] != 0;
-      const float P = pr;                     // un-dropped probability (Python passes it when p > 0)
-      const float dP = kp ? g / keep_scale : 0.f;
-      v = P * (dP - dot);
-    } else {
-      v = pr * (g - dot);
-    }
+    const float v = to_f32<T>(yr[k]) * (to_f32<T>(dr[k]) - dot);
     if (dbias) dbias[row * Sk + k] = from_f32<T>(v);
     ds[row * Sk + k] = from_f32<T>(v * scale);
   }
 }
 
-// with dropout the dot product must use the un-dropped P and the effective dP
+// ------------------------------------------------------------------ block-sparse (BSR) softmax
+// x: [B, nnz, blk, blk] — the non-zero blocks of a [H, S/blk, S/blk] layout in (head, block-row, block-col) order, so
+// the CSR position of a block is its index in x.  One warp per (batch, head, block-row, row-in-block).
+struct BsrArgs {
+  const int* row_ptr;   // [H * nrb + 1]
+  const int* col_idx;   // [nnz] block column
+  int H, nrb, ncb, blk, nnz;
+  const void* rpe;      // [H, S, S] or null (rpe_sb = batch stride, 0 = shared)
+  long long rpe_sb;
+  const void* kpm;      // [B, S] or null
+  const void* amask;    // [S, S] or null
+  int kpm_mode, amask_mode;   // 1 = add, 2 = mul (0 -> -inf, else unchanged)
+  float scale;
+};
+
 template <typename T>
 __global__ void __launch_bounds__(256)
-biased_softmax_dropout_bwd_kernel(const T* __restrict__ prob, const T* __restrict__ dy,
-                                  const uint8_t* __restrict__ keep, T* __restrict__ ds, T* __restrict__ dbias,
-                                  int Sk, float scale, float p) {
-  __shared__ float red[32];
-  const long long row = blockIdx.x;
-  const T* pr = prob + row * Sk;
-  const T* dr = dy + row * Sk;
-  const uint8_t* kr = keep + row * Sk;
-  const float inv = 1.f / (1.f - p);
+bsr_softmax_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, BsrArgs a, long long n_rows) {
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= n_rows) return;
+  const int r = (int)(w % a.blk);
+  const long long t = w / a.blk;
+  const int hr = (int)(t % ((long long)a.H * a.nrb));   // head * nrb + block-row
+  const long long b = t / ((long long)a.H * a.nrb);
+  const int h = hr / a.nrb, rb = hr % a.nrb;
+  const int j0 = a.row_ptr[hr], j1 = a.row_ptr[hr + 1];
+  const int S = a.nrb * a.blk, Sk = a.ncb * a.blk;
+  const int q = rb * a.blk + r;
+  const int ncol = (j1 - j0) * a.blk;
+  const T* rpe = a.rpe ? static_cast<const T*>(a.rpe) + b * a.rpe_sb + ((long long)h * S + q) * Sk : nullptr;
+  const T* kpm = a.kpm ? static_cast<const T*>(a.kpm) + b * Sk : nullptr;
+  const T* am = a.amask ? static_cast<const T*>(a.amask) + (long long)q * Sk : nullptr;
+  auto addr = [&](int i) -> long long {
+    const int j = j0 + i / a.blk, c = i % a.blk;
+    return (((long long)b * a.nnz + j) * a.blk + r) * a.blk + c;
+  };
+  auto val = [&](int i) -> float {
+    const int j = j0 + i / a.blk, c = i % a.blk;
+    const int k = a.col_idx[j] * a.blk + c;
+    float v = to_f32<T>(x[(((long long)b * a.nnz + j) * a.blk + r) * a.blk + c]) * a.scale;
+    if (rpe) v += to_f32<T>(rpe[k]);
+    if (kpm) {
+      const float m = to_f32<T>(kpm[k]);
+      v = a.kpm_mode == 2 ? (m == 0.f ? -INFINITY : v) : v + m;
+    }
+    if (am) {
+      const float m = to_f32<T>(am[k]);
+      v = a.amask_mode == 2 ? (m == 0.f ? -INFINITY : v) : v + m;
+    }
+    return v;
+  };
+  float mx = -INFINITY;
+  for (int i = lane; i < ncol; i += 32) mx = fmaxf(mx, val(i));
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int i = lane; i < ncol; i += 32) {
+    const float v = val(i);
+    sum += (v > -INFINITY) ? __expf(v - mx) : 0.f;
+  }
+  sum = warp_sum(sum);
+  const float inv = sum > 0.f ? 1.f / sum : 0.f;
+  for (int i = lane; i < ncol; i += 32) {
+    const float v = val(i);
+    y[addr(i)] = from_f32<T>((v > -INFINITY) ? __expf(v - mx) * inv : 0.f);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+bsr_softmax_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, BsrArgs a,
+                       long long n_rows) {
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= n_rows) return;
+  const int r = (int)(w % a.blk);
+  const long long t = w / a.blk;
+  const int hr = (int)(t % ((long long)a.H * a.nrb));
+  const long long b = t / ((long long)a.H * a.nrb);
+  const int j0 = a.row_ptr[hr], j1 = a.row_ptr[hr + 1];
+  const int ncol = (j1 - j0) * a.blk;
+  auto addr = [&](int i) -> long long {
+    const int j = j0 + i / a.blk, c = i % a.blk;
+    return (((long long)b * a.nnz + j) * a.blk + r) * a.blk + c;
+  };
   float dot = 0.f;
-  for (int k = threadIdx.x; k < Sk; k += blockDim.x)
-    if (kr[k]) dot += to_f32<T>(pr[k]) * to_f32<T>(dr[k]) * inv;
-  dot = block_sum(dot, red);
-  for (int k = threadIdx.x; k < Sk; k += blockDim.x) {
-    const float P = to_f32<T>(pr[k]);
-    const float dP = kr[k] ? to_f32<T>(dr[k]) * inv : 0.f;
-    const float v = P * (dP - dot);
-    if (dbias) dbias[row * Sk + k] = from_f32<T>(v);
-    ds[row * Sk + k] = from_f32<T>(v * scale);
+  for (int i = lane; i < ncol; i += 32) {
+    const long long o = addr(i);
+    dot += to_f32<T>(y[o]) * to_f32<T>(dy[o]);
+  }
+  dot = warp_sum(dot);
+  for (int i = lane; i < ncol; i += 32) {
+    const long long o = addr(i);
+    dx[o] = from_f32<T>(to_f32<T>(y[o]) * (to_f32<T>(dy[o]) - dot) * a.scale);
   }
 }
 
 }  // namespace sd
 }  // namespace sxb
+
+using namespace sxb;
+
+#define SD_DISPATCH(dtype, ...)                                    \
+  switch (dtype) {                                                 \
+    case kBF16: { using T = __nv_bfloat16; __VA_ARGS__; break; }   \
+    case kF16: { using T = __half; __VA_ARGS__; break; }           \
+    case kF32: { using T = float; __VA_ARGS__; break; }            \
+    default: return SXB_ERR_UNSUPPORTED;                           \
+  }
+
+static inline unsigned sd_blocks(long long n, int per_block) {
+  long long b = (n + per_block - 1) / per_block;
+  const long long cap = 148LL * 16;
+  return (unsigned)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+// out = residual + dropout(x + bias); ``keep`` (uint8 per element) may be null when p == 0.  n % 4 == 0, cols % 4 == 0.
+SXB_API int sxb_bias_dropout_residual(const void* x, const void* bias, const void* residual, void* out, void* keep,
+                                      long long n, int cols, float p, long long seed, long long offset, int dtype,
+                                      void* stream) {
+  if (n <= 0) return SXB_OK;
+  if ((n & 3) || (cols & 3) || p < 0.f || p > 1.f) return SXB_ERR_BAD_ARG;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  SD_DISPATCH(dtype, sd::bias_dropout_residual_kernel<T><<<sd_blocks(n / 4, 256), 256, 0, s>>>(
+                         static_cast<const T*>(x), static_cast<const T*>(bias), static_cast<const T*>(residual),
+                         static_cast<T*>(out), static_cast<uint8_t*>(keep), n / 4, cols, p,
+                         (unsigned long long)seed, (unsigned long long)offset));
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+SXB_API int sxb_dropout_bwd(const void* dy, const void* keep, void* dx, long long n, float p, int dtype,
+                            void* stream) {
+  if (n <= 0) return SXB_OK;
+  if (p < 0.f || p >= 1.f) return SXB_ERR_BAD_ARG;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  SD_DISPATCH(dtype, sd::dropout_bwd_kernel<T><<<sd_blocks(n, 256 * 4), 256, 0, s>>>(
+                         static_cast<const T*>(dy), static_cast<const uint8_t*>(keep), static_cast<T*>(dx), n,
+                         1.f / (1.f - p)));
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+// scores/out [B, H, Sq, Sk] contiguous; bias strides in elements (b, h, q, k), 0 = broadcast.
+SXB_API int sxb_biased_softmax_fwd(const void* scores, void* out, const void* bias1, long long b1b, long long b1h,
+                                   long long b1q, long long b1k, const void* bias2, long long b2b, long long b2h,
+                                   long long b2q, long long b2k, long long B, int H, int Sq, int Sk, float scale,
+                                   int dtype, void* stream) {
+  const long long rows = B * H * Sq;
+  if (rows <= 0 || Sk <= 0) return SXB_OK;
+  if (rows > 0x7fffffffLL) return SXB_ERR_TOO_LARGE;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  sd::BiasDesc d1{bias1, b1b, b1h, b1q, b1k}, d2{bias2, b2b, b2h, b2q, b2k};
+  SD_DISPATCH(dtype, sd::biased_softmax_fwd_kernel<T><<<(unsigned)rows, 256, 0, s>>>(
+                         static_cast<const T*>(scores), static_cast<T*>(out), d1, d2, H, Sq, Sk, scale));
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+SXB_API int sxb_biased_softmax_bwd(const void* y, const void* dy, void* ds, void* dbias, long long rows, int Sk,
+                                   float scale, int dtype, void* stream) {
+  if (rows <= 0 || Sk <= 0) return SXB_OK;
+  if (rows > 0x7fffffffLL) return SXB_ERR_TOO_LARGE;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  SD_DISPATCH(dtype, sd::biased_softmax_bwd_kernel<T><<<(unsigned)rows, 256, 0, s>>>(
+                         static_cast<const T*>(y), static_cast<const T*>(dy), static_cast<T*>(ds),
+                         static_cast<T*>(dbias), Sk, scale));
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+SXB_API int sxb_bsr_softmax_fwd(const void* x, void* y, const void* row_ptr, const void* col_idx, long long B, int H,
+                                int nrb, int ncb, int blk, int nnz, const void* rpe, long long rpe_sb, const void* kpm,
+                                int kpm_mode, const void* amask, int amask_mode, float scale, int dtype,
+                                void* stream) {
+  const long long n_rows = B * H * nrb * blk;
+  if (n_rows <= 0 || nnz <= 0) return SXB_OK;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  sd::BsrArgs a{static_cast<const int*>(row_ptr), static_cast<const int*>(col_idx), H, nrb, ncb, blk, nnz, rpe, rpe_sb,
+                kpm, amask, kpm_mode, amask_mode, scale};
+  const unsigned blocks = (unsigned)((n_rows + 7) / 8);
+  SD_DISPATCH(dtype, sd::bsr_softmax_fwd_kernel<T><<<blocks, 256, 0, s>>>(static_cast<const T*>(x),
+                                                                          static_cast<T*>(y), a, n_rows));
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+SXB_API int sxb_bsr_softmax_bwd(const void* y, const void* dy, void* dx, const void* row_ptr, const void* col_idx,
+                                long long B, int H, int nrb, int ncb, int blk, int nnz, float scale, int dtype,
+                                void* stream) {
+  const long long n_rows = B * H * nrb * blk;
+  if (n_rows <= 0 || nnz <= 0) return SXB_OK;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  sd::BsrArgs a{static_cast<const int*>(row_ptr), static_cast<const int*>(col_idx), H, nrb, ncb, blk, nnz, nullptr, 0,
+                nullptr, nullptr, 0, 0, scale};
+  const unsigned blocks = (unsigned)((n_rows + 7) / 8);
+  SD_DISPATCH(dtype, sd::bsr_softmax_bwd_kernel<T><<<blocks, 256, 0, s>>>(
+                         static_cast<const T*>(y), static_cast<const T*>(dy), static_cast<T*>(dx), a, n_rows));
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}

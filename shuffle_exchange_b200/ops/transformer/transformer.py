@@ -1,0 +1,222 @@
+"""BERT-style fused training transformer layer (``DeepSpeedTransformerLayer``).
+
+Reference: ``deepspeed/ops/transformer/transformer.py`` — config (:19-139), the autograd function around the native
+``forward_fp16/backward_fp16`` entry points (:142-293) and the layer module with its 12 parameters, init rule and
+forward signature (:296-412).  The native module is absent from the reference tree; this is a fresh
+B200 implementation on the framework's own kernels:
+
+==========================  ==============================================================================
+ QKV / out / FFN GEMMs       tcgen05 bf16 GEMM (``csrc/gemm_tcgen05.cu``) through ``ops.functional.linear``
+ LayerNorm (pre/post)        ``sxb_layernorm_fwd/bwd`` (one pass, fp32 statistics)
+ attention, no mask          TMA/tcgen05 flash attention (``csrc/attention.cu``), non-causal
+ attention, additive mask    batched GEMM + ``sxb_biased_softmax`` (mask broadcast inside the kernel)
+ bias + GELU                 ``sxb_bias_act`` fused epilogue
+ bias + dropout + residual   ``sxb_bias_dropout_residual`` (Philox keep-mask, 1 byte/element)
+==========================  ==============================================================================
+
+The memory options of the reference map to activation recomputation of the same sub-blocks:
+``gelu_checkpoint`` recomputes the FFN-in GEMM epilogue, ``attn_dropout_checkpoint`` recomputes attention
+probabilities + dropout, ``normalize_invertible`` recomputes the LayerNorm output instead of saving it.
+``stochastic_mode`` only relaxes determinism in the reference; kernels here are deterministic, the flag is accepted.
+"""
+from __future__ import annotations
+
+import json
+import math
+from typing import Optional
+
+import torch
+from torch import nn
+from torch.utils.checkpoint import checkpoint as _ckpt
+
+from .. import functional as F
+from ..fused_softmax import bias_dropout_residual, biased_softmax, dropout as fused_dropout
+
+
+class TransformerConfig:
+
+    def __init__(self, batch_size, hidden_size, intermediate_size, heads, attn_dropout_ratio, hidden_dropout_ratio,
+                 num_hidden_layers, initializer_range):
+        self.layer_id = -1
+        self.batch_size = batch_size
+        self.hidden_size = hidden_size
+        self.intermediate_size = intermediate_size
+        self.heads = heads
+        self.attn_dropout_ratio = attn_dropout_ratio
+        self.hidden_dropout_ratio = hidden_dropout_ratio
+        self.num_hidden_layers = num_hidden_layers
+        self.initializer_range = initializer_range
+
+
+class DeepSpeedTransformerConfig(TransformerConfig):
+    """Same fields and defaults as the reference config (``transformer.py:35-126``)."""
+
+    def __init__(self, batch_size=-1, hidden_size=-1, intermediate_size=-1, heads=-1, attn_dropout_ratio=-1,
+                 hidden_dropout_ratio=-1, num_hidden_layers=-1, initializer_range=-1, layer_norm_eps=1e-12,
+                 local_rank=-1, seed=-1, fp16=False, pre_layer_norm=True, normalize_invertible=False,
+                 gelu_checkpoint=False, adjust_init_range=True, attn_dropout_checkpoint=False,
+                 stochastic_mode=False, return_tuple=False, training=True, bf16=False):
+        super().__init__(batch_size, hidden_size, (intermediate_size if intermediate_size > 0 else 4 * hidden_size),
+                         heads, attn_dropout_ratio, hidden_dropout_ratio, num_hidden_layers, initializer_range)
+        self.fp16 = fp16
+        self.bf16 = bf16
+        self.pre_layer_norm = pre_layer_norm
+        self.local_rank = local_rank
+        self.seed = seed
+        self.normalize_invertible = normalize_invertible
+        self.gelu_checkpoint = gelu_checkpoint
+        self.adjust_init_range = adjust_init_range
+        self.test_gemm = False
+        self.layer_norm_eps = layer_norm_eps
+        self.training = training
+        self.is_grad_enabled = True
+        self.attn_dropout_checkpoint = attn_dropout_checkpoint
+        self.stochastic_mode = stochastic_mode
+        self.return_tuple = return_tuple
+
+    @classmethod
+    def from_dict(cls, json_object):
+        config = cls()
+        for key, value in json_object.items():
+            config.__dict__[key] = value
+        return config
+
+    @classmethod
+    def from_json_file(cls, json_file):
+        with open(json_file, "r", encoding="utf-16") as reader:
+            return cls.from_dict(json.loads(reader.read()))
+
+
+def _attention(layer: "DeepSpeedTransformerLayer", qkv: torch.Tensor, mask: Optional[torch.Tensor]) -> torch.Tensor:
+    cfg = layer.config
+    B, S, _ = qkv.shape
+    H, Dh = cfg.heads, cfg.hidden_size // cfg.heads
+    q, k, v = qkv.view(B, S, 3, H, Dh).unbind(2)
+    p_attn = cfg.attn_dropout_ratio if layer.training else 0.0
+    flash_ok = (mask is None and p_attn <= 0 and qkv.is_cuda and qkv.dtype == torch.bfloat16 and Dh in (64, 128))
+    if flash_ok:
+        return F.flash_attention(q, k, v, causal=False).reshape(B, S, H * Dh)
+    # scores materialised: batched GEMM (library) + one fused mask/scale/softmax pass (+ fused dropout)
+    qh, kh, vh = (t.permute(0, 2, 1, 3) for t in (q, k, v))
+    scores = torch.matmul(qh, kh.transpose(-1, -2))
+    if mask is not None and mask.dim() == 2:          # [B, S] additive
+        mask = mask[:, None, None, :]
+    elif mask is not None and mask.dim() == 3:        # [B, S, S]
+        mask = mask[:, None]
+    probs = biased_softmax(scores, mask, None, 1.0 / math.sqrt(Dh))
+    probs = fused_dropout(probs, p_attn, layer.training)
+    ctx = torch.matmul(probs, vh)
+    return ctx.permute(0, 2, 1, 3).reshape(B, S, H * Dh)
+
+
+def _attn_block(layer, x, mask):
+    cfg = layer.config
+    h = F.layer_norm(x, layer.attn_nw, layer.attn_nb, cfg.layer_norm_eps) if cfg.pre_layer_norm else x
+    qkv = F.linear(h, layer.attn_qkvw, layer.attn_qkvb)
+    if cfg.attn_dropout_checkpoint and torch.is_grad_enabled() and x.requires_grad:
+        ctx = _ckpt(lambda t: _attention(layer, t, mask), qkv, use_reentrant=False, preserve_rng_state=True)
+    else:
+        ctx = _attention(layer, qkv, mask)
+    out = F.linear(ctx, layer.attn_ow)
+    out = bias_dropout_residual(out, layer.attn_ob, x, cfg.hidden_dropout_ratio, layer.training)
+    if not cfg.pre_layer_norm:
+        out = F.layer_norm(out, layer.attn_nw, layer.attn_nb, cfg.layer_norm_eps)
+    return out
+
+
+def _ffn_in(layer, h):
+    return F.bias_act(F.linear(h, layer.inter_w), layer.inter_b, "gelu")
+
+
+def _ffn_block(layer, x):
+    cfg = layer.config
+    h = F.layer_norm(x, layer.norm_w, layer.norm_b, cfg.layer_norm_eps) if cfg.pre_layer_norm else x
+    if cfg.gelu_checkpoint and torch.is_grad_enabled() and x.requires_grad:
+        inter = _ckpt(lambda t: _ffn_in(layer, t), h, use_reentrant=False)
+    else:
+        inter = _ffn_in(layer, h)
+    out = F.linear(inter, layer.output_w)
+    out = bias_dropout_residual(out, layer.output_b, x, cfg.hidden_dropout_ratio, layer.training)
+    if not cfg.pre_layer_norm:
+        out = F.layer_norm(out, layer.norm_w, layer.norm_b, cfg.layer_norm_eps)
+    return out
+
+
+class DeepSpeedTransformerLayer(nn.Module):
+    """Drop-in for the reference layer: same parameter names/shapes (``attn_qkvw [3H,H]``, ``attn_qkvb``, ``attn_ow``,
+    ``attn_ob``, ``attn_nw``, ``attn_nb``, ``inter_w [I,H]``, ``inter_b``, ``output_w [H,I]``, ``output_b``,
+    ``norm_w``, ``norm_b``), same init rule and forward signature."""
+    layer_id = 0
+
+    def __init__(self, config: DeepSpeedTransformerConfig, initial_weights=None, initial_biases=None):
+        super().__init__()
+        self.config = config
+        self.config.layer_id = DeepSpeedTransformerLayer.layer_id
+        DeepSpeedTransformerLayer.layer_id += 1
+        if self.config.local_rank >= 0 and torch.cuda.is_available():
+            torch.cuda.set_device(self.config.local_rank)
+        Hd, I = config.hidden_size, config.intermediate_size
+        if initial_weights is None and initial_biases is None:
+            self.attn_qkvw = nn.Parameter(torch.empty(Hd * 3, Hd))
+            self.attn_qkvb = nn.Parameter(torch.empty(Hd * 3))
+            self.attn_ow = nn.Parameter(torch.empty(Hd, Hd))
+            self.attn_ob = nn.Parameter(torch.empty(Hd))
+            self.attn_nw = nn.Parameter(torch.empty(Hd))
+            self.attn_nb = nn.Parameter(torch.empty(Hd))
+            self.inter_w = nn.Parameter(torch.empty(I, Hd))
+            self.inter_b = nn.Parameter(torch.empty(I))
+            self.output_w = nn.Parameter(torch.empty(Hd, I))
+            self.output_b = nn.Parameter(torch.empty(Hd))
+            self.norm_w = nn.Parameter(torch.empty(Hd))
+            self.norm_b = nn.Parameter(torch.empty(Hd))
+            self.init_transformer_weights(self.config.adjust_init_range)
+        else:
+            # unit-test path of the reference: q/k/v weights arrive separately (:341-364)
+            q, k, v = (initial_weights[i].data for i in range(3))
+            self.attn_qkvw = nn.Parameter(torch.cat((q, k, v)))
+            self.attn_qkvb = nn.Parameter(torch.zeros(Hd * 3, dtype=q.dtype, device=q.device))
+            self.attn_ow, self.attn_ob = initial_weights[3], initial_biases[3]
+            self.attn_nw, self.attn_nb = initial_weights[4], initial_biases[4]
+            self.inter_w, self.inter_b = initial_weights[5], initial_biases[5]
+            self.output_w, self.output_b = initial_weights[6], initial_biases[6]
+            self.norm_w, self.norm_b = initial_weights[7], initial_biases[7]
+        if config.seed is not None and config.seed >= 0:
+            self._seed = int(config.seed) + self.config.layer_id
+
+    def init_transformer_weights(self, adjust_init_range=False):
+        num_layers = self.config.num_hidden_layers
+        output_std = self.config.initializer_range
+        if adjust_init_range and num_layers > 0:
+            output_std = self.config.initializer_range / math.sqrt(2.0 * num_layers)
+        with torch.no_grad():
+            self.attn_qkvw.normal_(mean=0.0, std=self.config.initializer_range)
+            self.attn_qkvb.zero_()
+            self.attn_ow.normal_(mean=0.0, std=output_std)
+            self.attn_ob.zero_()
+            self.attn_nw.fill_(1.0)
+            self.attn_nb.zero_()
+            self.inter_w.normal_(mean=0.0, std=self.config.initializer_range)
+            self.inter_b.zero_()
+            self.output_w.normal_(mean=0.0, std=output_std)
+            self.output_b.zero_()
+            self.norm_w.fill_(1.0)
+            self.norm_b.zero_()
+
+    def forward(self, hidden_states, attention_mask=None, head_mask=None, layer_head_mask=None,
+                encoder_hidden_states=None, encoder_attention_mask=None, past_key_value=None,
+                output_attentions=False, grads=None):
+        self.config.is_grad_enabled = torch.is_grad_enabled()
+        self.config.training = self.training
+        x = hidden_states
+        if attention_mask is not None and attention_mask.dtype == torch.bool:
+            attention_mask = torch.zeros_like(attention_mask, dtype=x.dtype).masked_fill(~attention_mask,
+                                                                                        torch.finfo(x.dtype).min)
+        if self.config.normalize_invertible and torch.is_grad_enabled() and x.requires_grad:
+            # drop the saved LayerNorm outputs: the whole sub-block is recomputed from its input in backward
+            x = _ckpt(lambda t: _attn_block(self, t, attention_mask), x, use_reentrant=False,
+                      preserve_rng_state=True)
+            x = _ckpt(lambda t: _ffn_block(self, t), x, use_reentrant=False, preserve_rng_state=True)
+        else:
+            x = _attn_block(self, x, attention_mask)
+            x = _ffn_block(self, x)
+        return (x,) if self.config.return_tuple else x

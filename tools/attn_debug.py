@@ -16,7 +16,9 @@ for _ in range(3):
 torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for _ in range(5):
+        with torch.no_grad():
+            F.flash_attention(q, k, v, causal=True)
         o.backward(g, retain_graph=True)
     torch.cuda.synchronize()
 out = {e.key[:40]: round(e.device_time_total / 5000.0, 3) for e in prof.key_averages() if "attn" in e.key}
-print(json.dumps({"mode": os.environ.get("SXB_ATTN_DEBUG", "0"), "ms": out}))
+print(json.dumps({"mode": os.environ.get("SXB_ATTN_DEBUG", "0"), "mc": os.environ.get("SXB_ATTN_MC", "1"), "ms": out}))
