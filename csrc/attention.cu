@@ -415,13 +415,11 @@ struct DqSmem {
   static constexpr int kQ = BQ * D * 2;      // Q and dO tiles
   static constexpr int kKV = BC * D * 2;
   static constexpr int kStages = 4;
-  static constexpr int kDS = BQ * BC * 2;
   static constexpr int oQ = 0;
   static constexpr int oDO = oQ + kQ;
   static constexpr int oK = oDO + kQ;
   static constexpr int oV = oK + kStages * kKV;
-  static constexpr int oDS = oV + kStages * kKV;
-  static constexpr int oBar = oDS + kDS;
+  static constexpr int oBar = oV + kStages * kKV;
   static constexpr int kTotal = oBar + 128 + 1024;
 };
 
@@ -460,7 +458,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       for (int i = 0; i < NS; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], MC); }
       mbar_init(&s_full[0], 1);
       mbar_init(&s_full[1], 1);
-      mbar_init(ds_full, 256);
+      mbar_init(ds_full, 8);   // one arrival per row warp
       mbar_init(dq_done, 1);
       mbar_init(&s_free[0], 8);
       mbar_init(&s_free[1], 8);
@@ -517,7 +515,6 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
     const uint32_t idesc_dq = make_idesc(BQ, D, 1, 1, 0, 1);
     const uint32_t sQ = sbase + L::oQ, sDO = sbase + L::oDO;
-    const uint32_t sDS = sbase + L::oDS;
     auto issue_sdp = [&](int j) -> bool {
       const int st = j % NS;
       if (!__all_sync(0xffffffffu, mbar_wait_to(&kv_full[st], (j / NS) & 1, 29, j))) return false;
@@ -549,7 +546,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       if (elected) {
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)
-          umma_f16(tDQ_u, desc_kmajor_1(sDS, kk), desc_mnmajor(sK, BC, kk), idesc_dq, (j | kk) != 0);
+          umma_f16_ts(tDQ_u, tm_u + (j & 1) * 128 + (kk >> 1) * 32 + (kk & 1) * 8, desc_mnmajor(sK, BC, kk),
+                      idesc_dq, (j | kk) != 0);
         if (MC > 1) umma_commit_mc(&kv_empty[st], 3);
         else umma_commit(&kv_empty[st]);
         umma_commit(dq_done);
@@ -566,7 +564,6 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const long long stat_idx = ((long long)b * p.Hq + h) * p.S + min(qpos, p.S - 1);
     const float lse2 = p.lse[stat_idx] * kLog2e;
     const float dlt = p.delta[stat_idx];
-    uint8_t* sDS = smem + L::oDS;
     for (int j = 0; j < nblk; ++j) {
       if (!mbar_wait_to(&s_full[j & 1], (j >> 1) & 1, 31, j)) goto done;
       tc_fence_after();
@@ -590,11 +587,18 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           s[c] = pr * (dp[c] - dlt) * p.scale;
         }
       }
-      if (j > 0) if (!mbar_wait_to(dq_done, (j - 1) & 1, 32, j)) goto done;  // dQ(j-1) no longer reads sDS
-      store_half_sw128(sDS, row, half, s);
-      fence_async_smem();
+      {
+        // dS (bf16) is parked in TMEM over the first half of this warp's own S columns and consumed from there as
+        // the A operand of dQ += dS K (no smem round trip, no async-proxy fence, one arrival per warp)
+        uint32_t pk[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) pk[c] = pack_bf16(s[2 * c], s[2 * c + 1]);
+        tmem_st_32x16(tS, pk);
+        tmem_st_wait();
+      }
       tc_fence_before();
-      mbar_arrive(ds_full);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(ds_full);
     }
     if (!mbar_wait_to(dq_done, (nblk - 1) & 1, 33)) goto done;
     tc_fence_after();
