@@ -117,12 +117,10 @@ struct FwdSmem {
   static constexpr int kQ = BQ * D * 2;
   static constexpr int kKV = BC * D * 2;
   static constexpr int kStages = 2;
-  static constexpr int kP = BQ * BC * 2;
   static constexpr int oQ = 0;
   static constexpr int oK = oQ + kQ;
   static constexpr int oV = oK + kStages * kKV;
-  static constexpr int oP = oV + kStages * kKV;
-  static constexpr int oBar = oP + kP;
+  static constexpr int oBar = oV + kStages * kKV;   // 96 KB + barriers at D = 128: two CTAs per SM
   static constexpr int kTotal = oBar + 128 + 1024;
 };
 
@@ -170,7 +168,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         mbar_init(&k_full[i], 1); mbar_init(&v_full[i], 1); mbar_init(&k_empty[i], MC);
         mbar_init(&v_empty[i], MC); mbar_init(&s_full[i], 1);
       }
-      mbar_init(p_full, 128);
+      mbar_init(p_full, 4);     // one arrival per row warp
       mbar_init(o_done, 1);
       mbar_init(&s_free[0], 4);
       mbar_init(&s_free[1], 4);
@@ -257,7 +255,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
     const uint32_t idesc_o = make_idesc(BQ, D, 1, 1, 0, 1);
     const uint32_t sQ = sbase + L::oQ;
-    const uint32_t sP = sbase + L::oP;
     auto issue_qk = [&](int j) -> bool {
       const int st = j & 1;
       if (!__all_sync(0xffffffffu, mbar_wait_to(&k_full[st], (j >> 1) & 1, 11, j))) return false;
@@ -289,8 +286,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const uint32_t sV = sbase + L::oV + st * L::kKV;
       if (elected) {
 #pragma unroll
-        for (int kk = 0; kk < BC / 16; ++kk)
-          umma_f16(tO_u, desc_kmajor_1(sP, kk), desc_mnmajor(sV, BC, kk), idesc_o, (j | kk) != 0);
+        for (int kk = 0; kk < BC / 16; ++kk)   // A = P(j), bf16-packed over the first 32 columns of S(j) in TMEM
+          umma_f16_ts(tO_u, tS_u + (j & 1) * BC + kk * 8, desc_mnmajor(sV, BC, kk), idesc_o, (j | kk) != 0);
         if (MC > 1) umma_commit_mc(&v_empty[st], 3);
         else umma_commit(&v_empty[st]);
         umma_commit(o_done);
@@ -304,7 +301,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int qpos = q0 + row;
     const float sc = p.scale * kLog2e;
     float m_run = -INFINITY, l_run = 0.f;
-    uint8_t* sP = smem + L::oP;
     for (int j = 0; j < nblk; ++j) {
       if (!mbar_wait_to(&s_full[j & 1], (j >> 1) & 1, 24)) goto done;
       tc_fence_after();
@@ -360,10 +356,22 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       m_run = m_new;
       l_run += rs;
-      store_row_sw128(sP, row, s);
-      fence_async_smem();
+      // P(j) goes back into TMEM over S(j).  S(j+1) shares the 128-column group: a tcgen05.st into a group the tensor
+      // core is still accumulating into was measured to corrupt data, so QK(j+1) must have landed first (it was
+      // issued a whole iteration ago; this wait is normally already satisfied).
+      if (j + 1 < nblk) {
+        if (!mbar_wait_to(&s_full[(j + 1) & 1], ((j + 1) >> 1) & 1, 27)) goto done;
+      }
+      {
+        uint32_t pk[32];
+#pragma unroll
+        for (int c = 0; c < 32; ++c) pk[c] = pack_bf16(s[2 * c], s[2 * c + 1]);
+        tmem_st_32x32(tS + (j & 1) * BC + lane_off, pk);
+        tmem_st_wait();
+      }
       tc_fence_before();
-      mbar_arrive(p_full);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full);
     }
     if (!mbar_wait_to(o_done, (nblk - 1) & 1, 26)) goto done;
     tc_fence_after();

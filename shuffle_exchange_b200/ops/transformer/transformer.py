@@ -111,7 +111,7 @@ def _attention(layer: "DeepSpeedTransformerLayer", qkv: torch.Tensor, mask: Opti
 
 def _attn_block(layer, x, mask):
     cfg = layer.config
-    h = F.layer_norm(x, layer.attn_nw, layer.attn_nb, cfg.layer_norm_eps) if cfg.pre_layer_norm else x
+    h = F.layer_norm(x, layer.attn_nw, layer.attn_nb, cfg.layer_norm_eps)[0] if cfg.pre_layer_norm else x
     qkv = F.linear(h, layer.attn_qkvw, layer.attn_qkvb)
     if cfg.attn_dropout_checkpoint and torch.is_grad_enabled() and x.requires_grad:
         ctx = _ckpt(lambda t: _attention(layer, t, mask), qkv, use_reentrant=False, preserve_rng_state=True)
@@ -120,7 +120,7 @@ def _attn_block(layer, x, mask):
     out = F.linear(ctx, layer.attn_ow)
     out = bias_dropout_residual(out, layer.attn_ob, x, cfg.hidden_dropout_ratio, layer.training)
     if not cfg.pre_layer_norm:
-        out = F.layer_norm(out, layer.attn_nw, layer.attn_nb, cfg.layer_norm_eps)
+        out = F.layer_norm(out, layer.attn_nw, layer.attn_nb, cfg.layer_norm_eps)[0]
     return out
 
 
@@ -130,7 +130,7 @@ def _ffn_in(layer, h):
 
 def _ffn_block(layer, x):
     cfg = layer.config
-    h = F.layer_norm(x, layer.norm_w, layer.norm_b, cfg.layer_norm_eps) if cfg.pre_layer_norm else x
+    h = F.layer_norm(x, layer.norm_w, layer.norm_b, cfg.layer_norm_eps)[0] if cfg.pre_layer_norm else x
     if cfg.gelu_checkpoint and torch.is_grad_enabled() and x.requires_grad:
         inter = _ckpt(lambda t: _ffn_in(layer, t), h, use_reentrant=False)
     else:
@@ -138,7 +138,7 @@ def _ffn_block(layer, x):
     out = F.linear(inter, layer.output_w)
     out = bias_dropout_residual(out, layer.output_b, x, cfg.hidden_dropout_ratio, layer.training)
     if not cfg.pre_layer_norm:
-        out = F.layer_norm(out, layer.norm_w, layer.norm_b, cfg.layer_norm_eps)
+        out = F.layer_norm(out, layer.norm_w, layer.norm_b, cfg.layer_norm_eps)[0]
     return out
 
 

@@ -14,8 +14,24 @@ def main():
     n = int(sys.argv[2]) if len(sys.argv) > 2 else 25
     out = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
-    print(rows[0][1][:120])
-    hdr, data = rows[1], rows[2:]
+    # one table per kernel: a short title row, a header row, then the SASS lines
+    tables, i = [], 0
+    while i < len(rows):
+        if len(rows[i]) <= 3 and i + 1 < len(rows) and "Source" in rows[i + 1]:
+            j = i + 2
+            while j < len(rows) and not (len(rows[j]) <= 3 and j + 1 < len(rows) and "Source" in rows[j + 1]):
+                j += 1
+            tables.append((rows[i], rows[i + 1], [r for r in rows[i + 2:j] if len(r) == len(rows[i + 1])]))
+            i = j
+        else:
+            i += 1
+    for title, hdr, data in tables:
+        report(title, hdr, data, n)
+
+
+def report(title, hdr, data, n):
+    print("=" * 100)
+    print(title[1][:120] if len(title) > 1 else title)
     isrc, ins, iex = hdr.index("Source"), hdr.index("# Samples"), hdr.index("Instructions Executed")
     stalls = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
     tot = sum(int(r[ins] or 0) for r in data)
