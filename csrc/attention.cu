@@ -428,7 +428,7 @@ struct DqSmem {
   static constexpr int oK = oDO + kQ;
   static constexpr int oV = oK + kStages * kKV;
   static constexpr int oBar = oV + kStages * kKV;
-  static constexpr int kTotal = oBar + 128 + 1024;
+  static constexpr int kTotal = oBar + 256 + 1024;
 };
 
 template <int D, int MC>   // MC = 2: K/V ring filled by multicast from a 2-CTA cluster over a q-head pair (see forward)
@@ -450,7 +450,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   uint64_t* ds_full = bars + 11;  // dS written (256 arrivals)
   uint64_t* dq_done = bars + 12;  // dQ MMA of block j finished
   uint64_t* s_free = bars + 13;   // [2] row warps copied S/dP of buffer b out of TMEM (one arrive per warp)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+  uint64_t* qa_full = bars + 15;  // Q / dO copied into TMEM as A operands (one arrival per row warp)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = gridDim.z - 1 - blockIdx.z;   // heaviest causal tiles first across all heads
@@ -467,6 +468,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       mbar_init(&s_full[0], 1);
       mbar_init(&s_full[1], 1);
       mbar_init(ds_full, 8);   // one arrival per row warp
+      mbar_init(qa_full, 8);
       mbar_init(dq_done, 1);
       mbar_init(&s_free[0], 8);
       mbar_init(&s_free[1], 8);
@@ -481,7 +483,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   tc_fence_after();
   const uint32_t crank = (MC > 1) ? cluster_ctarank() : 0;
   const uint32_t tmem = *tmem_slot;
-  // buffer b: S at 128*b, dP at 128*b + 64 ; dQ at 256
+  // buffer b: S at 128*b, dP at 128*b + 64 ; dQ at 256 ; Q as A operand at 384, dO at 448 (bf16 pairs, D/2 columns)
   const uint32_t tDQ = tmem + 256;
 
   if (warp == 0) {
@@ -522,7 +524,6 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const uint32_t tDQ_u = tm_u + 256;
     const uint32_t idesc_s = make_idesc(BQ, BC, 1, 1, 0, 0);
     const uint32_t idesc_dq = make_idesc(BQ, D, 1, 1, 0, 1);
-    const uint32_t sQ = sbase + L::oQ, sDO = sbase + L::oDO;
     auto issue_sdp = [&](int j) -> bool {
       const int st = j % NS;
       if (!__all_sync(0xffffffffu, mbar_wait_to(&kv_full[st], (j / NS) & 1, 29, j))) return false;
@@ -533,16 +534,20 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       if (elected) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
-          umma_f16(tS, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, BC, kk), idesc_s, kk != 0);
+          umma_f16_ts(tS, tm_u + 384 + kk * 8, desc_kmajor_d(sK, BC, kk), idesc_s, kk != 0);
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
-          umma_f16(tDP, desc_kmajor_d(sDO, BQ, kk), desc_kmajor_d(sV, BC, kk), idesc_s, kk != 0);
+          umma_f16_ts(tDP, tm_u + 448 + kk * 8, desc_kmajor_d(sV, BC, kk), idesc_s, kk != 0);
         umma_commit(&s_full[j & 1]);
       }
       __syncwarp();
       return true;
     };
-    if (!__all_sync(0xffffffffu, mbar_wait_to(q_full, 0, 28))) goto done;
+    // Q and dO are the A operands of every S / dP MMA of this CTA: the row warps park them in TMEM once, so those
+    // MMAs read only the K / V tile from shared memory (operand fetch from smem, not the tensor pipe, was the
+    // measured limiter: ~70 B/clk/SM)
+    if (!__all_sync(0xffffffffu, mbar_wait_to(qa_full, 0, 28))) goto done;
+    tc_fence_after();
     if (!issue_sdp(0)) goto done;
     for (int j = 0; j < nblk; ++j) {
       const int st = j % NS;
@@ -572,6 +577,26 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const long long stat_idx = ((long long)b * p.Hq + h) * p.S + min(qpos, p.S - 1);
     const float lse2 = p.lse[stat_idx] * kLog2e;
     const float dlt = p.delta[stat_idx];
+    {
+      // half 0 copies its Q rows, half 1 its dO rows: undo the 128B swizzle, 16 bytes = 4 packed columns at a time
+      if (!mbar_wait_to(q_full, 0, 43)) goto done;
+      const uint8_t* tile = smem + (half == 0 ? L::oQ : L::oDO) + row * 128;
+      const uint32_t tA = tmem + 384 + half * 64 + lane_off;
+#pragma unroll
+      for (int hh = 0; hh < NH; ++hh) {
+        uint32_t w[32];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const uint4 v = *reinterpret_cast<const uint4*>(tile + hh * (BQ * 128) + ((c ^ (row & 7)) << 4));
+          w[c * 4 + 0] = v.x; w[c * 4 + 1] = v.y; w[c * 4 + 2] = v.z; w[c * 4 + 3] = v.w;
+        }
+        tmem_st_32x32(tA + hh * 32, w);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(qa_full);
+    }
     for (int j = 0; j < nblk; ++j) {
       if (!mbar_wait_to(&s_full[j & 1], (j >> 1) & 1, 31, j)) goto done;
       tc_fence_after();
