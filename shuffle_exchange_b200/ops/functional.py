@@ -551,6 +551,68 @@ class _FlashAttn(torch.autograd.Function):
         return dq, dk, dv, None, None
 
 
+def attention_fwd_lse(q, k, v, causal: bool, scale: float):
+    """Raw (non-autograd) attention forward returning ``(out [B,S,Hq,D], lse [B,Hq,S] natural log)`` — the building
+    block of chunked / ring schedules that merge partial results themselves (``sequence/fpdt_layer.py``)."""
+    B, S, Hq, D = q.shape
+    if q.is_cuda:
+        q, k, v = (t if _attn_layout_ok(t) else t.contiguous() for t in (q, k, v))
+        out = torch.empty((B, S, Hq, D), dtype=q.dtype, device=q.device)
+        lse = torch.empty((B, Hq, S), dtype=torch.float32, device=q.device)
+        _n.call("sxb_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), lse.data_ptr(),
+                B, S, Hq, k.shape[2], D, q.stride(1), k.stride(1), v.stride(1), out.stride(1), int(causal),
+                float(scale), _n.stream_ptr())
+        return out, lse
+    Hk = k.shape[2]
+    qf = q.float().permute(0, 2, 1, 3)
+    kf = k.float().permute(0, 2, 1, 3).repeat_interleave(Hq // Hk, dim=1)
+    vf = v.float().permute(0, 2, 1, 3).repeat_interleave(Hq // Hk, dim=1)
+    s = qf @ kf.transpose(-1, -2) * scale
+    if causal:
+        s = s.masked_fill(~torch.ones(S, k.shape[1], dtype=torch.bool).tril(), float("-inf"))
+    lse = torch.logsumexp(s, dim=-1)
+    out = (torch.softmax(s, -1) @ vf).permute(0, 2, 1, 3).to(q.dtype)
+    return out, lse
+
+
+def attention_bwd_raw(q, k, v, out, dout, lse, causal: bool, scale: float):
+    """Raw attention backward for one (q-block, kv-block) pair given the FINAL ``out``/``lse`` of the q rows (which may
+    have been merged over many kv blocks): returns this pair's ``(dq, dk, dv)`` contributions."""
+    B, S, Hq, D = q.shape
+    Hk = k.shape[2]
+    if q.is_cuda:
+        q, k, v, out, dout = (t if _attn_layout_ok(t) else t.contiguous() for t in (q, k, v, out, dout))
+        dq = torch.empty_like(q)
+        dk = torch.empty_like(k)
+        dv = torch.empty_like(v)
+        delta = torch.empty((B, Hq, S), dtype=torch.float32, device=q.device)
+        _n.call("sxb_attn_bwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), dout.data_ptr(),
+                lse.data_ptr(), delta.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(),
+                B, S, Hq, Hk, D, q.stride(1), k.stride(1), v.stride(1), out.stride(1), dout.stride(1),
+                dq.stride(1), dk.stride(1), dv.stride(1), int(causal), float(scale), _n.stream_ptr())
+        return dq, dk, dv
+    g = Hq // Hk
+    qf = q.float().permute(0, 2, 1, 3)
+    kf = k.float().permute(0, 2, 1, 3).repeat_interleave(g, dim=1)
+    vf = v.float().permute(0, 2, 1, 3).repeat_interleave(g, dim=1)
+    of = out.float().permute(0, 2, 1, 3)
+    dof = dout.float().permute(0, 2, 1, 3)
+    s = qf @ kf.transpose(-1, -2) * scale
+    if causal:
+        s = s.masked_fill(~torch.ones(S, k.shape[1], dtype=torch.bool).tril(), float("-inf"))
+    p = torch.exp(s - lse.float()[..., None])
+    dv_ = p.transpose(-1, -2) @ dof
+    dp = dof @ vf.transpose(-1, -2)
+    delta = (dof * of).sum(-1, keepdim=True)
+    ds = p * (dp - delta) * scale
+    dq_ = ds @ kf
+    dk_ = ds.transpose(-1, -2) @ qf
+    dk_ = dk_.view(B, Hk, g, k.shape[1], D).sum(2)
+    dv_ = dv_.view(B, Hk, g, k.shape[1], D).sum(2)
+    return (dq_.permute(0, 2, 1, 3).to(q.dtype), dk_.permute(0, 2, 1, 3).to(k.dtype),
+            dv_.permute(0, 2, 1, 3).to(v.dtype))
+
+
 def _attn_layout_ok(t):
     B, S, H, D = t.shape
     return t.stride(3) == 1 and t.stride(2) == D and t.stride(0) == S * t.stride(1)

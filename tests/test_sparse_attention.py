@@ -173,7 +173,7 @@ def _ref_layer(layer, x, mask):
     if not c.pre_layer_norm:
         a = ln(a, layer.attn_nw, layer.attn_nb)
     h2 = ln(a, layer.norm_w, layer.norm_b) if c.pre_layer_norm else a
-    inter = torch.nn.functional.gelu(h2 @ layer.inter_w.t() + layer.inter_b)
+    inter = torch.nn.functional.gelu(h2 @ layer.inter_w.t() + layer.inter_b, approximate="tanh")
     o = inter @ layer.output_w.t() + layer.output_b + a
     if not c.pre_layer_norm:
         o = ln(o, layer.norm_w, layer.norm_b)
