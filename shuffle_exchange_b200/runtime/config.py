@@ -210,6 +210,8 @@ class CompileConfig(DeepSpeedConfigModel):
     sync_after_reduce: bool = False
     sync_before_allgather: bool = False
     sync_after_allgather: bool = False
+    keep_int_input_tensors: bool = True
+    keep_all_input_tensors: bool = False
 
 
 class HybridEngineConfig(DeepSpeedConfigModel):

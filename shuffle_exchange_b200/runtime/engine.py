@@ -582,6 +582,10 @@ class DeepSpeedEngine(nn.Module):
                 kwargs.update({"curriculum_seqlen": self.curriculum_scheduler_legacy.get_current_difficulty()})
         if self.training_dataloader is None:
             self.tput_timer.start()
+        if getattr(self, "launch_compile_passes", None) is not None and self.module.training:
+            self.launch_compile_passes(self.global_steps)
+            for hook in self.__dict__.get("_compile_hooks", {}).get("pre_forward", ()):
+                hook()
         self._start_timers(self.engine_timers.forward_timers)
         if hasattr(self.optimizer, "set_gradient_accumulation_boundary"):
             self.optimizer.set_gradient_accumulation_boundary(self.is_gradient_accumulation_boundary())
@@ -692,6 +696,8 @@ class DeepSpeedEngine(nn.Module):
                 self.block_eigenvalue = self.eigenvalue.compute_eigenvalue(self.module, self.device)
             if self.progressive_layer_drop:
                 self.progressive_layer_drop.update_state(self.global_steps)
+            for hook in self.__dict__.get("_compile_hooks", {}).get("pre_step", ()):
+                hook()
             self._take_model_step(lr_kwargs)
             report = True
             if getattr(self, "_decoupled_commit_pending", False):
@@ -993,10 +999,28 @@ class DeepSpeedEngine(nn.Module):
             self.optimizer.empty_partition_cache()
             get_accelerator().empty_cache()
 
+    def is_deepcompile_enabled(self):
+        return bool(self._config.compile_config.deepcompile)
+
     def compile(self, backend=None, compile_kwargs=None, schedule=None):
-        """``torch.compile`` is deliberately not the hot path on B200 (hand-written kernels + CUDA
-        graphs are); kept for API compatibility — compiles the wrapped module's forward."""
-        self.module.compile(backend=backend or "inductor", **(compile_kwargs or {}))
+        """With ``compile.deepcompile`` the schedule compiler (``shuffle_exchange_b200.compile``) takes over gather /
+        release / reduce scheduling and offload decisions from the ZeRO unit trace (reference ``engine.py:3970-4040``
+        wires DeepCompile into ``torch.compile`` here).  Without it this only marks the engine compiled: a tracing
+        compiler is deliberately not the hot path on B200 (hand-written kernels + CUDA graphs are)."""
+        compile_kwargs = compile_kwargs or {}
+        if self.is_deepcompile_enabled():
+            stage = self.zero_optimization_stage()
+            cfg = self._config.compile_config
+            if stage == 3:
+                from ..compile.init_z3 import init_z3
+                self._compile_backend = init_z3(self, backend, cfg, compile_kwargs, schedule)
+            elif stage in (1, 2):
+                from ..compile.init_z1 import init_z1
+                self._compile_backend = init_z1(self, backend, cfg, compile_kwargs, schedule, use_z2=(stage == 2))
+            else:
+                logger.warning("deepcompile needs ZeRO stage 1-3; ignoring")
+            from ..compile.backend import launch_compile_passes
+            self.launch_compile_passes = lambda step: launch_compile_passes(step, self)
         self._is_compiled = True
 
     @property

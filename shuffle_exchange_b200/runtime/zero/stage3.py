@@ -336,6 +336,17 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         """Issue gathers for the units that follow ``u`` in the recorded order."""
         if not self._trace_complete or self.world == 1:
             return
+        table = getattr(self, "_compiled_prefetch", None)
+        if table is not None and (u.index, forward) in table:
+            # schedule produced by the schedule compiler (compile/backend.py: apply_plan): explicit gather list
+            for nxt in table[(u.index, forward)]:
+                nu = self.units[nxt]
+                if nu.persistent or nu.available or nu.fetch_event is not None:
+                    continue
+                if self._live_numel + nu.numel > self.max_live_parameters:
+                    break
+                self._gather_unit(nu, async_on_side_stream=True)
+            return
         order = self._trace if forward else list(reversed(self._trace))
         try:
             pos = order.index(u.index)
@@ -540,6 +551,14 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
 
     def empty_partition_cache(self):
         self.release_all()
+
+    def make_persistent(self, u: Unit):
+        """Promote a unit to persistent at run time (schedule compiler's selective gather): gather it once, then it
+        is never released and its gathered copy is refreshed after every step like the build-time persistent units."""
+        if u.persistent:
+            return
+        self._fetch(u)
+        u.persistent = True
 
     def destroy(self):
         for h in self._hooks:
