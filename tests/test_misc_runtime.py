@@ -1,0 +1,137 @@
+"""state_dict_factory (Megatron TP merge/split), MoQ quantizer schedule, weight quantizer, autocast / compiler helpers."""
+import os
+
+import pytest
+import torch
+
+
+def _megatron_sd(h=16):
+    torch.manual_seed(0)
+    pre = "transformer.layers.0."
+    return {pre + "attention.query_key_value.weight": torch.randn(3 * h, h),
+            pre + "attention.query_key_value.bias": torch.randn(3 * h),
+            pre + "attention.dense.weight": torch.randn(h, h), pre + "attention.dense.bias": torch.randn(h),
+            pre + "mlp.dense_h_to_4h.weight": torch.randn(4 * h, h), pre + "mlp.dense_h_to_4h.bias": torch.randn(4 * h),
+            pre + "mlp.dense_4h_to_h.weight": torch.randn(h, 4 * h), pre + "mlp.dense_4h_to_h.bias": torch.randn(h),
+            "word_embeddings.weight": torch.randn(32, h)}
+
+
+@pytest.mark.parametrize("version", [0, 2.0])
+def test_sd_loader_split_then_merge_roundtrip(tmp_path, version):
+    from shuffle_exchange_b200.runtime.state_dict_factory import SDLoaderFactory
+    full = _megatron_sd()
+    p = str(tmp_path / "full.pt")
+    torch.save({"module": full, "checkpoint_version": version}, p)
+    loader = SDLoaderFactory.get_sd_loader([p], None, "Megatron", version=version)
+    files = []
+    for r in range(2):
+        path, sd, (scales, merge_count) = loader.load(2, r)
+        assert path == p and scales is None and merge_count == 1
+        assert sd["module"]["transformer.layers.0.attention.dense.weight"].shape == (16, 8)
+        assert sd["module"]["transformer.layers.0.attention.query_key_value.weight"].shape == (24, 16)
+        assert sd["module"]["transformer.layers.0.attention.dense.bias"].shape == (16,)      # replicated
+        f = str(tmp_path / f"mp_rank_0{r}.pt")
+        torch.save({"module": sd["module"], "checkpoint_version": version, "mp_world_size": 2}, f)
+        files.append(f)
+    merged_loader = SDLoaderFactory.get_sd_loader_json({"type": "Megatron", "checkpoints": files,
+                                                        "version": version}, None)
+    _, sd, (_, merge_count) = merged_loader.load(1, 0)
+    assert merge_count == 2
+    for k, v in full.items():
+        assert torch.equal(sd["module"][k], v), k
+    # same degree: own file, optionally quantised
+    _, sd0, _ = merged_loader.load(2, 0)
+    assert torch.equal(sd0["module"]["word_embeddings.weight"], full["word_embeddings.weight"][:16])
+    _, sdq, (scales, _) = merged_loader.load(1, 0, quantize=True, quantize_groups=4)
+    assert sdq["module"]["transformer.layers.0.mlp.dense_4h_to_h.weight"].dtype == torch.int8
+    assert scales.shape[0] == 1 and scales.shape[1] == 4
+    with pytest.raises(AssertionError):
+        SDLoaderFactory.get_sd_loader(files, None, "Unknown")
+    assert SDLoaderFactory.get_sd_loader_json({"type": "bloom", "checkpoints": [], "version": 1}, None)["type"] == "bloom"
+
+
+def test_weight_quantization_error_bound_and_model_quantize():
+    from shuffle_exchange_b200.runtime.weight_quantizer import WeightQuantization
+    torch.manual_seed(0)
+    wq = WeightQuantization(mlp_extra_grouping=True, mp_size=1)
+    w = torch.randn(64, 16)
+    q, s = wq.quantize_data(w, 8, 4)
+    assert q.dtype == torch.int8 and s.shape == (4, 1)
+    deq = (q.float().reshape(4, -1) / s).reshape(w.shape)
+    assert (deq - w).abs().max() <= (1.0 / s.min()).item() + 1e-6      # the positive extreme clamps 128 -> 127
+    assert wq.is_mlp(torch.empty(64, 16)) and wq.is_qkv(torch.empty(48, 16)) and not wq.is_qkv(torch.empty(16, 16))
+
+    class BertLayer(torch.nn.Module):            # matched by name through the built-in policy list
+        def __init__(self):
+            super().__init__()
+            self.qkv = torch.nn.Linear(16, 48)
+            self.out = torch.nn.Linear(16, 16)
+            self.up = torch.nn.Linear(16, 64)
+            self.down = torch.nn.Linear(64, 16)
+
+    model = torch.nn.Sequential(BertLayer(), BertLayer())
+    _, scales = WeightQuantization().model_quantize(model, None, 8, 2)
+    assert scales.shape[0] == 2 and scales.shape[1] == 4
+    assert float(model[0].qkv.weight.abs().max()) <= 128 and float(model[0].qkv.weight.frac().abs().max()) == 0.0
+
+
+def test_moq_schedule_reduces_precision_to_target():
+    from shuffle_exchange_b200.runtime.quantize import Quantizer
+    torch.manual_seed(0)
+    q = Quantizer(q_groups=4, q_type="symmetric", q_rounding="nearest")
+    w = torch.nn.Parameter(torch.randn(8, 16))
+    w.start_bits, w.target_bits, w.q_period = 8, 4, 2
+    seen = set()
+    for _ in range(40):
+        q.quantize([[w]], overflow=False, eigenvalue_enabled=False)
+        seen.add(w.start_bits)
+    assert w.start_bits == 4 and seen == {8, 7, 6, 5, 4}
+    assert w.data.reshape(4, -1)[0].unique().numel() <= 16
+    q.quantize([[w]], overflow=True, eigenvalue_enabled=False)      # skipped on overflow
+    assert q.qsteps == 40
+    t = Quantizer(q_groups=1, q_type="symmetric", q_rounding="nearest")
+    x = torch.randn(4, 8)
+    assert t.quantize_binary(x).abs().unique().numel() == 1
+    assert t.quantize_tenary(x).unique().numel() <= 3
+    mixed = Quantizer(q_groups=1, q_mixed_fp16=True, q_change_ratio=0.5, q_type="asymmetric", q_rounding="nearest")
+    mixed.update_fp16_ratio()
+    mixed.update_fp16_ratio()
+    mixed.update_fp16_ratio()
+    assert mixed.quantize_real_ratio == 0.0
+
+
+def test_autocast_and_compiler_helpers():
+    from shuffle_exchange_b200.runtime import compiler, torch_autocast as ta
+
+    class Eng:
+        module = torch.nn.Sequential(torch.nn.Linear(4, 4), torch.nn.LayerNorm(4))
+        communication_data_type = torch.float32
+        def fp16_enabled(self): return False
+        def bfloat16_enabled(self): return False
+        def torch_autocast_enabled(self): return True
+
+    eng = Eng()
+    ta.init_autocast_params(eng, torch.bfloat16, None)
+    assert ta.is_autocast_initialized()
+    lin, ln = eng.module[0], eng.module[1]
+    assert ta.get_autocast_dtype(lin.weight) == torch.bfloat16 and not ta.has_autocast_dtype(ln.weight)
+    assert ta.get_all_autocast_dtypes(eng.module.parameters()) == {torch.bfloat16, torch.float32}
+    assert ta.sort_dtypes([torch.float32, torch.bfloat16]) == [torch.bfloat16, torch.float32]
+    with pytest.raises(ValueError):
+        ta.init_autocast_params(eng, torch.bfloat16, ["not.a.module.Class"])
+    with torch.autocast("cpu", dtype=torch.bfloat16):
+        ta.validate_nested_autocast(eng)            # allowed (warns once)
+        eng.torch_autocast_enabled = lambda: False
+        with pytest.raises(AssertionError):
+            ta.validate_nested_autocast(eng)
+
+    @compiler.enable
+    def f(x):
+        return x + 1
+
+    @compiler.enable("99.0.0")
+    def g(x):
+        return x + 2
+
+    assert f(1) == 2 and g(1) == 3 and compiler.is_compile_supported() and not compiler.is_compiling()
+    assert compiler.disable(f)(2) == 3
