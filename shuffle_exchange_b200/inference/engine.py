@@ -63,6 +63,12 @@ class InferenceEngine(nn.Module):
             self._apply_injection_policy(config)
         if config.checkpoint is not None:
             self._load_checkpoint(config.checkpoint)
+        post_q = getattr(getattr(config.quant, "weight", None), "post_init_quant", None)
+        if post_q:
+            # group-wise INT4/INT8 weights, converted layer by layer before the move to the device
+            from .quantization import _init_group_wise_weight_quantization
+            self.module = _init_group_wise_weight_quantization(self.module,
+                                                               {"weight_quantization": {"post_init_quant": post_q}})
         dev = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
         if not config.keep_module_on_host:
             self.module.to(dev)

@@ -135,3 +135,43 @@ def test_autocast_and_compiler_helpers():
 
     assert f(1) == 2 and g(1) == 3 and compiler.is_compile_supported() and not compiler.is_compiling()
     assert compiler.disable(f)(2) == 3
+
+
+def test_inference_post_init_weight_quantization():
+    from torch import nn
+    from shuffle_exchange_b200.inference.quantization import (DeQuantizer, QuantizedEmbedding, QuantizedLinear,
+                                                              Quantizer, _init_group_wise_weight_quantization)
+    torch.manual_seed(0)
+
+    class M(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.embed = nn.Embedding(64, 32)
+            self.fc1 = nn.Linear(32, 64)
+            self.fc2 = nn.Linear(64, 32)
+            self.head = nn.Linear(32, 64, bias=False)
+
+        def forward(self, ids):
+            return self.head(self.fc2(torch.relu(self.fc1(self.embed(ids)))))
+
+    m = M().to(torch.bfloat16)
+    ids = torch.randint(0, 64, (2, 5))
+    ref = m(ids).float()
+    q8 = {"num_bits": 8, "group_size": 16, "group_dim": 1, "symmetric": False}
+    q4 = {"num_bits": 4, "group_size": 16, "group_dim": 1, "symmetric": False}
+    m = _init_group_wise_weight_quantization(m, {"weight_quantization": {"post_init_quant": {"fc": q8, "embed": q4}}})
+    assert isinstance(m.fc1, QuantizedLinear) and isinstance(m.embed, QuantizedEmbedding)
+    assert type(m.head) is nn.Linear                                  # no key matched
+    assert m.fc1.weight.dtype == torch.uint8 and m.embed.weight.numel() < 64 * 32
+    assert (m(ids).float() - ref).abs().max() < 0.1
+    w = torch.randn(4, 16)
+    qz = Quantizer({"num_bits": 4, "group_size": 8, "group_dim": 1, "symmetric": False})
+    codes, scale, mn = qz.quantize(w)
+    assert codes.shape == (4, 8) and codes.dtype == torch.uint8
+    back = DeQuantizer(qz.config, torch.float32).dequantize(codes, scale, mn)
+    step = (w.reshape(4, 2, 8).amax(-1) - w.reshape(4, 2, 8).amin(-1)) / 15
+    assert (back - w).abs().max() <= step.max() / 2 + 1e-5
+    with pytest.raises(AssertionError):
+        Quantizer({"num_bits": 3, "group_size": 8, "group_dim": 1, "symmetric": False})
+    with pytest.raises(AssertionError):
+        _init_group_wise_weight_quantization(M().half(), {"weight_quantization": {"post_init_quant": {"fc": q8, "c1": q8}}})
