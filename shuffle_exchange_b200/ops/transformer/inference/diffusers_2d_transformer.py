@@ -1,0 +1,7 @@
+"""Config of the diffusers 2-D transformer wrapper (reference ``diffusers_2d_transformer.py``)."""
+
+
+class Diffusers2DTransformerConfig:
+
+    def __init__(self, int8_quantization=False):
+        self.int8_quantization = int8_quantization
