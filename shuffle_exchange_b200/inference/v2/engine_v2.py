@@ -16,15 +16,7 @@ from .ragged.manager import DSStateManager
 from .ragged.ragged_wrapper import RaggedBatchWrapper
 
 
-class SchedulingResult:
-    Success, EngineSequenceLimitExceeded, BatchSequenceLimitExceeded, BatchTokenLimitExceeded, KVCacheLimitExceeded, \
-        SequenceTokenLimitExceeded = range(6)
-
-
-class SchedulingError(RuntimeError):
-    def __init__(self, result: int) -> None:
-        self.result = result
-        super().__init__(f"Batch scheduling failed with result {result}")
+from .scheduling_utils import SchedulingError, SchedulingResult  # noqa: E402,F401
 
 
 class InferenceEngineV2:
