@@ -1,47 +1,77 @@
 """Engine construction helpers (reference: ``inference/v2/engine_factory.py:33-145``)."""
 from __future__ import annotations
 
+import logging
+import os
+import pickle
+
 import torch
 
+from .checkpoint import HuggingFaceCheckpointEngine, InMemoryModelEngine
 from .config_v2 import RaggedInferenceEngineConfig
 from .engine_v2 import InferenceEngineV2
-
-_SUPPORTED = ("llama", "mistral", "mixtral", "qwen2", "qwen2_moe", "phi3")
+from .logging import inference_logger
+from .model_implementations.policies import POLICIES
 
 
 def build_engine_from_model(causal_lm, engine_config: RaggedInferenceEngineConfig = None, moe_layers=None, top_k: int = 2,
                             device=None) -> InferenceEngineV2:
+    """Serve one of the framework's own training models (``models.llama`` / ``models.mixtral`` layouts) directly."""
     from .model_implementations.llama_v2 import RaggedLlamaModel
     return InferenceEngineV2(lambda sm: RaggedLlamaModel(causal_lm, sm, moe_layers=moe_layers, top_k=top_k),
                              engine_config, device=device)
 
 
-def build_hf_engine(path: str, engine_config: RaggedInferenceEngineConfig = None, debug_level: int = 0) -> InferenceEngineV2:
-    """Load a HuggingFace checkpoint directory of a supported architecture and wrap it in an engine."""
-    import json
-    import os
-    from ...models.llama import LlamaConfig, LlamaForCausalLM
-    with open(os.path.join(path, "config.json")) as f:
-        hf = json.load(f)
-    mt = hf.get("model_type", "").lower()
-    if mt not in _SUPPORTED:
-        raise ValueError(f"Unsupported model type {mt}; supported: {_SUPPORTED}")
-    if mt in ("mixtral", "qwen2_moe"):
-        raise NotImplementedError("MoE checkpoints: build the model with models.mixtral and use build_engine_from_model")
-    cfg = LlamaConfig(vocab_size=hf["vocab_size"], hidden_size=hf["hidden_size"], intermediate_size=hf["intermediate_size"],
-                      num_hidden_layers=hf["num_hidden_layers"], num_attention_heads=hf["num_attention_heads"],
-                      num_key_value_heads=hf.get("num_key_value_heads", hf["num_attention_heads"]),
-                      max_position_embeddings=hf.get("max_position_embeddings", 8192),
-                      rope_theta=hf.get("rope_theta", 10000.0), rms_norm_eps=hf.get("rms_norm_eps", 1e-5),
-                      tie_word_embeddings=hf.get("tie_word_embeddings", False), activation_checkpointing=False)
-    dev = "cuda" if torch.cuda.is_available() else "cpu"
-    model = LlamaForCausalLM(cfg, device=dev, dtype=torch.bfloat16)
-    sd = {}
-    for fn in sorted(os.listdir(path)):
-        if fn.endswith(".safetensors"):
-            from safetensors.torch import load_file
-            sd.update(load_file(os.path.join(path, fn)))
-        elif fn.endswith(".bin") and fn.startswith("pytorch_model"):
-            sd.update(torch.load(os.path.join(path, fn), map_location="cpu", weights_only=True))
-    model.load_hf_state_dict(sd)
-    return build_engine_from_model(model.eval(), engine_config)
+def _policy_for(model_config, checkpoint_engine):
+    mt = getattr(model_config, "model_type", "").lower()
+    if mt not in POLICIES:
+        raise ValueError(f"Unsupported model type {mt}; supported: {sorted(POLICIES)}")
+    if mt == "opt" and not getattr(model_config, "do_layer_norm_before", True):
+        raise ValueError("Detected OPT-350m model. This model is not currently supported.")
+    return POLICIES[mt](model_config, checkpoint_engine=checkpoint_engine)
+
+
+def build_engine_from_hf_model(hf_model: torch.nn.Module, engine_config: RaggedInferenceEngineConfig = None,
+                               device=None) -> InferenceEngineV2:
+    """Wrap an instantiated HuggingFace ``*ForCausalLM`` (parameters are read through ``InMemoryModelEngine``)."""
+    engine_config = engine_config or RaggedInferenceEngineConfig()
+    ce = InMemoryModelEngine(hf_model)
+    policy = _policy_for(hf_model.config, ce)
+    policy._engine_config = engine_config
+    first = next(iter(hf_model.parameters()), None)
+    if first is not None and first.is_floating_point():
+        policy.dtype_override = first.dtype
+    return InferenceEngineV2(policy, engine_config, device=device)
+
+
+def build_engine_from_ds_checkpoint(path: str, engine_config: RaggedInferenceEngineConfig,
+                                    debug_level: int = logging.INFO) -> InferenceEngineV2:
+    """Directory written by ``InferenceEngineV2.serialize``: ``ds_model_config.pkl`` + ``params_rank_0.pt``."""
+    inference_logger(level=debug_level)
+    with open(os.path.join(path, "ds_model_config.pkl"), "rb") as f:
+        model_config = pickle.load(f)
+
+    class _Saved(InMemoryModelEngine):
+        def __init__(self, file):
+            self.file, self.model_config = file, model_config
+
+        def parameters(self):
+            yield from torch.load(self.file, map_location="cpu", weights_only=True).items()
+
+    policy = _policy_for(model_config, _Saved(os.path.join(path, "params_rank_0.pt")))
+    policy._engine_config = engine_config
+    return InferenceEngineV2(policy, engine_config)
+
+
+def build_hf_engine(path: str, engine_config: RaggedInferenceEngineConfig = None,
+                    debug_level: int = logging.INFO) -> InferenceEngineV2:
+    """Engine for a local HuggingFace checkpoint directory (or a serialized v2 checkpoint) of a supported
+    architecture: llama, mistral, mixtral, falcon, opt, phi, phi3, qwen, qwen2, qwen2_moe."""
+    engine_config = engine_config or RaggedInferenceEngineConfig()
+    if os.path.exists(os.path.join(path, "ds_model_config.pkl")):
+        return build_engine_from_ds_checkpoint(path, engine_config, debug_level=debug_level)
+    inference_logger(level=debug_level)
+    ce = HuggingFaceCheckpointEngine(path)
+    policy = _policy_for(ce.model_config, ce)
+    policy._engine_config = engine_config
+    return InferenceEngineV2(policy, engine_config)

@@ -2,7 +2,7 @@
 from enum import Enum
 from typing import Dict, Optional
 
-from ....inference_utils import ActivationType, DtypeEnum, NormTypeEnum
+from ...inference_utils import ActivationType, DtypeEnum, NormTypeEnum
 from ..ds_module import DSModuleConfig
 from .....runtime.config_utils import DeepSpeedConfigModel
 
