@@ -175,3 +175,34 @@ def test_transformer_layer_gpu_matches_cpu(masked):
     gpu.train()
     y1, y2 = gpu(xg, None), gpu(xg, None)
     assert y1.shape == y2.shape and not torch.equal(y1, y2)
+
+
+@pytest.mark.parametrize("arch", ["llama", "mixtral", "opt"])
+def test_fastgen_policy_engine_gpu_bf16(arch):
+    """v2 engine on the CUDA kernels (ragged embed, blocked-KV rotary, paged attention, tcgen05 GEMMs) vs HF in fp32."""
+    transformers = pytest.importorskip("transformers")
+    from transformers import AutoConfig, AutoModelForCausalLM
+    from shuffle_exchange_b200.inference.v2.config_v2 import RaggedInferenceEngineConfig
+    from shuffle_exchange_b200.inference.v2.engine_factory import build_engine_from_hf_model
+    dev = _cuda()
+    torch.manual_seed(0)
+    common = dict(vocab_size=512, hidden_size=256, num_hidden_layers=2, num_attention_heads=4,
+                  max_position_embeddings=512)
+    kw = {"llama": dict(model_type="llama", intermediate_size=512, num_key_value_heads=2, **common),
+          "mixtral": dict(model_type="mixtral", intermediate_size=256, num_key_value_heads=2, num_local_experts=4,
+                          num_experts_per_tok=2, **common),
+          "opt": dict(model_type="opt", vocab_size=512, hidden_size=256, num_hidden_layers=2, num_attention_heads=4,
+                      ffn_dim=512, max_position_embeddings=512, word_embed_proj_dim=256)}[arch]
+    ref_model = AutoModelForCausalLM.from_config(AutoConfig.for_model(**kw)).float().eval()
+    ids = torch.randint(0, 512, (1, 40), generator=torch.Generator().manual_seed(1))
+    with torch.no_grad():
+        ref = ref_model(ids).logits[0]
+    import copy
+    gpu_model = copy.deepcopy(ref_model).to(dev, torch.bfloat16)
+    eng = build_engine_from_hf_model(gpu_model, RaggedInferenceEngineConfig())
+    out = eng.put([1], [ids[0, :33]]).float().cpu()
+    scale = ref.abs().max().item()
+    assert (out[0] - ref[32]).abs().max() < 0.06 * scale + 0.05
+    out = eng.put([1], [ids[0, 33:]]).float().cpu()
+    assert (out[0] - ref[39]).abs().max() < 0.06 * scale + 0.05
+    assert out[0].argmax() == ref[39].argmax() or (ref[39].topk(2).values.diff().abs() < 0.05 * scale)
