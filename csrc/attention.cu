@@ -1034,9 +1034,19 @@ static int launch_cluster2(K kernel, dim3 grid, int threads, int smem_bytes, cud
 
 // Head-pair multicast needs D = 128 (two 64-wide halves to split) and an even GQA group (pair shares its K/V head).
 // SXB_ATTN_MC=0 forces the single-CTA kernels (A/B measurements).
-static bool use_multicast(int Hq, int Hk, int D) {
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
+// GPU's memory hung the GPU: K/V that are not plain allocations of the current device take the single-CTA kernels.
+static bool owned_by_current_device(const void* p) {
+  cudaPointerAttributes a{};
+  int dev = -1;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  return a.type == cudaMemoryTypeDevice && a.device == dev;
+}
+static bool use_multicast(int Hq, int Hk, int D, const void* k, const void* v) {
   static const int env = [] { const char* e = getenv("SXB_ATTN_MC"); return e ? atoi(e) : 1; }();
-  return env != 0 && D == 128 && Hk > 0 && ((Hq / Hk) % 2 == 0) && (Hq % 2 == 0);
+  return env != 0 && D == 128 && Hk > 0 && ((Hq / Hk) % 2 == 0) && (Hq % 2 == 0) &&
+         owned_by_current_device(k) && owned_by_current_device(v);
 }
 
 }  // namespace attn
@@ -1073,7 +1083,7 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
   p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
   dim3 grid(Hq, B, (S + BQ - 1) / BQ);
   cudaStream_t s = (cudaStream_t)stream;
-  if (use_multicast(Hq, Hk, D)) {
+  if (use_multicast(Hq, Hk, D, k, v)) {
     if ((rc = set_smem(attn_fwd_kernel<128, 2>, FwdSmem<128>::kTotal))) return rc;
     if ((rc = launch_cluster2(attn_fwd_kernel<128, 2>, grid, kThreads, FwdSmem<128>::kTotal, s, tq, tk, tv, p)))
       return rc;
@@ -1125,7 +1135,7 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BC))) return rc;
     p.out = dq; p.out_stride = dq_stride;
     dim3 grid(Hq, B, (S + BQ - 1) / BQ);
-    if (use_multicast(Hq, Hk, D)) {
+    if (use_multicast(Hq, Hk, D, k, v)) {
       if ((rc = set_smem(attn_bwd_dq_kernel<128, 2>, DqSmem<128>::kTotal))) return rc;
       if ((rc = launch_cluster2(attn_bwd_dq_kernel<128, 2>, grid, kBwdThreads, DqSmem<128>::kTotal, s, tq, tk, tv,
                                 tdo, p)))
