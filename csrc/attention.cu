@@ -447,9 +447,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   uint64_t* kv_full = bars + 1;   // [4]
   uint64_t* kv_empty = bars + 5;  // [4]
   uint64_t* s_full = bars + 9;    // [2] S and dP of buffer b ready
-  uint64_t* ds_full = bars + 11;  // dS written (256 arrivals)
-  uint64_t* dq_done = bars + 12;  // dQ MMA of block j finished
-  uint64_t* s_free = bars + 13;   // [2] row warps copied S/dP of buffer b out of TMEM (one arrive per warp)
+  uint64_t* dq_done = bars + 12;  // committed once, after the last block's dQ MMAs
+  // [2] dS of buffer b parked in TMEM (one arrival per row warp).  Row warps can finish block j+1 before the MMA warp
+  // has observed block j, so the two in-flight blocks need distinct barriers (a single one would alias phases).
+  uint64_t* ds_full = bars + 13;
   uint64_t* qa_full = bars + 15;  // Q / dO copied into TMEM as A operands (one arrival per row warp)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
@@ -467,11 +468,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       for (int i = 0; i < NS; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], MC); }
       mbar_init(&s_full[0], 1);
       mbar_init(&s_full[1], 1);
-      mbar_init(ds_full, 8);   // one arrival per row warp
+      mbar_init(&ds_full[0], 8);   // one arrival per row warp
+      mbar_init(&ds_full[1], 8);
       mbar_init(qa_full, 8);
       mbar_init(dq_done, 1);
-      mbar_init(&s_free[0], 8);
-      mbar_init(&s_free[1], 8);
       mbar_fence_init();
     }
     __syncwarp();
@@ -553,7 +553,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       const int st = j % NS;
       // buffer (j+1)&1 was last read for block j-1, whose ds_full this warp already waited on
       if (j + 1 < nblk && !issue_sdp(j + 1)) goto done;
-      if (!__all_sync(0xffffffffu, mbar_wait_to(ds_full, j & 1, 30, j))) goto done;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&ds_full[j & 1], (j >> 1) & 1, 30, j))) goto done;
       tc_fence_after();
       const uint32_t sK = sbase + L::oK + st * L::kKV;
       if (elected) {
@@ -563,7 +563,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                       idesc_dq, (j | kk) != 0);
         if (MC > 1) umma_commit_mc(&kv_empty[st], 3);
         else umma_commit(&kv_empty[st]);
-        umma_commit(dq_done);
+        if (j == nblk - 1) umma_commit(dq_done);
       }
       __syncwarp();
     }
@@ -631,9 +631,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(ds_full);
+      if (lane == 0) mbar_arrive(&ds_full[j & 1]);
     }
-    if (!mbar_wait_to(dq_done, (nblk - 1) & 1, 33)) goto done;
+    if (!mbar_wait_to(dq_done, 0, 33)) goto done;
     tc_fence_after();
     __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
                           ((long long)b * p.S + min(qpos, p.S - 1)) * p.out_stride + (long long)h * D;
@@ -701,11 +701,13 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint64_t* q_empty = bars + 5;   // [NS]
   uint64_t* s_full = bars + 9;    // [2] S^T(it) in TMEM
   uint64_t* dp_full = bars + 11;  // [2] dP^T(it) in TMEM
-  uint64_t* p_full = bars + 13;   // P^T packed into TMEM (one arrival per row warp)
-  uint64_t* ds_full = bars + 14;  // dS^T packed into TMEM
-  uint64_t* acc_done = bars + 15;
+  uint64_t* acc_done = bars + 15;  // committed once, after the last iteration's dK MMAs
   uint64_t* stat_full = bars + 16;  // [NS] lse / delta of the stage's 64 queries staged in smem
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
+  // [2] each: P^T / dS^T of buffer b packed into TMEM (one arrival per row warp).  Row warps can finish iteration
+  // it+1 before the MMA warp has observed iteration it, so consecutive iterations use distinct barriers.
+  uint64_t* p_full = bars + 22;
+  uint64_t* ds_full = bars + 24;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kt = blockIdx.z;                   // key tile 0 sees every query block: heaviest first
@@ -723,8 +725,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       for (int i = 0; i < NS; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
       for (int i = 0; i < NS; ++i) mbar_init(&stat_full[i], 1);
       for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&dp_full[i], 1); }
-      mbar_init(p_full, 8);        // one arrival per row warp
-      mbar_init(ds_full, 8);
+      for (int i = 0; i < 2; ++i) { mbar_init(&p_full[i], 8); mbar_init(&ds_full[i], 8); }   // one arrival per row warp
       mbar_init(acc_done, 1);
       mbar_fence_init();
     }
@@ -823,7 +824,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       // S^T/dP^T(it+1) overwrite the TMEM buffer that held P^T/dS^T(it-1): safe without a barrier because the
       // dV/dK MMAs that read them were issued earlier by this same thread and the tensor pipe runs in order.
       if (it + 1 < niter && !issue_first(it + 1)) goto done;
-      if (!__all_sync(0xffffffffu, mbar_wait_to(p_full, it & 1, 37, it))) goto done;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&p_full[it & 1], (it >> 1) & 1, 37, it))) goto done;
       tc_fence_after();
       const uint32_t sQ = sbase + L::oQ + st * L::kQ;
       const uint32_t sDO = sbase + L::oDO + st * L::kQ;
@@ -837,7 +838,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                       (it | kk) != 0);
       }
       __syncwarp();
-      if (!__all_sync(0xffffffffu, mbar_wait_to(ds_full, it & 1, 39, it))) goto done;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&ds_full[it & 1], (it >> 1) & 1, 39, it))) goto done;
       tc_fence_after();
       if (elected) {
 #pragma unroll
@@ -845,7 +846,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           umma_f16_ts(tDK_u, tDST + (kk >> 1) * 32 + (kk & 1) * 8, desc_mnmajor(sQ, BC, kk), idesc_acc,
                       (it | kk) != 0);
         umma_commit(&q_empty[st]);
-        umma_commit(acc_done);
+        if (it == niter - 1) umma_commit(acc_done);
       }
       __syncwarp();
     }
@@ -903,7 +904,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(p_full);                      // dV += P^T dO can start
+      if (lane == 0) mbar_arrive(&p_full[it & 1]);             // dV += P^T dO can start
       {
         uint32_t x[32], dk[16];
         tmem_ld_32x32(tST + 64, x);
@@ -923,12 +924,12 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(ds_full);
+      if (lane == 0) mbar_arrive(&ds_full[it & 1]);
       if (++qrel == per_head) qrel = 0;
       if (++st == NS) { st = 0; ph ^= 1; }
     }
     if (niter > 0) {
-      if (!mbar_wait_to(acc_done, (niter - 1) & 1, 40)) goto done;
+      if (!mbar_wait_to(acc_done, 0, 40)) goto done;
       tc_fence_after();
     }
     // half 0 drains dV, half 1 drains dK

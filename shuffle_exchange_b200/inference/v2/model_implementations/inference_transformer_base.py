@@ -24,6 +24,7 @@ from ..modules import heuristics
 from ..modules.configs import (DSEmbeddingsConfig, DSLinearConfig, DSMoEConfig, DSNormConfig, DSSelfAttentionConfig,
                                DSUnembedConfig, MaskingType, PositionalEmbeddingType, RotateHalfConfig)
 from ..ragged.kv_cache import KVCacheConfig
+from . import sharding
 
 
 @dataclass
@@ -99,6 +100,18 @@ class DSTransformerModelBase(DSInferenceModelBase):
         self._engine_config = engine_config or RaggedInferenceEngineConfig()
         self.state_manager = state_manager
         self._base_mp_group = base_mp_group
+        self._tp_size, self._tp_rank = 1, 0
+        if base_mp_group is not None:
+            import torch.distributed as dist
+            self._tp_size, self._tp_rank = dist.get_world_size(base_mp_group), dist.get_rank(base_mp_group)
+        if self._tp_size > 1:
+            # tensor parallelism (reference ``inference_transformer_base.py:199-560``): QKV / MLP-in column-parallel,
+            # attention-out / MLP-out row-parallel with one all-reduce each, vocabulary-parallel unembedding
+            cache = weights.setdefault("_tp_local", {})
+            key = (self._tp_rank, self._tp_size)
+            if key not in cache:
+                cache[key] = sharding.shard_weights(weights, spec, self._tp_rank, self._tp_size)
+            weights = cache[key]
         self.weights = weights
         self._build_modules()
 
@@ -114,11 +127,17 @@ class DSTransformerModelBase(DSInferenceModelBase):
     @property
     def n_heads(self): return self.spec.n_heads
     @property
-    def n_heads_q_local(self): return self.spec.n_heads
+    def n_heads_q_local(self):
+        s = self.spec
+        return sharding.get_local_heads(self._tp_rank, self._tp_size, s.n_heads,
+                                        None if s.n_heads_kv == s.n_heads else s.n_heads_kv)[0]
     @property
     def n_heads_kv(self): return self.spec.n_heads_kv
     @property
-    def n_heads_kv_local(self): return self.spec.n_heads_kv
+    def n_heads_kv_local(self):
+        s = self.spec
+        return sharding.get_local_heads(self._tp_rank, self._tp_size, s.n_heads,
+                                        None if s.n_heads_kv == s.n_heads else s.n_heads_kv)[1]
     @property
     def intermediate_dim(self): return self.spec.intermediate_dim
     @property
@@ -132,9 +151,31 @@ class DSTransformerModelBase(DSInferenceModelBase):
     @property
     def max_sequence_length(self): return self.spec.max_seq_len
     @property
-    def tp_size(self): return 1
+    def tp_size(self): return self._tp_size
     @property
-    def tp_rank(self): return 0
+    def tp_rank(self): return self._tp_rank
+
+    def _local_dim(self, n: int) -> int:
+        return sharding.sharded_intermediate_dim(n, self._tp_size, self._tp_rank) if self._tp_size > 1 else n
+
+    def _reduce(self, x: torch.Tensor) -> torch.Tensor:
+        """Sum the partial outputs of a row-parallel projection over the tensor-parallel group."""
+        if self._tp_size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(x, group=self._base_mp_group)
+        return x
+
+    def _gather_logits(self, local: torch.Tensor) -> torch.Tensor:
+        """Concatenate vocabulary shards (shards may differ by one row: pad to the largest, trim after)."""
+        if self._tp_size == 1:
+            return local
+        import torch.distributed as dist
+        sizes = [sharding.sharded_unembed_dim(self.spec.vocab_size, r, self._tp_size) for r in range(self._tp_size)]
+        width = max(sizes)
+        send = local if local.shape[-1] == width else torch.nn.functional.pad(local, (0, width - local.shape[-1]))
+        parts = [torch.empty_like(send) for _ in sizes]
+        dist.all_gather(parts, send.contiguous(), group=self._base_mp_group)
+        return torch.cat([p[..., :n] for p, n in zip(parts, sizes)], dim=-1)
 
     # ------------------------------------------------------------------------------------------ module construction
     def _build_modules(self) -> None:
@@ -145,8 +186,9 @@ class DSTransformerModelBase(DSInferenceModelBase):
         rot = None
         if s.positional == PositionalEmbeddingType.rotate_half:
             rot = RotateHalfConfig(theta_base=s.rope_theta, rotate_dim=s.rotary_dim)
+        hq, hkv = self.n_heads_q_local, self.n_heads_kv_local
         self.attn = heuristics.instantiate_attention(DSSelfAttentionConfig(
-            max_tokens=mt, n_heads_q=s.n_heads, n_heads_kv=s.n_heads_kv, head_size=s.head_size,
+            max_tokens=mt, n_heads_q=hq, n_heads_kv=hkv, head_size=s.head_size,
             max_sequences=sm.max_ragged_sequence_count,
             scale_factor=s.attn_scale if s.attn_scale is not None else s.head_size ** -0.5, input_dtype=dt,
             output_dtype=dt, masking_type=MaskingType.causal, positional_embedding_type=s.positional,
@@ -157,26 +199,28 @@ class DSTransformerModelBase(DSInferenceModelBase):
         lin = lambda i, o, act=ActivationType.IDENTITY: heuristics.instantiate_linear(   # noqa: E731
             DSLinearConfig(max_tokens=mt, in_channels=i, out_channels=o, activation=act, input_dtype=dt,
                            output_dtype=dt), ec)
-        qkv_out = (s.n_heads + 2 * s.n_heads_kv) * s.head_size
+        qkv_out = (hq + 2 * hkv) * s.head_size
         self.qkv = lin(s.model_dim, qkv_out)
-        self.attn_out = lin(s.n_heads * s.head_size, s.model_dim)
+        self.attn_out = lin(hq * s.head_size, s.model_dim)
         if s.n_experts > 0:
             self.moe = heuristics.instantiate_moe(DSMoEConfig(
-                max_tokens=mt, model_dim=s.model_dim, intermediate_features=s.moe_intermediate_dim or s.intermediate_dim,
+                max_tokens=mt, model_dim=s.model_dim,
+                intermediate_features=self._local_dim(s.moe_intermediate_dim or s.intermediate_dim),
                 n_experts=s.n_experts, top_k=s.top_k, input_dtype=dt, output_dtype=dt, activation=s.mlp_activation,
                 normalize_scores=s.normalize_expert_scores), ec)
             if s.shared_expert_dim > 0:
-                self.shared_in = lin(s.model_dim, s.shared_expert_dim, s.mlp_activation)
-                self.shared_out = lin(s.shared_expert_dim, s.model_dim)
+                self.shared_in = lin(s.model_dim, self._local_dim(s.shared_expert_dim), s.mlp_activation)
+                self.shared_out = lin(self._local_dim(s.shared_expert_dim), s.model_dim)
         else:
-            self.mlp_in = lin(s.model_dim, s.intermediate_dim, s.mlp_activation)
-            self.mlp_out = lin(s.intermediate_dim, s.model_dim)
+            self.mlp_in = lin(s.model_dim, self._local_dim(s.intermediate_dim), s.mlp_activation)
+            self.mlp_out = lin(self._local_dim(s.intermediate_dim), s.model_dim)
         self.norm = heuristics.instantiate_pre_norm(DSNormConfig(
             max_tokens=mt, type=s.norm_type, channels=s.model_dim, residual_dtype=dt, input_dtype=dt, output_dtype=dt,
             eps=s.norm_eps), ec)
         self.unembed = heuristics.instantiate_unembed(DSUnembedConfig(
             max_tokens=mt, dtype=dt, norm_type=s.norm_type, model_dim=s.model_dim,
-            max_sequences=sm.max_ragged_sequence_count, vocab_size=s.vocab_size, eps=s.norm_eps), ec)
+            max_sequences=sm.max_ragged_sequence_count,
+            vocab_size=sharding.sharded_unembed_dim(s.vocab_size, self._tp_rank, self._tp_size), eps=s.norm_eps), ec)
         # let the linear implementation pick its storage (e.g. FP6) for every 2-D projection weight (once: the engine
         # builds the model twice — a sizing probe and the real one — over the same weight dict)
         if self.weights.get("_transformed"):
@@ -191,7 +235,7 @@ class DSTransformerModelBase(DSInferenceModelBase):
     # ------------------------------------------------------------------------------------------ KV planning
     def kv_cache_config(self, block_size: int) -> KVCacheConfig:
         s = self.spec
-        return KVCacheConfig(block_size=block_size, cache_shape=(s.num_layers, s.n_heads_kv, s.head_size),
+        return KVCacheConfig(block_size=block_size, cache_shape=(s.num_layers, self.n_heads_kv_local, s.head_size),
                              cache_dtype=s.dtype)
 
     def get_kv_requirements(self, sequence, max_new_tokens: int, max_new_blocks: int):
@@ -224,13 +268,13 @@ class DSTransformerModelBase(DSInferenceModelBase):
                 if lw.shared_gate is not None:
                     sh = sh * torch.sigmoid(torch.nn.functional.linear(x, lw.shared_gate))
                 y = y + sh
-            return y
-        return self.mlp_out(self.mlp_in(x, lw.w_in, lw.b_in), lw.w_out, lw.b_out)
+            return self._reduce(y)
+        return self._reduce(self.mlp_out(self.mlp_in(x, lw.w_in, lw.b_in), lw.w_out, lw.b_out))
 
     def _attention(self, li: int, lw: LayerWeights, x: torch.Tensor, batch) -> torch.Tensor:
         qkv = self.qkv(x, lw.wqkv, lw.bqkv)
         ctx = self.attn(qkv, self.state_manager.get_cache(li), batch)
-        return self.attn_out(ctx, lw.wo, lw.bo)
+        return self._reduce(self.attn_out(ctx, lw.wo, lw.bo))
 
     @torch.no_grad()
     def forward(self, batch) -> torch.Tensor:
@@ -249,5 +293,5 @@ class DSTransformerModelBase(DSInferenceModelBase):
                 residual, x = self.norm(residual, attn, lw.ln2_w, lw.ln2_b)
                 hidden = self._mlp(lw, x)
         residual = residual + hidden if hidden is not None else residual
-        return self.unembed(residual, W["unembed"], batch, W.get("unembed_b"), W["final_norm_w"],
-                            W.get("final_norm_b"))
+        return self._gather_logits(self.unembed(residual, W["unembed"], batch, W.get("unembed_b"), W["final_norm_w"],
+                                                W.get("final_norm_b")))

@@ -1,0 +1,34 @@
+"""Repeat the attention numerics cases many times (timing-dependent faults show up as run-to-run variation).
+    python tools/attn_stress.py [repeats]
+Prints one JSON line: worst error per case over all repeats and the number of repeats above tolerance."""
+import importlib.util
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+_spec = importlib.util.spec_from_file_location("gpu_selftest", os.path.join(ROOT, "tools", "gpu_selftest.py"))
+st = importlib.util.module_from_spec(_spec)
+_spec.loader.exec_module(st)
+
+
+def main():
+    reps = int(sys.argv[1]) if len(sys.argv) > 1 else 25
+    cases = list(st._ATTN_CFGS) + [(1, 300, 4, 1, 128, True), (2, 200, 2, 2, 128, True), (1, 8192, 8, 2, 128, True),
+                                   (1, 1000, 4, 4, 64, True)]
+    out = {}
+    for cfg in cases:
+        worst, bad = 0.0, 0
+        for _ in range(reps if cfg[1] < 4096 else 3):
+            r = st._attn_case(*cfg, bwd=True)
+            e = max((v if isinstance(v, float) else 1e9) for v in r.values())
+            worst = max(worst, e)
+            bad += int(not (e < 2e-2))
+        out["x".join(str(int(v)) for v in cfg)] = {"worst": worst, "bad": bad}
+    print(json.dumps(out))
+    return int(any(v["bad"] for v in out.values()))
+
+
+if __name__ == "__main__":
+    sys.exit(main())
