@@ -46,19 +46,16 @@ def build_engine_from_hf_model(hf_model: torch.nn.Module, engine_config: RaggedI
 
 def build_engine_from_ds_checkpoint(path: str, engine_config: RaggedInferenceEngineConfig,
                                     debug_level: int = logging.INFO) -> InferenceEngineV2:
-    """Directory written by ``InferenceEngineV2.serialize``: ``ds_model_config.pkl`` + ``params_rank_0.pt``."""
+    """Directory written by ``InferenceEngineV2.serialize``: ``ds_model_config.pkl`` plus, per TP rank,
+    ``params_rank_R_of_N.pt`` (one flat byte buffer) and ``metadata_rank_R_of_N.json`` (reference
+    ``engine_factory.py:33-66``)."""
     inference_logger(level=debug_level)
     with open(os.path.join(path, "ds_model_config.pkl"), "rb") as f:
         model_config = pickle.load(f)
-
-    class _Saved(InMemoryModelEngine):
-        def __init__(self, file):
-            self.file, self.model_config = file, model_config
-
-        def parameters(self):
-            yield from torch.load(self.file, map_location="cpu", weights_only=True).items()
-
-    policy = _policy_for(model_config, _Saved(os.path.join(path, "params_rank_0.pt")))
+    mt = getattr(model_config, "model_type", "").lower()
+    if mt not in POLICIES:
+        raise ValueError(f"Unsupported model type {mt}; supported: {sorted(POLICIES)}")
+    policy = POLICIES[mt](model_config, checkpoint_engine=None, inf_checkpoint_path=path)
     policy._engine_config = engine_config
     return InferenceEngineV2(policy, engine_config)
 

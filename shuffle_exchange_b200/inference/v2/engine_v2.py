@@ -23,6 +23,9 @@ class InferenceEngineV2:
     def __init__(self, policy_or_model, engine_config: RaggedInferenceEngineConfig = None, device=None) -> None:
         """``policy_or_model``: a callable ``(state_manager) -> model`` or a training ``LlamaForCausalLM``."""
         self._config = engine_config or RaggedInferenceEngineConfig()
+        self._base_mp_group = self._initialize_tp_group()
+        if hasattr(policy_or_model, "set_mp_group"):
+            policy_or_model.set_mp_group(self._base_mp_group)
         from .model_implementations.llama_v2 import RaggedLlamaModel
         if callable(policy_or_model) and not isinstance(policy_or_model, torch.nn.Module):
             builder = policy_or_model
@@ -30,11 +33,26 @@ class InferenceEngineV2:
             builder = lambda sm: RaggedLlamaModel(policy_or_model, sm)
         probe = builder(None)
         kv_cfg = probe.kv_cache_config(self._config.kv_block_size)
-        self._state_manager = DSStateManager(self._config.state_manager, kv_cfg, device=device)
+        self._state_manager = DSStateManager(self._config.state_manager, kv_cfg, device=device,
+                                             mp_group=self._base_mp_group)
         self._model = builder(self._state_manager)
         sm = self._config.state_manager
         self._batch = RaggedBatchWrapper(sm.max_ragged_batch_size, sm.max_ragged_sequence_count,
                                          self._state_manager.max_blocks_per_seq, device=device)
+
+    def _initialize_tp_group(self):
+        """Tensor-parallel group over the first ``tp_size`` ranks (reference ``engine_v2.py:95-105``); every rank of
+        the job must construct the engine so the collective group creation matches."""
+        tp = self._config.tensor_parallel.tp_size
+        if tp <= 1:
+            return None
+        import torch.distributed as dist
+        from ...comm import comm
+        if not dist.is_initialized():
+            comm.init_distributed()
+        if dist.get_world_size() < tp:
+            raise ValueError(f"tensor_parallel.tp_size={tp} exceeds the world size {dist.get_world_size()}")
+        return dist.new_group(ranks=list(range(tp)))
 
     @property
     def free_blocks(self) -> int:
@@ -108,3 +126,22 @@ class InferenceEngineV2:
 
     def flush(self, uid: int) -> None:
         self._state_manager.flush_sequence(uid)
+
+    def serialize(self, save_path: str) -> None:
+        """Write this rank's (sharded, fused, possibly quantised) parameters as one flat buffer plus its table of
+        contents, and on TP rank 0 the model config (reference ``engine_v2.py:251-268``).  ``build_hf_engine`` /
+        ``build_engine_from_ds_checkpoint`` reload the directory without touching the original checkpoint."""
+        import os
+        import pickle
+        from .model_implementations.flat_model_helpers import (flatten_inference_model, make_metadata_filename,
+                                                              make_model_config_filename, make_param_filename)
+        m = self._model
+        os.makedirs(save_path, exist_ok=True)
+        if getattr(m, "flattened_params", None) is None:
+            m.flattened_params, m.flattened_param_metadata = flatten_inference_model(m.weights, m.tp_rank, m.tp_size)
+        torch.save(m.flattened_params.cpu(), make_param_filename(save_path, m.tp_rank, m.tp_size))
+        with open(make_metadata_filename(save_path, m.tp_rank, m.tp_size), "w") as f:
+            f.write(m.flattened_param_metadata.json())
+        if m.tp_rank == 0:
+            with open(make_model_config_filename(save_path), "wb") as f:
+                pickle.dump(getattr(m, "model_config", None) or m.spec, f)

@@ -65,6 +65,11 @@ class InferenceV2Policy(ABC):
         self._engine_config: Optional[RaggedInferenceEngineConfig] = None
         self.container_map = ContainerMap()
         self.dtype_override: Optional[torch.dtype] = None      # e.g. the dtype of an in-memory model's parameters
+        self._mp_group = None
+
+    def set_mp_group(self, group) -> None:
+        """Tensor-parallel group the engine created; models built afterwards shard their weights over it."""
+        self._mp_group = group
 
     def resolved_spec(self) -> ArchSpec:
         spec = self.spec(self._model_config)
@@ -94,8 +99,31 @@ class InferenceV2Policy(ABC):
             return None
         return raw[names[0]] if len(names) == 1 else torch.cat([raw[n] for n in names], dim=0)
 
+    def _load_flat(self, rank: int, size: int) -> Dict:
+        """Weights written by ``InferenceEngineV2.serialize``: already fused, sharded for ``(rank, size)`` and
+        transformed, restored as views into one buffer (reference ``inference_policy_base.py:156-180``)."""
+        from .flat_model_helpers import (ModelMetadata, make_metadata_filename, make_param_filename,
+                                         restore_inference_model)
+        base = self._inf_checkpoint_path
+        with open(make_metadata_filename(base, rank, size)) as f:
+            md = ModelMetadata.parse_raw(f.read())
+        buf = torch.load(make_param_filename(base, rank, size), map_location="cpu", weights_only=True).to(self._device())
+        weights = restore_inference_model(buf, md)
+        weights["_transformed"] = True
+        weights["_presharded"] = (rank, size)
+        weights["_flat"] = (buf, md)
+        if isinstance(weights.get("embed"), torch.Tensor) and weights["embed"].is_floating_point():
+            self.dtype_override = weights["embed"].dtype
+        return weights
+
     def load_weights(self) -> Dict:
         if self._weights is not None:
+            return self._weights
+        if self._inf_checkpoint_path is not None:
+            import torch.distributed as dist
+            g = self._mp_group
+            rank, size = (dist.get_rank(g), dist.get_world_size(g)) if g is not None else (0, 1)
+            self._weights = self._load_flat(rank, size)
             return self._weights
         spec = self.resolved_spec()
         dev, dt = self._device(), spec.dtype
@@ -147,8 +175,13 @@ class InferenceV2Policy(ABC):
                     state_manager=None) -> DSTransformerModelBase:
         self._engine_config = engine_config
         spec = self.resolved_spec()
-        model = DSTransformerModelBase(spec, self.load_weights(), engine_config, state_manager, mp_group)
+        if mp_group is not None:
+            self._mp_group = mp_group
+        weights = self.load_weights()
+        spec = self.resolved_spec()             # a flat checkpoint fixes the activation dtype
+        model = DSTransformerModelBase(spec, weights, engine_config, state_manager, self._mp_group)
+        model.model_config = self._model_config
         return model
 
     def __call__(self, state_manager):
-        return self.build_model(self._engine_config or RaggedInferenceEngineConfig(), None, state_manager)
+        return self.build_model(self._engine_config or RaggedInferenceEngineConfig(), self._mp_group, state_manager)

@@ -104,7 +104,14 @@ class DSTransformerModelBase(DSInferenceModelBase):
         if base_mp_group is not None:
             import torch.distributed as dist
             self._tp_size, self._tp_rank = dist.get_world_size(base_mp_group), dist.get_rank(base_mp_group)
-        if self._tp_size > 1:
+        self.flattened_params = self.flattened_param_metadata = None
+        if weights.get("_flat") is not None:
+            self.flattened_params, self.flattened_param_metadata = weights["_flat"]
+        if weights.get("_presharded") is not None:
+            if tuple(weights["_presharded"]) != (self._tp_rank, self._tp_size):
+                raise ValueError(f"checkpoint was serialized for TP rank/size {weights['_presharded']}, "
+                                 f"engine runs {(self._tp_rank, self._tp_size)}")
+        elif self._tp_size > 1:
             # tensor parallelism (reference ``inference_transformer_base.py:199-560``): QKV / MLP-in column-parallel,
             # attention-out / MLP-out row-parallel with one all-reduce each, vocabulary-parallel unembedding
             cache = weights.setdefault("_tp_local", {})

@@ -22,7 +22,7 @@ class KVCacheConfig:
 
 class BlockedKVCache:
     def __init__(self, config: KVCacheConfig, num_blocks: Optional[int] = None, memory_fraction: float = 0.8,
-                 device=None) -> None:
+                 device=None, reserve_bytes: Optional[int] = None, mp_group=None) -> None:
         self._config = config
         n_layers, n_kv, d = config.cache_shape
         elem = torch.tensor([], dtype=config.cache_dtype).element_size()
@@ -31,9 +31,16 @@ class BlockedKVCache:
         if num_blocks is None:
             if torch.device(dev).type == "cuda":
                 free, _ = torch.cuda.mem_get_info()
-                num_blocks = max(1, int(free * memory_fraction) // per_block)
+                usable = free - reserve_bytes if reserve_bytes is not None else int(free * memory_fraction)
+                num_blocks = max(1, int(usable) // per_block)
             else:
                 num_blocks = 256
+            if mp_group is not None:
+                # tensor-parallel ranks must agree on the block count (reference ``kv_cache.py:116-124``: MIN all-reduce)
+                import torch.distributed as dist
+                t = torch.tensor([num_blocks], dtype=torch.int64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MIN, group=mp_group)
+                num_blocks = int(t.item())
         self._num_blocks = num_blocks
         self._cache = torch.zeros(n_layers, num_blocks, config.block_size, 2, n_kv, d, dtype=config.cache_dtype, device=dev)
         self._allocator = BlockedAllocator(num_blocks)

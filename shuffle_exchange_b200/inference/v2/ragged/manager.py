@@ -19,14 +19,32 @@ class DSStateManagerConfig:
     memory_config_fraction: float = 0.8
     num_kv_blocks: Optional[int] = None
     offload: bool = False
+    memory_config: Optional["MemoryConfig"] = None      # reference spelling; overrides the two fields above when set
+
+    def __post_init__(self):
+        if isinstance(self.memory_config, dict):
+            from .manager_configs import MemoryConfig
+            self.memory_config = MemoryConfig(**self.memory_config)
+        if self.max_ragged_sequence_count > self.max_tracked_sequences:
+            raise ValueError("max_ragged_sequence_count must not exceed max_tracked_sequences")
+        if self.max_ragged_sequence_count > self.max_ragged_batch_size:
+            raise ValueError("max_ragged_sequence_count must not exceed max_ragged_batch_size")
 
 
 class DSStateManager:
-    def __init__(self, config: DSStateManagerConfig, kv_config: KVCacheConfig, device=None) -> None:
+    def __init__(self, config: DSStateManagerConfig, kv_config: KVCacheConfig, device=None, mp_group=None) -> None:
         self._config, self._kv_config = config, kv_config
         self._seqs: Dict[int, DSSequenceDescriptor] = {}
-        self._kv_cache = BlockedKVCache(kv_config, num_blocks=config.num_kv_blocks,
-                                        memory_fraction=config.memory_config_fraction, device=device)
+        num_blocks, reserve = config.num_kv_blocks, None
+        mc = config.memory_config
+        if mc is not None:
+            from .manager_configs import AllocationMode
+            if mc.mode == AllocationMode.ALLOCATE:
+                num_blocks = int(mc.size)
+            else:
+                reserve = int(mc.size)
+        self._kv_cache = BlockedKVCache(kv_config, num_blocks=num_blocks, memory_fraction=config.memory_config_fraction,
+                                        device=device, reserve_bytes=reserve, mp_group=mp_group)
         self.max_blocks_per_seq = (config.max_context + kv_config.block_size - 1) // kv_config.block_size
 
     def get_sequence(self, uid: int) -> Optional[DSSequenceDescriptor]:
