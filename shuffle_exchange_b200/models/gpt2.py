@@ -71,12 +71,9 @@ class GPT2Block(nn.Module):
         nh, d = cfg.n_head, H // cfg.n_head
         x, residual = F.layer_norm(h, self.ln_1_w, self.ln_1_b, cfg.layer_norm_epsilon, residual)
         qkv = F.linear(x, self.c_attn_w, self.c_attn_b)
-        q = qkv[..., :H].view(B, S, nh, d)
-        k = qkv[..., H:2 * H].view(B, S, nh, d)
-        v = qkv[..., 2 * H:].view(B, S, nh, d)
         if h.is_cuda and d not in (64, 128):
             raise RuntimeError("head_dim must be 64 or 128 on the CUDA path")
-        o = F.flash_attention(q, k, v, causal=True)
+        o = F.flash_attention_qkv(qkv, nh, nh, d, causal=True)
         h = F.linear(o.reshape(B, S, H), self.c_proj_w, self.c_proj_b)
         x, residual = F.layer_norm(h, self.ln_2_w, self.ln_2_b, cfg.layer_norm_epsilon, residual)
         a = F.bias_act(F.linear(x, self.c_fc_w), self.c_fc_b, "gelu")

@@ -119,10 +119,7 @@ class LlamaDecoderLayer(nn.Module):
         qkv = F.linear(x, self.wqkv)
         C = qkv.shape[-1]
         qkv = F.rope(qkv, positions, cos, sin, self.n_q + self.n_kv, self.d)
-        q = qkv[..., : self.n_q * self.d].view(B, S, self.n_q, self.d)
-        k = qkv[..., self.n_q * self.d: (self.n_q + self.n_kv) * self.d].view(B, S, self.n_kv, self.d)
-        v = qkv[..., (self.n_q + self.n_kv) * self.d:].view(B, S, self.n_kv, self.d)
-        o = F.flash_attention(q, k, v, causal=True)
+        o = F.flash_attention_qkv(qkv, self.n_q, self.n_kv, self.d, causal=True)
         h = F.linear(o.reshape(B, S, self.n_q * self.d), self.wo)
         x, residual = F.rms_norm(h, self.post_attention_layernorm, eps, residual)
         a = F.swiglu(F.linear(x, self.w_gate_up))

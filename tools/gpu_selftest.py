@@ -417,6 +417,28 @@ for _cfg in _ATTN_CFGS:
     CHECKS[f"attn_bwd_{_tag}"] = _mk_attn_check(_cfg, True)
 
 
+@check("attn_fused_qkv")
+def _():
+    """Fused-QKV entry point (gradient returned as one tensor) against the fp32 reference, GQA and MHA."""
+    import torch
+    from shuffle_exchange_b200.ops import functional as F
+    worst, detail = 0.0, {}
+    for (B, S, Hq, Hk, D) in ((2, 384, 4, 2, 128), (1, 300, 2, 2, 64)):
+        torch.manual_seed(0)
+        qkv = torch.randn(B, S, (Hq + 2 * Hk) * D, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+        out = F.flash_attention_qkv(qkv, Hq, Hk, D, True)
+        g = torch.randn_like(out)
+        out.backward(g)
+        qr = qkv.detach().float().requires_grad_()
+        q2, k2, v2 = F._split_qkv(qr, Hq, Hk, D)
+        ref = F.attention_ref(q2, k2, v2, True)
+        ref.backward(g.float())
+        r = {"fwd": _rel_err(out, ref), "dqkv": _rel_err(qkv.grad, qr.grad)}
+        detail[f"{B}x{S}x{Hq}x{Hk}x{D}"] = r
+        worst = max(worst, *r.values())
+    return {"err": worst, "detail": detail}
+
+
 @check("attn_perf")
 def _():
     import torch

@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--seq", type=int, default=8192)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--out", default="gpurun_out/step_profile.json")
+    ap.add_argument("--trace-kernel", default="", help="comma-separated kernel-name substrings: report which CPU ops launch them")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -69,6 +70,23 @@ def main():
         cpu = sorted(((e.key, e.count / a.steps, e.self_cpu_time_total / 1000.0 / a.steps) for e in prof.key_averages()),
                      key=lambda r: -r[2])[:12]
         out["cpu_top"] = [{"op": k[:70], "calls": c, "ms": round(ms, 3)} for k, c, ms in cpu]
+        if a.trace_kernel:
+            # which autograd / aten op chain launches the named kernels (finds stray fills and copies)
+            from collections import Counter
+            subs = [t for t in a.trace_kernel.split(",") if t]
+            chains = {t: Counter() for t in subs}
+            for e in prof.events():
+                ks = getattr(e, "kernels", None) or []
+                for k in ks:
+                    for t in subs:
+                        if t in k.name:
+                            chain, cur = [], e
+                            while cur is not None and len(chain) < 6:
+                                chain.append(cur.name[:48])
+                                cur = cur.cpu_parent
+                            chains[t][" <- ".join(chain)] += 1
+            out["kernel_origins"] = {t: [{"chain": c, "launches_per_step": n / a.steps} for c, n in ct.most_common(12)]
+                                     for t, ct in chains.items()}
         os.makedirs(os.path.dirname(a.out), exist_ok=True)
         json.dump(out, open(a.out, "w"), indent=1)
         print(json.dumps(out)[:6000])
