@@ -174,6 +174,10 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     import shuffle_exchange_b200 as sxb
+    from shuffle_exchange_b200.utils.logging import logger as _sxb_logger
+    for _h in _sxb_logger.handlers:          # stdout carries exactly one JSON line; progress logs go to stderr
+        if hasattr(_h, "setStream"):
+            _h.setStream(sys.stderr)
     from shuffle_exchange_b200.models.llama import LlamaForCausalLM, llama_config
     from shuffle_exchange_b200.native import lib as nlib
 
