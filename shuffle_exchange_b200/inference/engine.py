@@ -59,7 +59,7 @@ class InferenceEngine(nn.Module):
             if moe and dist.is_initialized() and dist.get_world_size() > 1:
                 self._create_ep_parallel_group(config.moe.moe_experts if hasattr(config.moe, "moe_experts") else [1])
         self._convert_dtype(config)
-        if config.tensor_parallel.tp_size > 1:
+        if config.tensor_parallel.tp_size > 1 or config.replace_with_kernel_inject:
             self._apply_injection_policy(config)
         if config.checkpoint is not None:
             self._load_checkpoint(config.checkpoint)

@@ -25,12 +25,70 @@ def _module_match(module):
 
 
 def generic_injection(module, dtype=None, enable_cuda_graph=True):
-    """Diffusers-style generic injection (attention blocks of UNet/VAE): kept as a no-op pass-through that reports what
-    it would replace; the reference swaps in ``DeepSpeedDiffusersAttention`` (triton/CUDA kernels absent here)."""
-    n = sum(1 for m in module.modules() if type(m).__name__ in ("CrossAttention", "Attention", "BasicTransformerBlock"))
-    if n:
-        logger.info(f"generic_injection: {n} diffusers attention blocks found; running them unmodified")
+    """Diffusers pipelines (reference ``replace_module.py:86-180``): wrap ``unet`` / ``vae`` / ``text_encoder``
+    sub-models in their graphed wrappers; a bare UNet / VAE is wrapped directly."""
+    for policy in (p() for p in __import__(__package__ + ".replace_policy", fromlist=["generic_policies"]).generic_policies):
+        if policy.match(module):
+            return policy.apply(module, enable_cuda_graph=enable_cuda_graph)
+    wrapped = 0
+    for name in ("unet", "vae", "text_encoder"):
+        sub = getattr(module, name, None)
+        if sub is None:
+            continue
+        p = _module_match(sub)
+        if p is not None:
+            setattr(module, name, p.apply(sub, enable_cuda_graph=enable_cuda_graph))
+            wrapped += 1
+        elif name == "text_encoder" and type(sub).__name__ == "CLIPTextModel":
+            from ..model_implementations.transformers.clip_encoder import DSClipEncoder
+            setattr(module, name, DSClipEncoder(sub, enable_cuda_graph=enable_cuda_graph))
+            wrapped += 1
+    if wrapped:
+        logger.info(f"generic_injection: wrapped {wrapped} diffusers sub-model(s)")
     return module
+
+
+def _policy_for_layer(module, injection_policy=None):
+    from .containers import POLICY_TO_CONTAINER
+    from .replace_policy import replace_policies
+    for pol in (injection_policy,) if injection_policy is not None else replace_policies:
+        if pol in POLICY_TO_CONTAINER and pol.match(module):
+            return pol
+    return None
+
+
+def _inject_kernels(model, config, model_config, injection_policy=None):
+    """``replace_with_kernel_inject``: every layer a policy recognises becomes a fused
+    :class:`DeepSpeedTransformerInference` carrying the client's weights (tensor-parallel slices when ``tp_size > 1``);
+    returns the number of layers replaced (reference ``replace_module.py:261-411``)."""
+    from .containers import POLICY_TO_CONTAINER, HFLayerAdapter
+    from ..model_implementations.transformers.ds_transformer import DeepSpeedTransformerInference
+    from ..ops.transformer.inference.ds_attention import DeepSpeedSelfAttention
+    DeepSpeedTransformerInference.layer_id = 0
+    DeepSpeedSelfAttention.num_layers = 0
+    count = 0
+
+    def walk(parent):
+        nonlocal count
+        for name, child in list(parent.named_children()):
+            pol = _policy_for_layer(child, injection_policy)
+            if pol is None:
+                walk(child)
+                continue
+            policy = pol(child, inference=True)
+            container = POLICY_TO_CONTAINER[pol](policy, config, model_config, count, child)
+            container.create_ds_model_config()
+            container.initialize_tensors()
+            container.apply_tensor_parallelism()
+            fused = container.create_module()
+            dev = next(child.parameters()).device
+            adapter = HFLayerAdapter(fused.to(dev), returns_tuple=pol.returns_tuple)
+            adapter._orig_layer = [child]          # kept out of the module tree so revert can restore it
+            setattr(parent, name, adapter)
+            count += 1
+
+    walk(model)
+    return count
 
 
 def replace_transformer_layer(orig_layer_impl, model, checkpoint_dict, config, model_config):
@@ -44,6 +102,15 @@ def replace_transformer_layer(orig_layer_impl, model, checkpoint_dict, config, m
         set_num_kv_heads(kv)
         set_num_attention_heads(getattr(model_config, "num_attention_heads", None))
         set_n_embd(getattr(model_config, "hidden_size", None))
+    if getattr(config, "replace_with_kernel_inject", False):
+        n = _inject_kernels(model, config, model_config, orig_layer_impl if isinstance(orig_layer_impl, type) and
+                            hasattr(orig_layer_impl, "get_hidden_heads") else None)
+        if n == 0:
+            raise ValueError("replace_with_kernel_inject: no layer of this model matches an injection policy "
+                             "(supported: BERT/RoBERTa, DistilBERT, GPT-2, GPT-J, GPT-Neo, GPT-NeoX, BLOOM, OPT, LLaMA, "
+                             "InternLM, CLIP, Megatron-GPT); use AutoTP (kernel_inject=False) instead")
+        logger.info(f"kernel injection: {n} transformer layers replaced")
+        return model
     if mp_size <= 1:
         return model
     policies = config.injection_policy_tuple if getattr(config, "injection_policy_tuple", None) else None
@@ -62,8 +129,14 @@ def replace_transformer_layer(orig_layer_impl, model, checkpoint_dict, config, m
 
 
 def revert_transformer_layer(orig_layer_impl, model, config, preln=False):
-    raise NotImplementedError("reverting kernel injection is only meaningful for container-based injection, which this "
-                              "framework replaces with the ragged v2 engine")
+    """Put the client layers back where :func:`replace_transformer_layer` injected fused ones (weights untouched:
+    injection copies, it does not move)."""
+    from .containers import HFLayerAdapter
+    for parent in list(model.modules()):
+        for name, child in list(parent.named_children()):
+            if isinstance(child, HFLayerAdapter) and getattr(child, "_orig_layer", None):
+                setattr(parent, name, child._orig_layer[0])
+    return model
 
 
 def replace_module(model, orig_class, replace_fn, _replace_policy, checkpoint=None):

@@ -53,6 +53,8 @@ class DeepSpeedSelfAttention(nn.Module):
         self.norm_factor = math.sqrt(head_dim)
         if not config.use_mup:
             self.norm_factor = math.sqrt(self.norm_factor)
+        if not getattr(config, "scale_attention", True):
+            self.norm_factor = 1.0                      # GPT-Neo: raw dot products
         if config.scale_attn_by_inverse_layer_idx:
             self.norm_factor *= math.sqrt(config.layer_id + 1)
         self.qkv_func = QKVGemmOp(config)

@@ -108,12 +108,19 @@ class MLPGemmOp(BaseOp):
     def forward(self, input, residual, weight_interm, weight_out, input_bias, bias, gamma, beta):
         c = self.config
         x = input if input_bias is None else input + input_bias
+        if not c.mlp_after_attn:
+            # parallel residual with its own MLP norm (GPT-NeoX): the MLP reads norm(layer input), not the attention sum
+            x, residual = residual, None
         if c.norm_type == NormType.RMSNorm:
             normed, pre = F.rms_norm(x, gamma, c.epsilon, residual=residual)
         else:
             normed, pre = F.layer_norm(x, gamma, beta, c.epsilon, residual=residual)
         inter = _activate(F.linear(normed, _w(weight_interm, self.tm)), bias, c.mlp_act_func_type)
-        return F.linear(inter, _w(weight_out, self.tm)), pre
+        out = F.linear(inter, _w(weight_out, self.tm))
+        if not c.mlp_after_attn:
+            return out, None
+        # the value the final residual adds to: the pre-norm sum for pre-LN blocks, the normed sum for post-LN blocks
+        return out, (pre if c.pre_layer_norm else normed)
 
 
 class GELUGemmOp(BaseOp):
@@ -127,7 +134,7 @@ class ResidualAddOp(BaseOp):
                 residual_add=None):
         c = self.config
         if c.mlp_after_attn:
-            base = residual_add if (residual_add is not None and c.pre_layer_norm) else residual
+            base = residual_add if residual_add is not None else residual
             if residual_add is None and attention_output is not None:
                 base = residual + attention_output + (attention_bias if attention_bias is not None else 0)
             out = hidden_state + base

@@ -1,0 +1,77 @@
+"""``init_inference(..., replace_with_kernel_inject=True)``: every supported architecture's layers are replaced by the
+fused inference layer and the model still produces the HuggingFace outputs (CPU, fp32, random tiny models)."""
+import pytest
+import torch
+
+transformers = pytest.importorskip("transformers")
+from transformers import AutoConfig, AutoModel, AutoModelForCausalLM  # noqa: E402
+
+import shuffle_exchange_b200 as sxb  # noqa: E402
+from shuffle_exchange_b200.module_inject.containers import HFLayerAdapter  # noqa: E402
+
+_C = dict(vocab_size=96, hidden_size=32, num_hidden_layers=2, num_attention_heads=4, max_position_embeddings=64)
+CAUSAL = {
+    "gpt2": dict(model_type="gpt2", vocab_size=96, n_embd=32, n_layer=2, n_head=4, n_positions=64),
+    "opt": dict(model_type="opt", vocab_size=96, hidden_size=32, num_hidden_layers=2, num_attention_heads=4, ffn_dim=64,
+                max_position_embeddings=64, word_embed_proj_dim=32),
+    "llama": dict(model_type="llama", intermediate_size=48, num_key_value_heads=2, **_C),
+    "gptj": dict(model_type="gptj", vocab_size=96, n_embd=32, n_layer=2, n_head=4, n_positions=64, rotary_dim=4),
+    "gpt_neox": dict(model_type="gpt_neox", intermediate_size=64, rotary_pct=0.5, use_parallel_residual=True, **_C),
+    "gpt_neox_seq": dict(model_type="gpt_neox", intermediate_size=64, rotary_pct=1.0, use_parallel_residual=False, **_C),
+    "gpt_neo": dict(model_type="gpt_neo", vocab_size=96, hidden_size=32, num_layers=2, num_heads=4,
+                    attention_types=[[["global"], 2]], max_position_embeddings=64),
+    "bloom": dict(model_type="bloom", vocab_size=96, hidden_size=32, n_layer=2, n_head=4),
+}
+ENCODERS = {
+    "bert": dict(model_type="bert", intermediate_size=64, **_C),
+    "distilbert": dict(model_type="distilbert", vocab_size=96, dim=32, n_layers=2, n_heads=4, hidden_dim=64,
+                       max_position_embeddings=64),
+}
+
+
+def _inject(model):
+    eng = sxb.init_inference(model, dtype=torch.float32, replace_with_kernel_inject=True)
+    n = sum(isinstance(m, HFLayerAdapter) for m in eng.module.modules())
+    assert n == 2, f"expected both layers to be replaced, got {n}"
+    return eng
+
+
+@pytest.mark.parametrize("name", sorted(CAUSAL))
+def test_causal_lm_logits_survive_kernel_injection(name):
+    torch.manual_seed(0)
+    m = AutoModelForCausalLM.from_config(AutoConfig.for_model(**CAUSAL[name])).float().eval()
+    ids = torch.randint(0, 96, (2, 11), generator=torch.Generator().manual_seed(1))
+    with torch.no_grad():
+        ref = m(ids, use_cache=False).logits.clone()
+        eng = _inject(m)
+        out = eng.module(ids, use_cache=False).logits
+    tol = 2e-3                        # the fused layer uses tanh-GELU where some clients use erf-GELU
+    assert (out - ref).abs().max() < tol, (name, float((out - ref).abs().max()))
+
+
+@pytest.mark.parametrize("name", sorted(ENCODERS))
+def test_encoder_hidden_states_survive_kernel_injection(name):
+    torch.manual_seed(0)
+    m = AutoModel.from_config(AutoConfig.for_model(**ENCODERS[name])).float().eval()
+    ids = torch.randint(0, 96, (2, 9), generator=torch.Generator().manual_seed(2))
+    mask = torch.ones(2, 9, dtype=torch.long)
+    mask[1, 6:] = 0                   # padding on the second row exercises the additive mask path
+    with torch.no_grad():
+        ref = m(ids, attention_mask=mask).last_hidden_state.clone()
+        eng = _inject(m)
+        out = eng.module(ids, attention_mask=mask).last_hidden_state
+    keep = mask.bool()
+    assert (out - ref)[keep].abs().max() < 5e-3, (name, float((out - ref)[keep].abs().max()))
+
+
+def test_revert_restores_client_layers_and_unknown_model_is_rejected():
+    from shuffle_exchange_b200.module_inject.replace_module import revert_transformer_layer
+    torch.manual_seed(0)
+    m = AutoModelForCausalLM.from_config(AutoConfig.for_model(**CAUSAL["gpt2"])).float().eval()
+    eng = _inject(m)
+    revert_transformer_layer(None, eng.module, None)
+    assert not any(isinstance(x, HFLayerAdapter) for x in eng.module.modules())
+    assert sum(type(x).__name__ == "GPT2Block" for x in eng.module.modules()) == 2
+    with pytest.raises(ValueError):
+        sxb.init_inference(torch.nn.Sequential(torch.nn.Linear(4, 4)), dtype=torch.float32,
+                           replace_with_kernel_inject=True)
