@@ -1,0 +1,10 @@
+"""Chunked multi-tensor launcher (reference: ``ops/lion/multi_tensor_apply.py``; same helper as ``ops/adam``)."""
+
+
+class MultiTensorApply:
+
+    def __init__(self, chunk_size: int):
+        self.chunk_size = chunk_size
+
+    def __call__(self, op, noop_flag_buffer, tensor_lists, *args):
+        return op(self.chunk_size, noop_flag_buffer, tensor_lists, *args)

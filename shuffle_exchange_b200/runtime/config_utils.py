@@ -121,3 +121,14 @@ def dict_raise_error_on_duplicate_keys(ordered_pairs):
         keys = [key for key, value in counter.items() if value > 1]
         raise ValueError(f"Duplicate keys in DeepSpeed config: {keys}")
     return d
+
+
+class DeepSpeedConfigObject:
+    """Plain attribute bag with a JSON repr — base of the older, hand-parsed config sections (reference
+    ``config_utils.py:176-187``)."""
+
+    def repr(self):
+        return self.__dict__
+
+    def __repr__(self):
+        return json.dumps(self.__dict__, sort_keys=True, indent=4, cls=ScientificNotationEncoder)

@@ -1,0 +1,128 @@
+"""Config sections under their reference import paths, data-efficiency config normalisation, comm call introspection,
+IO staging buffers, launcher helper environment mapping."""
+import os
+
+import pytest
+import torch
+
+
+def test_section_configs_parse_from_the_whole_dictionary():
+    from shuffle_exchange_b200.monitor.config import get_monitor_config
+    from shuffle_exchange_b200.nebula.config import DeepSpeedNebulaConfig
+    from shuffle_exchange_b200.profiling.config import DeepSpeedFlopsProfilerConfig
+    from shuffle_exchange_b200.runtime.activation_checkpointing.config import DeepSpeedActivationCheckpointingConfig
+    from shuffle_exchange_b200.runtime.precision_config import get_bfloat16_config, get_float16_config
+    from shuffle_exchange_b200.utils.config import get_timers_config
+    pd = {"fp16": {"enabled": True, "initial_scale_power": 8, "hysteresis": 3}, "bfloat16": {"enabled": True},
+          "nebula": {"enabled": True, "persistent_storage_path": "/x", "num_of_version_in_retention": 5},
+          "flops_profiler": {"enabled": True, "profile_step": 7},
+          "activation_checkpointing": {"partition_activations": True, "number_checkpoints": 4},
+          "csv_monitor": {"enabled": True, "output_path": "/tmp/o"}, "timers": {"throughput": {"synchronized": False}}}
+    f = get_float16_config(pd)
+    assert f.initial_dynamic_scale() == 256 and f.dynamic_loss_scale_args()["delayed_shift"] == 3
+    assert get_bfloat16_config(pd).enabled                       # the old "bfloat16" spelling is honoured
+    n = DeepSpeedNebulaConfig(pd)
+    assert n.enabled and n.persistent_storage_path == "/x" and n.num_of_version_in_retention == 5 \
+        and n.persistent_time_interval == 100
+    assert DeepSpeedFlopsProfilerConfig(pd).profile_step == 7
+    a = DeepSpeedActivationCheckpointingConfig(pd)
+    assert a.partition_activations and a.number_checkpoints == 4 and not a.cpu_checkpointing
+    m = get_monitor_config(pd)
+    assert m.enabled and m.csv_monitor.output_path == "/tmp/o" and not m.tensorboard.enabled
+    assert not get_timers_config(pd).synchronized and get_timers_config({}).enabled
+    import shuffle_exchange_b200.pipe as pipe
+    from shuffle_exchange_b200 import constants
+    assert pipe.PipelineModule and pipe.LayerSpec and constants.TORCH_DISTRIBUTED_DEFAULT_PORT == 29500
+
+
+def test_data_efficiency_config_is_fully_defaulted():
+    from shuffle_exchange_b200.runtime.data_pipeline import config as dc
+    full = dc.get_data_efficiency_config({})
+    assert full == {"enabled": False, "seed": 1234,
+                    "data_sampling": {"enabled": False, "num_epochs": 1000, "num_workers": 0, "pin_memory": False,
+                                      "curriculum_learning": {"enabled": False},
+                                      "dynamic_batching": {"enabled": False, "lr_scaling_method": "linear",
+                                                           "min_batch_size": 1, "max_batch_size": None,
+                                                           "sequence_picking_order": "dataloader", "verbose": False}},
+                    "data_routing": {"enabled": False, "random_ltd": {"enabled": False,
+                                                                       "layer_token_lr_schedule": {"enabled": False}}}}
+    pd = {"data_efficiency": {"enabled": True, "seed": 7, "data_sampling": {
+        "enabled": True, "num_workers": 2,
+        "curriculum_learning": {"enabled": True, "curriculum_metrics": {"seqlen": {"min_difficulty": 8}}}},
+        "data_routing": {"enabled": True, "random_ltd": {"enabled": True, "total_layer_num": 12,
+                                                          "layer_token_lr_schedule": {"enabled": True}}}}}
+    c = dc.get_data_efficiency_config(pd)
+    assert c["seed"] == 7 and c["data_sampling"]["num_workers"] == 2
+    assert c["data_sampling"]["curriculum_learning"]["curriculum_metrics"]["seqlen"]["min_difficulty"] == 8
+    assert c["data_routing"]["random_ltd"]["total_layer_num"] == 12
+    assert c["data_routing"]["random_ltd"]["layer_token_lr_schedule"]["enabled"]
+    with pytest.raises(ValueError):
+        dc.get_curriculum_learning({"curriculum_learning": {"enabled": True}})
+    with pytest.raises(ValueError):
+        dc.get_dynamic_batching({"dynamic_batching": {"enabled": True}})
+    assert dc.get_curriculum_params_legacy({}) is False
+    assert dc.get_curriculum_params_legacy({"curriculum_learning": {"enabled": True, "curriculum_type": "seqlen"}}) == \
+        {"curriculum_type": "seqlen"}
+
+
+def test_comm_utils_find_the_payload():
+    from shuffle_exchange_b200.comm import utils as cu
+
+    def all_reduce(tensor, op=None, group=None, async_op=False): ...
+    def all_gather(tensor_list, tensor, group=None): ...
+    t = torch.zeros(10, dtype=torch.float32)
+    assert cu.get_tensor_position(all_reduce) == 0 and cu.get_msg_size_from_args(all_reduce, t) == 40
+    assert cu.get_msg_size_from_args(all_reduce, tensor=t.half()) == 20
+    assert cu.get_msg_size_from_args(all_gather, [t, t], t) == 40            # "tensor" is the payload by convention
+    assert cu.get_default_args(all_reduce) == {"op": None, "group": None, "async_op": False}
+    assert cu.get_debug_log_name({"log_name": "x"}, "caller") == "x | [Caller Func: caller]"
+    old = dict(os.environ)
+    try:
+        os.environ.pop("LOCAL_RANK", None); os.environ["OMPI_COMM_WORLD_LOCAL_RANK"] = "3"
+        assert cu.get_local_rank_from_launcher() == 3
+    finally:
+        os.environ.clear(); os.environ.update(old)
+
+
+@pytest.mark.parametrize("kind", ["single", "double"])
+def test_io_buffers_write_every_byte_in_order(tmp_path, kind):
+    from shuffle_exchange_b200.io.double_io_buffer import Double_IO_Buffer
+    from shuffle_exchange_b200.io.single_io_buffer import Single_IO_Buffer
+    from shuffle_exchange_b200.ops.aio import aio_handle
+    h = aio_handle(block_size=4096, queue_depth=4, single_submit=False, overlap_events=True, intra_op_parallelism=1)
+    pinned = torch.empty(8192, dtype=torch.uint8).pin_memory() if torch.cuda.is_available() else torch.empty(8192, dtype=torch.uint8)
+    buf = (Single_IO_Buffer if kind == "single" else Double_IO_Buffer)(pinned, h)
+    data = torch.arange(0, 3000, dtype=torch.int32)               # 12000 bytes: several drains + an unaligned tail
+    path = str(tmp_path / "out.bin")
+    open(path, "wb").close()
+    src_off, file_off = 0, 0
+    total = data.numel() * 4
+    while src_off < total:
+        src_off += buf.fill(data, src_off)
+        if buf.is_full() or src_off == total:
+            n = buf.get_aligned_num_bytes()
+            if n:
+                buf.drain(n, path, file_off)
+                file_off += n
+    buf.complete_ongoing_drain()
+    tail = buf.get_unaligned_num_bytes()
+    assert tail == total % 1024 == buf.get_offset()
+    with open(path, "r+b") as f:
+        f.seek(file_off)
+        f.write(buf.get_buffer()[:tail].numpy().tobytes())
+    got = torch.frombuffer(bytearray(open(path, "rb").read()), dtype=torch.int32)
+    assert torch.equal(got, data)
+    buf.reset()
+    assert buf.is_empty()
+
+
+def test_launcher_helper_maps_mpi_environment():
+    from shuffle_exchange_b200.launcher import launcher_helper as lh
+    a = lh.parse_args(["--launcher", "mpich", "--module", "train.py", "--lr", "1"])
+    assert a.launcher == "mpich" and a.module and a.user_script == "train.py" and a.user_args == ["--lr", "1"]
+    env = lh.env_mapping({"PMI_RANK": "5", "MPI_LOCALRANKID": "1"}, ["PMI_RANK"], ["MPI_LOCALRANKID"])
+    assert env["RANK"] == "5" and env["LOCAL_RANK"] == "1"
+    with pytest.raises(EnvironmentError):
+        lh.env_mapping({"A": "1", "B": "2", "L": "0"}, ["A", "B"], ["L"])
+    with pytest.raises(EnvironmentError):
+        lh.env_mapping({}, ["A"], ["L"])
