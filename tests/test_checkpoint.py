@@ -162,3 +162,35 @@ def _universal_worker(rank, world, tmp):
 def test_universal_checkpoint_roundtrip(tmp_path):
     from conftest import run_dist
     run_dist(_universal_worker, 2, (str(tmp_path),))
+
+
+def test_2d_and_3d_layout_reshape_and_zero_checkpoint_merge(tmp_path):
+    import torch
+    from shuffle_exchange_b200.checkpoint import (ZeROCheckpoint, get_model_3d_descriptor, get_mpu_ranks,
+                                                  model_3d_desc, reshape_meg_2d_parallel)
+    m = reshape_meg_2d_parallel(old_pp_degree=2, old_tp_degree=4, new_pp_degree=1, new_tp_degree=2)
+    assert m.get_data(0, 0) == [0, 1, 4, 5] and m.get_data(0, 1) == [2, 3, 6, 7]
+    tp, pp, dp = get_mpu_ranks(tp_size=2, pp_size=2, dp_size=2)
+    assert tp == [[0, 1], [2, 3], [4, 5], [6, 7]] and pp == [[0, 4], [1, 5], [2, 6], [3, 7]]
+    assert dp == [[0, 2], [1, 3], [4, 6], [5, 7]]
+    src = model_3d_desc(pp_degree=1, tp_degree=2, dp_degree=4)
+    ok, errs = src.can_reshape(model_3d_desc(1, 4, 1))
+    assert not ok and "TP" in errs[0]
+    maps = src.reshape(model_3d_desc(1, 1, 2))
+    assert len(maps) == 2 and maps[0].get_data(0, 0) == [0, 1, 2, 3] and maps[1].get_data(0, 0) == [4, 5, 6, 7]
+    # a folder with tp=1, pp=1, dp=4 ZeRO files: merge to dp=2 concatenates the flat partitions without their padding
+    for r in range(4):
+        torch.save({"module": {}}, tmp_path / "mp_rank_00_model_states.pt")
+        sd = {"optimizer_state_dict": {"base_optimizer_state": {"state": {0: {"exp_avg": torch.full((6,), float(r))}}},
+                                       "group_paddings": [2], "partition_count": [4]}}
+        torch.save(sd, tmp_path / f"zero_pp_rank_{r}_mp_rank_00_optim_states.pt")
+    d = get_model_3d_descriptor(str(tmp_path))
+    assert (d.pp_degree, d.tp_degree, d.dp_degree) == (1, 1, 4)
+    z = ZeROCheckpoint(str(tmp_path))
+    assert z.get_src_dp_degree() == 4 and len(z.get_files_for_rank(0, 0, 3)) == 1
+    z.reshape(model_3d_desc(1, 1, 2))
+    assert [f.split("zero_pp_rank_")[1][0] for f in z.get_files_for_rank(0, 0, 1)] == ["2", "3"]
+    st = z.get_state_for_rank(0, 0, 1)
+    ea = st["optimizer_state_dict"]["base_optimizer_state"]["state"][0]["exp_avg"]
+    assert ea.tolist() == [2.0] * 4 + [3.0] * 4
+    assert st["optimizer_state_dict"]["partition_count"] == [2] and st["optimizer_state_dict"]["group_paddings"] == [0]

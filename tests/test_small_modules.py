@@ -126,3 +126,22 @@ def test_launcher_helper_maps_mpi_environment():
         lh.env_mapping({"A": "1", "B": "2", "L": "0"}, ["A", "B"], ["L"])
     with pytest.raises(EnvironmentError):
         lh.env_mapping({}, ["A"], ["L"])
+
+
+def _backend_obj(rank, world):
+    from shuffle_exchange_b200.comm.torch import TorchBackend
+    cdb = TorchBackend(backend="gloo")
+    assert cdb.is_initialized() and cdb.get_world_size() == world and cdb.get_rank() == rank
+    t = torch.full((4,), float(rank + 1))
+    cdb.all_reduce(t)
+    assert t.tolist() == [3.0] * 4
+    out = torch.empty(8)
+    cdb.all_gather_into_tensor(out, torch.full((4,), float(rank)))
+    assert out.tolist() == [0.0] * 4 + [1.0] * 4
+    g = cdb.new_group([0, 1])
+    assert cdb.get_all_ranks_from_group(g) == [0, 1] and cdb.has_all_gather_into_tensor()
+
+
+def test_torch_backend_object_forwards_to_the_facade():
+    from conftest import run_dist
+    run_dist(_backend_obj, world=2)
