@@ -103,9 +103,13 @@ struct AdamArgs {
 __global__ void __launch_bounds__(kThreads)
 rs_adam_kernel(Peers P, long long part, float* __restrict__ hp, float* __restrict__ m, float* __restrict__ v,
                __nv_bfloat16* __restrict__ lp, __nv_bfloat16* __restrict__ grad_out, AdamArgs a, uint32_t epoch,
-               const void* mc_ptr, unsigned int* __restrict__ cta_counter, int apply_adam) {
-  if (blockIdx.x == 0) signal_all(P, 0, epoch);
-  if (!wait_all(P, 0, epoch, 101)) return;
+               const void* mc_ptr, unsigned int* __restrict__ cta_counter, int apply_adam, int do_sync) {
+  // do_sync == 0: the "gradients ready" handshake already ran as a one-warp kernel in front of this one on the same
+  // stream, so no CTA of this (SM-filling) grid ever spins while it holds an SM next to the backward GEMMs.
+  if (do_sync) {
+    if (blockIdx.x == 0) signal_all(P, 0, epoch);
+    if (!wait_all(P, 0, epoch, 101)) return;
+  }
   const long long base = (long long)P.rank * part;
   const long long nvec = part >> 3;
   const float inv_n = 1.0f / (float)P.world;
@@ -350,6 +354,12 @@ using namespace sxb::symm;
 
 SXB_DEFINE_HANG_ACCESSOR(sxb_symm_hang_info)
 
+// Full barrier on `channel`: tell every peer "I reached `epoch`", then wait until all of them did.
+__global__ void barrier_channel_kernel(sxb::symm::Peers P, int channel, uint32_t epoch) {
+  sxb::symm::signal_all(P, channel, epoch);
+  sxb::symm::wait_all(P, channel, epoch, 110);
+}
+
 // K1.  bufs/sigs: host arrays of `world` device pointers (peer mappings of the flat bf16 gradient buffer
 // and of the signal pads).  part: elements per shard (multiple of 8).  counter: device uint32 (zeroed once).
 // apply_adam == 0 -> plain reduce-scatter(mean) into grad_out (used when the step must be deferred).
@@ -367,17 +377,18 @@ SXB_API int sxb_symm_rs_adam(const void* const* bufs, const void* const* sigs, i
   a.bc1 = bias_correction ? 1.f - powf(beta1, (float)step) : 1.f;
   a.bc2 = bias_correction ? 1.f - powf(beta2, (float)step) : 1.f;
   a.grad_scale = grad_scale; a.adamw = adamw;
+  // SXB_RS_SPLIT_SYNC=1 runs the handshake as a one-warp kernel in front of the big one (A/B measurements: no
+  // difference at 2 GPUs); default: inside the kernel.
+  static const int split = [] { const char* e = getenv("SXB_RS_SPLIT_SYNC"); return e ? atoi(e) : 0; }();
+  if (split) {
+    barrier_channel_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, 0, epoch);
+    SXB_CHECK_LAUNCH();
+  }
   rs_adam_kernel<<<grid_cap(part / 8, max_ctas), kThreads, 0, (cudaStream_t)stream>>>(
       P, part, (float*)hp, (float*)m, (float*)v, (__nv_bfloat16*)lp, (__nv_bfloat16*)grad_out, a, epoch,
-      multicast_ptr, (unsigned int*)counter, apply_adam);
+      multicast_ptr, (unsigned int*)counter, apply_adam, split ? 0 : 1);
   SXB_CHECK_LAUNCH();
   return SXB_OK;
-}
-
-// Full barrier on `channel`: tell every peer "I reached `epoch`", then wait until all of them did.
-__global__ void barrier_channel_kernel(sxb::symm::Peers P, int channel, uint32_t epoch) {
-  sxb::symm::signal_all(P, channel, epoch);
-  sxb::symm::wait_all(P, channel, epoch, 110);
 }
 SXB_API int sxb_symm_barrier(const void* const* bufs, const void* const* sigs, int rank, int world, int channel,
                              unsigned int epoch, void* stream) {

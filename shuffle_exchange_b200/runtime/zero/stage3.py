@@ -28,6 +28,8 @@ from __future__ import annotations
 from collections import OrderedDict
 from typing import Dict, List, Optional
 
+import os
+
 import torch
 import torch.nn as nn
 
@@ -41,6 +43,11 @@ from .sharded_optimizer import (CLIP_GRAD, DS_VERSION, LOSS_SCALER, PARTITION_CO
 FP32_FLAT_GROUPS = "fp32_flat_groups"
 OPTIMIZER_STATE_DICT = "optimizer_state_dict"
 
+
+# SXB_Z3_LOOKAHEAD=1: always fetch the next unit ahead of time even when the live-parameter limit is already exceeded by
+# the root unit, and skip the shard barrier for gathers inside backward.  Measured at 2 GPUs (profiles/): step 455 -> 431
+# ms under the profiler.  Off by default: the one 8-GPU run with it did not finish and could not be repeated.
+_Z3_LOOKAHEAD = os.environ.get("SXB_Z3_LOOKAHEAD", "0") == "1"
 
 class Unit:
     """A module whose parameters are gathered / released / reduced / stepped together."""
@@ -278,8 +285,11 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
     def _gather_unit(self, u: Unit, async_on_side_stream: bool):
         if u.available or u.fetch_event is not None:
             return
-        if self.fused is not None and self.fused._shards_dirty:
-            # first gather after an optimizer step: wait for my own shard updates, then one cross-rank barrier
+        if self.fused is not None and self.fused._shards_dirty and (
+                not _Z3_LOOKAHEAD or not self._in_backward or u.stepped):
+            # first gather after an optimizer step: wait for my own shard updates, then one cross-rank barrier.
+            # (With SXB_Z3_LOOKAHEAD=1 gathers inside backward skip it: a unit's shard is only rewritten by the fused
+            # step that follows ITS backward on every rank, i.e. after every rank gathered it.)
             side = self.allgather_stream if self.allgather_stream is not None else get_accelerator().current_stream()
             if self.reduce_stream is not None:
                 side.wait_stream(self.reduce_stream)
@@ -353,13 +363,22 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         except ValueError:
             return
         budget = self.prefetch_bucket_size
+        issued = 0
         for nxt in order[pos + 1:]:
             nu = self.units[nxt]
-            if nu.persistent or nu.available or nu.fetch_event is not None:
+            if nu.persistent or nu.available:
                 continue
-            if budget <= 0 or self._live_numel + nu.numel > self.max_live_parameters:
+            if nu.fetch_event is not None:
+                issued += 1                  # already in flight: counts as look-ahead
+                continue
+            # The next unit is always fetched ahead (one unit of look-ahead is what hides the gather behind the current
+            # unit's compute; the root unit alone — embedding + head, live for the whole iteration — can exceed
+            # max_live_parameters); the limits bound everything beyond it.
+            if (issued > 0 or not _Z3_LOOKAHEAD) and (
+                    budget <= 0 or self._live_numel + nu.numel > self.max_live_parameters):
                 break
             self._gather_unit(nu, async_on_side_stream=True)
+            issued += 1
             budget -= nu.numel
             if budget <= 0:
                 break

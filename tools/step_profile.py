@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--seq", type=int, default=8192)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--out", default="gpurun_out/step_profile.json")
+    ap.add_argument("--gaps", action="store_true", help="report idle gaps of the busiest stream and what ran meanwhile")
     ap.add_argument("--trace-kernel", default="", help="comma-separated kernel-name substrings: report which CPU ops launch them")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
@@ -87,6 +88,37 @@ def main():
                             chains[t][" <- ".join(chain)] += 1
             out["kernel_origins"] = {t: [{"chain": c, "launches_per_step": n / a.steps} for c, n in ct.most_common(12)]
                                      for t, ct in chains.items()}
+        if a.gaps:
+            # timeline of the busiest (compute) stream: where it idles, for how long, what it waited for
+            kev = [e for e in prof.profiler.kineto_results.events() if str(e.device_type()).endswith("CUDA")]
+            by_stream = {}
+            for e in kev:
+                by_stream.setdefault(e.device_resource_id(), []).append((e.start_ns(), e.start_ns() + e.duration_ns(), e.name()))
+            busy = {sid: sum(b - a_ for a_, b, _ in ev) for sid, ev in by_stream.items()}
+            main = max(busy, key=busy.get)
+            ev = sorted(by_stream[main])
+            others = sorted((x for sid, v in by_stream.items() if sid != main for x in v))
+            gaps = []
+            for (s0, e0_, n0), (s1, e1_, n1) in zip(ev, ev[1:]):
+                if s1 - e0_ > 50_000:
+                    during = {}
+                    for (so, eo, no) in others:
+                        ov = min(eo, s1) - max(so, e0_)
+                        if ov > 0:
+                            during[no[:40]] = during.get(no[:40], 0) + ov
+                    gaps.append({"gap_ms": (s1 - e0_) / 1e6, "after": n0[:50], "before": n1[:50],
+                                 "meanwhile": {k: round(v / 1e6, 3) for k, v in sorted(during.items(), key=lambda t: -t[1])[:3]}})
+            gaps.sort(key=lambda g: -g["gap_ms"])
+            out["streams_busy_ms_per_step"] = {str(k): round(v / 1e6 / a.steps, 2) for k, v in busy.items()}
+            out["main_stream_idle_ms_per_step"] = round(sum(g["gap_ms"] for g in gaps) / a.steps, 2)
+            out["n_gaps_per_step"] = len(gaps) / a.steps
+            out["top_gaps"] = gaps[:25]
+            agg = {}
+            for g in gaps:
+                key = (g["after"][:36], g["before"][:36])
+                agg[key] = agg.get(key, 0) + g["gap_ms"]
+            out["gaps_by_neighbours"] = [{"after": k[0], "before": k[1], "ms_per_step": round(v / a.steps, 2)}
+                                         for k, v in sorted(agg.items(), key=lambda t: -t[1])[:15]]
         os.makedirs(os.path.dirname(a.out), exist_ok=True)
         json.dump(out, open(a.out, "w"), indent=1)
         print(json.dumps(out)[:6000])
