@@ -75,3 +75,49 @@ def test_revert_restores_client_layers_and_unknown_model_is_rejected():
     with pytest.raises(ValueError):
         sxb.init_inference(torch.nn.Sequential(torch.nn.Linear(4, 4)), dtype=torch.float32,
                            replace_with_kernel_inject=True)
+
+
+def test_container_features_meta_load_and_hybrid_lora_refresh():
+    from shuffle_exchange_b200.inference.config import DeepSpeedInferenceConfig
+    from shuffle_exchange_b200.module_inject.containers import DS_LLAMAContainer, LLAMALayerPolicy
+    from shuffle_exchange_b200.module_inject.containers.features import HybridGatedMLPContainer, MetaTensorContainer
+    torch.manual_seed(0)
+    cfg = AutoConfig.for_model(**CAUSAL["llama"])
+    m = AutoModelForCausalLM.from_config(cfg).float().eval()
+    layer = m.model.layers[0]
+    sd = {"model.layers.0." + k: v.clone() for k, v in layer.state_dict().items()}
+    with torch.device("meta"):
+        meta_layer = type(layer)(cfg, 0)
+
+    class MetaLlama(MetaTensorContainer, DS_LLAMAContainer):
+        pass
+
+    icfg = DeepSpeedInferenceConfig(dtype=torch.float32)
+    c = MetaLlama(LLAMALayerPolicy(meta_layer), icfg, cfg, 0, meta_layer)
+    assert c.is_meta
+    with pytest.raises(RuntimeError):
+        c.initialize_tensors()
+    c.load_params(sd, prefix="model.layers.0.")
+    assert not c.is_meta
+    c.create_ds_model_config(); c.initialize_tensors(); fused = c.create_module()
+    assert torch.allclose(fused.attention.attn_ow.t(), layer.self_attn.o_proj.weight)
+
+    class HybridLlama(HybridGatedMLPContainer, DS_LLAMAContainer):
+        pass
+
+    # LoRA on the client's down projection: fold -> refresh -> fused layer carries the merged weight; unfold restores
+    down = layer.mlp.down_proj
+    down.lora_right_weight = torch.nn.Parameter(torch.randn(down.in_features, 2) * 0.1)
+    down.lora_left_weight = torch.nn.Parameter(torch.randn(2, down.out_features) * 0.1)
+    down.lora_scaling = 0.5
+    h = HybridLlama(LLAMALayerPolicy(layer), icfg, cfg, 0, layer)
+    h.create_ds_model_config(); h.initialize_tensors(); fused = h.create_module()
+    assert len(h.lora_params) == 1 and len(h.get_lora_params()) == 2
+    before = down.weight.data.clone()
+    h.fuse_lora(); h.refresh()
+    merged = before + 0.5 * (down.lora_left_weight.t() @ down.lora_right_weight.t())
+    assert torch.allclose(fused.mlp.output_w.t(), merged, atol=1e-6)
+    h.unfuse_lora(); h.transform_for_inference()
+    assert torch.allclose(fused.mlp.output_w.t(), before, atol=1e-6)
+    up, gate = h.set_mlp_gate()
+    assert torch.equal(fused.mlp.inter_w.t(), torch.cat([up, gate], 0))
