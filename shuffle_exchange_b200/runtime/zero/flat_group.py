@@ -22,6 +22,8 @@ from __future__ import annotations
 import math
 from typing import Dict, List, Optional
 
+import os
+
 import torch
 
 from ...comm import comm as dist
@@ -32,6 +34,8 @@ ALIGN = 64  # elements: keeps every parameter 128-byte aligned for TMA/vector ac
 def _align(n: int, a: int) -> int:
     return (n + a - 1) // a * a
 
+
+_POISON_RELEASED = os.environ.get("SXB_DEBUG_POISON", "0") == "1"
 
 class FlatGroup:
     def __init__(self, params: List[torch.nn.Parameter], names: List[str], world: int, rank: int, process_group,
@@ -122,6 +126,11 @@ class FlatGroup:
         """Free the gathered buffer (ZeRO-3); parameters become empty placeholders."""
         if self.keep_full_params:
             return
+        if _POISON_RELEASED and self.flat_lp is not None and self.flat_lp.is_floating_point():
+            # debug build (SXB_DEBUG_POISON=1): a released gathered buffer is overwritten with NaN before it goes back
+            # to the allocator, so a kernel that still reads it (missing stream wait, stale view) poisons the loss
+            # instead of silently using old-but-plausible weights
+            self.flat_lp.fill_(float("nan"))
         self.flat_lp = None
         for p in self.params:
             p.data = torch.empty(0, dtype=self.lp_dtype, device=self.device)

@@ -145,3 +145,46 @@ def _backend_obj(rank, world):
 def test_torch_backend_object_forwards_to_the_facade():
     from conftest import run_dist
     run_dist(_backend_obj, world=2)
+
+
+def test_flag_protocol_checker_invariants():
+    from shuffle_exchange_b200.comm.symm_check import MAX_PEERS, PadMonitor, check_pad
+    world = 4
+    def pad(rows):        # rows: {channel: [values per peer]}
+        p = [0] * (8 * MAX_PEERS)
+        for c, vals in rows.items():
+            for i, v in enumerate(vals):
+                p[c * MAX_PEERS + i] = v
+        return p
+    epochs = [5, 5, 0, 0, 2, 0, 0, 0]
+    assert check_pad(pad({0: [5, 5, 6, 5], 1: [5, 5, 5, 5], 4: [2, 2, 2, 2]}), epochs, world) == []
+    v = check_pad(pad({0: [5, 4, 5, 5]}), epochs, world, channels=[0])
+    assert len(v) == 1 and v[0].rule == "completed waits" and v[0].peer == 1
+    v = check_pad(pad({0: [5, 5, 8, 5]}), epochs, world, channels=[0])
+    assert [x.rule for x in v] == ["bounded lead"] and "grads_ready" in str(v[0])
+    v = check_pad(pad({0: [5, 5, 5, 5]}), epochs, world, prev=pad({0: [5, 6, 5, 5]}), channels=[0])
+    assert [x.rule for x in v] == ["no regress"]
+    v = check_pad(pad({4: [2, 2, 3, 2]}), epochs, world, quiescent=True, channels=[4])
+    assert [x.rule for x in v] == ["quiescent agreement"]
+    # wrap-around: 0xFFFFFFFF -> 0 is an advance, not a regress
+    assert check_pad(pad({0: [0, 0, 0, 0]}), [0] * 8, world, prev=pad({0: [0xFFFFFFFF] * 4}), channels=[0]) == []
+
+    from types import SimpleNamespace
+    Buf = SimpleNamespace(epochs=epochs, world=world)
+    mon = PadMonitor()
+    assert mon.check(Buf, pad=pad({0: [5, 5, 5, 5], 1: [5] * 4, 4: [2] * 4})) == []
+    with pytest.raises(AssertionError):
+        mon.check(Buf, pad=pad({0: [5, 5, 4, 5], 1: [5] * 4, 4: [2] * 4}))
+
+
+def test_released_parameters_are_poisoned_in_debug_mode(monkeypatch):
+    from shuffle_exchange_b200.runtime.zero import flat_group as fgm
+    monkeypatch.setattr(fgm, "_POISON_RELEASED", True)
+    p = torch.nn.Parameter(torch.ones(8))
+    fg = fgm.FlatGroup([p], ["w"], world=1, rank=0, process_group=None, device=torch.device("cpu"),
+                       lp_dtype=torch.float32, keep_full_params=False)
+    if fg.flat_lp is None:
+        fg.allocate_full()
+    stale = fg.flat_lp
+    fg.release_params()
+    assert torch.isnan(stale).all() and fg.flat_lp is None
