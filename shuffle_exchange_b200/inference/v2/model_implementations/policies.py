@@ -246,6 +246,32 @@ class FalconPolicy(InferenceV2Policy):
         self._extra_used_layer = used
 
 
+# The same architectures assembled through the declarative containers (``containers.py``); selectable with
+# ``engine_factory`` keyword ``use_containers=True`` or by instantiating these classes directly.
+from .containers import (ContainerPolicyMixin, FalconNewArchTransformerContainer, FalconNonTransformerContainer,  # noqa: E402
+                         Llama2NonTransformerContainer, Llama2TransformerContainer, MixtralNonTransformerContainer,
+                         MixtralTransformerContainer, OPTNonTransformerContainer, OPTTransformerContainer)
+
+
+class Llama2ContainerPolicy(ContainerPolicyMixin, Llama2Policy):
+    transformer_container, non_transformer_container = Llama2TransformerContainer, Llama2NonTransformerContainer
+
+
+class MixtralContainerPolicy(ContainerPolicyMixin, MixtralPolicy):
+    transformer_container, non_transformer_container = MixtralTransformerContainer, MixtralNonTransformerContainer
+
+
+class OPTContainerPolicy(ContainerPolicyMixin, OPTPolicy):
+    transformer_container, non_transformer_container = OPTTransformerContainer, OPTNonTransformerContainer
+
+
+class FalconNewArchContainerPolicy(ContainerPolicyMixin, FalconPolicy):
+    transformer_container, non_transformer_container = FalconNewArchTransformerContainer, FalconNonTransformerContainer
+
+
+CONTAINER_POLICIES = {"llama": Llama2ContainerPolicy, "mistral": Llama2ContainerPolicy, "qwen2": Llama2ContainerPolicy,
+                      "mixtral": MixtralContainerPolicy, "opt": OPTContainerPolicy}
+
 POLICIES = {"llama": Llama2Policy, "mistral": MistralPolicy, "mixtral": MixtralPolicy, "falcon": FalconPolicy,
             "opt": OPTPolicy, "phi": PhiPolicy, "phi3": Phi3Policy, "qwen": QwenPolicy, "qwen2": Qwen2Policy,
             "qwen2_moe": Qwen2MoePolicy}

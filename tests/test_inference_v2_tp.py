@@ -141,3 +141,80 @@ def _tp_serialize(rank, world, path):
 
 def test_serialize_and_reload_per_rank_flat_checkpoint(tmp_path):
     run_dist(_tp_serialize, world=2, args=(str(tmp_path),))
+
+
+def test_parameter_dsl_assembles_in_any_order_and_reports_gaps():
+    from types import SimpleNamespace
+    from shuffle_exchange_b200.inference.v2.model_implementations.common_parameters import (
+        GQAMegatronQKVParameter, UnfusedMoEGatedMLPParameter, UnfusedQKVParameter)
+    from shuffle_exchange_b200.inference.v2.model_implementations.containers import (Llama2TransformerContainer,
+                                                                                      MixtralTransformerContainer)
+    from shuffle_exchange_b200.inference.v2.model_implementations.layer_container_base import LayerContainer
+    model = SimpleNamespace(n_experts=2, n_heads=4, n_heads_kv=2, head_size=2)
+    p = UnfusedQKVParameter(model)
+    p.v_params = torch.full((2, 3), 3.0); p.q_params = torch.full((4, 3), 1.0)
+    assert not p.is_complete
+    p.k_params = torch.full((2, 3), 2.0)
+    assert p.is_complete and p.value[:, 0].tolist() == [1.0] * 4 + [2.0] * 2 + [3.0] * 2
+    with pytest.raises(ValueError):
+        p.q_params = torch.zeros(1)
+    moe = UnfusedMoEGatedMLPParameter(model)
+    moe.up_experts[1] = torch.full((2, 3), 4.0); moe.gating_experts[0] = torch.full((2, 3), 1.0)
+    moe.gating_experts[1] = torch.full((2, 3), 3.0); moe.up_experts[0] = torch.full((2, 3), 2.0)
+    assert moe.value.shape == (2, 4, 3) and moe.value[:, :, 0].tolist() == [[1.0, 1.0, 2.0, 2.0], [3.0, 3.0, 4.0, 4.0]]
+    # grouped rows [kv group][q0 q1 k v] -> q|k|v
+    g = GQAMegatronQKVParameter(model)
+    rows = torch.arange(2 * 4 * 2).float().view(-1, 1)          # 2 groups x (2 q + k + v) x head_size 2
+    g.params = rows
+    assert g.value.view(-1).tolist() == [0, 1, 2, 3, 8, 9, 10, 11, 4, 5, 12, 13, 6, 7, 14, 15]
+    c = Llama2TransformerContainer(model)
+    assert c.n_params == 7 and not c.is_populated and "qkv_b" not in c.unfinished() and c.qkv_w is None
+    assert not c.set_dependency("self_attn.rotary_emb.inv_freq", torch.zeros(1))
+    for n in ("q", "k", "v"):
+        assert c.set_dependency(f"self_attn.{n}_proj.weight", torch.zeros(2, 3))
+    assert c.qkv_w.shape == (6, 3) and c.unfinished() == ["attn_out_w", "mlp_1_w", "mlp_2_w", "attn_norm_gamma",
+                                                          "mlp_norm_gamma"]
+    mc = MixtralTransformerContainer(model)
+    assert mc.set_dependency("block_sparse_moe.experts.1.w2.weight", torch.zeros(3, 2)) and mc.moe_mlp_2 is None
+    mc.set_dependency("block_sparse_moe.experts.0.w2.weight", torch.zeros(3, 2))
+    assert mc.moe_mlp_2.shape == (2, 3, 2) and mc.to_layer_weights()["moe_w2"] is mc.moe_mlp_2
+    with pytest.raises(TypeError):
+        class Bad(LayerContainer):
+            qkv_w: UnfusedQKVParameter
+            PARAM_MAPPING = {"x": "qkv_w.nope"}
+
+
+@pytest.mark.parametrize("name", ["llama", "mixtral", "opt"])
+def test_container_policy_builds_the_same_weights_as_the_rule_policy(name, tmp_path):
+    transformers = pytest.importorskip("transformers")
+    from transformers import AutoConfig, AutoModelForCausalLM
+    from shuffle_exchange_b200.inference.v2.checkpoint import HuggingFaceCheckpointEngine
+    from shuffle_exchange_b200.inference.v2.config_v2 import RaggedInferenceEngineConfig
+    from shuffle_exchange_b200.inference.v2.engine_v2 import InferenceEngineV2
+    from shuffle_exchange_b200.inference.v2.model_implementations.policies import CONTAINER_POLICIES, POLICIES
+    common = dict(vocab_size=96, hidden_size=32, num_hidden_layers=2, num_attention_heads=4, max_position_embeddings=64)
+    cfgs = {"llama": dict(model_type="llama", intermediate_size=64, num_key_value_heads=2, **common),
+            "mixtral": dict(model_type="mixtral", intermediate_size=64, num_key_value_heads=2, num_local_experts=4,
+                            num_experts_per_tok=2, **common),
+            "opt": dict(model_type="opt", ffn_dim=64, word_embed_proj_dim=32, **common)}
+    torch.manual_seed(0)
+    m = AutoModelForCausalLM.from_config(AutoConfig.for_model(**cfgs[name])).float().eval()
+    m.save_pretrained(str(tmp_path), safe_serialization=True)       # per-expert tensors on disk
+    a = POLICIES[name](m.config, checkpoint_engine=HuggingFaceCheckpointEngine(str(tmp_path)))
+    b = CONTAINER_POLICIES[name](m.config, checkpoint_engine=HuggingFaceCheckpointEngine(str(tmp_path)))
+    a.dtype_override = b.dtype_override = torch.float32
+    wa, wb = a.load_weights(), b.load_weights()
+    assert set(k for k in wa if k != "layers") == set(k for k in wb if k != "layers")
+    for k in wa:
+        if k != "layers":
+            assert torch.equal(wa[k], wb[k]), k
+    for la, lb in zip(wa["layers"], wb["layers"]):
+        assert set(la) == set(lb), (sorted(la), sorted(lb))
+        for k in la:
+            assert torch.equal(la[k], lb[k]), k
+    b._engine_config = RaggedInferenceEngineConfig()
+    eng = InferenceEngineV2(b, b._engine_config)
+    ids = torch.randint(0, 96, (1, 7), generator=torch.Generator().manual_seed(3))
+    with torch.no_grad():
+        ref = m(ids).logits[0, -1]
+    assert (eng.put([1], [ids[0]])[0] - ref).abs().max() < 1e-4
