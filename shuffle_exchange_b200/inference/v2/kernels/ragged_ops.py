@@ -107,3 +107,151 @@ def paged_attention(q: torch.Tensor, cache: torch.Tensor, tok_seq: torch.Tensor,
         p = torch.softmax(s, dim=-1)
         out[t] = torch.einsum("hn,nhd->hd", p, v).to(q.dtype)
     return out
+
+
+# ================================================================================================ class interface
+# The reference exposes every ragged kernel as a small callable object constructed once per model with the static
+# shape information (``inference/v2/kernels/ragged_ops/*``); these are those objects over the functions above.  All of
+# them take the :class:`RaggedBatchWrapper` where the reference does.
+
+def get_q_block_size(head_size: int) -> int:
+    """Query rows per attention atom (reference ``ragged_ops/blocked_flash``: larger tiles for smaller heads)."""
+    return 128 if head_size <= 64 else 64
+
+
+def get_kv_block_size(head_size: int) -> int:
+    return 128 if head_size <= 128 else 64
+
+
+class RaggedEmbeddingKernel:
+    """``ragged_ops/embed``: token (+ learned position) embedding of a ragged batch."""
+    supported_dtypes = (torch.float16, torch.bfloat16, torch.float32)
+
+    def __init__(self, embed_dtype: torch.dtype, token_dtype: torch.dtype, embed_dim: int):
+        if embed_dtype not in self.supported_dtypes:
+            raise ValueError(f"Unsupported embedding data type: {embed_dtype}")
+        if token_dtype not in (torch.int32, torch.int64):
+            raise ValueError(f"Unsupported token data type: {token_dtype}")
+        if embed_dim % (16 // torch.tensor([], dtype=embed_dtype).element_size()) != 0:
+            raise ValueError(f"Embedding dimension {embed_dim} must be a multiple of 16 bytes")
+        self.embed_dim = embed_dim
+
+    def __call__(self, embedded_tokens: torch.Tensor, ragged_wrapper, embedding_weight: torch.Tensor,
+                 position_embed_weight: torch.Tensor = None, position_embed_offset: int = 0) -> torch.Tensor:
+        n = ragged_wrapper.current_tokens
+        out = ragged_embed(ragged_wrapper.input_ids()[:n], embedding_weight,
+                           ragged_wrapper.token_positions()[:n] if position_embed_weight is not None else None,
+                           position_embed_weight, position_embed_offset)
+        embedded_tokens[:n].copy_(out)
+        return embedded_tokens
+
+
+class RaggedLogitsGather:
+    """``ragged_ops/logits_gather``: hidden state of the last token of every sequence."""
+
+    def __init__(self, model_dim: int, fp_dtype: torch.dtype):
+        self.model_dim = model_dim
+
+    def __call__(self, final_token_activations: torch.Tensor, all_activations: torch.Tensor, ragged_wrapper):
+        n = ragged_wrapper.current_sequences
+        final_token_activations[:n].copy_(logits_gather(all_activations, ragged_wrapper.last_token_index()[:n]))
+        return final_token_activations
+
+
+class BlockedRotaryEmbeddings:
+    """``ragged_ops/linear_blocked_kv_rotary``: rotate q/k in place (frequencies from ``theta_base``) and append k/v to
+    the paged cache."""
+
+    def __init__(self, head_size: int, n_q_heads: int, n_kv_heads: int, dtype: torch.dtype, rotary_dim: int,
+                 theta_base: float):
+        if head_size not in (64, 80, 96, 128):
+            raise ValueError(f"Unsupported head size: {head_size}")
+        if n_q_heads % n_kv_heads:
+            raise ValueError("query heads must be a multiple of key/value heads")
+        self.head_size, self.n_q, self.n_kv = head_size, n_q_heads, n_kv_heads
+        self.rotary_dim, self.theta_base = rotary_dim, theta_base
+
+    def __call__(self, kv_cache: torch.Tensor, qkv: torch.Tensor, ragged_batch) -> None:
+        n = ragged_batch.current_tokens
+        kv_rotary_blocked(qkv[:n], kv_cache, ragged_batch.token_to_seq()[:n], ragged_batch.token_positions()[:n],
+                          ragged_batch.block_tables(), self.n_q, self.n_kv, self.head_size, self.rotary_dim,
+                          self.theta_base)
+
+
+class BlockedTrainedRotaryEmbeddings(BlockedRotaryEmbeddings):
+    """Same with an explicit inverse-frequency table: accepted when it equals ``theta ** (-2i/d)`` (the kernels
+    regenerate frequencies from theta), otherwise refused loudly."""
+
+    def __init__(self, head_size: int, n_q_heads: int, n_kv_heads: int, dtype: torch.dtype):
+        super().__init__(head_size, n_q_heads, n_kv_heads, dtype, head_size, 10000.0)
+
+    def __call__(self, kv_cache, qkv, ragged_batch, inverse_freqs: torch.Tensor) -> None:
+        d = inverse_freqs.numel() * 2
+        theta = float(inverse_freqs[1].item() ** (-d / 2.0)) if inverse_freqs.numel() > 1 else self.theta_base
+        expect = theta ** (-torch.arange(0, d, 2, dtype=torch.float32, device=inverse_freqs.device) / d)
+        if not torch.allclose(expect, inverse_freqs.float(), rtol=1e-3, atol=1e-6):
+            raise ValueError("inverse frequency table is not a plain theta ** (-2i/d) schedule")
+        self.rotary_dim, self.theta_base = d, theta
+        super().__call__(kv_cache, qkv, ragged_batch)
+
+
+class LinearBlockedKVCopy(BlockedRotaryEmbeddings):
+    """No positional rotation (learned / no position embeddings): only the cache append."""
+
+    def __init__(self, head_size: int, n_q_heads: int, n_kv_heads: int, dtype: torch.dtype):
+        super().__init__(head_size, n_q_heads, n_kv_heads, dtype, 0, 10000.0)
+
+
+class BlockedFlashAttn:
+    """``ragged_ops/blocked_flash``: causal attention of the batch's new tokens over their sequences' paged KV."""
+
+    def __init__(self, head_size: int, dtype: torch.dtype):
+        if head_size not in (64, 128):
+            raise ValueError(f"Unsupported head size: {head_size} (64 and 128 run on the sm_100a kernel)")
+        self.head_size = head_size
+
+    def __call__(self, out: torch.Tensor, q: torch.Tensor, kv_cache: torch.Tensor, atoms_or_batch,
+                 softmax_scale: float) -> torch.Tensor:
+        b = atoms_or_batch
+        n = b.current_tokens
+        T = q.shape[0]
+        q3 = q[:n].view(n, -1, self.head_size)
+        res = paged_attention(q3, kv_cache, b.token_to_seq()[:n], b.token_positions()[:n], b.block_tables(),
+                              softmax_scale)
+        out[:n].copy_(res.reshape(n, -1))
+        return out
+
+
+class RaggedTopKGating:
+    """``ragged_ops/top_k_gating``: softmax top-k with per-expert counts / slots."""
+
+    def __init__(self, logit_dtype: torch.dtype = torch.float32):
+        self.logit_dtype = logit_dtype
+
+    def __call__(self, logits: torch.Tensor, top_k: int, renormalize: bool = True):
+        from ....ops import moe_ops
+        return moe_ops.top_k_gating(logits, top_k, renormalize=renormalize)
+
+
+class MoEScatter:
+    """``ragged_ops/moe_scatter``: tokens -> expert-contiguous rows."""
+
+    def __init__(self, dtype: torch.dtype, channels: int):
+        self.channels = channels
+
+    def __call__(self, activations, assignments, offsets, expert_counts):
+        from ....ops import moe_ops
+        return moe_ops.moe_scatter(activations, assignments, offsets, expert_counts)
+
+
+class MoEGather:
+    """``ragged_ops/moe_gather``: score-weighted sum of each token's expert outputs."""
+
+    def __init__(self, dtype: torch.dtype, channels: int, normalize_scores: bool = False):
+        self.normalize_scores = normalize_scores
+
+    def __call__(self, moe_output, scores, mapped_slots):
+        from ....ops import moe_ops
+        if self.normalize_scores:
+            scores = scores / scores.sum(dim=-1, keepdim=True)
+        return moe_ops.moe_gather(moe_output, scores, mapped_slots)
