@@ -118,6 +118,15 @@ int sxbh_destroy_lion(int id);
 int sxbh_lion_update(int id, long long step, float lr, float b1, float b2, float wd, float* p, const float* g,
                      float* m, long long n, void* lp, int lp_kind);
 
+/* ---- host library: shared-memory all-reduce among the processes of one host, for CPU tensors
+ *      (reference: ShareMemCommBuilder / torch.ops.deepspeed.inference_all_reduce_, comm/torch.py:29-35,166-171).
+ *      init is collective (rank 0 creates /dev/shm/<name>); slot_bytes: multiple of 64, >= 4096; larger buffers are
+ *      reduced in pieces.  dtype: 0 fp32, 1 bf16, 2 fp16; accumulation in fp32.  Returns 0 or -errno. */
+int sxbh_shm_init(const char* name, int world, int rank, long long slot_bytes);
+int sxbh_shm_allreduce(void* buf, long long numel, int dtype);
+int sxbh_shm_barrier(void);
+int sxbh_shm_finalize(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -297,8 +297,19 @@ def all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op=False):
 
 @timed_op
 def inference_all_reduce(tensor, op=ReduceOp.SUM, group=None):
+    """Latency-oriented all-reduce of the inference paths.  CPU tensors of a single-host job go through the
+    shared-memory engine (``comm/shm.py``, reference ``comm/torch.py:166-171``); everything else is ``all_reduce``."""
     if _off("ALL_REDUCE") or not is_initialized():
         return tensor
+    if tensor.device.type == "cpu" and op == ReduceOp.SUM and (group is None or group is tdist.group.WORLD) \
+            and os.environ.get("SXB_SHM_ALLREDUCE", "1") != "0":
+        from . import shm
+        if shm.all_ranks_on_this_host() and shm.ShmAllReduce.supports(tensor):
+            eng = shm.get_shm_comm()
+            if not eng.initialized:
+                eng.initialize(tdist.get_world_size(), tdist.get_rank())
+            eng.all_reduce(tensor)
+            return tensor
     tdist.all_reduce(tensor, op=_op(op), group=group)
     return tensor
 

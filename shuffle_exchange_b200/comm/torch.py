@@ -27,8 +27,13 @@ def disable_compiler_collective(func):
 
 
 def build_shm_op():
-    """The reference builds a CPU shared-memory all-reduce extension here; intra-node CPU collectives use gloo."""
-    return None
+    """Shared-memory all-reduce engine for CPU tensors (``comm/shm.py`` over ``csrc/host/shm_comm.cpp``); ``None`` when
+    the host library is unavailable."""
+    try:
+        from .shm import get_shm_comm
+        return get_shm_comm()
+    except Exception:
+        return None
 
 
 def has_coalescing_manager() -> bool:

@@ -188,3 +188,34 @@ def test_released_parameters_are_poisoned_in_debug_mode(monkeypatch):
     stale = fg.flat_lp
     fg.release_params()
     assert torch.isnan(stale).all() and fg.flat_lp is None
+
+
+def _shm_allreduce(rank, world):
+    import time
+    import torch.distributed as td
+    from shuffle_exchange_b200 import comm as dist
+    from shuffle_exchange_b200.comm.shm import get_shm_comm
+    eng = get_shm_comm()
+    eng.initialize(world, rank, name=f"sxb200_test_{os.environ['MASTER_PORT']}", slot_bytes=64 * 1024)
+    g = torch.Generator().manual_seed(rank)
+    for dtype, n, tol in ((torch.float32, 1000, 1e-6), (torch.bfloat16, 70001, 2e-2), (torch.float16, 33, 2e-3),
+                          (torch.float32, 50000, 1e-5)):            # 50000 fp32 > one 64 KiB slot: several pieces
+        x = torch.randn(n, generator=g).to(dtype)
+        ref = x.clone().float()
+        td.all_reduce(ref)
+        eng.all_reduce(x)
+        assert (x.float() - ref).abs().max() <= tol * max(1.0, ref.abs().max().item()), (dtype, n)
+    # the facade picks the engine when the whole job is on this host
+    os.environ["LOCAL_WORLD_SIZE"] = str(world)
+    y = torch.full((5,), float(rank + 1))
+    dist.inference_all_reduce(y)
+    assert y.tolist() == [float(sum(range(1, world + 1)))] * 5
+    with pytest.raises(TypeError):
+        eng.all_reduce(torch.zeros(4, dtype=torch.int32))
+    eng.finalize()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_shared_memory_allreduce_matches_gloo(world):
+    from conftest import run_dist
+    run_dist(_shm_allreduce, world=world)
