@@ -175,3 +175,10 @@ def test_inference_post_init_weight_quantization():
         Quantizer({"num_bits": 3, "group_size": 8, "group_dim": 1, "symmetric": False})
     with pytest.raises(AssertionError):
         _init_group_wise_weight_quantization(M().half(), {"weight_quantization": {"post_init_quant": {"fc": q8, "c1": q8}}})
+
+
+def test_contiguous_allocator_randomized_workload_and_param_rebinding():
+    from shuffle_exchange_b200.runtime.zero import test as alloc_check
+    stats = alloc_check.random_workload(steps=600, size=2048, seed=3)
+    assert stats["allocations"] > 100 and stats["defragmentations"] > 0 and stats["max_allocated"] <= 2048
+    alloc_check.param_rebinding()
