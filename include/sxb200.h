@@ -127,6 +127,18 @@ int sxbh_shm_allreduce(void* buf, long long numel, int dtype);
 int sxbh_shm_barrier(void);
 int sxbh_shm_finalize(void);
 
+/* ---- host library: schedule-compiler core (reference: the C++ runtime behind DeepCompileBuilder, compile/util.py,
+ *      compile/list_schedule.py:171-209).  A plan is parallel arrays per node: kind (0 gather, 1 compute, 2 release,
+ *      3 reduce, 4 offload, 5 reload), unit, phase (0 fwd, 1 bwd), bytes, time_us.
+ *      simulate: out[0] peak bytes, out[1] time (us), out[2] exposed communication (us).
+ *      hoist_gathers: perm[i] = input index of the node placed at position i after memory-bounded hoisting. */
+int sxbh_plan_simulate(int n, const int* kind, const int* unit, const int* phase, const long long* bytes,
+                       const double* time_us, const int* persistent, int n_persistent, long long base_bytes,
+                       double* out);
+int sxbh_plan_hoist_gathers(int n, const int* kind, const int* unit, const int* phase, const long long* bytes,
+                            const double* time_us, const int* persistent, int n_persistent, long long budget,
+                            int* perm);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,7 +5,8 @@ memory budget allows) and ``fast_free_schedule`` (:275-, schedule so parameters 
 place all-gathers greedily).  Same two policies, on :class:`~.plan.ExecutionPlan` instead of FX graphs."""
 from __future__ import annotations
 
-from typing import List
+import os
+from typing import List, Optional
 
 from .plan import COMPUTE, GATHER, RELEASE, ExecutionPlan, PlanNode
 
@@ -42,12 +43,23 @@ def fast_free_schedule(plan: ExecutionPlan, available_mem: int, output_size: int
 
 
 def simple_prefetch(plan: ExecutionPlan, available_mem: int, output_size: int = 0,
-                    debug_log: bool = False) -> ExecutionPlan:
+                    debug_log: bool = False, use_native: Optional[bool] = None) -> ExecutionPlan:
     """Starting from the low-memory schedule, move each GATHER earlier, one COMPUTE at a time, while the simulated
     peak of gathered bytes stays within ``available_mem - output_size``.  Gathers keep their relative order so the
     communication stream never reorders (NCCL requires identical order on all ranks)."""
     out = fast_free_schedule(plan, available_mem, output_size, debug_log)
     budget = max(0, int(available_mem) - int(output_size))
+    if use_native is None:
+        use_native = os.environ.get("SXB_NATIVE_SCHED", "1") != "0"
+    if use_native:
+        from . import native_sched
+        if native_sched.available():         # same loop in C++ (csrc/host/plan_sched.cpp)
+            perm = native_sched.hoist_gathers(out, budget)
+            out.nodes = [out.nodes[j] for j in perm]
+            out.validate()
+            if debug_log:
+                out.meta["schedule_log"] = [f"{n.phase}:{n.kind}:{n.unit}" for n in out.nodes]
+            return out
     nodes = out.nodes
     i = 0
     while i < len(nodes):

@@ -182,3 +182,22 @@ def test_contiguous_allocator_randomized_workload_and_param_rebinding():
     stats = alloc_check.random_workload(steps=600, size=2048, seed=3)
     assert stats["allocations"] > 100 and stats["defragmentations"] > 0 and stats["max_allocated"] <= 2048
     alloc_check.param_rebinding()
+
+
+def test_fused_qkv_attention_entry_point_matches_split_path_on_cpu():
+    """``flash_attention_qkv`` (one fused tensor in, fused gradient out) is the same function as slicing q, k, v and
+    calling ``flash_attention`` — forward and gradient — for GQA and MHA layouts."""
+    import torch
+    from shuffle_exchange_b200.ops import functional as F
+    for (B, S, hq, hk, d) in ((2, 9, 4, 2, 8), (1, 5, 3, 3, 4)):
+        torch.manual_seed(0)
+        qkv = torch.randn(B, S, (hq + 2 * hk) * d, requires_grad=True)
+        out = F.flash_attention_qkv(qkv, hq, hk, d, causal=True)
+        g = torch.randn_like(out)
+        out.backward(g)
+        ref_in = qkv.detach().clone().requires_grad_()
+        q, k, v = F._split_qkv(ref_in, hq, hk, d)
+        ref = F.flash_attention(q, k, v, causal=True)
+        ref.backward(g)
+        assert out.shape == (B, S, hq, d)
+        assert torch.allclose(out, ref, atol=1e-6) and torch.allclose(qkv.grad, ref_in.grad, atol=1e-6)
