@@ -257,9 +257,8 @@ class BaseTransformerContainer:
         m.inter_w = cut_rows(m.inter_w, [inter, inter] if gated else [inter])
         m.inter_b = cut_rows(m.inter_b, [inter, inter] if gated else [inter])
         m.out_w = m.out_w[:, r * (inter // n):(r + 1) * (inter // n)].contiguous()
-        if r != 0:                   # row-parallel biases are added once, after the all-reduce
-            a.ob = None if a.ob is None else torch.zeros_like(a.ob)
-            m.out_b = None if m.out_b is None else torch.zeros_like(m.out_b)
+        # row-parallel biases (attention output, MLP output) stay whole on every rank: the fused layer adds them AFTER
+        # the all-reduce of the partial products
 
     # -------------------------------------------------------------------------------------- module
     def create_module(self, config=None):

@@ -61,7 +61,16 @@ class DeepSpeedMLP(nn.Module):
             output, residual_add = self.mlp_gemm_func(input=input, residual=residual, weight_interm=inter_w,
                                                       weight_out=self.output_w, input_bias=bias, bias=inter_b,
                                                       gamma=self.attn_nw, beta=self.attn_nb)
-        if self.mp_group is not None and dist.is_initialized() and dist.get_world_size(group=self.mp_group) > 1:
+        tp = self.mp_group is not None and dist.is_initialized() and dist.get_world_size(group=self.mp_group) > 1
+        if tp and not self.config.mlp_after_attn:
+            # parallel attention + MLP block: the attention partial product was NOT reduced (ds_attention skips it),
+            # so both partial sums travel in one all-reduce; residual and biases are added once afterwards
+            output = output + input
+            dist.all_reduce(output, group=self.mp_group)
+            return self.residual_add_func(hidden_state=output, residual=residual, add_bias=bias is not None,
+                                          attention_output=None, attention_bias=bias, final_bias=self.output_b,
+                                          residual_add=residual_add)
+        if tp:
             dist.all_reduce(output, group=self.mp_group)
         return self.residual_add_func(hidden_state=output, residual=residual, add_bias=bias is not None,
                                       attention_output=input,

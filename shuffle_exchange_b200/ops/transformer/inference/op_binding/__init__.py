@@ -142,7 +142,9 @@ class ResidualAddOp(BaseOp):
                 out = out + final_bias
             return out
         # parallel attention + MLP (GPT-J / NeoX): everything hangs off the same residual
-        out = hidden_state + residual + attention_output
+        out = hidden_state + residual
+        if attention_output is not None:
+            out = out + attention_output
         if add_bias and attention_bias is not None:
             out = out + attention_bias
         if final_bias is not None:

@@ -70,22 +70,30 @@ def _tp_engine(rank, world, name):
     common = dict(vocab_size=131, hidden_size=64, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
                   max_position_embeddings=128, intermediate_size=128)
     cfgs = {"llama": dict(model_type="llama", **common),
-            "mixtral": dict(model_type="mixtral", num_local_experts=4, num_experts_per_tok=2, **common)}
+            "mixtral": dict(model_type="mixtral", num_local_experts=4, num_experts_per_tok=2, **common),
+            "qwen2": dict(model_type="qwen2", **common),
+            "opt": dict(model_type="opt", vocab_size=131, hidden_size=64, num_hidden_layers=2, num_attention_heads=4,
+                        ffn_dim=128, max_position_embeddings=128, word_embed_proj_dim=64)}
     torch.manual_seed(0)
     m = AutoModelForCausalLM.from_config(AutoConfig.for_model(**cfgs[name])).float().eval()
+    g = torch.Generator().manual_seed(11)
+    with torch.no_grad():              # HF zero-initialises biases, which would hide bias-placement mistakes
+        for n, p in m.named_parameters():
+            if n.endswith("bias"):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.2)
     ids = torch.randint(0, 131, (1, 9), generator=torch.Generator().manual_seed(1))
     with torch.no_grad():
         ref = m(ids).logits[0]
     eng = build_engine_from_hf_model(m, RaggedInferenceEngineConfig(tensor_parallel=DeepSpeedTPConfig(tp_size=world)))
     model = eng.model()
-    assert model.tp_size == world and model.tp_rank == rank and model.n_heads_kv_local == 1
+    assert model.tp_size == world and model.tp_rank == rank and model.n_heads_kv_local == (2 if name == "opt" else 1)
     out = eng.put([7], [ids[0, :6]])
     assert out.shape[-1] == 131 and (out[0] - ref[5]).abs().max() < 1e-4
     out = eng.put([7], [ids[0, 6:9]])
     assert (out[0] - ref[8]).abs().max() < 1e-4
 
 
-@pytest.mark.parametrize("name", ["llama", "mixtral"])
+@pytest.mark.parametrize("name", ["llama", "mixtral", "qwen2", "opt"])
 def test_two_rank_tensor_parallel_engine_matches_huggingface(name):
     run_dist(_tp_engine, world=2, args=(name,))
 

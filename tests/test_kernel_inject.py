@@ -29,6 +29,15 @@ ENCODERS = {
 }
 
 
+def _randomize_biases(model):
+    """HF initialises every bias (and LayerNorm shift) to zero, which would hide bias-placement mistakes."""
+    g = torch.Generator().manual_seed(11)
+    with torch.no_grad():
+        for n, p in model.named_parameters():
+            if n.endswith("bias"):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.2)
+
+
 def _inject(model):
     eng = sxb.init_inference(model, dtype=torch.float32, replace_with_kernel_inject=True)
     n = sum(isinstance(m, HFLayerAdapter) for m in eng.module.modules())
@@ -40,6 +49,7 @@ def _inject(model):
 def test_causal_lm_logits_survive_kernel_injection(name):
     torch.manual_seed(0)
     m = AutoModelForCausalLM.from_config(AutoConfig.for_model(**CAUSAL[name])).float().eval()
+    _randomize_biases(m)
     ids = torch.randint(0, 96, (2, 11), generator=torch.Generator().manual_seed(1))
     with torch.no_grad():
         ref = m(ids, use_cache=False).logits.clone()
@@ -53,6 +63,7 @@ def test_causal_lm_logits_survive_kernel_injection(name):
 def test_encoder_hidden_states_survive_kernel_injection(name):
     torch.manual_seed(0)
     m = AutoModel.from_config(AutoConfig.for_model(**ENCODERS[name])).float().eval()
+    _randomize_biases(m)
     ids = torch.randint(0, 96, (2, 9), generator=torch.Generator().manual_seed(2))
     mask = torch.ones(2, 9, dtype=torch.long)
     mask[1, 6:] = 0                   # padding on the second row exercises the additive mask path
@@ -121,3 +132,25 @@ def test_container_features_meta_load_and_hybrid_lora_refresh():
     assert torch.allclose(fused.mlp.output_w.t(), before, atol=1e-6)
     up, gate = h.set_mlp_gate()
     assert torch.equal(fused.mlp.inter_w.t(), torch.cat([up, gate], 0))
+
+
+def _inject_tp(rank, world, name):
+    torch.manual_seed(0)
+    m = AutoModelForCausalLM.from_config(AutoConfig.for_model(**CAUSAL[name])).float().eval()
+    _randomize_biases(m)
+    ids = torch.randint(0, 96, (2, 10), generator=torch.Generator().manual_seed(5))
+    with torch.no_grad():
+        ref = m(ids, use_cache=False).logits.clone()
+        eng = sxb.init_inference(m, dtype=torch.float32, replace_with_kernel_inject=True,
+                                 tensor_parallel={"tp_size": world})
+        layer = next(x for x in eng.module.modules() if isinstance(x, HFLayerAdapter)).ds_layer
+        assert layer.config.mp_size == world
+        assert layer.attention.attn_ow.shape[0] == layer.config.hidden_size // world      # row-parallel slice
+        out = eng.module(ids, use_cache=False).logits
+    assert (out - ref).abs().max() < 2e-3, (name, rank, float((out - ref).abs().max()))
+
+
+@pytest.mark.parametrize("name", ["gpt2", "llama", "gptj"])
+def test_kernel_injection_with_two_way_tensor_parallelism(name):
+    from conftest import run_dist
+    run_dist(_inject_tp, world=2, args=(name,))
