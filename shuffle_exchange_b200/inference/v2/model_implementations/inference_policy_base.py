@@ -54,7 +54,7 @@ class InferenceV2Policy(ABC):
     layer_prefix: str = "model.layers."
     layer_rules: Dict[str, Source] = {}
     global_rules: Dict[str, Source] = {}
-    ignore_patterns: Tuple[str, ...] = (r"rotary_emb\.inv_freq", r"masked_bias", r"attn\.bias$")
+    ignore_patterns: Tuple[str, ...] = (r"rotary_emb\.inv_freq", r"masked_bias", r"(^|\.)attn\.bias$")
 
     def __init__(self, model_config: Any, checkpoint_engine: Optional[CheckpointEngineBase] = None,
                  inf_checkpoint_path: Optional[str] = None) -> None:

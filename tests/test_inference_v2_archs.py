@@ -33,7 +33,13 @@ CASES = {
 
 def _model(name):
     torch.manual_seed(0)
-    return AutoModelForCausalLM.from_config(AutoConfig.for_model(**CASES[name])).float().eval()
+    m = AutoModelForCausalLM.from_config(AutoConfig.for_model(**CASES[name])).float().eval()
+    g = torch.Generator().manual_seed(11)
+    with torch.no_grad():          # HF zero-initialises biases: randomise them so a misplaced bias shows up
+        for n, p in m.named_parameters():
+            if n.endswith("bias"):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.2)
+    return m
 
 
 @pytest.mark.parametrize("name", sorted(CASES))
