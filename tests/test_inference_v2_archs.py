@@ -39,6 +39,8 @@ def _model(name):
         for n, p in m.named_parameters():
             if n.endswith("bias"):
                 p.copy_(torch.randn(p.shape, generator=g) * 0.2)
+            elif p.dim() == 1 and n.endswith("weight"):          # norm scales are initialised to exactly 1
+                p.copy_(1 + torch.randn(p.shape, generator=g) * 0.1)
     return m
 
 

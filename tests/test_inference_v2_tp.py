@@ -81,6 +81,8 @@ def _tp_engine(rank, world, name):
         for n, p in m.named_parameters():
             if n.endswith("bias"):
                 p.copy_(torch.randn(p.shape, generator=g) * 0.2)
+            elif p.dim() == 1 and n.endswith("weight"):          # norm scales are initialised to exactly 1
+                p.copy_(1 + torch.randn(p.shape, generator=g) * 0.1)
     ids = torch.randint(0, 131, (1, 9), generator=torch.Generator().manual_seed(1))
     with torch.no_grad():
         ref = m(ids).logits[0]

@@ -110,6 +110,13 @@ def test_training_layer_injection_and_layer_quantisation():
                                num_attention_heads=4, intermediate_size=64, max_position_embeddings=32,
                                hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
     m = AutoModel.from_config(cfg).float().eval()
+    g = torch.Generator().manual_seed(11)
+    with torch.no_grad():              # zero-initialised biases / unit LayerNorm scales would hide swapped tensors
+        for n, p in m.named_parameters():
+            if n.endswith("bias"):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.2)
+            elif "LayerNorm.weight" in n:
+                p.copy_(1 + torch.randn(p.shape, generator=g) * 0.1)
     layer = m.encoder.layer[0]
     x = torch.randn(2, 6, 32)
     with torch.no_grad():
