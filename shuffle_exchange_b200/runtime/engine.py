@@ -954,6 +954,193 @@ class DeepSpeedEngine(nn.Module):
     def swap_tensor_config(self): return self._config.zero_config.offload_optimizer
     def autotuning_enabled(self): return self._config.autotuning_config.get("enabled", False)
     def autotuning_metric(self): return self._config.autotuning_config.get("metric", "throughput")
+    def autotuning_start_profile_step(self): return self._config.autotuning_config.get("start_profile_step", 3)
+    def autotuning_end_profile_step(self): return self._config.autotuning_config.get("end_profile_step", 5)
+    def autotuning_metric_path(self):
+        path = self._config.autotuning_config.get("metric_path")
+        return path if path else os.path.join(os.getcwd(), "autotuning_metric.json")
+    def autotuning_model_info_path(self):
+        path = self._config.autotuning_config.get("model_info_path")
+        return path if path else os.path.join(os.getcwd(), "autotuning_model_info.json")
+    def autotuning_profile_model_info(self):
+        mi = self._config.autotuning_config.get("model_info") or {}
+        return bool(self.autotuning_enabled() and mi.get("profile", False))
+    def checkpoint_serialization_enabled(self): return bool(self._config.checkpoint_config.parallel_write.get("serialization", True))
+    def checkpoint_writer_enabled(self): return self._config.checkpoint_config.writer is not None
+    def zero_nvme_offload_optimizer(self):
+        oo = self._config.zero_config.offload_optimizer
+        return oo is not None and str(getattr(oo, "device", "none")).lower().endswith("nvme")
+    def zero_module_granularity_threshold(self): return getattr(self._config.zero_config, "module_granularity_threshold", 0)
+    def zero_allgather_partitions(self): return getattr(self._config.zero_config, "allgather_partitions", True)
+    def zero_log_trace_cache_warnings(self): return getattr(self._config.zero_config, "log_trace_cache_warnings", False)
+    def tensor_parallel_config(self): return self._config.tensor_parallel_config
+    def autotp_size(self): return self._config.tensor_parallel_config.autotp_size
+    def torch_autocast_dtype(self): return self._config.torch_autocast_dtype
+    def torch_autocast_lower_precision_safe_modules(self): return self._config.torch_autocast_lower_precision_safe_modules
+    def get_sequence_parallel_group(self): return getattr(self, "seq_parallel_group", None)
+    def get_pld_theta(self):
+        return self.progressive_layer_drop.get_theta() if self.progressive_layer_drop is not None else None
+
+    def quantize_training(self):
+        """``(in_forward, enabled, target_bits, start_bits, period, offset, groups, fp16_mixed, change_ratio, type,
+        rounding, verbose, use_kernel)`` of the weight-quantisation (MoQ) schedule (reference ``engine.py:842-858``)."""
+        wq = (self._config.compression_config or {}).get("weight_quantization", {})
+        shared = wq.get("shared_parameters", {})
+        groups = wq.get("different_groups", {})
+        first = next(iter(groups.values()), {}).get("params", {}) if groups else {}
+        mixed = shared.get("fp16_mixed_quantize", {})
+        return (shared.get("quantize_weight_in_forward", False), shared.get("enabled", False),
+                first.get("target_bits", 8), first.get("start_bits", 16), first.get("quantization_period", 1000),
+                shared.get("schedule_offset", 1000), shared.get("quantize_groups", 1), mixed.get("enabled", False),
+                mixed.get("quantize_change_ratio", 0.001), shared.get("quantization_type", "symmetric"),
+                shared.get("rounding", "nearest"), shared.get("quantize_verbose", False),
+                shared.get("quantizer_kernel", False))
+
+    # ---- datasets / data pipeline
+    @staticmethod
+    def is_map_style_dataset(obj): return hasattr(obj, "__getitem__") and hasattr(obj, "__len__")
+    @staticmethod
+    def is_iterable_style_dataset(obj): return isinstance(obj, torch.utils.data.IterableDataset)
+
+    def set_data_post_process_func(self, post_process_func):
+        """Hook applied to every batch the curriculum / data-sampling loader yields (e.g. truncating to the current
+        sequence-length difficulty)."""
+        if self.training_dataloader is not None:
+            self.training_dataloader.post_process_func = post_process_func
+
+    def set_custom_curriculum_learning_schedule(self, schedule_func_dict):
+        """``{metric_name: fn(global_step) -> difficulty}`` for curriculum metrics declared with the ``custom``
+        schedule type."""
+        sampler = getattr(self.training_dataloader, "data_sampler", None) if self.training_dataloader is not None else None
+        if sampler is not None and hasattr(sampler, "set_custom_curriculum_learning_schedule"):
+            sampler.set_custom_curriculum_learning_schedule(schedule_func_dict)
+        legacy = getattr(self, "curriculum_scheduler_legacy", None)
+        if legacy is not None and None in schedule_func_dict:
+            legacy.set_custom_get_difficulty(schedule_func_dict[None])
+
+    def random_ltd_initialize(self):
+        """Build the random layer-token-drop scheduler and hand it to every converted layer (call after
+        ``convert_to_random_ltd``)."""
+        from .data_pipeline.data_routing.basic_layer import RandomLayerTokenDrop
+        from .data_pipeline.data_routing.scheduler import RandomLTDScheduler
+        from .data_pipeline import constants as K
+        cfg = dict(self.random_ltd_config())
+        cfg.setdefault(K.RANDOM_LTD_GLOBAL_BATCH_SIZE, self.train_batch_size())
+        cfg.setdefault(K.RANDOM_LTD_MICRO_BATCH_SIZE, self.train_micro_batch_size_per_gpu())
+        self.random_ltd_scheduler = RandomLTDScheduler(cfg)
+        layer_id = 0
+        for m in self.module.modules():
+            if isinstance(m, RandomLayerTokenDrop):
+                m.init_config(cfg, self.random_ltd_scheduler, layer_id)
+                layer_id += 1
+        if layer_id != cfg.get(K.RANDOM_LTD_LAYER_NUM, layer_id):
+            raise ValueError(f"random_ltd_layer_num={cfg.get(K.RANDOM_LTD_LAYER_NUM)} but {layer_id} layers were converted")
+        return self.random_ltd_scheduler
+
+    # ---- sparse gradients (embedding tables): all-gather indices + values instead of the dense all-reduce
+    def sparse_all_gather(self, value, dp_group):
+        """All-gather tensors whose first dimension differs per rank: pad to the longest, gather, trim."""
+        my = torch.tensor([value.size(0)], dtype=torch.long, device=value.device)
+        sizes = self.all_gather_scalar(my, dp_group)
+        longest = int(max(int(t.item()) for t in sizes))
+        pad = value.new_zeros((longest - value.size(0),) + tuple(value.shape[1:]))
+        send = torch.cat([value, pad]) if pad.numel() else value
+        world = dist.get_world_size(group=dp_group)
+        out = [send.new_empty(send.shape) for _ in range(world)]
+        dist.all_gather(out, send.contiguous(), group=dp_group)
+        return [t[: int(n.item())] for t, n in zip(out, sizes)]
+
+    def all_gather_scalar(self, value, dp_group):
+        world = dist.get_world_size(group=dp_group)
+        out = [value.new_zeros(value.size()) for _ in range(world)]
+        dist.all_gather(out, value, group=dp_group)
+        return out
+
+    def sparse_allreduce(self, sparse, dp_group, dp_world_size=None):
+        """``sparse``: :class:`SparseTensor`; returns it holding every rank's rows with values pre-scaled so that a
+        ``to_dense()`` (which sums duplicates) is the mean gradient."""
+        if dp_world_size is None:
+            dp_world_size = dist.get_world_size(group=dp_group)
+        original = sparse.values.dtype
+        values = sparse.values.to(self.communication_data_type) if self.communication_data_type != original \
+            else sparse.values
+        if self.postscale_gradients():
+            if self.gradient_average:
+                values = values * (self.gradient_predivide_factor() / dp_world_size)
+        else:
+            values = values / dp_world_size
+        sparse.indices = torch.cat(self.sparse_all_gather(sparse.indices, dp_group))
+        sparse.values = torch.cat(self.sparse_all_gather(values, dp_group)).to(original)
+        return sparse
+
+    def sparse_allreduce_bucket(self, bucket, dp_group, dp_world_size=None):
+        return [self.sparse_allreduce(sp, dp_group, dp_world_size) for sp in bucket]
+
+    def sparse_allreduce_no_retain(self, bucket, dp_group, dp_world_size=None):
+        for sp in self.sparse_allreduce_bucket(bucket, dp_group, dp_world_size):
+            if sp.is_sparse:
+                sp.orig_dense_tensor.data = sp.to_coo_tensor()
+            else:
+                sp.orig_dense_tensor.data = sp.to_dense()
+
+    # ---- MoE checkpoints
+    @staticmethod
+    def load_moe_state_dict(checkpoint_path, tag, state_dict, old_moe_load, model=None, mpu=None, num_experts=1,
+                            checkpoint_engine=None):
+        """Merge per-expert checkpoint files into ``state_dict`` under this rank's local expert indices (reference
+        ``engine.py:3065-3135``).  ``old_moe_load``: one global expert numbering shared by all MoE layers."""
+        from ..moe.layer import MoE
+        from ..utils import groups as _groups
+        from .checkpointing import _get_expert_ckpt_name
+        loader = checkpoint_engine.load if checkpoint_engine is not None else \
+            (lambda path, map_location=None: torch.load(path, map_location=map_location, weights_only=False))
+        if old_moe_load:
+            group = _groups._get_max_expert_size_name()
+            expp_rank = _groups._get_expert_parallel_rank(group)
+            ep_size = _groups._get_expert_parallel_world_size(group)
+            n_local = max(num_experts) // ep_size if isinstance(num_experts, (list, tuple)) else num_experts // ep_size
+            for local_id in range(n_local):
+                gid = expp_rank * n_local + local_id
+                esd = loader(_get_expert_ckpt_name(checkpoint_path, -1, gid, tag, mpu), map_location="cpu")
+                for k, v in esd.items():
+                    state_dict[k.replace(f"{gid}", f"{local_id}", 1) if f".{gid}." in k else k] = v
+            return
+        moe_layer_id = 0
+        for name, module in model.named_modules():
+            if not isinstance(module, MoE):
+                continue
+            expp_rank = _groups._get_expert_parallel_rank(module.expert_group_name)
+            prefix = f"{name}.deepspeed_moe.experts.deepspeed_experts."
+            for local_id in range(module.num_local_experts):
+                gid = expp_rank * module.num_local_experts + local_id
+                esd = loader(_get_expert_ckpt_name(checkpoint_path, moe_layer_id, gid, tag, mpu), map_location="cpu")
+                for k, v in esd.items():
+                    state_dict[k.replace(f"{prefix}{gid}.", f"{prefix}{local_id}.")] = v
+            moe_layer_id += 1
+
+    # ---- timing / compile bookkeeping
+    def print_forward_breakdown(self, fwd_time):
+        """MoE forward time split (gate / experts / all-to-all) from the layers' own timers, once per print interval."""
+        from ..moe.layer import MoE
+        gate = moe = falltoall = salltoall = 0.0
+        for m in self.module.modules():
+            if isinstance(m, MoE):
+                inner = m.deepspeed_moe
+                gate += getattr(inner, "gate_time", 0.0) or 0.0
+                moe += getattr(inner, "time_moe", 0.0) or 0.0
+                falltoall += getattr(inner, "time_falltoall", 0.0) or 0.0
+                salltoall += getattr(inner, "time_salltoall", 0.0) or 0.0
+        log_dist(f"time (ms) | fwd: {fwd_time:.2f} (fwd_moe: {moe:.2f}, 1st_a2a: {falltoall:.2f}, "
+                 f"2nd_a2a: {salltoall:.2f}, top_k: {gate:.2f})", ranks=[0])
+
+    def get_compile_time(self):
+        return getattr(self, "_compile_time_s", 0.0)
+
+    def register_compile_pass(self, pass_name: str, pass_fn) -> None:
+        """Make ``pass_fn(plan, engine, ...)`` available to ``compile.passes`` schedules under ``pass_name``."""
+        from ..compile import backend as _backend
+        _backend.register_compile_pass(pass_name, pass_fn)
+
     def get_data_types(self):
         model_dtype = torch.float16 if self.fp16_enabled() else (torch.bfloat16 if self.bfloat16_enabled() else torch.float32)
         return model_dtype, self._grad_accum_dtype(model_dtype)

@@ -201,3 +201,44 @@ def test_fused_qkv_attention_entry_point_matches_split_path_on_cpu():
         ref.backward(g)
         assert out.shape == (B, S, hq, d)
         assert torch.allclose(out, ref, atol=1e-6) and torch.allclose(qkv.grad, ref_in.grad, atol=1e-6)
+
+
+def _engine_helpers(rank, world):
+    import torch
+    import shuffle_exchange_b200 as sxb
+    from shuffle_exchange_b200.runtime.sparse_tensor import SparseTensor
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Embedding(16, 4), torch.nn.Linear(4, 4))
+    engine, *_ = sxb.initialize(model=model, model_parameters=model.parameters(), config={
+        "train_micro_batch_size_per_gpu": 2, "steps_per_print": 1 << 30,
+        "optimizer": {"type": "Adam", "params": {"lr": 1e-3}},
+        "autotuning": {"enabled": True, "start_profile_step": 4, "model_info": {"profile": True}},
+        "compression_training": {"weight_quantization": {"shared_parameters": {"enabled": True, "quantize_groups": 4},
+                                                         "different_groups": {"g": {"params": {"target_bits": 4}}}}}})
+    assert engine.autotuning_start_profile_step() == 4 and engine.autotuning_end_profile_step() == 5
+    assert engine.autotuning_profile_model_info() and engine.autotuning_metric_path().endswith("autotuning_metric.json")
+    q = engine.quantize_training()
+    assert len(q) == 13 and q[1] is True and q[2] == 4 and q[6] == 4
+    assert engine.is_map_style_dataset([1, 2]) and not engine.is_iterable_style_dataset([1, 2])
+    assert engine.get_pld_theta() is None and not engine.checkpoint_writer_enabled() and engine.autotp_size() in (0, 1, None)
+    # rows touched differ per rank: rank r has rows {r, 5}
+    dense = torch.zeros(8, 3)
+    dense[rank] = 1.0 + rank
+    dense[5] = 10.0
+    sp = SparseTensor(dense)
+    group = torch.distributed.group.WORLD
+    out = engine.sparse_allreduce(sp, group)
+    ref = dense.clone()
+    torch.distributed.all_reduce(ref)
+    assert torch.allclose(out.to_dense(), ref / world)
+    gathered = engine.sparse_all_gather(torch.arange(rank + 1, dtype=torch.float32), group)
+    assert [t.numel() for t in gathered] == [1, 2]
+    seen = []
+    engine.register_compile_pass("noop_for_test", lambda plan, ctx: seen.append(1) or plan)
+    from shuffle_exchange_b200.compile.backend import opt_passes
+    assert "noop_for_test" in opt_passes and engine.get_compile_time() == 0.0
+
+
+def test_engine_helper_methods_two_ranks():
+    from conftest import run_dist
+    run_dist(_engine_helpers, world=2)
