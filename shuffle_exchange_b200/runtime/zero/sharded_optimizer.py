@@ -247,6 +247,172 @@ class ShardedOptimizerBase:
             for p in g.params:
                 p.grad = None
 
+    # ------------------------------------------------------------- reference optimizer-object surface
+    # The reference's ZeRO optimizers expose these to the engine, to ``utils/tensor_fragment`` and to user scripts
+    # (``stage3.py:2315-2563``, ``stage_1_and_2.py:1995-2056``).  Here they are thin views over the flat groups.
+    def has_overflow(self, partition_gradients=True) -> bool:
+        """Any inf / nan in this step's (reduced) gradients, agreed across the data-parallel group."""
+        return bool(self.compute_grad_norm_and_overflow()[1])
+
+    def check_overflow(self, partition_gradients=True) -> None:
+        self.overflow = self.has_overflow(partition_gradients)
+
+    def has_overflow_serial(self, params=None) -> bool:
+        ps = params if params is not None else [p for g in self.groups for p in g.params]
+        return any(p.grad is not None and not bool(torch.isfinite(p.grad).all()) for p in ps)
+
+    def scaled_global_norm(self, norm_type=2):
+        """Global gradient norm of the loss-SCALED gradients (multiply-by-loss-scale of ``get_global_grad_norm``)."""
+        norm, overflow = self.compute_grad_norm_and_overflow()
+        return float("inf") if overflow else norm * self.loss_scale
+
+    def unscale_and_clip_grads(self, sub_group_id_or_grads=None, total_norm=None) -> float:
+        """Factor the step kernels apply to the raw gradients: 1 / loss_scale, times the clip ratio when
+        ``total_norm`` (unscaled) exceeds ``clip_grad``.  Gradients are not touched here — unscale and clip are folded
+        into the fused optimizer kernel."""
+        norm = total_norm if total_norm is not None else self.compute_grad_norm_and_overflow()[0]
+        return self._combined_scale(norm)
+
+    def get_param_id(self, param) -> int:
+        ids = self.__dict__.setdefault("_param_ids", {})
+        if not ids:
+            for g in self.groups:
+                for p in g.params:
+                    ids[id(p)] = len(ids)
+        return ids[id(param)]
+
+    def get_bit16_param_group(self, group_no: int):
+        return list(self.groups[group_no].params)
+
+    def get_groups_without_padding(self, groups_with_padding=None):
+        """fp32 shard of every group with the alignment padding of the last rank removed (checkpoint layout)."""
+        out = []
+        for g in self.groups:
+            n = self._valid_shard_numel(g)
+            out.append(g.hp_param.data[:n])
+        return out
+
+    def get_lean_optimizer_state(self):
+        """Per group, the base optimizer's state tensors without padding (reference ``_get_base_optimizer_state``)."""
+        out = []
+        for g in self.groups:
+            n = self._valid_shard_numel(g)
+            st = self._optimizer_state_for(g)
+            out.append({k: (v[:n] if torch.is_tensor(v) and v.dim() == 1 and v.numel() >= n else v)
+                        for k, v in st.items()})
+        return out
+
+    def get_fp32_grad_partitions(self):
+        return {i: {0: g.grad_shard} for i, g in enumerate(self.groups) if g.grad_shard is not None}
+
+    def refresh_fp32_params(self):
+        """fp32 master shards := current low-precision shards (after weights were loaded into the module)."""
+        for g in self.groups:
+            if g.lp_shard is not None:
+                g.hp_param.data.copy_(g.lp_shard.to(g.hp_param.device, torch.float32))
+
+    def backward_prologue(self):
+        self._pre_backward()
+
+    def backward_epilogue(self):
+        self._post_backward()
+
+    def checkpoint_event_prologue(self):
+        """Before a checkpoint is written: nothing is swapped out in this design unless NVMe offload is active."""
+        sw = getattr(self, "optimizer_swapper", None)
+        if sw is not None and hasattr(sw, "swap_in_all"):
+            sw.swap_in_all()
+
+    def checkpoint_event_epilogue(self):
+        sw = getattr(self, "optimizer_swapper", None)
+        if sw is not None and hasattr(sw, "swap_out_all"):
+            sw.swap_out_all()
+
+    def reset_swap_buffers(self):
+        sw = getattr(self, "optimizer_swapper", None)
+        if sw is not None and hasattr(sw, "reset_buffers"):
+            sw.reset_buffers()
+
+    def dump_pre_step_gradients(self, debug_fp32_grads=None):
+        """Debug aid (reference ``stage3.py:2176-2188``): norm of every group's reduced gradient shard."""
+        for i, g in enumerate(self.groups):
+            if g.grad_shard is not None:
+                print(f"Pre-Step Dump Norms for Group {i} grad_norm = {float(g.grad_shard.float().norm()):.6f}")
+
+    def dump_post_step_gradients(self):
+        for i, g in enumerate(self.groups):
+            print(f"Post-Step Dump Norms for Group {i} fp32_norm = {float(g.hp_param.data.float().norm()):.6f}")
+
+    def print_rank_0(self, message):
+        if dist.get_rank() == 0:
+            print(message)
+
+    def offload_states(self, include=None, device="cpu", pin_memory=True, non_blocking=False):
+        from .offload_states import offload_optimizer_states
+        return offload_optimizer_states(self, include=include, device=device, pin_memory=pin_memory,
+                                        non_blocking=non_blocking)
+
+    def reload_states(self, non_blocking=False):
+        from .offload_states import reload_optimizer_states
+        return reload_optimizer_states(self, non_blocking=non_blocking)
+
+    # tensor-fragment API on the optimizer object (the reference attaches the optimizer to every parameter as
+    # ``param._z3_optimizer`` and ``utils/tensor_fragment`` calls these)
+    def get_full_hp_param(self, param, optim_state_key=None):
+        from ...utils import tensor_fragment as tf
+        return tf.safe_get_full_fp32_param(param) if optim_state_key is None else \
+            tf.safe_get_full_optimizer_state(param, optim_state_key)
+
+    def set_full_hp_param(self, value, param, optim_state_key=None):
+        from ...utils import tensor_fragment as tf
+        return tf.safe_set_full_fp32_param(param, value) if optim_state_key is None else \
+            tf.safe_set_full_optimizer_state(param, value, optim_state_key)
+
+    def get_fp32_grad_for_param(self, param):
+        from ...utils import tensor_fragment as tf
+        return tf.safe_get_full_grad(param)
+
+    def set_fp32_grad_for_param(self, value, param):
+        from ...utils import tensor_fragment as tf
+        return tf.safe_set_full_grad(param, value)
+
+    def update_fp32_grad_for_param_vectorized(self, update_func, param_list):
+        from ...utils import tensor_fragment as tf
+        return tf.safe_update_full_grad_vectorized(param_list, update_func)
+
+    def get_local_fp32_param(self, param, optim_state_key=None):
+        from ...utils import tensor_fragment as tf
+        return tf.safe_get_local_fp32_param(param) if optim_state_key is None else \
+            tf.safe_get_local_optimizer_state(param, optim_state_key)
+
+    def set_local_hp_param(self, value, param, optim_state_key=None):
+        from ...utils import tensor_fragment as tf
+        return tf.safe_set_local_fp32_param(param, value) if optim_state_key is None else \
+            tf.safe_set_local_optimizer_state(param, value, optim_state_key)
+
+    def get_local_fp32_grad_for_param(self, param):
+        from ...utils import tensor_fragment as tf
+        return tf.safe_get_local_grad(param)
+
+    def set_local_grad_for_param(self, value, param):
+        from ...utils import tensor_fragment as tf
+        return tf.safe_set_local_grad(param, value)
+
+    def get_hp_param_device(self, param, optim_state_key=None):
+        link = None
+        try:
+            from ...utils.tensor_fragment import get_hp_fragment_mapping
+            link = get_hp_fragment_mapping(param)
+        except Exception:
+            pass
+        for g in self.groups:
+            if any(p is param for p in g.params):
+                if optim_state_key is None:
+                    return g.hp_param.device
+                st = self._optimizer_state_for(g).get(optim_state_key)
+                return st.device if torch.is_tensor(st) else g.hp_param.device
+        return None
+
     # ------------------------------------------------------------------------------ state dict
     def _base_state_dict(self):
         """Base optimizer state with tensors keyed by group index (one fp32 shard per group)."""

@@ -123,3 +123,38 @@ def _zero_init_worker(rank, world):
 
 def test_zero_init_context():
     run_dist(_zero_init_worker, 2)
+
+
+def _optimizer_surface(rank, world, stage):
+    import shuffle_exchange_b200 as sxb
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.ReLU(), torch.nn.Linear(16, 8))
+    engine, opt, *_ = sxb.initialize(model=model, model_parameters=model.parameters(), config={
+        "train_micro_batch_size_per_gpu": 2, "steps_per_print": 1 << 30, "gradient_clipping": 0.5,
+        "optimizer": {"type": "Adam", "params": {"lr": 1e-2}}, "zero_optimization": {"stage": stage}})
+    x = torch.randn(2, 8, generator=torch.Generator().manual_seed(rank))
+    loss = engine(x).pow(2).mean()
+    engine.backward(loss)
+    p = next(engine.module.parameters())
+    g_full = opt.get_fp32_grad_for_param(p)
+    assert g_full is None or g_full.shape == (16, 8)
+    assert not opt.has_overflow() and opt.scaled_global_norm() > 0
+    f = opt.unscale_and_clip_grads(total_norm=2.0)
+    assert abs(f - 0.5 / (2.0 + 1e-6)) < 1e-6                      # loss scale 1, clip 0.5 at norm 2
+    engine.step()
+    w = opt.get_full_hp_param(p)
+    assert w.shape == (16, 8) and opt.get_full_hp_param(p, "exp_avg").shape == (16, 8)
+    opt.set_full_hp_param(torch.full((16, 8), 0.25), p)
+    assert torch.allclose(opt.get_full_hp_param(p), torch.full((16, 8), 0.25))
+    assert opt.get_param_id(p) == 0 and len(opt.get_bit16_param_group(0)) >= 1
+    lean = opt.get_lean_optimizer_state()
+    assert len(lean) == len(opt.groups) and "exp_avg" in lean[0]
+    assert len(opt.get_groups_without_padding()) == len(opt.groups)
+    assert opt.get_hp_param_device(p).type == "cpu"
+    opt.check_overflow(); assert opt.overflow is False
+    opt.checkpoint_event_prologue(); opt.checkpoint_event_epilogue(); opt.reset_swap_buffers()
+
+
+@pytest.mark.parametrize("stage", [2, 3])
+def test_optimizer_object_surface(stage):
+    run_dist(_optimizer_surface, world=2, args=(stage,))
