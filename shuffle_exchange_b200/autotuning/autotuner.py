@@ -236,6 +236,111 @@ class Autotuner:
             out[GLOBAL_TUNING_SPACE] = glob
         return out
 
+    # ------------------------------------------------------------------- micro-batch-size search
+    def get_gas_from_user_config(self) -> int:
+        gas = self.user_config.get(GRADIENT_ACCUMULATION_STEPS, 1)
+        if isinstance(gas, int):
+            return max(1, gas)
+        if gas == "auto":                     # the launcher script decides: read it from the mapped user argument
+            v = self.get_val_from_user_args(GRADIENT_ACCUMULATION_STEPS)
+            return max(1, int(v)) if v is not None else 1
+        raise ValueError(f"gradient_accumulation_steps must be an int or 'auto', got {gas!r}")
+
+    def get_val_from_user_args(self, ds_name: str):
+        """Value the user's command line gives to the script argument mapped (``arg_mappings``) to a config key."""
+        mappings = self.autotuning_config.arg_mappings or {}
+        arg_name = mappings.get(ds_name)
+        user_args = list(getattr(self.args, "user_args", []) or [])
+        if not arg_name:
+            return None
+        for i, tok in enumerate(user_args):
+            if tok == arg_name and i + 1 < len(user_args):
+                return user_args[i + 1]
+            if tok.startswith(arg_name + "="):
+                return tok.split("=", 1)[1]
+        return None
+
+    def _mbs_config(self, stage: int, mbs: int, gas: int) -> dict:
+        cfg = copy.deepcopy(self.user_config)
+        z = dict(cfg.get(ZERO_OPTIMIZATION, {}) or {})
+        z[ZERO_OPTIMIZATION_STAGE] = stage
+        cfg[ZERO_OPTIMIZATION] = z
+        cfg[TRAIN_MICRO_BATCH_SIZE_PER_GPU] = mbs
+        cfg[GRADIENT_ACCUMULATION_STEPS] = gas
+        world = max(1, self.exp_num_gpus * self.exp_num_nodes // self.mp_size())
+        cfg[TRAIN_BATCH_SIZE] = mbs * gas * world
+        return cfg
+
+    def run_tuning_micro_batch_sizes(self, tuning_micro_batch_sizes, max_train_batch_size_per_gpu, min_gas, stage,
+                                     tuning_space_name=None):
+        """Run one experiment per candidate micro-batch size (ascending); stops at the first size that fails or that
+        would exceed ``max_train_batch_size_per_gpu``.  Returns the largest size that ran."""
+        name = tuning_space_name or f"{TUNING_MICRO_BATCH_SIZE_PREFIX}{stage}"
+        largest = 0
+        for mbs in sorted(set(tuning_micro_batch_sizes)):
+            gas = min_gas
+            if max_train_batch_size_per_gpu and mbs * gas > max_train_batch_size_per_gpu:
+                break
+            exp, metric_val = self.run_ds_config(self._mbs_config(stage, mbs, gas), f"z{stage}_gas{gas}_tmbspg{mbs}")
+            if not metric_val:
+                logger.info(f"micro batch size {mbs} did not run at ZeRO stage {stage}")
+                break
+            self.update_records(name, exp, metric_val, 1)
+            largest = mbs
+        return largest
+
+    def get_min_max_micro_batch_size(self, stage, min_micro_batch_size, calculated_max_micro_batch_size,
+                                     max_train_batch_size_per_gpu=None):
+        """Smallest and largest micro-batch size that actually run: the minimum is tried first (``-1, -1`` if even that
+        fails), then the estimate from the memory model; if the estimate fails the answer is found by bisection, if it
+        succeeds sizes keep doubling until one fails or the batch-size cap is hit."""
+        name = f"{TUNING_MICRO_BATCH_SIZE_PREFIX}{stage}"
+        gas = self.get_gas_from_user_config()
+        cap = max_train_batch_size_per_gpu or float("inf")
+        ran = {}
+
+        def runs(mbs: int) -> bool:
+            if mbs not in ran:
+                if mbs * gas > cap:
+                    ran[mbs] = False
+                else:
+                    exp, val = self.run_ds_config(self._mbs_config(stage, mbs, gas), f"z{stage}_gas{gas}_tmbspg{mbs}")
+                    ran[mbs] = bool(val)
+                    if val:
+                        self.update_records(name, exp, val, 1)
+            return ran[mbs]
+
+        lo = max(1, int(min_micro_batch_size))
+        if not runs(lo):
+            return -1, -1
+        hi = max(lo, int(calculated_max_micro_batch_size))
+        if hi > lo and runs(hi):
+            good = hi
+            while good * 2 * gas <= cap and runs(good * 2):
+                good *= 2
+            return lo, good
+        good, bad = lo, hi
+        while bad - good > 1:
+            mid = (good + bad) // 2
+            if runs(mid):
+                good = mid
+            else:
+                bad = mid
+        return lo, good
+
+    def get_plateau_mbs(self, tuning_space_name):
+        """Micro-batch size after which the metric stops improving by more than ``METRIC_PERCENT_DIFF_CONST``."""
+        recs = sorted(((exp["ds_config"][TRAIN_MICRO_BATCH_SIZE_PER_GPU], val)
+                       for exp, val, _ in self.records.get(tuning_space_name, []) if val), key=lambda t: t[0])
+        if not recs:
+            return 0
+        plateau, prev = recs[0][0], recs[0][1]
+        for mbs, val in recs[1:]:
+            if val < prev * (1 + METRIC_PERCENT_DIFF_CONST):
+                break
+            plateau, prev = mbs, val
+        return plateau
+
     # ------------------------------------------------------------------------------------ tuning
     def tune_space(self, tuning_space, prev_max_mbs=0, prev_best_mbs=0, prev_best_metric_val=0):
         stage = tuning_space.get(ZERO_OPTIMIZATION, {}).get(ZERO_OPTIMIZATION_STAGE, 0)

@@ -268,6 +268,64 @@ class InferenceEngine(nn.Module):
             self._model_times.append((time.time() - start) * 1e3)
         return outputs
 
+    def destroy(self):
+        """Release engine-owned state: KV workspace of the injected layers, CUDA graphs, the shared TP group handle."""
+        from ..model_implementations.transformers.ds_transformer import DeepSpeedTransformerInference
+        DeepSpeedTransformerInference.layer_id = 0
+        if DeepSpeedTransformerInference.workspace is not None:
+            DeepSpeedTransformerInference.workspace.release_workspace()
+            DeepSpeedTransformerInference.workspace = None
+        self._cuda_graphs = None
+        self.cuda_graph_created = False
+        InferenceEngine.inference_mp_group = None
+
+    def is_compiled(self) -> bool:
+        return getattr(self, "_is_compiled", False)
+
+    def load_model_with_checkpoint(self, r_module):
+        """Stream the configured checkpoint's state dicts into ``r_module`` (meta-device models are materialised)."""
+        from ..module_inject.load_checkpoint import load_model_with_checkpoint
+        sd = getattr(self, "sd", None)
+        if sd is None:
+            raise RuntimeError("no checkpoint state dict is loaded: pass `checkpoint=` to init_inference")
+        return load_model_with_checkpoint(r_module, sd, getattr(self, "mp_replace", None),
+                                          ckpt_type=getattr(self, "ckpt_type", "pp"),
+                                          ckpt_mp_size=getattr(self, "ckpt_mp_size", 1), container=None)
+
+    def build_alibi_tensor(self):
+        """Tensor-parallel ranks hold a slice of the heads: patch the client's ALiBi builder so each rank gets ITS
+        heads' slopes (BLOOM-style models; reference ``inference/engine.py:197-206``)."""
+        from ..module_inject import auto_tp_model_utils as u
+        tr = getattr(self.module, "transformer", None)
+        if tr is None:
+            return
+        if hasattr(tr, "build_alibi_tensor"):
+            tr.build_alibi_tensor = u.build_bloom_alibi_tensor
+        if hasattr(tr, "build_mpt_alibi_tensor"):
+            from types import MethodType
+            tr.build_mpt_alibi_tensor_orig = tr.build_mpt_alibi_tensor
+            tr.build_mpt_alibi_tensor = MethodType(u.build_mpt_alibi_tensor, tr)
+        model = getattr(self.module, "model", None)
+        if model is not None and hasattr(model, "get_alibi_mask"):
+            from types import MethodType
+            model.get_alibi_mask_orig = model.get_alibi_mask
+            model.get_alibi_mask = MethodType(u.get_alibi_mask, model)
+
+    def build_attn_bias(self):
+        tr = getattr(self.module, "transformer", None)
+        if tr is not None and hasattr(tr, "_attn_bias"):
+            from types import MethodType
+            from ..module_inject.auto_tp_model_utils import build_mpt_atten_bias_tensor
+            tr._attn_bias_orig = tr._attn_bias
+            tr._attn_bias = MethodType(build_mpt_atten_bias_tensor, tr)
+
+    def remove_mask_prepare_for_bloom(self):
+        """The fused BLOOM attention builds its own causal mask: make the client's ``_prepare_attn_mask`` a
+        pass-through."""
+        tr = getattr(self.module, "transformer", None)
+        if tr is not None and hasattr(tr, "_prepare_attn_mask"):
+            tr._prepare_attn_mask = lambda attention_mask, *args, **kwargs: attention_mask
+
     def _generate(self, *inputs, **kwargs):
         num_beams = kwargs.get("num_beams", 1)
         if "generation_config" in kwargs:

@@ -127,6 +127,40 @@ class PipelineEngine(DeepSpeedEngine):
         pipe_dataloader = self.deepspeed_io(dataset, data_sampler=sampler)
         self.set_dataloader(RepeatingLoader(pipe_dataloader))
 
+    def log_for_device(self, *msg):
+        """Print from the ranks of one device position (reference ``pipe/engine.py:1351-1362``): the first stage's
+        first data-parallel replica unless ``SXB_PIPE_LOG_RANKS`` names other global ranks."""
+        import os
+        ranks = os.environ.get("SXB_PIPE_LOG_RANKS")
+        wanted = {int(r) for r in ranks.split(",")} if ranks else {0}
+        if self.global_rank in wanted:
+            print(f"RANK={self.global_rank} PIPE-ID={self.stage_id} DATA-ID={self.grid.data_parallel_id} "
+                  f"MBATCH-ID={getattr(self, 'microbatch_id', 0)} STEP-ID={getattr(self, 'log_batch_step_id', -1)} ::",
+                  *msg, flush=True)
+
+    def mem_status(self, msg, print_rank=-1, reset_max=False):
+        """Allocated / cached device memory and their deltas since the previous call, printed on ``print_rank`` (-1:
+        rank 0)."""
+        acc = get_accelerator()
+        if not acc.is_available():
+            return
+        rank = self.global_rank
+        if print_rank != -1 and rank != print_rank:
+            return
+        if print_rank == -1 and rank != 0:
+            return
+        acc.synchronize()
+        if reset_max:
+            acc.reset_max_memory_cached(); acc.reset_max_memory_allocated()
+        new_alloced, new_cached = acc.memory_allocated(), acc.memory_cached()
+        prev = getattr(self, "_mem_status_prev", (0, 0))
+        self._mem_status_prev = (new_alloced, new_cached)
+        gb = 1024 ** 3
+        print(f"RANK={rank} STAGE={self.stage_id} STEP={self.global_steps} MEMSTATS", msg,
+              f"current alloc={new_alloced / gb:0.4f}GB (delta={(new_alloced - prev[0]) / gb:0.4f}GB max="
+              f"{acc.max_memory_allocated() / gb:0.4f}GB) current cache={new_cached / gb:0.4f}GB "
+              f"(delta={(new_cached - prev[1]) / gb:0.4f}GB max={acc.max_memory_cached() / gb:0.4f}GB)", flush=True)
+
     def is_first_stage(self):
         return self.stage_id == 0
 

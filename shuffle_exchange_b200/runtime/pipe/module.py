@@ -221,6 +221,11 @@ class PipelineModule(nn.Module):
         self._local_stop = stop
 
     # ---------------------------------------------------------------------------------- forward
+    def set_checkpoint_interval(self, interval: int) -> None:
+        """Recompute granularity: every ``interval`` consecutive layers form one checkpointed segment (0 = off)."""
+        assert interval >= 0
+        self.activation_checkpoint_interval = interval
+
     def forward(self, forward_input):
         self.micro_offset += 1
 

@@ -195,4 +195,11 @@ class PipelineParallelGrid:
     def get_slice_parallel_rank(self):
         return self._topo.get_coord(self.global_rank).model if "model" in self._topo.get_axis_names() else 0
     def get_slice_parallel_world_size(self): return self.slice_parallel_size
+    # Megatron-style aliases
+    def get_pipeline_model_parallel_rank(self): return self.get_pipe_parallel_rank()
+    def get_pipeline_model_parallel_world_size(self): return self.get_pipe_parallel_world_size()
+    def get_tensor_model_parallel_rank(self): return self.get_slice_parallel_rank()
+    def get_tensor_model_parallel_world_size(self): return self.get_slice_parallel_world_size()
+    def get_data_parallel_group_ranks(self):
+        return next((list(g) for g in self.dp_groups if self.global_rank in g), [self.global_rank])
     def get_slice_parallel_group(self): return self.slice_proc_group

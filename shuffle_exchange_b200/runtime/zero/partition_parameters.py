@@ -71,6 +71,7 @@ class Init:
         self.remote_device = remote_device
         self.pin_memory = pin_memory
         self.group = data_parallel_group or sequence_data_parallel_group
+        self.zero_param_process_group = zero_param_parallel_group
         self.depth = 0
         self._orig_init = None
         self._seen = set()
@@ -86,6 +87,23 @@ class Init:
             self._convert_module(module)
 
     # -------------------------------------------------------------------------------- context
+    # ---- partitioning geometry (reference ``partition_parameters.py:1100-1140``)
+    def get_dp_process_group(self):
+        """Group the parameters are sharded over (the hpZ secondary group when one was given)."""
+        return self.zero_param_process_group or self.group or (dist.get_world_group() if dist.is_initialized() else None)
+
+    def get_partition_dp_group(self, param=None):
+        return getattr(param, "ds_process_group", None) or self.get_dp_process_group()
+
+    def get_partition_rank(self) -> int:
+        g = self.get_dp_process_group()
+        return dist.get_rank(group=g) if dist.is_initialized() else 0
+
+    @property
+    def num_partitions(self) -> int:
+        g = self.get_dp_process_group()
+        return dist.get_world_size(group=g) if dist.is_initialized() else 1
+
     def __enter__(self):
         global _active_init, zero_init_context
         if not self.enabled:

@@ -72,6 +72,31 @@ class PartitionedParameterCoordinator:
         logger.info("ZeRO-3 unit trace invalidated; it will be re-recorded on the next iteration")
         self.opt._trace, self.opt._trace_complete, self.opt._trace_pos = [], False, 0
 
+    def trace_prologue(self, sub_module) -> None:
+        """Before a sub-module runs: in COMPLETE mode check that execution still follows the recorded order and fall
+        back to re-recording when it does not (reference ``coordinator.py:179-213``)."""
+        u = self._unit_of_module(sub_module)
+        if u is None or not self.opt._trace_complete:
+            return
+        pos = getattr(self.opt, "_trace_pos", 0)
+        if pos < len(self.opt._trace) and self.opt._trace[pos] != u.index and not self.opt._in_backward:
+            logger.info(f"ZeRO-3 trace mismatch at step {pos}: expected unit {self.opt._trace[pos]}, running {u.index}")
+            self._invalidate_trace()
+
+    def record_module(self, sub_module) -> None:
+        """RECORD mode: append the sub-module's unit to the trace."""
+        u = self._unit_of_module(sub_module)
+        if u is None:
+            return
+        if self.opt._trace_complete:
+            raise RuntimeError("attempted to record trace when status = COMPLETE")
+        self.opt._trace.append(u.index)
+
+    def record_parameters(self, sub_module) -> None:
+        """Parameters travel with their unit here, so recording the module records its parameters."""
+        if self.opt._trace_complete:
+            raise RuntimeError("attempted to record trace when status = COMPLETE")
+
     def construct_parameter_trace_from_module_trace(self):
         self.opt._trace_complete = len(self.opt._trace) > 0
 

@@ -242,3 +242,35 @@ def _engine_helpers(rank, world):
 def test_engine_helper_methods_two_ranks():
     from conftest import run_dist
     run_dist(_engine_helpers, world=2)
+
+
+def test_autotuner_micro_batch_size_search_with_a_fake_runner():
+    from types import SimpleNamespace
+    from shuffle_exchange_b200.autotuning.autotuner import Autotuner
+    from shuffle_exchange_b200.autotuning import constants as C
+    t = Autotuner.__new__(Autotuner)
+    t.user_config = {"gradient_accumulation_steps": "auto", "zero_optimization": {"stage": 1}}
+    t.autotuning_config = SimpleNamespace(arg_mappings={"gradient_accumulation_steps": "--gas"}, mp_size=1)
+    t.args = SimpleNamespace(user_args=["--lr", "1", "--gas", "2"])
+    t.exp_num_gpus, t.exp_num_nodes, t.records = 2, 1, {}
+    assert t.get_val_from_user_args("gradient_accumulation_steps") == "2" and t.get_gas_from_user_config() == 2
+    calls = []
+
+    def fake_run(ds_config, name):                     # runs up to mbs 11; throughput saturates around mbs 8
+        mbs = ds_config[C.TRAIN_MICRO_BATCH_SIZE_PER_GPU]
+        calls.append(mbs)
+        assert ds_config[C.TRAIN_BATCH_SIZE] == mbs * ds_config[C.GRADIENT_ACCUMULATION_STEPS] * 2
+        val = None if mbs > 11 else 100.0 * min(mbs, 8) + mbs
+        return {"name": name, "ds_config": ds_config}, val
+
+    t.run_ds_config = fake_run
+    assert t.get_min_max_micro_batch_size(1, 1, 32) == (1, 11)            # estimate too high: bisection
+    assert max(calls) == 32 and len(calls) <= 8
+    t.records.clear(); calls.clear()
+    assert t.get_min_max_micro_batch_size(1, 1, 2) == (1, 8)              # estimate too low: doubling until 16 fails
+    assert t.get_min_max_micro_batch_size(1, 64, 64) == (-1, -1)
+    t.records.clear()
+    assert t.run_tuning_micro_batch_sizes([2, 4, 8, 10, 16], None, 1, stage=1) == 10
+    name = f"{C.TUNING_MICRO_BATCH_SIZE_PREFIX}1"
+    assert t.get_plateau_mbs(name) == 8
+    assert t.run_tuning_micro_batch_sizes([4, 8], 6, 1, stage=1) == 4     # batch-size cap
