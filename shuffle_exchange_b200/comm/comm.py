@@ -519,3 +519,79 @@ def monitored_barrier(group=None, timeout=None, wait_all_ranks=False):
     if tdist.get_backend(group) == "gloo":
         return tdist.monitored_barrier(group=group, timeout=timeout, wait_all_ranks=wait_all_ranks)
     return tdist.barrier(group=group)
+
+
+# ---- backend bookkeeping and cloud-launcher environment patches (reference ``comm/comm.py:42-120,760-840``)
+ProcessGroup = tdist.ProcessGroup
+cdb = None                      # the active TorchBackend object once ``init_deepspeed_backend`` / ``set_backend`` ran
+
+
+def set_backend():
+    """Make sure ``cdb`` names the backend object matching the running process group."""
+    global cdb
+    if cdb is None and tdist.is_initialized():
+        from .torch import TorchBackend
+        cdb = TorchBackend(backend=tdist.get_backend())
+    return cdb
+
+
+def init_deepspeed_backend(ds_backend, timeout=None, init_method=None):
+    """Select a non-default transport by name.  This platform has one transport for plumbing (torch.distributed over
+    NCCL / gloo); ``ccl`` / ``hccl`` / ``mpi`` are other vendors' or launchers' and report that they are unavailable."""
+    global cdb
+    name = str(ds_backend).lower()
+    if name in ("nccl", "gloo"):
+        from .torch import TorchBackend
+        cdb = TorchBackend(backend=name, timeout=timeout, init_method=init_method)
+        return cdb
+    if name in ("ccl", "hccl", "sccl", "mpi"):
+        logger.debug(f"communication backend {name!r} is not available on this platform")
+        return None
+    raise ValueError(f"unknown communication backend {ds_backend!r}")
+
+
+def in_aml() -> bool:
+    """Running as an Azure Machine Learning job."""
+    return "AZUREML_EXPERIMENT_ID" in os.environ
+
+
+def in_aws_sm() -> bool:
+    """Running as an AWS SageMaker job."""
+    return "SM_TRAINING_ENV" in os.environ
+
+
+def in_dlts() -> bool:
+    """Running on a DLTS cluster."""
+    return "DLTS_JOB_ID" in os.environ
+
+
+def patch_aml_env_for_torch_nccl_backend(master_port=6105, verbose=True):
+    """AzureML exports Open MPI variables and its own master-node name; translate to torch.distributed's."""
+    os.environ["RANK"] = os.environ["OMPI_COMM_WORLD_RANK"]
+    os.environ["WORLD_SIZE"] = os.environ["OMPI_COMM_WORLD_SIZE"]
+    single_node = int(os.environ["OMPI_COMM_WORLD_LOCAL_SIZE"]) == int(os.environ["WORLD_SIZE"])
+    if not single_node:
+        master = os.environ["AZ_BATCH_MASTER_NODE"].split(":")
+        os.environ["MASTER_ADDR"] = master[0]
+        os.environ.setdefault("MASTER_PORT", str(master_port))
+    else:
+        os.environ["MASTER_ADDR"] = os.environ["AZ_BATCHAI_MPI_MASTER_NODE"]
+        os.environ["MASTER_PORT"] = os.environ.get("MASTER_PORT", "54965")
+    os.environ["LOCAL_RANK"] = os.environ["OMPI_COMM_WORLD_LOCAL_RANK"]
+    os.environ.setdefault("NCCL_SOCKET_IFNAME", "^docker0,lo")
+    if verbose:
+        logger.info("NCCL_SOCKET_IFNAME original value = {}".format(os.environ["NCCL_SOCKET_IFNAME"]))
+        logger.info("Discovered AzureML settings of world_rank={}, local_rank={}, world_size={}, master_addr={}, "
+                    "master_port={}".format(os.environ["RANK"], os.environ["LOCAL_RANK"], os.environ["WORLD_SIZE"],
+                                            os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"]))
+
+
+def patch_aws_sm_env_for_torch_nccl_backend(verbose=True):
+    """SageMaker also starts ranks through Open MPI; MASTER_ADDR / MASTER_PORT are already exported."""
+    os.environ["RANK"] = os.environ["OMPI_COMM_WORLD_RANK"]
+    os.environ["LOCAL_RANK"] = os.environ["OMPI_COMM_WORLD_LOCAL_RANK"]
+    os.environ["WORLD_SIZE"] = os.environ["OMPI_COMM_WORLD_SIZE"]
+    if verbose:
+        logger.info("Discovered AWS SageMaker settings of world_rank={}, local_rank={}, world_size={}, master_addr={}, "
+                    "master_port={}".format(os.environ["RANK"], os.environ["LOCAL_RANK"], os.environ["WORLD_SIZE"],
+                                            os.environ.get("MASTER_ADDR"), os.environ.get("MASTER_PORT")))

@@ -140,3 +140,43 @@ class TorchBackend(Backend):
 
     def _reduce_op(self, op):
         return _c._op(op) if not isinstance(op, tdist.ReduceOp) else op
+
+
+# ---- collective kill switches (reference ``comm/torch.py:16-87``): run a step with a class of collectives disabled to
+# measure compute-only time.  They set the environment flags the façade (``comm.comm._off``) consults, so the switch is
+# seen by every code path, and ``flag=False`` re-enables.
+from .comm import Noop  # noqa: E402,F401
+
+
+def _switch(kind: str, flag: bool) -> None:
+    global DS_COMM_ALL_GATHER_OFF, DS_COMM_REDUCE_SCATTER_OFF, DS_COMM_BROADCAST_OFF, DS_COMM_ALL_REDUCE_OFF, \
+        DS_COMM_REDUCE_OFF
+    os.environ[f"DS_COMM_{kind}_OFF"] = "1" if flag else "0"
+    globals()[f"DS_COMM_{kind}_OFF"] = bool(flag)
+
+
+def all_gather_comm_off(flag=False):
+    _switch("ALL_GATHER", flag)
+
+
+def reduce_scatter_comm_off(flag=False):
+    _switch("REDUCE_SCATTER", flag)
+
+
+def broadcast_comm_off(flag=False):
+    _switch("BROADCAST", flag)
+
+
+def all_reduce_comm_off(flag=False):
+    _switch("ALL_REDUCE", flag)
+
+
+def reduce_comm_off(flag=False):
+    _switch("REDUCE", flag)
+
+
+def backward_comm_off(flag=False):
+    """Everything the backward pass communicates: gradient reduce-scatter / all-reduce and the ZeRO-3 re-gather."""
+    all_gather_comm_off(flag)
+    reduce_scatter_comm_off(flag)
+    all_reduce_comm_off(flag)

@@ -376,3 +376,36 @@ class WarmupCosineLR(_StepSchedule):
             return [0.0] * len(self.org_lrs)
         r = self.get_lr_ratio()
         return [lr * r for lr in self.org_lrs]
+
+
+# ---- command-line overrides of a config's scheduler block (reference ``lr_schedules.py:130-206``)
+def override_lr_range_test_params(args, params):
+    for key in (LR_RANGE_TEST_MIN_LR, LR_RANGE_TEST_STEP_RATE, LR_RANGE_TEST_STEP_SIZE, LR_RANGE_TEST_STAIRCASE):
+        if getattr(args, key, None) is not None:
+            params[key] = getattr(args, key)
+
+
+def override_1cycle_params(args, params):
+    for key in (CYCLE_FIRST_STEP_SIZE, CYCLE_FIRST_STAIR_COUNT, CYCLE_SECOND_STEP_SIZE, CYCLE_SECOND_STAIR_COUNT,
+                DECAY_STEP_SIZE, CYCLE_MIN_LR, CYCLE_MAX_LR, DECAY_LR_RATE, CYCLE_MIN_MOM, CYCLE_MAX_MOM, DECAY_MOM_RATE):
+        if getattr(args, key, None) is not None:
+            params[key] = getattr(args, key)
+
+
+def override_warmupLR_params(args, params):
+    for key in (WARMUP_MIN_LR, WARMUP_MAX_LR, WARMUP_NUM_STEPS, WARMUP_TYPE):
+        if getattr(args, key, None) is not None:
+            params[key] = getattr(args, key)
+
+
+def override_params(args, params):
+    """Flags given on the command line win over the values in the config's ``scheduler.params``."""
+    override_lr_range_test_params(args, params)
+    override_1cycle_params(args, params)
+    override_warmupLR_params(args, params)
+
+
+def update_lr(param_groups, lrs):
+    for group, lr in zip(param_groups, lrs):
+        group["lr"] = lr
+    return [group["lr"] for group in param_groups]

@@ -312,3 +312,288 @@ def align_dense_tensors(tensor_list, alignment):
 
 def empty_cache():
     get_accelerator().empty_cache()
+
+
+# ================================================================ further reference utilities (``runtime/utils.py``)
+class DummyOptim:
+    """Stand-in optimizer for engines built without one (inference-style ZeRO-3): holds the parameters only."""
+
+    def __init__(self, params):
+        self.param_groups = [{"params": list(params)}]
+
+
+graph_cache = {}
+
+
+def graph_process(replay_first_step, func, *args, **kwargs):
+    """Capture ``func(*args, **kwargs)`` into a CUDA graph on the first call (keyed by ``func.__name__``) and replay it
+    afterwards.  ``replay_first_step``: also replay right after capture (capture itself does not execute)."""
+    name = func.__name__
+    if name not in graph_cache:
+        acc = get_accelerator()
+        stream = acc.Stream()
+        stream.wait_stream(acc.current_stream())
+        with acc.stream(stream):
+            func(*args, **kwargs)              # warm-up outside capture
+        acc.current_stream().wait_stream(stream)
+        graph_cache[name] = acc.create_graph()
+        with acc.capture_to_graph(graph_cache[name]):
+            func(*args, **kwargs)
+        if replay_first_step:
+            acc.replay_graph(graph_cache[name])
+    else:
+        get_accelerator().replay_graph(graph_cache[name])
+
+
+def noop_context(fn, *args, **kwargs):
+    """Context manager that calls ``fn`` on entry and does nothing else."""
+    import contextlib
+
+    @contextlib.contextmanager
+    def ctx():
+        yield fn(*args, **kwargs) if callable(fn) else None
+    return ctx()
+
+
+def copy_to_device(item, device, criterion_func):
+    """Deep-copy a nested structure, cloning onto ``device`` every element ``criterion_func`` selects."""
+    if criterion_func(item):
+        return item.to(device)
+    if isinstance(item, list):
+        return [copy_to_device(v, device, criterion_func) for v in item]
+    if isinstance(item, tuple):
+        return tuple(copy_to_device(v, device, criterion_func) for v in item)
+    if isinstance(item, dict):
+        return {k: copy_to_device(v, device, criterion_func) for k, v in item.items()}
+    return item
+
+
+def move_to_device(item, device, criterion_func=None):
+    """Like :func:`copy_to_device` but in place for tensors (``.data`` re-pointed) — no second copy stays alive."""
+    crit = criterion_func or torch.is_tensor
+    if crit(item):
+        moved = item.to(device)
+        item.data = moved.data
+        return item
+    if isinstance(item, list):
+        return [move_to_device(v, device, criterion_func) for v in item]
+    if isinstance(item, tuple):
+        return tuple(move_to_device(v, device, criterion_func) for v in item)
+    if isinstance(item, dict):
+        return {k: move_to_device(v, device, criterion_func) for k, v in item.items()}
+    return item
+
+
+def mask_nan_or_inf_with_val_inplace(input, device=None, val=-1.0):
+    """Replace a non-finite scalar / tensor by ``val`` without a host sync (arithmetic select)."""
+    bad = ~torch.isfinite(input)
+    input.masked_fill_(bad, val) if input.dim() else input.copy_(torch.where(bad, torch.full_like(input, val), input))
+    return input
+
+
+def get_flattened_grad_norm(parameters, norm_type=2, mpu=None, grad_norm_mask=None):
+    """Norm of the gradients of ``parameters`` (optionally masking index ranges per parameter), reduced over the
+    model-parallel group; -1 when not finite."""
+    parameters = [p for p in ([parameters] if torch.is_tensor(parameters) else parameters) if p.grad is not None]
+    if not parameters:
+        return 0.0
+    grads = []
+    for i, p in enumerate(parameters):
+        g = p.grad.detach().float().reshape(-1)
+        if grad_norm_mask is not None and len(grad_norm_mask[i]) > 0:
+            keep = torch.ones_like(g, dtype=torch.bool)
+            for lo, hi in grad_norm_mask[i].tolist():
+                keep[lo:hi] = False
+            g = g * keep
+        grads.append(g)
+    return get_global_norm_of_tensors(grads, norm_type=norm_type, mpu=mpu)
+
+
+def get_grad_zeros(parameters, mpu=None):
+    """Number of exactly-zero gradient elements over ``parameters`` (summed across model-parallel ranks)."""
+    parameters = [p for p in ([parameters] if torch.is_tensor(parameters) else parameters) if p.grad is not None]
+    total = 0.0
+    tp_rank = bwc_rank(mpu)
+    for p in parameters:
+        if hasattr(p, "ds_pipe_replicated") and p.ds_pipe_replicated:
+            continue
+        if tp_rank > 0 and not is_model_parallel_parameter(p):
+            continue
+        total += float(p.grad.numel() - torch.count_nonzero(p.grad))
+    t = torch.tensor([total], dtype=torch.float32, device=get_accelerator().current_device_name()
+                     if get_accelerator().is_available() else "cpu")
+    if mpu is not None and dist.is_initialized():
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=mpu.get_model_parallel_group())
+    return t[0].item()
+
+
+def bwc_rank(mpu) -> int:
+    if mpu is None:
+        return 0
+    for n in ("get_tensor_model_parallel_rank", "get_model_parallel_rank"):
+        if hasattr(mpu, n):
+            return getattr(mpu, n)()
+    return 0
+
+
+def get_weight_norm(parameters, norm_type=2, mpu=None):
+    """Norm of the parameter VALUES (replicated parameters counted once across model-parallel ranks)."""
+    parameters = [parameters] if torch.is_tensor(parameters) else list(parameters)
+    tp_rank = bwc_rank(mpu)
+    own = [p.detach().float() for p in parameters
+           if not (hasattr(p, "ds_pipe_replicated") and p.ds_pipe_replicated)
+           and (tp_rank == 0 or is_model_parallel_parameter(p))]
+    if not own:
+        return 0.0
+    return get_global_norm_of_tensors(own, norm_type=norm_type, mpu=mpu)
+
+
+mem_alloced = 0
+mem_cached = 0
+
+
+def memory_status(msg, print_rank=-1, reset_max=False):
+    """Allocated / cached device memory with deltas since the previous call."""
+    global mem_alloced, mem_cached
+    acc = get_accelerator()
+    if not acc.is_available():
+        return
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    if print_rank != -1 and rank != print_rank:
+        return
+    acc.synchronize()
+    if reset_max:
+        acc.reset_max_memory_cached(); acc.reset_max_memory_allocated()
+    new_alloced, new_cached = acc.memory_allocated(), acc.memory_cached()
+    da, dc = new_alloced - mem_alloced, new_cached - mem_cached
+    mem_alloced, mem_cached = new_alloced, new_cached
+    gb = 1024 ** 3
+    print(f"RANK={rank} MEMSTATS", msg, f"device={acc.current_device_name()} current alloc={new_alloced / gb:0.4f}GB "
+          f"(delta={da / gb:0.4f}GB max={acc.max_memory_allocated() / gb:0.4f}GB) current cache={new_cached / gb:0.4f}GB "
+          f"(delta={dc / gb:0.4f}GB max={acc.max_memory_cached() / gb:0.4f}GB)")
+
+
+def get_ma_status():
+    """Bytes currently allocated on the device (0 on other ranks than 0 when distributed, as the reference)."""
+    if dist.is_initialized() and dist.get_rank() != 0:
+        return 0
+    return get_accelerator().memory_allocated() if get_accelerator().is_available() else 0
+
+
+def all_gather_into_tensor_dp_groups(groups_flat, outputs, dp_process_group):
+    """``outputs[i]`` := all-gather of ``groups_flat[i]`` over that group's data-parallel process group."""
+    for gid, flat in enumerate(groups_flat):
+        pg = dp_process_group[gid] if isinstance(dp_process_group, (list, tuple)) else dp_process_group
+        dist.all_gather_into_tensor(outputs[gid], flat, group=pg)
+
+
+def get_tensor_bytes(item) -> int:
+    """Bytes of every tensor inside a nested list / tuple / dict structure."""
+    if torch.is_tensor(item):
+        return item.numel() * item.element_size()
+    if isinstance(item, (list, tuple)):
+        return sum(get_tensor_bytes(v) for v in item)
+    if isinstance(item, dict):
+        return sum(get_tensor_bytes(v) for v in item.values())
+    return 0
+
+
+def get_checkpoint_folder_size(save_dir, tag, local_rank=None) -> float:
+    """Size in GB of ``save_dir/tag``; ``local_rank`` restricts the answer to local rank 0 (node-local storage)."""
+    import os
+    if local_rank is not None and local_rank != 0:
+        return 0.0
+    folder = os.path.join(save_dir, str(tag))
+    total = 0
+    for root, _, files in os.walk(folder):
+        for f in files:
+            fp = os.path.join(root, f)
+            if not os.path.islink(fp):
+                total += os.path.getsize(fp)
+    return total / (1024 ** 3)
+
+
+class TLinear(torch.nn.Linear):
+    """Linear layer that stores its weight TRANSPOSED (``[in, out]``) so a ZeRO-3 gathered weight can be used by
+    ``matmul`` without a transpose copy (reference ``runtime/utils.py:1110-1133``)."""
+
+    def __init__(self, orig_layer, name=""):
+        self.name = name
+        super().__init__(orig_layer.weight.shape[1], orig_layer.weight.shape[0], bias=(orig_layer.bias is not None))
+        self.weight.data = orig_layer.weight.data.t().contiguous()
+        self.bias = orig_layer.bias
+        self._fwd_func = self._fwd_bias_add if self.bias is not None else self._fwd
+
+    def _fwd(self, input):
+        return torch.matmul(input, self.weight)
+
+    def _fwd_bias_add(self, input):
+        return self._fwd(input) + self.bias
+
+    def forward(self, input):
+        return self._fwd_func(input)
+
+
+def get_inactive_params(param_list):
+    """ZeRO-3 parameters that are currently partitioned away (must be gathered before use)."""
+    from .zero.partition_parameters import ZeroParamStatus
+    return [p for p in param_list if hasattr(p, "ds_id") and p.ds_status == ZeroParamStatus.NOT_AVAILABLE]
+
+
+def get_norm_with_moe_layers(non_expert_norm, mpu, expert_tensors, norm_type=2):
+    """Global gradient norm of a model with experts: non-expert norm (already global) combined with every expert
+    group's norm, each reduced over ITS expert-parallel group (experts are not replicated across it)."""
+    def to_tensor(v):
+        return v.detach().float().reshape(1) if torch.is_tensor(v) else torch.tensor([float(v)])
+    dev = next((t.device for ts in expert_tensors.values() for t in ts), torch.device("cpu"))
+    inf_norm = norm_type == float("inf")
+    total = to_tensor(non_expert_norm).to(dev)
+    total = total if inf_norm else total ** norm_type
+    for group_name, tensors in expert_tensors.items():
+        if not tensors:
+            continue
+        if inf_norm:
+            local = torch.stack([t.detach().abs().max().float() for t in tensors]).max().reshape(1)
+        else:
+            local = torch.stack([t.detach().float().norm(norm_type) ** norm_type for t in tensors]).sum().reshape(1)
+        group = groups._get_expert_parallel_group(group_name) if dist.is_initialized() else None
+        if group is not None:
+            dist.all_reduce(local, op=dist.ReduceOp.MAX if inf_norm else dist.ReduceOp.SUM, group=group)
+        total = torch.maximum(total, local) if inf_norm else total + local
+    total = total if inf_norm else total ** (1.0 / norm_type)
+    out = float(total.item())
+    return -1 if (out == float("inf") or out != out) else out
+
+
+def get_norm_with_moe_layers_fast(all_groups_norm, group):
+    """Variant for BF16 / ZeRO-1 where ``all_groups_norm`` already holds this rank's contribution: average the scaled
+    norm over ``group`` so expert parameters (sharded over expert-data-parallel ranks) are counted once."""
+    scaled = all_groups_norm * 1.0 / float(dist.get_world_size(group=group))
+    t = torch.tensor([float(scaled)], dtype=torch.float32,
+                     device=get_accelerator().current_device_name() if get_accelerator().is_available() else "cpu")
+    dist.all_reduce(t, group=group)
+    return t.item()
+
+
+def offload_adam_states(optimizer, device, pin_memory=False, non_blocking=False):
+    from .zero.offload_states import offload_adam_states as _f
+    return _f(optimizer, device, pin_memory=pin_memory, non_blocking=non_blocking)
+
+
+def reload_adam_states(optimizer, device, non_blocking=False):
+    from .zero.offload_states import reload_adam_states as _f
+    return _f(optimizer, device, non_blocking=non_blocking)
+
+
+def compare_tensors_in_structures(inputs1, inputs2) -> bool:
+    """Same nesting, same keys, and ``torch.equal`` tensors (non-tensor leaves compared with ``==``)."""
+    if type(inputs1) != type(inputs2):
+        return False
+    if isinstance(inputs1, (list, tuple)):
+        return len(inputs1) == len(inputs2) and all(compare_tensors_in_structures(a, b) for a, b in zip(inputs1, inputs2))
+    if isinstance(inputs1, dict):
+        return inputs1.keys() == inputs2.keys() and all(compare_tensors_in_structures(inputs1[k], inputs2[k])
+                                                        for k in inputs1)
+    if torch.is_tensor(inputs1):
+        return inputs1.device == inputs2.device and torch.equal(inputs1, inputs2)
+    return inputs1 == inputs2

@@ -101,6 +101,8 @@ def get_model_parallel_world_size():
 def get_tensor_model_parallel_rank():
     if mpu is not None:
         return _mpu_call("get_tensor_model_parallel_rank", "get_model_parallel_rank")
+    if globals().get("_TP_RANK_OVERRIDE") is not None:
+        return globals()["_TP_RANK_OVERRIDE"]
     g = _TENSOR_PARALLEL_GROUP
     return dist.get_rank(g) if g is not None else 0
 
@@ -405,3 +407,27 @@ def reset_for_tests():
     for d in (_EXPERT_PARALLEL_GROUP, _EXPERT_DATA_PARALLEL_GROUP, _EXPERT_PARALLEL_RANKS,
               _EXPERT_DATA_PARALLEL_RANKS, _ALL_TO_ALL_GROUP):
         d.clear()
+
+
+# ---- explicit overrides used by inference / hybrid code that builds its own tensor-parallel layout
+_TP_RANK_OVERRIDE = None
+
+
+def set_tensor_model_parallel_world_size(world_size):
+    global _TP_SIZE
+    _TP_SIZE = int(world_size)
+
+
+def set_tensor_model_parallel_rank(rank):
+    global _TP_RANK_OVERRIDE
+    _TP_RANK_OVERRIDE = None if rank is None else int(rank)
+
+
+def get_tensor_model_parallel_src_rank():
+    """Global rank of the first member of this rank's tensor-parallel group (the broadcast source for its inputs)."""
+    tp = max(1, get_tensor_model_parallel_world_size() or 1)
+    return (dist.get_rank() // tp) * tp if dist.is_initialized() else 0
+
+
+def get_data_parallel_rank():
+    return _get_data_parallel_rank()

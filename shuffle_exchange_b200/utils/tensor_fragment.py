@@ -213,3 +213,37 @@ def set_full_hp_param(self, value, optim_state_key=None):
     if optim_state_key is None:
         return safe_set_full_fp32_param(self, value)
     return safe_set_full_optimizer_state(self, value, optim_state_key)
+
+
+# ---- reference-named helpers (``tensor_fragment.py:19-70,134-190``)
+class fragment_address:
+    """``numel`` elements starting at ``start`` of a flat buffer."""
+
+    def __init__(self, numel: int, start: int):
+        self.numel, self.start = int(numel), int(start)
+
+    def __repr__(self):
+        return f"fragment_address(numel={self.numel}, start={self.start})"
+
+
+def map_to_flat_opt_states(flat_hp_tensor, lp_tensors, optim_state, opt_keys):
+    """The reference builds, for every optimizer-state key, one flat tensor out of the per-parameter fragments and
+    re-points the fragments into it.  Here optimizer state is CREATED flat (one tensor per flat group, parameters are
+    views by offset), so there is nothing to re-map; the call validates that the flat state exists for the keys."""
+    state = optim_state.get(flat_hp_tensor, {})
+    missing = [k for k in opt_keys if k not in state]
+    if missing:
+        raise KeyError(f"optimizer state of the flat group lacks {missing}")
+    for k in opt_keys:
+        if torch.is_tensor(state[k]) and state[k].numel() not in (1, flat_hp_tensor.numel()):
+            raise ValueError(f"optimizer state {k!r} is not flat over the group ({state[k].numel()} vs "
+                             f"{flat_hp_tensor.numel()} elements)")
+
+
+def get_full_hp_grad(self):
+    """Bound as ``param.get_full_hp_grad()``: full fp32 gradient assembled from the shards (collective)."""
+    return safe_get_full_grad(self)
+
+
+def set_full_hp_grad(self, value):
+    return safe_set_full_grad(self, value)

@@ -274,3 +274,35 @@ def test_autotuner_micro_batch_size_search_with_a_fake_runner():
     name = f"{C.TUNING_MICRO_BATCH_SIZE_PREFIX}1"
     assert t.get_plateau_mbs(name) == 8
     assert t.run_tuning_micro_batch_sizes([4, 8], 6, 1, stage=1) == 4     # batch-size cap
+
+
+def test_runtime_utils_reference_helpers(tmp_path):
+    import torch
+    from shuffle_exchange_b200.runtime import utils as U
+    nested = {"a": [torch.ones(2), (torch.zeros(3, dtype=torch.float16), 5)], "b": "x"}
+    assert U.get_tensor_bytes(nested) == 2 * 4 + 3 * 2
+    c = U.copy_to_device(nested, "cpu", torch.is_tensor)
+    assert U.compare_tensors_in_structures(nested, c) and c["a"][0] is not None
+    c["a"][0][0] = 7
+    assert U.compare_tensors_in_structures(nested, c) == bool(nested["a"][0][0] == 7)
+    assert not U.compare_tensors_in_structures([1], (1,))
+    t = torch.tensor([1.0, float("inf"), float("nan")])
+    assert U.mask_nan_or_inf_with_val_inplace(t, val=-1.0).tolist() == [1.0, -1.0, -1.0]
+    lin = torch.nn.Linear(4, 3)
+    tl = U.TLinear(lin)
+    x = torch.randn(2, 4)
+    assert tl.weight.shape == (4, 3) and torch.allclose(tl(x), lin(x), atol=1e-6)
+    p = torch.nn.Parameter(torch.tensor([3.0, 0.0, 4.0]))
+    p.grad = torch.tensor([3.0, 0.0, 4.0])
+    assert abs(U.get_flattened_grad_norm([p]) - 5.0) < 1e-6 and U.get_grad_zeros([p]) == 1.0
+    assert abs(U.get_flattened_grad_norm([p], grad_norm_mask=[torch.tensor([[0, 1]])]) - 4.0) < 1e-6
+    assert abs(U.get_weight_norm([p]) - 5.0) < 1e-6
+    assert U.get_norm_with_moe_layers(3.0, None, {"ep": [torch.tensor([4.0])]}) == 5.0
+    assert U.get_norm_with_moe_layers(float("inf"), None, {}) == -1
+    (tmp_path / "tag").mkdir(); (tmp_path / "tag" / "f.bin").write_bytes(b"x" * 2048)
+    assert abs(U.get_checkpoint_folder_size(str(tmp_path), "tag") - 2048 / 1024 ** 3) < 1e-12
+    assert U.get_checkpoint_folder_size(str(tmp_path), "tag", local_rank=1) == 0.0
+    assert U.DummyOptim([p]).param_groups[0]["params"] == [p] and U.get_ma_status() == 0
+    with U.noop_context(lambda: 3) as v:
+        assert v == 3
+    assert U.get_inactive_params([p]) == []

@@ -219,3 +219,40 @@ def _shm_allreduce(rank, world):
 def test_shared_memory_allreduce_matches_gloo(world):
     from conftest import run_dist
     run_dist(_shm_allreduce, world=world)
+
+
+def test_reference_named_helpers_lr_overrides_groups_debug_comm_switches(capsys):
+    import argparse
+    from shuffle_exchange_b200.comm import comm
+    from shuffle_exchange_b200.comm.torch import all_reduce_comm_off, backward_comm_off
+    from shuffle_exchange_b200.runtime import lr_schedules as L
+    from shuffle_exchange_b200.utils import debug, groups
+    from shuffle_exchange_b200.utils import tensor_fragment as tf
+    p = {"warmup_max_lr": 0.1}
+    L.override_params(argparse.Namespace(warmup_max_lr=0.5, cycle_min_lr=None), p)
+    assert p == {"warmup_max_lr": 0.5} and L.update_lr([{"lr": 0}, {"lr": 0}], [1, 2]) == [1, 2]
+    groups.set_tensor_model_parallel_world_size(4); groups.set_tensor_model_parallel_rank(3)
+    try:
+        assert groups.get_tensor_model_parallel_world_size() == 4 and groups.get_tensor_model_parallel_rank() == 3
+    finally:
+        groups.set_tensor_model_parallel_rank(None); groups.set_tensor_model_parallel_world_size(1)
+    assert groups.get_tensor_model_parallel_src_rank() == 0
+    m = torch.nn.Linear(2, 2)
+    debug.debug_extract_module_and_param_names(m)
+    assert "numel=4" in debug.debug_param2name_id_numel(m.weight) and "Linear" in debug.debug_module2name_class(m)
+    debug.print_backward_tensors(m(torch.ones(1, 2)).sum())
+    assert "leaf (2, 2)" in capsys.readouterr().out
+    debug.debug_clear_module_and_param_names()
+    assert debug.debug_param2name(m.weight) == "unknown"
+    w = torch.zeros(4)
+    tf.map_to_flat_opt_states(w, [], {w: {"exp_avg": torch.zeros(4)}}, ["exp_avg"])
+    with pytest.raises(KeyError):
+        tf.map_to_flat_opt_states(w, [], {w: {}}, ["exp_avg"])
+    try:
+        all_reduce_comm_off(True)
+        assert comm._off("ALL_REDUCE") and isinstance(comm.all_reduce(torch.ones(1)), (comm.Noop, torch.Tensor, type(None)))
+    finally:
+        backward_comm_off(False)
+    assert not comm._off("ALL_REDUCE") and not comm.in_aml() and comm.init_deepspeed_backend("hccl") is None
+    with pytest.raises(ValueError):
+        comm.init_deepspeed_backend("carrier-pigeon")
