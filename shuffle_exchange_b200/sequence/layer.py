@@ -20,25 +20,38 @@ from torch.nn import Module
 from ..comm import comm as dist
 
 
+def pre_all2all_fun(P: int, scatter_idx: int):
+    """Layout step in front of the equal-split all-to-all: split dim ``scatter_idx`` into ``[P, s/P]`` and bring the
+    ``P`` axis to the front, contiguous (one block per destination rank)."""
+    def pre(x: Tensor) -> Tensor:
+        assert x.shape[scatter_idx] % P == 0, f"dim {scatter_idx} ({x.shape[scatter_idx]}) not divisible by sp={P}"
+        shp = list(x.shape)
+        shp[scatter_idx: scatter_idx + 1] = [P, shp[scatter_idx] // P]
+        return x.reshape(shp).movedim(scatter_idx, 0).contiguous()
+    return pre
+
+
+def post_all2all(gather_idx: int):
+    """Layout step behind it: ``out[p]`` is the block received from rank ``p``; concatenate the blocks along
+    ``gather_idx``."""
+    def post(out: Tensor) -> Tensor:
+        out = out.movedim(0, gather_idx)               # [.., P, gather, ..]
+        shp = list(out.shape)
+        shp[gather_idx: gather_idx + 2] = [shp[gather_idx] * shp[gather_idx + 1]]
+        return out.reshape(shp)
+    return post
+
+
 def _a2a_equal(x: Tensor, scatter_idx: int, gather_idx: int, group) -> Tensor:
     """All-to-all that splits dim ``scatter_idx`` into P parts and concatenates the received parts
     along ``gather_idx`` (P = group size).  Works for any tensor rank."""
     P = dist.get_world_size(group)
     if P == 1:
         return x
-    assert x.shape[scatter_idx] % P == 0, f"dim {scatter_idx} ({x.shape[scatter_idx]}) not divisible by sp={P}"
-    # [.., P, s/P, ..] -> bring the P axis to the front
-    shp = list(x.shape)
-    shp[scatter_idx: scatter_idx + 1] = [P, shp[scatter_idx] // P]
-    t = x.reshape(shp).movedim(scatter_idx, 0).contiguous()
+    t = pre_all2all_fun(P, scatter_idx)(x)
     out = torch.empty_like(t)
     dist.all_to_all_single(out, t, group=group)
-    # out[p] is the block received from rank p: concatenate along gather_idx
-    g = gather_idx if gather_idx < scatter_idx else gather_idx  # dims after removal of the split axis keep index
-    out = out.movedim(0, g)                       # [.., P, gather, ..]
-    shp = list(out.shape)
-    shp[g: g + 2] = [shp[g] * shp[g + 1]]
-    return out.reshape(shp)
+    return post_all2all(gather_idx)(out)
 
 
 def _a2a_uneven_heads(x: Tensor, scatter_idx: int, gather_idx: int, group, num_heads: int) -> Tensor:
@@ -62,6 +75,22 @@ def _a2a_uneven_heads(x: Tensor, scatter_idx: int, gather_idx: int, group, num_h
         recv.append(torch.empty(shp, dtype=x.dtype, device=x.device))
     dist.all_to_all(recv, parts, group=group)
     return torch.cat(recv, dim=gather_idx)
+
+
+def uneven_heads_all2all(input: Tensor, scatter_idx: int, gather_idx: int, batch_dim_idx: int, group,
+                         num_heads: Optional[int] = None) -> Tensor:
+    """Ulysses all-to-all for head counts that do not divide the sequence-parallel size (reference
+    ``sequence/layer.py:110-215``): the first ``num_heads % P`` ranks take one head more.  Forward direction (heads
+    scattered, sequence gathered) infers ``num_heads`` from the tensor; the reverse direction needs it."""
+    if num_heads is None:
+        if scatter_idx >= 2:
+            num_heads = input.shape[scatter_idx]
+        else:
+            from ..module_inject.tp_shard import get_num_attention_heads
+            num_heads = get_num_attention_heads()
+            if not num_heads:
+                raise ValueError("reverse uneven all-to-all needs num_heads")
+    return _a2a_uneven_heads(input, scatter_idx, gather_idx, group, num_heads)
 
 
 def single_all_to_all(input: Tensor, scatter_idx: int, gather_idx: int, batch_dim_idx: int, group,
