@@ -393,3 +393,147 @@ class BNLayer_Compress(nn.BatchNorm2d):
         self.running_mean = self.running_mean[keep]
         self.running_var = self.running_var[keep]
         self.num_features = self.weight.size(0)
+
+
+# ================================================================================= Megatron-style tensor-parallel variants
+# Reference ``compression/basic_layer.py:600-840``: Megatron's ColumnParallelLinear / RowParallelLinear re-based on
+# LinearLayer_Compress so QAT / pruning also applies to tensor-parallel models.  ``mpu`` is the Megatron model-parallel
+# unit (``get_model_parallel_world_size / _rank / _group``).
+def _mp_group(mpu):
+    return mpu.get_model_parallel_group() if hasattr(mpu, "get_model_parallel_group") else mpu.get_tensor_model_parallel_group()
+
+
+def _mp_world(mpu) -> int:
+    return mpu.get_model_parallel_world_size() if hasattr(mpu, "get_model_parallel_world_size") \
+        else mpu.get_tensor_model_parallel_world_size()
+
+
+def _mp_rank(mpu) -> int:
+    return mpu.get_model_parallel_rank() if hasattr(mpu, "get_model_parallel_rank") else mpu.get_tensor_model_parallel_rank()
+
+
+def split_tensor_along_last_dim(tensor, num_partitions, contiguous_split_chunks=False):
+    assert tensor.size(-1) % num_partitions == 0, f"{tensor.size(-1)} is not divisible by {num_partitions}"
+    parts = torch.split(tensor, tensor.size(-1) // num_partitions, dim=-1)
+    return tuple(p.contiguous() for p in parts) if contiguous_split_chunks else parts
+
+
+def _reduce(input_, mpu):
+    if _mp_world(mpu) > 1:
+        from .. import comm as dist
+        dist.all_reduce(input_, group=_mp_group(mpu))
+    return input_
+
+
+def _split(input_, mpu):
+    world = _mp_world(mpu)
+    return input_ if world == 1 else split_tensor_along_last_dim(input_, world)[_mp_rank(mpu)].contiguous()
+
+
+def _gather(input_, mpu):
+    world = _mp_world(mpu)
+    if world == 1:
+        return input_
+    from .. import comm as dist
+    parts = [torch.empty_like(input_) for _ in range(world)]
+    parts[_mp_rank(mpu)] = input_
+    dist.all_gather(parts, input_.contiguous(), group=_mp_group(mpu))
+    return torch.cat(parts, dim=-1).contiguous()
+
+
+class _CopyToModelParallelRegion(torch.autograd.Function):
+    """Identity forward, all-reduce backward (input of a column-parallel layer)."""
+    @staticmethod
+    def forward(ctx, input_, mpu):
+        ctx.mpu = mpu
+        return input_
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        return _reduce(grad_output.clone(), ctx.mpu), None
+
+
+class _ReduceFromModelParallelRegion(torch.autograd.Function):
+    """All-reduce forward, identity backward (output of a row-parallel layer)."""
+    @staticmethod
+    def forward(ctx, input_, mpu):
+        return _reduce(input_.clone(), mpu)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        return grad_output, None
+
+
+class _ScatterToModelParallelRegion(torch.autograd.Function):
+    """Keep this rank's chunk of the last dimension; gather in backward."""
+    @staticmethod
+    def forward(ctx, input_, mpu):
+        ctx.mpu = mpu
+        return _split(input_, mpu)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        return _gather(grad_output, ctx.mpu), None
+
+
+class _GatherFromModelParallelRegion(torch.autograd.Function):
+    """Concatenate the ranks' chunks along the last dimension; split in backward."""
+    @staticmethod
+    def forward(ctx, input_, mpu):
+        ctx.mpu = mpu
+        return _gather(input_, mpu)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        return _split(grad_output, ctx.mpu), None
+
+
+def copy_to_model_parallel_region(input_, mpu): return _CopyToModelParallelRegion.apply(input_, mpu)
+def reduce_from_model_parallel_region(input_, mpu): return _ReduceFromModelParallelRegion.apply(input_, mpu)
+def scatter_to_model_parallel_region(input_, mpu): return _ScatterToModelParallelRegion.apply(input_, mpu)
+def gather_from_model_parallel_region(input_, mpu): return _GatherFromModelParallelRegion.apply(input_, mpu)
+
+
+class ColumnParallelLinear_Compress(LinearLayer_Compress):
+    """``Y = X A + b`` with ``A`` split by output columns over the model-parallel group."""
+
+    def __init__(self, mpu, input_size, output_size, bias=True, gather_output=True, skip_bias_add=False):
+        self.mpu = mpu
+        self.input_size, self.output_size = input_size, output_size
+        self.gather_output, self.skip_bias_add = gather_output, skip_bias_add
+        world = _mp_world(mpu)
+        assert output_size % world == 0, f"output size {output_size} is not divisible by the model-parallel size {world}"
+        self.output_size_per_partition = output_size // world
+        super().__init__(input_size, self.output_size_per_partition, bias=bias)
+
+    def forward(self, input_):
+        x = copy_to_model_parallel_region(input_, self.mpu)
+        bias = self.bias if not self.skip_bias_add else None
+        out, b = super().forward(x, True)
+        if bias is not None and b is not None:
+            out = out + b
+        if self.gather_output:
+            out = gather_from_model_parallel_region(out, self.mpu)
+        return out, (self.bias if self.skip_bias_add else None)
+
+
+class RowParallelLinear_Compress(LinearLayer_Compress):
+    """``Y = X A + b`` with ``A`` split by input rows: partial products are all-reduced, the bias added once."""
+
+    def __init__(self, mpu, input_size, output_size, bias=True, input_is_parallel=False, skip_bias_add=False):
+        self.mpu = mpu
+        self.input_size, self.output_size = input_size, output_size
+        self.input_is_parallel, self.skip_bias_add = input_is_parallel, skip_bias_add
+        world = _mp_world(mpu)
+        assert input_size % world == 0, f"input size {input_size} is not divisible by the model-parallel size {world}"
+        self.input_size_per_partition = input_size // world
+        super().__init__(self.input_size_per_partition, output_size, bias=bias)
+
+    def forward(self, input_):
+        x = input_ if self.input_is_parallel else scatter_to_model_parallel_region(input_, self.mpu)
+        partial, b = super().forward(x, True)
+        out = reduce_from_model_parallel_region(partial, self.mpu)
+        if not self.skip_bias_add and b is not None:
+            out = out + b
+            return out, None
+        return out, b

@@ -12,6 +12,7 @@ import base64
 import copy
 import json
 import os
+from enum import Enum
 from typing import Any, Dict, List, Optional, Union
 
 import hjson
@@ -497,3 +498,175 @@ class DeepSpeedConfig:
             if arg != "_param_dict":
                 logger.info(f"  {arg} {'.' * (29 - len(arg))} {getattr(self, arg)}")
         self.print_user_config()
+
+
+# ================================================================================================================
+# Module-level getters under the reference's names (``runtime/config.py:111-640``): each reads ONE setting straight
+# from a raw config dictionary, applying the same default the engine uses.  Kept for scripts that import them.
+class DtypeEnum(Enum):
+    fp16 = (torch.float16, "torch.float16", "fp16", "float16", "half")
+    fp32 = (torch.float32, "torch.float32", "fp32", "float32", "float")
+    bf16 = (torch.bfloat16, "torch.bfloat16", "bf16", "bfloat16", "bfloat")
+    int8 = (torch.int8, "torch.int8", "int8")
+
+    def __new__(cls, *values):
+        obj = object.__new__(cls)
+        obj._value_ = values[0]
+        for other in values[1:]:
+            cls._value2member_map_[other] = obj
+        obj._all_values = values
+        return obj
+
+    def __repr__(self):
+        return f"<{type(self).__name__}.{self.name}: {', '.join(map(repr, self._all_values))}>"
+
+
+def _sec(d, key):
+    v = (d or {}).get(key, {})
+    return v if isinstance(v, dict) else {}
+
+
+def get_pld_enabled(d): return bool(_sec(d, "progressive_layer_drop").get("enabled", False))
+def get_pld_params(d):
+    if "progressive_layer_drop" not in (d or {}):
+        return False
+    p = dict(_sec(d, "progressive_layer_drop")); p.pop("enabled", None); return p
+def get_amp_enabled(d): return bool(_sec(d, "amp").get("enabled", False))
+def get_amp_params(d):
+    if "amp" not in (d or {}):
+        return False
+    p = dict(_sec(d, "amp")); p.pop("enabled", None); return p
+def get_torch_autocast_enabled(d): return bool(_sec(d, "torch_autocast").get("enabled", False))
+def get_torch_autocast_dtype(d):
+    return DtypeEnum(_sec(d, "torch_autocast").get("dtype", "bfloat16")).value
+def get_lower_precision_safe_modules(d): return _sec(d, "torch_autocast").get("lower_precision_safe_modules")
+def get_gradient_accumulation_steps(d): return (d or {}).get("gradient_accumulation_steps", None)
+def get_sparse_gradients_enabled(d): return (d or {}).get("sparse_gradients", False)
+def get_communication_data_type(d, key="communication_data_type"):
+    v = (d or {}).get(key, None)
+    if v is None:
+        return None
+    if v not in _COMM_DTYPES:
+        raise ValueError(f"Invalid communication_data_type. Supported data types: ['fp16', 'bf16', 'fp32']. Got: {v}")
+    return _COMM_DTYPES[v]
+def get_prescale_gradients(d): return (d or {}).get("prescale_gradients", False)
+def get_gradient_predivide_factor(d): return (d or {}).get("gradient_predivide_factor", 1.0)
+def get_steps_per_print(d): return (d or {}).get("steps_per_print", 10)
+def get_disable_allgather(d): return (d or {}).get("disable_allgather", False)
+def get_dump_state(d): return (d or {}).get("dump_state", False)
+def get_gradient_clipping(d): return (d or {}).get("gradient_clipping", 0.0)
+def get_graph_harvesting(d): return (d or {}).get("graph_harvesting", False)
+def get_train_batch_size(d): return (d or {}).get("train_batch_size", None)
+def get_train_micro_batch_size_per_gpu(d): return (d or {}).get("train_micro_batch_size_per_gpu", None)
+def get_wall_clock_breakdown(d): return (d or {}).get("wall_clock_breakdown", False)
+def get_memory_breakdown(d): return (d or {}).get("memory_breakdown", False)
+def get_dataloader_drop_last(d): return (d or {}).get("dataloader_drop_last", False)
+def get_zero_allow_untested_optimizer(d): return (d or {}).get("zero_allow_untested_optimizer", False)
+def get_zero_force_ds_cpu_optimizer(d): return (d or {}).get("zero_force_ds_cpu_optimizer", True)
+
+
+def get_optimizer_name(d):
+    o = _sec(d, "optimizer")
+    return o.get("type") if "type" in o else None
+def get_optimizer_params(d):
+    return _sec(d, "optimizer").get("params") if get_optimizer_name(d) is not None else None
+def get_optimizer_gradient_clipping(d):
+    p = get_optimizer_params(d)
+    return p.get("max_grad_norm") if p else None
+def get_optimizer_legacy_fusion(d): return _sec(d, "optimizer").get("legacy_fusion", False)
+def get_scheduler_name(d):
+    s = _sec(d, "scheduler")
+    return s.get("type") if "type" in s else None
+def get_scheduler_params(d):
+    return _sec(d, "scheduler").get("params") if get_scheduler_name(d) is not None else None
+
+
+def get_pipeline_config(d):
+    """``pipeline`` section with defaults filled."""
+    return PipelineConfig(**_sec(d, "pipeline")).model_dump()
+def get_hybrid_engine_config(d): return HybridEngineConfig(**_sec(d, "hybrid_engine"))
+def get_expert_data_topo_config(d): return (d or {}).get("use_data_before_expert_parallelism", False)
+def get_checkpoint_params(d): return _sec(d, "checkpoint")
+def get_data_types_params(d): return _sec(d, "data_types")
+def get_checkpoint_tag_validation_mode(checkpoint_params):
+    mode = str(checkpoint_params.get("tag_validation", "Warn")).upper()
+    if mode not in ("IGNORE", "WARN", "FAIL"):
+        raise DeepSpeedConfigError(f"Checkpoint config contains invalid tag_validation value of {mode}, expecting one of "
+                                   f"['IGNORE', 'WARN', 'FAIL']")
+    return mode
+def get_checkpoint_parallel_write_pipeline(checkpoint_params):
+    v = checkpoint_params.get("parallel_write", {}).get("pipeline_stage", False)
+    if v not in (True, False):
+        raise DeepSpeedConfigError(f"checkpoint::parallel_write::pipeline_stage value of '{v}' is invalid, "
+                                   f"expecting: true or false")
+    return v
+
+
+def get_eigenvalue_config(d):
+    if get_eigenvalue_enabled(d):
+        return (True, get_eigenvalue_verbose(d), get_eigenvalue_max_iter(d), get_eigenvalue_tol(d),
+                get_eigenvalue_stability(d), get_eigenvalue_gas_boundary_resolution(d), get_eigenvalue_layer_name(d),
+                get_eigenvalue_layer_num(d))
+    e = EigenvalueConfig()
+    return (False, e.verbose, e.max_iter, e.tol, e.stability, e.gas_boundary_resolution, e.layer_name, e.layer_num)
+def get_eigenvalue_enabled(d): return bool(_sec(d, "eigenvalue").get("enabled", False))
+def _eig(d, k): return _sec(d, "eigenvalue").get(k, getattr(EigenvalueConfig(), k))
+def get_eigenvalue_verbose(d): return _eig(d, "verbose")
+def get_eigenvalue_max_iter(d): return _eig(d, "max_iter")
+def get_eigenvalue_tol(d): return _eig(d, "tol")
+def get_eigenvalue_stability(d): return _eig(d, "stability")
+def get_eigenvalue_gas_boundary_resolution(d): return _eig(d, "gas_boundary_resolution")
+def get_eigenvalue_layer_name(d): return _eig(d, "layer_name")
+def get_eigenvalue_layer_num(d): return _eig(d, "layer_num")
+
+
+# ---- "sparse_attention" section: mode + that mode's layout parameters with defaults
+_SPARSE_COMMON = {"block": 16, "different_layout_per_head": False}
+_SPARSE_MODES = {
+    "dense": {},
+    "fixed": {"num_local_blocks": 4, "num_global_blocks": 1, "attention": "bidirectional",
+              "horizontal_global_attention": False, "num_different_global_patterns": 1},
+    "variable": {"num_random_blocks": 0, "local_window_blocks": [4], "global_block_indices": [0],
+                 "global_block_end_indices": None, "attention": "bidirectional", "horizontal_global_attention": False},
+    "bigbird": {"num_random_blocks": 1, "num_sliding_window_blocks": 3, "num_global_blocks": 1},
+    "bslongformer": {"num_sliding_window_blocks": 3, "global_block_indices": [0], "global_block_end_indices": None},
+}
+
+
+def get_sparse_attention_mode(sparsity): return sparsity.get("mode", "fixed")
+def get_sparse_attention_type(d): return _sec(d, "sparse_attention").get("attention", "bidirectional")
+def _sparse_cfg(sparsity, mode):
+    out = {"mode": mode, **{k: sparsity.get(k, v) for k, v in _SPARSE_COMMON.items()}}
+    out.update({k: sparsity.get(k, v) for k, v in _SPARSE_MODES[mode].items()})
+    return out
+def get_sparse_dense_config(sparsity): return _sparse_cfg(sparsity, "dense")
+def get_sparse_fixed_config(sparsity): return _sparse_cfg(sparsity, "fixed")
+def get_sparse_variable_config(sparsity): return _sparse_cfg(sparsity, "variable")
+def get_sparse_bigbird_config(sparsity): return _sparse_cfg(sparsity, "bigbird")
+def get_sparse_bslongformer_config(sparsity): return _sparse_cfg(sparsity, "bslongformer")
+def get_sparse_attention(d):
+    if "sparse_attention" not in (d or {}):
+        return None
+    sparsity = d["sparse_attention"]
+    mode = get_sparse_attention_mode(sparsity)
+    if mode not in _SPARSE_MODES:
+        raise NotImplementedError(f"Given sparsity mode, {mode}, has not been implemented yet!")
+    return _sparse_cfg(sparsity, mode)
+
+
+class DeepSpeedConfigWriter:
+    """Build / load / save a config dictionary (reference ``runtime/config.py:643-660``)."""
+
+    def __init__(self, data=None):
+        self.data = data if data is not None else {}
+
+    def add_config(self, key, value):
+        self.data[key] = value
+
+    def load_config(self, filename):
+        with open(filename, "r") as f:
+            self.data = json.load(f, object_pairs_hook=dict_raise_error_on_duplicate_keys)
+
+    def write_config(self, filename):
+        with open(filename, "w") as outfile:
+            json.dump(self.data, outfile)

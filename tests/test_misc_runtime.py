@@ -306,3 +306,39 @@ def test_runtime_utils_reference_helpers(tmp_path):
     with U.noop_context(lambda: 3) as v:
         assert v == 3
     assert U.get_inactive_params([p]) == []
+
+
+def _compress_tp(rank, world):
+    import torch
+    import torch.distributed as td
+    from shuffle_exchange_b200.compression.basic_layer import ColumnParallelLinear_Compress, RowParallelLinear_Compress
+
+    class MPU:
+        def get_model_parallel_world_size(self): return world
+        def get_model_parallel_rank(self): return rank
+        def get_model_parallel_group(self): return td.group.WORLD
+
+    torch.manual_seed(0)
+    full1, full2 = torch.nn.Linear(8, 12), torch.nn.Linear(12, 8)
+    col = ColumnParallelLinear_Compress(MPU(), 8, 12, gather_output=False)
+    row = RowParallelLinear_Compress(MPU(), 12, 8, input_is_parallel=True)
+    n = 12 // world
+    with torch.no_grad():
+        col.weight.copy_(full1.weight[rank * n:(rank + 1) * n]); col.bias.copy_(full1.bias[rank * n:(rank + 1) * n])
+        row.weight.copy_(full2.weight[:, rank * n:(rank + 1) * n]); row.bias.copy_(full2.bias)
+    x = torch.randn(3, 8, requires_grad=True)
+    xr = x.detach().clone().requires_grad_()
+    h, _ = col(x)
+    y, _ = row(torch.relu(h))
+    ref = full2(torch.relu(full1(xr)))
+    assert torch.allclose(y, ref, atol=1e-5)
+    y.sum().backward(); ref.sum().backward()
+    assert torch.allclose(x.grad, xr.grad, atol=1e-5)                  # input grad all-reduced over the group
+    assert torch.allclose(col.weight.grad, full1.weight.grad[rank * n:(rank + 1) * n], atol=1e-5)
+    col.enable_weight_quantization(8, 8, 1, True, "symmetric", 1)       # compression methods still apply
+    assert col(x.detach())[0].shape == (3, n)
+
+
+def test_compression_tensor_parallel_layers_match_dense():
+    from conftest import run_dist
+    run_dist(_compress_tp, world=2)
