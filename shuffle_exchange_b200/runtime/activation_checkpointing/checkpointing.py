@@ -375,3 +375,129 @@ def configure(mpu_, deepspeed_config=None, partition_activations=None, contiguou
 
 def is_configured():
     return _S.configured
+
+
+# ============================================================ reference-named helpers (``checkpointing.py:196-486``)
+# The checkpoint function above keeps its inputs as `_Saved` records; these are the same operations as free functions,
+# for code that drives partitioned / host-resident activations itself.
+def detach_variable(inputs, device=None):
+    """Detached copies (same ``requires_grad``) of a tensor or tuple of tensors, optionally moved to ``device``."""
+    if isinstance(inputs, tuple):
+        out = []
+        for inp in inputs:
+            if not torch.is_tensor(inp):
+                out.append(inp)
+                continue
+            x = inp.to(device=device) if device is not None else inp
+            x = x.detach()
+            x.requires_grad = inp.requires_grad
+            out.append(x)
+        return tuple(out)
+    raise RuntimeError("Only tuple of tensors is supported. Got Unsupported input type: ", type(inputs).__name__)
+
+
+def get_partition_size(item) -> int:
+    """Elements of ``item`` each model-parallel rank keeps (ceil division: the last rank's piece is zero-padded)."""
+    size = item.numel()
+    return (size + _S.mp_size - 1) // _S.mp_size if _S.mp_size > 1 else size
+
+
+def get_partition_start(item) -> int:
+    return min(get_partition_size(item) * _S.mp_rank, item.numel())
+
+
+def is_activation_to_checkpoint(item) -> bool:
+    """Tensors worth partitioning / offloading: floating point and at least one element per rank."""
+    return torch.is_tensor(item) and item.is_floating_point() and item.numel() >= max(1, _S.mp_size)
+
+
+def extract_tensors(all_objects):
+    """Split a tuple into ``(tensors, non_tensors, tensor_flags)`` so the tensors can go through autograd's
+    ``save_for_backward`` while everything else is kept aside."""
+    tensors = [o for o in all_objects if torch.is_tensor(o)]
+    non_tensors = [o for o in all_objects if not torch.is_tensor(o)]
+    flags = [torch.is_tensor(o) for o in all_objects]
+    if isinstance(all_objects, tuple):
+        return tuple(tensors), tuple(non_tensors), tuple(flags)
+    return tensors, non_tensors, flags
+
+
+def merge_tensors(tensor_objects, non_tensor_objects, tensor_flags):
+    """Inverse of :func:`extract_tensors`."""
+    merged, ti, ni = [], 0, 0
+    real_flags = tensor_flags[:-1] if len(tensor_flags) > len(tensor_objects) + len(non_tensor_objects) else tensor_flags
+    for is_tensor in real_flags:
+        if is_tensor:
+            merged.append(tensor_objects[ti]); ti += 1
+        else:
+            merged.append(non_tensor_objects[ni]); ni += 1
+    return tuple(merged)
+
+
+def partition_activations(args, cpu_checkpoint=False, contiguous_checkpoint=False):
+    """``[piece_0, size_0, piece_1, size_1, ...]``: this rank's slice of every checkpointable tensor followed by its
+    original shape (as a tensor), the layout :func:`gather_partitioned_activations` consumes."""
+    out = []
+    for item in args:
+        if not is_activation_to_checkpoint(item):
+            out.append(item)
+            continue
+        part = get_partition_size(item)
+        lo = get_partition_start(item)
+        flat = item.detach().contiguous().view(-1)
+        piece = flat.new_zeros(part)
+        hi = min(lo + part, flat.numel())
+        piece[: hi - lo] = flat[lo:hi]
+        if cpu_checkpoint:
+            piece = piece.to("cpu")
+        out.append(piece)
+        out.append(torch.tensor(list(item.shape), dtype=torch.long))
+    return out
+
+
+def gather_partitioned_activations(tensors, device=None):
+    """Rebuild full activations from ``[piece, size, piece, size, ...]`` (all-gather over the model-parallel group)."""
+    assert len(tensors) % 2 == 0, f"Expected even count of tensors, instead got {len(tensors)}"
+    out = []
+    for i in range(len(tensors) // 2):
+        piece, size = tensors[2 * i], tensors[2 * i + 1]
+        if not is_activation_to_checkpoint(piece) and piece.numel() * max(1, _S.mp_size) < max(1, _S.mp_size):
+            out.append(piece)
+            continue
+        shape = [int(s) for s in size.tolist()]
+        numel = 1
+        for s in shape:
+            numel *= s
+        if device is not None:
+            piece = piece.to(device)
+        if _S.mp_size > 1:
+            full = torch.empty(piece.numel() * _S.mp_size, dtype=piece.dtype, device=piece.device)
+            dist.all_gather_into_tensor(full, piece.contiguous(), group=_S.mp_group)
+        else:
+            full = piece
+        out.append(full[:numel].view(shape))
+    return out
+
+
+def get_partitioned_activations_for_backward(args, inputs, contiguous_checkpoint=False):
+    """What a checkpoint with partitioned activations saves: for every checkpointable input its piece and shape, other
+    inputs unchanged followed by a ``None`` placeholder (keeps the pairs aligned)."""
+    new_args = []
+    for i, (arg, inp) in enumerate(zip(args, inputs)):
+        if not is_activation_to_checkpoint(arg):
+            new_args += [arg, None]
+            continue
+        piece = partition_activations([arg])[0]
+        new_args += [piece, torch.tensor(list(arg.shape), dtype=torch.long)]
+    return new_args
+
+
+def get_cpu_activations_for_backward(args, inputs):
+    """Host copies of the checkpointable inputs (``cpu_checkpointing`` without partitioning)."""
+    new_args = []
+    for arg, inp in zip(args, inputs):
+        if not is_activation_to_checkpoint(arg):
+            new_args.append(arg)
+        else:
+            new_args.append(inp.detach().to("cpu"))
+    return new_args
