@@ -159,6 +159,40 @@ def parse_num_nodes(str_num_nodes: str, elastic_training: bool):
     raise RuntimeError("num_nodes {} is not in MIN:MAX format".format(str_num_nodes))
 
 
+def parse_node_config(node_config: str):
+    """``"host"`` -> ``("host", [])`` (all slots); ``"host:0,2,5"`` -> ``("host", [0, 2, 5])``."""
+    SLOT_LIST_START, SLOT_SEP = ":", ","
+    if SLOT_LIST_START not in node_config:
+        return node_config, []
+    hostname, slots = node_config.split(SLOT_LIST_START)
+    return hostname, [int(x) for x in slots.split(SLOT_SEP)]
+
+
+def parse_node_config_list(node_config_list):
+    """``["a:0,1", "b"]`` (the ``@``-separated pieces of an include / exclude string) -> ``{host: [slots]}``."""
+    out = collections.OrderedDict()
+    for node_config in node_config_list:
+        hostname, slots = parse_node_config(node_config)
+        if hostname in out:
+            raise ValueError(f"Duplicate hostname found in resource filter: {hostname}")
+        out[hostname] = slots
+    return out
+
+
+def run_autotuning(args, active_resources):
+    """``--autotuning {tune,run}``: explore ZeRO stage / micro-batch configurations with the Autotuner; ``run`` also
+    launches the job with the best configuration found (reference ``launcher/runner.py:356-382``)."""
+    from ..autotuning import Autotuner
+    tuner = Autotuner(args, active_resources)
+    logger.info("[Start] Running autotuning")
+    tuner.tune()
+    tuner.print_tuning_results()
+    logger.info("[End] Running autotuning")
+    tuner.write_optimal_config()
+    if args.autotuning == "run":
+        tuner.run_after_tuning()
+
+
 def main(args=None):
     args = parse_args(args)
     resource_pool = fetch_hostfile(args.hostfile)
@@ -189,6 +223,9 @@ def main(args=None):
             args.master_addr = out.split()[0]
         except Exception:
             args.master_addr = first
+    if args.autotuning != "":
+        run_autotuning(args, active)
+        return
     world_info = encode_world_info(active)
     multi_node_exec = args.force_multi or len(active) > 1
     env = os.environ.copy()

@@ -217,3 +217,193 @@ class MMapIndexedDatasetBuilder:
     def finalize(self, index_file):
         self._data_file.close()
         _Index.write(index_file, self._dtype, self._sizes, self._doc_idx)
+
+
+# ================================================================ helpers of the legacy ("lazy" / "cached") format
+# Reference ``indexed_dataset.py:60-330``: the pre-mmap fairseq format — ``TNTIDX`` header, explicit ``sizes`` /
+# ``data_offsets`` / ``dim_offsets`` arrays in the index, items read with ``file.readinto``.  Kept so datasets written
+# by older tooling can still be read and produced; new data should use the mmap builder above.
+_LEGACY_MAGIC = b"TNTIDX\x00\x00"
+
+
+def read_longs(f, n):
+    a = np.empty(n, dtype=np.int64)
+    f.readinto(a)
+    return a
+
+
+def write_longs(f, a):
+    f.write(np.array(a, dtype=np.int64))
+
+
+def create_doc_idx(sizes):
+    """Item indices at which documents start: an item of size 0 terminates a document."""
+    doc_idx = [0]
+    for i, s in enumerate(sizes):
+        if s == 0:
+            doc_idx.append(i + 1)
+    return doc_idx
+
+
+def exscan_from_cumsum_(arr):
+    """In place: an inclusive prefix sum becomes the exclusive one (shift right, first element 0)."""
+    if arr.size > 1:
+        arr[1:] = arr[:-1]
+    if arr.size > 0:
+        arr[0] = 0
+
+
+def get_pointers_with_total(sizes, elemsize, dtype):
+    """Byte offset of every item given item lengths (elements) and the element size; also the total byte count."""
+    pointers = np.array(sizes, dtype=dtype)
+    pointers *= elemsize
+    np.cumsum(pointers, axis=0, out=pointers)
+    total = int(pointers[-1]) if len(sizes) > 0 else 0
+    exscan_from_cumsum_(pointers)
+    return pointers, total
+
+
+class IndexedDatasetBuilder:
+    """Writer of the legacy format: ``add_item`` appends a tensor, an item of size 0 (``end_document``) closes a
+    document, ``finalize(index_file)`` writes the index."""
+    element_sizes = {np.uint8: 1, np.int8: 1, np.int16: 2, np.int32: 4, np.int64: 8, np.float32: 4, np.float64: 8,
+                     np.uint16: 2}
+
+    def __init__(self, out_file, dtype=np.int32):
+        self.out_file = open(out_file, "wb")
+        self.dtype = dtype
+        self.data_offsets, self.dim_offsets, self.sizes, self.doc_idx = [0], [0], [], [0]
+        self.element_size = self.element_sizes[self.dtype]
+
+    def add_item(self, tensor):
+        arr = np.array(tensor.numpy() if torch.is_tensor(tensor) else tensor, dtype=self.dtype)
+        nbytes = self.out_file.write(arr)
+        self.data_offsets.append(self.data_offsets[-1] + nbytes // self.element_size)
+        for s in arr.shape:
+            self.sizes.append(s)
+        self.dim_offsets.append(self.dim_offsets[-1] + arr.ndim)
+
+    def end_document(self):
+        self.doc_idx.append(len(self.sizes))
+
+    def merge_file_(self, another_file):
+        other = IndexedDataset(another_file)
+        assert other.dtype == self.dtype
+        base = self.data_offsets[-1]
+        self.data_offsets.extend(base + o for o in other.data_offsets[1:])
+        self.sizes.extend(other.sizes)
+        dbase = self.dim_offsets[-1]
+        self.dim_offsets.extend(dbase + o for o in other.dim_offsets[1:])
+        ibase = len(self.sizes) - len(other.sizes)
+        self.doc_idx.extend(ibase + d for d in other.doc_idx[1:])
+        with open(data_file_path(another_file), "rb") as f:
+            while True:
+                chunk = f.read(1 << 20)
+                if not chunk:
+                    break
+                self.out_file.write(chunk)
+
+    def finalize(self, index_file):
+        self.out_file.close()
+        import struct
+        with open(index_file, "wb") as f:
+            f.write(_LEGACY_MAGIC)
+            f.write(struct.pack("<Q", 1))
+            f.write(struct.pack("<QQ", code(self.dtype), self.element_size))
+            f.write(struct.pack("<QQ", len(self.data_offsets) - 1, len(self.sizes)))
+            f.write(struct.pack("<Q", len(self.doc_idx)))
+            write_longs(f, self.dim_offsets)
+            write_longs(f, self.data_offsets)
+            write_longs(f, self.sizes)
+            write_longs(f, self.doc_idx)
+
+
+class IndexedDataset(torch.utils.data.Dataset):
+    """Reader of the legacy format (items read from the ``.bin`` file on demand)."""
+
+    def __init__(self, path):
+        super().__init__()
+        self.path = path
+        import struct
+        with open(index_file_path(path), "rb") as f:
+            magic = f.read(8)
+            assert magic == _LEGACY_MAGIC, "Index file doesn't match expected format. Make sure that --dataset-impl is configured properly."
+            assert struct.unpack("<Q", f.read(8)) == (1,)
+            dcode, self.element_size = struct.unpack("<QQ", f.read(16))
+            self.dtype = _DTYPES[dcode]
+            self._len, n_sizes = struct.unpack("<QQ", f.read(16))
+            n_docs = struct.unpack("<Q", f.read(8))[0]
+            self.dim_offsets = read_longs(f, self._len + 1)
+            self.data_offsets = read_longs(f, self._len + 1)
+            self.sizes = read_longs(f, n_sizes)
+            self.doc_idx = read_longs(f, n_docs)
+        self.data_file = None
+
+    def _open(self):
+        if self.data_file is None:
+            self.data_file = open(data_file_path(self.path), "rb", buffering=0)
+
+    def __len__(self):
+        return self._len
+
+    def __getitem__(self, i):
+        if not 0 <= i < self._len:
+            raise IndexError("index out of range")
+        self._open()
+        shape = tuple(int(s) for s in self.sizes[self.dim_offsets[i]:self.dim_offsets[i + 1]])
+        a = np.empty(shape, dtype=self.dtype)
+        self.data_file.seek(int(self.data_offsets[i]) * self.element_size)
+        self.data_file.readinto(a)
+        return a
+
+    def __del__(self):
+        if getattr(self, "data_file", None):
+            self.data_file.close()
+
+    @staticmethod
+    def exists(path):
+        return os.path.exists(index_file_path(path)) and os.path.exists(data_file_path(path))
+
+    @property
+    def supports_prefetch(self):
+        return False
+
+
+class IndexedCachedDataset(IndexedDataset):
+    """Legacy reader with an in-memory cache filled by ``prefetch(indices)`` (one contiguous buffer)."""
+
+    def __init__(self, path):
+        super().__init__(path)
+        self.cache = None
+        self.cache_index = {}
+
+    @property
+    def supports_prefetch(self):
+        return True
+
+    def prefetch(self, indices):
+        if all(i in self.cache_index for i in indices):
+            return
+        self._open()
+        indices = sorted(set(indices))
+        total = sum(int(self.data_offsets[i + 1] - self.data_offsets[i]) for i in indices)
+        self.cache = np.empty(total, dtype=self.dtype)
+        self.cache_index.clear()
+        ptx = 0
+        for i in indices:
+            self.cache_index[i] = ptx
+            size = int(self.data_offsets[i + 1] - self.data_offsets[i])
+            a = self.cache[ptx: ptx + size]
+            self.data_file.seek(int(self.data_offsets[i]) * self.element_size)
+            self.data_file.readinto(a)
+            ptx += size
+        self.data_file.close()
+        self.data_file = None
+
+    def __getitem__(self, i):
+        if i not in self.cache_index:
+            return super().__getitem__(i)
+        shape = tuple(int(s) for s in self.sizes[self.dim_offsets[i]:self.dim_offsets[i + 1]])
+        ptx = self.cache_index[i]
+        n = int(np.prod(shape)) if shape else 1
+        return self.cache[ptx: ptx + n].reshape(shape).copy()
