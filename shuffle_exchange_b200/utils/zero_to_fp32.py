@@ -85,10 +85,82 @@ def get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag=None, exclude_f
     return out
 
 
-def convert_zero_checkpoint_to_fp32_state_dict(checkpoint_dir, output_file, tag=None, exclude_frozen_parameters=False):
+def _parse_size(size) -> int:
+    """``"5GB"`` / ``"200MB"`` / ``"1GiB"`` / int -> bytes."""
+    if isinstance(size, int):
+        return size
+    m = re.fullmatch(r"\s*([0-9.]+)\s*([KMGT]?i?B?)\s*", str(size), re.I)
+    if not m:
+        raise ValueError(f"cannot parse size {size!r}")
+    num, unit = float(m.group(1)), m.group(2).upper()
+    base = 1024 if "I" in unit else 1000
+    power = {"": 0, "B": 0, "K": 1, "M": 2, "G": 3, "T": 4}[unit.replace("I", "").replace("B", "") or ""]
+    return int(num * base ** power)
+
+
+def _shard_state_dict(sd, max_shard_bytes):
+    """Greedy split in insertion order: a new shard starts when the next tensor would exceed ``max_shard_bytes``."""
+    shards, cur, cur_bytes = [], OrderedDict(), 0
+    for name, t in sd.items():
+        nbytes = t.numel() * t.element_size() if torch.is_tensor(t) else 0
+        if cur and cur_bytes + nbytes > max_shard_bytes:
+            shards.append(cur)
+            cur, cur_bytes = OrderedDict(), 0
+        cur[name] = t
+        cur_bytes += nbytes
+    if cur or not shards:
+        shards.append(cur)
+    return shards
+
+
+def convert_zero_checkpoint_to_fp32_state_dict(checkpoint_dir, output_dir, max_shard_size="5GB",
+                                               safe_serialization=False, tag=None, exclude_frozen_parameters=False):
+    """Consolidate a ZeRO-1/2/3 checkpoint into fp32 weights loadable without this framework.
+
+    ``output_dir`` ending in ``.bin`` / ``.pt`` / ``.pth`` / ``.safetensors`` writes that single file (the older
+    calling convention).  Otherwise a directory is written the way HuggingFace shards checkpoints:
+    ``pytorch_model.bin`` (or ``model.safetensors``) when everything fits ``max_shard_size``, else
+    ``pytorch_model-0000i-of-0000n.bin`` plus ``pytorch_model.bin.index.json`` with the ``weight_map``."""
+    import json
     sd = get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag, exclude_frozen_parameters)
-    print(f"Saving fp32 state dict to {output_file}")
-    torch.save(sd, output_file)
+    save = torch.save
+    if safe_serialization:
+        try:
+            from safetensors.torch import save_file
+        except ImportError:
+            print("If you want to use `safe_serialization`, please `pip install safetensors`")
+            raise
+        save = lambda obj, path: save_file({k: v.contiguous() for k, v in obj.items()}, path, metadata={"format": "pt"})  # noqa: E731
+    if str(output_dir).endswith((".bin", ".pt", ".pth", ".safetensors")):
+        print(f"Saving fp32 state dict to {output_dir}")
+        save(sd, output_dir)
+        return sd
+    os.makedirs(output_dir, exist_ok=True)
+    base = "model.safetensors" if safe_serialization else "pytorch_model.bin"
+    if safe_serialization:                       # safetensors refuses aliased tensors: materialise ties
+        seen_ptr = set()
+        for k in list(sd):
+            ptr = sd[k].untyped_storage().data_ptr()
+            if ptr in seen_ptr:
+                sd[k] = sd[k].clone()
+            seen_ptr.add(sd[k].untyped_storage().data_ptr())
+    shards = _shard_state_dict(sd, _parse_size(max_shard_size))
+    if len(shards) == 1:
+        print(f"Saving fp32 state dict to {os.path.join(output_dir, base)}")
+        save(shards[0], os.path.join(output_dir, base))
+        return sd
+    stem, ext = base.rsplit(".", 1)
+    weight_map, total = OrderedDict(), 0
+    for i, shard in enumerate(shards):
+        fname = f"{stem}-{i + 1:05d}-of-{len(shards):05d}.{ext}"
+        save(shard, os.path.join(output_dir, fname))
+        for k, v in shard.items():
+            weight_map[k] = fname
+            total += v.numel() * v.element_size()
+    index = {"metadata": {"total_size": total}, "weight_map": weight_map}
+    with open(os.path.join(output_dir, base + ".index.json"), "w", encoding="utf-8") as f:
+        f.write(json.dumps(index, indent=2, sort_keys=True) + "\n")
+    print(f"Saved {len(shards)} shards and {base}.index.json to {output_dir}")
     return sd
 
 
@@ -102,9 +174,16 @@ def load_state_dict_from_zero_checkpoint(model, checkpoint_dir, tag=None):
 if __name__ == "__main__":
     parser = argparse.ArgumentParser()
     parser.add_argument("checkpoint_dir", type=str, help="path to the checkpoint folder (the one holding `latest`)")
-    parser.add_argument("output_file", type=str, help="path to the pytorch fp32 state_dict output file")
+    parser.add_argument("output_dir", type=str,
+                        help="directory for the fp32 state_dict files (or a single .bin/.pt/.safetensors file)")
+    parser.add_argument("--max_shard_size", type=str, default="5GB",
+                        help="maximum size of one output file, e.g. 5GB; larger checkpoints are split and indexed")
+    parser.add_argument("--safe_serialization", default=False, action="store_true",
+                        help="write safetensors instead of pickled torch files")
     parser.add_argument("-t", "--tag", type=str, default=None, help="checkpoint tag, e.g. global_step14")
-    parser.add_argument("--exclude_frozen_parameters", action="store_true")
+    parser.add_argument("--exclude_frozen_parameters", action="store_true", help="exclude frozen parameters")
+    parser.add_argument("-d", "--debug", action="store_true", help="enable debug")
     a = parser.parse_args()
-    convert_zero_checkpoint_to_fp32_state_dict(a.checkpoint_dir, a.output_file, tag=a.tag,
+    convert_zero_checkpoint_to_fp32_state_dict(a.checkpoint_dir, a.output_dir, max_shard_size=a.max_shard_size,
+                                               safe_serialization=a.safe_serialization, tag=a.tag,
                                                exclude_frozen_parameters=a.exclude_frozen_parameters)

@@ -58,6 +58,32 @@ def _save_load_worker(rank, world, stage, tmp):
         sd = get_fp32_state_dict_from_zero_checkpoint(tmp)
         e3 = _make(stage, world) if False else None
         assert set(sd.keys()) >= {n for n, _ in e1.module.named_parameters()}
+        # sharded + indexed output (HuggingFace layout), single-file output, safetensors
+        import json
+        from shuffle_exchange_b200.utils.zero_to_fp32 import _parse_size, convert_zero_checkpoint_to_fp32_state_dict
+        assert _parse_size("5GB") == 5 * 1000 ** 3 and _parse_size("2MiB") == 2 * 1024 ** 2 and _parse_size(7) == 7
+        biggest = max(v.numel() * v.element_size() for v in sd.values())
+        out = os.path.join(tmp, "fp32_sharded")
+        convert_zero_checkpoint_to_fp32_state_dict(tmp, out, max_shard_size=biggest)
+        index = json.load(open(os.path.join(out, "pytorch_model.bin.index.json")))
+        assert set(index["weight_map"]) == set(sd) and len(set(index["weight_map"].values())) > 1
+        merged = {}
+        for f in set(index["weight_map"].values()):
+            merged.update(torch.load(os.path.join(out, f), weights_only=True))
+        assert all(torch.equal(merged[k], sd[k]) for k in sd)
+        one = os.path.join(tmp, "fp32_one")
+        convert_zero_checkpoint_to_fp32_state_dict(tmp, one)
+        assert os.path.exists(os.path.join(one, "pytorch_model.bin"))
+        single = os.path.join(tmp, "all.pt")
+        convert_zero_checkpoint_to_fp32_state_dict(tmp, single)
+        assert set(torch.load(single, weights_only=True)) == set(sd)
+        try:
+            import safetensors.torch as st
+            convert_zero_checkpoint_to_fp32_state_dict(tmp, os.path.join(tmp, "fp32_st"), safe_serialization=True)
+            loaded = st.load_file(os.path.join(tmp, "fp32_st", "model.safetensors"))
+            assert all(torch.equal(loaded[k], sd[k]) for k in sd)
+        except ImportError:
+            pass
 
 
 @pytest.mark.parametrize("stage", [1, 2, 3])
