@@ -64,3 +64,42 @@ def get_compression_config(param_dict):
     out = {name: _technique(sub, name) for name in TECHNIQUES}
     out[LAYER_REDUCTION] = get_layer_reduction(sub)
     return out
+
+
+# ---- per-technique getters under the reference's names (``compression/config.py:60-450``); each takes the
+# ``compression_training`` sub-dictionary and returns the section with defaults filled, as ``_technique`` does
+def get_layer_reduction_enabled(param_dict):
+    return param_dict.get(LAYER_REDUCTION, {}).get(LAYER_REDUCTION_ENABLED, LAYER_REDUCTION_ENABLED_DEFAULT) \
+        if LAYER_REDUCTION in param_dict else False
+
+
+def get_layer_reduction_params(param_dict):
+    if LAYER_REDUCTION not in param_dict:
+        return False
+    params = dict(param_dict[LAYER_REDUCTION])
+    params.pop(LAYER_REDUCTION_ENABLED, None)
+    return params
+
+
+def get_quantize_enabled(param_dict):
+    return bool(param_dict.get(COMPRESSION_TRAINING, {}).get(WEIGHT_QUANTIZATION, {}).get(SHARED_PARAMETERS, {})
+                .get(TECHNIQUE_ENABLED, False))
+
+
+def _make_getters(name):
+    def whole(param_dict): return _technique(param_dict, name)
+    def shared(param_dict): return _technique(param_dict, name)[SHARED_PARAMETERS]
+    def groups(param_dict): return _technique(param_dict, name)[DIFFERENT_GROUPS]
+    return whole, shared, groups
+
+
+(get_weight_quantization, get_weight_quantization_shared_parameters,
+ get_weight_quantization_different_groups) = _make_getters(WEIGHT_QUANTIZATION)
+(get_activation_quantization, get_activation_quantization_shared_parameters,
+ get_activation_quantization_different_groups) = _make_getters(ACTIVATION_QUANTIZATION)
+(get_sparse_pruning, get_sparse_pruning_shared_parameters,
+ get_sparse_pruning_different_groups) = _make_getters(SPARSE_PRUNING)
+(get_row_pruning, get_row_pruning_shared_parameters, get_row_pruning_different_groups) = _make_getters(ROW_PRUNING)
+(get_head_pruning, get_head_pruning_shared_parameters, get_head_pruning_different_groups) = _make_getters(HEAD_PRUNING)
+(get_channel_pruning, get_channel_pruning_shared_parameters,
+ get_channel_pruning_different_groups) = _make_getters(CHANNEL_PRUNING)
