@@ -2,6 +2,8 @@
 from __future__ import annotations
 
 import torch
+
+from ..utils.logging import logger
 from torch import nn
 
 from .basic_layer import BNLayer_Compress, Conv2dLayer_Compress, Embedding_Compress, LinearLayer_Compress
@@ -115,3 +117,52 @@ def convert_conv1d_to_linear(model, convert_type):
                 lin.bias.data = m.bias.data
             recursive_setattr(model, name, lin)
     return model
+
+
+# ---- snip_momentum sparse pruning through Intel neural-compressor (reference ``compression/helper.py:274-322``)
+def generate_pruners(config, model):
+    """Create neural-compressor pruners for ``model`` from its pruning config list.  neural-compressor is optional: it
+    is only needed for the ``snip_momentum`` method, every other pruning method is built in."""
+    try:
+        from neural_compressor.compression.pruner import utils as nc_utils
+        from neural_compressor.compression.pruner.pruners import get_pruner
+    except ImportError as e:
+        raise ImportError("snip_momentum pruning needs neural-compressor >= 2.1.1 (`pip install neural-compressor`)") from e
+    assert isinstance(model, torch.nn.Module)
+    pruners_info = nc_utils.process_config(config)
+    pruners = []
+    for info in pruners_info:
+        modules = nc_utils.parse_to_prune(info, model)
+        if not modules:
+            logger.warning("one pruner hooks no layers, please have a check")
+        pruners.append(get_pruner(info, modules))
+        info["modules"] = list(modules.keys())
+        info["len_of_modules"] = len(info["modules"])
+        logger.info(info)
+    return pruners
+
+
+def register_on_step_begin(model):
+    """Run every pruner's ``on_step_begin`` right before each forward (global step counter kept by the pruner)."""
+    def hook(module, input):
+        for pruner in getattr(module, "pruners", ()):
+            pruner.on_step_begin(0)
+    return model.register_forward_pre_hook(hook)
+
+
+def rewrite_optimizer_step(opt):
+    """Bracket ``opt.step`` with the pruners' ``on_before_optimizer_step`` / ``on_after_optimizer_step`` (the mask is
+    re-applied after the update so pruned weights stay zero)."""
+    import types
+
+    def new_step(self, closure=None):
+        for pruner in getattr(self, "pruners", ()):
+            pruner.on_before_optimizer_step()
+        res = self.orig_step(closure) if closure is not None else self.orig_step()
+        for pruner in getattr(self, "pruners", ()):
+            pruner.on_after_optimizer_step()
+        return res
+
+    opt.orig_step = opt.step
+    opt.step = types.MethodType(new_step, opt)
+    return opt

@@ -116,3 +116,27 @@ def cli_main():
 
 if __name__ == "__main__":
     cli_main()
+
+
+def ninja_installed() -> bool:
+    try:
+        import ninja  # noqa: F401
+        return True
+    except ImportError:
+        return False
+
+
+def human_readable_size(size) -> str:
+    """``1536 -> '1.50 KB'`` (powers of 1024)."""
+    units = ["B", "KB", "MB", "GB", "TB", "PB"]
+    size = float(size)
+    i = 0
+    while size >= 1024 and i < len(units) - 1:
+        size /= 1024
+        i += 1
+    return f"{size:.2f} {units[i]}"
+
+
+def installed_cann_path():
+    """Ascend toolkit location — never present on this platform."""
+    return None

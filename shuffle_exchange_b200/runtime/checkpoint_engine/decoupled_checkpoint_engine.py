@@ -82,3 +82,52 @@ class DecoupledCheckpointEngine(FastCheckpointEngine):
         self._wait_durable()
         self._q.put(None)
         self._thread.join(timeout=60)
+
+
+# ---- reference vocabulary (``decoupled_checkpoint_engine.py:22-80``): the reference runs the writer in a separate
+# PROCESS and talks to it with these events; here the writer is a thread of the training process (the snapshot is taken
+# into pinned host memory first, so the training loop is decoupled from disk either way) and the names are kept for
+# callers that refer to them.
+from enum import Enum as _Enum
+
+
+class DecoupledEvent(_Enum):
+    SAVE_EVENT = 1
+    COMMIT_EVENT = 2
+    EXIT_EVENT = 3
+
+
+class CheckpointSize:
+    """Running totals of what a checkpoint wrote (before / after serialisation, and on disk)."""
+
+    def __init__(self):
+        self._pre = self._post = self._gigabytes = 0
+
+    def pre_size(self): return self._pre
+    def post_size(self): return self._post
+    def gb_size(self): return self._gigabytes
+
+    def set_pre_size(self, size): self._pre = size
+    def set_post_size(self, size): self._post = size
+    def set_gb_size(self):
+        self._gigabytes = (self._post - self._pre) / (1024 ** 3)
+
+
+def init_decoupled_checkpoint(config_params, dp_writer_config=None, save_event=None, save_queue=None,
+                              optimize_dp_state=True):
+    """Entry point of the reference's writer process.  With a thread-based writer it builds the engine (which starts
+    its writer thread) and, when a queue is supplied, serves ``(state, path)`` items from it until ``None`` arrives."""
+    engine = DecoupledCheckpointEngine(config_params, dp_writer_config, optimize_dp_state)
+    if save_queue is None:
+        return engine
+    while True:
+        item = save_queue.get()
+        if item is None or item == DecoupledEvent.EXIT_EVENT:
+            break
+        if item == DecoupledEvent.COMMIT_EVENT:
+            engine.commit(getattr(engine, "_pending_tag", None))
+            continue
+        state, path = item
+        engine.save(state, path)
+    engine.cleanup() if hasattr(engine, "cleanup") else None
+    return engine
