@@ -1,31 +1,39 @@
-"""Availability checks for the optional monitor back ends (reference: ``monitor/utils.py``): each raises an
-``ImportError`` with the install hint when the package is missing."""
+"""Is an optional monitor back end importable?  (reference: ``monitor/utils.py``.)  Each check re-raises the
+``ImportError`` after printing what to install, so enabling a monitor in the config without its package fails at
+start-up rather than at the first write."""
+import importlib
+
+_HINTS = {
+    "tensorboard": "If you want to use tensorboard logging, please `pip install tensorboard`",
+    "wandb": "If you want to use wandb logging, please `pip install wandb` and follow the instructions at "
+             "https://docs.wandb.ai/quickstart",
+    "comet_ml": 'If you want to use comet logging, please `pip install "comet_ml>=3.41.0"`',
+}
+_COMET_MIN = (3, 41)
+
+
+def _require(package: str, also=()):
+    try:
+        mod = importlib.import_module(package)
+        for extra in also:
+            importlib.import_module(extra)
+        return mod
+    except ImportError:
+        print(_HINTS[package])
+        raise
 
 
 def check_tb_availability():
-    try:
-        import tensorboard  # noqa: F401
-        from torch.utils.tensorboard import SummaryWriter  # noqa: F401
-    except ImportError:
-        print('If you want to use tensorboard logging, please `pip install tensorboard`')
-        raise
+    _require("tensorboard", also=("torch.utils.tensorboard",))
 
 
 def check_wandb_availability():
-    try:
-        import wandb  # noqa: F401
-    except ImportError:
-        print('If you want to use wandb logging, please `pip install wandb` and follow the instructions at '
-              'https://docs.wandb.ai/quickstart')
-        raise
+    _require("wandb")
 
 
 def check_comet_availability():
-    try:
-        import comet_ml
-        version = tuple(int(x) for x in comet_ml.__version__.split(".")[:2])
-        if version < (3, 41):
-            raise ImportError("`comet_ml` must have at least version 3.41.0")
-    except ImportError:
-        print('If you want to use comet logging, please `pip install "comet_ml>=3.41.0"`')
-        raise
+    comet = _require("comet_ml")
+    found = tuple(int(x) for x in comet.__version__.split(".")[:2])
+    if found < _COMET_MIN:
+        print(_HINTS["comet_ml"])
+        raise ImportError(f"`comet_ml` must have at least version {_COMET_MIN[0]}.{_COMET_MIN[1]}.0 (found {comet.__version__})")
