@@ -38,3 +38,43 @@ class BF16_Optimizer(DeepSpeedZeroOptimizer):
 
     def get_grads_for_reduction(self):
         return [g.flat_grad for g in self.groups if g.flat_grad is not None], {}
+
+    # ---- reference-named gradient plumbing (``bf16_optimizer.py:330-470``)
+    def create_grad_acc_hooks(self):
+        """Gradient hand-off hooks are installed when the flat groups are built (main-grad views the wgrad kernels
+        write into, plus post-accumulate hooks for everything else); nothing to add afterwards."""
+        return None
+
+    def accumulate_hp_grads_and_remove_lp(self, lp_param, group_idx, param_idx):
+        """Fold ``lp_param.grad`` into the group's high-precision accumulator and drop the low-precision gradient."""
+        g = self.groups[group_idx]
+        if lp_param.grad is not None:
+            g.ensure_flat_grad()
+            view = g.grad_view(param_idx)
+            view.add_(lp_param.grad.reshape(view.shape).to(view.dtype))
+            lp_param.grad = None
+
+    def clear_hp_grads(self):
+        for g in self.groups:
+            if g.flat_grad is not None:
+                g.flat_grad.zero_()
+            if g.grad_shard is not None and (g.flat_grad is None or g.grad_shard.data_ptr() != g.flat_grad.data_ptr()):
+                g.grad_shard.zero_()
+
+    def get_grads_for_norm(self, for_clipping=False):
+        """Gradient tensors that enter the global norm on this rank.  ``for_clipping``: also return them grouped by
+        flat group (the reference returns ``(non_expert_grads, expert_grads)``; experts here are separate groups whose
+        norm is reduced over their own process group by ``compute_grad_norm_and_overflow``)."""
+        grads = [g.grad_shard if g.grad_shard is not None else g.flat_grad for g in self.groups]
+        grads = [t for t in grads if t is not None]
+        if not for_clipping:
+            return grads
+        experts = {}
+        for g in self.groups:
+            name = (g.param_group or {}).get("name") if getattr(g, "param_group", None) else None
+            if name and (g.param_group or {}).get("moe", False):
+                t = g.grad_shard if g.grad_shard is not None else g.flat_grad
+                if t is not None:
+                    experts.setdefault(name, []).append(t)
+        flat_experts = {id(t) for ts in experts.values() for t in ts}
+        return [t for t in grads if id(t) not in flat_experts], experts

@@ -158,3 +158,31 @@ def _optimizer_surface(rank, world, stage):
 @pytest.mark.parametrize("stage", [2, 3])
 def test_optimizer_object_surface(stage):
     run_dist(_optimizer_surface, world=2, args=(stage,))
+
+
+def _bf16_optimizer_methods(rank, world):
+    import shuffle_exchange_b200 as sxb
+    from shuffle_exchange_b200.runtime.bf16_optimizer import BF16_Optimizer
+    torch.manual_seed(0)
+    model = torch.nn.Linear(8, 8).to(torch.bfloat16)
+    engine, opt, *_ = sxb.initialize(model=model, model_parameters=model.parameters(), config={
+        "train_micro_batch_size_per_gpu": 2, "steps_per_print": 1 << 30, "bf16": {"enabled": True},
+        "optimizer": {"type": "Adam", "params": {"lr": 1e-2}}})
+    assert isinstance(opt, BF16_Optimizer), type(opt)
+    loss = engine(torch.randn(2, 8, dtype=torch.bfloat16)).float().pow(2).mean()
+    engine.backward(loss)
+    gs = opt.get_grads_for_norm()
+    assert len(gs) >= 1 and all(torch.is_tensor(t) for t in gs)
+    non_expert, expert = opt.get_grads_for_norm(for_clipping=True)
+    assert expert == {} and len(non_expert) == len(gs)
+    engine.step()
+    p = next(model.parameters())
+    p.grad = torch.ones_like(p)
+    opt.accumulate_hp_grads_and_remove_lp(p, 0, 0)
+    assert p.grad is None and float(opt.groups[0].grad_view(0).sum()) == p.numel()
+    opt.clear_hp_grads()
+    assert float(opt.groups[0].flat_grad.abs().sum()) == 0.0 and opt.create_grad_acc_hooks() is None
+
+
+def test_bf16_optimizer_reference_named_methods():
+    run_dist(_bf16_optimizer_methods, world=2)
