@@ -95,6 +95,92 @@ class DeepSpeedHybridEngine(DeepSpeedEngine):
                 self.mp_group = g
         DeepSpeedHybridEngine.inference_mp_group = self.mp_group
 
+    # ------------------------------------------------------------------------------- inference containers
+    # Optional fused-layer path (reference ``hybrid_engine.py:78-176``): every layer an injection policy recognises gets
+    # a hybrid container whose fused inference layer is refreshed from the training weights before generation.
+    # ``generate`` uses the training module directly unless ``create_inference_module`` was called.
+    def populate_all_inference_policies(self):
+        from ..module_inject.replace_policy import generic_policies, replace_policies
+        self.inference_policies = {}
+        for pol in replace_policies:
+            name = getattr(pol, "_orig_layer_class_name", None)
+            if name:
+                self.inference_policies[name] = pol
+        self.inference_policies.update({nn_cls: self._replace_linear_layer for nn_cls in (torch.nn.Linear,)})
+        self._generic_policies = list(generic_policies)
+        return self.inference_policies
+
+    def _replace_linear_layer(self, child, name=None):
+        return child
+
+    def new_inference_container(self, orig_layer, policy_cls, layer_id):
+        from ..inference.config import DeepSpeedInferenceConfig
+        from ..module_inject.containers import POLICY_TO_CONTAINER
+        from ..module_inject.containers.features import HybridEngineContainer
+        base = POLICY_TO_CONTAINER[policy_cls]
+        hybrid_cls = type("Hybrid" + base.__name__, (HybridEngineContainer, base), {})
+        dtype = torch.bfloat16 if self.bfloat16_enabled() else (torch.float16 if self.fp16_enabled() else torch.float32)
+        icfg = DeepSpeedInferenceConfig(dtype=dtype, tensor_parallel={"tp_size": self._inference_tp},
+                                        max_out_tokens=self._config.hybrid_engine.max_out_tokens)
+        if self.mp_group is not None:
+            icfg.tensor_parallel.tp_group = self.mp_group
+        container = hybrid_cls(policy_cls(orig_layer, inference=True), icfg, getattr(self.module, "config", None),
+                               layer_id, orig_layer)
+        container.create_ds_model_config()
+        container.initialize_tensors()
+        container.apply_tensor_parallelism()
+        container.create_module()
+        return container
+
+    def create_inference_containers(self, module, layer_id=0):
+        if not hasattr(self, "inference_policies"):
+            self.populate_all_inference_policies()
+            self._inference_containers, self._orig_layers = [], []
+        for name, child in module.named_children():
+            pol = self.inference_policies.get(type(child).__name__)
+            if isinstance(pol, type) and pol.match(child):
+                c = self.new_inference_container(child, pol, layer_id)
+                self._inference_containers.append(c)
+                self._orig_layers.append((module, name, child))
+                layer_id += 1
+            else:
+                layer_id = self.create_inference_containers(child, layer_id)
+        return layer_id
+
+    def create_inference_module(self):
+        """Build the containers (once).  ``refresh_inference_module`` re-reads the training weights; swapping the fused
+        layers into the module tree for a generation phase is ``use_inference_layers(True)``."""
+        self._inference_containers, self._orig_layers = [], []
+        self.populate_all_inference_policies()
+        self.create_inference_containers(self.module)
+        return len(self._inference_containers)
+
+    def refresh_inference_module(self):
+        for c in getattr(self, "_inference_containers", ()):
+            c.refresh()
+
+    def use_inference_layers(self, enable: bool):
+        from ..module_inject.containers import HFLayerAdapter
+        for c, (parent, name, orig) in zip(getattr(self, "_inference_containers", ()), getattr(self, "_orig_layers", ())):
+            if enable:
+                setattr(parent, name, HFLayerAdapter(c.module, returns_tuple=type(c.policy).returns_tuple))
+            else:
+                setattr(parent, name, orig)
+
+    def convert_to_linear_transposed(self, model):
+        """Replace ``nn.Linear`` layers by ``TLinear`` (weight stored transposed: a ZeRO-3 gathered weight feeds
+        ``matmul`` without a transpose copy)."""
+        from .utils import TLinear
+
+        def walk(m):
+            for name, child in list(m.named_children()):
+                if isinstance(child, torch.nn.Linear) and not isinstance(child, TLinear):
+                    setattr(m, name, TLinear(child, name=name))
+                else:
+                    walk(child)
+        walk(model)
+        return model
+
     # ------------------------------------------------------------------------------------------ LoRA
     def fuse_lora_weight(self):
         if self.is_lora_fused:

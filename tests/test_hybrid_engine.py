@@ -95,3 +95,47 @@ def _worker(rank, world, stage):
 @pytest.mark.parametrize("stage", [1, 3])
 def test_hybrid_engine_generate_train_cycle(stage):
     run_dist(_worker, world=2, args=(stage,))
+
+
+def _hybrid_containers(rank, world):
+    transformers = pytest.importorskip("transformers")
+    from transformers import AutoConfig, AutoModelForCausalLM
+    import shuffle_exchange_b200 as ds
+    torch.manual_seed(0)
+    model = AutoModelForCausalLM.from_config(AutoConfig.for_model(
+        model_type="gpt2", vocab_size=64, n_embd=32, n_layer=2, n_head=4, n_positions=32)).float()
+    cfg = {"train_micro_batch_size_per_gpu": 2, "steps_per_print": 1 << 30,
+           "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}}, "zero_optimization": {"stage": 1},
+           "hybrid_engine": {"enabled": True}}
+    engine, *_ = ds.initialize(model=model, config=cfg, model_parameters=model.parameters())
+    assert engine.create_inference_module() == 2
+    ids = torch.randint(0, 64, (2, 6), generator=torch.Generator().manual_seed(3))
+    engine.eval()
+    with torch.no_grad():
+        ref = engine.module(ids, use_cache=False).logits.clone()
+        engine.use_inference_layers(True)
+        fused = engine.module(ids, use_cache=False).logits.clone()
+        engine.use_inference_layers(False)
+    assert (fused - ref).abs().max() < 2e-3
+    # one training step changes the weights; a refresh carries them into the fused layers
+    engine.train()
+    out = engine(ids, labels=ids)
+    engine.backward(out.loss)
+    engine.step()
+    engine.eval()
+    engine.refresh_inference_module()
+    with torch.no_grad():
+        ref2 = engine.module(ids, use_cache=False).logits.clone()
+        engine.use_inference_layers(True)
+        fused2 = engine.module(ids, use_cache=False).logits.clone()
+        engine.use_inference_layers(False)
+    assert (ref2 - ref).abs().max() > 1e-4 and (fused2 - ref2).abs().max() < 2e-3
+    lin = torch.nn.Sequential(torch.nn.Linear(4, 3))
+    x = torch.randn(2, 4)
+    y = lin(x)
+    engine.convert_to_linear_transposed(lin)
+    assert type(lin[0]).__name__ == "TLinear" and torch.allclose(lin(x), y, atol=1e-6)
+
+
+def test_hybrid_engine_inference_containers_follow_training():
+    run_dist(_hybrid_containers, 2)
