@@ -25,9 +25,9 @@ LLAMA3_8B = dict(vocab_size=128256, hidden_size=4096, intermediate_size=14336, n
 
 
 def run(args, ClockSampler, ds_config_fn):
-    if not os.path.isdir(os.path.join(REF, "deepspeed")):
-        from baseline import make_ref
-        make_ref.main()
+    from baseline import make_ref
+    if not make_ref.is_staged():
+        make_ref.main()          # raises with the staging instructions when /root/reference is not mounted
     sys.path.insert(0, REF)
     import torch
     rank = int(os.environ.get("RANK", "0"))

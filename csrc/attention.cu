@@ -1037,17 +1037,15 @@ static int launch_cluster2(K kernel, dim3 grid, int threads, int smem_bytes, cud
 // SXB_ATTN_MC=0 forces the single-CTA kernels (A/B measurements).
 // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
 // GPU's memory hung the GPU: K/V that are not plain allocations of the current device take the single-CTA kernels.
-static bool owned_by_current_device(const void* p) {
-  cudaPointerAttributes a{};
-  int dev = -1;
-  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
-  if (cudaGetDevice(&dev) != cudaSuccess) return false;
-  return a.type == cudaMemoryTypeDevice && a.device == dev;
-}
-static bool use_multicast(int Hq, int Hk, int D, const void* k, const void* v) {
+// The test itself (runtime attributes + driver allocation range + foreign-range registry) is range_is_local().
+static bool use_multicast(int Hq, int Hk, int D, const void* k, long long k_bytes, const void* v, long long v_bytes) {
   static const int env = [] { const char* e = getenv("SXB_ATTN_MC"); return e ? atoi(e) : 1; }();
   return env != 0 && D == 128 && Hk > 0 && ((Hq / Hk) % 2 == 0) && (Hq % 2 == 0) &&
-         owned_by_current_device(k) && owned_by_current_device(v);
+         range_is_local(k, k_bytes) && range_is_local(v, v_bytes);
+}
+// bytes spanned by a [B, S, H, D] bf16 tensor with row pitch `stride` elements
+static long long span_bytes(int B, int S, int H, int D, long long stride) {
+  return (((long long)B * S - 1) * stride + (long long)H * D) * 2;
 }
 
 }  // namespace attn
@@ -1057,6 +1055,12 @@ using namespace sxb;
 using namespace sxb::attn;
 
 SXB_DEFINE_HANG_ACCESSOR(sxb_attn_hang_info)
+
+// Which kernel family sxb_attn_fwd / the dQ pass would pick for these K/V: 1 = 2-CTA multicast, 0 = single CTA.
+SXB_API int sxb_attn_would_multicast(const void* k, const void* v, int B, int S, int Hq, int Hk, int D,
+                                     long long k_stride, long long v_stride) {
+  return use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride)) ? 1 : 0;
+}
 
 static bool attn_args_ok(int B, int S, int Hq, int Hk, int D, long long qs, long long ks,
                          long long vs) {
@@ -1084,7 +1088,7 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
   p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
   dim3 grid(Hq, B, (S + BQ - 1) / BQ);
   cudaStream_t s = (cudaStream_t)stream;
-  if (use_multicast(Hq, Hk, D, k, v)) {
+  if (use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride))) {
     if ((rc = set_smem(attn_fwd_kernel<128, 2>, FwdSmem<128>::kTotal))) return rc;
     if ((rc = launch_cluster2(attn_fwd_kernel<128, 2>, grid, kThreads, FwdSmem<128>::kTotal, s, tq, tk, tv, p)))
       return rc;
@@ -1136,7 +1140,7 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BC))) return rc;
     p.out = dq; p.out_stride = dq_stride;
     dim3 grid(Hq, B, (S + BQ - 1) / BQ);
-    if (use_multicast(Hq, Hk, D, k, v)) {
+    if (use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride))) {
       if ((rc = set_smem(attn_bwd_dq_kernel<128, 2>, DqSmem<128>::kTotal))) return rc;
       if ((rc = launch_cluster2(attn_bwd_dq_kernel<128, 2>, grid, kBwdThreads, DqSmem<128>::kTotal, s, tq, tk, tv,
                                 tdo, p)))

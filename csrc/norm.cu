@@ -329,7 +329,11 @@ SXB_API int sxb_layernorm_bwd(const void* dy, const void* x, const void* w, cons
 // and must be serialised by the caller.
 // Set-up: the first call on each device resolves the array's device address with
 // cudaGetSymbolAddress while that device is current and caches it; make that first call before any
-// stream capture begins.  Later calls do no runtime queries at all.
+// stream capture begins AND before the process commits the rest of the device's memory: with CUDA's
+// lazy module loading (the default) the array only receives its 9.3 MiB of backing store when this
+// file's module is first loaded on that device — by that first call or by any other norm kernel — so a
+// first call made after memory has run out can itself fail with an out-of-memory error.  Later calls
+// only ask which device is current (cudaGetDevice) and launch.
 constexpr int SXB_NOALLOC_NORM_MAX_H = 8192;
 constexpr int kNoAllocMaxGrid = 148 * 2;
 constexpr long long kNoAllocScratchElems = (long long)kNoAllocMaxGrid * SXB_NOALLOC_NORM_MAX_H;

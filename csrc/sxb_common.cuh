@@ -475,6 +475,9 @@ __device__ __forceinline__ float fast_exp2(float x) {
 }
 // Host helper (defined in tensormap.cu): encode a rank-N tiled tensor map with 128B swizzle.
 // dims/strides/box are innermost-first; strides (bytes) has rank-1 entries.
+// true only for ordinary allocations of the current device, whole extent inside one allocation, not registered as
+// foreign (tensormap.cu) — the precondition for covering a range with a TMA multicast tensor map
+bool range_is_local(const void* p, long long bytes);
 int encode_tensor_map(CUtensorMap* m, int dtype_code, int rank, const void* ptr,
                       const unsigned long long* dims, const unsigned long long* strides_bytes,
                       const unsigned int* box, int swizzle_bytes);

@@ -100,10 +100,27 @@ struct AdamArgs {
 // ------------------------------------------------------------------------------------ K1
 // Each rank reduces ITS shard [rank*part, (rank+1)*part) of every peer's flat bf16 gradient buffer and
 // immediately applies AdamW.  channel 0 = "gradients ready", channel 1 = "finished reading".
-__global__ void __launch_bounds__(kThreads)
-rs_adam_kernel(Peers P, long long part, float* __restrict__ hp, float* __restrict__ m, float* __restrict__ v,
-               __nv_bfloat16* __restrict__ lp, __nv_bfloat16* __restrict__ grad_out, AdamArgs a, uint32_t epoch,
-               const void* mc_ptr, unsigned int* __restrict__ cta_counter, int apply_adam, int do_sync) {
+struct RsAdamArgs {
+  Peers P;
+  long long part;
+  float *hp, *m, *v;
+  __nv_bfloat16 *lp, *grad_out;
+  AdamArgs a;
+  uint32_t epoch;
+  const void* mc_ptr;
+  unsigned int* cta_counter;
+  int apply_adam, do_sync;
+};
+__device__ __forceinline__ void rs_adam_body(const RsAdamArgs& A) {
+  const Peers& P = A.P;
+  const long long part = A.part;
+  float* __restrict__ hp = A.hp; float* __restrict__ m = A.m; float* __restrict__ v = A.v;
+  __nv_bfloat16* __restrict__ lp = A.lp; __nv_bfloat16* __restrict__ grad_out = A.grad_out;
+  const AdamArgs a = A.a;
+  const uint32_t epoch = A.epoch;
+  const void* mc_ptr = A.mc_ptr;
+  unsigned int* __restrict__ cta_counter = A.cta_counter;
+  const int apply_adam = A.apply_adam, do_sync = A.do_sync;
   // do_sync == 0: the "gradients ready" handshake already ran as a one-warp kernel in front of this one on the same
   // stream, so no CTA of this (SM-filling) grid ever spins while it holds an SM next to the backward GEMMs.
   if (do_sync) {
@@ -113,63 +130,86 @@ rs_adam_kernel(Peers P, long long part, float* __restrict__ hp, float* __restric
   const long long base = (long long)P.rank * part;
   const long long nvec = part >> 3;
   const float inv_n = 1.0f / (float)P.world;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
-       i += (long long)gridDim.x * blockDim.x) {
-    float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  constexpr int U = 2;     // independent 16-byte reduce loads in flight per thread (NVLink round trip ~4 us)
+  const long long tstride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += U * tstride) {
+    float g[U][8];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[u][k] = 0.f;
     if (mc_ptr) {
       // NVLS: one load returns the in-switch sum over all ranks (fp32 accumulation inside the switch)
-      uint4 r;
-      const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(mc_ptr) + base + i * 8;
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
-                   : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                   : "l"(src)
-                   : "memory");
-      bf16x8_acc(r, g);
-    } else {
-      uint4 r[kMaxPeers];
+      uint4 r[U];
 #pragma unroll
-      for (int pi = 0; pi < kMaxPeers; ++pi) {
-        if (pi < P.world) {
-          const int peer = (P.rank + pi) % P.world;       // stagger so ranks do not hammer one peer
-          r[pi] = ld_peer16(reinterpret_cast<const __nv_bfloat16*>(P.buf[peer]) + base + i * 8);
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * tstride;
+        if (i < nvec) {
+          const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(mc_ptr) + base + i * 8;
+          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(r[u].x), "=r"(r[u].y), "=r"(r[u].z), "=r"(r[u].w)
+                       : "l"(src)
+                       : "memory");
         }
       }
 #pragma unroll
-      for (int pi = 0; pi < kMaxPeers; ++pi)
-        if (pi < P.world) bf16x8_acc(r[pi], g);
-    }
-    if (apply_adam) {
-      float4 p0 = *reinterpret_cast<float4*>(hp + i * 8), p1 = *reinterpret_cast<float4*>(hp + i * 8 + 4);
-      float4 m0 = *reinterpret_cast<float4*>(m + i * 8), m1 = *reinterpret_cast<float4*>(m + i * 8 + 4);
-      float4 v0 = *reinterpret_cast<float4*>(v + i * 8), v1 = *reinterpret_cast<float4*>(v + i * 8 + 4);
-      float pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
-      float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-      float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        float gg = g[k] * inv_n * a.grad_scale;
-        if (!a.adamw) gg += a.weight_decay * pp[k];
-        mm[k] = a.beta1 * mm[k] + (1.f - a.beta1) * gg;
-        vv[k] = a.beta2 * vv[k] + (1.f - a.beta2) * gg * gg;
-        float upd = (mm[k] / a.bc1) / (sqrtf(vv[k] / a.bc2) + a.eps);
-        if (a.adamw) upd += a.weight_decay * pp[k];
-        pp[k] -= a.lr * upd;
-      }
-      *reinterpret_cast<float4*>(hp + i * 8) = make_float4(pp[0], pp[1], pp[2], pp[3]);
-      *reinterpret_cast<float4*>(hp + i * 8 + 4) = make_float4(pp[4], pp[5], pp[6], pp[7]);
-      *reinterpret_cast<float4*>(m + i * 8) = make_float4(mm[0], mm[1], mm[2], mm[3]);
-      *reinterpret_cast<float4*>(m + i * 8 + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
-      *reinterpret_cast<float4*>(v + i * 8) = make_float4(vv[0], vv[1], vv[2], vv[3]);
-      *reinterpret_cast<float4*>(v + i * 8 + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
-      uint4 o;
-      o.x = pack_bf16(pp[0], pp[1]); o.y = pack_bf16(pp[2], pp[3]);
-      o.z = pack_bf16(pp[4], pp[5]); o.w = pack_bf16(pp[6], pp[7]);
-      *reinterpret_cast<uint4*>(lp + i * 8) = o;
+      for (int u = 0; u < U; ++u)
+        if (i0 + u * tstride < nvec) bf16x8_acc(r[u], g[u]);
     } else {
-      uint4 o;
-      o.x = pack_bf16(g[0] * inv_n, g[1] * inv_n); o.y = pack_bf16(g[2] * inv_n, g[3] * inv_n);
-      o.z = pack_bf16(g[4] * inv_n, g[5] * inv_n); o.w = pack_bf16(g[6] * inv_n, g[7] * inv_n);
-      *reinterpret_cast<uint4*>(grad_out + i * 8) = o;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * tstride;
+        if (i >= nvec) continue;
+        uint4 r[kMaxPeers];
+#pragma unroll
+        for (int pi = 0; pi < kMaxPeers; ++pi) {
+          if (pi < P.world) {
+            const int peer = (P.rank + pi) % P.world;       // stagger so ranks do not hammer one peer
+            r[pi] = ld_peer16(reinterpret_cast<const __nv_bfloat16*>(P.buf[peer]) + base + i * 8);
+          }
+        }
+#pragma unroll
+        for (int pi = 0; pi < kMaxPeers; ++pi)
+          if (pi < P.world) bf16x8_acc(r[pi], g[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * tstride;
+      if (i >= nvec) continue;
+      if (apply_adam) {
+        float4 p0 = *reinterpret_cast<float4*>(hp + i * 8), p1 = *reinterpret_cast<float4*>(hp + i * 8 + 4);
+        float4 m0 = *reinterpret_cast<float4*>(m + i * 8), m1 = *reinterpret_cast<float4*>(m + i * 8 + 4);
+        float4 v0 = *reinterpret_cast<float4*>(v + i * 8), v1 = *reinterpret_cast<float4*>(v + i * 8 + 4);
+        float pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+        float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+        float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          float gg = g[u][k] * inv_n * a.grad_scale;
+          if (!a.adamw) gg += a.weight_decay * pp[k];
+          mm[k] = a.beta1 * mm[k] + (1.f - a.beta1) * gg;
+          vv[k] = a.beta2 * vv[k] + (1.f - a.beta2) * gg * gg;
+          float upd = (mm[k] / a.bc1) / (sqrtf(vv[k] / a.bc2) + a.eps);
+          if (a.adamw) upd += a.weight_decay * pp[k];
+          pp[k] -= a.lr * upd;
+        }
+        *reinterpret_cast<float4*>(hp + i * 8) = make_float4(pp[0], pp[1], pp[2], pp[3]);
+        *reinterpret_cast<float4*>(hp + i * 8 + 4) = make_float4(pp[4], pp[5], pp[6], pp[7]);
+        *reinterpret_cast<float4*>(m + i * 8) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+        *reinterpret_cast<float4*>(m + i * 8 + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
+        *reinterpret_cast<float4*>(v + i * 8) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+        *reinterpret_cast<float4*>(v + i * 8 + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
+        uint4 o;
+        o.x = pack_bf16(pp[0], pp[1]); o.y = pack_bf16(pp[2], pp[3]);
+        o.z = pack_bf16(pp[4], pp[5]); o.w = pack_bf16(pp[6], pp[7]);
+        *reinterpret_cast<uint4*>(lp + i * 8) = o;
+      } else {
+        uint4 o;
+        o.x = pack_bf16(g[u][0] * inv_n, g[u][1] * inv_n); o.y = pack_bf16(g[u][2] * inv_n, g[u][3] * inv_n);
+        o.z = pack_bf16(g[u][4] * inv_n, g[u][5] * inv_n); o.w = pack_bf16(g[u][6] * inv_n, g[u][7] * inv_n);
+        *reinterpret_cast<uint4*>(grad_out + i * 8) = o;
+      }
     }
   }
   // last CTA to finish tells the peers that this rank no longer reads their gradient buffers
@@ -185,6 +225,12 @@ rs_adam_kernel(Peers P, long long part, float* __restrict__ hp, float* __restric
     signal_all(P, 1, epoch);
   }
 }
+__global__ void __launch_bounds__(kThreads) rs_adam_kernel(RsAdamArgs A) { rs_adam_body(A); }
+// Single-GPU emulation of `world` ranks as ONE cooperative grid (blockIdx.y = logical rank): the ranks wait on one
+// another, so they must be co-resident by construction — separate launches on one GPU give no such guarantee.
+__global__ void __launch_bounds__(kThreads) rs_adam_emu_kernel(const RsAdamArgs* per_rank) {
+  rs_adam_body(per_rank[blockIdx.y]);
+}
 
 // Wait until every peer finished reading (channel 1) — launched before a symmetric buffer is reused.
 __global__ void wait_channel_kernel(Peers P, int channel, uint32_t epoch) { wait_all(P, channel, epoch, 102); }
@@ -196,9 +242,22 @@ struct Members {
   int count;
 };
 template <typename T>
-__global__ void __launch_bounds__(kThreads)
-subset_mean_kernel(Peers P, Members M, T* __restrict__ out, long long n, uint32_t epoch,
-                   unsigned int* __restrict__ cta_counter) {
+struct SubsetMeanArgs {
+  Peers P;
+  Members M;
+  T* out;
+  long long n;
+  uint32_t epoch;
+  unsigned int* cta_counter;
+};
+template <typename T>
+__device__ __forceinline__ void subset_mean_body(const SubsetMeanArgs<T>& A) {
+  const Peers& P = A.P;
+  const Members& M = A.M;
+  T* __restrict__ out = A.out;
+  const long long n = A.n;
+  const uint32_t epoch = A.epoch;
+  unsigned int* __restrict__ cta_counter = A.cta_counter;
   if (blockIdx.x == 0) signal_all(P, 2, epoch);
   if (!wait_all(P, 2, epoch, 103)) return;
   const long long nvec = n >> 3;
@@ -236,14 +295,33 @@ subset_mean_kernel(Peers P, Members M, T* __restrict__ out, long long n, uint32_
     signal_all(P, 3, epoch);
   }
 }
+template <typename T>
+__global__ void __launch_bounds__(kThreads) subset_mean_kernel(SubsetMeanArgs<T> A) { subset_mean_body<T>(A); }
+template <typename T>
+__global__ void __launch_bounds__(kThreads) subset_mean_emu_kernel(const SubsetMeanArgs<T>* per_rank) {
+  if (per_rank[blockIdx.y].n >= 0) subset_mean_body<T>(per_rank[blockIdx.y]);   // n < 0: rank is not a member
+}
 
 // ------------------------------------------------------------------------------------ K2 (gather)
 // Pull-based all-gather: dst[(r*part) ...] <- peer r's shard, chunk by chunk; after each chunk the CTA
 // that copied it bumps `chunk_flags[chunk]` to `epoch` (release, gpu scope) so a GEMM running on the
 // remaining SMs can consume weight tiles as they arrive.  Chunks are visited in flat order.
-__global__ void __launch_bounds__(kThreads)
-all_gather_kernel(Peers P, long long part_bytes, uint8_t* __restrict__ dst, long long chunk_bytes,
-                  uint32_t* __restrict__ chunk_flags, uint32_t epoch) {
+struct AllGatherArgs {
+  Peers P;
+  long long part_bytes;
+  uint8_t* dst;
+  long long chunk_bytes;
+  uint32_t* chunk_flags;
+  uint32_t epoch;       // handshake epoch (0 = barrier-free pull)
+  uint32_t flag_value;  // value published in chunk_flags
+};
+__device__ __forceinline__ void all_gather_body(const AllGatherArgs& A) {
+  const Peers& P = A.P;
+  const long long part_bytes = A.part_bytes;
+  uint8_t* __restrict__ dst = A.dst;
+  const long long chunk_bytes = A.chunk_bytes;
+  uint32_t* __restrict__ chunk_flags = A.chunk_flags;
+  const uint32_t epoch = A.epoch;
   // epoch == 0: barrier-free pull (the caller established shard readiness once per step with sxb_symm_barrier)
   if (epoch != 0) {
     if (blockIdx.x == 0) signal_all(P, 4, epoch);
@@ -277,9 +355,13 @@ all_gather_kernel(Peers P, long long part_bytes, uint8_t* __restrict__ dst, long
     __syncthreads();
     if (threadIdx.x == 0 && chunk_flags) {
       __threadfence();
-      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(chunk_flags + c), "r"(epoch) : "memory");
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(chunk_flags + c), "r"(A.flag_value) : "memory");
     }
   }
+}
+__global__ void __launch_bounds__(kThreads) all_gather_kernel(AllGatherArgs A) { all_gather_body(A); }
+__global__ void __launch_bounds__(kThreads) all_gather_emu_kernel(const AllGatherArgs* per_rank) {
+  all_gather_body(per_rank[blockIdx.y]);
 }
 
 // ------------------------------------------------------------------------------------ a2a rows
@@ -291,9 +373,21 @@ struct A2A {
   long long recv_off[kMaxPeers];
   long long count[kMaxPeers];
 };
-__global__ void __launch_bounds__(256)
-a2a_rows_kernel(Peers P, A2A T, const uint8_t* __restrict__ src, int row_bytes, uint32_t epoch,
-                unsigned int* __restrict__ cta_counter) {
+struct A2AArgs {
+  Peers P;
+  A2A T;
+  const uint8_t* src;
+  int row_bytes;
+  uint32_t epoch;
+  unsigned int* cta_counter;
+};
+__device__ __forceinline__ void a2a_rows_body(const A2AArgs& A) {
+  const Peers& P = A.P;
+  const A2A& T = A.T;
+  const uint8_t* __restrict__ src = A.src;
+  const int row_bytes = A.row_bytes;
+  const uint32_t epoch = A.epoch;
+  unsigned int* __restrict__ cta_counter = A.cta_counter;
   // channel 5: destination buffers free (previous consumer done) ; channel 6: my rows have landed
   if (blockIdx.x == 0) signal_all(P, 5, epoch);
   if (!wait_all(P, 5, epoch, 105)) return;
@@ -326,6 +420,8 @@ a2a_rows_kernel(Peers P, A2A T, const uint8_t* __restrict__ src, int row_bytes, 
     signal_all(P, 6, epoch);
   }
 }
+__global__ void __launch_bounds__(256) a2a_rows_kernel(A2AArgs A) { a2a_rows_body(A); }
+__global__ void __launch_bounds__(256) a2a_rows_emu_kernel(const A2AArgs* per_rank) { a2a_rows_body(per_rank[blockIdx.y]); }
 
 static int fill_peers(Peers& P, const void* const* bufs, const void* const* sigs, int rank, int world) {
   if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return SXB_ERR_BAD_ARG;
@@ -346,6 +442,39 @@ static int grid_cap(long long work_items, int max_ctas) {
   return (int)g;
 }
 
+static AdamArgs make_adam(float lr, float beta1, float beta2, float eps, float weight_decay, int step, int adamw,
+                          int bias_correction, float grad_scale) {
+  AdamArgs a;
+  a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay;
+  a.bc1 = bias_correction ? 1.f - powf(beta1, (float)step) : 1.f;
+  a.bc2 = bias_correction ? 1.f - powf(beta2, (float)step) : 1.f;
+  a.grad_scale = grad_scale; a.adamw = adamw;
+  return a;
+}
+
+// Emulation launches: per-rank argument structs are copied to a device staging area (stream-ordered), then ONE
+// cooperative grid (x = CTAs per logical rank, y = world) runs every rank's body.
+template <typename Args>
+static int launch_emu(const void* kernel, const Args* host_args, int world, int ctas, int threads, cudaStream_t s) {
+  static void* staging[2] = {nullptr, nullptr};
+  static int which = 0;
+  const size_t bytes = sizeof(Args) * kMaxPeers;
+  if (bytes > (1u << 16)) return SXB_ERR_TOO_LARGE;
+  which ^= 1;
+  if (!staging[which]) {
+    cudaError_t e = cudaMalloc(&staging[which], 1u << 16);
+    if (e != cudaSuccess) return (int)e;
+  }
+  cudaError_t e = cudaMemcpyAsync(staging[which], host_args, sizeof(Args) * world, cudaMemcpyHostToDevice, s);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaStreamSynchronize(s);     // host_args lives on the caller's stack
+  if (e != cudaSuccess) return (int)e;
+  const Args* dev_args = reinterpret_cast<const Args*>(staging[which]);
+  void* params[] = {(void*)&dev_args};
+  e = cudaLaunchCooperativeKernel(kernel, dim3(ctas, world), dim3(threads), params, 0, s);
+  return e == cudaSuccess ? SXB_OK : (int)e;
+}
+
 }  // namespace symm
 }  // namespace sxb
 
@@ -360,42 +489,84 @@ __global__ void barrier_channel_kernel(sxb::symm::Peers P, int channel, uint32_t
   sxb::symm::wait_all(P, channel, epoch, 110);
 }
 
+// One-warp "rank reached `epoch` on `channel`" announcement, stream-ordered after the work it publishes.
+__global__ void signal_channel_kernel(sxb::symm::Peers P, int channel, uint32_t epoch) {
+  __threadfence_system();
+  sxb::symm::signal_all(P, channel, epoch);
+}
+
 // K1.  bufs/sigs: host arrays of `world` device pointers (peer mappings of the flat bf16 gradient buffer
 // and of the signal pads).  part: elements per shard (multiple of 8).  counter: device uint32 (zeroed once).
 // apply_adam == 0 -> plain reduce-scatter(mean) into grad_out (used when the step must be deferred).
+// handshake_done != 0: the caller already announced "gradients ready" (sxb_symm_signal on the stream that produced
+// them) and waited for the peers (sxb_symm_wait on this stream); no CTA of this grid spins.
 SXB_API int sxb_symm_rs_adam(const void* const* bufs, const void* const* sigs, int rank, int world, long long part,
                              void* hp, void* m, void* v, void* lp, void* grad_out, float lr, float beta1,
                              float beta2, float eps, float weight_decay, int step, int adamw, int bias_correction,
                              float grad_scale, unsigned int epoch, const void* multicast_ptr, void* counter,
-                             int apply_adam, int max_ctas, void* stream) {
-  Peers P;
-  int rc = fill_peers(P, bufs, sigs, rank, world);
+                             int apply_adam, int max_ctas, int handshake_done, void* stream) {
+  RsAdamArgs A;
+  int rc = fill_peers(A.P, bufs, sigs, rank, world);
   if (rc) return rc;
   if (part <= 0 || (part & 7)) return SXB_ERR_UNSUPPORTED;
-  AdamArgs a;
-  a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay;
-  a.bc1 = bias_correction ? 1.f - powf(beta1, (float)step) : 1.f;
-  a.bc2 = bias_correction ? 1.f - powf(beta2, (float)step) : 1.f;
-  a.grad_scale = grad_scale; a.adamw = adamw;
-  // SXB_RS_SPLIT_SYNC=1 runs the handshake as a one-warp kernel in front of the big one (A/B measurements: no
-  // difference at 2 GPUs); default: inside the kernel.
-  static const int split = [] { const char* e = getenv("SXB_RS_SPLIT_SYNC"); return e ? atoi(e) : 0; }();
+  A.part = part; A.hp = (float*)hp; A.m = (float*)m; A.v = (float*)v;
+  A.lp = (__nv_bfloat16*)lp; A.grad_out = (__nv_bfloat16*)grad_out;
+  A.a = make_adam(lr, beta1, beta2, eps, weight_decay, step, adamw, bias_correction, grad_scale);
+  A.epoch = epoch; A.mc_ptr = multicast_ptr; A.cta_counter = (unsigned int*)counter; A.apply_adam = apply_adam;
+  // SXB_RS_SPLIT_SYNC=1 runs the in-kernel handshake as a one-warp kernel in front of the big one
+  static const int split_env = [] { const char* e = getenv("SXB_RS_SPLIT_SYNC"); return e ? atoi(e) : 0; }();
+  const int split = split_env && !handshake_done;
   if (split) {
-    barrier_channel_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, 0, epoch);
+    barrier_channel_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(A.P, 0, epoch);
     SXB_CHECK_LAUNCH();
   }
-  rs_adam_kernel<<<grid_cap(part / 8, max_ctas), kThreads, 0, (cudaStream_t)stream>>>(
-      P, part, (float*)hp, (float*)m, (float*)v, (__nv_bfloat16*)lp, (__nv_bfloat16*)grad_out, a, epoch,
-      multicast_ptr, (unsigned int*)counter, apply_adam, split ? 0 : 1);
+  A.do_sync = (split || handshake_done) ? 0 : 1;
+  rs_adam_kernel<<<grid_cap(part / 8, max_ctas), kThreads, 0, (cudaStream_t)stream>>>(A);
   SXB_CHECK_LAUNCH();
   return SXB_OK;
 }
+
+// K1, `world` logical ranks emulated on ONE GPU by one cooperative grid.  bufs/sigs as above (all local);
+// hp/m/v/lp/grad_out/counters: host arrays of `world` per-rank device pointers.  ctas_per_rank * world CTAs of 512
+// threads must be co-resident (cudaLaunchCooperativeKernel refuses otherwise).
+SXB_API int sxb_symm_rs_adam_emu(const void* const* bufs, const void* const* sigs, int world, long long part,
+                                 void* const* hp, void* const* m, void* const* v, void* const* lp,
+                                 void* const* grad_out, float lr, float beta1, float beta2, float eps,
+                                 float weight_decay, int step, int adamw, int bias_correction, float grad_scale,
+                                 unsigned int epoch, void* const* counters, int apply_adam, int ctas_per_rank,
+                                 void* stream) {
+  if (world < 1 || world > kMaxPeers || part <= 0 || (part & 7) || ctas_per_rank < 1) return SXB_ERR_BAD_ARG;
+  RsAdamArgs A[kMaxPeers];
+  for (int r = 0; r < world; ++r) {
+    int rc = fill_peers(A[r].P, bufs, sigs, r, world);
+    if (rc) return rc;
+    A[r].part = part;
+    A[r].hp = apply_adam ? (float*)hp[r] : nullptr; A[r].m = apply_adam ? (float*)m[r] : nullptr;
+    A[r].v = apply_adam ? (float*)v[r] : nullptr; A[r].lp = apply_adam ? (__nv_bfloat16*)lp[r] : nullptr;
+    A[r].grad_out = apply_adam ? nullptr : (__nv_bfloat16*)grad_out[r];
+    A[r].a = make_adam(lr, beta1, beta2, eps, weight_decay, step, adamw, bias_correction, grad_scale);
+    A[r].epoch = epoch; A[r].mc_ptr = nullptr; A[r].cta_counter = (unsigned int*)counters[r];
+    A[r].apply_adam = apply_adam; A[r].do_sync = 1;
+  }
+  return launch_emu((const void*)rs_adam_emu_kernel, A, world, ctas_per_rank, kThreads, (cudaStream_t)stream);
+}
+
 SXB_API int sxb_symm_barrier(const void* const* bufs, const void* const* sigs, int rank, int world, int channel,
                              unsigned int epoch, void* stream) {
   Peers P;
   int rc = fill_peers(P, bufs, sigs, rank, world);
   if (rc) return rc;
   barrier_channel_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, channel, epoch);
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+SXB_API int sxb_symm_signal(const void* const* bufs, const void* const* sigs, int rank, int world, int channel,
+                            unsigned int epoch, void* stream) {
+  Peers P;
+  int rc = fill_peers(P, bufs, sigs, rank, world);
+  if (rc) return rc;
+  signal_channel_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, channel, epoch);
   SXB_CHECK_LAUNCH();
   return SXB_OK;
 }
@@ -411,64 +582,133 @@ SXB_API int sxb_symm_wait(const void* const* bufs, const void* const* sigs, int 
 }
 
 // K9.  members: host array of `n_members` group ranks (must contain `rank`); out: local (non-symmetric) result.
+static int fill_members(Members& M, const int* members, int n_members) {
+  if (n_members < 1 || n_members > kMaxPeers) return SXB_ERR_BAD_ARG;
+  M.count = n_members;
+  for (int i = 0; i < kMaxPeers; ++i) M.idx[i] = i < n_members ? members[i] : 0;
+  return SXB_OK;
+}
 SXB_API int sxb_symm_subset_mean(const void* const* bufs, const void* const* sigs, int rank, int world,
                                  const int* members, int n_members, void* out, long long n, int dtype,
                                  unsigned int epoch, void* counter, int max_ctas, void* stream) {
   Peers P;
   int rc = fill_peers(P, bufs, sigs, rank, world);
   if (rc) return rc;
-  if (n_members < 1 || n_members > kMaxPeers) return SXB_ERR_BAD_ARG;
   Members M;
-  M.count = n_members;
-  for (int i = 0; i < kMaxPeers; ++i) M.idx[i] = i < n_members ? members[i] : 0;
+  if ((rc = fill_members(M, members, n_members))) return rc;
   const int grid = grid_cap(n / 8 + 1, max_ctas);
   cudaStream_t s = (cudaStream_t)stream;
-  if (dtype == kBF16) subset_mean_kernel<__nv_bfloat16><<<grid, kThreads, 0, s>>>(P, M, (__nv_bfloat16*)out, n, epoch, (unsigned int*)counter);
-  else if (dtype == kF16) subset_mean_kernel<__half><<<grid, kThreads, 0, s>>>(P, M, (__half*)out, n, epoch, (unsigned int*)counter);
-  else return SXB_ERR_BAD_ARG;
+  if (dtype == kBF16) {
+    SubsetMeanArgs<__nv_bfloat16> A{P, M, (__nv_bfloat16*)out, n, epoch, (unsigned int*)counter};
+    subset_mean_kernel<__nv_bfloat16><<<grid, kThreads, 0, s>>>(A);
+  } else if (dtype == kF16) {
+    SubsetMeanArgs<__half> A{P, M, (__half*)out, n, epoch, (unsigned int*)counter};
+    subset_mean_kernel<__half><<<grid, kThreads, 0, s>>>(A);
+  } else {
+    return SXB_ERR_BAD_ARG;
+  }
   SXB_CHECK_LAUNCH();
   return SXB_OK;
 }
+// K9 emulated (bf16): outs[r] may be NULL for ranks outside `members` (they take no part, as in the real launch).
+SXB_API int sxb_symm_subset_mean_emu(const void* const* bufs, const void* const* sigs, int world, const int* members,
+                                     int n_members, void* const* outs, long long n, unsigned int epoch,
+                                     void* const* counters, int ctas_per_rank, void* stream) {
+  if (world < 1 || world > kMaxPeers || ctas_per_rank < 1) return SXB_ERR_BAD_ARG;
+  Members M;
+  int rc;
+  if ((rc = fill_members(M, members, n_members))) return rc;
+  SubsetMeanArgs<__nv_bfloat16> A[kMaxPeers];
+  for (int r = 0; r < world; ++r) {
+    if ((rc = fill_peers(A[r].P, bufs, sigs, r, world))) return rc;
+    A[r].M = M; A[r].out = (__nv_bfloat16*)outs[r]; A[r].n = outs[r] ? n : -1; A[r].epoch = epoch;
+    A[r].cta_counter = (unsigned int*)counters[r];
+  }
+  return launch_emu((const void*)subset_mean_emu_kernel<__nv_bfloat16>, A, world, ctas_per_rank, kThreads,
+                    (cudaStream_t)stream);
+}
 
+// K2 gather half.  chunk_flags (optional, device uint32[ceil(world*part_bytes / chunk_bytes)]): chunk c is set to
+// `flag_value` (release, gpu scope) once all of its bytes are in dst — the gated GEMM polls these.
 SXB_API int sxb_symm_all_gather(const void* const* bufs, const void* const* sigs, int rank, int world,
                                 long long part_bytes, void* dst, long long chunk_bytes, void* chunk_flags,
-                                unsigned int epoch, int max_ctas, void* stream) {
-  Peers P;
-  int rc = fill_peers(P, bufs, sigs, rank, world);
+                                unsigned int epoch, int max_ctas, unsigned int flag_value, void* stream) {
+  AllGatherArgs A;
+  int rc = fill_peers(A.P, bufs, sigs, rank, world);
   if (rc) return rc;
   if ((part_bytes & 15) || (chunk_bytes & 15) || chunk_bytes <= 0) return SXB_ERR_UNSUPPORTED;
   const long long nchunks = (part_bytes * world + chunk_bytes - 1) / chunk_bytes;
   int grid = max_ctas > 0 ? max_ctas : 64;
   if (grid > nchunks) grid = (int)nchunks;
-  all_gather_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(P, part_bytes, (uint8_t*)dst, chunk_bytes,
-                                                               (uint32_t*)chunk_flags, epoch);
+  A.part_bytes = part_bytes; A.dst = (uint8_t*)dst; A.chunk_bytes = chunk_bytes;
+  A.chunk_flags = (uint32_t*)chunk_flags; A.epoch = epoch; A.flag_value = flag_value ? flag_value : epoch;
+  all_gather_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(A);
   SXB_CHECK_LAUNCH();
   return SXB_OK;
 }
+SXB_API int sxb_symm_all_gather_emu(const void* const* bufs, const void* const* sigs, int world, long long part_bytes,
+                                    void* const* dsts, long long chunk_bytes, void* const* chunk_flags,
+                                    unsigned int epoch, unsigned int flag_value, int ctas_per_rank, void* stream) {
+  if (world < 1 || world > kMaxPeers || ctas_per_rank < 1) return SXB_ERR_BAD_ARG;
+  if ((part_bytes & 15) || (chunk_bytes & 15) || chunk_bytes <= 0) return SXB_ERR_UNSUPPORTED;
+  AllGatherArgs A[kMaxPeers];
+  for (int r = 0; r < world; ++r) {
+    int rc = fill_peers(A[r].P, bufs, sigs, r, world);
+    if (rc) return rc;
+    A[r].part_bytes = part_bytes; A[r].dst = (uint8_t*)dsts[r]; A[r].chunk_bytes = chunk_bytes;
+    A[r].chunk_flags = chunk_flags ? (uint32_t*)chunk_flags[r] : nullptr; A[r].epoch = epoch;
+    A[r].flag_value = flag_value ? flag_value : epoch;
+  }
+  return launch_emu((const void*)all_gather_emu_kernel, A, world, ctas_per_rank, kThreads, (cudaStream_t)stream);
+}
 
 // send_off / recv_off / count: host arrays of `world` int64 (rows).
-SXB_API int sxb_symm_a2a_rows(const void* const* bufs, const void* const* sigs, int rank, int world,
-                              const void* src, const long long* send_off, const long long* recv_off,
-                              const long long* count, int row_bytes, unsigned int epoch, void* counter,
-                              int max_ctas, void* stream) {
-  Peers P;
-  int rc = fill_peers(P, bufs, sigs, rank, world);
-  if (rc) return rc;
-  if (row_bytes & 15) return SXB_ERR_UNSUPPORTED;
-  A2A T;
+static int fill_a2a(A2A& T, const long long* send_off, const long long* recv_off, const long long* count, int world,
+                    long long* total_out) {
   long long total = 0;
   for (int i = 0; i < kMaxPeers; ++i) {
     T.send_off[i] = i < world ? send_off[i] : 0;
     T.recv_off[i] = i < world ? recv_off[i] : 0;
     T.count[i] = i < world ? count[i] : 0;
+    if (T.count[i] < 0) return SXB_ERR_BAD_ARG;
     total += T.count[i];
   }
+  *total_out = total;
+  return SXB_OK;
+}
+SXB_API int sxb_symm_a2a_rows(const void* const* bufs, const void* const* sigs, int rank, int world,
+                              const void* src, const long long* send_off, const long long* recv_off,
+                              const long long* count, int row_bytes, unsigned int epoch, void* counter,
+                              int max_ctas, void* stream) {
+  A2AArgs A;
+  int rc = fill_peers(A.P, bufs, sigs, rank, world);
+  if (rc) return rc;
+  if (row_bytes & 15) return SXB_ERR_UNSUPPORTED;
+  long long total = 0;
+  if ((rc = fill_a2a(A.T, send_off, recv_off, count, world, &total))) return rc;
   long long g = (total + 7) / 8;
   if (g < 1) g = 1;
   const int cap = max_ctas > 0 ? max_ctas : 148;
   if (g > cap) g = cap;
-  a2a_rows_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(P, T, (const uint8_t*)src, row_bytes, epoch,
-                                                            (unsigned int*)counter);
+  A.src = (const uint8_t*)src; A.row_bytes = row_bytes; A.epoch = epoch; A.cta_counter = (unsigned int*)counter;
+  a2a_rows_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(A);
   SXB_CHECK_LAUNCH();
   return SXB_OK;
+}
+// Emulated: srcs[r], and send_off/recv_off/count as [world][world] row-major int64 tables (row r = rank r's tables).
+SXB_API int sxb_symm_a2a_rows_emu(const void* const* bufs, const void* const* sigs, int world, const void* const* srcs,
+                                  const long long* send_off, const long long* recv_off, const long long* count,
+                                  int row_bytes, unsigned int epoch, void* const* counters, int ctas_per_rank,
+                                  void* stream) {
+  if (world < 1 || world > kMaxPeers || ctas_per_rank < 1 || (row_bytes & 15)) return SXB_ERR_BAD_ARG;
+  A2AArgs A[kMaxPeers];
+  for (int r = 0; r < world; ++r) {
+    int rc = fill_peers(A[r].P, bufs, sigs, r, world);
+    if (rc) return rc;
+    long long total = 0;
+    if ((rc = fill_a2a(A[r].T, send_off + r * world, recv_off + r * world, count + r * world, world, &total))) return rc;
+    A[r].src = (const uint8_t*)srcs[r]; A[r].row_bytes = row_bytes; A[r].epoch = epoch;
+    A[r].cta_counter = (unsigned int*)counters[r];
+  }
+  return launch_emu((const void*)a2a_rows_emu_kernel, A, world, ctas_per_rank, 256, (cudaStream_t)stream);
 }

@@ -51,7 +51,65 @@ int encode_tensor_map(CUtensorMap* m, int dtype_code, int rank, const void* ptr,
   return r == CUDA_SUCCESS ? SXB_OK : SXB_ERR_DRIVER;
 }
 
+// ---- local-ownership test for anything a TMA multicast tensor map will cover ---------------------
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
+// GPU's memory hung the GPU.  A range counts as local only if (1) the runtime reports an ordinary device
+// allocation of the current device, (2) the driver's allocation range contains the WHOLE extent and (3) the
+// extent touches none of the ranges registered as foreign (peer / multicast mappings of symmetric memory,
+// registered by comm/symm.py when a buffer is rendezvoused).  Anything else selects the non-multicast kernels.
+namespace {
+struct ForeignRange { uintptr_t lo, hi; };
+ForeignRange g_foreign[4096];
+int g_n_foreign = 0;
+typedef CUresult (*AddrRangeFn)(CUdeviceptr*, size_t*, CUdeviceptr);
+AddrRangeFn resolve_addr_range() {
+  static AddrRangeFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<AddrRangeFn>(ptr);
+  }
+  return fn;
+}
+}  // namespace
+
+bool range_is_local(const void* p, long long bytes) {
+  if (p == nullptr || bytes <= 0) return false;
+  const uintptr_t lo = reinterpret_cast<uintptr_t>(p), hi = lo + (uintptr_t)bytes;
+  for (int i = 0; i < g_n_foreign; ++i)
+    if (lo < g_foreign[i].hi && g_foreign[i].lo < hi) return false;
+  cudaPointerAttributes a{};
+  int dev = -1;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  if (a.type != cudaMemoryTypeDevice || a.device != dev) return false;
+  AddrRangeFn ar = resolve_addr_range();
+  if (!ar) return false;
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  if (ar(&base, &size, (CUdeviceptr)lo) != CUDA_SUCCESS) return false;
+  return (uintptr_t)base <= lo && hi <= (uintptr_t)base + size;
+}
+
 }  // namespace sxb
+
+// Declare [p, p+bytes) as NOT this GPU's memory (a peer's buffer or a multicast window mapped into this
+// process).  Append-only; returns SXB_ERR_TOO_LARGE when the table is full (callers then must not rely on it).
+SXB_API int sxb_register_foreign_range(const void* p, long long bytes) {
+  if (p == nullptr || bytes <= 0) return SXB_ERR_BAD_ARG;
+  const uintptr_t lo = reinterpret_cast<uintptr_t>(p), hi = lo + (uintptr_t)bytes;
+  for (int i = 0; i < sxb::g_n_foreign; ++i)
+    if (sxb::g_foreign[i].lo == lo && sxb::g_foreign[i].hi >= hi) return SXB_OK;
+  if (sxb::g_n_foreign >= 4096) return SXB_ERR_TOO_LARGE;
+  sxb::g_foreign[sxb::g_n_foreign].lo = lo;
+  sxb::g_foreign[sxb::g_n_foreign].hi = hi;
+  ++sxb::g_n_foreign;
+  return SXB_OK;
+}
+// 1 when [p, p+bytes) passes the local-ownership test above, else 0.
+SXB_API int sxb_range_is_local(const void* p, long long bytes) { return sxb::range_is_local(p, bytes) ? 1 : 0; }
 
 // Library/version probe used by Python to verify that the loaded .so matches the sources.
 SXB_API int sxb_abi_version() { return 3; }

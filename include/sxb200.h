@@ -25,6 +25,15 @@ int sxb_gemm_hang_info(unsigned int* out_host);
  * problems; single-CTA 128x256 kernel otherwise), 1 = force single-CTA, 2 = force CTA-pair. */
 int sxb_gemm_set_mode(int mode);
 int sxb_attn_hang_info(unsigned int* out_host);
+/* Local-ownership registry for TMA multicast (no counterpart in the reference).  Kernels that multicast a tile
+ * across a cluster only do so when the tensor map covers this GPU's memory alone: ordinary allocation of the
+ * current device, whole extent inside one allocation, not registered here.  comm/symm.py registers every peer /
+ * multicast mapping of symmetric memory.  sxb_range_is_local returns 1/0; sxb_attn_would_multicast reports which
+ * kernel family (1 = 2-CTA multicast, 0 = single CTA) sxb_attn_fwd / the dQ pass would take for these K/V. */
+int sxb_register_foreign_range(const void* p, long long bytes);
+int sxb_range_is_local(const void* p, long long bytes);
+int sxb_attn_would_multicast(const void* k, const void* v, int B, int S, int Hq, int Hk, int D, long long k_stride,
+                             long long v_stride);
 
 /* ---- tcgen05 GEMM: C[M,N] (+)= alpha * op(A) op(B); layout 0 NT, 1 NN, 2 TN.
  *      Replaces cuBLAS behind F.linear (inference/v2/kernels/core_ops/blas_kernels/blas_utils.h:31-41). */
@@ -61,11 +70,13 @@ int sxb_rmsnorm_bwd(const void* dy, const void* x, const void* w, const void* rs
  * memory plan already owns the whole GPU, a server that gave the device to its KV-cache pool, a
  * recovery path running because an allocation failed).  No counterpart in the reference: the reference
  * always allocates through torch.  Identical to sxb_rmsnorm_bwd except that the weight-gradient
- * partials live in a ~9.3 MiB scratch array inside the library image (held by every GPU that loads
- * the library).  Limit: H <= sxb_rmsnorm_bwd_noalloc_max_h() (8192), otherwise returns -3.  One array
+ * partials live in a ~9.3 MiB scratch array inside the library image (every GPU on which the norm
+ * module of the library has been loaded holds it until the process exits; with CUDA's default lazy
+ * module loading that happens at the first norm kernel or the first call of this function).  Limit: H <= sxb_rmsnorm_bwd_noalloc_max_h() (8192), otherwise returns -3.  One array
  * per device, shared by all calls: calls that overlap on the GPU race and must be serialised by the
  * caller; nothing needs zeroing between calls.  The first call on a device looks up the array's device
- * address (cudaGetSymbolAddress) — make it before any stream capture.  Never calls cudaMalloc/cudaFree. */
+ * address (cudaGetSymbolAddress) — make it before any stream capture and before the rest of the device
+ * memory is committed (the lazily loaded array needs its 9.3 MiB then).  Never calls cudaMalloc/cudaFree. */
 int sxb_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w, const void* rstd, const void* dres,
                             void* dx, void* dw, long long rows, int H, int dtype, int accumulate_dw, void* stream);
 int sxb_rmsnorm_bwd_noalloc_max_h(void);

@@ -1,18 +1,18 @@
-""""Fake peer" mode: N logical ranks on ONE GPU.
+"""Emulated peers: N logical ranks on ONE GPU.
 
 The peer-memory kernels only see pointer tables (``bufs[world]``, ``sigs[world]``) and a rank index, so the same
-kernels run unchanged when all ``world`` buffers and signal pads live on one device: rank ``r``'s kernel is launched
-on its own stream with a small grid (so the ``world`` grids are co-resident — they spin on each other's flags and
-would deadlock if one could not be scheduled), and "peer" loads / stores are ordinary local accesses.  This exercises
-the flag protocol, the indexing and the arithmetic of every fused collective without a second GPU; it says nothing
-about NVLink ordering or NVLS (no multicast pointer here).
+device code runs when all ``world`` buffers and signal pads live on one device.  The ranks of a collective wait on
+one another's flags, and separate launches on one GPU carry no guarantee of running at the same time — so every
+collective here is ONE cooperative grid (``blockIdx.y`` = logical rank, entry points ``sxb_symm_*_emu``): the
+launch itself fails if the ``world x ctas`` CTAs cannot be co-resident.  "Peer" loads / stores are ordinary local
+accesses; this exercises the flag protocol, the indexing and the arithmetic of every fused collective without a
+second GPU.  It says nothing about NVLink ordering or NVLS (no multicast pointer here).
 
-Use from a single process on a CUDA device; ``tools/symm_fake_peer_check.py`` compares every kernel with its PyTorch
-statement.  (Not yet part of the pytest ``gpu`` tier: written after this round's GPU time was spent.)"""
+``tests/test_symm_emulated_gpu.py`` compares every kernel with its PyTorch statement in the ``gpu`` pytest tier."""
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional
+from typing import List, Optional, Sequence
 
 import torch
 
@@ -20,7 +20,19 @@ from ..native import lib as _n
 from . import symm as _symm      # registers the kernel signatures
 from .symm import CH_A2A_FREE, CH_A2A_LANDED, CH_AG_READY, CH_AVG_READ, CH_AVG_READY, CH_GRADS_READ, CH_GRADS_READY
 
-MAX_CTAS = 8          # per logical rank: world * MAX_CTAS CTAs must be resident together
+_n.register({
+    "sxb_symm_rs_adam_emu": "ppil" "ppppp" "fffff" "iii" "f" "i" "p" "ii" "p",
+    "sxb_symm_subset_mean_emu": "ppi" "pi" "pl" "i" "p" "i" "p",
+    "sxb_symm_all_gather_emu": "ppil" "pl" "p" "iii" "p",
+    "sxb_symm_a2a_rows_emu": "ppi" "pppp" "ii" "p" "i" "p",
+})
+
+MAX_CTAS = 8          # per logical rank: world * MAX_CTAS CTAs run as one cooperative grid
+
+
+def _ptr_array(tensors: Sequence[Optional[torch.Tensor]]):
+    arr = (ctypes.c_void_p * len(tensors))(*[None if t is None else t.data_ptr() for t in tensors])
+    return arr, ctypes.cast(arr, ctypes.c_void_p)
 
 
 class FakePeerBuffer:
@@ -52,25 +64,16 @@ class FakePeerBuffer:
 
 
 class FakePeerGroup:
-    """Launches one kernel per logical rank, each on its own stream, then joins them."""
+    """Runs each collective for all logical ranks as one cooperative launch on the current stream."""
 
     def __init__(self, world: int, device=None):
         self.world = world
         self.device = device or torch.device("cuda", torch.cuda.current_device())
-        self.streams = [torch.cuda.Stream(device=self.device) for _ in range(world)]
-        self.counters = torch.zeros(world, 16, dtype=torch.int32, device=self.device)
+        self.counters = [torch.zeros(16, dtype=torch.int32, device=self.device) for _ in range(world)]
 
-    def _each_rank(self, fn) -> None:
-        cur = torch.cuda.current_stream()
-        for r, s in enumerate(self.streams):
-            s.wait_stream(cur)
-            with torch.cuda.stream(s):
-                fn(r)
-        for s in self.streams:
-            cur.wait_stream(s)
-
-    def _ctr(self, rank: int, i: int) -> int:
-        return self.counters.data_ptr() + 4 * (rank * 16 + i)
+    def _ctrs(self, i: int):
+        arr = (ctypes.c_void_p * self.world)(*[c.data_ptr() + 4 * i for c in self.counters])
+        return arr, ctypes.cast(arr, ctypes.c_void_p)
 
     # K1: reduce-scatter (+ AdamW); per-rank optimizer tensors are lists indexed by logical rank
     def rs_adam(self, grads: FakePeerBuffer, part: int, hp, m, v, lp, cfg: dict, step: int, adamw: bool = True,
@@ -79,40 +82,46 @@ class FakePeerGroup:
         grads.epochs[CH_GRADS_READ] = epoch
         b1, b2 = cfg["betas"]
         apply = grad_out is None
-
-        def launch(r):
-            _n.call("sxb_symm_rs_adam", grads.bufs, grads.sigs, r, self.world, int(part),
-                    _n.ptr(hp[r]) if apply else None, _n.ptr(m[r]) if apply else None, _n.ptr(v[r]) if apply else None,
-                    _n.ptr(lp[r]) if apply else None, None if apply else _n.ptr(grad_out[r]),
-                    float(cfg["lr"]), float(b1), float(b2), float(cfg["eps"]), float(cfg["weight_decay"]), int(step),
-                    int(adamw), int(bool(cfg.get("bias_correction", True))), float(grad_scale), int(epoch), None,
-                    self._ctr(r, 0), int(apply), MAX_CTAS, _n.stream_ptr())
-        self._each_rank(launch)
+        none = [None] * self.world
+        keep = [_ptr_array(x if x is not None else none) for x in (hp, m, v, lp, grad_out)]
+        ck, cp = self._ctrs(0)
+        _n.call("sxb_symm_rs_adam_emu", grads.bufs, grads.sigs, self.world, int(part),
+                keep[0][1], keep[1][1], keep[2][1], keep[3][1], keep[4][1],
+                float(cfg["lr"]), float(b1), float(b2), float(cfg["eps"]), float(cfg["weight_decay"]), int(step),
+                int(adamw), int(bool(cfg.get("bias_correction", True))), float(grad_scale), int(epoch), cp,
+                int(apply), MAX_CTAS, _n.stream_ptr())
 
     # K9: mean over a subset of ranks
     def subset_mean(self, src: FakePeerBuffer, members: List[int], out: List[torch.Tensor], n: int) -> None:
         epoch = src.next_epoch(CH_AVG_READY)
         src.epochs[CH_AVG_READ] = epoch
         arr = (ctypes.c_int * len(members))(*members)
+        ok, op = _ptr_array([out[r] if r in members else None for r in range(self.world)])
+        ck, cp = self._ctrs(1)
+        _n.call("sxb_symm_subset_mean_emu", src.bufs, src.sigs, self.world, ctypes.cast(arr, ctypes.c_void_p),
+                len(members), op, int(n), int(epoch), cp, MAX_CTAS, _n.stream_ptr())
 
-        def launch(r):
-            if r in members:
-                _n.call("sxb_symm_subset_mean", src.bufs, src.sigs, r, self.world, ctypes.cast(arr, ctypes.c_void_p),
-                        len(members), out[r].data_ptr(), int(n), _n.dtype_code(out[r].dtype), int(epoch),
-                        self._ctr(r, 1), MAX_CTAS, _n.stream_ptr())
-        self._each_rank(launch)
-
-    # K2: all-gather of ``part_numel`` elements per rank
-    def all_gather(self, shard: FakePeerBuffer, part_numel: int, dst: List[torch.Tensor]) -> None:
+    # K2: all-gather of ``part_numel`` elements per rank (+ per-chunk arrival flags)
+    def all_gather(self, shard: FakePeerBuffer, part_numel: int, dst: List[torch.Tensor], chunk_bytes: int = 1 << 16,
+                   chunk_flags: Optional[List[torch.Tensor]] = None, flag_value: int = 0) -> None:
         epoch = shard.next_epoch(CH_AG_READY)
         es = dst[0].element_size()
+        dk, dp = _ptr_array(dst)
+        fk, fp = _ptr_array(chunk_flags) if chunk_flags is not None else (None, None)
+        _n.call("sxb_symm_all_gather_emu", shard.bufs, shard.sigs, self.world, int(part_numel * es), dp,
+                int(chunk_bytes), fp, int(epoch), int(flag_value), MAX_CTAS, _n.stream_ptr())
 
-        def launch(r):
-            _n.call("sxb_symm_all_gather", shard.bufs, shard.sigs, r, self.world, int(part_numel * es),
-                    dst[r].data_ptr(), 1 << 16, None, int(epoch), MAX_CTAS, _n.stream_ptr())
-        self._each_rank(launch)
-
-    def barrier(self, buf: FakePeerBuffer, channel: int = CH_AG_READY) -> None:
-        epoch = buf.next_epoch(channel)
-        self._each_rank(lambda r: _n.call("sxb_symm_barrier", buf.bufs, buf.sigs, r, self.world, int(channel),
-                                           int(epoch), _n.stream_ptr()))
+    # row all-to-all: tables[r][d] = (send_off, recv_off, count) of rank r towards destination d
+    def a2a_rows(self, dst: FakePeerBuffer, srcs: List[torch.Tensor], send_off, recv_off, count, row_bytes: int) -> None:
+        epoch = dst.next_epoch(CH_A2A_FREE)
+        dst.epochs[CH_A2A_LANDED] = epoch
+        W = self.world
+        L = ctypes.c_longlong * (W * W)
+        so = L(*[int(send_off[r][d]) for r in range(W) for d in range(W)])
+        ro = L(*[int(recv_off[r][d]) for r in range(W) for d in range(W)])
+        ct = L(*[int(count[r][d]) for r in range(W) for d in range(W)])
+        sk, sp = _ptr_array(srcs)
+        ck, cp = self._ctrs(2)
+        _n.call("sxb_symm_a2a_rows_emu", dst.bufs, dst.sigs, W, sp, ctypes.cast(so, ctypes.c_void_p),
+                ctypes.cast(ro, ctypes.c_void_p), ctypes.cast(ct, ctypes.c_void_p), int(row_bytes), int(epoch), cp,
+                MAX_CTAS, _n.stream_ptr())

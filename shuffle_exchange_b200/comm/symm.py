@@ -25,14 +25,21 @@ import torch
 from ..native import lib as _n
 
 _n.register({
-    "sxb_symm_rs_adam": "ppiil" "ppppp" "fffff" "iii" "f" "i" "pp" "ii" "p",
+    "sxb_symm_rs_adam": "ppiil" "ppppp" "fffff" "iii" "f" "i" "pp" "iii" "p",
     "sxb_symm_wait": "ppiiiip",
+    "sxb_symm_signal": "ppiiiip",
     "sxb_symm_barrier": "ppiiiip",
     "sxb_symm_subset_mean": "ppiipiplii" "pip",
-    "sxb_symm_all_gather": "ppiilplpiip",
+    "sxb_symm_all_gather": "ppiilplpiiip",
     "sxb_symm_a2a_rows": "ppiippppiipip",
     "sxb_symm_hang_info": "p",
+    "sxb_register_foreign_range": "pl",
+    "sxb_range_is_local": "pl",
+    "sxb_attn_would_multicast": "pp" "iiiii" "ll",
 })
+
+import os as _os
+_RS_CTAS = int(_os.environ.get("SXB_RS_CTAS", "148"))   # grid cap of the reduce-scatter+Adam kernel (1 CTA / SM)
 
 CH_GRADS_READY, CH_GRADS_READ, CH_AVG_READY, CH_AVG_READ, CH_AG_READY, CH_A2A_FREE, CH_A2A_LANDED = range(7)
 
@@ -63,6 +70,15 @@ class SymmBuffer:
         mc = getattr(self.handle, "multicast_ptr", 0) or 0
         self.multicast_ptr = int(mc)
         self.epochs = [0] * 16          # per-buffer, per-channel (signal pads belong to the buffer)
+        # Every mapping of ANOTHER rank's memory (and the multicast window) is declared foreign to the kernel
+        # library: TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
+        # another GPU's memory hung the GPU — kernels that would multicast check this registry and fall back.
+        nbytes = int(numel) * self.tensor.element_size()
+        for r, p in enumerate(self.handle.buffer_ptrs):
+            if r != self.rank:
+                _n.call("sxb_register_foreign_range", int(p), nbytes)
+        if self.multicast_ptr:
+            _n.call("sxb_register_foreign_range", self.multicast_ptr, nbytes)
 
     def next_epoch(self, ch: int) -> int:
         self.epochs[ch] += 1
@@ -118,13 +134,29 @@ class SymmGroup:
         return self.counter.data_ptr() + 4 * i
 
     # ------------------------------------------------------------------------------------- K1
-    def rs_adam(self, grads: SymmBuffer, part: int, hp, m, v, lp, group_cfg: dict, step: int, adamw: bool = True,
-                grad_scale: float = 1.0, grad_out: Optional[torch.Tensor] = None, use_multicast: bool = True,
-                max_ctas: int = 0):
-        """Reduce this rank's shard of every peer's flat bf16 gradient buffer and (unless ``grad_out`` is
-        given) apply AdamW to ``hp/m/v`` writing the bf16 shard ``lp`` — one kernel, no NCCL."""
+    def announce_grads(self, grads: SymmBuffer) -> int:
+        """Tell every peer, on the CURRENT stream (the one that produced the gradients), that this rank's
+        gradients in ``grads`` are complete.  Returns the epoch to hand to :meth:`rs_adam` — which then only waits
+        for the peers with a one-warp kernel instead of spinning an SM-filling grid next to the backward GEMMs."""
         epoch = grads.next_epoch(CH_GRADS_READY)
         grads.epochs[CH_GRADS_READ] = epoch
+        _n.call("sxb_symm_signal", grads.bufs, grads.sigs, self.rank, self.world, CH_GRADS_READY, int(epoch),
+                _n.stream_ptr())
+        return epoch
+
+    def rs_adam(self, grads: SymmBuffer, part: int, hp, m, v, lp, group_cfg: dict, step: int, adamw: bool = True,
+                grad_scale: float = 1.0, grad_out: Optional[torch.Tensor] = None, use_multicast: bool = True,
+                max_ctas: int = 0, announced_epoch: Optional[int] = None):
+        """Reduce this rank's shard of every peer's flat bf16 gradient buffer and (unless ``grad_out`` is
+        given) apply AdamW to ``hp/m/v`` writing the bf16 shard ``lp`` — one kernel, no NCCL.
+        ``announced_epoch``: epoch returned by :meth:`announce_grads` (handshake split out of the kernel)."""
+        if announced_epoch is not None:
+            epoch = announced_epoch
+            _n.call("sxb_symm_wait", grads.bufs, grads.sigs, self.rank, self.world, CH_GRADS_READY, int(epoch),
+                    _n.stream_ptr())
+        else:
+            epoch = grads.next_epoch(CH_GRADS_READY)
+            grads.epochs[CH_GRADS_READ] = epoch
         b1, b2 = group_cfg["betas"]
         apply = grad_out is None
         mc = grads.multicast_ptr if use_multicast else 0
@@ -133,7 +165,8 @@ class SymmGroup:
                 float(group_cfg["lr"]), float(b1), float(b2), float(group_cfg["eps"]),
                 float(group_cfg["weight_decay"]), int(step), int(adamw),
                 int(bool(group_cfg.get("bias_correction", True))), float(grad_scale), int(epoch),
-                mc if mc else None, self._ctr(0), int(apply), int(max_ctas), _n.stream_ptr())
+                mc if mc else None, self._ctr(0), int(apply), int(max_ctas or _RS_CTAS),
+                int(announced_epoch is not None), _n.stream_ptr())
         return epoch
 
     def wait_readers(self, buf: SymmBuffer, channel: int = CH_GRADS_READ, epoch: Optional[int] = None):
@@ -160,13 +193,16 @@ class SymmGroup:
         return epoch
 
     def all_gather(self, shard: SymmBuffer, part_numel: int, dst: torch.Tensor, chunk_bytes: int = 1 << 20,
-                   chunk_flags: Optional[torch.Tensor] = None, max_ctas: int = 32, barrier: bool = True):
+                   chunk_flags: Optional[torch.Tensor] = None, max_ctas: int = 32, barrier: bool = True,
+                   flag_value: int = 0):
         """``barrier=False``: pure pull, no cross-rank handshake (the shards were declared ready by an earlier
-        :meth:`barrier` and do not change until the next one)."""
+        :meth:`barrier` and do not change until the next one).  ``chunk_flags[c]`` is set to ``flag_value`` (release)
+        when chunk ``c`` of ``dst`` is complete — the arrival signal the gated GEMM polls (K2)."""
         epoch = shard.next_epoch(CH_AG_READY) if barrier else 0
         es = dst.element_size()
         _n.call("sxb_symm_all_gather", shard.bufs, shard.sigs, self.rank, self.world, int(part_numel * es),
-                dst.data_ptr(), int(chunk_bytes), _n.ptr(chunk_flags), int(epoch), int(max_ctas), _n.stream_ptr())
+                dst.data_ptr(), int(chunk_bytes), _n.ptr(chunk_flags), int(epoch), int(max_ctas), int(flag_value),
+                _n.stream_ptr())
         return epoch
 
     # ------------------------------------------------------------------------------- a2a rows

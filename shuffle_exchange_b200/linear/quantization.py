@@ -51,9 +51,8 @@ class QuantizedParameter(nn.Parameter):
         return self.data
 
     def offload(self, revert=False):
-        if getattr(self.quantizer, "q_config", None) is not None or True:
-            self.data = self.data.to("cuda" if revert else "cpu", non_blocking=True)
-            self.quantizer.to("cuda" if revert else "cpu")
+        self.data = self.data.to("cuda" if revert else "cpu", non_blocking=True)
+        self.quantizer.to("cuda" if revert else "cpu")
 
     def __getstate__(self):
         state = self.__dict__.copy()

@@ -118,12 +118,11 @@ def top1_route(logits: Tensor, capacity_factor: float, min_capacity: int, used_t
                                "min_capacity to 0 or increase your batch size.")
     # capacity selection: random token selection (RTS) or first-come order
     score = mask1.float() * (torch.rand(mask1.shape, device=logits.device) if use_rts else 1.0)
-    if use_rts or True:
-        cap_k = min(capacity, S)
-        top_idx = torch.topk(score if use_rts else mask1.float() * (S - torch.arange(S, device=logits.device).unsqueeze(1).float()) / S,
-                             k=cap_k, dim=0)[1]
-        sel = torch.zeros_like(mask1).scatter_(0, top_idx, 1)
-        mask1 = mask1 * sel
+    cap_k = min(capacity, S)
+    if not use_rts:      # first-come order: earlier tokens win
+        score = mask1.float() * (S - torch.arange(S, device=logits.device).unsqueeze(1).float()) / S
+    top_idx = torch.topk(score, k=cap_k, dim=0)[1]
+    mask1 = mask1 * torch.zeros_like(mask1).scatter_(0, top_idx, 1)
     loc = _positions_within_expert(mask1)
     slot = (loc * mask1).sum(1)
     keep = mask1.sum(1) > 0

@@ -8,11 +8,13 @@
 The reference JIT-builds one pybind module per op through ``op_builder`` (absent from its tree,
 see SURVEY.md §2.3).  Here there is a single C-ABI library per side, built with plain ``nvcc`` /
 ``g++`` in a few seconds, loaded through ``ctypes`` (``native/lib.py``) and declared in
-``include/sxb200.h``.  Objects are cached on source mtime.
+``include/sxb200.h``.  Objects are cached on a content hash of the source, every header it can include
+and the compiler flags (``<obj>.sha``), so a stale object cannot outlive a source change whatever the mtimes say.
 """
 from __future__ import annotations
 
 import concurrent.futures as cf
+import hashlib
 import os
 import shutil
 import subprocess
@@ -42,13 +44,24 @@ def _nvcc() -> str:
     raise RuntimeError("nvcc not found; cannot build libsxb200.so")
 
 
-def _stale(src: Path, obj: Path, extra_deps) -> bool:
-    if not obj.exists():
+def _digest(src: Path, extra_deps, flags) -> str:
+    h = hashlib.sha256()
+    h.update("\0".join(flags).encode())
+    for f in [src, *sorted(extra_deps)]:
+        h.update(f.name.encode() + b"\0")
+        h.update(f.read_bytes())
+    return h.hexdigest()
+
+
+def _stale(src: Path, obj: Path, extra_deps, flags) -> bool:
+    sha = obj.with_suffix(obj.suffix + ".sha")
+    if not obj.exists() or not sha.exists():
         return True
-    t = obj.stat().st_mtime
-    if src.stat().st_mtime > t:
-        return True
-    return any(d.stat().st_mtime > t for d in extra_deps)
+    return sha.read_text().strip() != _digest(src, extra_deps, flags)
+
+
+def _stamp(src: Path, obj: Path, extra_deps, flags):
+    obj.with_suffix(obj.suffix + ".sha").write_text(_digest(src, extra_deps, flags))
 
 
 def _run(cmd):
@@ -65,19 +78,23 @@ def build_cuda(verbose: bool = False, force: bool = False) -> Path:
     srcs = sorted(CSRC.glob("*.cu"))
     jobs = []
     objs = []
+    rebuilt = []
     for s in srcs:
         o = OBJ_DIR / (s.stem + ".o")
         objs.append(o)
-        if force or _stale(s, o, headers):
+        if force or _stale(s, o, headers, NVCC_FLAGS):
             cmd = [nvcc, *NVCC_FLAGS, "-I", str(ROOT / "include"), "-I", str(CSRC), "-c", str(s), "-o", str(o)]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             jobs.append(cmd)
+            rebuilt.append((s, o))
     if jobs:
         with cf.ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             for out in ex.map(_run, jobs):
                 if verbose and out:
                     print(out)
+        for s, o in rebuilt:
+            _stamp(s, o, headers, NVCC_FLAGS)
     lib = OUT_DIR / "libsxb200.so"
     if jobs or not lib.exists():
         _run([nvcc, "-shared", "-o", str(lib), *map(str, objs), "-gencode", "arch=compute_100a,code=sm_100a",
@@ -90,15 +107,18 @@ def build_host(verbose: bool = False, force: bool = False) -> Path:
     gxx = shutil.which("g++") or "g++"
     srcs = sorted((CSRC / "host").glob("*.cpp"))
     headers = list((CSRC / "host").glob("*.h")) + list((ROOT / "include").glob("*.h"))
-    jobs, objs = [], []
+    jobs, objs, rebuilt = [], [], []
     for s in srcs:
         o = OBJ_DIR / ("host_" + s.stem + ".o")
         objs.append(o)
-        if force or _stale(s, o, headers):
+        if force or _stale(s, o, headers, HOST_FLAGS):
             jobs.append([gxx, *HOST_FLAGS, "-I", str(ROOT / "include"), "-c", str(s), "-o", str(o)])
+            rebuilt.append((s, o))
     if jobs:
         with cf.ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(_run, jobs))
+        for s, o in rebuilt:
+            _stamp(s, o, headers, HOST_FLAGS)
     lib = OUT_DIR / "libsxb200_host.so"
     if srcs and (jobs or not lib.exists()):
         _run([gxx, "-shared", "-o", str(lib), *map(str, objs), "-fopenmp", "-pthread", "-ldl"])

@@ -87,6 +87,41 @@ def gemm(a: torch.Tensor, b: torch.Tensor, layout: int = GEMM_NT, out: Optional[
     return out
 
 
+# ---------------------------------------------------------------------- gradient-use accounting
+# A parameter used k times in one forward (tied embedding / LM head, a shared projection) delivers k
+# contributions through the main-grad protocol, one per use.  The sharded optimizers must not start a
+# unit's reduction before the LAST one landed, so every protocol op notes its use of the parameter in
+# forward; the optimizer compares deliveries against that count (runtime/zero/sharded_optimizer.py:
+# ``GradUseCounter``).  Uses are counted only while the window is open: it closes when backward starts
+# (recomputation inside backward replays forwards that must not count) and a new one opens after it.
+_use_window = {"gen": 0, "open": True}
+
+
+def close_use_window():
+    _use_window["open"] = False
+
+
+def open_use_window():
+    _use_window["gen"] += 1
+    _use_window["open"] = True
+
+
+def expected_uses(param) -> int:
+    """How many main-grad deliveries this backward will make for ``param`` (>= 1)."""
+    if getattr(param, "_sxb_use_gen", -1) != _use_window["gen"]:
+        return 1
+    return max(1, getattr(param, "_sxb_uses", 1))
+
+
+def _note_use(param):
+    if not _use_window["open"] or getattr(param, "_sxb_grad_ready", None) is None:
+        return
+    if getattr(param, "_sxb_use_gen", -1) != _use_window["gen"]:
+        param._sxb_use_gen = _use_window["gen"]
+        param._sxb_uses = 0
+    param._sxb_uses += 1
+
+
 def _deliver_wgrad(weight, dy2, x2):
     """dW = dy^T x, either returned or written into the parameter's main-grad view."""
     mg = getattr(weight, "_sxb_main_grad", None)
@@ -111,6 +146,7 @@ class _Linear(torch.autograd.Function):
         gemm(x2, weight, GEMM_NT, out=y.view(-1, weight.shape[0]))
         if bias is not None:
             y.add_(bias)
+        _note_use(weight)
         ctx.save_for_backward(x2, weight)
         ctx.has_bias = bias is not None
         ctx.xshape = x.shape
@@ -180,6 +216,7 @@ class _RMSNorm(torch.autograd.Function):
         _n.call("sxb_rmsnorm_fwd", x2.data_ptr(), _n.ptr(r2), weight.data_ptr(), y.data_ptr(),
                 _n.ptr(h), rstd.data_ptr(), rows, H, float(eps), _n.dtype_code(x.dtype), _n.stream_ptr())
         src = h if h is not None else x2
+        _note_use(weight)
         ctx.save_for_backward(src, weight, rstd)
         ctx.has_res = residual is not None
         ctx.shape = x.shape
@@ -467,6 +504,7 @@ class _Embedding(torch.autograd.Function):
         out = torch.empty((flat.numel(), table.shape[1]), dtype=table.dtype, device=table.device)
         _n.call("sxb_embedding_fwd", flat.data_ptr(), table.data_ptr(), out.data_ptr(), flat.numel(),
                 table.shape[1], _n.dtype_code(table.dtype), _n.stream_ptr())
+        _note_use(table)
         ctx.save_for_backward(flat, table)
         return out.view(*ids.shape, table.shape[1])
 

@@ -256,7 +256,9 @@ def _save_moe_checkpoint(self, save_dir, tag, client_state={}, exclude_frozen_pa
     if exp_dp_rank == 0 and not hasattr(self.optimizer, "groups"):
         osd = {"optimizer": self.optimizer.state_dict() if self.optimizer and not self.zero_optimization() else None}
         self.checkpoint_engine.save(osd, self._get_optimizer_ckpt_name(save_dir, tag, expp_rank))
-    if expp_rank == 0 and exp_dp_rank == 0 and self.global_rank == 0 or (self.global_rank == 0):
+    # non-expert state: one writer per model-parallel rank — the first rank of the largest expert group's
+    # (expert-parallel, expert-data-parallel) grid; its file is mp_rank_XX (reference: engine.py:3523-3545)
+    if expp_rank == 0 and exp_dp_rank == 0:
         non_expert = OrderedDict((k, v) for k, v in full_sd.items() if k not in expert_keys)
         state = _model_state_payload(self, client_state, exclude_frozen_parameters, non_expert)
         state["num_experts"] = self.num_experts
@@ -356,8 +358,9 @@ def _load_zero_checkpoint(self, load_dir, tag, load_optimizer_states=True):
         first = self.checkpoint_engine.load(files[0], map_location="cpu")["optimizer_state_dict"]
         pc = first.get("partition_count")
         saved_slice = pc[0] if isinstance(pc, (list, tuple)) else pc
-        if not (self.zero_elastic_checkpoint() or self.load_universal_checkpoint() or True):
-            raise RuntimeError("DP size changed; enable elastic_checkpoint or use a universal checkpoint")
+        # Re-partitioning to a new data-parallel size is always available here: the optimizer files carry unpadded
+        # per-group state plus ``param_offsets``.  ``elastic_checkpoint`` is therefore accepted and has no effect
+        # (the reference refuses this load unless elastic/universal: engine.py:3238-3243).
         sds = [first] + [self.checkpoint_engine.load(f, map_location="cpu")["optimizer_state_dict"]
                          for f in files[1:saved_slice]]
     opt.load_state_dict(sds, load_optimizer_states=load_optimizer_states,

@@ -128,7 +128,14 @@ class FusedZ3Comm:
             fg.attach_main_grads()
             fg.mark_grads_unwritten()
 
-    def reduce_and_step(self, fg, fuse_step: bool, accumulate: bool, grad_scale: float = 1.0):
+    def announce(self, fg) -> int:
+        """On the compute stream, right behind the unit's last wgrad: publish "my gradients of this group are
+        complete" to all peers (one-warp kernel).  The reduce stream then never holds SMs while a slower rank is
+        still computing."""
+        return self.sg.announce_grads(fg._symm_grad)
+
+    def reduce_and_step(self, fg, fuse_step: bool, accumulate: bool, grad_scale: float = 1.0,
+                        announced_epoch: Optional[int] = None):
         """K1 for one flat group.  ``fuse_step``: update master + bf16 shard in the same kernel; otherwise
         write the reduced (mean) gradient shard for a deferred step."""
         opt = self.opt
@@ -139,12 +146,13 @@ class FusedZ3Comm:
             self._shards_dirty = True
             self.sg.rs_adam(view, fg.part, fg.hp_param.data, st["exp_avg"], st["exp_avg_sq"], fg.lp_shard,
                             fg.param_group, st["step"], adamw=bool(getattr(opt.optimizer, "adam_w_mode", 1)),
-                            grad_scale=grad_scale, use_multicast=self.use_multicast)
+                            grad_scale=grad_scale, use_multicast=self.use_multicast,
+                            announced_epoch=announced_epoch)
             fg.grad_shard = None
             return True
         out = torch.empty(fg.part, dtype=fg.grad_dtype, device=fg.device)
         self.sg.rs_adam(view, fg.part, None, None, None, None, fg.param_group, 1, grad_out=out,
-                        use_multicast=self.use_multicast)
+                        use_multicast=self.use_multicast, announced_epoch=announced_epoch)
         if accumulate and fg.grad_shard is not None:
             fg.grad_shard.add_(out)
         else:

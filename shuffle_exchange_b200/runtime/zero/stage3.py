@@ -35,6 +35,7 @@ import torch.nn as nn
 
 from ...comm import comm as dist
 from ...device import get_accelerator
+from ...ops import functional as _F
 from ...utils.logging import logger
 from ...version import __version__
 from .flat_group import FlatGroup
@@ -44,10 +45,14 @@ FP32_FLAT_GROUPS = "fp32_flat_groups"
 OPTIMIZER_STATE_DICT = "optimizer_state_dict"
 
 
-# SXB_Z3_LOOKAHEAD=1: always fetch the next unit ahead of time even when the live-parameter limit is already exceeded by
-# the root unit, and skip the shard barrier for gathers inside backward.  Measured at 2 GPUs (profiles/): step 455 -> 431
-# ms under the profiler.  Off by default: the one 8-GPU run with it did not finish and could not be repeated.
-_Z3_LOOKAHEAD = os.environ.get("SXB_Z3_LOOKAHEAD", "0") == "1"
+# Look-ahead (default on; SXB_Z3_LOOKAHEAD=0 restores the strictly bounded behaviour): the unit that follows the
+# current one is always fetched ahead of time — one unit of look-ahead is what hides a gather behind compute — and
+# gathers issued inside backward skip the cross-rank shard barrier.  The skip is safe because a peer rewrites its
+# shard of unit u only in the fused step that follows the reduction of u, which cannot start before EVERY rank
+# announced its gradients of u, i.e. after every rank's gather of u (stream-ordered before its backward of u)
+# completed.  The root unit (embedding + LM head) is live for the whole iteration and is not charged against
+# ``stage3_max_live_parameters``: the limit bounds what is fetched ahead of use.
+_Z3_LOOKAHEAD = os.environ.get("SXB_Z3_LOOKAHEAD", "1") == "1"
 
 class Unit:
     """A module whose parameters are gathered / released / reduced / stepped together."""
@@ -258,6 +263,16 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
 
     def _install_ready_hooks(self, u: Unit, fg: FlatGroup):
         def on_ready(param, u=u):
+            # one call per USE of the parameter (a tied embedding / LM-head weight delivers twice): the unit is
+            # complete when every distinct parameter received all the contributions its forward uses announced
+            if u.reduced:
+                raise RuntimeError(
+                    f"ZeRO-3: a gradient contribution for a parameter of {u} arrived after the unit's reduction was "
+                    "launched (a parameter used by both main-grad ops and plain autograd ops, or a forward that "
+                    "ran outside the counted window); its gradient would be dropped")
+            param._sxb_calls = getattr(param, "_sxb_calls", 0) + 1
+            if param._sxb_calls != _F.expected_uses(param):
+                return
             u.grads_ready += 1
             if u.grads_ready >= u.n_trainable:
                 self._unit_backward_done(u)
@@ -310,7 +325,8 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             for fg in u.groups:
                 self._gather_fg(fg)
             u.available = True
-        self._live_numel += u.numel
+        if u is not self.root_unit:
+            self._live_numel += u.numel
 
     def _gather_fg(self, fg: FlatGroup):
         if self.fused is not None and getattr(fg, "_symm_shard", None) is not None:
@@ -340,7 +356,8 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         for fg in u.groups:
             fg.release_params()
         u.available = False
-        self._live_numel -= u.numel
+        if u is not self.root_unit:
+            self._live_numel -= u.numel
 
     def _prefetch_after(self, u: Unit, forward: bool):
         """Issue gathers for the units that follow ``u`` in the recorded order."""
@@ -432,6 +449,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
 
     def _pre_backward(self):
         self._in_backward = True
+        _F.close_use_window()
         if self._trace and not self._trace_complete:
             self._trace_complete = True
         for u in self.units:
@@ -441,6 +459,8 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             u.attached = False
             for fg in u.groups:
                 fg.mark_grads_unwritten()
+                for p in fg.params:
+                    p._sxb_calls = 0
             if u is self.root_unit or u.module is self.module:
                 self._attach_unit(u)       # no module-level backward hook for the root unit
 
@@ -457,6 +477,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             for fg in u.groups:
                 fg.micro_steps_accumulated += 1
         self._in_backward = False
+        _F.open_use_window()
 
     def _unit_backward_done(self, u: Unit, force: bool = False):
         if u.reduced:
@@ -465,14 +486,16 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         accumulate = any(fg.micro_steps_accumulated > 0 for fg in u.groups)
         fuse = self._is_boundary and self._fused_step_active()
         stream = self.reduce_stream
-        if stream is not None:
-            stream.wait_stream(get_accelerator().current_stream())
         if self.fused is not None:
             if not getattr(u, "attached", False):
                 self._attach_unit(u)
+            # announce on the compute stream, wait + reduce on the reduce stream
+            epochs = [self.fused.announce(fg) for fg in u.groups]
+            if stream is not None:
+                stream.wait_stream(get_accelerator().current_stream())
             with get_accelerator().stream(stream):
-                for fg in u.groups:
-                    if self.fused.reduce_and_step(fg, fuse, accumulate):
+                for fg, ep in zip(u.groups, epochs):
+                    if self.fused.reduce_and_step(fg, fuse, accumulate, announced_epoch=ep):
                         u.stepped = True
                     fg.flat_grad = None
                     fg.detach_main_grads()
@@ -486,6 +509,8 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             if not u.persistent and not force:
                 self._release(u)
             return
+        if stream is not None:
+            stream.wait_stream(get_accelerator().current_stream())
         with get_accelerator().stream(stream):
             for fg in u.groups:
                 if fg.flat_grad is None:

@@ -22,6 +22,7 @@ import torch
 
 from ...comm import comm as dist
 from ...device import get_accelerator
+from ...ops import functional as _F
 from ...utils import groups as groups_mod
 from ...utils.logging import logger
 from ...version import __version__
@@ -152,6 +153,16 @@ class DeepSpeedZeroOptimizer(ShardedOptimizerBase):
         fg.grads_ready = 0
 
         def on_ready(param, fg=fg):
+            # called once per USE of the parameter (tied embedding / LM head: twice); the group is complete when
+            # every distinct parameter received all the contributions its forward uses announced
+            if getattr(fg, "_reduced_this_micro_step", False) and self._reduce_now():
+                raise RuntimeError(
+                    f"ZeRO-{self.zero_stage}: a gradient contribution for flat group {fg.group_index} arrived after its "
+                    "reduction was launched (a parameter used by both main-grad ops and plain autograd ops, or a "
+                    "forward that ran outside the counted window); its gradient would be dropped")
+            param._sxb_calls = getattr(param, "_sxb_calls", 0) + 1
+            if param._sxb_calls != _F.expected_uses(param):
+                return
             fg.grads_ready += 1
             if fg.grads_ready == fg.n_trainable and self._reduce_now():
                 self._launch_group_reduce(fg)
@@ -187,8 +198,11 @@ class DeepSpeedZeroOptimizer(ShardedOptimizerBase):
 
     # --------------------------------------------------------------------------------- backward
     def _pre_backward(self):
+        _F.close_use_window()
         for g in self.groups:
             g.grads_ready = 0
+            for p in g.params:
+                p._sxb_calls = 0
             g.attach_main_grads()
             if self.partition_gradients or self._first_micro_step():
                 g.mark_grads_unwritten()
@@ -197,6 +211,7 @@ class DeepSpeedZeroOptimizer(ShardedOptimizerBase):
         return all(g.micro_steps_accumulated == 0 for g in self.groups)
 
     def _post_backward(self):
+        _F.open_use_window()
         for g in self.groups:
             g.micro_steps_accumulated += 1
 
@@ -414,8 +429,13 @@ class DeepSpeedZeroOptimizer(ShardedOptimizerBase):
                 hp[: piece.numel()] = piece
             else:
                 hp = self._repartition(fg, [sd[SINGLE_PARTITION_OF_FP32_GROUPS][gi] for sd in state_dict_list])
-            if load_from_fp32_weights or True:
+            if load_from_fp32_weights:
                 fg.hp_param.data.copy_(hp.to(fg.hp_param.device))
+            else:
+                # zero_optimization.load_from_fp32_weights = false: the master is rebuilt from the bit16 module
+                # weights the engine loaded just before (reference: stage_1_and_2.py _restore_from_bit16_weights)
+                # (the parameters alias the flat bit16 buffer, so its shard already holds the loaded values)
+                fg.hp_param.data.copy_(fg.lp_shard.to(fg.hp_param.device, dtype=torch.float32))
             if load_optimizer_states:
                 if same:
                     saved = (state_dict_list[mine_idx if len(state_dict_list) > 1 else 0])[BASE_OPTIMIZER_STATE][gi]

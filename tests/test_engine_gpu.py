@@ -69,3 +69,35 @@ def test_checkpoint_roundtrip_gpu(tmp_path):
     path, client = e2.load_checkpoint(str(tmp_path))
     assert path is not None and client["hello"] == 7 and e2.global_steps == 3
     assert abs(float(e2(ids, labels=ids)) - l_next) < 1e-3
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("stage", [1, 2, 3])
+def test_tied_embedding_gradients_match_fp32_oracle(stage):
+    """Llama with ``tie_word_embeddings``: the shared table receives one wgrad (LM head) and one scatter-add
+    (embedding) through the main-grad protocol; the reduced gradient must contain both."""
+    import copy
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(29600 + stage), RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    import shuffle_exchange_b200 as sxb
+    from shuffle_exchange_b200.models.llama import LlamaForCausalLM, llama_config
+    from shuffle_exchange_b200.utils.tensor_fragment import safe_get_full_grad
+    torch.manual_seed(0)
+    cfg = llama_config("llama-tiny", hidden_size=256, num_attention_heads=4, num_key_value_heads=2,
+                       tie_word_embeddings=True)
+    model = LlamaForCausalLM(cfg, device="cuda", dtype=torch.bfloat16)
+    oracle = copy.deepcopy(model).float().cpu()          # CPU branch of every op = plain PyTorch fp32
+    engine, _, _, _ = sxb.initialize(model=model, model_parameters=model.parameters(), config={
+        "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "steps_per_print": 1 << 30,
+        "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}},
+        "zero_optimization": {"stage": stage, "fused_step": False}})
+    ids = torch.randint(0, cfg.vocab_size, (2, 128), device="cuda")
+    loss = engine(ids, labels=ids)
+    engine.backward(loss)
+    got = {n: safe_get_full_grad(p).float().cpu() for n, p in engine.module.named_parameters()}
+    oracle(ids.cpu(), labels=ids.cpu()).backward()
+    for n, p in oracle.named_parameters():
+        ref = p.grad
+        err = (got[n] - ref).abs()
+        tol = 0.06 * ref.abs().max() + 0.06 * ref.abs()
+        assert bool((err <= tol).all()), (stage, n, err.max().item(), ref.abs().max().item())

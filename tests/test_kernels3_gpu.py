@@ -206,3 +206,33 @@ def test_fastgen_policy_engine_gpu_bf16(arch):
     out = eng.put([1], [ids[0, 33:]]).float().cpu()
     assert (out[0] - ref[39]).abs().max() < 0.06 * scale + 0.05
     assert out[0].argmax() == ref[39].argmax() or (ref[39].topk(2).values.diff().abs() < 0.05 * scale)
+
+
+@pytest.mark.gpu
+def test_multicast_kernels_only_for_local_kv():
+    """K/V that are not provably this GPU's own memory must select the single-CTA (non-multicast) attention kernels:
+    a range registered as foreign (what comm/symm.py does for every peer mapping), a host-pinned buffer, or an extent
+    that runs past its allocation."""
+    import ctypes
+    from shuffle_exchange_b200.native import lib as nlib
+    from shuffle_exchange_b200.comm import symm  # noqa: F401  (registers the signatures)
+    L = nlib.load()
+    B, S, Hq, Hk, D = 1, 256, 8, 2, 128
+    k = torch.zeros(B, S, Hk, D, dtype=torch.bfloat16, device="cuda")
+    v = torch.zeros_like(k)
+    st = Hk * D
+    assert L.sxb_attn_would_multicast(k.data_ptr(), v.data_ptr(), B, S, Hq, Hk, D, st, st) == 1
+    assert L.sxb_range_is_local(k.data_ptr(), k.numel() * 2) == 1
+    # extent beyond the allocation
+    assert L.sxb_range_is_local(k.data_ptr(), 1 << 40) == 0
+    # host memory
+    h = torch.zeros(1 << 16, dtype=torch.bfloat16).pin_memory()
+    assert L.sxb_range_is_local(h.data_ptr(), 1 << 16) == 0
+    # foreign registration (stands for a peer mapping): a separate allocation so the other tests keep multicast
+    big = torch.zeros(1 << 22, dtype=torch.bfloat16, device="cuda")
+    fk = big[: k.numel()].view_as(k)
+    assert L.sxb_attn_would_multicast(fk.data_ptr(), v.data_ptr(), B, S, Hq, Hk, D, st, st) == 1
+    assert L.sxb_register_foreign_range(fk.data_ptr(), fk.numel() * 2) == 0
+    assert L.sxb_attn_would_multicast(fk.data_ptr(), v.data_ptr(), B, S, Hq, Hk, D, st, st) == 0
+    assert L.sxb_attn_would_multicast(k.data_ptr(), fk.data_ptr(), B, S, Hq, Hk, D, st, st) == 0
+    test_multicast_kernels_only_for_local_kv._keep = big       # never freed: the range stays registered
