@@ -73,7 +73,12 @@ def run(args, ClockSampler, ds_config_fn):
     ckpt_mode = "per-layer (HF gradient_checkpointing)"
     if getattr(args, "ckpt_layers", "auto") == "auto":
         total = torch.cuda.get_device_properties(dev).total_memory
-        need = cfg.num_hidden_layers * int(2.3e9 * (B * S) / 8192) + 30 * 2 ** 30
+        # torch.optim.AdamW allocates exp_avg / exp_avg_sq (8 bytes per owned parameter) lazily in the FIRST step —
+        # they are not in memory_allocated() yet (omitting them let a 1-GPU run drop recomputation and then run out
+        # of memory in its second step)
+        n_params = sum(getattr(p, "ds_numel", p.numel()) for p in model.parameters())
+        lazy_adam = 8 * n_params // world
+        need = cfg.num_hidden_layers * int(2.3e9 * (B * S) / 8192) + 36 * 2 ** 30 + lazy_adam
         fits = torch.tensor([1 if total - torch.cuda.memory_allocated(dev) >= need else 0], device=dev)
         if world > 1:
             torch.distributed.all_reduce(fits, op=torch.distributed.ReduceOp.MIN)

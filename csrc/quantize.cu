@@ -711,3 +711,64 @@ SXB_API int sxb_token_move(void* full, void* part, const void* idx, int batch, i
   SXB_CHECK_LAUNCH();
   return SXB_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Row-wise e4m3 quantisation for the tcgen05 fp8 GEMM (gemm_ext.cu): one scale per row = amax / 448, values
+// stored as fp8 e4m3 in a [rows, cols] byte matrix of pitch ld_out.  (The reference's FP quantizer stores a
+// per-group fp32 scale behind every group of a flat buffer — ops/fp_quantizer/quantize.py:48-95 — a layout a
+// tensor-core operand cannot be fetched from; same number format, scales kept in a side vector.)
+namespace sxb {
+namespace quant {
+__device__ __forceinline__ uint32_t f32x4_to_e4m3x4(float a, float b, float c, float d) {
+  uint16_t lo, hi;
+  asm volatile("cvt.rn.satfinite.e4m3x2.f32 %0, %2, %1;" : "=h"(lo) : "f"(a), "f"(b));
+  asm volatile("cvt.rn.satfinite.e4m3x2.f32 %0, %2, %1;" : "=h"(hi) : "f"(c), "f"(d));
+  return (uint32_t)lo | ((uint32_t)hi << 16);
+}
+__global__ void __launch_bounds__(256)
+fp8_rowwise_quant_kernel(const __nv_bfloat16* __restrict__ in, uint8_t* __restrict__ out, float* __restrict__ scales,
+                         long long rows, int cols, long long ld_in, long long ld_out) {
+  __shared__ float red[32];
+  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+    const __nv_bfloat16* x = in + r * ld_in;
+    float amax = 0.f;
+    for (int c = threadIdx.x * 8; c < cols; c += blockDim.x * 8) {
+      const uint4 v = *reinterpret_cast<const uint4*>(x + c);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        amax = fmaxf(amax, fmaxf(fabsf(__low2float(h[i])), fabsf(__high2float(h[i]))));
+    }
+    amax = block_max(amax, red);
+    const float scale = amax > 0.f ? amax * (1.0f / 448.0f) : 1.0f;
+    const float inv = 1.0f / scale;
+    if (threadIdx.x == 0) scales[r] = scale;
+    uint8_t* o = out + r * ld_out;
+    for (int c = threadIdx.x * 8; c < cols; c += blockDim.x * 8) {
+      const uint4 v = *reinterpret_cast<const uint4*>(x + c);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+      uint2 q;
+      q.x = f32x4_to_e4m3x4(__low2float(h[0]) * inv, __high2float(h[0]) * inv, __low2float(h[1]) * inv,
+                            __high2float(h[1]) * inv);
+      q.y = f32x4_to_e4m3x4(__low2float(h[2]) * inv, __high2float(h[2]) * inv, __low2float(h[3]) * inv,
+                            __high2float(h[3]) * inv);
+      *reinterpret_cast<uint2*>(o + c) = q;
+    }
+    __syncthreads();
+  }
+}
+}  // namespace quant
+}  // namespace sxb
+
+// in: bf16 [rows, cols] (pitch ld_in elements, cols % 8 == 0, 16-byte aligned rows); out: e4m3 bytes (pitch ld_out,
+// multiple of 8); scales: fp32 [rows].  Dequantised value = e4m3 * scale.
+SXB_API int sxb_fp8_rowwise_quant(const void* in, void* out, void* scales, long long rows, int cols, long long ld_in,
+                                  long long ld_out, void* stream) {
+  if (rows <= 0) return SXB_OK;
+  if (cols <= 0 || (cols % 8) || (ld_in % 8) || (ld_out % 8)) return SXB_ERR_UNSUPPORTED;
+  const int grid = (int)(rows < 148 * 8 ? rows : 148 * 8);
+  sxb::quant::fp8_rowwise_quant_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)in, (uint8_t*)out, (float*)scales, rows, cols, ld_in, ld_out);
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}

@@ -544,7 +544,8 @@ namespace sxb {
 // Poll-loop companion of mbar_wait_to: `c_next` is a clock64 deadline owned by the caller (initialise to 0);
 // `t0` is the globaltimer value at the last progress (0 = unknown).  Cheap unless the deadline passed.
 __device__ __forceinline__ bool hang_should_abort(unsigned long long& t0, uint32_t tag, uint32_t aux,
-                                                  long long* c_next = nullptr) {
+                                                  long long* c_next = nullptr,
+                                                  unsigned long long timeout_ns = 2000000000ull) {
   static_assert(sizeof(long long) == 8, "");
   if (c_next) {
     const long long c = clock64();
@@ -555,7 +556,7 @@ __device__ __forceinline__ bool hang_should_abort(unsigned long long& t0, uint32
   if (*reinterpret_cast<volatile unsigned int*>(&g_sxb_hang[0]) != 0) return true;
   const unsigned long long now = global_ns();
   if (t0 == 0) { t0 = now; return false; }
-  if (now - t0 > 2000000000ull) { hang_record(tag, 0, aux); return true; }
+  if (now - t0 > timeout_ns) { hang_record(tag, 0, aux); return true; }
   return false;
 }
 }  // namespace sxb

@@ -76,7 +76,9 @@ __device__ __forceinline__ bool wait_all(const Peers& P, int channel, uint32_t e
     unsigned long long t0 = 0;
     long long c_next = 0;
     while ((int32_t)(ld_acquire_sys(s) - epoch) < 0) {
-      if (hang_should_abort(t0, tag, threadIdx.x, &c_next)) { ok_flag = 0; break; }
+      // cross-rank waits absorb start-up skew between processes (allocator warm-up, first-touch page faults):
+      // 30 s, not the 2 s of the on-chip pipelines — a false alarm here corrupts the step
+      if (hang_should_abort(t0, tag, threadIdx.x, &c_next, 30000000000ull)) { ok_flag = 0; break; }
     }
   }
   __syncthreads();
@@ -299,7 +301,7 @@ template <typename T>
 __global__ void __launch_bounds__(kThreads) subset_mean_kernel(SubsetMeanArgs<T> A) { subset_mean_body<T>(A); }
 template <typename T>
 __global__ void __launch_bounds__(kThreads) subset_mean_emu_kernel(const SubsetMeanArgs<T>* per_rank) {
-  if (per_rank[blockIdx.y].n >= 0) subset_mean_body<T>(per_rank[blockIdx.y]);   // n < 0: rank is not a member
+  subset_mean_body<T>(per_rank[blockIdx.y]);
 }
 
 // ------------------------------------------------------------------------------------ K2 (gather)
@@ -610,18 +612,18 @@ SXB_API int sxb_symm_subset_mean(const void* const* bufs, const void* const* sig
   SXB_CHECK_LAUNCH();
   return SXB_OK;
 }
-// K9 emulated (bf16): outs[r] may be NULL for ranks outside `members` (they take no part, as in the real launch).
+// K9 emulated (bf16).  As in the real launch EVERY rank runs the kernel, each over its own ring: members is a
+// [world][16] row-major table, n_members[r] the length of row r (row r must contain r).
 SXB_API int sxb_symm_subset_mean_emu(const void* const* bufs, const void* const* sigs, int world, const int* members,
-                                     int n_members, void* const* outs, long long n, unsigned int epoch,
+                                     const int* n_members, void* const* outs, long long n, unsigned int epoch,
                                      void* const* counters, int ctas_per_rank, void* stream) {
   if (world < 1 || world > kMaxPeers || ctas_per_rank < 1) return SXB_ERR_BAD_ARG;
-  Members M;
   int rc;
-  if ((rc = fill_members(M, members, n_members))) return rc;
   SubsetMeanArgs<__nv_bfloat16> A[kMaxPeers];
   for (int r = 0; r < world; ++r) {
     if ((rc = fill_peers(A[r].P, bufs, sigs, r, world))) return rc;
-    A[r].M = M; A[r].out = (__nv_bfloat16*)outs[r]; A[r].n = outs[r] ? n : -1; A[r].epoch = epoch;
+    if ((rc = fill_members(A[r].M, members + r * kMaxPeers, n_members[r]))) return rc;
+    A[r].out = (__nv_bfloat16*)outs[r]; A[r].n = n; A[r].epoch = epoch;
     A[r].cta_counter = (unsigned int*)counters[r];
   }
   return launch_emu((const void*)subset_mean_emu_kernel<__nv_bfloat16>, A, world, ctas_per_rank, kThreads,

@@ -22,7 +22,7 @@ from .symm import CH_A2A_FREE, CH_A2A_LANDED, CH_AG_READY, CH_AVG_READ, CH_AVG_R
 
 _n.register({
     "sxb_symm_rs_adam_emu": "ppil" "ppppp" "fffff" "iii" "f" "i" "p" "ii" "p",
-    "sxb_symm_subset_mean_emu": "ppi" "pi" "pl" "i" "p" "i" "p",
+    "sxb_symm_subset_mean_emu": "ppi" "pp" "pl" "i" "p" "i" "p",
     "sxb_symm_all_gather_emu": "ppil" "pl" "p" "iii" "p",
     "sxb_symm_a2a_rows_emu": "ppi" "pppp" "ii" "p" "i" "p",
 })
@@ -91,15 +91,21 @@ class FakePeerGroup:
                 int(adamw), int(bool(cfg.get("bias_correction", True))), float(grad_scale), int(epoch), cp,
                 int(apply), MAX_CTAS, _n.stream_ptr())
 
-    # K9: mean over a subset of ranks
-    def subset_mean(self, src: FakePeerBuffer, members: List[int], out: List[torch.Tensor], n: int) -> None:
+    # K9: every rank averages over ITS ring (``rings``: list of member lists partitioning the ranks)
+    def subset_mean(self, src: FakePeerBuffer, rings: List[List[int]], out: List[torch.Tensor], n: int) -> None:
         epoch = src.next_epoch(CH_AVG_READY)
         src.epochs[CH_AVG_READ] = epoch
-        arr = (ctypes.c_int * len(members))(*members)
-        ok, op = _ptr_array([out[r] if r in members else None for r in range(self.world)])
+        ring_of = {r: ring for ring in rings for r in ring}
+        table = (ctypes.c_int * (self.world * 16))()
+        counts = (ctypes.c_int * self.world)()
+        for r in range(self.world):
+            counts[r] = len(ring_of[r])
+            for j, mbr in enumerate(ring_of[r]):
+                table[r * 16 + j] = mbr
+        ok, op = _ptr_array(out)
         ck, cp = self._ctrs(1)
-        _n.call("sxb_symm_subset_mean_emu", src.bufs, src.sigs, self.world, ctypes.cast(arr, ctypes.c_void_p),
-                len(members), op, int(n), int(epoch), cp, MAX_CTAS, _n.stream_ptr())
+        _n.call("sxb_symm_subset_mean_emu", src.bufs, src.sigs, self.world, ctypes.cast(table, ctypes.c_void_p),
+                ctypes.cast(counts, ctypes.c_void_p), op, int(n), int(epoch), cp, MAX_CTAS, _n.stream_ptr())
 
     # K2: all-gather of ``part_numel`` elements per rank (+ per-chunk arrival flags)
     def all_gather(self, shard: FakePeerBuffer, part_numel: int, dst: List[torch.Tensor], chunk_bytes: int = 1 << 16,
@@ -125,3 +131,58 @@ class FakePeerGroup:
         _n.call("sxb_symm_a2a_rows_emu", dst.bufs, dst.sigs, W, sp, ctypes.cast(so, ctypes.c_void_p),
                 ctypes.cast(ro, ctypes.c_void_p), ctypes.cast(ct, ctypes.c_void_p), int(row_bytes), int(epoch), cp,
                 MAX_CTAS, _n.stream_ptr())
+
+
+# ------------------------------------------------------------------------------------------------
+# Expert-parallel exchange (csrc/moe_ep.cu) with all logical ranks on one GPU.
+_n.register({
+    "sxb_moe_ep_plan_emu": "ppi" "pp" "iii" "iii" "p",
+    "sxb_moe_ep_push_emu": "ppi" "pppp" "ppp" "iiiii" "i" "i" "pi" "p",
+    "sxb_moe_ep_pull_emu": "ppi" "ppp" "ppp" "iiiii" "i" "i" "pi" "p",
+})
+
+
+class FakeEP:
+    """``world`` logical expert-parallel ranks: per-rank receive / return / count buffers and tables, and the three
+    kernels of ``moe/fused_ep.py`` launched for all ranks at once."""
+
+    def __init__(self, world: int, num_experts: int, hidden: int, cap_rows: int, device=None):
+        dev = device or torch.device("cuda", torch.cuda.current_device())
+        self.world, self.E, self.L, self.H, self.cap = world, num_experts, num_experts // world, hidden, cap_rows
+        self.recv = FakePeerBuffer(world, cap_rows * hidden, torch.bfloat16, dev)
+        self.ret = FakePeerBuffer(world, cap_rows * hidden, torch.bfloat16, dev)
+        self.counts = FakePeerBuffer(world, world * num_experts, torch.int32, dev)
+        self.ret.pads = [torch.zeros(32 * 16, dtype=torch.int32, device=dev) for _ in range(world)]
+        self.ret._sigs = (ctypes.c_void_p * world)(*[p.data_ptr() for p in self.ret.pads])
+        self.tables = [torch.zeros(num_experts + 2 * self.L + 2, dtype=torch.int32, device=dev) for _ in range(world)]
+        self.counters = [torch.zeros(16, dtype=torch.int32, device=dev) for _ in range(world)]
+        self.epoch = 0
+        self.pull_epoch = 0
+
+    def _ctrs(self, i):
+        arr = (ctypes.c_void_p * self.world)(*[c.data_ptr() + 4 * i for c in self.counters])
+        return arr, ctypes.cast(arr, ctypes.c_void_p)
+
+    def plan(self, counts: Optional[List[torch.Tensor]]):
+        self.epoch += 1
+        ck, cp = _ptr_array(counts if counts is not None else [None] * self.world)
+        tk, tp = _ptr_array(self.tables)
+        _n.call("sxb_moe_ep_plan_emu", self.counts.bufs, self.ret.sigs, self.world, cp, tp, self.E, self.L, self.cap,
+                self.epoch, self.pull_epoch, int(counts is not None), _n.stream_ptr())
+
+    def push(self, x, assign, offsets, T, K, weights=None, pulled=None, d_scores=None):
+        keep = [_ptr_array(v) if v is not None else (None, None) for v in (x, weights, pulled, d_scores, assign, offsets,
+                                                                             self.tables)]
+        ck, cp = self._ctrs(3)
+        _n.call("sxb_moe_ep_push_emu", self.recv.bufs, self.ret.sigs, self.world, keep[0][1], keep[1][1], keep[2][1],
+                keep[3][1], keep[4][1], keep[5][1], keep[6][1], T, K, self.H, self.E, self.L, self.cap, self.epoch, cp,
+                MAX_CTAS, _n.stream_ptr())
+
+    def pull(self, out, assign, offsets, T, K, weights=None, keep_rows=None):
+        keep = [_ptr_array(v) if v is not None else (None, None) for v in (out, weights, keep_rows, assign, offsets,
+                                                                             self.tables)]
+        ck, cp = self._ctrs(4)
+        _n.call("sxb_moe_ep_pull_emu", self.ret.bufs, self.ret.sigs, self.world, keep[0][1], keep[1][1], keep[2][1],
+                keep[3][1], keep[4][1], keep[5][1], T, K, self.H, self.E, self.L, self.cap, self.epoch, cp, MAX_CTAS,
+                _n.stream_ptr())
+        self.pull_epoch = self.epoch

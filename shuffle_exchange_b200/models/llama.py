@@ -93,6 +93,10 @@ def llama_config(name: str, **overrides) -> LlamaConfig:
 
 
 class LlamaDecoderLayer(nn.Module):
+    # every matrix parameter of this block is consumed through ops.functional.linear only: ZeRO-3 may hand them to
+    # the GEMMs while their all-gather is still in flight (gated B operand, runtime/zero/stage3.py: K2)
+    _sxb_linear_only_weights = True
+
     def __init__(self, cfg: LlamaConfig, layer_idx: int, device=None, dtype=None):
         super().__init__()
         kw = dict(device=device, dtype=dtype)

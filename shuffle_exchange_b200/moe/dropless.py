@@ -47,6 +47,23 @@ class _AllToAllV(torch.autograd.Function):
         return None, out, None, None
 
 
+class _RouterLogits(torch.autograd.Function):
+    """fp32 router logits from bf16 activations / gate weights: tcgen05 GEMM with an fp32 epilogue, fp32 gradients in."""
+
+    @staticmethod
+    def forward(ctx, x, wg):
+        ctx.save_for_backward(x, wg)
+        return F.gemm(x, wg, F.GEMM_NT, out_dtype=torch.float32)
+
+    @staticmethod
+    def backward(ctx, dl):
+        x, wg = ctx.saved_tensors
+        dlb = dl.to(torch.bfloat16)
+        dx = F.gemm(dlb, wg, F.GEMM_NN) if ctx.needs_input_grad[0] else None
+        dw = F.gemm(dlb, x, F.GEMM_TN, out_dtype=wg.dtype) if ctx.needs_input_grad[1] else None
+        return dx, dw
+
+
 class SwiGLUExpert(nn.Module):
     def __init__(self, hidden: int, intermediate: int, device=None, dtype=None):
         super().__init__()
@@ -64,7 +81,8 @@ class SwiGLUExpert(nn.Module):
 
 class DroplessMoE(MoE):
     def __init__(self, hidden_size: int, intermediate_size: int, num_experts: int, ep_size: int = 1, k: int = 2,
-                 aux_loss_coef: float = 0.0, device=None, dtype=None):
+                 aux_loss_coef: float = 0.0, device=None, dtype=None, fused_exchange: Optional[bool] = None,
+                 fp8_experts: bool = False, ep_capacity_factor: float = 1.5):
         nn.Module.__init__(self)
         assert num_experts % ep_size == 0, f"Number of experts ({num_experts}) should be divisible by expert parallel size ({ep_size})"
         self.hidden_size, self.num_experts, self.ep_size, self.k = hidden_size, num_experts, ep_size, k
@@ -73,6 +91,12 @@ class DroplessMoE(MoE):
         self.use_residual = False
         self.enable_expert_tensor_parallelism = False
         self.aux_loss_coef = aux_loss_coef
+        # fused_exchange: None = use the symmetric-memory dispatch/combine + grouped GEMM whenever it is available
+        # (CUDA bf16; NCCL group with symmetric memory, or a single rank); False = NCCL all_to_all_single path
+        self.fused_exchange = fused_exchange
+        self.fp8_experts = fp8_experts
+        self.ep_capacity_factor = ep_capacity_factor
+        self._fused_ep = None
         self.wg = nn.Parameter(torch.empty(num_experts, hidden_size, device=device, dtype=dtype))
         self.experts = nn.ModuleList([SwiGLUExpert(hidden_size, intermediate_size, device, dtype)
                                       for _ in range(self.num_local_experts)])
@@ -110,12 +134,55 @@ class DroplessMoE(MoE):
             return pieces[0]                   # one local expert (EP = number of experts): no concatenation copy
         return torch.cat(pieces) if pieces else out
 
+    # ------------------------------------------------------------------------------ fused path
+    def _fused_available(self, x) -> bool:
+        if self.fused_exchange is False or not x.is_cuda or x.dtype != torch.bfloat16:
+            return False
+        import os
+        if os.environ.get("SXB_MOE_FUSED", "1") == "0":
+            return False
+        ep = self.ep_size if (self.ep_group is not None and self.ep_size > 1) else 1
+        if ep == 1:
+            return True
+        from ..comm import symm
+        return symm.available(self.ep_group)
+
+    def _stacked(self, name: str):
+        """[L, N, K] weights of the local experts; for one local expert the parameter itself (main-grad protocol
+        stays attached), otherwise a stacked copy that autograd un-stacks."""
+        ws = [getattr(e, name) for e in self.experts]
+        return ws[0] if len(ws) == 1 else torch.stack(ws)
+
+    def _forward_fused(self, x, scores, assign, offsets, counts):
+        """K4/K5: device-side count exchange, fused permute+dispatch, grouped expert GEMMs (optionally fp8 forward),
+        fused combine+un-permute — no host synchronisation anywhere (moe/fused_ep.py)."""
+        from . import fused_ep
+        from ..ops.gemm_ext import grouped_linear
+        ep = self.ep_size if (self.ep_group is not None and self.ep_size > 1) else 1
+        fe = fused_ep.FusedEP.get(self.ep_group if ep > 1 else None, self.hidden_size, self.num_experts, x.shape[0],
+                                  self.k, self.ep_capacity_factor)
+        self._fused_ep = fe
+        plan = fused_ep.make_plan(fe, counts, assign, offsets)
+        rows = fused_ep.dispatch(x, fe, plan)
+        h = grouped_linear(rows, self._stacked("w_gate_up"), plan.group_offsets, self.fp8_experts)
+        a = F.swiglu(h)
+        c = grouped_linear(a, self._stacked("w_down"), plan.group_offsets, self.fp8_experts, out=fe.ret_rows)
+        return fused_ep.combine(c, scores.to(torch.float32), fe, plan)
+
+    def check_overflow(self):
+        if self._fused_ep is not None:
+            self._fused_ep.check_overflow()
+
     def forward(self, hidden_states: torch.Tensor, used_token: Optional[torch.Tensor] = None):
         shape = hidden_states.shape
         x = hidden_states.reshape(-1, shape[-1])
         T = x.shape[0]
-        # router: [T, H] x [E, H]^T with E << 128 — a plain library GEMM (cuBLAS); not worth a tensor-core tile
-        logits = torch.nn.functional.linear(x, self.wg)
+        # router: [T, H] x [E, H]^T; fp32 logits out of the tcgen05 GEMM on CUDA (the reference gates in fp32,
+        # moe/sharded_moe.py:500-531)
+        if x.is_cuda and x.dtype == torch.bfloat16 and self.wg.dtype == torch.bfloat16 and shape[-1] % 8 == 0:
+            logits = _RouterLogits.apply(x.contiguous(), self.wg)
+        else:
+            logits = torch.nn.functional.linear(x, self.wg)
         scores, assign, offsets, counts = moe_ops.top_k_gating(logits.detach(), self.k, renormalize=True)
         # the scores must carry gradient to the router: recompute them differentiably from the logits
         probs = torch.softmax(logits.float(), dim=-1)
@@ -125,6 +192,9 @@ class DroplessMoE(MoE):
         if self.aux_loss_coef > 0.0 or self.training:
             frac = counts.float() / max(1, T * self.k)
             self.l_aux = self.num_experts * torch.sum(frac * probs.mean(dim=0))
+        if self._fused_available(x):
+            y = self._forward_fused(x, scores, assign, offsets, counts)
+            return y.reshape(shape), self.l_aux, self.exp_counts
         moe_in, cumsum, slots = moe_ops.moe_scatter(x, assign, offsets, counts)
         ep = self.ep_size if (self.ep_group is not None and self.ep_size > 1) else 1
         if ep == 1:

@@ -143,7 +143,13 @@ class _Linear(torch.autograd.Function):
         # allocate with the final shape so the returned tensor is not a view (in-place consumers
         # such as RoPE may then modify it)
         y = torch.empty((*x.shape[:-1], weight.shape[0]), dtype=x.dtype, device=x.device)
-        gemm(x2, weight, GEMM_NT, out=y.view(-1, weight.shape[0]))
+        gate = getattr(weight, "_sxb_gate", None)
+        if gate is not None:
+            # K2: the weight is still being gathered; the kernel waits for the tiles it needs (ops/gemm_ext.py)
+            from .gemm_ext import gemm_gated
+            gemm_gated(x2, weight, GEMM_NT, gate, out=y.view(-1, weight.shape[0]))
+        else:
+            gemm(x2, weight, GEMM_NT, out=y.view(-1, weight.shape[0]))
         if bias is not None:
             y.add_(bias)
         _note_use(weight)
@@ -160,7 +166,12 @@ class _Linear(torch.autograd.Function):
             dy2 = dy2.contiguous()
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            dx = gemm(dy2, weight, GEMM_NN).view(ctx.xshape)
+            gate = getattr(weight, "_sxb_gate", None)
+            if gate is not None:
+                from .gemm_ext import gemm_gated
+                dx = gemm_gated(dy2, weight, GEMM_NN, gate).view(ctx.xshape)
+            else:
+                dx = gemm(dy2, weight, GEMM_NN).view(ctx.xshape)
         if ctx.needs_input_grad[1]:
             dw = _deliver_wgrad(weight, dy2, x2)
         if ctx.has_bias and ctx.needs_input_grad[2]:

@@ -134,6 +134,8 @@ class FlatGroup:
         self.flat_lp = None
         for p in self.params:
             p.data = torch.empty(0, dtype=self.lp_dtype, device=self.device)
+            if getattr(p, "_sxb_gate", None) is not None:
+                p._sxb_gate = None
 
     def refresh_full_from_shard(self, async_op: bool = False):
         """Post-step parameter refresh for ZeRO-1/2: in-place all-gather of the updated shards."""

@@ -70,20 +70,36 @@ class FusedZ3Comm:
             fg.lp_shard = view.tensor
             fg._symm_shard = view
             off += fg.part
-        # ---- rotating gradient arenas sized for the largest unit ----------------------------------------
-        # Unit i writes its gradients into arena i % N and may only start once EVERY peer has finished reducing
-        # the arena's previous occupant (unit i - N).  With N = 2 that couples the compute streams of all ranks
-        # one unit apart (measured: 98 ms of exposed waiting per step at 8 GPUs); N = 4 leaves three units of slack.
-        biggest = max(sum(fg.total for fg in u.groups) for u in optimizer.units)
-        self.n_arenas = 4 if len(optimizer.units) > 4 else 2
+        # ---- gradient arenas ---------------------------------------------------------------------------
+        # Units whose gradients stay open for the WHOLE backward (the root unit: LM-head wgrad first, embedding
+        # scatter-add last) own a dedicated arena; every other unit takes the next of N rotating arenas sized for
+        # the largest of them.  (A long-lived unit must never share a rotating arena: the units that cycle through
+        # it would zero and overwrite its early gradients, and its late gradients would race with their reduction.)
+        # Unit i of the rotation may only start once EVERY peer has finished reducing the arena's previous occupant
+        # (unit i - N).  With N = 2 that couples the compute streams of all ranks one unit apart (measured: 98 ms of
+        # exposed waiting per step at 8 GPUs); N = 4 leaves three units of slack.
+        long_lived = [u for u in optimizer.units if self._is_long_lived(u)]
+        rotating = [u for u in optimizer.units if not self._is_long_lived(u)]
+        self.pinned_arenas = {u.index: symm.SymmBuffer(sum(fg.total for fg in u.groups), dtype, group)
+                              for u in long_lived}
+        biggest = max((sum(fg.total for fg in u.groups) for u in rotating), default=0)
+        self.n_arenas = (4 if len(rotating) > 4 else 2) if rotating else 0
         self.grad_arenas = [symm.SymmBuffer(biggest, dtype, group) for _ in range(self.n_arenas)]
         self._slot = 0
+        self._gate_seq = 0
         self._shards_dirty = True        # a step rewrote shards since the last cross-rank barrier
         import os
         self.gather_mode = os.environ.get("SXB_Z3_GATHER", "ce")   # "ce" (copy engines) | "sm" (pull kernel)
-        self.use_multicast = bool(self.grad_arenas[0].multicast_ptr)
+        any_arena = (self.grad_arenas + list(self.pinned_arenas.values()))[0]
+        self.use_multicast = bool(any_arena.multicast_ptr)
+        pinned_mib = sum(b.tensor.numel() for b in self.pinned_arenas.values()) * 2 / 2 ** 20
         logger.info(f"[rank {self.rank}] ZeRO-3 fused collectives: shard arena {total_part * 2 / 2**20:.0f} MiB, "
-                    f"{self.n_arenas} x {biggest * 2 / 2**20:.0f} MiB gradient arenas, NVLS multicast={self.use_multicast}")
+                    f"{self.n_arenas} x {biggest * 2 / 2**20:.0f} MiB rotating + {pinned_mib:.0f} MiB dedicated gradient "
+                    f"arenas, NVLS multicast={self.use_multicast}")
+
+    def _is_long_lived(self, u) -> bool:
+        """Gradients of this unit are attached at the start of backward and reduced at its end."""
+        return u is self.opt.root_unit or u.module is self.opt.module
 
     # ----------------------------------------------------------------------------------- params
     def shards_ready_barrier(self):
@@ -95,28 +111,78 @@ class FusedZ3Comm:
             self.sg.barrier(self.shards)
             self._shards_dirty = False
 
-    def gather(self, fg):
-        """Full flat buffer of ``fg`` from the peers' shards (kernel-driven, on the current stream)."""
+    def gather(self, fg, gated: bool = False):
+        """Full flat buffer of ``fg`` from the peers' shards (on the current stream).
+
+        ``gated`` (K2): every piece of the gather publishes an arrival flag behind itself and the unit's matrix
+        parameters carry a :class:`~...ops.gemm_ext.Gate`; the GEMMs that consume them (``ops.functional.linear``,
+        forward and dgrad) wait for the weight tiles they need INSIDE the kernel, so the compute stream does not
+        wait for the gather as a whole.  The few non-matrix parameters (norm weights) are fetched first; the event
+        returned for them is the only thing the compute stream waits on."""
         flat = fg.allocate_full()
+        small_event = None
+        if gated:
+            from ...ops.gemm_ext import Gate, stream_write_u32
+            self._gate_seq += 1
+            seq = self._gate_seq
+            if self.gather_mode == "ce":
+                chunk_bytes, nflags = fg.part * flat.element_size(), self.world
+            else:
+                chunk_bytes = 1 << 20
+                nflags = (fg.total * flat.element_size() + chunk_bytes - 1) // chunk_bytes
+            flags = getattr(fg, "_gate_flags", None)
+            if flags is None or flags.numel() != nflags:
+                flags = fg._gate_flags = torch.zeros(nflags, dtype=torch.int32, device=flat.device)
+            view = fg._symm_shard
+            # non-matrix parameters first: tiny copies out of whichever shards hold them
+            for i, p in enumerate(fg.params):
+                if len(fg.shapes[i]) >= 2:
+                    continue
+                lo, hi = fg.offsets[i], fg.offsets[i] + fg.numels[i]
+                while lo < hi:
+                    r = lo // fg.part
+                    end = min(hi, (r + 1) * fg.part)
+                    src = self.shards.peer_tensor(r)[view.offset + lo - r * fg.part: view.offset + end - r * fg.part]
+                    flat[lo:end].copy_(src, non_blocking=True)
+                    lo = end
+            small_event = torch.cuda.Event()
+            small_event.record()
         if self.gather_mode == "ce":
             # copy-engine pull: world-1 peer-to-peer DMA copies + one local copy; leaves every SM to the GEMMs that
             # run concurrently on the compute stream (the SM pull kernel below costs them issue slots and L2)
             view = fg._symm_shard
             for i in range(self.world):
-                r = (self.rank + 1 + i) % self.world          # start with the next rank: spreads load over links
+                r = (self.rank + i) % self.world if gated else (self.rank + 1 + i) % self.world
                 src = self.shards.peer_tensor(r)[view.offset: view.offset + fg.part]
                 flat[r * fg.part: (r + 1) * fg.part].copy_(src, non_blocking=True)
+                if gated:
+                    stream_write_u32(flags, r, seq)      # front-end write behind the copy: no SM involved
         else:
-            self.sg.all_gather(fg._symm_shard, fg.part, flat, chunk_bytes=1 << 20, chunk_flags=None, max_ctas=48,
-                               barrier=False)
+            self.sg.all_gather(fg._symm_shard, fg.part, flat, chunk_bytes=1 << 20,
+                               chunk_flags=flags if gated else None, max_ctas=48, barrier=False,
+                               flag_value=seq if gated else 0)
         fg._bind_params()
+        if gated:
+            gate = Gate(flags, seq, chunk_bytes, flat.data_ptr())
+            for i, p in enumerate(fg.params):
+                p._sxb_gate = gate if len(fg.shapes[i]) >= 2 else None
+        return small_event
 
     # ------------------------------------------------------------------------------------ grads
+    def arena_key(self, unit):
+        """Which arena ``attach_unit_grads(unit)`` will use next: ('pin', unit index) or ('rot', slot)."""
+        if unit.index in self.pinned_arenas:
+            return ("pin", unit.index)
+        return ("rot", self._slot)
+
     def attach_unit_grads(self, unit):
-        """Give the unit a zeroed slice of the next gradient arena (after every peer finished reading
-        that arena's previous occupant) and point the parameters' main-grad views into it."""
-        arena = self.grad_arenas[self._slot]
-        self._slot = (self._slot + 1) % self.n_arenas
+        """Give the unit a zeroed slice of its gradient arena (after every peer finished reading the arena's
+        previous occupant) and point the parameters' main-grad views into it."""
+        if unit.index in self.pinned_arenas:
+            arena = self.pinned_arenas[unit.index]
+        else:
+            arena = self.grad_arenas[self._slot]
+            self._slot = (self._slot + 1) % self.n_arenas
         self.sg.wait_readers(arena, symm.CH_GRADS_READ)
         off = 0
         for fg in unit.groups:

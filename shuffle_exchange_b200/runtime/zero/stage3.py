@@ -53,6 +53,7 @@ OPTIMIZER_STATE_DICT = "optimizer_state_dict"
 # completed.  The root unit (embedding + LM head) is live for the whole iteration and is not charged against
 # ``stage3_max_live_parameters``: the limit bounds what is fetched ahead of use.
 _Z3_LOOKAHEAD = os.environ.get("SXB_Z3_LOOKAHEAD", "1") == "1"
+_Z3_GATED = os.environ.get("SXB_Z3_GATED", "1") == "1"
 
 class Unit:
     """A module whose parameters are gathered / released / reduced / stepped together."""
@@ -313,46 +314,74 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                 self.fused.shards_ready_barrier()
             if side is not get_accelerator().current_stream() and not async_on_side_stream:
                 get_accelerator().current_stream().wait_stream(side)
-        if async_on_side_stream and self.allgather_stream is not None:
+        gated = self._unit_is_gated(u)
+        if (async_on_side_stream or gated) and self.allgather_stream is not None:
             self.allgather_stream.wait_stream(get_accelerator().current_stream())
             with get_accelerator().stream(self.allgather_stream):
-                for fg in u.groups:
-                    self._gather_fg(fg)
+                small = [self._gather_fg(fg, gated) for fg in u.groups]
                 ev = get_accelerator().Event()
                 ev.record(self.allgather_stream)
             u.fetch_event = ev
+            # gated units: the compute stream only waits for the non-matrix parameters; the GEMMs gate themselves
+            u.small_events = [e for e in small if e is not None] if gated else None
         else:
             for fg in u.groups:
-                self._gather_fg(fg)
+                self._gather_fg(fg, False)
             u.available = True
         if u is not self.root_unit:
             self._live_numel += u.numel
 
-    def _gather_fg(self, fg: FlatGroup):
-        if self.fused is not None and getattr(fg, "_symm_shard", None) is not None:
-            self.fused.gather(fg)
-        else:
-            fg.gather_params()
+    def _unit_is_gated(self, u: Unit) -> bool:
+        """K2 applies to units whose module declares that all of its matrix parameters are consumed through
+        ``ops.functional.linear`` (``_sxb_linear_only_weights``), on the fused copy/pull gather.  SXB_Z3_GATED=0
+        turns it off."""
+        return (_Z3_GATED and self.fused is not None and self.allgather_stream is not None and u.module is not None
+                and getattr(u.module, "_sxb_linear_only_weights", False))
 
-    def _wait_unit(self, u: Unit):
+    def _gather_fg(self, fg: FlatGroup, gated: bool = False):
+        if self.fused is not None and getattr(fg, "_symm_shard", None) is not None:
+            return self.fused.gather(fg, gated)
+        fg.gather_params()
+        return None
+
+    def _wait_unit(self, u: Unit, full: bool = True):
+        """``full=False`` (module hooks of a gated unit): wait only for the non-matrix parameters; the completion
+        event of the whole gather is kept in ``u.full_event`` and honoured before the buffer is released or handed
+        to anything but a gated GEMM."""
+        cur = get_accelerator().current_stream()
         if u.fetch_event is not None:
-            get_accelerator().current_stream().wait_event(u.fetch_event)
+            small = getattr(u, "small_events", None)
+            if small is not None and not full:
+                for e in small:
+                    cur.wait_event(e)
+                u.full_event = u.fetch_event
+            else:
+                cur.wait_event(u.fetch_event)
+                u.full_event = None
             for fg in u.groups:
                 if fg.flat_lp is not None:
-                    fg.flat_lp.record_stream(get_accelerator().current_stream())
+                    fg.flat_lp.record_stream(cur)
             u.fetch_event = None
+            u.small_events = None
             u.available = True
+        elif full and getattr(u, "full_event", None) is not None:
+            cur.wait_event(u.full_event)
+            u.full_event = None
 
-    def _fetch(self, u: Unit):
+    def _fetch(self, u: Unit, full: bool = True):
         if u.persistent:
             return
         if not u.available and u.fetch_event is None:
             self._gather_unit(u, async_on_side_stream=False)
-        self._wait_unit(u)
+        self._wait_unit(u, full)
 
     def _release(self, u: Unit):
         if u.persistent or not u.available:
             return
+        if getattr(u, "full_event", None) is not None:
+            # every copy of the gather must have landed before the buffer goes back to the allocator
+            get_accelerator().current_stream().wait_event(u.full_event)
+            u.full_event = None
         for fg in u.groups:
             fg.release_params()
         u.available = False
@@ -410,7 +439,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
     def _pre_forward(self, u: Unit):
         if not self._trace_complete and not self._in_backward:
             self._trace.append(u.index)
-        self._fetch(u)
+        self._fetch(u, full=False)
         self._prefetch_after(u, forward=not self._in_backward)
 
     def _post_forward(self, u: Unit):
@@ -419,7 +448,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         self._release(u)
 
     def _pre_backward_unit(self, u: Unit):
-        self._fetch(u)
+        self._fetch(u, full=False)
         self._attach_unit(u)
         self._prefetch_after(u, forward=False)
 
@@ -430,10 +459,12 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             return
         u.attached = True
         if self.fused is not None:
-            ev = getattr(self, "_arena_free_events", [None] * self.fused.n_arenas)[self.fused._slot]
+            if not hasattr(self, "_arena_free_events"):
+                self._arena_free_events = {}
+            u._arena_key = self.fused.arena_key(u)
+            ev = self._arena_free_events.get(u._arena_key)
             if ev is not None:
                 get_accelerator().current_stream().wait_event(ev)   # my own reduce of this arena's last occupant
-            u._arena_slot = self.fused._slot
             self.fused.attach_unit_grads(u)
             return
         for fg in u.groups:
@@ -501,9 +532,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                     fg.detach_main_grads()
                 ev = get_accelerator().Event()
                 ev.record(stream if stream is not None else get_accelerator().current_stream())
-            if not hasattr(self, "_arena_free_events"):
-                self._arena_free_events = [None] * self.fused.n_arenas
-            self._arena_free_events[u._arena_slot] = ev
+            self._arena_free_events[u._arena_key] = ev
             if stream is not None:
                 self._pending_reduce.append(u)
             if not u.persistent and not force:

@@ -50,17 +50,18 @@ def test_emulated_collectives_match_pytorch(world):
     torch.cuda.synchronize()
     for r in range(world):
         _close(out[r], mean[r * part:(r + 1) * part], 8e-3, 1e-6)
-    # ---- K9: subset mean over the even ranks (odd ranks take no part)
-    members = list(range(0, world, 2))
+    # ---- K9: two rings (even / odd ranks); every rank averages over its own ring, as in the shuffle method
+    rings = [list(range(0, world, 2)), list(range(1, world, 2))]
     src = FakePeerBuffer(world, part, torch.bfloat16, dev)
     for t in src.tensors:
         t.copy_(torch.randn(part, device=dev).to(torch.bfloat16))
     sm_out = [torch.empty(part, device=dev, dtype=torch.bfloat16) for _ in range(world)]
-    grp.subset_mean(src, members, sm_out, part)
+    grp.subset_mean(src, rings, sm_out, part)
     torch.cuda.synchronize()
-    sm_ref = torch.stack([src.tensors[r].float() for r in members]).mean(0)
-    for r in members:
-        _close(sm_out[r], sm_ref, 8e-3, 1e-6)
+    for ring in rings:
+        sm_ref = torch.stack([src.tensors[r].float() for r in ring]).mean(0)
+        for r in ring:
+            _close(sm_out[r], sm_ref, 8e-3, 1e-6)
     # ---- K2 gather half: exact copy + every chunk flag published
     sh = FakePeerBuffer(world, part, torch.bfloat16, dev)
     for t in sh.tensors:
