@@ -58,9 +58,15 @@ class _RouterLogits(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dl):
         x, wg = ctx.saved_tensors
+        E = wg.shape[0]
+        pad = (-E) % 8                       # the GEMM wants 16-byte rows: pad the expert dimension with zeros
         dlb = dl.to(torch.bfloat16)
-        dx = F.gemm(dlb, wg, F.GEMM_NN) if ctx.needs_input_grad[0] else None
-        dw = F.gemm(dlb, x, F.GEMM_TN, out_dtype=wg.dtype) if ctx.needs_input_grad[1] else None
+        wgp = wg
+        if pad:
+            dlb = torch.nn.functional.pad(dlb, (0, pad))
+            wgp = torch.nn.functional.pad(wg, (0, 0, 0, pad))
+        dx = F.gemm(dlb, wgp, F.GEMM_NN) if ctx.needs_input_grad[0] else None
+        dw = F.gemm(dlb, x, F.GEMM_TN, out_dtype=wg.dtype)[:E] if ctx.needs_input_grad[1] else None
         return dx, dw
 
 

@@ -2,23 +2,32 @@
 
     "nebula": {"enabled": true, "persistent_storage_path": "/foo/bar", "persistent_time_interval": 100,
                "num_of_version_in_retention": 2, "enable_nebula_load": true}
-
-``NEBULA_<KEY>`` is the JSON key and ``NEBULA_<KEY>_DEFAULT`` its default, generated from one table."""
+"""
 NEBULA = "nebula"
 
-_FIELDS = {
-    # constant stem                  json key                        default   meaning
-    "ENABLED":                      ("enabled",                      False),  # use the service at all
-    "LOAD_PATH":                    ("nebula_load_path",             None),   # tier-3 location preferred on load
-    "ENABLE_NEBULA_LOAD":           ("enable_nebula_load",           True),   # load through the service when possible
-    "PERSISTENT_STORAGE_PATH":      ("persistent_storage_path",      None),   # where versions are persisted
-    "PERSISTENT_TIME_INTERVAL":     ("persistent_time_interval",     100),    # min seconds between persisted versions
-    "NUM_OF_VERSION_IN_RETENTION":  ("num_of_version_in_retention",  2),      # versions kept
-}
-for _stem, (_key, _default) in _FIELDS.items():
-    globals()[f"NEBULA_{_stem}"] = _key
-    globals()[f"NEBULA_{_stem}_DEFAULT"] = _default
-del _stem, _key, _default
+# use the service at all
+NEBULA_ENABLED = "enabled"
+NEBULA_ENABLED_DEFAULT = False
+
+# tier-3 location preferred on load
+NEBULA_LOAD_PATH = "nebula_load_path"
+NEBULA_LOAD_PATH_DEFAULT = None
+
+# load through the service when possible
+NEBULA_ENABLE_NEBULA_LOAD = "enable_nebula_load"
+NEBULA_ENABLE_NEBULA_LOAD_DEFAULT = True
+
+# where versions are persisted
+NEBULA_PERSISTENT_STORAGE_PATH = "persistent_storage_path"
+NEBULA_PERSISTENT_STORAGE_PATH_DEFAULT = None
+
+# minimum seconds between persisted versions
+NEBULA_PERSISTENT_TIME_INTERVAL = "persistent_time_interval"
+NEBULA_PERSISTENT_TIME_INTERVAL_DEFAULT = 100
+
+# versions kept
+NEBULA_NUM_OF_VERSION_IN_RETENTION = "num_of_version_in_retention"
+NEBULA_NUM_OF_VERSION_IN_RETENTION_DEFAULT = 2
 
 # variables the service's runtime reads; the launcher forwards them to every node
 NEBULA_EXPORT_ENVS = [

@@ -87,6 +87,41 @@ def gemm(a: torch.Tensor, b: torch.Tensor, layout: int = GEMM_NT, out: Optional[
     return out
 
 
+# ------------------------------------------------------------------------- matmul front ends
+def _tc_ok(*ts) -> bool:
+    return all(t.is_cuda and t.dtype == torch.bfloat16 for t in ts)
+
+
+def matmul_nt(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """``x[..., K] @ w[N, K]^T`` — the tcgen05 GEMM for bf16 CUDA operands; PyTorch for CPU tensors (oracle / gloo
+    tests) and for dtypes the kernel does not take."""
+    if _tc_ok(x, w) and x.shape[-1] % 8 == 0:
+        x2 = x.reshape(-1, x.shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        return gemm(x2, w if w.stride(-1) == 1 else w.contiguous(), GEMM_NT).view(*x.shape[:-1], w.shape[0])
+    return torch.matmul(x, w.t())
+
+
+def matmul_nn(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """``x[..., K] @ w[K, N]`` (dgrad form)."""
+    if _tc_ok(x, w) and x.shape[-1] % 8 == 0 and w.shape[-1] % 8 == 0:
+        x2 = x.reshape(-1, x.shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        return gemm(x2, w if w.stride(-1) == 1 else w.contiguous(), GEMM_NN).view(*x.shape[:-1], w.shape[1])
+    return torch.matmul(x, w)
+
+
+def matmul_tn(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """``a[R, M]^T @ b[R, N]`` (wgrad form); leading dimensions of both are flattened into ``R``."""
+    a2, b2 = a.reshape(-1, a.shape[-1]), b.reshape(-1, b.shape[-1])
+    if _tc_ok(a2, b2) and a2.shape[1] % 8 == 0 and b2.shape[1] % 8 == 0:
+        return gemm(a2 if a2.is_contiguous() else a2.contiguous(), b2 if b2.is_contiguous() else b2.contiguous(),
+                    GEMM_TN)
+    return torch.matmul(a2.t(), b2)
+
+
 # ---------------------------------------------------------------------- gradient-use accounting
 # A parameter used k times in one forward (tied embedding / LM head, a shared projection) delivers k
 # contributions through the main-grad protocol, one per use.  The sharded optimizers must not start a

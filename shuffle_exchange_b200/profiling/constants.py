@@ -1,20 +1,30 @@
-"""Key names and defaults of the ``"flops_profiler"`` config section (reference: ``profiling/constants.py``).
-
-``FLOPS_PROFILER_<KEY>`` is the JSON key, ``FLOPS_PROFILER_<KEY>_DEFAULT`` its default; both are generated from the
-one table below so the two can never drift apart."""
+"""Key names and defaults of the ``"flops_profiler"`` config section (reference: ``profiling/constants.py``)."""
 FLOPS_PROFILER = "flops_profiler"
 
-_FIELDS = {
-    "enabled": False,              # run the profiler at `profile_step`
-    "recompute_fwd_factor": 0.0,   # extra forward FLOPs counted for activation recomputation
-    "profile_step": 1,             # global step that is profiled
-    "module_depth": -1,            # depth of the per-module table (-1: innermost)
-    "top_modules": 1,              # how many modules per depth in the aggregated table
-    "detailed": True,              # print the per-module tree
-    "output_file": None,           # None: stdout
-}
+# run the profiler at `profile_step`
+FLOPS_PROFILER_ENABLED = "enabled"
+FLOPS_PROFILER_ENABLED_DEFAULT = False
 
-for _key, _default in _FIELDS.items():
-    globals()[f"FLOPS_PROFILER_{_key.upper()}"] = _key
-    globals()[f"FLOPS_PROFILER_{_key.upper()}_DEFAULT"] = _default
-del _key, _default
+# extra forward FLOPs counted for activation recomputation
+FLOPS_PROFILER_RECOMPUTE_FWD_FACTOR = "recompute_fwd_factor"
+FLOPS_PROFILER_RECOMPUTE_FWD_FACTOR_DEFAULT = 0.0
+
+# global step that is profiled
+FLOPS_PROFILER_PROFILE_STEP = "profile_step"
+FLOPS_PROFILER_PROFILE_STEP_DEFAULT = 1
+
+# depth of the per-module table (-1: innermost)
+FLOPS_PROFILER_MODULE_DEPTH = "module_depth"
+FLOPS_PROFILER_MODULE_DEPTH_DEFAULT = -1
+
+# how many modules per depth in the aggregated table
+FLOPS_PROFILER_TOP_MODULES = "top_modules"
+FLOPS_PROFILER_TOP_MODULES_DEFAULT = 1
+
+# print the per-module tree
+FLOPS_PROFILER_DETAILED = "detailed"
+FLOPS_PROFILER_DETAILED_DEFAULT = True
+
+# None: stdout
+FLOPS_PROFILER_OUTPUT_FILE = "output_file"
+FLOPS_PROFILER_OUTPUT_FILE_DEFAULT = None

@@ -60,7 +60,11 @@ def reduce_scatter_coalesced(tensors: List[Tensor], group=None) -> List[Tensor]:
     return out
 
 
-def _local_world() -> int:
+def _local_world(groups=None) -> int:
+    """Ranks per node: what the group builder used (``utils.groups._get_local_all_to_all_group``), else the number of
+    visible devices."""
+    if groups is not None and "devices_per_node" in groups:
+        return int(groups["devices_per_node"])
     return max(1, torch.cuda.device_count()) if torch.cuda.is_available() else 1
 
 
@@ -70,7 +74,7 @@ def all_to_all_quant_reduce(tensors: List[Tensor], groups: Dict[str, object]) ->
     dequant + mean over nodes.  ``groups`` holds ``local_<node>`` and ``global_<local rank>`` process groups
     (``utils.groups._get_local_all_to_all_group``).  1-D tensors and sizes not divisible by ``2 * world`` take the
     plain reduce-scatter."""
-    local = _local_world()
+    local = _local_world(groups)
     world = dist.get_world_size()
     nodes = max(1, world // local)
     rank = dist.get_rank()
@@ -111,7 +115,7 @@ def all_to_all_loco_quant_reduce(params: List[Tensor], groups: Dict[str, object]
     buffers are reset every ``reset_T`` steps."""
     loco_param = loco_param or {"err_beta": 0.8, "reset_T": 1024}
     beta, reset_T = loco_param["err_beta"], loco_param["reset_T"]
-    local = _local_world()
+    local = _local_world(groups)
     world = dist.get_world_size()
     nodes = max(1, world // local)
     rank = dist.get_rank()

@@ -7,6 +7,7 @@ import torch
 import torch.nn as nn
 
 from ... import comm as dist
+from ...ops import functional as F
 
 
 class DominoAsyncColumnParallelLinearImpl(torch.autograd.Function):
@@ -15,20 +16,20 @@ class DominoAsyncColumnParallelLinearImpl(torch.autograd.Function):
         ctx.save_for_backward(inp, weight)
         ctx.use_bias = bias is not None
         ctx.handle_dic, ctx.h_id, ctx.group = handle_dic, h_id, group
-        out = torch.matmul(inp, weight.t())
+        out = F.matmul_nt(inp, weight)
         return out + bias if bias is not None else out
 
     @staticmethod
     def backward(ctx, grad_output):
         inp, weight = ctx.saved_tensors
-        grad_input = grad_output.matmul(weight)
+        grad_input = F.matmul_nn(grad_output, weight)
         handle = None
         if ctx.group is not None and dist.is_initialized() and dist.get_world_size(group=ctx.group) > 1:
             handle = dist.all_reduce(grad_input, group=ctx.group, async_op=True)
             if ctx.handle_dic is not None:
                 ctx.handle_dic[ctx.h_id] = handle
         g2 = grad_output.reshape(-1, grad_output.shape[-1])
-        grad_weight = g2.t().matmul(inp.reshape(-1, inp.shape[-1]))
+        grad_weight = F.matmul_tn(grad_output, inp)
         grad_bias = g2.sum(dim=0) if ctx.use_bias else None
         if handle is not None and ctx.handle_dic is None:
             handle.wait()

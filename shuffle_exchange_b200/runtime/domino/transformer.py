@@ -16,6 +16,7 @@ import torch.nn as nn
 import torch.nn.functional as TF
 
 from ... import comm as dist
+from ...ops import functional as F
 from .async_linear import DominoAsyncColumnParallelLinear
 
 
@@ -29,14 +30,36 @@ def _tp(group):
 
 
 class _AsyncReduce:
+    """In-place sum of a row-parallel partial result over the group, waited for by the consumer.  The reduction runs on
+    the detached storage: for autograd it is the identity (every rank back-propagates the same replicated loss)."""
+
     def __init__(self, t, group):
         self.t = t
-        self.h = dist.all_reduce(t, group=group, async_op=True) if _tp(group) > 1 else None
+        self.h = dist.all_reduce(t.detach(), group=group, async_op=True) if _tp(group) > 1 else None
 
     def wait(self):
         if self.h is not None:
             self.h.wait()
         return self.t
+
+
+class _WaitInputGrad(torch.autograd.Function):
+    """Identity placed in front of a column-parallel linear.  Its backward runs when autograd reaches the producer of
+    the linear's input: only there is the asynchronous all-reduce of the input gradient (issued by the linear's backward
+    and parked in ``handle_dic[key]``) waited for — the other micro-batch's backward computes in between."""
+
+    @staticmethod
+    def forward(ctx, x, handle_dic, key):
+        ctx.handle_dic, ctx.key = handle_dic, key
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        h = ctx.handle_dic.get(ctx.key)
+        if h is not None:
+            h.wait()
+            ctx.handle_dic[ctx.key] = None
+        return g, None, None
 
 
 class _RowParallel(torch.autograd.Function):
@@ -45,13 +68,12 @@ class _RowParallel(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight):
         ctx.save_for_backward(x, weight)
-        return torch.matmul(x, weight.t())
+        return F.matmul_nt(x, weight)
 
     @staticmethod
     def backward(ctx, g):
         x, w = ctx.saved_tensors
-        g2 = g.reshape(-1, g.shape[-1])
-        return g.matmul(w), g2.t().matmul(x.reshape(-1, x.shape[-1]))
+        return F.matmul_nn(g, w), F.matmul_tn(g, x)
 
 
 class DominoTransformerLayer(nn.Module):
@@ -78,9 +100,14 @@ class DominoTransformerLayer(nn.Module):
     def _attn_partial(self, x, key):
         B, S, _ = x.shape
         qkv = self.query_key_value(x, DominoUtil.HANDLE_DIC, key).view(B, S, 3, self.heads_local, self.hd)
-        q, k, v = (t.transpose(1, 2) for t in qkv.unbind(dim=2))
-        ctx = TF.scaled_dot_product_attention(q, k, v, is_causal=True, dropout_p=self.attn_p if self.training else 0.0)
-        return _RowParallel.apply(ctx.transpose(1, 2).reshape(B, S, self.heads_local * self.hd), self.dense)
+        q, k, v = qkv.unbind(dim=2)                       # [B, S, heads, hd] each
+        if self.attn_p > 0.0 and self.training:
+            # attention dropout has no fused kernel here: PyTorch attention for that configuration only
+            ctx = TF.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2), is_causal=True,
+                                                  dropout_p=self.attn_p).transpose(1, 2)
+        else:
+            ctx = F.flash_attention(q.contiguous(), k.contiguous(), v.contiguous(), causal=True)
+        return _RowParallel.apply(ctx.reshape(B, S, self.heads_local * self.hd), self.dense)
 
     def _mlp_partial(self, x, key):
         return _RowParallel.apply(TF.gelu(self.dense_h_to_4h(x, DominoUtil.HANDLE_DIC, key)), self.dense_4h_to_h)
@@ -90,18 +117,22 @@ class DominoTransformerLayer(nn.Module):
         communication."""
         B = hidden_states.shape[0]
         halves = hidden_states.chunk(2, dim=0) if B >= 2 else (hidden_states,)
-        # ---- attention: issue half 0's reduce, compute half 1 meanwhile
+        # ---- attention: issue half 0's reduce, compute half 1 meanwhile.  Both halves' inputs are wrapped BEFORE
+        # either half computes, so that in backward half 1's input-gradient all-reduce overlaps half 0's backward.
+        D = DominoUtil.HANDLE_DIC
+        ln = [_WaitInputGrad.apply(self.input_layernorm(h), D, str(i)) for i, h in enumerate(halves)]
         parts = []
-        for i, h in enumerate(halves):
-            parts.append(_AsyncReduce(self._attn_partial(self.input_layernorm(h), str(i)), self.tp_group))
+        for i, x in enumerate(ln):
+            parts.append(_AsyncReduce(self._attn_partial(x, str(i)), self.tp_group))
         attn_out = []
         for h, p in zip(halves, parts):
             o = p.wait() + self.dense_bias
             attn_out.append(h + TF.dropout(o, self.hidden_p, self.training))
         # ---- MLP, same interleave
+        ln = [_WaitInputGrad.apply(self.post_attention_layernorm(h), D, str(2 + i)) for i, h in enumerate(attn_out)]
         parts = []
-        for i, h in enumerate(attn_out):
-            parts.append(_AsyncReduce(self._mlp_partial(self.post_attention_layernorm(h), str(2 + i)), self.tp_group))
+        for i, x in enumerate(ln):
+            parts.append(_AsyncReduce(self._mlp_partial(x, str(2 + i)), self.tp_group))
         outs = []
         for h, p in zip(attn_out, parts):
             o = p.wait() + self.mlp_bias

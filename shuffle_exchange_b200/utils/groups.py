@@ -391,6 +391,7 @@ def _get_local_all_to_all_group(devices_per_node: Optional[int] = None):
             _ALL_TO_ALL_GROUP[f"global_{i}"] = dist.new_group(ranks=[i + per * j for j in range(nodes)])
     for i in range(nodes):
         _ALL_TO_ALL_GROUP[f"local_{i}"] = dist.new_group(ranks=[j + per * i for j in range(per)])
+    _ALL_TO_ALL_GROUP["devices_per_node"] = per      # read back by runtime/comm/coalesced_collectives.py
     return _ALL_TO_ALL_GROUP
 
 
