@@ -42,6 +42,9 @@ def parse():
                     help="decoder layers that recompute activations in backward: 'auto' = as few as HBM allows, "
                          "'all', or a count")
     ap.add_argument("--no-fused", action="store_true", help="NCCL baseline path for the ZeRO-3 collectives")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the secondary measurements (exposed communication, fused-path rooflines, the line at "
+                         "the reference's recompute setting)")
     return ap.parse_args()
 
 
@@ -274,6 +277,10 @@ def run_ours(args):
         ems = max_over_ranks(t0.elapsed_time(t1), dev)
         e2e = {"value": tokens_per_step * args.steps / (ems / 1e3), "unit": "tokens/s",
                "h2d_bytes_per_step": B * S * 8, "d2h_bytes_per_step": 4, "ms_per_step": ems / args.steps}
+    extras = {}
+    if not args.no_extras and not is_moe:
+        extras = secondary_measurements(args, engine, cfg, step_device, barrier_sync, max_over_ranks, dev, world, ms / args.steps,
+                                        B, S)
     hang = nlib.hang_info("gemm") or nlib.hang_info("attn")
     if rank == 0:
         flops = cfg.flops_per_token(S) * tokens_per_step / world
@@ -293,7 +300,7 @@ def run_ours(args):
                        "params": cfg.num_parameters()},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "gpu_launches_per_step": launches / max(1, args.steps),
-            "model_tflops_per_gpu": flops / (ms / args.steps / 1e3) / 1e12, "loss": loss_val,
+            "model_tflops_per_gpu": flops / (ms / args.steps / 1e3) / 1e12, "loss": loss_val, **extras,
             "peak_mem_gb": torch.cuda.max_memory_allocated() / 2 ** 30, "watchdog": hang,
         }
         print(json.dumps(out))
@@ -301,6 +308,75 @@ def run_ours(args):
         import torch.distributed as td
         td.barrier()
         td.destroy_process_group()
+
+
+def secondary_measurements(args, engine, cfg, step_device, barrier_sync, max_over_ranks, dev, world, ms_per_step, B, S):
+    """Numbers that explain the headline, taken AFTER it (they never touch the timed region above):
+
+    * ``fused_paths``: per fused compute+collective path, device time per step (CUDA events around every launch, max
+      over ranks), the bytes it moves over NVLink and the fraction of the NVLink roofline (bytes / measured peer-copy
+      bandwidth, B200_PROFILING.md: 770 GB/s per direction) that this is;
+    * ``exposed_comm_ms``: step time minus the step time with every collective served from this rank's own memory
+      (no NVLink traffic, no cross-rank waits — same kernels, same bytes through HBM), max over ranks; the model's
+      weights are garbage afterwards, so this runs last;
+    * ``at_reference_recompute``: the same metric with every layer recomputing activations — the policy the
+      reference arm (all-or-nothing Hugging Face gradient checkpointing) falls back to when HBM is short."""
+    import torch
+    out = {}
+    opt = engine.optimizer
+    fused = getattr(opt, "fused", None)
+    n = max(2, min(3, args.steps))
+
+    def timed(k):
+        barrier_sync()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(k):
+            step_device(i)
+        b.record()
+        barrier_sync()
+        return max_over_ranks(a.elapsed_time(b), dev) / k
+
+    # like-for-like recompute policy
+    if cfg.checkpoint_layers != cfg.num_hidden_layers:
+        keep = cfg.checkpoint_layers
+        cfg.checkpoint_layers = cfg.num_hidden_layers
+        step_device(0)
+        t = timed(n)
+        cfg.checkpoint_layers = keep
+        out["at_reference_recompute"] = {"activation_checkpointing": f"{cfg.num_hidden_layers} of {cfg.num_hidden_layers} layers",
+                                         "ms_per_step": t, "value": B * S * world / (t / 1e3), "unit": "tokens/s"}
+        step_device(0)
+    if fused is None:
+        out["exposed_comm_ms"] = 0.0
+        out["exposed_comm_note"] = "single rank / NCCL path: no fused collective ran"
+        return out
+    # per-path device time and NVLink roofline
+    LINK = 770e9
+    fused.timing = []
+    step_device(0)
+    per = fused.timing_summary()
+    fused.timing = None
+    paths = {}
+    for what, (cnt, t_ms, nbytes) in per.items():
+        t_max = max_over_ranks(t_ms, dev)
+        paths[what] = {"launches_per_step": cnt, "device_ms_per_step": t_max, "nvlink_bytes_per_step": nbytes,
+                       "roofline_ms": nbytes / LINK * 1e3,
+                       "roofline_fraction": (nbytes / LINK * 1e3) / t_max if t_max > 0 else None}
+    out["fused_paths"] = paths
+    out["fused_paths_note"] = ("device time of every launch of the path summed over a step (launches overlap compute "
+                               "on side streams, so this is occupancy of the path, not exposed time); roofline = bytes "
+                               "received over NVLink / 770 GB/s measured peer-copy bandwidth per direction")
+    # exposed communication
+    t_normal = timed(n)
+    fused.local_mode = True
+    step_device(0)
+    t_local = timed(n)
+    out["exposed_comm_ms"] = max(0.0, t_normal - t_local)
+    out["exposed_comm_fraction"] = max(0.0, t_normal - t_local) / t_normal
+    out["exposed_comm_note"] = (f"step {t_normal:.1f} ms vs {t_local:.1f} ms with all peer traffic served from local "
+                                "memory (max over ranks, measured after the timed region)")
+    return out
 
 
 def run_reference(args):

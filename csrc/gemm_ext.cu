@@ -144,10 +144,8 @@ __device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
 // Whole-warp wait until flags[c] reached `value` for every chunk of [c_lo, c_hi]; [known_lo, known_hi] caches
 // what this warp has already seen.  The data the flags cover was written through the generic proxy (pull kernel)
 // or by a copy engine; the proxy fence orders the following TMA (async proxy) reads after the acquire.
-__device__ __forceinline__ bool gate_wait(const XParams& p, long long c_lo, long long c_hi, long long& known_lo,
-                                          long long& known_hi) {
-  if (c_lo >= known_lo && c_hi <= known_hi) return true;
-  for (long long c = c_lo; c <= c_hi; ++c) {
+__device__ __forceinline__ bool gate_wait(const XParams& p, int c_lo, int c_hi, int& known_lo, int& known_hi) {
+  for (int c = c_lo; c <= c_hi; ++c) {
     if (c >= known_lo && c <= known_hi) continue;
     unsigned long long t0 = 0;
     long long c_next = 0;
@@ -165,6 +163,11 @@ __device__ __forceinline__ bool gate_wait(const XParams& p, long long c_lo, long
   }
   asm volatile("fence.proxy.async.global;" ::: "memory");
   return true;
+}
+// chunk index of a byte offset: 32-bit arithmetic on 256-byte units (a 64-bit division per k-block costs the producer
+// more than the k-block's MMA time: measured 2x slowdown of the gated NN GEMM)
+__device__ __forceinline__ int gate_chunk_of(long long byte_off, uint32_t chunk256) {
+  return (int)((uint32_t)(byte_off >> 8) / chunk256);
 }
 
 __device__ __forceinline__ void umma_f8_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
@@ -236,7 +239,12 @@ gemm_pair_x_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     const bool elected = elect_one();
     int stage = 0;
     uint32_t phase = 0;
-    long long known_lo = 1, known_hi = 0;
+    int known_lo = 1, known_hi = 0;
+    bool gate_on = (p.gate_flags != nullptr);
+    const uint32_t chunk256 = gate_on ? (uint32_t)(p.gate_chunk >> 8) : 1u;
+    const int c_first = gate_on ? gate_chunk_of(p.gate_base, chunk256) : 0;
+    const int c_last = gate_on ? min(gate_chunk_of(p.gate_base + (long long)p.b_rows * p.ldb_bytes - 1, chunk256),
+                                     (int)p.gate_nchunks - 1) : 0;
     Sched<BKE> sched(p);
     Tile ti;
     for (int t = pair_id; sched.get(t, ti); t += num_pairs) {
@@ -245,17 +253,25 @@ gemm_pair_x_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       const int b_goff = (p.group_mode == kRaggedM) ? ti.g * p.b_group_rows : 0;
       for (int kb = 0; kb < ti.num_kb; ++kb) {
         const int k0 = kb * BKE;
-        if (p.gate_flags != nullptr && (b_mn || kb == 0)) {
+        if (gate_on && (b_mn || kb == 0)) {
           // rows of the stored B matrix this load (b_mn) or this whole tile (K-major) touches
-          long long r_lo = b_mn ? (long long)k0 : (long long)nb;
+          const long long r_lo = b_mn ? (long long)k0 : (long long)nb;
           long long r_hi = b_mn ? r_lo + BKE : r_lo + 128;
           if (r_hi > p.b_rows) r_hi = p.b_rows;
           if (r_hi > r_lo) {
-            const long long lo = p.gate_base + r_lo * p.ldb_bytes;
-            const long long hi = p.gate_base + r_hi * p.ldb_bytes - 1;
-            long long c_hi = hi / p.gate_chunk;
-            if (c_hi >= p.gate_nchunks) c_hi = p.gate_nchunks - 1;
-            if (!gate_wait(p, lo / p.gate_chunk, c_hi, known_lo, known_hi)) goto done;
+            const int c_lo = gate_chunk_of(p.gate_base + r_lo * p.ldb_bytes, chunk256);
+            int c_hi = min(gate_chunk_of(p.gate_base + r_hi * p.ldb_bytes - 1, chunk256), c_last);
+            if (!(c_lo >= known_lo && c_hi <= known_hi)) {
+              // not seen yet: wait for the flags of the next 16 k-blocks in one go, so the cross-proxy fence behind
+              // a successful wait is paid once per 16 loads
+              if (b_mn) {
+                long long r_far = r_lo + 16 * BKE;
+                if (r_far > p.b_rows) r_far = p.b_rows;
+                c_hi = max(c_hi, min(gate_chunk_of(p.gate_base + r_far * p.ldb_bytes - 1, chunk256), c_last));
+              }
+              if (!gate_wait(p, c_lo, c_hi, known_lo, known_hi)) goto done;
+              if (known_lo <= c_first && known_hi >= c_last) gate_on = false;   // the whole matrix has arrived
+            }
           }
         }
         const bool ok = mbar_wait_to(&empty_bar[stage], phase ^ 1, 41, kb);
@@ -540,7 +556,9 @@ SXB_API int sxb_gemm_ext(const void* A, const void* B, void* C, int M, int N, in
   if (group_mode == kRaggedM && layout == NN && (K % 64)) return SXB_ERR_UNSUPPORTED;
   if (group_mode == kPlain && (M <= 0 || N <= 0 || K <= 0)) return SXB_OK;
   if (N <= 0) return SXB_OK;
-  if (gate_flags != nullptr && (gate_chunk <= 0 || gate_nchunks <= 0 || gate_base < 0)) return SXB_ERR_BAD_ARG;
+  if (gate_flags != nullptr && (gate_chunk <= 0 || (gate_chunk & 255) || gate_nchunks <= 0 || gate_base < 0 ||
+                                ((gate_chunk * gate_nchunks) >> 8) > 0xFFFFFFFFll))
+    return SXB_ERR_BAD_ARG;   // chunks are multiples of 256 bytes; flagged buffers up to 1 TiB
   const bool tma_c = (c_dtype == kBF16) && !accumulate && alpha == 1.0f && (ldc % 8 == 0) &&
                      ((reinterpret_cast<uintptr_t>(C) & 15) == 0) &&
                      (group_mode != kRaggedK || (c_group_stride == (long long)M * ldc));

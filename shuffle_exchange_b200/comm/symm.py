@@ -146,11 +146,21 @@ class SymmGroup:
 
     def rs_adam(self, grads: SymmBuffer, part: int, hp, m, v, lp, group_cfg: dict, step: int, adamw: bool = True,
                 grad_scale: float = 1.0, grad_out: Optional[torch.Tensor] = None, use_multicast: bool = True,
-                max_ctas: int = 0, announced_epoch: Optional[int] = None):
+                max_ctas: int = 0, announced_epoch: Optional[int] = None, local_only: bool = False):
         """Reduce this rank's shard of every peer's flat bf16 gradient buffer and (unless ``grad_out`` is
         given) apply AdamW to ``hp/m/v`` writing the bf16 shard ``lp`` — one kernel, no NCCL.
         ``announced_epoch``: epoch returned by :meth:`announce_grads` (handshake split out of the kernel)."""
-        if announced_epoch is not None:
+        bufs = grads.bufs
+        if local_only:
+            # measurement aid (bench.py exposed-communication figure): every "peer" buffer is this rank's own, no
+            # handshake — the kernel does the same arithmetic and memory traffic with NVLink taken out
+            epoch = grads.next_epoch(CH_GRADS_READY)
+            use_multicast = False
+            tbl = (ctypes.c_void_p * self.world)(*([ctypes.cast(grads.bufs, ctypes.POINTER(ctypes.c_void_p))[self.rank]]
+                                                   * self.world))
+            bufs = ctypes.cast(tbl, ctypes.c_void_p)
+            announced_epoch = epoch
+        elif announced_epoch is not None:
             epoch = announced_epoch
             _n.call("sxb_symm_wait", grads.bufs, grads.sigs, self.rank, self.world, CH_GRADS_READY, int(epoch),
                     _n.stream_ptr())
@@ -160,7 +170,7 @@ class SymmGroup:
         b1, b2 = group_cfg["betas"]
         apply = grad_out is None
         mc = grads.multicast_ptr if use_multicast else 0
-        _n.call("sxb_symm_rs_adam", grads.bufs, grads.sigs, self.rank, self.world, int(part),
+        _n.call("sxb_symm_rs_adam", bufs, grads.sigs, self.rank, self.world, int(part),
                 _n.ptr(hp), _n.ptr(m), _n.ptr(v), _n.ptr(lp), _n.ptr(grad_out),
                 float(group_cfg["lr"]), float(b1), float(b2), float(group_cfg["eps"]),
                 float(group_cfg["weight_decay"]), int(step), int(adamw),

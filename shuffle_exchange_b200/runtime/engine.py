@@ -475,6 +475,7 @@ class DeepSpeedEngine(nn.Module):
                    elastic_checkpoint=zc.elastic_checkpoint, aio_config=self._config.aio_config,
                    zero_hpz_partition_size=zc.zero_hpz_partition_size, zero_quantized_weights=zc.zero_quantized_weights,
                    zero_quantized_nontrainable_weights=zc.zero_quantized_nontrainable_weights,
+                   zero_quantized_gradients=zc.zero_quantized_gradients,
                    zeropp_loco_param=zc.zeropp_loco_param, fused_step=zc.fused_step,
                    fused_collectives=zc.fused_collectives, **common)
 

@@ -37,11 +37,16 @@ def _align(n: int, a: int) -> int:
 
 _POISON_RELEASED = os.environ.get("SXB_DEBUG_POISON", "0") == "1"
 
+class _GradHolder:
+    """Carrier of ``.grad`` and the LoCo error-feedback buffers for one flat group."""
+    grad = None
+
+
 class FlatGroup:
     def __init__(self, params: List[torch.nn.Parameter], names: List[str], world: int, rank: int, process_group,
                  device: torch.device, lp_dtype: torch.dtype, grad_dtype: Optional[torch.dtype] = None,
                  group_index: int = 0, param_group: Optional[dict] = None, keep_full_params: bool = True,
-                 hp_on_cpu: bool = False, pin: bool = False, allocator=None):
+                 hp_on_cpu: bool = False, pin: bool = False, allocator=None, lp_on_cpu: bool = False):
         self.params = list(params)
         self.names = list(names)
         self.world, self.rank, self.pg = world, rank, process_group
@@ -77,6 +82,10 @@ class FlatGroup:
         self.lp_shard = self.flat_lp[rank * self.part: (rank + 1) * self.part]
         if not keep_full_params:
             self.lp_shard = self.lp_shard.clone()
+        if lp_on_cpu and not keep_full_params:
+            # offload_param = cpu: the low-precision shard lives in (pinned) host memory between uses
+            host = self.lp_shard.to("cpu")
+            self.lp_shard = host.pin_memory() if (pin and torch.cuda.is_available()) else host
         self._bind_params()
 
         # ---- fp32 master ---------------------------------------------------------------------
@@ -109,16 +118,51 @@ class FlatGroup:
                             torch.empty(self.total, dtype=self.lp_dtype, device=self.device))
         return self.flat_lp
 
-    def gather_params(self, async_op: bool = False, allocator=None):
+    # ZeRO++ / ZeRO-Infinity switches of the NCCL gather path (set by the stage-3 optimizer from the config):
+    quantized_gradients = None    # qgZ: (all-to-all groups dict, LoCo parameters or None)
+    quantized_weights = False     # qwZ: int8 group-quantised all-gather (reference partition_parameters.py:1320-1460)
+    hpz_group = None              # hpZ: secondary shards inside this sub-group serve the backward gathers (:1747-1797)
+    hpz_secondary = None
+
+    def _device_shard(self) -> torch.Tensor:
+        """This rank's low-precision shard on the compute device (``offload_param``: staged from pinned host memory)."""
+        if self.lp_shard.device == self.device:
+            return self.lp_shard
+        return self.lp_shard.to(self.device, non_blocking=True)
+
+    def gather_params(self, async_op: bool = False, allocator=None, backward: bool = False):
         """Materialise the full flat buffer from the shards and re-point the parameters."""
         if self.flat_lp is not None and self.keep_full_params:
             return None
         flat = self.allocate_full(allocator)
         handle = None
         if self.world == 1:
-            flat.copy_(self.lp_shard)
+            flat.copy_(self._device_shard())
+        elif backward and self.hpz_secondary is not None:
+            # hpZ: the backward pass re-gathers from the secondary partition kept inside the (intra-node) sub-group
+            handle = dist.all_gather_into_tensor(flat, self.hpz_secondary, group=self.hpz_group, async_op=async_op)
+        elif self.quantized_weights:
+            from ...ops.quantizer import CUDAQuantizer
+            qz = CUDAQuantizer()
+            q, s = qz.quantize(self._device_shard())
+            qa = torch.empty((self.world,) + tuple(q.shape), dtype=q.dtype, device=q.device)
+            sa = torch.empty((self.world,) + tuple(s.shape), dtype=s.dtype, device=s.device)
+            dist.all_gather_into_tensor(qa.view(-1), q.reshape(-1), group=self.pg)
+            dist.all_gather_into_tensor(sa.view(-1), s.reshape(-1), group=self.pg)
+            for r in range(self.world):
+                flat[r * self.part: (r + 1) * self.part].copy_(qz.dequantize(qa[r], sa[r], self.lp_dtype).reshape(-1))
+            # this rank's own slice stays exact
+            flat[self.rank * self.part: (self.rank + 1) * self.part].copy_(self._device_shard())
         else:
-            handle = dist.all_gather_into_tensor(flat, self.lp_shard, group=self.pg, async_op=async_op)
+            handle = dist.all_gather_into_tensor(flat, self._device_shard(), group=self.pg, async_op=async_op)
+        if self.hpz_group is not None and not backward and self.hpz_secondary is None:
+            if handle is not None:
+                handle.wait()
+                handle = None
+            k = dist.get_world_size(self.hpz_group)
+            r = dist.get_rank(self.hpz_group)
+            sec = self.total // k
+            self.hpz_secondary = flat[r * sec: (r + 1) * sec].clone()
         self._bind_params()
         return handle
 
@@ -203,6 +247,25 @@ class FlatGroup:
             return None
         if predivide != 1.0:
             self.flat_grad.div_(predivide)
+        if self.quantized_gradients is not None and average and predivide == 1.0:
+            # qgZ (ZeRO++): int4 hierarchical all-to-all instead of the reduce-scatter; with LoCo error feedback when
+            # the config carries ``zeropp_loco_param`` (reference stage3.py:1388-1417, coalesced_collectives.py:30-156)
+            from ..comm import coalesced_collectives as cc
+            groups, loco = self.quantized_gradients
+            cols = 2048 if self.total % 2048 == 0 else self.part
+            t2d = self.flat_grad.view(-1, cols)
+            if loco is not None:
+                holder = self.__dict__.setdefault("_loco_holder", _GradHolder())
+                holder.grad = t2d
+                red = cc.all_to_all_loco_quant_reduce([holder], groups, loco)[0]
+            else:
+                red = cc.all_to_all_quant_reduce([t2d], groups)[0]
+            red = red.reshape(-1).to(self.grad_dtype)
+            if accumulate_into_shard:
+                self.grad_shard.add_(red)
+            else:
+                self.grad_shard.copy_(red)
+            return None
         tmp = torch.empty_like(self.grad_shard) if accumulate_into_shard else self.grad_shard
         op = dist.ReduceOp.AVG if (average and dist.get_backend(self.pg) == "nccl" and predivide == 1.0) else dist.ReduceOp.SUM
         h = dist.reduce_scatter_tensor(tmp, self.flat_grad, op=op, group=self.pg, async_op=False)

@@ -87,6 +87,11 @@ class FusedZ3Comm:
         self.grad_arenas = [symm.SymmBuffer(biggest, dtype, group) for _ in range(self.n_arenas)]
         self._slot = 0
         self._gate_seq = 0
+        # measurement aids: local_mode serves every collective from this rank's own memory (no NVLink, no cross-rank
+        # waits; results are meaningless) so that step_time - step_time(local_mode) = exposed communication;
+        # timing collects CUDA-event pairs around every gather / reduce launch
+        self.local_mode = False
+        self.timing = None
         self._shards_dirty = True        # a step rewrote shards since the last cross-rank barrier
         import os
         self.gather_mode = os.environ.get("SXB_Z3_GATHER", "ce")   # "ce" (copy engines) | "sm" (pull kernel)
@@ -108,7 +113,8 @@ class FusedZ3Comm:
         (A peer rewrites its shard of unit u only after every rank finished the backward of u — the gradient
         reduction of u cannot complete earlier — hence no gather of this step can still be reading it.)"""
         if self._shards_dirty:
-            self.sg.barrier(self.shards)
+            if not self.local_mode:
+                self.sg.barrier(self.shards)
             self._shards_dirty = False
 
     def gather(self, fg, gated: bool = False):
@@ -121,6 +127,7 @@ class FusedZ3Comm:
         returned for them is the only thing the compute stream waits on."""
         flat = fg.allocate_full()
         small_event = None
+        t0 = self._tick()
         if gated:
             from ...ops.gemm_ext import Gate, stream_write_u32
             self._gate_seq += 1
@@ -142,7 +149,8 @@ class FusedZ3Comm:
                 while lo < hi:
                     r = lo // fg.part
                     end = min(hi, (r + 1) * fg.part)
-                    src = self.shards.peer_tensor(r)[view.offset + lo - r * fg.part: view.offset + end - r * fg.part]
+                    src = self.shards.peer_tensor(self.rank if self.local_mode else r)[
+                        view.offset + lo - r * fg.part: view.offset + end - r * fg.part]
                     flat[lo:end].copy_(src, non_blocking=True)
                     lo = end
             small_event = torch.cuda.Event()
@@ -153,7 +161,7 @@ class FusedZ3Comm:
             view = fg._symm_shard
             for i in range(self.world):
                 r = (self.rank + i) % self.world if gated else (self.rank + 1 + i) % self.world
-                src = self.shards.peer_tensor(r)[view.offset: view.offset + fg.part]
+                src = self.shards.peer_tensor(self.rank if self.local_mode else r)[view.offset: view.offset + fg.part]
                 flat[r * fg.part: (r + 1) * fg.part].copy_(src, non_blocking=True)
                 if gated:
                     stream_write_u32(flags, r, seq)      # front-end write behind the copy: no SM involved
@@ -161,6 +169,7 @@ class FusedZ3Comm:
             self.sg.all_gather(fg._symm_shard, fg.part, flat, chunk_bytes=1 << 20,
                                chunk_flags=flags if gated else None, max_ctas=48, barrier=False,
                                flag_value=seq if gated else 0)
+        self._tock("gather", t0, fg.total * flat.element_size() * (self.world - 1) // self.world)
         fg._bind_params()
         if gated:
             gate = Gate(flags, seq, chunk_bytes, flat.data_ptr())
@@ -183,7 +192,8 @@ class FusedZ3Comm:
         else:
             arena = self.grad_arenas[self._slot]
             self._slot = (self._slot + 1) % self.n_arenas
-        self.sg.wait_readers(arena, symm.CH_GRADS_READ)
+        if not self.local_mode:
+            self.sg.wait_readers(arena, symm.CH_GRADS_READ)
         off = 0
         for fg in unit.groups:
             view = SymmView(arena, off, fg.total)
@@ -198,7 +208,31 @@ class FusedZ3Comm:
         """On the compute stream, right behind the unit's last wgrad: publish "my gradients of this group are
         complete" to all peers (one-warp kernel).  The reduce stream then never holds SMs while a slower rank is
         still computing."""
-        return self.sg.announce_grads(fg._symm_grad)
+        return None if self.local_mode else self.sg.announce_grads(fg._symm_grad)
+
+    # ------------------------------------------------------------------------------ measurement
+    def _tick(self):
+        if self.timing is None:
+            return None
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def _tock(self, what, e0, nvlink_bytes):
+        if e0 is None:
+            return
+        e1 = torch.cuda.Event(enable_timing=True)
+        e1.record()
+        self.timing.append((what, e0, e1, int(nvlink_bytes)))
+
+    def timing_summary(self):
+        """{what: (launches, summed ms, NVLink bytes received)} of the launches recorded since ``timing = []``."""
+        torch.cuda.synchronize()
+        out = {}
+        for what, e0, e1, b in self.timing or []:
+            n, ms, tot = out.get(what, (0, 0.0, 0))
+            out[what] = (n + 1, ms + e0.elapsed_time(e1), tot + b)
+        return out
 
     def reduce_and_step(self, fg, fuse_step: bool, accumulate: bool, grad_scale: float = 1.0,
                         announced_epoch: Optional[int] = None):
@@ -206,6 +240,9 @@ class FusedZ3Comm:
         write the reduced (mean) gradient shard for a deferred step."""
         opt = self.opt
         view = fg._symm_grad
+        t0 = self._tick()
+        # bytes this rank's reduction pulls over NVLink: its shard of every other rank's gradient buffer
+        nvl = fg.part * 2 * (self.world - 1)
         if fuse_step and not accumulate:
             st = opt.optimizer.flat_state(fg.hp_param)
             st["step"] += 1
@@ -213,12 +250,14 @@ class FusedZ3Comm:
             self.sg.rs_adam(view, fg.part, fg.hp_param.data, st["exp_avg"], st["exp_avg_sq"], fg.lp_shard,
                             fg.param_group, st["step"], adamw=bool(getattr(opt.optimizer, "adam_w_mode", 1)),
                             grad_scale=grad_scale, use_multicast=self.use_multicast,
-                            announced_epoch=announced_epoch)
+                            announced_epoch=announced_epoch, local_only=self.local_mode)
+            self._tock("reduce_scatter_adam", t0, nvl)
             fg.grad_shard = None
             return True
         out = torch.empty(fg.part, dtype=fg.grad_dtype, device=fg.device)
         self.sg.rs_adam(view, fg.part, None, None, None, None, fg.param_group, 1, grad_out=out,
-                        use_multicast=self.use_multicast, announced_epoch=announced_epoch)
+                        use_multicast=self.use_multicast, announced_epoch=announced_epoch, local_only=self.local_mode)
+        self._tock("reduce_scatter", t0, nvl)
         if accumulate and fg.grad_shard is not None:
             fg.grad_shard.add_(out)
         else:
@@ -230,7 +269,9 @@ def maybe_create(optimizer, group, requested: Optional[bool]):
     """Returns a FusedZ3Comm or None (NCCL path)."""
     if requested is False or optimizer.world <= 1 or optimizer.dtype != torch.bfloat16:
         return None
-    if not symm.available(group) or optimizer.offload_optimizer:
+    zeropp = (getattr(optimizer, "hpz_size", 1) > 1 or getattr(optimizer, "quantized_weights", False)
+              or getattr(optimizer, "quantized_gradients", False) or getattr(optimizer, "offload_param", False))
+    if not symm.available(group) or optimizer.offload_optimizer or zeropp:
         if requested:
             raise RuntimeError("fused_collectives requested but symmetric memory is unavailable")
         return None

@@ -209,13 +209,15 @@ class ShardedOptimizerBase:
         lp_out = fg.lp_shard if write_lp else None
         if self._fused:
             grad = fg.grad_shard
-            if fg.hp_on_cpu and grad.device.type != "cpu":
-                grad = grad.to("cpu", non_blocking=False)
-            if fg.hp_on_cpu and lp_out is not None and lp_out.device.type != "cpu":
+            if grad.device != hp.device:
+                grad = grad.to(hp.device, non_blocking=False)
+            if lp_out is not None and lp_out.device != hp.device:
+                # master and low-precision shard live on different devices (optimizer offload, or offload_param with a
+                # device-resident master): the kernel writes a staging shard next to the master, then one copy
                 stage = getattr(fg, "_lp_stage", None)
-                if stage is None:
-                    stage = torch.empty(fg.part, dtype=fg.lp_dtype, device="cpu",
-                                        pin_memory=get_accelerator().is_available())
+                if stage is None or stage.device != hp.device:
+                    stage = torch.empty(fg.part, dtype=fg.lp_dtype, device=hp.device,
+                                        pin_memory=(hp.device.type == "cpu" and get_accelerator().is_available()))
                     fg._lp_stage = stage
                 self.optimizer.step_flat(hp, grad, pg, lp_out=stage, grad_scale=grad_scale)
                 lp_out.copy_(stage, non_blocking=True)

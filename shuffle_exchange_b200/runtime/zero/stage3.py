@@ -112,7 +112,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                  communication_data_type=torch.float16, postscale_gradients=True, gradient_predivide_factor=1.0,
                  gradient_accumulation_steps=1, elastic_checkpoint=False, aio_config=None, all2all_process_group=None,
                  zero_hpz_partition_size=1, zero_quantized_weights=False, zero_quantized_nontrainable_weights=False,
-                 zero_module_granularity_threshold=0, zeropp_loco_param=None, log_trace_cache_warnings=False,
+                 zero_module_granularity_threshold=0, zeropp_loco_param=None, zero_quantized_gradients=False, log_trace_cache_warnings=False,
                  check_grad_overflow=None, dtype=None, fused_step=True, unit_modules=None, fused_collectives=None):
         first = next(p for g in init_optimizer.param_groups for p in g["params"])
         lp_dtype = dtype or (first.dtype if first.dtype != torch.float32 or getattr(first, "ds_tensor", None) is None
@@ -140,6 +140,30 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         self.offload_optimizer_pin = bool(self.offload_optimizer and getattr(offload_optimizer_config, "pin_memory", False))
         self.offload_param = bool(offload_param_config is not None and
                                   str(getattr(offload_param_config, "device", "none")).endswith("cpu"))
+        self.offload_param_pin = bool(self.offload_param and getattr(offload_param_config, "pin_memory", False))
+        # ---- ZeRO-Infinity / ZeRO++ switches (every accepted key either acts or raises — none is dropped silently)
+        opt_dev = str(getattr(offload_optimizer_config, "device", "none")) if offload_optimizer_config is not None else "none"
+        self.offload_optimizer_nvme = opt_dev.endswith("nvme")
+        if self.offload_optimizer_nvme:
+            self.offload_optimizer = True          # masters + optimizer state in host buffers between swaps
+            if getattr(offload_optimizer_config, "nvme_path", None) is None:
+                raise ValueError("offload_optimizer.device = nvme needs offload_optimizer.nvme_path")
+        self._offload_optimizer_config, self._aio_config = offload_optimizer_config, aio_config
+        self.offload_ratio = float(getattr(offload_optimizer_config, "ratio", 1.0)) if self.offload_optimizer else 0.0
+        if offload_param_config is not None and str(getattr(offload_param_config, "device", "none")).endswith("nvme"):
+            raise NotImplementedError(
+                "offload_param.device = nvme is not supported: parameter shards stay in device or (offload_param.device "
+                "= cpu) pinned host memory; NVMe offload is available for optimizer state (offload_optimizer.device = nvme)")
+        self.hpz_size = int(zero_hpz_partition_size or 1)
+        self.quantized_weights = bool(zero_quantized_weights)
+        self.quantized_gradients = bool(zero_quantized_gradients)
+        self.loco_param = zeropp_loco_param
+        if zero_quantized_nontrainable_weights:
+            raise NotImplementedError("zero_quantized_nontrainable_weights: frozen weights are gathered like trainable "
+                                      "ones; use zero_quantized_weights")
+        if int(sub_group_size) < 10 ** 12 and dist.get_rank() == 0:
+            logger.info("ZeRO-3: sub_group_size is accepted for compatibility; the sub-groups of this design are the "
+                        "parameter units (one flat group per transformer block)")
         self.elastic_checkpoint = elastic_checkpoint
         self._is_boundary = True
         self.fused_step_enabled = bool(fused_step)
@@ -174,6 +198,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             for p in pg["params"]:
                 pg_of[id(p)] = gi
         unit_mods = discover_units(self.module, unit_modules)
+        self._total_numel = sum(getattr(p, "ds_numel", p.numel()) for p in self.module.parameters() if id(p) in pg_of)
         claimed = set()
         self.units: List[Unit] = []
         for um in unit_mods:
@@ -197,9 +222,15 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             for gi, params in by_pg.items():
                 params = self._materialize_pre_partitioned(params)
                 names = [self.param_names.get(p, f"unit{u.index}.p{j}") for j, p in enumerate(params)]
+                # partial optimizer offload (offload_optimizer.ratio): the first `ratio` of the parameters (in unit
+                # order) keep master + state on the host, the rest step on the GPU (reference stage3.py:258-272)
+                seen = sum(g.unpadded_numel for g in self.groups)
+                on_cpu = self.offload_optimizer and (self.offload_ratio >= 1.0 or seen < self.offload_ratio * self._total_numel)
                 fg = FlatGroup(params, names, self.world, self.rank, self.dp_process_group, self.device, self.dtype,
                                grad_dtype=self.dtype, group_index=len(self.groups), keep_full_params=keep_full,
-                               hp_on_cpu=self.offload_optimizer, pin=self.offload_optimizer_pin)
+                               hp_on_cpu=on_cpu, pin=self.offload_optimizer_pin or self.offload_param_pin,
+                               lp_on_cpu=self.offload_param and not keep_full)
+                self._configure_zeropp(fg)
                 src_pg = self.optimizer.param_groups[gi]
                 pg = {k: v for k, v in src_pg.items() if k != "params"}
                 hp = self._register_group(fg, pg)
@@ -220,6 +251,60 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             del u._params
         self.optimizer.param_groups = new_param_groups
         self.optimizer.state.clear()
+
+    def _configure_zeropp(self, fg: FlatGroup):
+        """qwZ / hpZ / qgZ on the NCCL collectives of this flat group (the fused symmetric-memory path is not used with
+        them: ``fused_collectives.maybe_create``)."""
+        if self.world <= 1:
+            return
+        fg.quantized_weights = self.quantized_weights
+        if self.hpz_size > 1:
+            from ...utils import groups as _groups
+            if not _groups._zero_param_parallel_is_initialized():
+                _groups._create_zero_param_parallel_group(self.hpz_size)
+            fg.hpz_group = _groups._get_zero_param_intra_parallel_group()
+        if self.quantized_gradients:
+            from ...utils import groups as _groups
+            fg.quantized_gradients = (_groups._get_local_all_to_all_group(), self.loco_param)
+
+    def _swapper(self):
+        """NVMe swapper for masters + optimizer state (offload_optimizer.device = nvme), created on first use."""
+        sw = getattr(self, "optimizer_swapper", None)
+        if sw is None and self.offload_optimizer_nvme:
+            from ..swap_tensor import PartitionedOptimizerSwapper
+            from ..swap_tensor.aio_config import get_aio_config
+            aio = self._aio_config if isinstance(self._aio_config, dict) else get_aio_config({})
+            cfg = self._offload_optimizer_config
+            largest = max(fg.part for fg in self.groups)
+            sw = self.optimizer_swapper = PartitionedOptimizerSwapper(cfg, aio, str(cfg.nvme_path), self.optimizer, largest,
+                                                                      "cpu", torch.float32, None)
+            self._swapped = set()
+        return sw
+
+    def _swap_in(self, fg: FlatGroup):
+        sw = self._swapper()
+        if sw is not None and id(fg) in self._swapped:
+            sw.swap_in_optimizer_state(fg.hp_param)
+            self._swapped.discard(id(fg))
+
+    def _swap_out(self, fg: FlatGroup):
+        sw = self._swapper()
+        if sw is not None and fg.hp_on_cpu and id(fg) not in self._swapped:
+            sw.swap_out_optimizer_state(fg.hp_param)
+            self._swapped.add(id(fg))
+
+    def swap_in_all(self):
+        for fg in self.groups:
+            self._swap_in(fg)
+
+    def swap_out_all(self):
+        for fg in self.groups:
+            self._swap_out(fg)
+
+    def _step_group(self, fg: FlatGroup, grad_scale: float, write_lp: bool = True):
+        self._swap_in(fg)
+        super()._step_group(fg, grad_scale, write_lp)
+        self._swap_out(fg)
 
     def _materialize_pre_partitioned(self, params):
         """Parameters created under ``zero.Init`` hold only ``ds_tensor`` (their own 1/world slice);
@@ -336,12 +421,13 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         ``ops.functional.linear`` (``_sxb_linear_only_weights``), on the fused copy/pull gather.  SXB_Z3_GATED=0
         turns it off."""
         return (_Z3_GATED and self.fused is not None and self.allgather_stream is not None and u.module is not None
-                and getattr(u.module, "_sxb_linear_only_weights", False))
+                and getattr(u.module, "_sxb_linear_only_weights", False)
+                and all((fg.part * 2) % 256 == 0 for fg in u.groups))     # flag chunks are multiples of 256 bytes
 
     def _gather_fg(self, fg: FlatGroup, gated: bool = False):
         if self.fused is not None and getattr(fg, "_symm_shard", None) is not None:
             return self.fused.gather(fg, gated)
-        fg.gather_params()
+        fg.gather_params(backward=self._in_backward)
         return None
 
     def _wait_unit(self, u: Unit, full: bool = True):
@@ -601,6 +687,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             fg.micro_steps_accumulated = 0
             fg.grad_shard = None
             fg.release_flat_grad()
+            fg.hpz_secondary = None          # hpZ: the secondary partition is rebuilt by the next forward gather
         for u in self.units:
             if u.persistent and self.world > 1:
                 for fg in u.groups:      # persistent units keep a gathered copy: refresh it
@@ -643,6 +730,13 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         return t.detach().clone()
 
     def state_dict(self):
+        self.swap_in_all()
+        try:
+            return self._state_dict()
+        finally:
+            self.swap_out_all()
+
+    def _state_dict(self):
         sd = {}
         sd[ZERO_STAGE] = 3
         sd[LOSS_SCALER] = self.loss_scaler
