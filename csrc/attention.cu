@@ -36,7 +36,26 @@ struct Params {
   long long out2_stride;
   float* lse;           // [B, Hq, S] natural-log LSE (fwd writes, bwd reads)
   const float* delta;   // [B, Hq, S] rowsum(dO * O) (bwd)
+  // Row scatter (Ulysses K7: the kernel's epilogue returns every output row to the rank that owns that piece of the
+  // sequence, as direct peer stores): scatter_rows > 0 -> row s of the sequence goes to out_peers[s / scatter_rows],
+  // local row b * scatter_rows + s % scatter_rows.  Plain stores only; no TMA is involved on this path.
+  int scatter_rows;
+  void* out_peers[16];
+  void* out2_peers[16];
 };
+
+// Destination row pointer of output row (b, s): local buffer, or the owning peer's buffer when scattering.
+__device__ __forceinline__ __nv_bfloat16* out_row_ptr(const Params& p, bool second, int b, int s) {
+  if (p.scatter_rows > 0) {
+    const int peer = s / p.scatter_rows;
+    const long long r = (long long)b * p.scatter_rows + (s - peer * p.scatter_rows);
+    return second ? reinterpret_cast<__nv_bfloat16*>(p.out2_peers[peer]) + r * p.out2_stride
+                  : reinterpret_cast<__nv_bfloat16*>(p.out_peers[peer]) + r * p.out_stride;
+  }
+  const long long r = (long long)b * p.S + s;
+  return second ? reinterpret_cast<__nv_bfloat16*>(p.out2) + r * p.out2_stride
+                : reinterpret_cast<__nv_bfloat16*>(p.out) + r * p.out_stride;
+}
 
 // Write one row-thread's 64 bf16 values (128 B) into a [128 x 128B] K-major SW128 tile.
 __device__ __forceinline__ void store_row_sw128(uint8_t* tile, int row, const float (&v)[64]) {
@@ -380,8 +399,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       // tcgen05.ld is warp-collective (.sync.aligned): every lane issues it, only the global
       // stores are predicated on the row being inside the sequence.
       const bool valid = qpos < p.S;
-      __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                            ((long long)b * p.S + (valid ? qpos : 0)) * p.out_stride + (long long)h * D;
+      __nv_bfloat16* orow = out_row_ptr(p, false, b, valid ? qpos : 0) + (long long)h * D;
 #pragma unroll 1
       for (int c = 0; c < D / 32; ++c) {
         uint32_t o[32];
@@ -635,8 +653,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     }
     if (!mbar_wait_to(dq_done, 0, 33)) goto done;
     tc_fence_after();
-    __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                          ((long long)b * p.S + min(qpos, p.S - 1)) * p.out_stride + (long long)h * D;
+    __nv_bfloat16* orow = out_row_ptr(p, false, b, min(qpos, p.S - 1)) + (long long)h * D;
 #pragma unroll 1
     for (int c = half * (D / 64); c < (half + 1) * (D / 64); ++c) {
       uint32_t o[32];
@@ -933,11 +950,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       tc_fence_after();
     }
     // half 0 drains dV, half 1 drains dK
-    const long long orow_idx = (long long)b * p.S + min(kpos, p.S - 1);
     const bool is_dv = (half == 0);
-    __nv_bfloat16* dst_row = is_dv
-        ? reinterpret_cast<__nv_bfloat16*>(p.out2) + orow_idx * p.out2_stride + (long long)hk * D
-        : reinterpret_cast<__nv_bfloat16*>(p.out) + orow_idx * p.out_stride + (long long)hk * D;
+    __nv_bfloat16* dst_row = out_row_ptr(p, is_dv, b, min(kpos, p.S - 1)) + (long long)hk * D;
     const uint32_t t_acc = (is_dv ? tDV : tDK) + lane_off;
 #pragma unroll 1
     for (int cc = 0; cc < D / 32; ++cc) {
@@ -1070,6 +1084,24 @@ static bool attn_args_ok(int B, int S, int Hq, int Hk, int D, long long qs, long
   return true;
 }
 
+// Scatter configuration of the next launches on THIS host thread (set by the *_scatter entry points, cleared after).
+namespace {
+struct ScatterCfg {
+  int rows = 0;
+  void* out[16] = {};
+  void* out2[16] = {};
+};
+thread_local ScatterCfg g_scatter;
+thread_local long long g_dv_delta = 0;
+void apply_scatter(sxb::attn::Params& p, bool second_too) {
+  p.scatter_rows = g_scatter.rows;
+  for (int i = 0; i < 16; ++i) {
+    p.out_peers[i] = g_scatter.out[i];
+    p.out2_peers[i] = second_too ? g_scatter.out2[i] : nullptr;
+  }
+}
+}  // namespace
+
 // bf16 flash attention forward.  q/k/v/out: [B, S, H, D] with row pitches (elements) q_stride...
 // lse: [B, Hq, S] fp32 (may be NULL).
 SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out, void* lse, int B,
@@ -1086,6 +1118,7 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
   Params p{};
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
+  apply_scatter(p, false);
   dim3 grid(Hq, B, (S + BQ - 1) / BQ);
   cudaStream_t s = (cudaStream_t)stream;
   if (use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride))) {
@@ -1139,6 +1172,7 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     if ((rc = make_qkv_map(&tk, k, B, S, Hk, D, k_stride, BC))) return rc;
     if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BC))) return rc;
     p.out = dq; p.out_stride = dq_stride;
+    apply_scatter(p, false);
     dim3 grid(Hq, B, (S + BQ - 1) / BQ);
     if (use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride))) {
       if ((rc = set_smem(attn_bwd_dq_kernel<128, 2>, DqSmem<128>::kTotal))) return rc;
@@ -1162,6 +1196,15 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     if ((rc = make_qkv_map(&tk, k, B, S, Hk, D, k_stride, BQ))) return rc;
     if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BQ))) return rc;
     p.out = dk; p.out_stride = dk_stride; p.out2 = dv; p.out2_stride = dv_stride;
+    if (g_scatter.rows > 0) {
+      // dK / dV go to the same peers as dQ, at their own column offsets: the caller passes the dK bases in out2[]
+      // and the dV bases are dK + dv_col_delta (see sxb_attn_bwd_scatter)
+      p.scatter_rows = g_scatter.rows;
+      for (int i = 0; i < 16; ++i) {
+        p.out_peers[i] = g_scatter.out2[i];
+        p.out2_peers[i] = g_scatter.out2[i] ? (void*)((__nv_bfloat16*)g_scatter.out2[i] + g_dv_delta) : nullptr;
+      }
+    }
     dim3 grid(Hk, B, (S + BQ - 1) / BQ);
     if (D == 128) {
       if ((rc = set_smem(attn_bwd_dkv_kernel<128>, DkvSmem<128>::kTotal))) return rc;
@@ -1173,4 +1216,45 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     SXB_CHECK_LAUNCH();
   }
   return SXB_OK;
+}
+
+
+// K7 (Ulysses): forward attention whose epilogue stores each output row straight into the buffer of the rank that
+// owns that part of the sequence.  out_peers: host array of `world` device pointers — peer r's destination for the
+// rows [r*rows_per_peer, (r+1)*rows_per_peer) of this rank's heads (column offset already applied), row pitch
+// o_stride.  `out` is unused.  (reference: all_to_all_single after the local attention, sequence/layer.py:434-437)
+SXB_API int sxb_attn_fwd_scatter(const void* q, const void* k, const void* v, void* const* out_peers, int world,
+                                 int rows_per_peer, void* lse, int B, int S, int Hq, int Hk, int D,
+                                 long long q_stride, long long k_stride, long long v_stride, long long o_stride,
+                                 int causal, float scale, void* stream) {
+  if (world < 1 || world > 16 || rows_per_peer <= 0 || (long long)rows_per_peer * world < S) return SXB_ERR_BAD_ARG;
+  g_scatter = ScatterCfg{};
+  g_scatter.rows = rows_per_peer;
+  for (int i = 0; i < world; ++i) g_scatter.out[i] = out_peers[i];
+  const int rc = sxb_attn_fwd(q, k, v, out_peers[0], lse, B, S, Hq, Hk, D, q_stride, k_stride, v_stride, o_stride,
+                              causal, scale, stream);
+  g_scatter = ScatterCfg{};
+  return rc;
+}
+
+// Backward with scattered dQ / dK / dV: dq_peers[r] / dk_peers[r] are peer r's destinations (column offsets of this
+// rank's heads applied) with row pitches dq_stride / dk_stride; dV lands dv_col_delta elements after dK with pitch
+// dv_stride.
+SXB_API int sxb_attn_bwd_scatter(const void* q, const void* k, const void* v, const void* out, const void* d_out,
+                                 const void* lse, void* delta, void* const* dq_peers, void* const* dk_peers,
+                                 long long dv_col_delta, int world, int rows_per_peer, int B, int S, int Hq, int Hk,
+                                 int D, long long q_stride, long long k_stride, long long v_stride, long long o_stride,
+                                 long long do_stride, long long dq_stride, long long dk_stride, long long dv_stride,
+                                 int causal, float scale, void* stream) {
+  if (world < 1 || world > 16 || rows_per_peer <= 0 || (long long)rows_per_peer * world < S) return SXB_ERR_BAD_ARG;
+  g_scatter = ScatterCfg{};
+  g_scatter.rows = rows_per_peer;
+  for (int i = 0; i < world; ++i) { g_scatter.out[i] = dq_peers[i]; g_scatter.out2[i] = dk_peers[i]; }
+  g_dv_delta = dv_col_delta;
+  const int rc = sxb_attn_bwd(q, k, v, out, d_out, lse, delta, dq_peers[0], dk_peers[0],
+                              (__nv_bfloat16*)dk_peers[0] + dv_col_delta, B, S, Hq, Hk, D, q_stride, k_stride, v_stride,
+                              o_stride, do_stride, dq_stride, dk_stride, dv_stride, causal, scale, stream);
+  g_scatter = ScatterCfg{};
+  g_dv_delta = 0;
+  return rc;
 }
