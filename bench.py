@@ -42,6 +42,11 @@ def parse():
                     help="decoder layers that recompute activations in backward: 'auto' = as few as HBM allows, "
                          "'all', or a count")
     ap.add_argument("--no-fused", action="store_true", help="NCCL baseline path for the ZeRO-3 collectives")
+    ap.add_argument("--sp", type=int, default=1,
+                    help="Ulysses sequence-parallel degree: --seq is the FULL sequence, every rank holds seq/sp tokens "
+                         "(config 4: --sp 8 --seq 131072); ZeRO-3 still shards over all ranks")
+    ap.add_argument("--moe-nccl", action="store_true", help="Mixtral: NCCL all_to_all_single path instead of the fused one")
+    ap.add_argument("--fp8-experts", action="store_true", help="Mixtral: e4m3 expert GEMMs in forward")
     ap.add_argument("--no-extras", action="store_true",
                     help="skip the secondary measurements (exposed communication, fused-path rooflines, the line at "
                          "the reference's recompute setting)")
@@ -190,7 +195,8 @@ def run_ours(args):
         # (experts sharded 1/N per rank, ZeRO-2 for the dense part: the reference asserts MoE + ZeRO-3 unsupported,
         # runtime/engine.py:1760).  The full 8x7B model needs >= 8 GPUs of 180 GB for training state.
         from shuffle_exchange_b200.models.mixtral import MixtralForCausalLM, mixtral_config
-        cfg = mixtral_config(args.model, max_position_embeddings=max(args.seq, 8192), ep_size=world)
+        cfg = mixtral_config(args.model, max_position_embeddings=max(args.seq, 8192), ep_size=world,
+                             fused_exchange=(False if args.moe_nccl else None), fp8_experts=args.fp8_experts)
         if args.layers:
             cfg.num_hidden_layers = args.layers
         per_rank = cfg.num_parameters() - cfg.num_hidden_layers * (cfg.num_local_experts - cfg.num_local_experts // world) * 3 * cfg.hidden_size * cfg.intermediate_size
@@ -211,30 +217,56 @@ def run_ours(args):
         cfg = llama_config(args.model, max_position_embeddings=max(args.seq, 8192))
         if args.layers:
             cfg.num_hidden_layers = args.layers
+        if args.sp > 1:
+            assert args.sp == world and args.seq % args.sp == 0 and args.mbs == 1, "--sp must equal the number of ranks"
+            sxb.init_distributed(dist_backend="nccl")
+            from shuffle_exchange_b200.sequence.fused_ulysses import UlyssesPeers
+            cfg.ulysses = UlyssesPeers(torch.distributed.group.WORLD, args.seq // args.sp, cfg.num_attention_heads,
+                                       cfg.num_key_value_heads, cfg.head_dim)
         torch.manual_seed(1234)
         model = LlamaForCausalLM(cfg, device=dev, dtype=torch.bfloat16)
         conf = ds_config(args, world)
     engine, _, _, _ = sxb.initialize(model=model, config=conf, model_parameters=model.parameters())
     engine.train()
-    B, S = args.mbs, args.seq
+    sp = args.sp
+    B, S = args.mbs, args.seq // sp                 # tokens this rank processes per step
     # ZeRO-2 keeps a full-size low-precision gradient buffer that is allocated lazily in the first backward
     extra = sum(p.numel() for p in model.parameters()) * 2 if is_moe else 0
+    if is_moe and not args.moe_nccl:
+        extra += int(0.5 * cfg.activation_bytes_per_layer(B, S)) * 4     # capacity-sized routed-row buffers
     cfg.checkpoint_layers = pick_checkpoint_layers(args, cfg, B, S, dev, world, extra)
-    g = torch.Generator().manual_seed(1000 + rank)
     n_batches = 4
-    host = [torch.randint(0, cfg.vocab_size, (B, S), generator=g, dtype=torch.int64).pin_memory() for _ in range(n_batches)]
+    if sp > 1:
+        # one sequence for the whole group: every rank draws the same tokens and keeps its slice; labels are shifted
+        # BEFORE slicing (the next-token target of a rank's last token lives on the next rank)
+        g = torch.Generator().manual_seed(1000)
+        full = [torch.randint(0, cfg.vocab_size, (1, args.seq), generator=g, dtype=torch.int64) for _ in range(n_batches)]
+        host, host_lab = [], []
+        for f in full:
+            lab = torch.full_like(f, -100)
+            lab[:, :-1] = f[:, 1:]
+            host.append(f[:, rank * S:(rank + 1) * S].contiguous().pin_memory())
+            host_lab.append(lab[:, rank * S:(rank + 1) * S].contiguous().pin_memory())
+        pos = torch.arange(rank * S, (rank + 1) * S, device=dev).view(1, S)
+        kw = dict(position_ids=pos, shift_labels=False)
+    else:
+        g = torch.Generator().manual_seed(1000 + rank)
+        host = [torch.randint(0, cfg.vocab_size, (B, S), generator=g, dtype=torch.int64).pin_memory() for _ in range(n_batches)]
+        host_lab = host
+        kw = {}
     devb = [h.to(dev, non_blocking=True) for h in host]
+    devl = [h.to(dev, non_blocking=True) for h in host_lab] if sp > 1 else devb
 
     def step_device(i):
-        ids = devb[i % n_batches]
-        loss = engine(ids, labels=ids)
+        loss = engine(devb[i % n_batches], labels=devl[i % n_batches], **kw)
         engine.backward(loss)
         engine.step()
         return loss
 
     def step_e2e(i):
         ids = host[i % n_batches].to(dev, non_blocking=True)       # H2D from pinned memory, every step
-        loss = engine(ids, labels=ids)
+        lab = host_lab[i % n_batches].to(dev, non_blocking=True) if sp > 1 else ids
+        loss = engine(ids, labels=lab, **kw)
         engine.backward(loss)
         engine.step()
         return float(loss.item())                                    # D2H read of the step's result
@@ -278,21 +310,33 @@ def run_ours(args):
         e2e = {"value": tokens_per_step * args.steps / (ems / 1e3), "unit": "tokens/s",
                "h2d_bytes_per_step": B * S * 8, "d2h_bytes_per_step": 4, "ms_per_step": ems / args.steps}
     extras = {}
-    if not args.no_extras and not is_moe:
+    if is_moe:
+        for m in model.modules():
+            if hasattr(m, "check_overflow"):
+                m.check_overflow()          # raises if routing ever exceeded the receive-buffer capacity
+                break
+    if not args.no_extras and not is_moe and sp == 1:
         extras = secondary_measurements(args, engine, cfg, step_device, barrier_sync, max_over_ranks, dev, world, ms / args.steps,
                                         B, S)
     hang = nlib.hang_info("gemm") or nlib.hang_info("attn")
     if rank == 0:
-        flops = cfg.flops_per_token(S) * tokens_per_step / world
+        flops = cfg.flops_per_token(args.seq) * tokens_per_step / world
         out = {
-            "metric": ("tokens/sec/box Mixtral-8x7B EP" if is_moe else "tokens/sec/box Llama-3-8B ZeRO-3"),
+            "metric": ("tokens/sec/box Mixtral-8x7B EP" if is_moe else
+                       f"tokens/sec/box Llama-3-8B Ulysses SP={sp}" if sp > 1 else "tokens/sec/box Llama-3-8B ZeRO-3"),
             "value": value, "unit": "tokens/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
             "config": {"model": args.model + ("" if not args.layers else f"-DEBUG-{args.layers}-layers"),
-                       "global_batch": B * world, "seq_len": S, "parallelism": (f"ep{world}-zero2-dp{world}" if is_moe else f"zero3-dp{world}"),
-                       "collectives": ("nccl all-to-all of routed rows + ZeRO-2 gradient reduce" if is_moe else
-                                       "nccl" if args.no_fused or world == 1 else "fused symmetric-memory kernels"),
+                       "global_batch": B * world // sp, "seq_len": args.seq,
+                       "parallelism": (f"ep{world}-zero2-dp{world}" if is_moe else
+                                       f"ulysses-sp{sp}-zero3-dp{world}" if sp > 1 else f"zero3-dp{world}"),
+                       "collectives": (("nccl all-to-all of routed rows" if args.moe_nccl else
+                                        "fused symmetric-memory dispatch/combine + grouped expert GEMM"
+                                        + (" (fp8 forward)" if args.fp8_experts else "")) + " + ZeRO-2 gradient reduce"
+                                       if is_moe else
+                                       "nccl" if args.no_fused or world == 1 else "fused symmetric-memory kernels"
+                                       + (" + Ulysses exchanges in the GEMM / attention epilogues" if sp > 1 else "")),
                        "activation_checkpointing": f"{cfg.checkpoint_layers} of {cfg.num_hidden_layers} layers recompute "
                                                    f"(--ckpt-layers {args.ckpt_layers})",
                        "optimizer": "AdamW fp32 master",

@@ -400,6 +400,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       // stores are predicated on the row being inside the sequence.
       const bool valid = qpos < p.S;
       __nv_bfloat16* orow = out_row_ptr(p, false, b, valid ? qpos : 0) + (long long)h * D;
+      // scattering forward keeps a LOCAL copy of O as well (p.out, pitch out2_stride): the backward needs
+      // rowsum(dO * O) where the heads are, not where the sequence is
+      __nv_bfloat16* orow_keep = (p.scatter_rows > 0 && p.out != nullptr)
+          ? reinterpret_cast<__nv_bfloat16*>(p.out) + ((long long)b * p.S + (valid ? qpos : 0)) * p.out2_stride +
+                (long long)h * D
+          : nullptr;
 #pragma unroll 1
       for (int c = 0; c < D / 32; ++c) {
         uint32_t o[32];
@@ -414,6 +420,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             w.z = pack_bf16(__uint_as_float(o[i * 8 + 4]) * inv_l, __uint_as_float(o[i * 8 + 5]) * inv_l);
             w.w = pack_bf16(__uint_as_float(o[i * 8 + 6]) * inv_l, __uint_as_float(o[i * 8 + 7]) * inv_l);
             *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = w;
+            if (orow_keep) *reinterpret_cast<uint4*>(orow_keep + c * 32 + i * 8) = w;
           }
         }
       }
@@ -1093,6 +1100,8 @@ struct ScatterCfg {
 };
 thread_local ScatterCfg g_scatter;
 thread_local long long g_dv_delta = 0;
+thread_local void* g_keep = nullptr;
+thread_local long long g_keep_stride = 0;
 void apply_scatter(sxb::attn::Params& p, bool second_too) {
   p.scatter_rows = g_scatter.rows;
   for (int i = 0; i < 16; ++i) {
@@ -1119,6 +1128,7 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
   apply_scatter(p, false);
+  if (p.scatter_rows > 0) { p.out = g_keep; p.out2_stride = g_keep_stride; }
   dim3 grid(Hq, B, (S + BQ - 1) / BQ);
   cudaStream_t s = (cudaStream_t)stream;
   if (use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride))) {
@@ -1224,16 +1234,21 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
 // rows [r*rows_per_peer, (r+1)*rows_per_peer) of this rank's heads (column offset already applied), row pitch
 // o_stride.  `out` is unused.  (reference: all_to_all_single after the local attention, sequence/layer.py:434-437)
 SXB_API int sxb_attn_fwd_scatter(const void* q, const void* k, const void* v, void* const* out_peers, int world,
-                                 int rows_per_peer, void* lse, int B, int S, int Hq, int Hk, int D,
-                                 long long q_stride, long long k_stride, long long v_stride, long long o_stride,
-                                 int causal, float scale, void* stream) {
+                                 int rows_per_peer, void* out_keep, long long keep_stride, void* lse, int B, int S,
+                                 int Hq, int Hk, int D, long long q_stride, long long k_stride, long long v_stride,
+                                 long long o_stride, int causal, float scale, void* stream) {
+  // out_keep (may be NULL): local [B, S, Hq, D] copy of O with row pitch keep_stride, for the backward pass
   if (world < 1 || world > 16 || rows_per_peer <= 0 || (long long)rows_per_peer * world < S) return SXB_ERR_BAD_ARG;
+  if (keep_stride % 8) return SXB_ERR_UNSUPPORTED;
   g_scatter = ScatterCfg{};
   g_scatter.rows = rows_per_peer;
   for (int i = 0; i < world; ++i) g_scatter.out[i] = out_peers[i];
+  g_keep = out_keep;
+  g_keep_stride = keep_stride;
   const int rc = sxb_attn_fwd(q, k, v, out_peers[0], lse, B, S, Hq, Hk, D, q_stride, k_stride, v_stride, o_stride,
                               causal, scale, stream);
   g_scatter = ScatterCfg{};
+  g_keep = nullptr;
   return rc;
 }
 

@@ -63,6 +63,12 @@ struct XParams {
   const float* scale_a;
   const float* scale_b;
   int scale_b_group_stride;
+  // ---- column scatter to peers (Ulysses K6): 64-column block j of the result goes to peer scatter_table[2j] at
+  // column scatter_table[2j+1] of that peer's buffer, row scatter_row0 + (row of the result), pitch scatter_ld
+  const int* scatter_table;
+  void* scatter_peers[16];
+  long long scatter_ld;
+  long long scatter_row0;
 };
 
 struct Tile {
@@ -438,6 +444,24 @@ gemm_pair_x_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             tma_store_commit();
           }
           buf ^= 1;
+        } else if (p.scatter_table != nullptr) {
+          // direct peer stores: this thread's 64 values are 128 contiguous bytes of one destination row
+          if (gr < m_end && gc0 < p.N) {
+            const int owner = p.scatter_table[2 * (gc0 >> 6)];
+            const int dcol = p.scatter_table[2 * (gc0 >> 6) + 1];
+            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.scatter_peers[owner]) +
+                                                  (p.scatter_row0 + gr) * p.scatter_ld + dcol);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t* sv = (j < 4) ? &v0[j * 8] : &v1[(j - 4) * 8];
+              uint4 o;
+              o.x = pack_bf16(p.alpha * __uint_as_float(sv[0]), p.alpha * __uint_as_float(sv[1]));
+              o.y = pack_bf16(p.alpha * __uint_as_float(sv[2]), p.alpha * __uint_as_float(sv[3]));
+              o.z = pack_bf16(p.alpha * __uint_as_float(sv[4]), p.alpha * __uint_as_float(sv[5]));
+              o.w = pack_bf16(p.alpha * __uint_as_float(sv[6]), p.alpha * __uint_as_float(sv[7]));
+              dst[j] = o;
+            }
+          }
         } else if (gr < m_end) {
           if (p.c_dtype == kBF16) {
             __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + c_off + (size_t)gr * p.ldc;
@@ -612,6 +636,49 @@ SXB_API int sxb_gemm_ext(const void* A, const void* B, void* C, int M, int N, in
   cudaStream_t s = (cudaStream_t)stream;
   if (fp8) gemm_pair_x_kernel<true><<<grid, kThreads, Plan::kTotal, s>>>(ta, tb, tc, p);
   else gemm_pair_x_kernel<false><<<grid, kThreads, Plan::kTotal, s>>>(ta, tb, tc, p);
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+
+// K6 (Ulysses): C = A op(B) whose epilogue stores every 64-column block of the result straight into the buffer of the
+// rank that owns those heads (direct peer stores over NVLink).  table: device int32 [2 * N/64] = (owner, destination
+// column) per block; peers: host array of `world` device pointers; the result row r lands in row row0 + r of the
+// destination (pitch dst_ld elements).  bf16 only, plain (ungrouped) problem, N % 64 == 0.
+// (reference: QKV projection, then three all_to_all_single, sequence/layer.py:388-426)
+SXB_API int sxb_gemm_scatter(const void* A, const void* B, int M, int N, int K, int layout, long long lda,
+                             long long ldb, const void* table, void* const* peers, int world, long long dst_ld,
+                             long long row0, float alpha, int max_ctas, void* stream) {
+  if (layout < 0 || layout > 2 || world < 1 || world > 16 || table == nullptr) return SXB_ERR_BAD_ARG;
+  if ((N % 64) || (dst_ld % 8) || (lda % 8) || (ldb % 8) || (reinterpret_cast<uintptr_t>(A) & 15) ||
+      (reinterpret_cast<uintptr_t>(B) & 15))
+    return SXB_ERR_UNSUPPORTED;
+  if (M <= 0 || N <= 0 || K <= 0) return SXB_OK;
+  XParams p{};
+  p.M = M; p.N = N; p.K = K; p.layout = layout; p.c_dtype = kBF16; p.accumulate = 0; p.direct = 1;
+  p.C = nullptr; p.ldc = 0; p.alpha = alpha; p.ldb_bytes = ldb * 2;
+  p.scatter_table = (const int*)table; p.scatter_ld = dst_ld; p.scatter_row0 = row0;
+  for (int i = 0; i < 16; ++i) p.scatter_peers[i] = i < world ? peers[i] : nullptr;
+  unsigned long long a_rows, a_cols, b_rows, b_cols;
+  if (layout == TN) { a_rows = K; a_cols = M; } else { a_rows = M; a_cols = K; }
+  if (layout == NT) { b_rows = N; b_cols = K; } else { b_rows = K; b_cols = N; }
+  p.b_rows = (int)b_rows;
+  CUtensorMap ta, tb;
+  int rc;
+  if ((rc = make_map(&ta, A, a_rows, a_cols, lda, (layout == TN) ? 64 : 128, 2))) return rc;
+  if ((rc = make_map(&tb, B, b_rows, b_cols, ldb, (layout == NT) ? 128 : 64, 2))) return rc;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_pair_x_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Plan::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  int grid = num_sms() & ~1;
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas & ~1;
+  const long long tiles = (long long)((M + 255) / 256) * ((N + 255) / 256);
+  if (2 * tiles < grid) grid = (int)(2 * tiles);
+  if (grid < 2) grid = 2;
+  gemm_pair_x_kernel<false><<<grid, kThreads, Plan::kTotal, (cudaStream_t)stream>>>(ta, tb, ta, p);
   SXB_CHECK_LAUNCH();
   return SXB_OK;
 }

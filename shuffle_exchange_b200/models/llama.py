@@ -95,7 +95,9 @@ def llama_config(name: str, **overrides) -> LlamaConfig:
 class LlamaDecoderLayer(nn.Module):
     # every matrix parameter of this block is consumed through ops.functional.linear only: ZeRO-3 may hand them to
     # the GEMMs while their all-gather is still in flight (gated B operand, runtime/zero/stage3.py: K2)
-    _sxb_linear_only_weights = True
+    @property
+    def _sxb_linear_only_weights(self) -> bool:
+        return getattr(self.cfg, "ulysses", None) is None     # the fused Ulysses block reads wqkv / wo outside F.linear
 
     def __init__(self, cfg: LlamaConfig, layer_idx: int, device=None, dtype=None):
         super().__init__()
@@ -120,11 +122,18 @@ class LlamaDecoderLayer(nn.Module):
         B, S, H = h.shape
         eps = self.cfg.rms_norm_eps
         x, residual = F.rms_norm(h, self.input_layernorm, eps, residual)
-        qkv = F.linear(x, self.wqkv)
-        C = qkv.shape[-1]
-        qkv = F.rope(qkv, positions, cos, sin, self.n_q + self.n_kv, self.d)
-        o = F.flash_attention_qkv(qkv, self.n_q, self.n_kv, self.d, causal=True)
-        h = F.linear(o.reshape(B, S, self.n_q * self.d), self.wo)
+        sp = getattr(self.cfg, "ulysses", None)
+        if sp is not None:
+            # sequence parallel (Ulysses): h holds THIS rank's S tokens of a longer sequence; the attention block
+            # exchanges heads <-> sequence inside its GEMM / attention epilogues (sequence/fused_ulysses.py)
+            from ..sequence.fused_ulysses import ulysses_attention
+            assert B == 1, "the fused Ulysses block takes one sequence per rank"
+            h = ulysses_attention(x.view(S, H), self.wqkv, self.wo, cos, sin, sp, True).view(B, S, H)
+        else:
+            qkv = F.linear(x, self.wqkv)
+            qkv = F.rope(qkv, positions, cos, sin, self.n_q + self.n_kv, self.d)
+            o = F.flash_attention_qkv(qkv, self.n_q, self.n_kv, self.d, causal=True)
+            h = F.linear(o.reshape(B, S, self.n_q * self.d), self.wo)
         x, residual = F.rms_norm(h, self.post_attention_layernorm, eps, residual)
         a = F.swiglu(F.linear(x, self.w_gate_up))
         h = F.linear(a, self.w_down)
@@ -154,7 +163,8 @@ class LlamaModel(nn.Module):
         cfg = self.cfg
         dev = input_ids.device
         positions = position_ids.reshape(-1) if position_ids is not None else self._positions(B, S, dev)
-        max_pos = max(cfg.max_position_embeddings, S)
+        sp = getattr(cfg, "ulysses", None)
+        max_pos = max(cfg.max_position_embeddings, S if sp is None else sp.S)
         cos, sin = F.rope_tables(max_pos, cfg.head_dim, cfg.rope_theta, dev)
         h = F.embedding(input_ids, self.embed_tokens)
         residual = None

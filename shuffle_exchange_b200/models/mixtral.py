@@ -27,6 +27,9 @@ class MixtralConfig(LlamaConfig):
     num_experts_per_tok: int = 2
     router_aux_loss_coef: float = 0.02
     ep_size: int = 1
+    fused_exchange: object = None        # None: symmetric-memory dispatch/combine when available; False: NCCL
+    fp8_experts: bool = False            # e4m3 expert GEMMs in forward (tcgen05 kind::f8f6f4), bf16 backward
+    ep_capacity_factor: float = 1.5
 
     def num_parameters(self) -> int:
         h, f, v, d = self.hidden_size, self.intermediate_size, self.vocab_size, self.head_dim
@@ -78,7 +81,9 @@ class MixtralDecoderLayer(nn.Module):
         self.wo = nn.Parameter(torch.empty(h, self.n_q * d, **kw))
         self.post_attention_layernorm = nn.Parameter(torch.ones(h, **kw))
         self.moe = DroplessMoE(h, cfg.intermediate_size, cfg.num_local_experts, ep_size=cfg.ep_size,
-                               k=cfg.num_experts_per_tok, aux_loss_coef=cfg.router_aux_loss_coef, **kw)
+                               k=cfg.num_experts_per_tok, aux_loss_coef=cfg.router_aux_loss_coef,
+                               fused_exchange=cfg.fused_exchange, fp8_experts=cfg.fp8_experts,
+                               ep_capacity_factor=cfg.ep_capacity_factor, **kw)
 
     def reset_parameters(self, std: float):
         for w in (self.wqkv, self.wo):
