@@ -233,7 +233,7 @@ def run_ours(args):
     # ZeRO-2 keeps a full-size low-precision gradient buffer that is allocated lazily in the first backward
     extra = sum(p.numel() for p in model.parameters()) * 2 if is_moe else 0
     if is_moe and not args.moe_nccl:
-        extra += int(0.5 * cfg.activation_bytes_per_layer(B, S)) * 4     # capacity-sized routed-row buffers
+        extra += 2 * 2 ** 30                                             # symmetric receive / return buffers
     cfg.checkpoint_layers = pick_checkpoint_layers(args, cfg, B, S, dev, world, extra)
     n_batches = 4
     if sp > 1:

@@ -1,5 +1,9 @@
-"""``InferenceParameter``: a tensor that keeps named auxiliary tensors (quantisation scales etc.) attached through
-``.to()`` and views (reference ``inference/v2/inference_parameter.py``)."""
+"""``InferenceParameter`` — a tensor that carries named companion tensors (quantisation scales, zero points, ...).
+
+The companions live in one dict on the instance and are reachable as attributes; moving the parameter with ``.to()``
+moves them along, re-wrapping a plain tensor keeps them.  Same constructor surface as the reference class
+(``deepspeed/inference/v2/inference_parameter.py``): ``initialize(core, **aux)``, ``initialize_raw(**{CORE_PARAM: core,
+...})``, ``aux_attrs``."""
 from __future__ import annotations
 
 from typing import Dict
@@ -7,54 +11,60 @@ from typing import Dict
 import torch
 
 CORE_PARAM = "_ds_core_param_key"
-STR_TO_DTYPE = {"torch.float32": torch.float32, "torch.float64": torch.float64, "torch.float16": torch.float16,
-                "torch.bfloat16": torch.bfloat16, "torch.int64": torch.int64, "torch.int32": torch.int32,
-                "torch.int16": torch.int16, "torch.int8": torch.int8, "torch.uint8": torch.uint8,
-                "torch.bool": torch.bool}
+STR_TO_DTYPE = {str(dt): dt for dt in (torch.float32, torch.float64, torch.float16, torch.bfloat16, torch.int64,
+                                       torch.int32, torch.int16, torch.int8, torch.uint8, torch.bool)}
+_SLOT = "_aux_attrs"
+
+
+def _adopt(dst: torch.Tensor, companions: Dict[str, torch.Tensor]) -> None:
+    object.__setattr__(dst, _SLOT, companions)
+    for name, t in companions.items():
+        object.__setattr__(dst, name, t)
 
 
 class InferenceParameter(torch.Tensor):
 
     @staticmethod
     def __new__(cls, tensor, *args, **kwargs):
-        new = super().__new__(cls, tensor, *args, **kwargs)
-        if hasattr(tensor, "_aux_attrs"):
-            setattr(new, "_aux_attrs", tensor.aux_attrs)
-        return new
+        self = super().__new__(cls, tensor, *args, **kwargs)
+        inherited = getattr(tensor, _SLOT, None)
+        if inherited is not None:
+            _adopt(self, inherited)
+        return self
+
+    @property
+    def aux_attrs(self) -> Dict[str, torch.Tensor]:
+        return getattr(self, _SLOT, {})
 
     def to(self, *args, **kwargs):
-        new = super().to(*args, **kwargs)
-        if hasattr(self, "_aux_attrs"):
-            setattr(new, "_aux_attrs", self.aux_attrs)
-        try:
-            _ = torch.device(args[0])
-            for name, attr in new.aux_attrs.items():
-                moved = attr.to(*args, **kwargs)
-                setattr(new, name, moved)
-                new.aux_attrs[name] = moved
-        except Exception:
-            pass
-        return new
+        moved = super().to(*args, **kwargs)
+        companions = dict(self.aux_attrs)
+        # companions follow DEVICE moves only: a dtype cast of the payload must not touch fp32 scales
+        target = kwargs.get("device", args[0] if args and not isinstance(args[0], torch.dtype) else None)
+        if target is not None and not isinstance(target, torch.Tensor):
+            try:
+                dev = torch.device(target)
+                companions = {k: v.to(dev) for k, v in companions.items()}
+            except (TypeError, RuntimeError):
+                pass
+        _adopt(moved, companions)
+        return moved
 
     @classmethod
     def initialize(cls, core_param: torch.Tensor, **kwargs) -> "InferenceParameter":
         param = InferenceParameter(core_param)
-        setattr(param, "_aux_attrs", kwargs)
-        for name, attr in kwargs.items():
+        for name, t in kwargs.items():
+            if not isinstance(t, torch.Tensor):
+                raise ValueError(f"Attribute {name} must be a tensor.")
             if hasattr(param, name):
                 raise ValueError(f"Attribute {name} already exists on param.")
-            if not isinstance(attr, torch.Tensor):
-                raise ValueError(f"Attribute {name} must be a tensor.")
-            setattr(param, name, attr)
+        _adopt(param, dict(kwargs))
         return param
 
     @classmethod
     def initialize_raw(cls, **kwargs) -> "InferenceParameter":
-        if CORE_PARAM not in kwargs:
-            raise ValueError(f"Must provide core parameter, with key {CORE_PARAM}.")
-        return InferenceParameter.initialize(kwargs[CORE_PARAM],
-                                             **{k: v for k, v in kwargs.items() if k != CORE_PARAM})
-
-    @property
-    def aux_attrs(self) -> Dict[str, torch.Tensor]:
-        return getattr(self, "_aux_attrs", {})
+        try:
+            core = kwargs.pop(CORE_PARAM)
+        except KeyError:
+            raise ValueError(f"Must provide core parameter, with key {CORE_PARAM}.") from None
+        return cls.initialize(core, **kwargs)

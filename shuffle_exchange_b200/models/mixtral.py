@@ -29,7 +29,7 @@ class MixtralConfig(LlamaConfig):
     ep_size: int = 1
     fused_exchange: object = None        # None: symmetric-memory dispatch/combine when available; False: NCCL
     fp8_experts: bool = False            # e4m3 expert GEMMs in forward (tcgen05 kind::f8f6f4), bf16 backward
-    ep_capacity_factor: float = 1.5
+    ep_capacity_factor: float = 1.25
 
     def num_parameters(self) -> int:
         h, f, v, d = self.hidden_size, self.intermediate_size, self.vocab_size, self.head_dim
@@ -44,7 +44,13 @@ class MixtralConfig(LlamaConfig):
         t = batch * seq_len
         h, f, k = self.hidden_size, self.intermediate_size, self.num_experts_per_tok
         qkv = (self.num_attention_heads + 2 * self.num_key_value_heads) * self.head_dim
-        return t * elem * (5 * h + qkv) + t * k * elem * (3 * h + 3 * f) + t * 4 * (2 + self.num_attention_heads)
+        # the fused exchange sizes every routed-row tensor for the receive-buffer capacity (no host sync to learn the
+        # exact row count), plus one 256-row alignment pad per local expert
+        rows = t * k
+        if self.fused_exchange is not False and self.ep_size > 1:
+            rows = int(rows * self.ep_capacity_factor) + 256 * max(1, self.num_local_experts // self.ep_size)
+        return t * elem * (5 * h + qkv) + rows * elem * (3 * h + 3 * f) + t * k * elem * h \
+            + t * 4 * (2 + self.num_attention_heads)
 
     def flops_per_token(self, seq_len: int, causal: bool = True) -> float:
         h, f, d = self.hidden_size, self.intermediate_size, self.head_dim

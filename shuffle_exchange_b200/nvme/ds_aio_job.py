@@ -1,46 +1,50 @@
-"""Sub-process job wrapper used by the sweep driver."""
+"""One external command of the NVMe sweep (a benchmark run, ``sync``, a page-cache flush), run without a shell.
+
+``argv`` is executed as given — arguments are never joined into a shell string, so paths with spaces or shell
+metacharacters in a sweep configuration cannot change what runs (the reference wrapper,
+``deepspeed/nvme/ds_aio_job.py``, splits a joined string; the sweep's use is the same: run, capture output, fail
+loudly on a non-zero exit code)."""
 from __future__ import annotations
 
+import shlex
 import subprocess
+from dataclasses import dataclass, field
 from typing import List, Optional
 
 
+@dataclass
 class Job:
+    cmd_line: List[str]
+    output_file: Optional[str] = None      # stdout and stderr go here (None: inherit)
+    work_dir: Optional[str] = None
+    split_pieces: bool = True              # the sweep writes "--option value" as one piece: split those into words
+    returncode: Optional[int] = field(default=None, init=False)
 
-    def __init__(self, cmd_line: List[str], output_file: Optional[str] = None, work_dir: Optional[str] = None):
-        self.cmd_line, self.output_file, self.work_dir = cmd_line, output_file, work_dir
-        self.output_fd = None
+    # accessors kept for callers written against the reference class
+    def cmd(self) -> List[str]:
+        return list(self.cmd_line)
 
-    def cmd(self):
-        return self.cmd_line
-
-    def get_stdout(self):
-        return self.output_fd
-
-    def get_stderr(self):
-        return self.output_fd
-
-    def get_cwd(self):
+    def get_cwd(self) -> Optional[str]:
         return self.work_dir
 
-    def open_output_file(self):
-        if self.output_file is not None:
-            self.output_fd = open(self.output_file, "w")
-
-    def close_output_file(self):
-        if self.output_fd is not None:
-            self.output_fd.close()
-            self.output_fd = None
+    def run(self, verbose: bool = False) -> int:
+        if self.split_pieces:
+            argv = [word for piece in self.cmd_line for word in shlex.split(str(piece))]
+        else:
+            argv = [str(a) for a in self.cmd_line]
+        if verbose:
+            print("run:", argv)
+        if self.output_file is None:
+            done = subprocess.run(argv, cwd=self.work_dir)
+        else:
+            with open(self.output_file, "w") as sink:
+                done = subprocess.run(argv, cwd=self.work_dir, stdout=sink, stderr=subprocess.STDOUT)
+        self.returncode = done.returncode
+        return done.returncode
 
 
 def run_job(job: Job, verbose: bool = False) -> None:
-    args = " ".join(job.cmd())
-    if verbose:
-        print(f"args = {args}")
-    job.open_output_file()
-    try:
-        proc = subprocess.run(args=args, shell=True, stdout=job.get_stdout(), stderr=job.get_stderr(),
-                              cwd=job.get_cwd())
-    finally:
-        job.close_output_file()
-    assert proc.returncode == 0, f"'{args}' failed with exit code {proc.returncode}"
+    rc = job.run(verbose)
+    if rc != 0:
+        raise RuntimeError(f"{job.cmd_line!r} failed with exit code {rc}"
+                           + (f" (output in {job.output_file})" if job.output_file else ""))

@@ -187,7 +187,7 @@ def sweep_main(args):
     cfg = SweepConfig(args)
     cmd_lines = get_sweep_cmd_lines(cfg.search_space)
     if cfg.flush_cache:
-        flush = Job(cmd_line=["sudo", "bash -c", "\"echo 1 > /proc/sys/vm/drop_caches\""])
+        flush = Job(cmd_line=["sudo", "bash", "-c", "echo 1 > /proc/sys/vm/drop_caches"], split_pieces=False)
     else:
         flush = None
     sync_job = Job(cmd_line=["sync"])
