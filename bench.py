@@ -45,7 +45,9 @@ def parse():
     ap.add_argument("--sp", type=int, default=1,
                     help="Ulysses sequence-parallel degree: --seq is the FULL sequence, every rank holds seq/sp tokens "
                          "(config 4: --sp 8 --seq 131072); ZeRO-3 still shards over all ranks")
-    ap.add_argument("--moe-nccl", action="store_true", help="Mixtral: NCCL all_to_all_single path instead of the fused one")
+    ap.add_argument("--moe-nccl", action="store_true", help="Mixtral: NCCL all_to_all_single exchange (the default)")
+    ap.add_argument("--moe-fused", action="store_true",
+                    help="Mixtral: symmetric-memory dispatch/combine + grouped expert GEMM (moe/fused_ep.py)")
     ap.add_argument("--fp8-experts", action="store_true", help="Mixtral: e4m3 expert GEMMs in forward")
     ap.add_argument("--no-extras", action="store_true",
                     help="skip the secondary measurements (exposed communication, fused-path rooflines, the line at "
@@ -430,6 +432,8 @@ def run_reference(args):
 
 def main():
     args = parse()
+    if not args.moe_fused:
+        args.moe_nccl = True
     if args.impl == "reference":
         try:
             run_reference(args)

@@ -241,6 +241,7 @@ __global__ void wait_channel_kernel(Peers P, int channel, uint32_t epoch) { wait
 // out[i] = mean over `members` (ranks in the column group) of their symmetric shard; fp32 accumulate.
 struct Members {
   int idx[kMaxPeers];
+  float w[kMaxPeers];   // out = sum_k w[k] * shard[idx[k]]  (mean: 1/count; H-RR: 1/(rings*ring size); push-sum: alpha ratios)
   int count;
 };
 template <typename T>
@@ -263,27 +264,27 @@ __device__ __forceinline__ void subset_mean_body(const SubsetMeanArgs<T>& A) {
   if (blockIdx.x == 0) signal_all(P, 2, epoch);
   if (!wait_all(P, 2, epoch, 103)) return;
   const long long nvec = n >> 3;
-  const float inv = 1.0f / (float)M.count;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
        i += (long long)gridDim.x * blockDim.x) {
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int k = 0; k < M.count; ++k) {
       const uint4 r = ld_peer16(reinterpret_cast<const T*>(P.buf[M.idx[k]]) + i * 8);
       const T* h = reinterpret_cast<const T*>(&r);
+      const float wk = M.w[k];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += to_f32<T>(h[e]);
+      for (int e = 0; e < 8; ++e) acc[e] += wk * to_f32<T>(h[e]);
     }
     uint4 o;
     T* oh = reinterpret_cast<T*>(&o);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) oh[e] = from_f32<T>(acc[e] * inv);
+    for (int e = 0; e < 8; ++e) oh[e] = from_f32<T>(acc[e]);
     *reinterpret_cast<uint4*>(out + i * 8) = o;
   }
   for (long long i = (nvec << 3) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (long long)gridDim.x * blockDim.x) {
     float acc = 0.f;
-    for (int k = 0; k < M.count; ++k) acc += to_f32<T>(reinterpret_cast<const T*>(P.buf[M.idx[k]])[i]);
-    out[i] = from_f32<T>(acc * inv);
+    for (int k = 0; k < M.count; ++k) acc += M.w[k] * to_f32<T>(reinterpret_cast<const T*>(P.buf[M.idx[k]])[i]);
+    out[i] = from_f32<T>(acc);
   }
   __syncthreads();
   __shared__ unsigned int last;
@@ -583,21 +584,35 @@ SXB_API int sxb_symm_wait(const void* const* bufs, const void* const* sigs, int 
   return SXB_OK;
 }
 
+SXB_API int sxb_symm_subset_wsum(const void* const* bufs, const void* const* sigs, int rank, int world,
+                                 const int* members, const float* weights, int n_members, void* out, long long n,
+                                 int dtype, unsigned int epoch, void* counter, int max_ctas, void* stream);
 // K9.  members: host array of `n_members` group ranks (must contain `rank`); out: local (non-symmetric) result.
-static int fill_members(Members& M, const int* members, int n_members) {
+static int fill_members(Members& M, const int* members, int n_members, const float* weights = nullptr) {
   if (n_members < 1 || n_members > kMaxPeers) return SXB_ERR_BAD_ARG;
   M.count = n_members;
-  for (int i = 0; i < kMaxPeers; ++i) M.idx[i] = i < n_members ? members[i] : 0;
+  for (int i = 0; i < kMaxPeers; ++i) {
+    M.idx[i] = i < n_members ? members[i] : 0;
+    M.w[i] = i < n_members ? (weights ? weights[i] : 1.0f / (float)n_members) : 0.f;
+  }
   return SXB_OK;
 }
 SXB_API int sxb_symm_subset_mean(const void* const* bufs, const void* const* sigs, int rank, int world,
                                  const int* members, int n_members, void* out, long long n, int dtype,
                                  unsigned int epoch, void* counter, int max_ctas, void* stream) {
+  return sxb_symm_subset_wsum(bufs, sigs, rank, world, members, nullptr, n_members, out, n, dtype, epoch, counter,
+                              max_ctas, stream);
+}
+// K9, general form: out = sum_k weights[k] * shard of members[k] (weights == NULL: the mean).  One kernel serves RR
+// (all replicas), shuffle (my ring), H-RR (two-level mean as per-member weights) and Gossip push-sum (alpha ratios).
+SXB_API int sxb_symm_subset_wsum(const void* const* bufs, const void* const* sigs, int rank, int world,
+                                 const int* members, const float* weights, int n_members, void* out, long long n,
+                                 int dtype, unsigned int epoch, void* counter, int max_ctas, void* stream) {
   Peers P;
   int rc = fill_peers(P, bufs, sigs, rank, world);
   if (rc) return rc;
   Members M;
-  if ((rc = fill_members(M, members, n_members))) return rc;
+  if ((rc = fill_members(M, members, n_members, weights))) return rc;
   const int grid = grid_cap(n / 8 + 1, max_ctas);
   cudaStream_t s = (cudaStream_t)stream;
   if (dtype == kBF16) {

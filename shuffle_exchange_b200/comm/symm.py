@@ -30,6 +30,7 @@ _n.register({
     "sxb_symm_signal": "ppiiiip",
     "sxb_symm_barrier": "ppiiiip",
     "sxb_symm_subset_mean": "ppiipiplii" "pip",
+    "sxb_symm_subset_wsum": "ppiippiplii" "pip",
     "sxb_symm_all_gather": "ppiilplpiiip",
     "sxb_symm_a2a_rows": "ppiippppiipip",
     "sxb_symm_hang_info": "p",
@@ -117,7 +118,11 @@ class SymmGroup:
 
     @classmethod
     def get(cls, group=None) -> "SymmGroup":
-        key = id(group) if group is not None else 0
+        # keyed by the group's NAME (stable for the life of the process group; id() of a collected group object can be
+        # re-used by a different group)
+        key = getattr(group, "group_name", None) if group is not None else 0
+        if key is None:
+            key = id(group)
         inst = cls._instances.get(key)
         if inst is None:
             inst = cls._instances[key] = SymmGroup(group)
@@ -186,13 +191,19 @@ class SymmGroup:
             _n.call("sxb_symm_wait", buf.bufs, buf.sigs, self.rank, self.world, int(channel), int(e), _n.stream_ptr())
 
     # ------------------------------------------------------------------------------------- K9
-    def subset_mean(self, src: SymmBuffer, members: List[int], out: torch.Tensor, n: int, max_ctas: int = 0):
+    def subset_mean(self, src: SymmBuffer, members: List[int], out: torch.Tensor, n: int, max_ctas: int = 0,
+                    weights: Optional[List[float]] = None):
+        """``out = sum_k weights[k] * shard(members[k])`` (``weights=None``: the mean) read straight out of the
+        members' symmetric buffers.  Every rank of the group must call it in the same step (each with its own member
+        list): the kernel handshakes with ALL ranks before reading and tells all of them when it is done."""
         epoch = src.next_epoch(CH_AVG_READY)
         src.epochs[CH_AVG_READ] = epoch
         arr = (ctypes.c_int * len(members))(*members)
-        _n.call("sxb_symm_subset_mean", src.bufs, src.sigs, self.rank, self.world,
-                ctypes.cast(arr, ctypes.c_void_p), len(members), out.data_ptr(), int(n),
-                _n.dtype_code(out.dtype), int(epoch), self._ctr(1), int(max_ctas), _n.stream_ptr())
+        warr = (ctypes.c_float * len(members))(*weights) if weights is not None else None
+        _n.call("sxb_symm_subset_wsum", src.bufs, src.sigs, self.rank, self.world,
+                ctypes.cast(arr, ctypes.c_void_p), ctypes.cast(warr, ctypes.c_void_p) if warr is not None else None,
+                len(members), out.data_ptr(), int(n), _n.dtype_code(out.dtype), int(epoch), self._ctr(1),
+                int(max_ctas), _n.stream_ptr())
 
     # ------------------------------------------------------------------------------------- K2
     def barrier(self, buf: SymmBuffer, channel: int = CH_AG_READY):
@@ -252,8 +263,8 @@ class ReplicaAverageKernel:
     def fits(self, shard: torch.Tensor) -> bool:
         return shard.numel() <= self.buf.tensor.numel() and shard.dtype == self.buf.tensor.dtype
 
-    def run(self, shard: torch.Tensor, members: List[int]):
+    def run(self, shard: torch.Tensor, members: List[int], weights: Optional[List[float]] = None):
         n = shard.numel()
         self.sg.wait_readers(self.buf, CH_AVG_READ)           # peers finished reading the previous contents
         self.buf.tensor[:n].copy_(shard.view(-1))
-        self.sg.subset_mean(self.buf, members, shard.view(-1), n)
+        self.sg.subset_mean(self.buf, members, shard.view(-1), n, weights=weights)

@@ -157,9 +157,12 @@ class FusedEP:
         """Raise if any plan since the last call found a receive buffer too small (one small D2H read)."""
         if not self._overflow_sources:
             return
-        flags = torch.stack([t[self.E + 2 * self.L + 1] for t in self._overflow_sources])
+        flags = torch.stack([t[self.E + 2 * self.L + 1] for t in self._overflow_sources]).max().reshape(1)
         self._overflow_sources = []
-        if int(flags.max().item()) != 0:
+        if self.group is not None:
+            # every rank must reach the same verdict, or the ranks that did not overflow wait forever for the one that raised
+            torch.distributed.all_reduce(flags, op=torch.distributed.ReduceOp.MAX, group=self.group)
+        if int(flags.item()) != 0:
             raise RuntimeError(
                 f"expert-parallel receive buffer overflow: routing sent more than {self.cap_rows} rows to one rank; "
                 "raise the MoE layer's ep_capacity_factor")

@@ -193,10 +193,16 @@ class ReplicaAverager:
             return self._gossip_push(shards)
         for shard in shards:
             if self.method == "RR":
-                shard.div_(self.n_replicas)
-                dist.all_reduce(shard, group=self.column_pg)
+                # on symmetric memory: the same one-shot kernel with every replica as a member
+                if not self._try_fused(shard, list(range(self.n_replicas))):
+                    shard.div_(self.n_replicas)
+                    dist.all_reduce(shard, group=self.column_pg)
             elif self.method == "H-RR":
-                self._hierarchical(shard)
+                # reduce-to-head / all-reduce between heads / broadcast sums every replica once and divides by their
+                # number: numerically the global mean.  On a switch there is no hierarchy to exploit, so the one-shot
+                # kernel reads every replica directly; the three-hop p2p form remains the NCCL / gloo path.
+                if not self._try_fused(shard, list(range(self.n_replicas))):
+                    self._hierarchical(shard)
             else:
                 self._subset_mean(shard, self.schedule.ring_of(self.replica))
 
@@ -267,26 +273,32 @@ class ReplicaAverager:
     def _gossip_push(self, shards: List[torch.Tensor]):
         dests = self.schedule.gossip_destinations(self.step_count)
         senders_to_me = [r for r, d in enumerate(dests) if d == self.replica and r != self.replica]
-        self.alpha *= 0.5
-        dev = shards[0].device
-        payload_alpha = torch.tensor([self.alpha], dtype=torch.float32, device=dev)
+        # Push-sum weights depend on the (shared, seeded) schedule only, never on data: every rank tracks the weight of
+        # EVERY replica, so no alpha travels with the payload and nothing is read back from the device.
+        if not hasattr(self, "_alphas"):
+            self._alphas = [1.0 / self.n_replicas] * self.n_replicas
+            self._pending_alpha = [0.0] * self.n_replicas
+        for r in range(self.n_replicas):           # what merge() of the previous step added, then this step's halving
+            self._alphas[r] += self._pending_alpha[r]
+            self._pending_alpha[r] = 0.0
+        sent = [a * 0.5 for a in self._alphas]
+        self._alphas = list(sent)
+        for r, d in enumerate(dests):
+            self._pending_alpha[d] += sent[r]
+        self.alpha = self._alphas[self.replica]
         P2P = torch.distributed.P2POp
         ops, recv = [], []
         dst = self.column_ranks[dests[self.replica]]
-        ops.append(P2P(torch.distributed.isend, payload_alpha, dst, self.column_pg))
         for sh in shards:
             ops.append(P2P(torch.distributed.isend, sh, dst, self.column_pg))
         for s in senders_to_me:
-            a = torch.empty(1, dtype=torch.float32, device=dev)
             bufs = [torch.empty_like(sh) for sh in shards]
-            recv.append((a, bufs))
-            ops.append(P2P(torch.distributed.irecv, a, self.column_ranks[s], self.column_pg))
+            recv.append((sent[s], bufs))
             for b in bufs:
                 ops.append(P2P(torch.distributed.irecv, b, self.column_ranks[s], self.column_pg))
         for w in torch.distributed.batch_isend_irecv(ops):
             w.wait()
-        for a, bufs in recv:
-            self._inbox.append((float(a.item()), bufs))
+        self._inbox.extend(recv)
 
     def gossip_merge(self, masters: List[torch.Tensor]):
         """Start-of-step merge of queued messages: w <- (alpha w + sum alpha' w') / (alpha + sum alpha')."""
@@ -302,7 +314,7 @@ class ReplicaAverager:
         self._inbox = []
 
     # ------------------------------------------------------------------------------------ fused
-    def _try_fused(self, shard, members) -> bool:
+    def _try_fused(self, shard, members, weights=None) -> bool:
         if self.fused is False or not shard.is_cuda:
             return False
         try:
@@ -315,7 +327,7 @@ class ReplicaAverager:
             if self.fused:
                 raise RuntimeError("fused replica averaging requested but symmetric memory is unavailable")
             return False
-        self._symm.run(shard, [self.column_ranks.index(self.column_ranks[m]) for m in members])
+        self._symm.run(shard, list(members), weights)       # replica id == rank inside the column group
         return True
 
     def state_dict(self):
