@@ -579,7 +579,10 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                 for p in fg.params:
                     p._sxb_calls = 0
             if u is self.root_unit or u.module is self.module:
-                self._attach_unit(u)       # no module-level backward hook for the root unit
+                # no module-level backward hook for the root unit: make sure it is gathered (a pipeline stage runs the
+                # backward of an earlier micro-batch after another micro-batch's backward released it) and attached
+                self._fetch(u)
+                self._attach_unit(u)
 
     def _post_backward(self):
         # units whose gradients never (all) arrived — unused parameters — are flushed here

@@ -157,7 +157,7 @@ class DeepSpeedZeroOptimizer(ShardedOptimizerBase):
             # every distinct parameter received all the contributions its forward uses announced
             if getattr(fg, "_reduced_this_micro_step", False) and self._reduce_now():
                 raise RuntimeError(
-                    f"ZeRO-{self.zero_stage}: a gradient contribution for flat group {fg.group_index} arrived after its "
+                    f"ZeRO-{self.zero_stage}: a gradient contribution for flat group {fg.index} arrived after its "
                     "reduction was launched (a parameter used by both main-grad ops and plain autograd ops, or a "
                     "forward that ran outside the counted window); its gradient would be dropped")
             param._sxb_calls = getattr(param, "_sxb_calls", 0) + 1

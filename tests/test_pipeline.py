@@ -1,6 +1,7 @@
 """Pipeline parallelism on gloo: topology math, 1F1B schedule invariants, 2-stage training parity."""
 import copy
 
+import pytest
 import torch
 import torch.nn as nn
 
@@ -91,3 +92,57 @@ def _pipe_worker(rank, world):
 
 def test_two_stage_training_matches_sequential():
     run_dist(_pipe_worker, 2)
+
+
+def _pipe_zero_worker(rank, world, zero_stage):
+    """PP=2 x DP=2 with the stage's data-parallel pair running ZeRO-``zero_stage`` (the reference asserts stage < 2 under
+    pipeline parallelism, pipe/engine.py:77-78): two batches must match unsharded AdamW on the same data."""
+    import shuffle_exchange_b200 as ds
+    from shuffle_exchange_b200.runtime.pipe.module import LayerSpec, PipelineModule
+    torch.manual_seed(0)
+    d, micro, gas = 16, 4, 2
+    ref = nn.Sequential(*[_Block(d) for _ in range(4)])
+    ref_state = copy.deepcopy(ref.state_dict())
+    net = PipelineModule([LayerSpec(_Block, d) for _ in range(4)], num_stages=2, loss_fn=nn.MSELoss(),
+                         partition_method="uniform")
+    own = {k: v for k, v in ref_state.items() if int(k.split(".")[0]) in range(net._local_start, net._local_stop)}
+    net.load_state_dict(own, strict=True)
+    engine, _, _, _ = ds.initialize(model=net, model_parameters=[p for p in net.parameters()], config={
+        "train_micro_batch_size_per_gpu": micro, "gradient_accumulation_steps": gas, "steps_per_print": 10 ** 9,
+        "bf16": {"enabled": True}, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}},
+        "zero_optimization": {"stage": zero_stage, "stage3_param_persistence_threshold": 0}})
+    assert engine.zero_optimization_stage() == zero_stage
+    dp_rank = engine.grid.data_parallel_id
+    g = torch.Generator().manual_seed(11)
+    # data[batch][dp][micro] ; both stages of a replica draw the same stream (inputs enter at stage 0, labels at stage 1)
+    data = [[[(torch.randn(micro, d, generator=g), torch.randn(micro, d, generator=g)) for _ in range(gas)]
+             for _ in range(2)] for _ in range(2)]
+    losses = []
+    for b in range(2):
+        it = iter([(x.to(torch.bfloat16), y.to(torch.bfloat16)) for x, y in data[b][dp_rank]])
+        losses.append(float(engine.train_batch(data_iter=it)))
+    # oracle: fp32 master, bf16 compute weights, mean gradient over 2 replicas x gas micro-batches
+    master = [p.detach().float().clone().requires_grad_() for p in ref.parameters()]
+    opt = torch.optim.AdamW(master, lr=1e-2, weight_decay=0.0)
+    want = []
+    for b in range(2):
+        for p, m in zip(ref.parameters(), master):
+            p.data = m.detach().to(torch.bfloat16).float()
+        ref.zero_grad()
+        tot = 0.0
+        for dp in range(2):
+            for x, y in data[b][dp]:
+                l = nn.functional.mse_loss(ref(x.to(torch.bfloat16).float()), y.to(torch.bfloat16).float()) / (2 * gas)
+                l.backward()
+                tot += float(l)
+        for p, m in zip(ref.parameters(), master):
+            m.grad = p.grad.clone()
+        opt.step()
+        want.append(tot)
+    assert all(abs(a - b) < 3e-2 * max(1.0, abs(b)) for a, b in zip(losses, want)), (zero_stage, losses, want)
+    assert losses[1] < losses[0] + 1e-3 or want[1] >= want[0], (losses, want)
+
+
+@pytest.mark.parametrize("zero_stage", [2, 3])
+def test_zero_sharding_inside_pipeline_stages(zero_stage):
+    run_dist(_pipe_zero_worker, 4, (zero_stage,))
