@@ -1,109 +1,112 @@
-"""Straight-through quantisers and top-k binarizer (reference: ``deepspeed/compression/utils.py:13-189``)."""
+"""Fake-quantisation operators with straight-through gradients, and the top-k mask used by movement pruning.
+
+All four quantisers (symmetric / asymmetric uniform, ternary, binary) share one autograd shell: reshape to
+``[num_groups, -1]``, compute the per-group reconstruction in :meth:`_reconstruct`, reshape back; the backward pass
+hands the incoming gradient to the input untouched.  Call signature as in the reference
+(``deepspeed/compression/utils.py``): ``Quantizer.apply(input, num_bits, min_value, max_value, num_groups)``."""
 import torch
 from torch import autograd
 
 
 class TopKBinarizer(autograd.Function):
-    """mask = 1 for the ``threshold`` fraction of largest scores (``sigmoid`` maps a learnable threshold to (0,1));
-    gradients pass straight through to the scores and (summed) to the threshold."""
+    """``mask[i] = 1`` for the ``threshold`` fraction of entries with the largest score, else 0.  With ``sigmoid`` the
+    threshold is a learnable logit.  Gradient: straight through to the scores; to the threshold, the masked sum."""
 
     @staticmethod
-    def forward(ctx, inputs: torch.Tensor, threshold: float, sigmoid: bool):
-        if sigmoid:
-            threshold = torch.sigmoid(threshold).item()
-        ctx.sigmoid = sigmoid
-        mask = inputs.clone()
-        _, idx = inputs.flatten().sort(descending=True)
-        j = int(threshold * inputs.numel())
-        flat = mask.flatten()
-        flat[idx[j:]] = 0.0
-        flat[idx[:j]] = 1.0
+    def forward(ctx, inputs: torch.Tensor, threshold, sigmoid: bool):
+        frac = torch.sigmoid(threshold).item() if sigmoid else float(threshold)
+        keep = int(frac * inputs.numel())
+        mask = torch.zeros_like(inputs)
+        if keep > 0:
+            top = torch.topk(inputs.flatten(), keep, sorted=False).indices
+            mask.view(-1)[top] = 1.0
+        ctx.learn_threshold = bool(sigmoid)
         ctx.save_for_backward(mask)
         return mask
 
     @staticmethod
-    def backward(ctx, gradOutput):
+    def backward(ctx, grad_mask):
         mask, = ctx.saved_tensors
-        if ctx.sigmoid:
-            return gradOutput.clone(), ((gradOutput * mask).sum()).view(-1), None
-        return gradOutput.clone(), None, None
+        d_threshold = (grad_mask * mask).sum().view(-1) if ctx.learn_threshold else None
+        return grad_mask.clone(), d_threshold, None
 
 
-class SymQuantizer(torch.autograd.Function):
-    """Per-group symmetric uniform quantisation with a straight-through gradient."""
-
-    @staticmethod
-    def forward(ctx, input, num_bits, min_value=None, max_value=None, num_groups=1):
-        assert (min_value is None and max_value is None) or (min_value is not None and max_value is not None and num_groups == 1)
-        q_range = 2 ** num_bits
-        shape = input.shape
-        if min_value is None:
-            x = input.reshape(num_groups, -1)
-            max_in = torch.amax(torch.abs(x), dim=-1).view(num_groups, -1)
-        else:
-            x = input.reshape(1, -1)
-            max_in = torch.max(min_value.abs(), max_value).view(-1)
-        scale = 2 * max_in / q_range
-        scale = torch.where(scale == 0, torch.ones_like(scale), scale)
-        out = (x / scale).round().clamp(-q_range // 2, q_range // 2 - 1) * scale
-        return out.reshape(shape).contiguous()
+class _StraightThrough(autograd.Function):
+    """forward = per-group reconstruction, backward = identity on the input."""
 
     @staticmethod
-    def backward(ctx, grad_output):
-        return grad_output.clone(), None, None, None, None
+    def _reconstruct(x, num_bits, lo, hi):          # x: [groups, n]
+        raise NotImplementedError
 
+    @classmethod
+    def _check_range(cls, lo, hi, num_groups):
+        both_none, both_set = lo is None and hi is None, lo is not None and hi is not None
+        if not (both_none or (both_set and num_groups == 1)):
+            raise AssertionError("min_value / max_value go together and require num_groups == 1")
 
-class AsymQuantizer(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, input, num_bits, min_value=None, max_value=None, num_groups=1):
-        assert (min_value is None and max_value is None) or (min_value is not None and max_value is not None and num_groups == 1)
-        q_range = 2 ** num_bits
-        shape = input.shape
-        x = input.reshape(num_groups, -1)
-        if min_value is None:
-            min_value, max_value = x.amin(dim=-1, keepdim=True), x.amax(dim=-1, keepdim=True)
-        scale = (max_value - min_value) / q_range
-        scale = torch.where(scale == 0, torch.ones_like(scale), scale)
-        zero_point = (min_value / scale).round() * scale
-        out = ((x - zero_point) / scale).round().clamp(0, q_range - 1) * scale + zero_point
-        return out.reshape(shape).contiguous()
+    @classmethod
+    def forward(cls, ctx, input, num_bits, min_value=None, max_value=None, num_groups=1):
+        cls._check_range(min_value, max_value, num_groups)
+        grouped = input.reshape(num_groups, -1)
+        return cls._reconstruct(grouped, num_bits, min_value, max_value).reshape(input.shape).contiguous()
 
     @staticmethod
     def backward(ctx, grad_output):
         return grad_output.clone(), None, None, None, None
 
 
-class TernaryQuantizer(torch.autograd.Function):
-    """{-a, 0, +a} with threshold 0.7 * mean|x| per group (TWN)."""
+def _safe(scale):
+    return torch.where(scale == 0, torch.ones_like(scale), scale)
+
+
+class SymQuantizer(_StraightThrough):
+    """Uniform levels symmetric around zero: step = 2 * max|x| / 2^bits per group (or from the given range)."""
 
     @staticmethod
-    def forward(ctx, input, num_bits, min_value=None, max_value=None, num_groups=1):
-        assert min_value is None and max_value is None
-        x = input.reshape(num_groups, -1)
-        n = x.shape[1]
-        m = x.norm(p=1, dim=1).div(n)
-        thres = (0.7 * m).view(-1, 1)
-        pos, neg = (x > thres).type(input.type()), (x < -thres).type(input.type())
-        mask = (x.abs() > thres).type(input.type())
-        alpha = ((mask * x).abs().sum(dim=1) / mask.sum(dim=1).clamp(min=1)).view(-1, 1)
-        return (alpha * pos - alpha * neg).reshape(input.shape).contiguous()
+    def _reconstruct(x, num_bits, lo, hi):
+        levels = 2 ** num_bits
+        peak = x.abs().amax(dim=-1, keepdim=True) if lo is None else torch.max(lo.abs(), hi).view(-1)
+        step = _safe(2 * peak / levels)
+        return (x / step).round().clamp(-levels // 2, levels // 2 - 1) * step
+
+
+class AsymQuantizer(_StraightThrough):
+    """Uniform levels between the group's min and max (or the given range), zero point snapped to the grid."""
 
     @staticmethod
-    def backward(ctx, grad_output):
-        return grad_output.clone(), None, None, None, None
+    def _reconstruct(x, num_bits, lo, hi):
+        levels = 2 ** num_bits
+        if lo is None:
+            lo, hi = x.amin(dim=-1, keepdim=True), x.amax(dim=-1, keepdim=True)
+        step = _safe((hi - lo) / levels)
+        zero = (lo / step).round() * step
+        return ((x - zero) / step).round().clamp(0, levels - 1) * step + zero
 
 
-class BinaryQuantizer(torch.autograd.Function):
-    """sign(x) * mean|x| per group (BWN)."""
+class TernaryQuantizer(_StraightThrough):
+    """Ternary weight networks: {-a, 0, +a} with threshold 0.7 * mean|x| and a = mean of the surviving magnitudes."""
+
+    @classmethod
+    def _check_range(cls, lo, hi, num_groups):
+        if lo is not None or hi is not None:
+            raise AssertionError("the ternary quantiser takes no value range")
 
     @staticmethod
-    def forward(ctx, input, num_bits, min_value=None, max_value=None, num_groups=1):
-        assert min_value is None and max_value is None
-        x = input.reshape(num_groups, -1)
-        n = x.shape[1]
-        m = x.norm(p=1, dim=1, keepdim=True).div(n)
-        return x.sign().mul(m).reshape(input.shape).contiguous()
+    def _reconstruct(x, num_bits, lo, hi):
+        cut = 0.7 * x.abs().mean(dim=1, keepdim=True)
+        alive = (x.abs() > cut).to(x.dtype)
+        a = (alive * x.abs()).sum(dim=1, keepdim=True) / alive.sum(dim=1, keepdim=True).clamp(min=1)
+        return a * torch.sign(x) * alive
+
+
+class BinaryQuantizer(_StraightThrough):
+    """Binary weight networks: sign(x) * mean|x| per group."""
+
+    @classmethod
+    def _check_range(cls, lo, hi, num_groups):
+        if lo is not None or hi is not None:
+            raise AssertionError("the binary quantiser takes no value range")
 
     @staticmethod
-    def backward(ctx, grad_output):
-        return grad_output.clone(), None, None, None, None
+    def _reconstruct(x, num_bits, lo, hi):
+        return torch.sign(x) * x.abs().mean(dim=1, keepdim=True)
