@@ -42,7 +42,32 @@ struct Params {
   int scatter_rows;
   void* out_peers[16];
   void* out2_peers[16];
+  // Packed sequences ("varlen"): cu_seqlens[nseq + 1] row offsets into tensors of shape [1, S = total tokens, H, D];
+  // blockIdx.y is then the sequence index, tiles past a sequence's end exit, and lse / delta are laid out [Hq, S].
+  const int* cu_seqlens;
+  // Ragged inference (forward only): one CTA per attention atom (int32 [n_atoms, 6], blockIdx.z), queries from the
+  // ragged [T, Hq, D] tensor, K/V from the paged cache through the sequence's block table.
+  const int* atoms;
+  const int* block_tables;   // [n_seqs, max_blocks]
+  int max_blocks, block_size;
 };
+
+// The rows of the tensors one CTA works on: sequence b of a dense batch, or sequence b of a packed one.
+struct Win { int off, len, tb; };   // row offset inside TMA batch index `tb`, length
+__device__ __forceinline__ Win window(const Params& p, int b) {
+  Win w;
+  if (p.cu_seqlens != nullptr) {
+    w.off = p.cu_seqlens[b];
+    w.len = p.cu_seqlens[b + 1] - w.off;
+    w.tb = 0;
+  } else {
+    w.off = 0; w.len = p.S; w.tb = b;
+  }
+  return w;
+}
+__device__ __forceinline__ long long stat_base(const Params& p, const Win& w, int b, int h) {
+  return p.cu_seqlens != nullptr ? (long long)h * p.S + w.off : ((long long)b * p.Hq + h) * p.S;
+}
 
 // Destination row pointer of output row (b, s): local buffer, or the owning peer's buffer when scattering.
 __device__ __forceinline__ __nv_bfloat16* out_row_ptr(const Params& p, bool second, int b, int s) {
@@ -170,11 +195,25 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // tile index is the SLOWEST grid dimension: CTAs are handed out in linear block order, so every (head, batch)
   // of the heaviest causal tile starts before any lighter tile (longest-first packing over the 148 SMs)
-  const int qt = gridDim.z - 1 - blockIdx.z;
   const int h = blockIdx.x, b = blockIdx.y;
   const int hk = h / (p.Hq / p.Hk);
-  const int q0 = qt * BQ;
-  const int kv_len = p.causal ? min(p.S, q0 + BQ) : p.S;
+  // The tile: TMA row of its first query, that query's position inside its sequence, valid rows, keys it attends to.
+  Win w;
+  int q_row0, q_pos0, q_rows, kv_len;
+  const int* pages = nullptr;           // paged K/V: this sequence's block table
+  if (p.atoms != nullptr) {
+    // attention atom (csrc/host/ragged_host.cpp): (seq, q_start_idx, q_len, global_q_idx, kv_blocks, total_extent)
+    const int* a = p.atoms + 6 * (int)blockIdx.z;
+    w.off = 0; w.len = 0; w.tb = 0;
+    q_row0 = a[1]; q_rows = a[2]; q_pos0 = a[3]; kv_len = a[5];
+    pages = p.block_tables + (long long)a[0] * p.max_blocks;
+  } else {
+    const int q0 = (gridDim.z - 1 - blockIdx.z) * BQ;
+    w = window(p, b);
+    if (q0 >= w.len) return;   // packed mode: tile beyond this sequence (uniform over the CTA and its cluster peer)
+    q_row0 = w.off + q0; q_pos0 = q0; q_rows = min(BQ, w.len - q0);
+    kv_len = p.causal ? min(w.len, q0 + BQ) : w.len;
+  }
   const int nblk = (kv_len + BC - 1) / BC;
 
   if (warp == 0 && lane == 0) {
@@ -212,9 +251,35 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (elected) {
       mbar_expect_tx(q_full, L::kQ);
       for (int hh = 0; hh < NH; ++hh)
-        tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, q0, b);
+        tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, q_row0, w.tb);
     }
     __syncwarp();
+    // One 64-key tile of K or V into a ring slot: contiguous rows, or the rows of the page(s) the block table names
+    // (tensor map {D, Hk, block_size, n_blocks}; pages smaller than the tile take several boxes; a tile that reaches
+    // past the sequence re-reads its last page, the rows are masked).
+    auto load_kv = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* bar, int j) {
+      if (pages == nullptr) {
+        if (MC > 1) {
+          tma_load_4d_mc(dst + crank * (BC * 128), tm, bar, crank * 64, hk, w.off + j * BC, w.tb, 3);
+        } else {
+          for (int hh = 0; hh < NH; ++hh)
+            tma_load_4d(dst + hh * (BC * 128), tm, bar, hh * 64, hk, w.off + j * BC, w.tb);
+        }
+        return;
+      }
+      const int bs = p.block_size, sub = min(bs, BC), last = (kv_len - 1) / bs;
+      for (int r = 0; r < BC; r += sub) {
+        const int pos = j * BC + r;
+        const int blk = min(pos / bs, last);
+        const int page = pages[blk], in_page = (blk == pos / bs) ? pos % bs : 0;
+        if (MC > 1) {
+          tma_load_4d_mc(dst + crank * (BC * 128) + r * 128, tm, bar, crank * 64, hk, in_page, page, 3);
+        } else {
+          for (int hh = 0; hh < NH; ++hh)
+            tma_load_4d(dst + hh * (BC * 128) + r * 128, tm, bar, hh * 64, hk, in_page, page);
+        }
+      }
+    };
     // K and V rings advance independently (polling state machine): a K slot is recycled right
     // after its QK^T, so the next-but-one K tile is in flight ~2 iterations before it is needed.
     int jk = 0, jv = 0;
@@ -228,14 +293,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int st = jk & 1;
         if (elected) {
           mbar_expect_tx(&k_full[st], L::kKV);
-          if (MC > 1) {
-            tma_load_4d_mc(smem + L::oK + st * L::kKV + crank * (BC * 128), &tmK, &k_full[st], crank * 64, hk,
-                           jk * BC, b, 3);
-          } else {
-            for (int hh = 0; hh < NH; ++hh)
-              tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &k_full[st], hh * 64, hk,
-                          jk * BC, b);
-          }
+          load_kv(&tmK, smem + L::oK + st * L::kKV, &k_full[st], jk);
         }
         __syncwarp();
         ++jk;
@@ -247,14 +305,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int st = jv & 1;
         if (elected) {
           mbar_expect_tx(&v_full[st], L::kKV);
-          if (MC > 1) {
-            tma_load_4d_mc(smem + L::oV + st * L::kKV + crank * (BC * 128), &tmV, &v_full[st], crank * 64, hk,
-                           jv * BC, b, 3);
-          } else {
-            for (int hh = 0; hh < NH; ++hh)
-              tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &v_full[st], hh * 64, hk,
-                          jv * BC, b);
-          }
+          load_kv(&tmV, smem + L::oV + st * L::kKV, &v_full[st], jv);
         }
         __syncwarp();
         ++jv;
@@ -317,7 +368,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int quad = warp & 3;
     const int row = quad * 32 + lane;
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
-    const int qpos = q0 + row;
+    const int qpos = q_pos0 + row;
     const float sc = p.scale * kLog2e;
     float m_run = -INFINITY, l_run = 0.f;
     for (int j = 0; j < nblk; ++j) {
@@ -326,14 +377,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       float s[64];
       ld_row64(tS + (j & 1) * BC + lane_off, s);
       const int k0 = j * BC;
-      const bool need_mask = (p.causal && (k0 + BC - 1 > q0)) || (k0 + BC > p.S);
+      const bool need_mask = (p.causal && (k0 + BC - 1 > q_pos0)) || (k0 + BC > kv_len);
       // row max on raw scores (scale > 0 commutes with max); 4 independent chains
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
       if (need_mask) {
 #pragma unroll
         for (int c = 0; c < 64; ++c) {
           const int kp = k0 + c;
-          const bool ok = (kp < p.S) && (!p.causal || kp <= qpos);
+          const bool ok = (kp < kv_len) && (!p.causal || kp <= qpos);
           s[c] = ok ? s[c] : -INFINITY;
           mx4[c & 3] = fmaxf(mx4[c & 3], s[c]);
         }
@@ -398,12 +449,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     {
       // tcgen05.ld is warp-collective (.sync.aligned): every lane issues it, only the global
       // stores are predicated on the row being inside the sequence.
-      const bool valid = qpos < p.S;
-      __nv_bfloat16* orow = out_row_ptr(p, false, b, valid ? qpos : 0) + (long long)h * D;
+      const bool valid = row < q_rows;
+      const int grow = valid ? q_row0 + row : q_row0;   // row of the [rows, H, D] tensors
+      __nv_bfloat16* orow = out_row_ptr(p, false, w.tb, grow) + (long long)h * D;
       // scattering forward keeps a LOCAL copy of O as well (p.out, pitch out2_stride): the backward needs
       // rowsum(dO * O) where the heads are, not where the sequence is
       __nv_bfloat16* orow_keep = (p.scatter_rows > 0 && p.out != nullptr)
-          ? reinterpret_cast<__nv_bfloat16*>(p.out) + ((long long)b * p.S + (valid ? qpos : 0)) * p.out2_stride +
+          ? reinterpret_cast<__nv_bfloat16*>(p.out) + ((long long)w.tb * p.S + grow) * p.out2_stride +
                 (long long)h * D
           : nullptr;
 #pragma unroll 1
@@ -425,7 +477,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
       }
       if (valid && p.lse)
-        p.lse[((long long)b * p.Hq + h) * p.S + qpos] =
+        p.lse[stat_base(p, w, b, h) - w.off + grow] =
             (l_run > 0.f) ? (m_run + log2f(l_run)) * kLn2 : -INFINITY;
     }
   }
@@ -482,9 +534,12 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = gridDim.z - 1 - blockIdx.z;   // heaviest causal tiles first across all heads
   const int h = blockIdx.x, b = blockIdx.y;
+  const Win w = window(p, b);
+  const int S_ = w.len;
   const int hk = h / (p.Hq / p.Hk);
   const int q0 = qt * BQ;
-  const int kv_len = p.causal ? min(p.S, q0 + BQ) : p.S;
+  if (q0 >= S_) return;
+  const int kv_len = p.causal ? min(S_, q0 + BQ) : S_;
   const int nblk = (kv_len + BC - 1) / BC;
 
   if (warp == 1) {
@@ -516,8 +571,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     if (elected) {
       mbar_expect_tx(q_full, 2 * L::kQ);
       for (int hh = 0; hh < NH; ++hh) {
-        tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, q0, b);
-        tma_load_4d(smem + L::oDO + hh * (BQ * 128), &tmDO, q_full, hh * 64, h, q0, b);
+        tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, w.off + q0, w.tb);
+        tma_load_4d(smem + L::oDO + hh * (BQ * 128), &tmDO, q_full, hh * 64, h, w.off + q0, w.tb);
       }
     }
     __syncwarp();
@@ -528,15 +583,15 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         mbar_expect_tx(&kv_full[st], 2 * L::kKV);
         if (MC > 1) {
           tma_load_4d_mc(smem + L::oK + st * L::kKV + crank * (BC * 128), &tmK, &kv_full[st], crank * 64, hk,
-                         j * BC, b, 3);
+                         w.off + j * BC, w.tb, 3);
           tma_load_4d_mc(smem + L::oV + st * L::kKV + crank * (BC * 128), &tmV, &kv_full[st], crank * 64, hk,
-                         j * BC, b, 3);
+                         w.off + j * BC, w.tb, 3);
         } else {
           for (int hh = 0; hh < NH; ++hh) {
             tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &kv_full[st], hh * 64, hk,
-                        j * BC, b);
+                        w.off + j * BC, w.tb);
             tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &kv_full[st], hh * 64, hk,
-                        j * BC, b);
+                        w.off + j * BC, w.tb);
           }
         }
       }
@@ -599,7 +654,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
     const int qpos = q0 + row;
     const float sc = p.scale * kLog2e;
-    const long long stat_idx = ((long long)b * p.Hq + h) * p.S + min(qpos, p.S - 1);
+    const long long stat_idx = stat_base(p, w, b, h) + min(qpos, S_ - 1);
     const float lse2 = p.lse[stat_idx] * kLog2e;
     const float dlt = p.delta[stat_idx];
     {
@@ -629,12 +684,12 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       const uint32_t tS = tmem + (j & 1) * 128 + lane_off + half * 32;
       ld_row32x2(tS, tS + 64, s, dp);
       const int k0 = j * BC + half * 32;
-      const bool need_mask = (p.causal && (k0 + 31 > q0)) || (k0 + 32 > p.S) || (q0 + BQ > p.S);
+      const bool need_mask = (p.causal && (k0 + 31 > q0)) || (k0 + 32 > S_) || (q0 + BQ > S_);
       if (need_mask) {
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
           const int kp = k0 + c;
-          const bool ok = (kp < p.S) && (!p.causal || kp <= qpos) && (qpos < p.S);
+          const bool ok = (kp < S_) && (!p.causal || kp <= qpos) && (qpos < S_);
           const float pr = ok ? fast_exp2(fmaf(s[c], sc, -lse2)) : 0.f;
           s[c] = pr * (dp[c] - dlt) * p.scale;
         }
@@ -660,13 +715,13 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     }
     if (!mbar_wait_to(dq_done, 0, 33)) goto done;
     tc_fence_after();
-    __nv_bfloat16* orow = out_row_ptr(p, false, b, min(qpos, p.S - 1)) + (long long)h * D;
+    __nv_bfloat16* orow = out_row_ptr(p, false, w.tb, w.off + min(qpos, S_ - 1)) + (long long)h * D;
 #pragma unroll 1
     for (int c = half * (D / 64); c < (half + 1) * (D / 64); ++c) {
       uint32_t o[32];
       tmem_ld_32x32(tDQ + lane_off + c * 32, o);
       tmem_ld_wait();
-      if (qpos < p.S) {
+      if (qpos < S_) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           uint4 w;
@@ -736,9 +791,12 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kt = blockIdx.z;                   // key tile 0 sees every query block: heaviest first
   const int hk = blockIdx.x, b = blockIdx.y;
+  const Win w = window(p, b);
+  const int S_ = w.len;
   const int group = p.Hq / p.Hk;
   const int n0 = kt * BQ;
-  const int nq_blocks = (p.S + BC - 1) / BC;
+  if (n0 >= S_) return;
+  const int nq_blocks = (S_ + BC - 1) / BC;
   const int i_start = p.causal ? (n0 / BC) : 0;
   const int per_head = nq_blocks - i_start;
   const int niter = per_head * group;
@@ -768,8 +826,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     if (elected) {
       mbar_expect_tx(kv_full, 2 * L::kKV);
       for (int hh = 0; hh < NH; ++hh) {
-        tma_load_4d(smem + L::oK + hh * (BQ * 128), &tmK, kv_full, hh * 64, hk, n0, b);
-        tma_load_4d(smem + L::oV + hh * (BQ * 128), &tmV, kv_full, hh * 64, hk, n0, b);
+        tma_load_4d(smem + L::oK + hh * (BQ * 128), &tmK, kv_full, hh * 64, hk, w.off + n0, w.tb);
+        tma_load_4d(smem + L::oV + hh * (BQ * 128), &tmV, kv_full, hh * 64, hk, w.off + n0, w.tb);
       }
     }
     __syncwarp();
@@ -780,8 +838,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     uint32_t ph = 1;
     auto stat_load = [&](int hh, int qr, float (&v)[4]) {
       const int qb = (i_start + qr) * BC;
-      const long long base = ((long long)b * p.Hq + hk * group + hh) * p.S;
-      const int q0i = min(qb + lane, p.S - 1), q1i = min(qb + 32 + lane, p.S - 1);
+      const long long base = stat_base(p, w, b, hk * group + hh);
+      const int q0i = min(qb + lane, S_ - 1), q1i = min(qb + 32 + lane, S_ - 1);
       v[0] = -p.lse[base + q0i] * kLog2e;
       v[1] = -p.lse[base + q1i] * kLog2e;
       v[2] = p.delta[base + q0i];
@@ -797,9 +855,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         mbar_expect_tx(&q_full[st], 2 * L::kQ);
         for (int hh = 0; hh < NH; ++hh) {
           tma_load_4d(smem + L::oQ + st * L::kQ + hh * (BC * 128), &tmQ, &q_full[st], hh * 64, h,
-                      qi * BC, b);
+                      w.off + qi * BC, w.tb);
           tma_load_4d(smem + L::oDO + st * L::kQ + hh * (BC * 128), &tmDO, &q_full[st], hh * 64, h,
-                      qi * BC, b);
+                      w.off + qi * BC, w.tb);
         }
       }
       float* sp = stat + st * 128;
@@ -888,7 +946,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const int qb = (i_start + qrel) * BC + half * 32;
       const uint32_t tST = tmem + (it & 1) * 128 + lane_off + half * 32;
       const uint32_t sstat = stat_u + st * 512;
-      const bool need_mask = (p.causal && (n0 + BQ - 1 > qb)) || (qb + 32 > p.S) || (n0 + BQ > p.S);
+      const bool need_mask = (p.causal && (n0 + BQ - 1 > qb)) || (qb + 32 > S_) || (n0 + BQ > S_);
       if (!mbar_wait_to(&stat_full[st], ph, 41, it)) goto done;
       if (!mbar_wait_to(&s_full[it & 1], (it >> 1) & 1, 38, it)) goto done;
       // Measured: starting on S^T while the dP^T MMAs of the same buffer are still in flight corrupts results
@@ -913,7 +971,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
           const int qp = qb + c;
-          const bool ok = (qp < p.S) && (kpos < p.S) && (!p.causal || kpos <= qp);
+          const bool ok = (qp < S_) && (kpos < S_) && (!p.causal || kpos <= qp);
           s[c] = ok ? s[c] : 0.f;
         }
       }
@@ -958,7 +1016,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     }
     // half 0 drains dV, half 1 drains dK
     const bool is_dv = (half == 0);
-    __nv_bfloat16* dst_row = out_row_ptr(p, is_dv, b, min(kpos, p.S - 1)) + (long long)hk * D;
+    __nv_bfloat16* dst_row = out_row_ptr(p, is_dv, w.tb, w.off + min(kpos, S_ - 1)) + (long long)hk * D;
     const uint32_t t_acc = (is_dv ? tDV : tDK) + lane_off;
 #pragma unroll 1
     for (int cc = 0; cc < D / 32; ++cc) {
@@ -970,7 +1028,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
         for (int i = 0; i < 32; ++i) o[i] = 0u;
       }
-      if (kpos < p.S) {
+      if (kpos < S_) {
         __nv_bfloat16* dst = dst_row + cc * 32;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -1102,6 +1160,17 @@ thread_local ScatterCfg g_scatter;
 thread_local long long g_dv_delta = 0;
 thread_local void* g_keep = nullptr;
 thread_local long long g_keep_stride = 0;
+// Packed-sequence configuration of the next launches on this host thread (set by the *_varlen entry points).
+struct VarlenCfg {
+  const int* cu = nullptr;
+  int nseq = 0, max_len = 0;
+};
+thread_local VarlenCfg g_varlen;
+// grid over (heads, sequences, tiles of the longest sequence)
+dim3 attn_grid(int heads, int B, int S) {
+  if (g_varlen.cu != nullptr) return dim3(heads, g_varlen.nseq, (g_varlen.max_len + sxb::attn::BQ - 1) / sxb::attn::BQ);
+  return dim3(heads, B, (S + sxb::attn::BQ - 1) / sxb::attn::BQ);
+}
 void apply_scatter(sxb::attn::Params& p, bool second_too) {
   p.scatter_rows = g_scatter.rows;
   for (int i = 0; i < 16; ++i) {
@@ -1127,9 +1196,10 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
   Params p{};
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
+  p.cu_seqlens = g_varlen.cu;
   apply_scatter(p, false);
   if (p.scatter_rows > 0) { p.out = g_keep; p.out2_stride = g_keep_stride; }
-  dim3 grid(Hq, B, (S + BQ - 1) / BQ);
+  dim3 grid = attn_grid(Hq, B, S);
   cudaStream_t s = (cudaStream_t)stream;
   if (use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride))) {
     if ((rc = set_smem(attn_fwd_kernel<128, 2>, FwdSmem<128>::kTotal))) return rc;
@@ -1169,6 +1239,7 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
   Params p{};
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.lse = (float*)const_cast<void*>(lse); p.delta = (const float*)delta;
+  p.cu_seqlens = g_varlen.cu;
   {
     static int dbg = -1;
     if (dbg < 0) { const char* e = getenv("SXB_ATTN_DEBUG"); dbg = e ? atoi(e) : 0; }
@@ -1183,7 +1254,7 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
     if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BC))) return rc;
     p.out = dq; p.out_stride = dq_stride;
     apply_scatter(p, false);
-    dim3 grid(Hq, B, (S + BQ - 1) / BQ);
+    dim3 grid = attn_grid(Hq, B, S);
     if (use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride))) {
       if ((rc = set_smem(attn_bwd_dq_kernel<128, 2>, DqSmem<128>::kTotal))) return rc;
       if ((rc = launch_cluster2(attn_bwd_dq_kernel<128, 2>, grid, kBwdThreads, DqSmem<128>::kTotal, s, tq, tk, tv,
@@ -1215,7 +1286,7 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
         p.out2_peers[i] = g_scatter.out2[i] ? (void*)((__nv_bfloat16*)g_scatter.out2[i] + g_dv_delta) : nullptr;
       }
     }
-    dim3 grid(Hk, B, (S + BQ - 1) / BQ);
+    dim3 grid = attn_grid(Hk, B, S);
     if (D == 128) {
       if ((rc = set_smem(attn_bwd_dkv_kernel<128>, DkvSmem<128>::kTotal))) return rc;
       attn_bwd_dkv_kernel<128><<<grid, kBwdThreads, DkvSmem<128>::kTotal, s>>>(tq, tk, tv, tdo, p);
@@ -1272,4 +1343,82 @@ SXB_API int sxb_attn_bwd_scatter(const void* q, const void* k, const void* v, co
   g_scatter = ScatterCfg{};
   g_dv_delta = 0;
   return rc;
+}
+
+// Packed sequences (cu_seqlens int32 [nseq + 1] on the device; q/k/v/out [total, H, D]; lse / delta [Hq, total]):
+// every sequence attends only to itself.  The reference reaches this through flash-attn's varlen entry points
+// (sequence/fpdt_layer.py:14-20, inference/v2 blocked_flash); here it is the same three kernels with a per-CTA
+// row window.
+SXB_API int sxb_attn_fwd_varlen(const void* q, const void* k, const void* v, void* out, void* lse,
+                                const void* cu_seqlens, int nseq, int max_seqlen, int total, int Hq, int Hk, int D,
+                                long long q_stride, long long k_stride, long long v_stride, long long o_stride,
+                                int causal, float scale, void* stream) {
+  if (cu_seqlens == nullptr || nseq <= 0 || max_seqlen <= 0 || max_seqlen > total) return SXB_ERR_BAD_ARG;
+  g_varlen.cu = static_cast<const int*>(cu_seqlens);
+  g_varlen.nseq = nseq;
+  g_varlen.max_len = max_seqlen;
+  const int rc = sxb_attn_fwd(q, k, v, out, lse, 1, total, Hq, Hk, D, q_stride, k_stride, v_stride, o_stride, causal,
+                              scale, stream);
+  g_varlen = VarlenCfg{};
+  return rc;
+}
+
+SXB_API int sxb_attn_bwd_varlen(const void* q, const void* k, const void* v, const void* out, const void* d_out,
+                                const void* lse, void* delta, void* dq, void* dk, void* dv, const void* cu_seqlens,
+                                int nseq, int max_seqlen, int total, int Hq, int Hk, int D, long long q_stride,
+                                long long k_stride, long long v_stride, long long o_stride, long long do_stride,
+                                long long dq_stride, long long dk_stride, long long dv_stride, int causal, float scale,
+                                void* stream) {
+  if (cu_seqlens == nullptr || nseq <= 0 || max_seqlen <= 0 || max_seqlen > total) return SXB_ERR_BAD_ARG;
+  g_varlen.cu = static_cast<const int*>(cu_seqlens);
+  g_varlen.nseq = nseq;
+  g_varlen.max_len = max_seqlen;
+  const int rc = sxb_attn_bwd(q, k, v, out, d_out, lse, delta, dq, dk, dv, 1, total, Hq, Hk, D, q_stride, k_stride,
+                              v_stride, o_stride, do_stride, dq_stride, dk_stride, dv_stride, causal, scale, stream);
+  g_varlen = VarlenCfg{};
+  return rc;
+}
+
+// Blocked ("paged") flash attention over a ragged batch on the tensor cores: the forward kernel above, one CTA per
+// (attention atom, q head).  q/out [T, Hq, D]; cache [n_blocks, block_size, 2, Hk, D] (K then V per slot); atoms
+// int32 [n_atoms, 6] and block_tables int32 [n_seqs, max_blocks] on the device.  block_size: a multiple of 8 that
+// divides 64, or a multiple of 64.  Causal by position: query i of an atom sits at global_q_idx + i.
+// (reference: inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.cpp:21-101 over flash-attn's sm_80 kernels)
+SXB_API int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, const void* atoms, int n_atoms,
+                               const void* block_tables, int max_blocks, int n_blocks, int block_size, int T, int Hq,
+                               int Hk, int D, long long q_stride, long long o_stride, float scale, void* stream) {
+  if (n_atoms <= 0) return SXB_OK;
+  if (!attn_args_ok(1, T, Hq, Hk, D, q_stride, 8, 8) || (o_stride % 8)) return SXB_ERR_UNSUPPORTED;
+  if (block_size < 8 || (block_size % 8) || (block_size < BC ? (BC % block_size) : (block_size % BC)))
+    return SXB_ERR_UNSUPPORTED;
+  CUtensorMap tq, tk, tv;
+  int rc;
+  if ((rc = make_qkv_map(&tq, q, 1, T, Hq, D, q_stride, BQ))) return rc;
+  const long long slot = 2LL * Hk * D;   // elements per cached token: K heads then V heads
+  const int box_rows = block_size < BC ? block_size : BC;
+  const __nv_bfloat16* kbase = static_cast<const __nv_bfloat16*>(cache);
+  if ((rc = make_qkv_map(&tk, kbase, n_blocks, block_size, Hk, D, slot, box_rows))) return rc;
+  if ((rc = make_qkv_map(&tv, kbase + (long long)Hk * D, n_blocks, block_size, Hk, D, slot, box_rows))) return rc;
+  Params p{};
+  p.B = 1; p.S = T; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = 1; p.scale = scale;
+  p.out = out; p.out_stride = o_stride;
+  p.atoms = static_cast<const int*>(atoms);
+  p.block_tables = static_cast<const int*>(block_tables);
+  p.max_blocks = max_blocks; p.block_size = block_size;
+  dim3 grid(Hq, 1, n_atoms);
+  cudaStream_t s = (cudaStream_t)stream;
+  const long long cache_bytes = (long long)n_blocks * block_size * slot * 2;
+  if (use_multicast(Hq, Hk, D, cache, cache_bytes, cache, cache_bytes)) {
+    if ((rc = set_smem(attn_fwd_kernel<128, 2>, FwdSmem<128>::kTotal))) return rc;
+    if ((rc = launch_cluster2(attn_fwd_kernel<128, 2>, grid, kThreads, FwdSmem<128>::kTotal, s, tq, tk, tv, p)))
+      return rc;
+  } else if (D == 128) {
+    if ((rc = set_smem(attn_fwd_kernel<128, 1>, FwdSmem<128>::kTotal))) return rc;
+    attn_fwd_kernel<128, 1><<<grid, kThreads, FwdSmem<128>::kTotal, s>>>(tq, tk, tv, p);
+  } else {
+    if ((rc = set_smem(attn_fwd_kernel<64, 1>, FwdSmem<64>::kTotal))) return rc;
+    attn_fwd_kernel<64, 1><<<grid, kThreads, FwdSmem<64>::kTotal, s>>>(tq, tk, tv, p);
+  }
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
 }

@@ -16,6 +16,7 @@ _lib.register({
     "sxb_logits_gather": "ppp" "ii" "p",
     "sxb_kv_rotary_blocked": "ppppp" "iiiiiii" "f" "p",
     "sxb_paged_attention": "pppppp" "iiiiii" "l" "f" "p",
+    "sxb_attn_fwd_atoms": "ppp" "pi" "piii" "iiii" "ll" "f" "p",
 })
 
 
@@ -107,6 +108,38 @@ def paged_attention(q: torch.Tensor, cache: torch.Tensor, tok_seq: torch.Tensor,
         p = torch.softmax(s, dim=-1)
         out[t] = torch.einsum("hn,nhd->hd", p, v).to(q.dtype)
     return out
+
+
+def atoms_supported(q: torch.Tensor, cache: torch.Tensor) -> bool:
+    """Whether the tensor-core atom kernel takes this query / cache layout."""
+    bs = cache.shape[1]
+    return (q.is_cuda and q.dtype == torch.bfloat16 and cache.dtype == torch.bfloat16 and q.shape[-1] in (64, 128)
+            and q.stride(2) == 1 and q.stride(1) == q.shape[-1] and q.stride(0) % 8 == 0 and cache.is_contiguous()
+            and bs % 8 == 0 and (64 % bs == 0 if bs < 64 else bs % 64 == 0))
+
+
+def paged_attention_atoms(q: torch.Tensor, cache: torch.Tensor, atoms: torch.Tensor, block_tables: torch.Tensor,
+                          scale: float = None) -> torch.Tensor:
+    """The same attention as :func:`paged_attention`, scheduled by attention atoms on the tcgen05 flash kernel: one CTA
+    per (atom, q head) runs 128 queries of one sequence against that sequence's pages, K/V tiles fetched by TMA through
+    the block table (``csrc/attention.cu``: ``sxb_attn_fwd_atoms``).  Prefill re-reads K/V once per 128 queries instead
+    of once per query."""
+    T, n_q, D = q.shape
+    n_kv = cache.shape[3]
+    scale = 1.0 / math.sqrt(D) if scale is None else scale
+    out = torch.empty(T, n_q, D, dtype=q.dtype, device=q.device)
+    _lib.call("sxb_attn_fwd_atoms", q.data_ptr(), cache.data_ptr(), out.data_ptr(), atoms.data_ptr(), atoms.shape[0],
+              block_tables.data_ptr(), block_tables.shape[1], cache.shape[0], cache.shape[1], T, n_q, n_kv, D,
+              q.stride(0), out.stride(0), float(scale), _lib.stream_ptr())
+    return out
+
+
+def ragged_attention(q: torch.Tensor, cache: torch.Tensor, batch, scale: float = None) -> torch.Tensor:
+    """Attention of a finalized ragged batch: atoms on the tensor cores where the layout allows, else per token."""
+    atoms = batch.atoms() if hasattr(batch, "atoms") else None
+    if atoms is not None and atoms.shape[0] > 0 and atoms_supported(q, cache):
+        return paged_attention_atoms(q, cache, atoms, batch.block_tables(), scale)
+    return paged_attention(q, cache, batch.token_to_seq(), batch.token_positions(), batch.block_tables(), scale)
 
 
 # ================================================================================================ class interface
@@ -216,8 +249,7 @@ class BlockedFlashAttn:
         n = b.current_tokens
         T = q.shape[0]
         q3 = q[:n].view(n, -1, self.head_size)
-        res = paged_attention(q3, kv_cache, b.token_to_seq()[:n], b.token_positions()[:n], b.block_tables(),
-                              softmax_scale)
+        res = ragged_attention(q3, kv_cache, b, softmax_scale)
         out[:n].copy_(res.reshape(n, -1))
         return out
 

@@ -84,7 +84,7 @@ class RaggedLlamaModel:
             cache = self.state_manager.get_cache(li)
             R.kv_rotary_blocked(qkv, cache, t2s, pos, tables, nq, nkv, d, d, c.rope_theta)
             q = qkv.view(qkv.shape[0], nq + 2 * nkv, d)[:, :nq]
-            o = R.paged_attention(q, cache, t2s, pos, tables)
+            o = R.ragged_attention(q, cache, batch)
             h = F.linear(o.reshape(o.shape[0], nq * d), layer.wo)
             x, residual = F.rms_norm(h, layer.post_attention_layernorm, c.rms_norm_eps, residual)
             h = self._mlp(li, layer, x)

@@ -91,7 +91,7 @@ class DSDenseBlockedAttention(DSSelfAttentionBase):
         R.kv_rotary_blocked(q_k_v, kv_cache, t2s, pos, tables, c.n_heads_q, c.n_heads_kv, c.head_size, self._rot_dim,
                             self._theta)
         q = q_k_v.view(q_k_v.shape[0], c.n_heads_q + 2 * c.n_heads_kv, c.head_size)[:, :c.n_heads_q]
-        out = R.paged_attention(q, kv_cache, t2s, pos, tables, scale=c.scale_factor)
+        out = R.ragged_attention(q, kv_cache, batch, scale=c.scale_factor)
         return out.reshape(out.shape[0], c.n_heads_q * c.head_size)
 
 

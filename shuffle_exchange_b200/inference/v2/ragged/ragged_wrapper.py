@@ -1,12 +1,17 @@
 """Host-side assembly of one ragged batch and its upload (reference: ``inference/v2/ragged/ragged_wrapper.py:31-292``).
 
 All metadata of a forward pass lives in ONE pinned int32 staging buffer laid out as
-``[token ids | token->sequence | token position | last-token index per sequence | block tables]`` and is uploaded with
-a single ``cudaMemcpyAsync`` in ``finalize`` (the reference uses three pinned "fast host buffers",
-``ragged/csrc/fast_host_buffer.cu``)."""
+``[token ids | token->sequence | token position | last-token index per sequence | block tables | attention atoms]`` and
+is uploaded with a single ``cudaMemcpyAsync`` in ``finalize`` (the reference uses three pinned "fast host buffers",
+``ragged/csrc/fast_host_buffer.cu``).  The attention atoms (one per 128-query tile of a sequence, with the KV extent
+it attends to) are cut by the native scheduler ``sxbh_build_atoms`` (``csrc/host/ragged_host.cpp``) at ``finalize``
+and consumed by the tensor-core paged attention kernel (``sxb_attn_fwd_atoms``)."""
 from __future__ import annotations
 
 import torch
+
+ATOM_Q_BLOCK = 128          # query rows of one attention atom = the kernel's q tile
+ATOM_KV_BLOCK = 64
 
 
 class RaggedBatchWrapper:
@@ -14,7 +19,9 @@ class RaggedBatchWrapper:
                  device=None) -> None:
         self.max_tokens, self.max_seqs, self.max_blocks = max_ragged_batch_size, max_ragged_sequence_count, max_blocks_per_seq
         self.device = device if device is not None else ("cuda" if torch.cuda.is_available() else "cpu")
-        n = 3 * self.max_tokens + self.max_seqs + self.max_seqs * self.max_blocks
+        self.max_atoms = self.max_tokens // ATOM_Q_BLOCK + self.max_seqs
+        n = 3 * self.max_tokens + self.max_seqs + self.max_seqs * self.max_blocks + 6 * self.max_atoms
+        self._seq_meta = torch.zeros(3, self.max_seqs, dtype=torch.int32)      # start / in-flight tokens / seen tokens
         pin = torch.cuda.is_available()
         self._host = torch.zeros(n, dtype=torch.int32, pin_memory=pin)
         self._dev = torch.zeros(n, dtype=torch.int32, device=self.device)
@@ -23,11 +30,14 @@ class RaggedBatchWrapper:
     def clear(self) -> None:
         self._n_tokens = 0
         self._n_seqs = 0
+        self._n_atoms = 0
         self._finalized = False
 
     def _views(self, buf):
         T, S, B = self.max_tokens, self.max_seqs, self.max_blocks
-        return (buf[0:T], buf[T:2 * T], buf[2 * T:3 * T], buf[3 * T:3 * T + S], buf[3 * T + S:].view(S, B))
+        e = 3 * T + S + S * B
+        return (buf[0:T], buf[T:2 * T], buf[2 * T:3 * T], buf[3 * T:3 * T + S], buf[3 * T + S:e].view(S, B),
+                buf[e:].view(self.max_atoms, 6))
 
     def insert_sequence(self, seq_descriptor, tokens: torch.Tensor, do_checks: bool = True) -> None:
         n = tokens.numel()
@@ -36,8 +46,10 @@ class RaggedBatchWrapper:
                 raise RuntimeError(f"Ragged batch is full due to tokens: {self._n_tokens} + {n} > {self.max_tokens}")
             if self._n_seqs + 1 > self.max_seqs:
                 raise RuntimeError("Ragged batch is full due to sequences")
-        ids, t2s, pos, last, tables = self._views(self._host)
+        ids, t2s, pos, last, tables, _ = self._views(self._host)
         a, b = self._n_tokens, self._n_tokens + n
+        self._seq_meta[0, self._n_seqs], self._seq_meta[1, self._n_seqs] = a, n
+        self._seq_meta[2, self._n_seqs] = seq_descriptor.seen_tokens
         ids[a:b] = tokens.to(torch.int32)
         t2s[a:b] = self._n_seqs
         pos[a:b] = torch.arange(seq_descriptor.seen_tokens, seq_descriptor.seen_tokens + n, dtype=torch.int32)
@@ -47,6 +59,10 @@ class RaggedBatchWrapper:
         self._n_tokens, self._n_seqs = b, self._n_seqs + 1
 
     def finalize(self, padding: bool = False) -> None:
+        if self._n_seqs:
+            from ..kernels.atom_builder import AtomBuilder
+            m = self._seq_meta[:, : self._n_seqs].contiguous()
+            _, self._n_atoms = AtomBuilder()(self._views(self._host)[5], m[0], m[1], m[2], ATOM_Q_BLOCK, ATOM_KV_BLOCK)
         self._dev.copy_(self._host, non_blocking=True)
         self._finalized = True
 
@@ -65,6 +81,10 @@ class RaggedBatchWrapper:
 
     def block_tables(self):
         return self._views(self._dev)[4]
+
+    def atoms(self):
+        """int32 ``[n_atoms, 6]`` on the device: ``(seq, q_start_idx, q_len, global_q_idx, kv_blocks, total_extent)``."""
+        return self._views(self._dev)[5][: self._n_atoms]
 
     @property
     def current_tokens(self) -> int:

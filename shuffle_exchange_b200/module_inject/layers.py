@@ -51,6 +51,15 @@ def add_bias(input, bias):
     return input
 
 
+def _project(x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+    """``x @ weight^T`` of a TP linear: the framework's tcgen05 linear (forward, dgrad and wgrad) for bf16 CUDA operands
+    with 16-byte-aligned rows; PyTorch for CPU tensors and other dtypes."""
+    if x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 \
+            and x.shape[-1] % 8 == 0 and weight.shape[0] % 8 == 0:
+        return F.linear(x, weight)
+    return TF.linear(x, weight)
+
+
 def _tp_world(group) -> int:
     return dist.get_world_size(group=group) if (group is not None and dist.is_initialized()) else 1
 
@@ -139,7 +148,7 @@ class AsyncColumnParallel(torch.autograd.Function):
     def forward(ctx: Any, group, input: torch.Tensor, weight, bias) -> torch.Tensor:
         ctx.use_bias = bias is not None
         ctx.group = group
-        out = torch.matmul(input, weight.transpose(-1, -2))
+        out = F.matmul_nt(input, weight)
         if bias is not None:
             out = out + bias
         ctx.save_for_backward(input, weight)
@@ -148,10 +157,10 @@ class AsyncColumnParallel(torch.autograd.Function):
     @staticmethod
     def backward(ctx: Any, grad_output: torch.Tensor):
         input, weight = ctx.saved_tensors
-        grad_input = grad_output.matmul(weight)
+        grad_input = F.matmul_nn(grad_output, weight)
         handle = dist.all_reduce(grad_input.contiguous(), group=ctx.group, async_op=True) if _tp_world(ctx.group) > 1 else None
         g2 = grad_output.reshape(-1, grad_output.shape[-1])
-        grad_weight = g2.t().matmul(input.reshape(-1, input.shape[-1]))
+        grad_weight = F.matmul_tn(g2, input).to(weight.dtype)
         grad_bias = g2.sum(0) if ctx.use_bias else None
         if handle is not None:
             handle.wait()
@@ -273,11 +282,7 @@ class LinearAllreduce(TensorParallel_Layer):
             self.config_requires_grad(self.bias)
 
     def forward(self, input):
-        x2 = input.reshape(-1, input.shape[-1])
-        if x2.is_cuda and x2.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16 and not self.is_training_mode():
-            out = F.gemm(x2.contiguous(), self.weight, 0).reshape(*input.shape[:-1], self.weight.shape[0])
-        else:
-            out = torch.matmul(input, self.weight.transpose(-1, -2))
+        out = _project(input, self.weight)
         out = RowParallel.apply(self.mp_group, out, not self.is_training_mode())
         return add_bias(out, self.bias)
 
@@ -317,7 +322,7 @@ class LinearLayer(TensorParallel_Layer):
         if getattr(self, "__async_tp", False) and self.is_training_mode():
             return AsyncColumnParallel.apply(self.mp_group, input, self.weight, self.bias)
         input = ColumnParallel.apply(self.mp_group, input)
-        out = torch.matmul(input, self.weight.transpose(-1, -2))
+        out = _project(input, self.weight)
         return add_bias(out, self.bias)
 
     @torch.no_grad()
@@ -410,7 +415,7 @@ class LmHeadLinearAllreduce(LinearAllreduce):
         from .tp_shard import get_shard_size, get_shard_size_list
         width = get_shard_size(input.shape[-1], self.world_size, "lm_head")
         start = sum(get_shard_size_list(input.shape[-1], self.world_size, "lm_head")[: self.rank])
-        out = torch.matmul(input[..., start: start + width], self.weight.transpose(-1, -2))
+        out = _project(input[..., start: start + width], self.weight)
         out = RowParallel.apply(self.mp_group, out, not self.is_training_mode())
         return add_bias(out, self.bias)
 

@@ -122,6 +122,17 @@ def matmul_tn(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
     return torch.matmul(a2.t(), b2)
 
 
+def accumulate_tn(acc: torch.Tensor, a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """``acc[M, N] += a[R, M]^T @ b[R, N]`` with ``acc`` in fp32 — chunked weight gradients accumulate in the GEMM
+    epilogue instead of a separate add pass."""
+    a2, b2 = a.reshape(-1, a.shape[-1]), b.reshape(-1, b.shape[-1])
+    if _tc_ok(a2, b2) and a2.shape[1] % 8 == 0 and b2.shape[1] % 8 == 0 and acc.is_contiguous():
+        gemm(a2 if a2.is_contiguous() else a2.contiguous(), b2 if b2.is_contiguous() else b2.contiguous(), GEMM_TN,
+             out=acc, accumulate=True)
+        return acc
+    return acc.add_(torch.matmul(a2.t(), b2).to(acc.dtype))
+
+
 # ---------------------------------------------------------------------- gradient-use accounting
 # A parameter used k times in one forward (tied embedding / LM head, a shared projection) delivers k
 # contributions through the main-grad protocol, one per use.  The sharded optimizers must not start a
@@ -753,6 +764,79 @@ def attention_bwd_raw(q, k, v, out, dout, lse, causal: bool, scale: float):
     dv_ = dv_.view(B, Hk, g, k.shape[1], D).sum(2)
     return (dq_.permute(0, 2, 1, 3).to(q.dtype), dk_.permute(0, 2, 1, 3).to(k.dtype),
             dv_.permute(0, 2, 1, 3).to(v.dtype))
+
+
+# ------------------------------------------------------------------- packed-sequence ("varlen") attention
+_n.register({
+    "sxb_attn_fwd_varlen": "ppppp" "p" "iiiiii" "llll" "i" "f" "p",
+    "sxb_attn_bwd_varlen": "pppppppppp" "p" "iiiiii" "llllllll" "i" "f" "p",
+})
+
+
+def attention_varlen_ref(q, k, v, cu_seqlens, causal=True, scale=None):
+    """Oracle: every sequence ``[cu[i], cu[i+1])`` of the packed ``[T, H, D]`` tensors attends only to itself."""
+    out = torch.empty_like(q)
+    cu = cu_seqlens.tolist()
+    for a, b in zip(cu[:-1], cu[1:]):
+        if b > a:
+            out[a:b] = attention_ref(q[None, a:b], k[None, a:b], v[None, a:b], causal, scale)[0]
+    return out
+
+
+class _FlashAttnVarlen(torch.autograd.Function):
+    """q [T, Hq, D], k/v [T, Hk, D] packed; the same tcgen05 kernels as the dense path with a per-CTA row window
+    (``csrc/attention.cu``: ``sxb_attn_fwd_varlen`` / ``sxb_attn_bwd_varlen``)."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, cu_seqlens, max_seqlen, causal, scale):
+        T, Hq, D = q.shape
+        Hk = k.shape[1]
+        nseq = cu_seqlens.numel() - 1
+        out = torch.empty((T, Hq, D), dtype=q.dtype, device=q.device)
+        lse = torch.empty((Hq, T), dtype=torch.float32, device=q.device)
+        _n.call("sxb_attn_fwd_varlen", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), lse.data_ptr(),
+                cu_seqlens.data_ptr(), nseq, int(max_seqlen), T, Hq, Hk, D, q.stride(0), k.stride(0), v.stride(0),
+                out.stride(0), int(causal), float(scale), _n.stream_ptr())
+        ctx.save_for_backward(q, k, v, out, lse, cu_seqlens)
+        ctx.cfg = (int(max_seqlen), bool(causal), float(scale))
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        q, k, v, out, lse, cu = ctx.saved_tensors
+        max_seqlen, causal, scale = ctx.cfg
+        T, Hq, D = q.shape
+        Hk = k.shape[1]
+        if dout.stride(-1) != 1 or dout.stride(1) != D:
+            dout = dout.contiguous()
+        dqkv = torch.empty((T, (Hq + 2 * Hk) * D), dtype=q.dtype, device=q.device)
+        dq = dqkv[:, : Hq * D].view(T, Hq, D)
+        dk = dqkv[:, Hq * D: (Hq + Hk) * D].view(T, Hk, D)
+        dv = dqkv[:, (Hq + Hk) * D:].view(T, Hk, D)
+        delta = torch.empty((Hq, T), dtype=torch.float32, device=q.device)
+        _n.call("sxb_attn_bwd_varlen", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), dout.data_ptr(),
+                lse.data_ptr(), delta.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), cu.data_ptr(),
+                cu.numel() - 1, max_seqlen, T, Hq, Hk, D, q.stride(0), k.stride(0), v.stride(0), out.stride(0),
+                dout.stride(0), dq.stride(0), dk.stride(0), dv.stride(0), int(causal), float(scale), _n.stream_ptr())
+        return dq, dk, dv, None, None, None, None
+
+
+def flash_attention_varlen(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens: torch.Tensor,
+                           max_seqlen: int, causal: bool = True, scale: Optional[float] = None) -> torch.Tensor:
+    """Attention over packed sequences: q ``[T, Hq, D]``, k/v ``[T, Hk, D]`` (strided views of a fused QKV buffer are
+    fine), ``cu_seqlens`` int32 ``[n + 1]`` on the same device, ``max_seqlen`` = the longest sequence (a host int: it
+    sizes the grid)."""
+    D = q.shape[-1]
+    scale = scale if scale is not None else 1.0 / math.sqrt(D)
+    if not q.is_cuda:
+        return attention_varlen_ref(q, k, v, cu_seqlens, causal, scale)
+    if q.dtype != torch.bfloat16 or D not in (64, 128):
+        raise _n.NativeError(f"sxb flash_attention_varlen: bf16 and head_dim 64/128 only (got {q.dtype}, {D})")
+    if cu_seqlens.dtype != torch.int32 or not cu_seqlens.is_cuda:
+        raise _n.NativeError("sxb flash_attention_varlen: cu_seqlens must be an int32 CUDA tensor")
+    ok = lambda t: t.stride(2) == 1 and t.stride(1) == D
+    q, k, v = (t if ok(t) else t.contiguous() for t in (q, k, v))
+    return _FlashAttnVarlen.apply(q, k, v, cu_seqlens.contiguous(), max_seqlen, causal, scale)
 
 
 def _attn_layout_ok(t):

@@ -337,7 +337,7 @@ class FPDT_FFN(torch.autograd.Function):
             for i in range(num_chunk):
                 sl = slice(i * chunk_size, (i + 1) * chunk_size)
                 inter = F.bias_act(F.linear(x[sl], w1), b1, "gelu") if x.is_cuda else bias_gelu(
-                    torch.matmul(x[sl], w1.t()) + b1)
+                    F.matmul_nt(x[sl], w1) + b1)
                 result[sl] = F.linear(inter, w2, b2 if add_bias else None)
                 del inter
         ctx.save_for_backward(x, w1, b1, w2, b2)
@@ -356,14 +356,14 @@ class FPDT_FFN(torch.autograd.Function):
         for i in range(n):
             sl = slice(i * cs, (i + 1) * cs)
             xc, go = x[sl], grad_output[sl]
-            pre = torch.matmul(xc, w1.t()) + b1
+            pre = F.matmul_nt(xc, w1) + b1
             act = bias_gelu(pre)
-            gw2.add_(torch.matmul(go.reshape(-1, go.shape[-1]).t(), act.reshape(-1, act.shape[-1])).float())
-            ginter = bias_gelu_back(torch.matmul(go, w2), pre)
+            F.accumulate_tn(gw2, go, act)
+            ginter = bias_gelu_back(F.matmul_nn(go, w2), pre)
             del pre, act
-            gw1.add_(torch.matmul(ginter.reshape(-1, ginter.shape[-1]).t(), xc.reshape(-1, xc.shape[-1])).float())
+            F.accumulate_tn(gw1, ginter, xc)
             gb1.add_(ginter.reshape(-1, ginter.shape[-1]).sum(0).float())
-            gx[sl] = torch.matmul(ginter, w1)
+            gx[sl] = F.matmul_nn(ginter, w1)
             if ctx.add_bias:
                 gb2.add_(go.reshape(-1, go.shape[-1]).sum(0).float())
         dt = x.dtype
@@ -408,10 +408,10 @@ class FPDT_LogitsLoss(torch.autograd.Function):
         for i in range(n):
             sl = slice(i * cs, (i + 1) * cs)
             xc = lm_output[sl]
-            probs = torch.softmax(torch.matmul(xc, w.t()).float(), dim=-1)
+            probs = torch.softmax(F.matmul_nt(xc, w).float(), dim=-1)
             probs.scatter_add_(-1, labels[sl].unsqueeze(-1), -torch.ones_like(probs[..., :1]))
             probs.mul_(grad_output[sl].unsqueeze(-1))
             g = probs.to(lm_output.dtype)
-            gx[sl] = torch.matmul(g, w)
-            gw.add_(torch.matmul(g.reshape(-1, g.shape[-1]).t(), xc.reshape(-1, xc.shape[-1])).float())
+            gx[sl] = F.matmul_nn(g, w)
+            F.accumulate_tn(gw, g, xc)
         return gx, None, gw.to(w.dtype), None, None, None, None

@@ -1,0 +1,130 @@
+"""Packed-sequence (varlen) training attention and atom-scheduled paged attention on the tcgen05 kernels.
+
+Oracles are plain PyTorch fp32 computations of the same op (``attention_varlen_ref``; the per-token paged attention
+written out in ``ragged_ops.paged_attention``'s CPU branch)."""
+import math
+
+import pytest
+import torch
+
+from shuffle_exchange_b200.inference.v2.ragged.ragged_wrapper import RaggedBatchWrapper
+
+
+class _Seq:
+    def __init__(self, seen, blocks):
+        self.seen_tokens, self._blocks = seen, torch.tensor(blocks, dtype=torch.int32)
+
+    def kv_blocks(self):
+        return self._blocks
+
+
+def test_wrapper_cuts_atoms_on_cpu():
+    w = RaggedBatchWrapper(1024, 8, 16, device="cpu")
+    w.insert_sequence(_Seq(0, [3, 4, 5]), torch.arange(300))          # prefill: 3 atoms
+    w.insert_sequence(_Seq(77, [1]), torch.arange(1))                 # decode: 1 atom
+    w.insert_sequence(_Seq(100, [6, 7]), torch.arange(130))           # chunked prefill continuing at 100: 2 atoms
+    w.finalize()
+    atoms = w.atoms().tolist()
+    assert atoms == [[0, 0, 128, 0, 2, 128], [0, 128, 128, 128, 4, 256], [0, 256, 44, 256, 5, 300],
+                     [1, 300, 1, 77, 2, 78],
+                     [2, 301, 128, 100, 4, 228], [2, 429, 2, 228, 4, 230]]
+    w.clear()
+    w.finalize()
+    assert w.atoms().shape[0] == 0
+
+
+def _rel_err(a, b):
+    return ((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-9)).item()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,Hq,Hk", [(128, 8, 2), (64, 4, 4), (128, 3, 1)])
+@pytest.mark.parametrize("causal", [True, False])
+def test_varlen_forward_backward_matches_reference(D, Hq, Hk, causal):
+    from shuffle_exchange_b200.ops import functional as F
+    torch.manual_seed(0)
+    dev = "cuda"
+    lens = [200, 1, 128, 333, 64, 70]
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32, device=dev)
+    T = sum(lens)
+    qkv = torch.randn(T, (Hq + 2 * Hk) * D, device=dev, dtype=torch.bfloat16)
+    qkv.requires_grad_(True)
+    v3 = qkv.view(T, Hq + 2 * Hk, D)
+    q, k, v = v3[:, :Hq], v3[:, Hq:Hq + Hk], v3[:, Hq + Hk:]
+    out = F.flash_attention_varlen(q, k, v, cu, max(lens), causal=causal)
+    dout = torch.randn_like(out)
+    out.backward(dout)
+    got_grad = qkv.grad.clone()
+
+    ref_in = qkv.detach().float().requires_grad_(True)
+    r3 = ref_in.view(T, Hq + 2 * Hk, D)
+    ref = F.attention_varlen_ref(r3[:, :Hq], r3[:, Hq:Hq + Hk], r3[:, Hq + Hk:], cu.cpu(), causal)
+    ref.backward(dout.float())
+    assert _rel_err(out, ref) < 1e-2
+    # per-sequence check: a leak across a boundary shows up as a large error on a SHORT sequence
+    for a, b in zip(cu.tolist()[:-1], cu.tolist()[1:]):
+        assert _rel_err(out[a:b], ref[a:b]) < 2e-2, (a, b)
+        assert _rel_err(got_grad[a:b], ref_in.grad[a:b]) < 3e-2, (a, b)
+
+
+@pytest.mark.gpu
+def test_varlen_equals_dense_for_equal_lengths():
+    from shuffle_exchange_b200.ops import functional as F
+    torch.manual_seed(1)
+    B, S, Hq, Hk, D = 3, 256, 8, 4, 128
+    q = torch.randn(B, S, Hq, D, device="cuda", dtype=torch.bfloat16)
+    k = torch.randn(B, S, Hk, D, device="cuda", dtype=torch.bfloat16)
+    v = torch.randn(B, S, Hk, D, device="cuda", dtype=torch.bfloat16)
+    dense = F.flash_attention(q, k, v, causal=True)
+    cu = torch.arange(0, (B + 1) * S, S, dtype=torch.int32, device="cuda")
+    packed = F.flash_attention_varlen(q.view(B * S, Hq, D), k.view(B * S, Hk, D), v.view(B * S, Hk, D), cu, S)
+    assert torch.equal(packed.view(B, S, Hq, D), dense)          # same kernel, same tiles: bit-identical
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("block_size", [16, 64, 128])
+@pytest.mark.parametrize("D,Hq,Hk", [(128, 8, 2), (64, 4, 2)])
+def test_atom_paged_attention_matches_per_token_oracle(block_size, D, Hq, Hk):
+    from shuffle_exchange_b200.inference.v2.kernels import ragged_ops as R
+    torch.manual_seed(2)
+    dev = "cuda"
+    # (seen, new tokens): long prefill, decode with history, chunked prefill continuing mid-block, tiny prefill
+    plan = [(0, 300), (517, 1), (100, 130), (0, 5), (63, 1)]
+    max_blocks = 16 * 128 // block_size
+    n_blocks = 256 * 128 // block_size
+    cache = torch.randn(n_blocks, block_size, 2, Hk, D, device=dev, dtype=torch.bfloat16)
+    perm = torch.randperm(n_blocks).tolist()
+    w = RaggedBatchWrapper(1024, 8, max_blocks, device=dev)
+    for seen, n in plan:
+        need = (seen + n + block_size - 1) // block_size
+        blocks, perm = perm[:need], perm[need:]
+        w.insert_sequence(_Seq(seen, blocks), torch.zeros(n, dtype=torch.int64))
+    w.finalize()
+    T = w.current_tokens
+    q = torch.randn(T, Hq, D, device=dev, dtype=torch.bfloat16)
+    assert R.atoms_supported(q, cache)
+    got = R.ragged_attention(q, cache, w)
+    want = R.paged_attention(q.cpu(), cache.cpu(), w.token_to_seq().cpu(), w.token_positions().cpu(),
+                             w.block_tables().cpu())
+    assert _rel_err(got.cpu(), want) < 1e-2
+    for t in (0, 299, 300, 301, 430, 431, 435, 436):               # first / last rows of every atom
+        assert _rel_err(got[t].cpu(), want[t]) < 2e-2, t
+    simt = R.paged_attention(q, cache, w.token_to_seq(), w.token_positions(), w.block_tables())
+    assert _rel_err(got, simt) < 1e-2
+
+
+@pytest.mark.gpu
+def test_atom_attention_on_fused_qkv_view():
+    """q as a strided view of the fused QKV projection output (what the model passes)."""
+    from shuffle_exchange_b200.inference.v2.kernels import ragged_ops as R
+    torch.manual_seed(3)
+    Hq, Hk, D, bs = 8, 2, 128, 64
+    cache = torch.randn(32, bs, 2, Hk, D, device="cuda", dtype=torch.bfloat16)
+    w = RaggedBatchWrapper(512, 4, 8, device="cuda")
+    w.insert_sequence(_Seq(0, [5, 9, 2]), torch.zeros(150, dtype=torch.int64))
+    w.finalize()
+    qkv = torch.randn(150, (Hq + 2 * Hk) * D, device="cuda", dtype=torch.bfloat16)
+    q = qkv.view(150, Hq + 2 * Hk, D)[:, :Hq]
+    got = R.ragged_attention(q, cache, w, scale=1.0 / math.sqrt(D))
+    want = R.paged_attention(q.contiguous(), cache, w.token_to_seq(), w.token_positions(), w.block_tables())
+    assert _rel_err(got, want) < 1e-2
