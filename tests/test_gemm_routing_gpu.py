@@ -21,7 +21,7 @@ def test_autotp_linears_forward_backward_on_tcgen05():
             base = nn.Linear(256, 384, bias=True).cuda().bfloat16()
             layer = cls(base, mp_group=None)
             x = torch.randn(4, 64, 256, device="cuda", dtype=torch.bfloat16, requires_grad=True)
-            before = lib.launch_count() if hasattr(lib, "launch_count") else None
+            before = lib.launch_count
             y = layer(x)
             g = torch.randn_like(y)
             y.backward(g)
@@ -30,8 +30,7 @@ def test_autotp_linears_forward_backward_on_tcgen05():
             yf = torch.nn.functional.linear(xf, wf, base.bias.detach().float())
             yf.backward(g.float())
             assert _rel(y, yf) < 1e-2 and _rel(x.grad, xf.grad) < 1e-2 and _rel(layer.weight.grad, wf.grad) < 1e-2
-            if before is not None:
-                assert lib.launch_count() > before
+            assert lib.launch_count >= before + 3          # forward, dgrad and wgrad went through the native library
     finally:
         set_autotp_mode(training=False)
 

@@ -1,8 +1,8 @@
 """Short single-GPU workload that launches each kernel family once per iteration, for ``ncu`` (one capture per call):
 
     python tools/ncu_targets.py && ncu --set full --clock-control none --import-source on \
-        -k regex:'gemm_pair_x_kernel|gemm_pair_kernel|rs_adam_emu|push_emu|pull_emu|attn_fwd_kernel|all_gather_emu' \
-        -s 40 -c 14 -o gpurun_out/prof_r2 python tools/ncu_targets.py
+        -k regex:'gemm_pair_x_kernel|gemm_pair_kernel|rs_adam_emu|push_emu|pull_emu|attn_fwd_kernel|attn_bwd|all_gather_emu' \
+        -s 30 -c 15 -o gpurun_out/prof_r2 python tools/ncu_targets.py
 
 Kernels: base pair GEMM (qkv fwd shape), extended GEMM gated NN / grouped NT / fp8 NT, emulated (4 logical ranks) fused
 reduce-scatter+AdamW, all-gather with flags, MoE push / pull, attention forward with the row-scatter epilogue."""
@@ -60,7 +60,12 @@ def main():
     cos, sin = F.rope_tables(2 * Sl, D, 10000.0, dev)
     stages = [_Stage(up, r, True) for r in range(2)]
     xu = [torch.randn(Sl, 4096, device=dev).to(torch.bfloat16) for _ in range(2)]
+    qkv_d = (torch.randn(1, 8192, (32 + 16) * 128, device=dev) / 4).to(torch.bfloat16).requires_grad_(True)
     for it in range(4):
+        # dense causal attention at the Llama-3-8B layer shape: forward, dQ and dK/dV kernels
+        o_d = F.flash_attention_qkv(qkv_d, 32, 8, 128, causal=True)
+        o_d.backward(o_d.detach())
+        qkv_d.grad = None
         F.gemm(a, b, 0)
         gemm_gated(a, bn, 1, gate)
         grouped_gemm_nt(xg, wg, off)
