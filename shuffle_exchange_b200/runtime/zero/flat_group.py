@@ -189,9 +189,50 @@ class FlatGroup:
 
     # ------------------------------------------------------------------------------- gradients
     def ensure_flat_grad(self, zero: bool = True):
+        """The unit's flat gradient buffer.  With ``lazy_grad_zero`` it is NOT filled with zeros: every gradient producer overwrites on its
+        first delivery (``_sxb_grad_written``), so only the ranges no trainable parameter covers are cleared here and
+        parameters that never received a gradient are cleared right before the reduction
+        (:meth:`zero_unwritten_grads`) — a full fill of a Llama-3-8B layer unit cost 0.17 ms, 6 ms per step."""
         if self.flat_grad is None:
-            self.flat_grad = (torch.zeros if zero else torch.empty)(self.total, dtype=self.grad_dtype, device=self.device)
+            if zero and not self.lazy_grad_zero:
+                self.flat_grad = torch.zeros(self.total, dtype=self.grad_dtype, device=self.device)
+            else:
+                self.flat_grad = torch.empty(self.total, dtype=self.grad_dtype, device=self.device)
+                if zero:
+                    self.zero_dead_ranges(self.flat_grad)
         return self.flat_grad
+
+    # Opt-in (ZeRO-3 sets it): optimizers whose every reduction path calls ``zero_unwritten_grads`` first.
+    lazy_grad_zero = False
+
+    def dead_ranges(self):
+        """Element ranges of the flat layout that no trainable parameter covers: alignment gaps, frozen parameters and
+        the tail padding."""
+        dead = self.__dict__.get("_dead_ranges")
+        if dead is None:
+            dead, pos = [], 0
+            for i in sorted(range(len(self.params)), key=lambda j: self.offsets[j]):
+                if not self.trainable[i]:
+                    continue
+                if self.offsets[i] > pos:
+                    dead.append((pos, self.offsets[i]))
+                pos = max(pos, self.offsets[i] + self.numels[i])
+            if pos < self.total:
+                dead.append((pos, self.total))
+            self._dead_ranges = dead
+        return dead
+
+    def zero_dead_ranges(self, buf: torch.Tensor):
+        for a, b in self.dead_ranges():
+            buf[a:b].zero_()
+
+    def zero_unwritten_grads(self):
+        """Before the buffer is reduced: a trainable parameter nothing delivered a gradient for contributes zeros."""
+        if self.flat_grad is None or not self.lazy_grad_zero:
+            return
+        for i, p in enumerate(self.params):
+            if self.trainable[i] and not getattr(p, "_sxb_grad_written", False):
+                self.flat_grad[self.offsets[i]: self.offsets[i] + self.numels[i]].zero_()
 
     def grad_view(self, i: int) -> torch.Tensor:
         g = self.ensure_flat_grad()
@@ -235,6 +276,7 @@ class FlatGroup:
                      average: bool = True):
         """flat_grad --(reduce-scatter, mean over the group)--> grad_shard."""
         assert self.flat_grad is not None
+        self.zero_unwritten_grads()
         if self.grad_shard is None or not accumulate_into_shard:
             if self.grad_shard is None:
                 self.grad_shard = torch.zeros(self.part, dtype=self.grad_dtype, device=self.device)

@@ -185,7 +185,7 @@ class FusedZ3Comm:
         return ("rot", self._slot)
 
     def attach_unit_grads(self, unit):
-        """Give the unit a zeroed slice of its gradient arena (after every peer finished reading the arena's
+        """Give the unit a slice of its gradient arena (after every peer finished reading the arena's
         previous occupant) and point the parameters' main-grad views into it."""
         if unit.index in self.pinned_arenas:
             arena = self.pinned_arenas[unit.index]
@@ -197,7 +197,10 @@ class FusedZ3Comm:
         off = 0
         for fg in unit.groups:
             view = SymmView(arena, off, fg.total)
-            view.tensor.zero_()
+            if fg.lazy_grad_zero:
+                fg.zero_dead_ranges(view.tensor)   # parameters overwrite on first delivery; see ensure_flat_grad
+            else:
+                view.tensor.zero_()
             fg.flat_grad = view.tensor
             fg._symm_grad = view
             off += fg.total

@@ -231,6 +231,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                                hp_on_cpu=on_cpu, pin=self.offload_optimizer_pin or self.offload_param_pin,
                                lp_on_cpu=self.offload_param and not keep_full)
                 self._configure_zeropp(fg)
+                fg.lazy_grad_zero = os.environ.get("SXB_LAZY_GRAD_ZERO", "1") != "0"
                 src_pg = self.optimizer.param_groups[gi]
                 pg = {k: v for k, v in src_pg.items() if k != "params"}
                 hp = self._register_group(fg, pg)
@@ -610,6 +611,8 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             if not getattr(u, "attached", False):
                 self._attach_unit(u)
             # announce on the compute stream, wait + reduce on the reduce stream
+            for fg in u.groups:
+                fg.zero_unwritten_grads()
             epochs = [self.fused.announce(fg) for fg in u.groups]
             if stream is not None:
                 stream.wait_stream(get_accelerator().current_stream())
@@ -634,6 +637,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                 if fg.flat_grad is None:
                     fg.ensure_flat_grad()
                 if self.world == 1 and not accumulate:
+                    fg.zero_unwritten_grads()
                     fg.grad_shard = fg.flat_grad[: fg.part]     # alias: no copy on a single rank
                 else:
                     fg.reduce_grads(self.gradient_predivide_factor, accumulate_into_shard=accumulate)

@@ -107,3 +107,63 @@ def test_unsupported_switches_raise():
         DeepSpeedZeroOptimizer_Stage3(m, base, offload_param_config=_Cfg())
     with pytest.raises(NotImplementedError):
         DeepSpeedZeroOptimizer_Stage3(m, base, zero_quantized_nontrainable_weights=True)
+
+
+# ------------------------------------------------------------------ gradient buffers that are not zero-filled
+class _PartlyUsed(nn.Module):
+    """One layer's bias is frozen and one whole linear is never used in forward: their ranges of the flat gradient
+    buffer are never written by a gradient producer."""
+
+    def __init__(self):
+        super().__init__()
+        self.layers = nn.ModuleList([nn.Linear(64, 64) for _ in range(2)])
+        self.unused = nn.ModuleList([nn.Linear(64, 64)])
+        self.layers[0].bias.requires_grad_(False)
+
+    def forward(self, x):
+        for l in self.layers:
+            x = torch.tanh(l(x))
+        return (x.float() ** 2).mean()
+
+
+def _lazy_zero_worker(rank, world):
+    import shuffle_exchange_b200 as ds
+    from shuffle_exchange_b200.utils.tensor_fragment import safe_get_full_fp32_param
+    torch.manual_seed(0)
+    model = _PartlyUsed().to(torch.bfloat16)
+    before = {n: p.detach().float().clone() for n, p in model.named_parameters()}
+    cfg = {"train_micro_batch_size_per_gpu": 4, "steps_per_print": 10 ** 9, "bf16": {"enabled": True},
+           "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}},
+           "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}}
+    engine, opt, _, _ = ds.initialize(model=model, config=cfg, model_parameters=model.parameters())
+    assert all(fg.lazy_grad_zero for fg in opt.groups)
+    # poison what the allocator hands out next: a buffer that is read without having been written shows up as NaN
+    for fg in opt.groups:
+        assert fg.dead_ranges() is not None
+    real_empty = torch.empty
+
+    def poisoned(*a, **k):
+        t = real_empty(*a, **k)
+        if t.is_floating_point() and t.numel():
+            t.fill_(float("nan"))
+        return t
+    torch.empty = poisoned
+    try:
+        for _ in range(2):
+            loss = engine(torch.randn(4, 64).to(torch.bfloat16))
+            engine.backward(loss)
+            engine.step()
+    finally:
+        torch.empty = real_empty
+    after = {n: safe_get_full_fp32_param(p) for n, p in model.named_parameters()}
+    for n, a in after.items():
+        assert torch.isfinite(a).all(), n
+        moved = not torch.equal(a.cpu().float(), before[n])
+        if n.startswith("unused") or n == "layers.0.bias":
+            assert not moved, f"{n} has no gradient and no weight decay: it must not move"
+        else:
+            assert moved, n
+
+
+def test_unwritten_gradient_ranges_read_as_zero():
+    run_dist(_lazy_zero_worker, 2)
