@@ -150,6 +150,232 @@ int sxbh_plan_hoist_gathers(int n, const int* kind, const int* unit, const int* 
                             const double* time_us, const int* persistent, int n_persistent, long long budget,
                             int* perm);
 
+/* ==== declarations below are kept in step with csrc/ by tools/gen_header.py ==== */
+
+/* ---- csrc/attention.cu */
+/* K7 (Ulysses): forward attention whose epilogue stores each output row straight into the buffer of the rank that
+ * owns that part of the sequence.  out_peers: host array of `world` device pointers — peer r's destination for the
+ * rows [r*rows_per_peer, (r+1)*rows_per_peer) of this rank's heads (column offset already applied), row pitch
+ * o_stride.  `out` is unused.  (reference: all_to_all_single after the local attention, sequence/layer.py:434-437) */
+int sxb_attn_fwd_scatter(const void* q, const void* k, const void* v, void* const* out_peers, int world,
+                         int rows_per_peer, void* out_keep, long long keep_stride, void* lse, int B, int S, int Hq,
+                         int Hk, int D, long long q_stride, long long k_stride, long long v_stride,
+                         long long o_stride, int causal, float scale, void* stream);
+/* Backward with scattered dQ / dK / dV: dq_peers[r] / dk_peers[r] are peer r's destinations (column offsets of this
+ * rank's heads applied) with row pitches dq_stride / dk_stride; dV lands dv_col_delta elements after dK with pitch
+ * dv_stride. */
+int sxb_attn_bwd_scatter(const void* q, const void* k, const void* v, const void* out, const void* d_out,
+                         const void* lse, void* delta, void* const* dq_peers, void* const* dk_peers,
+                         long long dv_col_delta, int world, int rows_per_peer, int B, int S, int Hq, int Hk, int D,
+                         long long q_stride, long long k_stride, long long v_stride, long long o_stride,
+                         long long do_stride, long long dq_stride, long long dk_stride, long long dv_stride,
+                         int causal, float scale, void* stream);
+/* Packed sequences (cu_seqlens int32 [nseq + 1] on the device; q/k/v/out [total, H, D]; lse / delta [Hq, total]):
+ * every sequence attends only to itself.  The reference reaches this through flash-attn's varlen entry points
+ * (sequence/fpdt_layer.py:14-20, inference/v2 blocked_flash); here it is the same three kernels with a per-CTA
+ * row window. */
+int sxb_attn_fwd_varlen(const void* q, const void* k, const void* v, void* out, void* lse, const void* cu_seqlens,
+                        int nseq, int max_seqlen, int total, int Hq, int Hk, int D, long long q_stride,
+                        long long k_stride, long long v_stride, long long o_stride, int causal, float scale,
+                        void* stream);
+int sxb_attn_bwd_varlen(const void* q, const void* k, const void* v, const void* out, const void* d_out,
+                        const void* lse, void* delta, void* dq, void* dk, void* dv, const void* cu_seqlens,
+                        int nseq, int max_seqlen, int total, int Hq, int Hk, int D, long long q_stride,
+                        long long k_stride, long long v_stride, long long o_stride, long long do_stride,
+                        long long dq_stride, long long dk_stride, long long dv_stride, int causal, float scale,
+                        void* stream);
+/* Blocked ("paged") flash attention over a ragged batch on the tensor cores: the forward kernel above, one CTA per
+ * (attention atom, q head).  q/out [T, Hq, D]; cache [n_blocks, block_size, 2, Hk, D] (K then V per slot); atoms
+ * int32 [n_atoms, 6] and block_tables int32 [n_seqs, max_blocks] on the device.  block_size: a multiple of 8 that
+ * divides 64, or a multiple of 64.  Causal by position: query i of an atom sits at global_q_idx + i.
+ * (reference: inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.cpp:21-101 over flash-attn's sm_80 kernels) */
+int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, const void* atoms, int n_atoms,
+                       const void* block_tables, int max_blocks, int n_blocks, int block_size, int T, int Hq,
+                       int Hk, int D, long long q_stride, long long o_stride, float scale, void* stream);
+
+/* ---- csrc/gemm_ext.cu */
+/* C (+)= alpha * op(A) op(B) with optional gating / grouping / fp8 operands (see the file header).
+ *   ab_dtype: kBF16 (2) or kFP8E4M3 (3; NT layout only).  c_dtype: kBF16 or kF32.
+ *   gate_flags == NULL: no gating.  Else flags[c] >= gate_value (as a wrapping 32-bit sequence number) means bytes
+ *     [c*gate_chunk, (c+1)*gate_chunk) of the buffer B lives in have arrived; gate_base = byte offset of B in it.
+ *   group_mode 0: plain.  1 (ragged-M, NT/NN): offsets[num_groups+1] (device, rows, multiples of 256); A and C have
+ *     total_rows rows; B is the row-wise stack of the groups' matrices (NT: num_groups*N rows; NN: num_groups*K).
+ *     2 (ragged-K, TN): offsets multiples of 64; A [total_rows, M], B [total_rows, N]; C = num_groups matrices
+ *     [M, N] spaced c_group_stride elements apart (M multiple of 128).
+ *   scale_a[row of A] / scale_b[g*N + column]: fp8 dequantisation scales (either may be NULL). */
+int sxb_gemm_ext(const void* A, const void* B, void* C, int M, int N, int K, int layout, long long lda,
+                 long long ldb, long long ldc, int ab_dtype, int c_dtype, int accumulate, float alpha,
+                 const void* gate_flags, unsigned int gate_value, long long gate_base, long long gate_chunk,
+                 long long gate_nchunks, int group_mode, int num_groups, const void* offsets, long long total_rows,
+                 long long c_group_stride, const void* scale_a, const void* scale_b, int max_ctas, void* stream);
+/* K6 (Ulysses): C = A op(B) whose epilogue stores every 64-column block of the result straight into the buffer of the
+ * rank that owns those heads (direct peer stores over NVLink).  table: device int32 [2 * N/64] = (owner, destination
+ * column) per block; peers: host array of `world` device pointers; the result row r lands in row row0 + r of the
+ * destination (pitch dst_ld elements).  bf16 only, plain (ungrouped) problem, N % 64 == 0.
+ * (reference: QKV projection, then three all_to_all_single, sequence/layer.py:388-426) */
+int sxb_gemm_scatter(const void* A, const void* B, int M, int N, int K, int layout, long long lda, long long ldb,
+                     const void* table, void* const* peers, int world, long long dst_ld, long long row0,
+                     float alpha, int max_ctas, void* stream);
+int sxb_stream_write_u32(void* dst, unsigned int value, void* stream);
+
+/* ---- csrc/moe_ep.cu */
+/* All pointer tables are host arrays of `world` device pointers (peer mappings).  tables: device int32
+ * [E + 2L + 2] (layout above).  E = world * L.  cap_rows: rows of every receive / return buffer. */
+int sxb_moe_ep_plan(const void* const* counts, const void* const* sigs, int rank, int world, const void* my_counts,
+                    void* tables, int E, int L, int cap_rows, unsigned int epoch, unsigned int pulled_epoch,
+                    int exchange, void* stream);
+int sxb_moe_ep_plan_emu(const void* const* counts, const void* const* sigs, int world,
+                        const void* const* my_counts, void* const* tables, int E, int L, int cap_rows,
+                        unsigned int epoch, unsigned int pulled_epoch, int exchange, void* stream);
+int sxb_moe_ep_push(const void* const* recv, const void* const* sigs, int rank, int world, const void* x,
+                    const void* weights, const void* pulled, void* d_scores, const void* assign,
+                    const void* offsets, const void* tables, int T, int K, int H, int E, int L, int cap_rows,
+                    unsigned int epoch, void* counter, int max_ctas, void* stream);
+int sxb_moe_ep_push_emu(const void* const* recv, const void* const* sigs, int world, const void* const* x,
+                        const void* const* weights, const void* const* pulled, void* const* d_scores,
+                        const void* const* assign, const void* const* offsets, const void* const* tables, int T,
+                        int K, int H, int E, int L, int cap_rows, unsigned int epoch, void* const* counters,
+                        int ctas_per_rank, void* stream);
+int sxb_moe_ep_pull(const void* const* ret, const void* const* sigs, int rank, int world, void* out,
+                    const void* weights, void* keep, const void* assign, const void* offsets, const void* tables,
+                    int T, int K, int H, int E, int L, int cap_rows, unsigned int epoch, void* counter,
+                    int max_ctas, void* stream);
+int sxb_moe_ep_pull_emu(const void* const* ret, const void* const* sigs, int world, void* const* out,
+                        const void* const* weights, void* const* keep, const void* const* assign,
+                        const void* const* offsets, const void* const* tables, int T, int K, int H, int E, int L,
+                        int cap_rows, unsigned int epoch, void* const* counters, int ctas_per_rank, void* stream);
+
+/* ---- csrc/moe_ragged.cu */
+/* logits [T, E]; scores fp32 [T, K]; assignments / offsets int32 [T, K]; expert_counts int32 [E] (zeroed here). */
+int sxb_top_k_gating(const void* logits, void* scores, void* assignments, void* offsets, void* expert_counts,
+                     int n_tokens, int n_experts, int top_k, int renormalize, int dtype, void* stream);
+/* x [T, H] -> moe_input [T*K, H] grouped by expert; expert_cumsum int64 [E]; mapped_slots int32 [T, K]. */
+int sxb_moe_scatter(const void* x, void* moe_input, const void* assignments, const void* offsets,
+                    const void* expert_counts, void* expert_cumsum, void* mapped_slots, int n_tokens,
+                    int n_experts, int top_k, int hidden, int elem_size, void* stream);
+/* out [T, H] = sum_k scores * moe_output[slot]  (scores may be NULL: plain sum).  bf16 rows. */
+int sxb_moe_gather(const void* moe_output, void* out, const void* scores, const void* mapped_slots, int n_tokens,
+                   int top_k, int hidden, void* stream);
+/* Backward of gather: d_moe_output[slot] = scores * d_out ; d_scores[t,k] = <d_out[t], moe_output[slot]>. */
+int sxb_moe_gather_bwd(const void* d_out, const void* moe_output, const void* scores, const void* mapped_slots,
+                       void* d_moe_output, void* d_scores, int n_tokens, int top_k, int hidden, void* stream);
+int sxb_ragged_embed(const void* ids, const void* pos, const void* table, const void* pos_table, void* out,
+                     int n_tokens, int hidden, int pos_offset, void* stream);
+int sxb_logits_gather(const void* hidden_states, const void* last_token, void* out, int n_seqs, int hidden,
+                      void* stream);
+int sxb_kv_rotary_blocked(void* qkv, void* cache, const void* tok_seq, const void* tok_pos,
+                          const void* block_tables, int n_tokens, int max_blocks, int block_size, int Hq, int Hk,
+                          int D, int rot_dim, float theta, void* stream);
+int sxb_paged_attention(const void* q, void* out, const void* cache, const void* tok_seq, const void* tok_pos,
+                        const void* block_tables, int n_tokens, int max_blocks, int block_size, int Hq, int Hk,
+                        int D, long long q_stride, float scale, void* stream);
+
+/* ---- csrc/quantize.cu */
+/* Grouped integer quantisation.  in: [groups, group_size] of `dtype`; q: groups*group_size*bits/8 bytes;
+ * scales: fp32 [groups] (symmetric) or [groups, 2] = (scale, min) (asymmetric).  nodes/devs > 1 select the
+ * qgZ swizzled output order.  bits in {4, 8}. */
+int sxb_quantize_int(const void* in, void* q, void* scales, long long groups, int group_size, int bits,
+                     int symmetric, int stochastic, unsigned seed, int nodes, int devs, int dtype, void* stream);
+int sxb_dequantize_int(const void* q, const void* scales, void* out, long long groups, int group_size, int bits,
+                       int symmetric, int dtype, void* stream);
+/* q_in: [devs, out_groups] groups, reduced over devs and re-quantised into q_out [out_groups]. */
+int sxb_quantized_reduction(const void* q_in, const void* s_in, void* q_out, void* s_out, long long out_groups,
+                            int group_size, int bits, int symmetric, int devs, void* stream);
+/* out: [groups, group_size*q_bits/8 + 4] bytes (payload then the fp32 scale).  q_bits in {4, 6, 8, 12}. */
+int sxb_fp_quantize(const void* in, void* out, long long groups, int group_size, int q_bits, int stochastic,
+                    unsigned seed, int dtype, void* stream);
+/* rows == NULL: dequantise all `out_groups` groups.  Otherwise output row r is input row rows[r], a row
+ * being groups_per_row consecutive groups (selective dequantisation, e.g. of the experts actually routed to). */
+int sxb_fp_dequantize(const void* in, void* out, long long out_groups, int group_size, int q_bits,
+                      const void* rows, long long groups_per_row, int dtype, void* stream);
+int sxb_packbits(const void* in, void* out, long long n, int dtype, void* stream);
+int sxb_unpackbits(const void* in, void* out, long long n, float scale, int dtype, void* stream);
+/* idx: int32 [rows, k], sorted ascending in place per row (k <= 4096). */
+int sxb_token_sort(void* idx, int rows, int k, void* stream);
+/* full: [batch, seq, hidden] (batch_first) or [seq, batch, hidden]; part: same with seq -> k; idx int32 [batch, k].
+ * scatter = 0: part <- full[idx] ; scatter = 1: full[idx] <- part.  hidden*elem_size must be a multiple of 16. */
+int sxb_token_move(void* full, void* part, const void* idx, int batch, int seq, int k, int hidden, int elem_size,
+                   int batch_first, int scatter, void* stream);
+/* in: bf16 [rows, cols] (pitch ld_in elements, cols % 8 == 0, 16-byte aligned rows); out: e4m3 bytes (pitch ld_out,
+ * multiple of 8); scales: fp32 [rows].  Dequantised value = e4m3 * scale. */
+int sxb_fp8_rowwise_quant(const void* in, void* out, void* scales, long long rows, int cols, long long ld_in,
+                          long long ld_out, void* stream);
+
+/* ---- csrc/softmax_dropout.cu */
+/* out = residual + dropout(x + bias); ``keep`` (uint8 per element) may be null when p == 0.  n % 4 == 0, cols % 4 == 0. */
+int sxb_bias_dropout_residual(const void* x, const void* bias, const void* residual, void* out, void* keep,
+                              long long n, int cols, float p, long long seed, long long offset, int dtype,
+                              void* stream);
+int sxb_dropout_bwd(const void* dy, const void* keep, void* dx, long long n, float p, int dtype, void* stream);
+/* scores/out [B, H, Sq, Sk] contiguous; bias strides in elements (b, h, q, k), 0 = broadcast. */
+int sxb_biased_softmax_fwd(const void* scores, void* out, const void* bias1, long long b1b, long long b1h,
+                           long long b1q, long long b1k, const void* bias2, long long b2b, long long b2h,
+                           long long b2q, long long b2k, long long B, int H, int Sq, int Sk, float scale,
+                           int dtype, void* stream);
+int sxb_biased_softmax_bwd(const void* y, const void* dy, void* ds, void* dbias, long long rows, int Sk,
+                           float scale, int dtype, void* stream);
+int sxb_bsr_softmax_fwd(const void* x, void* y, const void* row_ptr, const void* col_idx, long long B, int H,
+                        int nrb, int ncb, int blk, int nnz, const void* rpe, long long rpe_sb, const void* kpm,
+                        int kpm_mode, const void* amask, int amask_mode, float scale, int dtype, void* stream);
+int sxb_bsr_softmax_bwd(const void* y, const void* dy, void* dx, const void* row_ptr, const void* col_idx,
+                        long long B, int H, int nrb, int ncb, int blk, int nnz, float scale, int dtype,
+                        void* stream);
+
+/* ---- csrc/symm_collectives.cu */
+/* K1.  bufs/sigs: host arrays of `world` device pointers (peer mappings of the flat bf16 gradient buffer
+ * and of the signal pads).  part: elements per shard (multiple of 8).  counter: device uint32 (zeroed once).
+ * apply_adam == 0 -> plain reduce-scatter(mean) into grad_out (used when the step must be deferred).
+ * handshake_done != 0: the caller already announced "gradients ready" (sxb_symm_signal on the stream that produced
+ * them) and waited for the peers (sxb_symm_wait on this stream); no CTA of this grid spins. */
+int sxb_symm_rs_adam(const void* const* bufs, const void* const* sigs, int rank, int world, long long part,
+                     void* hp, void* m, void* v, void* lp, void* grad_out, float lr, float beta1, float beta2,
+                     float eps, float weight_decay, int step, int adamw, int bias_correction, float grad_scale,
+                     unsigned int epoch, const void* multicast_ptr, void* counter, int apply_adam, int max_ctas,
+                     int handshake_done, void* stream);
+/* K1, `world` logical ranks emulated on ONE GPU by one cooperative grid.  bufs/sigs as above (all local);
+ * hp/m/v/lp/grad_out/counters: host arrays of `world` per-rank device pointers.  ctas_per_rank * world CTAs of 512
+ * threads must be co-resident (cudaLaunchCooperativeKernel refuses otherwise). */
+int sxb_symm_rs_adam_emu(const void* const* bufs, const void* const* sigs, int world, long long part,
+                         void* const* hp, void* const* m, void* const* v, void* const* lp, void* const* grad_out,
+                         float lr, float beta1, float beta2, float eps, float weight_decay, int step, int adamw,
+                         int bias_correction, float grad_scale, unsigned int epoch, void* const* counters,
+                         int apply_adam, int ctas_per_rank, void* stream);
+int sxb_symm_barrier(const void* const* bufs, const void* const* sigs, int rank, int world, int channel,
+                     unsigned int epoch, void* stream);
+int sxb_symm_signal(const void* const* bufs, const void* const* sigs, int rank, int world, int channel,
+                    unsigned int epoch, void* stream);
+int sxb_symm_wait(const void* const* bufs, const void* const* sigs, int rank, int world, int channel,
+                  unsigned int epoch, void* stream);
+int sxb_symm_subset_mean(const void* const* bufs, const void* const* sigs, int rank, int world, const int* members,
+                         int n_members, void* out, long long n, int dtype, unsigned int epoch, void* counter,
+                         int max_ctas, void* stream);
+/* K9, general form: out = sum_k weights[k] * shard of members[k] (weights == NULL: the mean).  One kernel serves RR
+ * (all replicas), shuffle (my ring), H-RR (two-level mean as per-member weights) and Gossip push-sum (alpha ratios). */
+int sxb_symm_subset_wsum(const void* const* bufs, const void* const* sigs, int rank, int world, const int* members,
+                         const float* weights, int n_members, void* out, long long n, int dtype,
+                         unsigned int epoch, void* counter, int max_ctas, void* stream);
+/* K9 emulated (bf16).  As in the real launch EVERY rank runs the kernel, each over its own ring: members is a
+ * [world][16] row-major table, n_members[r] the length of row r (row r must contain r). */
+int sxb_symm_subset_mean_emu(const void* const* bufs, const void* const* sigs, int world, const int* members,
+                             const int* n_members, void* const* outs, long long n, unsigned int epoch,
+                             void* const* counters, int ctas_per_rank, void* stream);
+/* K2 gather half.  chunk_flags (optional, device uint32[ceil(world*part_bytes / chunk_bytes)]): chunk c is set to
+ * `flag_value` (release, gpu scope) once all of its bytes are in dst — the gated GEMM polls these. */
+int sxb_symm_all_gather(const void* const* bufs, const void* const* sigs, int rank, int world,
+                        long long part_bytes, void* dst, long long chunk_bytes, void* chunk_flags,
+                        unsigned int epoch, int max_ctas, unsigned int flag_value, void* stream);
+int sxb_symm_all_gather_emu(const void* const* bufs, const void* const* sigs, int world, long long part_bytes,
+                            void* const* dsts, long long chunk_bytes, void* const* chunk_flags, unsigned int epoch,
+                            unsigned int flag_value, int ctas_per_rank, void* stream);
+int sxb_symm_a2a_rows(const void* const* bufs, const void* const* sigs, int rank, int world, const void* src,
+                      const long long* send_off, const long long* recv_off, const long long* count, int row_bytes,
+                      unsigned int epoch, void* counter, int max_ctas, void* stream);
+/* Emulated: srcs[r], and send_off/recv_off/count as [world][world] row-major int64 tables (row r = rank r's tables). */
+int sxb_symm_a2a_rows_emu(const void* const* bufs, const void* const* sigs, int world, const void* const* srcs,
+                          const long long* send_off, const long long* recv_off, const long long* count,
+                          int row_bytes, unsigned int epoch, void* const* counters, int ctas_per_rank,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -12,6 +12,19 @@ _spec.loader.exec_module(selftest)
 
 NUMERIC = [n for n in selftest.CHECKS if not n.endswith("_perf")]
 TOL = 2e-2
+# Element-wise bound |a - b| <= tol * (|b| + rms(b)).  Attention backward rounds P and dS to bf16 before the second
+# GEMMs (as every flash-attention implementation does); a CPU emulation of exactly that rounding gives 0.018-0.031
+# under this metric for the shapes tested here, so its bound is 5e-2.
+# The same emulation at 1k-4k tokens gives 0.03-0.06 (the maximum over more elements grows slowly with the sequence),
+# hence 0.12 for the 4k / 8k comparison against fp32 SDPA.
+TOL_BY_PREFIX = {"attn_bwd": 5e-2, "attn_fused_qkv": 5e-2, "attn_long_vs_sdpa": 0.12}
+
+
+def _tol(name):
+    for prefix, tol in TOL_BY_PREFIX.items():
+        if name.startswith(prefix):
+            return tol
+    return TOL
 
 
 @pytest.mark.gpu
@@ -24,7 +37,7 @@ def test_kernel_numerics(name):
     assert "hang" not in res, res
     assert lib.hang_info("gemm") is None and lib.hang_info("attn") is None
     err = res.get("err")
-    assert err is not None and err == err and err < TOL, (name, res)
+    assert err is not None and err == err and err < _tol(name), (name, res)
 
 
 @pytest.mark.gpu
