@@ -50,6 +50,10 @@ struct Params {
   const int* atoms;
   const int* block_tables;   // [n_seqs, max_blocks]
   int max_blocks, block_size;
+  // pack > 1 (atoms of at most 128 / pack queries, e.g. decode): the `pack` q heads that share one KV head are packed
+  // into the tile's rows (row r = query r / pack, head hk * pack + r % pack), one CTA per KV head: K/V are read once
+  // per KV head instead of once per q head.
+  int pack;
 };
 
 // The rows of the tensors one CTA works on: sequence b of a dense batch, or sequence b of a packed one.
@@ -195,8 +199,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // tile index is the SLOWEST grid dimension: CTAs are handed out in linear block order, so every (head, batch)
   // of the heaviest causal tile starts before any lighter tile (longest-first packing over the 148 SMs)
-  const int h = blockIdx.x, b = blockIdx.y;
-  const int hk = h / (p.Hq / p.Hk);
+  const int pack = p.pack > 1 ? p.pack : 1;
+  const int b = blockIdx.y;
+  const int hk = pack > 1 ? (int)blockIdx.x : (int)blockIdx.x / (p.Hq / p.Hk);
+  const int h = pack > 1 ? hk * pack : (int)blockIdx.x;      // (first) q head of this CTA
   // The tile: TMA row of its first query, that query's position inside its sequence, valid rows, keys it attends to.
   Win w;
   int q_row0, q_pos0, q_rows, kv_len;
@@ -368,7 +374,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int quad = warp & 3;
     const int row = quad * 32 + lane;
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
-    const int qpos = q_pos0 + row;
+    const int qtok = pack > 1 ? row / pack : row;               // query (token) index inside the tile
+    const int qhead = pack > 1 ? h + (row - qtok * pack) : h;
+    const int qpos = q_pos0 + qtok;
     const float sc = p.scale * kLog2e;
     float m_run = -INFINITY, l_run = 0.f;
     for (int j = 0; j < nblk; ++j) {
@@ -449,14 +457,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     {
       // tcgen05.ld is warp-collective (.sync.aligned): every lane issues it, only the global
       // stores are predicated on the row being inside the sequence.
-      const bool valid = row < q_rows;
-      const int grow = valid ? q_row0 + row : q_row0;   // row of the [rows, H, D] tensors
-      __nv_bfloat16* orow = out_row_ptr(p, false, w.tb, grow) + (long long)h * D;
+      const bool valid = qtok < q_rows;
+      const int grow = valid ? q_row0 + qtok : q_row0;   // row of the [rows, H, D] tensors
+      __nv_bfloat16* orow = out_row_ptr(p, false, w.tb, grow) + (long long)qhead * D;
       // scattering forward keeps a LOCAL copy of O as well (p.out, pitch out2_stride): the backward needs
       // rowsum(dO * O) where the heads are, not where the sequence is
       __nv_bfloat16* orow_keep = (p.scatter_rows > 0 && p.out != nullptr)
           ? reinterpret_cast<__nv_bfloat16*>(p.out) + ((long long)w.tb * p.S + grow) * p.out2_stride +
-                (long long)h * D
+                (long long)qhead * D
           : nullptr;
 #pragma unroll 1
       for (int c = 0; c < D / 32; ++c) {
@@ -477,7 +485,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
       }
       if (valid && p.lse)
-        p.lse[stat_base(p, w, b, h) - w.off + grow] =
+        p.lse[stat_base(p, w, b, qhead) - w.off + grow] =
             (l_run > 0.f) ? (m_run + log2f(l_run)) * kLn2 : -INFINITY;
     }
   }
@@ -1078,12 +1086,12 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __re
 }
 
 static int make_qkv_map(CUtensorMap* m, const void* ptr, int B, int S, int H, int D,
-                        long long row_stride, int box_rows) {
+                        long long row_stride, int box_rows, int box_heads = 1) {
   unsigned long long dims[4] = {(unsigned long long)D, (unsigned long long)H,
                                 (unsigned long long)S, (unsigned long long)B};
   unsigned long long strides[3] = {(unsigned long long)D * 2, (unsigned long long)row_stride * 2,
                                    (unsigned long long)row_stride * 2 * (unsigned long long)S};
-  unsigned int box[4] = {64, 1, (unsigned int)box_rows, 1};
+  unsigned int box[4] = {64, (unsigned int)box_heads, (unsigned int)box_rows, 1};
   return encode_tensor_map(m, kBF16, 4, ptr, dims, strides, box, 128);
 }
 
@@ -1384,10 +1392,15 @@ SXB_API int sxb_attn_bwd_varlen(const void* q, const void* k, const void* v, con
 // int32 [n_atoms, 6] and block_tables int32 [n_seqs, max_blocks] on the device.  block_size: a multiple of 8 that
 // divides 64, or a multiple of 64.  Causal by position: query i of an atom sits at global_q_idx + i.
 // (reference: inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.cpp:21-101 over flash-attn's sm_80 kernels)
+// n_packed: the LAST n_packed atoms of the table have at most 128 / (Hq / Hk) queries each and run with the GQA group
+// packed into the tile (one CTA per KV head); 0 = none.
 SXB_API int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, const void* atoms, int n_atoms,
-                               const void* block_tables, int max_blocks, int n_blocks, int block_size, int T, int Hq,
-                               int Hk, int D, long long q_stride, long long o_stride, float scale, void* stream) {
+                               int n_packed, const void* block_tables, int max_blocks, int n_blocks, int block_size,
+                               int T, int Hq, int Hk, int D, long long q_stride, long long o_stride, float scale,
+                               void* stream) {
   if (n_atoms <= 0) return SXB_OK;
+  const int group = Hk > 0 ? Hq / Hk : 0;
+  if (n_packed < 0 || n_packed > n_atoms || (n_packed > 0 && (group < 2 || BQ % group))) return SXB_ERR_BAD_ARG;
   if (!attn_args_ok(1, T, Hq, Hk, D, q_stride, 8, 8) || (o_stride % 8)) return SXB_ERR_UNSUPPORTED;
   if (block_size < 8 || (block_size % 8) || (block_size < BC ? (BC % block_size) : (block_size % BC)))
     return SXB_ERR_UNSUPPORTED;
@@ -1405,8 +1418,27 @@ SXB_API int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, cons
   p.atoms = static_cast<const int*>(atoms);
   p.block_tables = static_cast<const int*>(block_tables);
   p.max_blocks = max_blocks; p.block_size = block_size;
-  dim3 grid(Hq, 1, n_atoms);
   cudaStream_t s = (cudaStream_t)stream;
+  if (n_packed > 0) {
+    // Q box = {64, group heads, 128 / group queries}: the TMA writes rows in (query, head) order
+    CUtensorMap tqp;
+    if ((rc = make_qkv_map(&tqp, q, 1, T, Hq, D, q_stride, BQ / group, group))) return rc;
+    Params pp = p;
+    pp.pack = group;
+    pp.atoms = p.atoms + 6LL * (n_atoms - n_packed);
+    dim3 gridp(Hk, 1, n_packed);
+    if (D == 128) {
+      if ((rc = set_smem(attn_fwd_kernel<128, 1>, FwdSmem<128>::kTotal))) return rc;
+      attn_fwd_kernel<128, 1><<<gridp, kThreads, FwdSmem<128>::kTotal, s>>>(tqp, tk, tv, pp);
+    } else {
+      if ((rc = set_smem(attn_fwd_kernel<64, 1>, FwdSmem<64>::kTotal))) return rc;
+      attn_fwd_kernel<64, 1><<<gridp, kThreads, FwdSmem<64>::kTotal, s>>>(tqp, tk, tv, pp);
+    }
+    SXB_CHECK_LAUNCH();
+    n_atoms -= n_packed;
+    if (n_atoms == 0) return SXB_OK;
+  }
+  dim3 grid(Hq, 1, n_atoms);
   const long long cache_bytes = (long long)n_blocks * block_size * slot * 2;
   if (use_multicast(Hq, Hk, D, cache, cache_bytes, cache, cache_bytes)) {
     if ((rc = set_smem(attn_fwd_kernel<128, 2>, FwdSmem<128>::kTotal))) return rc;

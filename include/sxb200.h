@@ -189,7 +189,7 @@ int sxb_attn_bwd_varlen(const void* q, const void* k, const void* v, const void*
  * int32 [n_atoms, 6] and block_tables int32 [n_seqs, max_blocks] on the device.  block_size: a multiple of 8 that
  * divides 64, or a multiple of 64.  Causal by position: query i of an atom sits at global_q_idx + i.
  * (reference: inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.cpp:21-101 over flash-attn's sm_80 kernels) */
-int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, const void* atoms, int n_atoms,
+int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, const void* atoms, int n_atoms, int n_packed,
                        const void* block_tables, int max_blocks, int n_blocks, int block_size, int T, int Hq,
                        int Hk, int D, long long q_stride, long long o_stride, float scale, void* stream);
 

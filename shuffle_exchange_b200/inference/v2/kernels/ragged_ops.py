@@ -16,7 +16,7 @@ _lib.register({
     "sxb_logits_gather": "ppp" "ii" "p",
     "sxb_kv_rotary_blocked": "ppppp" "iiiiiii" "f" "p",
     "sxb_paged_attention": "pppppp" "iiiiii" "l" "f" "p",
-    "sxb_attn_fwd_atoms": "ppp" "pi" "piii" "iiii" "ll" "f" "p",
+    "sxb_attn_fwd_atoms": "ppp" "pii" "piii" "iiii" "ll" "f" "p",
 })
 
 
@@ -119,17 +119,18 @@ def atoms_supported(q: torch.Tensor, cache: torch.Tensor) -> bool:
 
 
 def paged_attention_atoms(q: torch.Tensor, cache: torch.Tensor, atoms: torch.Tensor, block_tables: torch.Tensor,
-                          scale: float = None) -> torch.Tensor:
+                          scale: float = None, n_packed: int = 0) -> torch.Tensor:
     """The same attention as :func:`paged_attention`, scheduled by attention atoms on the tcgen05 flash kernel: one CTA
     per (atom, q head) runs 128 queries of one sequence against that sequence's pages, K/V tiles fetched by TMA through
     the block table (``csrc/attention.cu``: ``sxb_attn_fwd_atoms``).  Prefill re-reads K/V once per 128 queries instead
-    of once per query."""
+    of once per query.  ``n_packed``: the last that many atoms have at most ``128 // (n_q // n_kv)`` queries and run
+    with the GQA group packed into the tile (K/V read once per KV head: decode)."""
     T, n_q, D = q.shape
     n_kv = cache.shape[3]
     scale = 1.0 / math.sqrt(D) if scale is None else scale
     out = torch.empty(T, n_q, D, dtype=q.dtype, device=q.device)
     _lib.call("sxb_attn_fwd_atoms", q.data_ptr(), cache.data_ptr(), out.data_ptr(), atoms.data_ptr(), atoms.shape[0],
-              block_tables.data_ptr(), block_tables.shape[1], cache.shape[0], cache.shape[1], T, n_q, n_kv, D,
+              int(n_packed), block_tables.data_ptr(), block_tables.shape[1], cache.shape[0], cache.shape[1], T, n_q, n_kv, D,
               q.stride(0), out.stride(0), float(scale), _lib.stream_ptr())
     return out
 
@@ -138,7 +139,11 @@ def ragged_attention(q: torch.Tensor, cache: torch.Tensor, batch, scale: float =
     """Attention of a finalized ragged batch: atoms on the tensor cores where the layout allows, else per token."""
     atoms = batch.atoms() if hasattr(batch, "atoms") else None
     if atoms is not None and atoms.shape[0] > 0 and atoms_supported(q, cache):
-        return paged_attention_atoms(q, cache, atoms, batch.block_tables(), scale)
+        group = q.shape[1] // cache.shape[3]
+        n_packed = 0
+        if group > 1 and 128 % group == 0 and hasattr(batch, "atoms_longer_than"):
+            n_packed = atoms.shape[0] - batch.atoms_longer_than(128 // group)
+        return paged_attention_atoms(q, cache, atoms, batch.block_tables(), scale, n_packed)
     return paged_attention(q, cache, batch.token_to_seq(), batch.token_positions(), batch.block_tables(), scale)
 
 

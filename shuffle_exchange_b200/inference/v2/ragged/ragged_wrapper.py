@@ -62,7 +62,13 @@ class RaggedBatchWrapper:
         if self._n_seqs:
             from ..kernels.atom_builder import AtomBuilder
             m = self._seq_meta[:, : self._n_seqs].contiguous()
-            _, self._n_atoms = AtomBuilder()(self._views(self._host)[5], m[0], m[1], m[2], ATOM_Q_BLOCK, ATOM_KV_BLOCK)
+            atoms, self._n_atoms = AtomBuilder()(self._views(self._host)[5], m[0], m[1], m[2], ATOM_Q_BLOCK, ATOM_KV_BLOCK)
+            # longest first: the kernel runs the short tail (decode tokens, chunk remainders) with the GQA group packed
+            # into one tile, and needs those atoms contiguous
+            live = atoms[: self._n_atoms]
+            order = torch.argsort(live[:, 2], descending=True, stable=True)
+            live.copy_(live[order])
+            self._atom_q_lens = live[:, 2].clone()
         self._dev.copy_(self._host, non_blocking=True)
         self._finalized = True
 
@@ -85,6 +91,10 @@ class RaggedBatchWrapper:
     def atoms(self):
         """int32 ``[n_atoms, 6]`` on the device: ``(seq, q_start_idx, q_len, global_q_idx, kv_blocks, total_extent)``."""
         return self._views(self._dev)[5][: self._n_atoms]
+
+    def atoms_longer_than(self, q_len: int) -> int:
+        """How many (leading) atoms have more than ``q_len`` queries; host-side, no synchronisation."""
+        return int((self._atom_q_lens > q_len).sum()) if self._n_atoms else 0
 
     @property
     def current_tokens(self) -> int:

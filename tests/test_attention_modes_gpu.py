@@ -25,9 +25,10 @@ def test_wrapper_cuts_atoms_on_cpu():
     w.insert_sequence(_Seq(100, [6, 7]), torch.arange(130))           # chunked prefill continuing at 100: 2 atoms
     w.finalize()
     atoms = w.atoms().tolist()
-    assert atoms == [[0, 0, 128, 0, 2, 128], [0, 128, 128, 128, 4, 256], [0, 256, 44, 256, 5, 300],
-                     [1, 300, 1, 77, 2, 78],
-                     [2, 301, 128, 100, 4, 228], [2, 429, 2, 228, 4, 230]]
+    # longest atoms first (stable), so the short tail can run with the GQA group packed into one tile
+    assert atoms == [[0, 0, 128, 0, 2, 128], [0, 128, 128, 128, 4, 256], [2, 301, 128, 100, 4, 228],
+                     [0, 256, 44, 256, 5, 300], [2, 429, 2, 228, 4, 230], [1, 300, 1, 77, 2, 78]]
+    assert (w.atoms_longer_than(32), w.atoms_longer_than(64), w.atoms_longer_than(1), w.atoms_longer_than(0)) == (4, 3, 5, 6)
     w.clear()
     w.finalize()
     assert w.atoms().shape[0] == 0
@@ -111,6 +112,30 @@ def test_atom_paged_attention_matches_per_token_oracle(block_size, D, Hq, Hk):
         assert _rel_err(got[t].cpu(), want[t]) < 2e-2, t
     simt = R.paged_attention(q, cache, w.token_to_seq(), w.token_positions(), w.block_tables())
     assert _rel_err(got, simt) < 1e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("Hq,Hk,D", [(32, 8, 128), (8, 1, 128), (16, 8, 64)])
+def test_packed_decode_atoms_match_oracle(Hq, Hk, D):
+    """Decode-only batch: every atom has one query, the whole GQA group shares a tile (one CTA per KV head)."""
+    from shuffle_exchange_b200.inference.v2.kernels import ragged_ops as R
+    torch.manual_seed(4)
+    bs, ctx = 64, [1, 63, 64, 65, 700, 1023, 130, 5]
+    cache = torch.randn(sum((c + bs) // bs for c in ctx) + 1, bs, 2, Hk, D, device="cuda", dtype=torch.bfloat16)
+    w = RaggedBatchWrapper(64, len(ctx), 17, device="cuda")
+    nxt = 0
+    for c in ctx:
+        need = (c + 1 + bs - 1) // bs
+        w.insert_sequence(_Seq(c, list(range(nxt, nxt + need))), torch.zeros(1, dtype=torch.int64))
+        nxt += need
+    w.finalize()
+    assert w.atoms_longer_than(128 // (Hq // Hk)) == 0
+    q = torch.randn(len(ctx), Hq, D, device="cuda", dtype=torch.bfloat16)
+    got = R.ragged_attention(q, cache, w)
+    want = R.paged_attention(q.cpu(), cache.cpu(), w.token_to_seq().cpu(), w.token_positions().cpu(),
+                             w.block_tables().cpu())
+    for t in range(len(ctx)):
+        assert _rel_err(got[t].cpu(), want[t]) < 2e-2, (t, ctx[t])
 
 
 @pytest.mark.gpu

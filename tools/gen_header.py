@@ -55,10 +55,44 @@ def wrap(sig, width=116):
     return "\n".join(lines) + ";"
 
 
+def _norm(sig):
+    return " ".join(sig.replace("SXB_API ", "").replace("(", " ( ").replace(")", " ) ").replace(",", " , ").split())
+
+
+def stale(text, entries):
+    """Entry points whose declaration in the header no longer matches the source: full text inside the generated
+    section, number of parameters in the hand-written part (parameter names may differ there)."""
+    cut = text.find(MARK)
+    out = []
+    for fn, name, sig, comment in entries:
+        m = re.search(r"\bint\s+" + name + r"\s*\([^;]*\)\s*;", text)
+        if not m:
+            continue
+        decl = m.group(0).rstrip(";").strip()
+        generated = cut >= 0 and m.start() > cut
+        same = _norm(decl) == _norm(sig) if generated else decl.count(",") == sig.count(",")
+        if not same:
+            out.append((fn, name, sig, comment, m, generated))
+    return out
+
+
 def main():
     text = open(HEADER).read()
+    entries = entry_points()
+    old = stale(text, entries)
+    if "--check" in sys.argv and old:
+        for fn, name, *_ in old:
+            print(f"{fn}: declaration of {name} in include/sxb200.h differs from the source")
+        sys.exit(1)
+    for fn, name, sig, comment, m, generated in sorted(old, key=lambda e: -e[4].start()):
+        if not generated:
+            raise SystemExit(f"{name}: hand-written declaration is stale; edit include/sxb200.h")
+        text = text[: m.start()] + wrap(sig.replace("SXB_API ", "")) + text[m.end():]
+    if old:
+        open(HEADER, "w").write(text)
+        print(f"refreshed {len(old)} declarations")
     have = declared(text)
-    missing = [e for e in entry_points() if e[1] not in have]
+    missing = [e for e in entries if e[1] not in have]
     if "--check" in sys.argv:
         for fn, name, _, _ in missing:
             print(f"{fn}: {name} is not declared in include/sxb200.h")

@@ -43,7 +43,7 @@ def case(name, plan, Hq=32, Hk=8, D=128, bs=64):
         nxt += need
     w.finalize()
     q = torch.randn(w.current_tokens, Hq, D, device="cuda", dtype=torch.bfloat16)
-    t_atoms = timed(lambda: R.paged_attention_atoms(q, cache, w.atoms(), w.block_tables()))
+    t_atoms = timed(lambda: R.ragged_attention(q, cache, w))
     t_simt = timed(lambda: R.paged_attention(q, cache, w.token_to_seq(), w.token_positions(), w.block_tables()),
                    n=3 if w.current_tokens > 2048 else 10)
     flops = sum(4.0 * Hq * D * (n * seen + n * (n + 1) / 2) for seen, n in plan)
