@@ -235,7 +235,10 @@ def run_ours(args):
     # ZeRO-2 keeps a full-size low-precision gradient buffer that is allocated lazily in the first backward
     extra = sum(p.numel() for p in model.parameters()) * 2 if is_moe else 0
     if is_moe and not args.moe_nccl:
-        extra += 2 * 2 ** 30                                             # symmetric receive / return buffers
+        # symmetric receive / return buffers, the per-layer copies the fused movers keep for backward (combined rows,
+        # capacity-padded expert inputs) and allocator slack for their capacity-sized blocks: the first 8-GPU run with
+        # a 2 GiB reserve ran out of memory at the start of backward with 171 GiB allocated
+        extra += 16 * 2 ** 30
     cfg.checkpoint_layers = pick_checkpoint_layers(args, cfg, B, S, dev, world, extra)
     n_batches = 4
     if sp > 1:

@@ -252,9 +252,79 @@ struct SubsetMeanArgs {
   long long n;
   uint32_t epoch;
   unsigned int* cta_counter;
+  int me;   // >= 0: two-phase form, this rank's position in M.idx; -1: every rank reads every member's whole shard
 };
+
+// Two-phase form for member sets in which EVERY member computes the same weighted sum (RR, H-RR): member k reduces
+// slice k of all members' shards into slice k of its OWN symmetric buffer (no rank reads that slice of that buffer in
+// this phase), a cross-rank barrier, then every member copies the reduced slices out of their owners.  Per rank
+// 2 (m-1)/m shard sizes cross NVLink instead of (m-1): the reduce-scatter + all-gather of a bandwidth-optimal
+// all-reduce, in one kernel.  All CTAs wait inside the kernel for the slowest rank, so the launch is cooperative
+// (co-residency is checked by the driver).  n must be a multiple of 8.
+template <typename T>
+__device__ __forceinline__ void subset_mean_two_phase(const SubsetMeanArgs<T>& A) {
+  const Peers& P = A.P;
+  const Members& M = A.M;
+  if (blockIdx.x == 0) signal_all(P, 2, A.epoch);
+  if (!wait_all(P, 2, A.epoch, 103)) return;
+  const long long nvec = A.n >> 3;
+  const long long per = (nvec + M.count - 1) / M.count;
+  const long long stride = (long long)gridDim.x * blockDim.x, t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  {
+    const long long lo = per * A.me, hi = min(nvec, lo + per);
+    T* mine = reinterpret_cast<T*>(const_cast<void*>(P.buf[P.rank]));
+    for (long long i = lo + t0; i < hi; i += stride) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int k = 0; k < M.count; ++k) {
+        const uint4 r = ld_peer16(reinterpret_cast<const T*>(P.buf[M.idx[k]]) + i * 8);
+        const T* h = reinterpret_cast<const T*>(&r);
+        const float wk = M.w[k];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] += wk * to_f32<T>(h[e]);
+      }
+      uint4 o;
+      T* oh = reinterpret_cast<T*>(&o);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) oh[e] = from_f32<T>(acc[e]);
+      *reinterpret_cast<uint4*>(mine + i * 8) = o;
+      *reinterpret_cast<uint4*>(A.out + i * 8) = o;
+    }
+  }
+  // every CTA of this rank finished its part of the slice -> tell the peers; then wait for theirs
+  __shared__ unsigned int last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    last = (atomicAdd(A.cta_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (last) {
+    if (threadIdx.x == 0) *A.cta_counter = 0u;
+    signal_all(P, 7, A.epoch);
+  }
+  if (!wait_all(P, 7, A.epoch, 107)) return;
+  for (int k = 0; k < M.count; ++k) {
+    if (k == A.me) continue;
+    const long long lo = per * k, hi = min(nvec, lo + per);
+    const T* src = reinterpret_cast<const T*>(P.buf[M.idx[k]]);
+    for (long long i = lo + t0; i < hi; i += stride)
+      *reinterpret_cast<uint4*>(A.out + i * 8) = ld_volatile16(src + i * 8);   // written by the owner in THIS kernel
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    last = (atomicAdd(A.cta_counter + 1, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (last) {
+    if (threadIdx.x == 0) A.cta_counter[1] = 0u;
+    signal_all(P, 3, A.epoch);
+  }
+}
+
 template <typename T>
 __device__ __forceinline__ void subset_mean_body(const SubsetMeanArgs<T>& A) {
+  if (A.me >= 0) { subset_mean_two_phase<T>(A); return; }
   const Peers& P = A.P;
   const Members& M = A.M;
   T* __restrict__ out = A.out;
@@ -584,6 +654,10 @@ SXB_API int sxb_symm_wait(const void* const* bufs, const void* const* sigs, int 
   return SXB_OK;
 }
 
+SXB_API int sxb_symm_subset_wsum2(const void* const* bufs, const void* const* sigs, int rank, int world,
+                                  const int* members, const float* weights, int n_members, void* out, long long n,
+                                  int dtype, unsigned int epoch, void* counter, int max_ctas, int shared_result,
+                                  void* stream);
 SXB_API int sxb_symm_subset_wsum(const void* const* bufs, const void* const* sigs, int rank, int world,
                                  const int* members, const float* weights, int n_members, void* out, long long n,
                                  int dtype, unsigned int epoch, void* counter, int max_ctas, void* stream);
@@ -608,22 +682,56 @@ SXB_API int sxb_symm_subset_mean(const void* const* bufs, const void* const* sig
 SXB_API int sxb_symm_subset_wsum(const void* const* bufs, const void* const* sigs, int rank, int world,
                                  const int* members, const float* weights, int n_members, void* out, long long n,
                                  int dtype, unsigned int epoch, void* counter, int max_ctas, void* stream) {
+  return sxb_symm_subset_wsum2(bufs, sigs, rank, world, members, weights, n_members, out, n, dtype, epoch, counter,
+                               max_ctas, 0, stream);
+}
+
+template <typename T>
+static int launch_subset(const Peers& P, const Members& M, void* out, long long n, unsigned int epoch, void* counter,
+                         int max_ctas, int me, cudaStream_t s) {
+  SubsetMeanArgs<T> A{P, M, (T*)out, n, epoch, (unsigned int*)counter, me};
+  if (me < 0) {
+    subset_mean_kernel<T><<<grid_cap(n / 8 + 1, max_ctas), kThreads, 0, s>>>(A);
+    return SXB_OK;
+  }
+  // cooperative: every CTA waits inside the kernel for the other ranks, so all of them must be resident
+  int per_sm = 0, dev = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, subset_mean_kernel<T>, kThreads, 0);
+  if (e != cudaSuccess) return (int)e;
+  if (per_sm < 1) return SXB_ERR_UNSUPPORTED;
+  int grid = grid_cap(n / 8 / (M.count > 0 ? M.count : 1) + 1, max_ctas);
+  if (grid > per_sm * sms) grid = per_sm * sms;
+  void* params[] = {(void*)&A};
+  e = cudaLaunchCooperativeKernel((const void*)subset_mean_kernel<T>, dim3(grid), dim3(kThreads), params, 0, s);
+  return e == cudaSuccess ? SXB_OK : (int)e;
+}
+
+// K9 with the choice of form.  shared_result != 0: every member of `members` calls with the SAME member list and
+// weights (RR, H-RR) -> two-phase form (see subset_mean_two_phase): `counter` must point at two zeroed words, n % 8 == 0,
+// and the symmetric buffer is overwritten with reduced values.  Falls back to the one-phase form for a single member.
+SXB_API int sxb_symm_subset_wsum2(const void* const* bufs, const void* const* sigs, int rank, int world,
+                                  const int* members, const float* weights, int n_members, void* out, long long n,
+                                  int dtype, unsigned int epoch, void* counter, int max_ctas, int shared_result,
+                                  void* stream) {
   Peers P;
   int rc = fill_peers(P, bufs, sigs, rank, world);
   if (rc) return rc;
   Members M;
   if ((rc = fill_members(M, members, n_members, weights))) return rc;
-  const int grid = grid_cap(n / 8 + 1, max_ctas);
-  cudaStream_t s = (cudaStream_t)stream;
-  if (dtype == kBF16) {
-    SubsetMeanArgs<__nv_bfloat16> A{P, M, (__nv_bfloat16*)out, n, epoch, (unsigned int*)counter};
-    subset_mean_kernel<__nv_bfloat16><<<grid, kThreads, 0, s>>>(A);
-  } else if (dtype == kF16) {
-    SubsetMeanArgs<__half> A{P, M, (__half*)out, n, epoch, (unsigned int*)counter};
-    subset_mean_kernel<__half><<<grid, kThreads, 0, s>>>(A);
-  } else {
-    return SXB_ERR_BAD_ARG;
+  int me = -1;
+  if (shared_result && n_members > 1) {
+    if (n % 8) return SXB_ERR_UNSUPPORTED;
+    for (int i = 0; i < n_members; ++i)
+      if (members[i] == rank) me = i;
+    if (me < 0) return SXB_ERR_BAD_ARG;
   }
+  cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == kBF16) rc = launch_subset<__nv_bfloat16>(P, M, out, n, epoch, counter, max_ctas, me, s);
+  else if (dtype == kF16) rc = launch_subset<__half>(P, M, out, n, epoch, counter, max_ctas, me, s);
+  else return SXB_ERR_BAD_ARG;
+  if (rc) return rc;
   SXB_CHECK_LAUNCH();
   return SXB_OK;
 }
@@ -631,8 +739,11 @@ SXB_API int sxb_symm_subset_wsum(const void* const* bufs, const void* const* sig
 // [world][16] row-major table, n_members[r] the length of row r (row r must contain r).
 SXB_API int sxb_symm_subset_mean_emu(const void* const* bufs, const void* const* sigs, int world, const int* members,
                                      const int* n_members, void* const* outs, long long n, unsigned int epoch,
-                                     void* const* counters, int ctas_per_rank, void* stream) {
+                                     void* const* counters, int ctas_per_rank, int shared_result, void* stream) {
+  // shared_result: two-phase form (every rank's row of `members` lists the same ring for all of the ring's ranks);
+  // counters[r] then points at two zeroed words
   if (world < 1 || world > kMaxPeers || ctas_per_rank < 1) return SXB_ERR_BAD_ARG;
+  if (shared_result && (n % 8)) return SXB_ERR_UNSUPPORTED;
   int rc;
   SubsetMeanArgs<__nv_bfloat16> A[kMaxPeers];
   for (int r = 0; r < world; ++r) {
@@ -640,6 +751,12 @@ SXB_API int sxb_symm_subset_mean_emu(const void* const* bufs, const void* const*
     if ((rc = fill_members(A[r].M, members + r * kMaxPeers, n_members[r]))) return rc;
     A[r].out = (__nv_bfloat16*)outs[r]; A[r].n = n; A[r].epoch = epoch;
     A[r].cta_counter = (unsigned int*)counters[r];
+    A[r].me = -1;
+    if (shared_result && n_members[r] > 1) {
+      for (int i = 0; i < n_members[r]; ++i)
+        if (members[r * kMaxPeers + i] == r) A[r].me = i;
+      if (A[r].me < 0) return SXB_ERR_BAD_ARG;
+    }
   }
   return launch_emu((const void*)subset_mean_emu_kernel<__nv_bfloat16>, A, world, ctas_per_rank, kThreads,
                     (cudaStream_t)stream);

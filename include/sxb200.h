@@ -358,7 +358,7 @@ int sxb_symm_subset_wsum(const void* const* bufs, const void* const* sigs, int r
  * [world][16] row-major table, n_members[r] the length of row r (row r must contain r). */
 int sxb_symm_subset_mean_emu(const void* const* bufs, const void* const* sigs, int world, const int* members,
                              const int* n_members, void* const* outs, long long n, unsigned int epoch,
-                             void* const* counters, int ctas_per_rank, void* stream);
+                             void* const* counters, int ctas_per_rank, int shared_result, void* stream);
 /* K2 gather half.  chunk_flags (optional, device uint32[ceil(world*part_bytes / chunk_bytes)]): chunk c is set to
  * `flag_value` (release, gpu scope) once all of its bytes are in dst — the gated GEMM polls these. */
 int sxb_symm_all_gather(const void* const* bufs, const void* const* sigs, int rank, int world,
@@ -374,6 +374,15 @@ int sxb_symm_a2a_rows(const void* const* bufs, const void* const* sigs, int rank
 int sxb_symm_a2a_rows_emu(const void* const* bufs, const void* const* sigs, int world, const void* const* srcs,
                           const long long* send_off, const long long* recv_off, const long long* count,
                           int row_bytes, unsigned int epoch, void* const* counters, int ctas_per_rank,
+                          void* stream);
+
+/* ---- csrc/symm_collectives.cu */
+/* K9 with the choice of form.  shared_result != 0: every member of `members` calls with the SAME member list and
+ * weights (RR, H-RR) -> two-phase form (see subset_mean_two_phase): `counter` must point at two zeroed words, n % 8 == 0,
+ * and the symmetric buffer is overwritten with reduced values.  Falls back to the one-phase form for a single member. */
+int sxb_symm_subset_wsum2(const void* const* bufs, const void* const* sigs, int rank, int world,
+                          const int* members, const float* weights, int n_members, void* out, long long n,
+                          int dtype, unsigned int epoch, void* counter, int max_ctas, int shared_result,
                           void* stream);
 
 #ifdef __cplusplus

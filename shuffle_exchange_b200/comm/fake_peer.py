@@ -22,7 +22,7 @@ from .symm import CH_A2A_FREE, CH_A2A_LANDED, CH_AG_READY, CH_AVG_READ, CH_AVG_R
 
 _n.register({
     "sxb_symm_rs_adam_emu": "ppil" "ppppp" "fffff" "iii" "f" "i" "p" "ii" "p",
-    "sxb_symm_subset_mean_emu": "ppi" "pp" "pl" "i" "p" "i" "p",
+    "sxb_symm_subset_mean_emu": "ppi" "pp" "pl" "i" "p" "ii" "p",
     "sxb_symm_all_gather_emu": "ppil" "pl" "p" "iii" "p",
     "sxb_symm_a2a_rows_emu": "ppi" "pppp" "ii" "p" "i" "p",
 })
@@ -92,7 +92,8 @@ class FakePeerGroup:
                 int(apply), MAX_CTAS, _n.stream_ptr())
 
     # K9: every rank averages over ITS ring (``rings``: list of member lists partitioning the ranks)
-    def subset_mean(self, src: FakePeerBuffer, rings: List[List[int]], out: List[torch.Tensor], n: int) -> None:
+    def subset_mean(self, src: FakePeerBuffer, rings: List[List[int]], out: List[torch.Tensor], n: int,
+                    shared: bool = False) -> None:
         epoch = src.next_epoch(CH_AVG_READY)
         src.epochs[CH_AVG_READ] = epoch
         ring_of = {r: ring for ring in rings for r in ring}
@@ -103,9 +104,10 @@ class FakePeerGroup:
             for j, mbr in enumerate(ring_of[r]):
                 table[r * 16 + j] = mbr
         ok, op = _ptr_array(out)
-        ck, cp = self._ctrs(1)
+        ck, cp = self._ctrs(6 if shared else 1)
         _n.call("sxb_symm_subset_mean_emu", src.bufs, src.sigs, self.world, ctypes.cast(table, ctypes.c_void_p),
-                ctypes.cast(counts, ctypes.c_void_p), op, int(n), int(epoch), cp, MAX_CTAS, _n.stream_ptr())
+                ctypes.cast(counts, ctypes.c_void_p), op, int(n), int(epoch), cp, MAX_CTAS, int(shared),
+                _n.stream_ptr())
 
     # K2: all-gather of ``part_numel`` elements per rank (+ per-chunk arrival flags)
     def all_gather(self, shard: FakePeerBuffer, part_numel: int, dst: List[torch.Tensor], chunk_bytes: int = 1 << 16,

@@ -31,6 +31,7 @@ _n.register({
     "sxb_symm_barrier": "ppiiiip",
     "sxb_symm_subset_mean": "ppiipiplii" "pip",
     "sxb_symm_subset_wsum": "ppiippiplii" "pip",
+    "sxb_symm_subset_wsum2": "ppiippiplii" "piip",
     "sxb_symm_all_gather": "ppiilplpiiip",
     "sxb_symm_a2a_rows": "ppiippppiipip",
     "sxb_symm_hang_info": "p",
@@ -192,18 +193,22 @@ class SymmGroup:
 
     # ------------------------------------------------------------------------------------- K9
     def subset_mean(self, src: SymmBuffer, members: List[int], out: torch.Tensor, n: int, max_ctas: int = 0,
-                    weights: Optional[List[float]] = None):
+                    weights: Optional[List[float]] = None, shared: bool = False):
         """``out = sum_k weights[k] * shard(members[k])`` (``weights=None``: the mean) read straight out of the
         members' symmetric buffers.  Every rank of the group must call it in the same step (each with its own member
-        list): the kernel handshakes with ALL ranks before reading and tells all of them when it is done."""
+        list): the kernel handshakes with ALL ranks before reading and tells all of them when it is done.
+
+        ``shared=True`` (every member passes the same list and weights — RR, H-RR): two-phase form, each member
+        reduces one slice and the reduced slices are exchanged; ``src`` is overwritten with reduced values."""
         epoch = src.next_epoch(CH_AVG_READY)
         src.epochs[CH_AVG_READ] = epoch
         arr = (ctypes.c_int * len(members))(*members)
         warr = (ctypes.c_float * len(members))(*weights) if weights is not None else None
-        _n.call("sxb_symm_subset_wsum", src.bufs, src.sigs, self.rank, self.world,
+        two_phase = bool(shared) and len(members) > 1 and n % 8 == 0
+        _n.call("sxb_symm_subset_wsum2", src.bufs, src.sigs, self.rank, self.world,
                 ctypes.cast(arr, ctypes.c_void_p), ctypes.cast(warr, ctypes.c_void_p) if warr is not None else None,
-                len(members), out.data_ptr(), int(n), _n.dtype_code(out.dtype), int(epoch), self._ctr(1),
-                int(max_ctas), _n.stream_ptr())
+                len(members), out.data_ptr(), int(n), _n.dtype_code(out.dtype), int(epoch),
+                self._ctr(6 if two_phase else 1), int(max_ctas), int(two_phase), _n.stream_ptr())
 
     # ------------------------------------------------------------------------------------- K2
     def barrier(self, buf: SymmBuffer, channel: int = CH_AG_READY):
@@ -263,8 +268,10 @@ class ReplicaAverageKernel:
     def fits(self, shard: torch.Tensor) -> bool:
         return shard.numel() <= self.buf.tensor.numel() and shard.dtype == self.buf.tensor.dtype
 
-    def run(self, shard: torch.Tensor, members: List[int], weights: Optional[List[float]] = None):
+    def run(self, shard: torch.Tensor, members: List[int], weights: Optional[List[float]] = None,
+            shared: bool = False):
+        """``shared``: every member averages over the same list with the same weights (two-phase kernel)."""
         n = shard.numel()
         self.sg.wait_readers(self.buf, CH_AVG_READ)           # peers finished reading the previous contents
         self.buf.tensor[:n].copy_(shard.view(-1))
-        self.sg.subset_mean(self.buf, members, shard.view(-1), n, weights=weights)
+        self.sg.subset_mean(self.buf, members, shard.view(-1), n, weights=weights, shared=shared)

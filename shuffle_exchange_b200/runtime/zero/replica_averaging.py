@@ -327,7 +327,10 @@ class ReplicaAverager:
             if self.fused:
                 raise RuntimeError("fused replica averaging requested but symmetric memory is unavailable")
             return False
-        self._symm.run(shard, list(members), weights)       # replica id == rank inside the column group
+        # replica id == rank inside the column group.  Without explicit weights every member of the list computes the
+        # same mean (RR, H-RR: all replicas; shuffle: the rings partition the replicas), so the two-phase kernel applies:
+        # each member reduces one slice, the reduced slices are exchanged.
+        self._symm.run(shard, list(members), weights, shared=weights is None)
         return True
 
     def state_dict(self):

@@ -56,12 +56,22 @@ def test_emulated_collectives_match_pytorch(world):
     for t in src.tensors:
         t.copy_(torch.randn(part, device=dev).to(torch.bfloat16))
     sm_out = [torch.empty(part, device=dev, dtype=torch.bfloat16) for _ in range(world)]
+    sm_refs = [torch.stack([src.tensors[r].float() for r in ring]).mean(0) for ring in rings]
     grp.subset_mean(src, rings, sm_out, part)
     torch.cuda.synchronize()
-    for ring in rings:
-        sm_ref = torch.stack([src.tensors[r].float() for r in ring]).mean(0)
+    for ring, sm_ref in zip(rings, sm_refs):
         for r in ring:
             _close(sm_out[r], sm_ref, 8e-3, 1e-6)
+    # two-phase form (every member of a ring has the same list): each member reduces one slice into its own buffer,
+    # the reduced slices are exchanged after an in-kernel barrier; all members end with bit-identical results
+    for o in sm_out:
+        o.zero_()
+    grp.subset_mean(src, rings, sm_out, part, shared=True)
+    torch.cuda.synchronize()
+    for ring, sm_ref in zip(rings, sm_refs):
+        for r in ring:
+            _close(sm_out[r], sm_ref, 8e-3, 1e-6)
+            assert torch.equal(sm_out[r], sm_out[ring[0]])
     # ---- K2 gather half: exact copy + every chunk flag published
     sh = FakePeerBuffer(world, part, torch.bfloat16, dev)
     for t in sh.tensors:
