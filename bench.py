@@ -276,6 +276,25 @@ def run_ours(args):
         engine.step()
         return float(loss.item())                                    # D2H read of the step's result
 
+    if is_moe and args.ckpt_layers == "auto":
+        # ZeRO-2 allocates optimizer state and the gradient buffers lazily (first backward / first step), so memory
+        # resident before the first step says little.  One untimed step with every layer recomputed, then size the
+        # recompute count from what is resident AFTER it plus that step's measured transient peak.
+        cfg.checkpoint_layers = cfg.num_hidden_layers
+        torch.cuda.reset_peak_memory_stats(dev)
+        step_device(0)
+        torch.cuda.synchronize()
+        resident = torch.cuda.memory_allocated(dev)
+        transient = torch.cuda.max_memory_allocated(dev) - resident
+        total = torch.cuda.get_device_properties(dev).total_memory
+        slack = 10 * 2 ** 30                                  # allocator fragmentation, NCCL / symmetric workspaces
+        free_layers = int(max(0, total - resident - transient - slack) // cfg.activation_bytes_per_layer(B, S))
+        t = torch.tensor([free_layers], device=dev, dtype=torch.int64)
+        if world > 1:
+            import torch.distributed as td
+            td.all_reduce(t, op=td.ReduceOp.MIN)
+        cfg.checkpoint_layers = max(0, cfg.num_hidden_layers - int(t.item()))
+        torch.cuda.reset_peak_memory_stats(dev)
     for i in range(args.warmup):
         step_device(i)
     barrier_sync()

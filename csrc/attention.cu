@@ -690,10 +690,19 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       tc_fence_after();
       float s[32], dp[32];
       const uint32_t tS = tmem + (j & 1) * 128 + lane_off + half * 32;
-      ld_row32x2(tS, tS + 64, s, dp);
+      if (p.debug < 2) {
+        ld_row32x2(tS, tS + 64, s, dp);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) { s[c] = 0.f; dp[c] = 0.f; }
+      }
       const int k0 = j * BC + half * 32;
       const bool need_mask = (p.causal && (k0 + 31 > q0)) || (k0 + 32 > S_) || (q0 + BQ > S_);
-      if (need_mask) {
+      if (p.debug >= 1) {
+        // profiling aid (SXB_ATTN_DEBUG): no exponentials, results are meaningless
+#pragma unroll
+        for (int c = 0; c < 32; ++c) s[c] = s[c] * dp[c];
+      } else if (need_mask) {
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
           const int kp = k0 + c;

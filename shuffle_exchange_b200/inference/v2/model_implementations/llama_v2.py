@@ -57,6 +57,10 @@ class RaggedLlamaModel:
             return F.linear(F.swiglu(F.linear(x, layer.w_gate_up)), layer.w_down)
         logits = F.linear(x, moe["gate"])
         scores, assign, offsets, counts = moe_ops.top_k_gating(logits, self.top_k, renormalize=True)
+        from ....moe import fused_ep
+        if fused_ep.grouped_inference_ok(x, moe["w_gate_up"], moe["w_down"]):
+            return fused_ep.grouped_experts_inference(x, scores, assign, offsets, counts, moe["w_gate_up"],
+                                                      moe["w_down"], F.swiglu, self.top_k)
         moe_in, cumsum, slots = moe_ops.moe_scatter(x, assign, offsets, counts)
         ends = cumsum.tolist()
         out = torch.empty_like(moe_in)

@@ -227,3 +227,29 @@ def make_plan(ep: FusedEP, counts, assign, offsets) -> EPPlan:
     tables = ep.plan(counts.contiguous())
     T, K = assign.shape
     return EPPlan(tables, assign.contiguous(), offsets.contiguous(), T, K, tables[ep.E: ep.E + ep.L + 1])
+
+
+@torch.no_grad()
+def grouped_experts_inference(x, scores, assign, offsets, counts, w1, w2, activation, top_k: int):
+    """Inference MoE body without a host synchronisation: expert-contiguous rows through the plan / push kernels (one
+    rank: every "peer" access is local), ONE grouped GEMM per projection over the 256-aligned groups, weighted
+    un-permute through the pull kernel.  ``w1`` ``[E, N1, H]``, ``w2`` ``[E, H, F]`` (stacked expert weights),
+    ``activation``: callable on the first projection's output (e.g. SwiGLU).  Replaces the per-expert loop over
+    ``cumsum.tolist()`` (reference: ``inference/v2/kernels/cutlass_ops/moe_gemm``)."""
+    from ..ops.gemm_ext import grouped_gemm_nt
+    T, H = x.shape
+    E = w1.shape[0]
+    ep = FusedEP.get(None, H, E, T, top_k, 1.0)
+    plan = make_plan(ep, counts, assign, offsets)
+    ep.push(x.contiguous(), plan)
+    h = activation(grouped_gemm_nt(ep.recv_rows, w1, plan.group_offsets))
+    grouped_gemm_nt(h, w2, plan.group_offsets, out=ep.ret_rows)
+    y = torch.empty((T, H), dtype=x.dtype, device=x.device)
+    ep.pull(y, plan, weights=scores.to(torch.float32).contiguous())
+    return y
+
+
+def grouped_inference_ok(x, w1, w2, *biases) -> bool:
+    return (x.is_cuda and x.dtype == torch.bfloat16 and w1.dtype == torch.bfloat16 and w2.dtype == torch.bfloat16
+            and w1.dim() == 3 and w2.dim() == 3 and w1.is_contiguous() and w2.is_contiguous()
+            and all(b is None for b in biases) and x.shape[1] % 64 == 0 and w1.shape[1] % 64 == 0)

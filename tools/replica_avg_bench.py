@@ -71,7 +71,9 @@ def main():
                 entry["kernel_vs_nccl_max_abs"] = float((a.float() - b.float()).abs().max())
         n_rep = world // slice_count
         members = n_rep if method in ("RR", "H-RR") else (n_rep // rings if method == "shuffle" else 2)
-        entry["nvlink_bytes_in"] = numel * 2 * (members - 1)
+        # two-phase kernel (members share their result): 2 (m-1)/m shard sizes arrive over NVLink per rank — the
+        # traffic of a bandwidth-optimal all-reduce; Gossip p2p: one shard
+        entry["nvlink_bytes_in"] = int(numel * 2 * 2 * (members - 1) / members) if method != "Gossip" else numel * 2
         if "kernel_ms" in entry:
             entry["kernel_gbps_in"] = entry["nvlink_bytes_in"] / entry["kernel_ms"] / 1e6
             entry["roofline_fraction_770"] = entry["kernel_gbps_in"] / 770.0
