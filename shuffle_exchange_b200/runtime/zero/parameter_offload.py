@@ -44,7 +44,9 @@ class DeepSpeedZeRoOffload:
             prefetch_bucket_size=prefetch_bucket_size, max_reuse_distance=max_reuse_distance,
             max_live_parameters=max_live_parameters, param_persistence_threshold=param_persistence_threshold,
             model_persistence_threshold=model_persistence_threshold, dp_process_group=dp_process_group,
-            offload_param_config=offload_param_config, mpu=mpu, fused_step=False, verbose=False)
+            offload_param_config=offload_param_config, mpu=mpu, fused_step=False, verbose=False,
+            zero_quantized_weights=zero_quantized_weights,
+            zero_quantized_nontrainable_weights=zero_quantized_nontrainable_weights)
         for p in frozen:
             p.requires_grad_(False)
         self.param_coordinator = PartitionedParameterCoordinator(self._engine)
