@@ -507,13 +507,23 @@ template <int D>
 struct DqSmem {
   static constexpr int kQ = BQ * D * 2;      // Q and dO tiles
   static constexpr int kKV = BC * D * 2;
-  static constexpr int kStages = 4;
+  // K/V ring: 4 stages of their own + 2 that reuse the Q and dO staging tiles (2 x kKV bytes each) once the row warps
+  // have parked Q and dO in TMEM.  The ring was the limiter: with 4 stages and the row warps doing nothing the kernel
+  // still ran at 55 % of the tensor pipe's rate — a K/V tile requested 3 iterations (~2300 cycles) ahead arrives late.
+  static constexpr int kOwnStages = 4;
+  static constexpr int kStages = 6;
   static constexpr int oQ = 0;
   static constexpr int oDO = oQ + kQ;
   static constexpr int oK = oDO + kQ;
-  static constexpr int oV = oK + kStages * kKV;
-  static constexpr int oBar = oV + kStages * kKV;
+  static constexpr int oV = oK + kOwnStages * kKV;
+  static constexpr int oBar = oV + kOwnStages * kKV;
   static constexpr int kTotal = oBar + 256 + 1024;
+  __host__ __device__ static constexpr int offK(int st) {
+    return st < kOwnStages ? oK + st * kKV : (st == kOwnStages ? oQ : oDO);
+  }
+  __host__ __device__ static constexpr int offV(int st) {
+    return st < kOwnStages ? oV + st * kKV : (st == kOwnStages ? oQ + kKV : oDO + kKV);
+  }
 };
 
 template <int D, int MC>   // MC = 2: K/V ring filled by multicast from a 2-CTA cluster over a q-head pair (see forward)
@@ -529,15 +539,17 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                                              ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
   uint64_t* q_full = bars + 0;
-  uint64_t* kv_full = bars + 1;   // [4]
-  uint64_t* kv_empty = bars + 5;  // [4]
+  uint64_t* kv_full = bars + 17;  // [NS]
+  uint64_t* kv_empty = bars + 23; // [NS]
   uint64_t* s_full = bars + 9;    // [2] S and dP of buffer b ready
   uint64_t* dq_done = bars + 12;  // committed once, after the last block's dQ MMAs
   // [2] dS of buffer b parked in TMEM (one arrival per row warp).  Row warps can finish block j+1 before the MMA warp
   // has observed block j, so the two in-flight blocks need distinct barriers (a single one would alias phases).
   uint64_t* ds_full = bars + 13;
   uint64_t* qa_full = bars + 15;  // Q / dO copied into TMEM as A operands (one arrival per row warp)
+  uint64_t* qa_all = bars + 29;   // ... in every CTA of the cluster (one commit-arrival per CTA's MMA warp)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+  static_assert(23 + NS <= 29, "barrier area is 256 bytes");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = gridDim.z - 1 - blockIdx.z;   // heaviest causal tiles first across all heads
@@ -559,6 +571,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       mbar_init(&ds_full[0], 8);   // one arrival per row warp
       mbar_init(&ds_full[1], 8);
       mbar_init(qa_full, 8);
+      mbar_init(qa_all, MC);
       mbar_init(dq_done, 1);
       mbar_fence_init();
     }
@@ -587,18 +600,21 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     for (int j = 0; j < nblk; ++j) {
       const int st = j % NS;
       if (!__all_sync(0xffffffffu, mbar_wait_to(&kv_empty[st], ((j / NS) & 1) ^ 1, 27, j))) goto done;
+      // stages 4 and 5 live where Q and dO were staged: free once the row warps have copied them into TMEM — in
+      // BOTH CTAs of a multicast pair, since each CTA's load lands in both (qa_all counts the peer's row warps too)
+      if (j == L::kOwnStages && !__all_sync(0xffffffffu, mbar_wait_to(qa_all, 0, 44))) goto done;
       if (elected) {
         mbar_expect_tx(&kv_full[st], 2 * L::kKV);
         if (MC > 1) {
-          tma_load_4d_mc(smem + L::oK + st * L::kKV + crank * (BC * 128), &tmK, &kv_full[st], crank * 64, hk,
+          tma_load_4d_mc(smem + L::offK(st) + crank * (BC * 128), &tmK, &kv_full[st], crank * 64, hk,
                          w.off + j * BC, w.tb, 3);
-          tma_load_4d_mc(smem + L::oV + st * L::kKV + crank * (BC * 128), &tmV, &kv_full[st], crank * 64, hk,
+          tma_load_4d_mc(smem + L::offV(st) + crank * (BC * 128), &tmV, &kv_full[st], crank * 64, hk,
                          w.off + j * BC, w.tb, 3);
         } else {
           for (int hh = 0; hh < NH; ++hh) {
-            tma_load_4d(smem + L::oK + st * L::kKV + hh * (BC * 128), &tmK, &kv_full[st], hh * 64, hk,
+            tma_load_4d(smem + L::offK(st) + hh * (BC * 128), &tmK, &kv_full[st], hh * 64, hk,
                         w.off + j * BC, w.tb);
-            tma_load_4d(smem + L::oV + st * L::kKV + hh * (BC * 128), &tmV, &kv_full[st], hh * 64, hk,
+            tma_load_4d(smem + L::offV(st) + hh * (BC * 128), &tmV, &kv_full[st], hh * 64, hk,
                         w.off + j * BC, w.tb);
           }
         }
@@ -616,8 +632,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       const int st = j % NS;
       if (!__all_sync(0xffffffffu, mbar_wait_to(&kv_full[st], (j / NS) & 1, 29, j))) return false;
       tc_fence_after();
-      const uint32_t sK = sbase + L::oK + st * L::kKV;
-      const uint32_t sV = sbase + L::oV + st * L::kKV;
+      const uint32_t sK = sbase + L::offK(st);
+      const uint32_t sV = sbase + L::offV(st);
       const uint32_t tS = tm_u + (j & 1) * 128, tDP = tS + 64;
       if (elected) {
 #pragma unroll
@@ -636,6 +652,12 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     // measured limiter: ~70 B/clk/SM)
     if (!__all_sync(0xffffffffu, mbar_wait_to(qa_full, 0, 28))) goto done;
     tc_fence_after();
+    if (elected) {
+      // tell the TMA warps of the whole cluster that THIS CTA's Q / dO staging tiles may be overwritten
+      if (MC > 1) umma_commit_mc(qa_all, 3);
+      else umma_commit(qa_all);
+    }
+    __syncwarp();
     if (!issue_sdp(0)) goto done;
     for (int j = 0; j < nblk; ++j) {
       const int st = j % NS;
@@ -643,7 +665,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       if (j + 1 < nblk && !issue_sdp(j + 1)) goto done;
       if (!__all_sync(0xffffffffu, mbar_wait_to(&ds_full[j & 1], (j >> 1) & 1, 30, j))) goto done;
       tc_fence_after();
-      const uint32_t sK = sbase + L::oK + st * L::kKV;
+      const uint32_t sK = sbase + L::offK(st);
       if (elected) {
 #pragma unroll
         for (int kk = 0; kk < BC / 16; ++kk)

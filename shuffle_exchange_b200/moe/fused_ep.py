@@ -112,7 +112,11 @@ class FusedEP:
     def get(cls, group, hidden, num_experts, max_tokens, top_k, capacity_factor=1.5) -> "FusedEP":
         key = (id(group) if group is not None else 0, hidden, num_experts, top_k)
         inst = cls._instances.get(key)
-        if inst is None or inst.cap_rows < int(max_tokens * top_k * capacity_factor):
+        world = 1 if group is None else torch.distributed.get_world_size(group)
+        cf = 1.0 if group is None else capacity_factor
+        # the same row count the constructor reserves: routed rows plus one alignment pad per local expert
+        need = int(max_tokens * top_k * cf) + (num_experts // world) * GROUP_ALIGN_M
+        if inst is None or inst.cap_rows < need:
             inst = cls._instances[key] = FusedEP(group, hidden, num_experts, max_tokens, top_k, capacity_factor)
         return inst
 
