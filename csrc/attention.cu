@@ -24,6 +24,10 @@ constexpr int BQ = 128;   // rows owned by the 128 row-threads (queries in fwd/d
 constexpr int BC = 64;    // inner block (keys in fwd/dq, queries in dkv)
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
+// SXB_ATTN_DEBUG=3: cycle accounting of the heaviest dQ tile (block 0,0,0) — [0] MMA warp total, [1] its wait for
+// K/V tiles, [2] its wait for dS, [3] iterations, [4] row warp total, [5] its wait for S/dP, [6] its TMEM load +
+// math, [7] its TMEM store + fence
+__device__ unsigned long long g_attn_prof[8];
 
 struct Params {
   int B, S, Hq, Hk, D;
@@ -507,11 +511,13 @@ template <int D>
 struct DqSmem {
   static constexpr int kQ = BQ * D * 2;      // Q and dO tiles
   static constexpr int kKV = BC * D * 2;
-  // K/V ring: 4 stages of their own + 2 that reuse the Q and dO staging tiles (2 x kKV bytes each) once the row warps
-  // have parked Q and dO in TMEM.  The ring was the limiter: with 4 stages and the row warps doing nothing the kernel
-  // still ran at 55 % of the tensor pipe's rate — a K/V tile requested 3 iterations (~2300 cycles) ahead arrives late.
+  // K/V ring.  Measured: deepening it to 6 stages (two reusing the Q / dO staging tiles once those are parked in TMEM)
+  // changed nothing (0.74 -> 0.76 ms at S=8192): the MMA warp waits ~120 cycles per iteration for K/V.  What bounds
+  // this kernel is the issue of the TS-form MMAs themselves: cycle accounting of one CTA (SXB_ATTN_DEBUG=3,
+  // tools/attn_prof.py) gives ~1500 cycles per 64-key iteration = 20 MMAs x ~64 cycles + ~230 cycles of waits — an
+  // A operand read from TMEM costs ~64 cycles per K=16 step whatever N is, so the N=64 S / dP MMAs run at half rate.
   static constexpr int kOwnStages = 4;
-  static constexpr int kStages = 6;
+  static constexpr int kStages = 4;
   static constexpr int oQ = 0;
   static constexpr int oDO = oQ + kQ;
   static constexpr int oK = oDO + kQ;
@@ -549,7 +555,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   uint64_t* qa_full = bars + 15;  // Q / dO copied into TMEM as A operands (one arrival per row warp)
   uint64_t* qa_all = bars + 29;   // ... in every CTA of the cluster (one commit-arrival per CTA's MMA warp)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
-  static_assert(23 + NS <= 29, "barrier area is 256 bytes");
+  static_assert(23 + NS <= 29 && NS >= L::kOwnStages, "barrier area is 256 bytes");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = gridDim.z - 1 - blockIdx.z;   // heaviest causal tiles first across all heads
@@ -602,7 +608,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       if (!__all_sync(0xffffffffu, mbar_wait_to(&kv_empty[st], ((j / NS) & 1) ^ 1, 27, j))) goto done;
       // stages 4 and 5 live where Q and dO were staged: free once the row warps have copied them into TMEM — in
       // BOTH CTAs of a multicast pair, since each CTA's load lands in both (qa_all counts the peer's row warps too)
-      if (j == L::kOwnStages && !__all_sync(0xffffffffu, mbar_wait_to(qa_all, 0, 44))) goto done;
+      if (NS > L::kOwnStages && j == L::kOwnStages && !__all_sync(0xffffffffu, mbar_wait_to(qa_all, 0, 44))) goto done;
       if (elected) {
         mbar_expect_tx(&kv_full[st], 2 * L::kKV);
         if (MC > 1) {
@@ -659,11 +665,17 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     }
     __syncwarp();
     if (!issue_sdp(0)) goto done;
+    const bool prof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+    long long pr_t0 = prof ? clock64() : 0, pr_kv = 0, pr_ds = 0;
     for (int j = 0; j < nblk; ++j) {
       const int st = j % NS;
       // buffer (j+1)&1 was last read for block j-1, whose ds_full this warp already waited on
+      long long c0 = prof ? clock64() : 0;
+      if (j + 1 < nblk && prof) { mbar_wait_to(&kv_full[(j + 1) % NS], ((j + 1) / NS) & 1, 29, j); pr_kv += clock64() - c0; }
       if (j + 1 < nblk && !issue_sdp(j + 1)) goto done;
+      c0 = prof ? clock64() : 0;
       if (!__all_sync(0xffffffffu, mbar_wait_to(&ds_full[j & 1], (j >> 1) & 1, 30, j))) goto done;
+      if (prof) pr_ds += clock64() - c0;
       tc_fence_after();
       const uint32_t sK = sbase + L::offK(st);
       if (elected) {
@@ -676,6 +688,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         if (j == nblk - 1) umma_commit(dq_done);
       }
       __syncwarp();
+    }
+    if (prof && lane == 0) {
+      g_attn_prof[0] = clock64() - pr_t0; g_attn_prof[1] = pr_kv; g_attn_prof[2] = pr_ds; g_attn_prof[3] = nblk;
     }
   } else {
     const int quad = warp & 3;                 // TMEM lane quadrant (hardware: warp id mod 4)
@@ -707,12 +722,17 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       __syncwarp();
       if (lane == 0) mbar_arrive(qa_full);
     }
+    const bool rprof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 2;
+    long long rp_t0 = rprof ? clock64() : 0, rp_wait = 0, rp_math = 0, rp_st = 0;
     for (int j = 0; j < nblk; ++j) {
+      long long rc0 = rprof ? clock64() : 0;
       if (!mbar_wait_to(&s_full[j & 1], (j >> 1) & 1, 31, j)) goto done;
       tc_fence_after();
+      long long rc1 = rprof ? clock64() : 0;
+      rp_wait += rc1 - rc0;
       float s[32], dp[32];
       const uint32_t tS = tmem + (j & 1) * 128 + lane_off + half * 32;
-      if (p.debug < 2) {
+      if (p.debug < 2 || p.debug == 3) {
         ld_row32x2(tS, tS + 64, s, dp);
       } else {
 #pragma unroll
@@ -720,7 +740,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
       const int k0 = j * BC + half * 32;
       const bool need_mask = (p.causal && (k0 + 31 > q0)) || (k0 + 32 > S_) || (q0 + BQ > S_);
-      if (p.debug >= 1) {
+      if (p.debug == 1 || p.debug == 2) {
         // profiling aid (SXB_ATTN_DEBUG): no exponentials, results are meaningless
 #pragma unroll
         for (int c = 0; c < 32; ++c) s[c] = s[c] * dp[c];
@@ -745,12 +765,19 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         uint32_t pk[16];
 #pragma unroll
         for (int c = 0; c < 16; ++c) pk[c] = pack_bf16(s[2 * c], s[2 * c + 1]);
+        long long rc2 = rprof ? clock64() : 0;
+        rp_math += rc2 - rc1;
         tmem_st_32x16(tS, pk);
         tmem_st_wait();
+        tc_fence_before();
+        if (rprof) rp_st += clock64() - rc2;
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&ds_full[j & 1]);
+    }
+    if (rprof && lane == 0) {
+      g_attn_prof[4] = clock64() - rp_t0; g_attn_prof[5] = rp_wait; g_attn_prof[6] = rp_math; g_attn_prof[7] = rp_st;
     }
     if (!mbar_wait_to(dq_done, 0, 33)) goto done;
     tc_fence_after();
@@ -1173,6 +1200,12 @@ using namespace sxb;
 using namespace sxb::attn;
 
 SXB_DEFINE_HANG_ACCESSOR(sxb_attn_hang_info)
+
+// SXB_ATTN_DEBUG=3 cycle accounting of the last dQ launch (8 x uint64, host pointer); see g_attn_prof.
+SXB_API int sxb_attn_prof(unsigned long long* out_host) {
+  cudaError_t e = cudaMemcpyFromSymbol(out_host, sxb::attn::g_attn_prof, sizeof(unsigned long long) * 8);
+  return e == cudaSuccess ? SXB_OK : (int)e;
+}
 
 // Which kernel family sxb_attn_fwd / the dQ pass would pick for these K/V: 1 = 2-CTA multicast, 0 = single CTA.
 SXB_API int sxb_attn_would_multicast(const void* k, const void* v, int B, int S, int Hq, int Hk, int D,

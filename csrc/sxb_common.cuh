@@ -510,7 +510,11 @@ static __device__ __noinline__ bool hang_record(uint32_t tag, uint32_t parity, u
 static __device__ __noinline__ bool mbar_wait_slow(uint64_t* bar, uint32_t parity, uint32_t tag, uint32_t aux) {
   unsigned long long t0 = 0;
   long long c_next = clock64() + 65536;
+#ifdef SXB_WAIT_SPIN
+  while (!mbar_test_wait(bar, parity)) {     // experiment: never suspend in try_wait
+#else
   while (!mbar_try_wait(bar, parity)) {
+#endif
     if (clock64() - c_next > 0) {
       c_next = clock64() + 65536;
       if (*reinterpret_cast<volatile unsigned int*>(&g_sxb_hang[0]) != 0) return false;
@@ -522,7 +526,11 @@ static __device__ __noinline__ bool mbar_wait_slow(uint64_t* bar, uint32_t parit
   return true;
 }
 __device__ __forceinline__ bool mbar_wait_to(uint64_t* bar, uint32_t parity, uint32_t tag, uint32_t aux = 0) {
+#ifdef SXB_WAIT_SPIN
+  if (mbar_test_wait(bar, parity)) return true;
+#else
   if (mbar_try_wait(bar, parity)) return true;
+#endif
   return mbar_wait_slow(bar, parity, tag, aux);
 }
 }  // namespace sxb

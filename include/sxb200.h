@@ -385,6 +385,10 @@ int sxb_symm_subset_wsum2(const void* const* bufs, const void* const* sigs, int 
                           int dtype, unsigned int epoch, void* counter, int max_ctas, int shared_result,
                           void* stream);
 
+/* ---- csrc/attention.cu */
+/* SXB_ATTN_DEBUG=3 cycle accounting of the last dQ launch (8 x uint64, host pointer); see g_attn_prof. */
+int sxb_attn_prof(unsigned long long* out_host);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,7 +73,9 @@ class NativeError(RuntimeError):
 
 
 def lib_path() -> Path:
-    return _HERE / "libsxb200.so"
+    # SXB_LIB_PATH: load an alternative build of the CUDA library (A/B experiments with different compile flags)
+    alt = os.environ.get("SXB_LIB_PATH")
+    return Path(alt) if alt else _HERE / "libsxb200.so"
 
 
 def host_lib_path() -> Path:

@@ -24,7 +24,7 @@ def main():
             r = st._attn_case(*cfg, bwd=True)
             e = max((v if isinstance(v, float) else 1e9) for v in r.values())
             worst = max(worst, e)
-            bad += int(not (e < 2e-2))
+            bad += int(not (e < 5e-2))      # element-wise bound of attention backward (tests/test_kernels_gpu.py)
         out["x".join(str(int(v)) for v in cfg)] = {"worst": worst, "bad": bad}
     print(json.dumps(out))
     return int(any(v["bad"] for v in out.values()))
