@@ -503,6 +503,700 @@ done:
   }
 }
 
+// ============================================================================ forward, 128-key blocks (D = 128)
+// Same roles and interfaces as attn_fwd_kernel; what differs is the block shape.  Measured on the 64-key kernel: both
+// CTAs of an SM together take ~2050 cycles per 64-key step although their MMAs need 1024 — S = Q K^T is an SS-form MMA
+// with N = 64 that re-reads the 4 KB Q slice for every 2 KB K slice, 128 KB of shared-memory operand traffic per
+// step and SM at the ~70 B/clk the tensor core sustains from shared memory.  With 128-key blocks the same Q slice
+// serves twice the keys (96 KB per 128 keys instead of 128 KB).  The price is TMEM: S is 128 fp32 columns, so there
+// is ONE S buffer next to O (256 columns, still two CTAs per SM) and inside a CTA the steps run strictly one after
+// the other — QK^T(j), softmax(j) (P overwrites S), O += P V(j) — the second CTA of the SM fills the gaps.  K and V
+// tiles are single slots of 32 KB each: K(j+1) is requested when QK^T(j) retires, V(j+1) when PV(j) does.
+// Eight row warps: two per TMEM lane quadrant, each owning 64 of the block's 128 columns (and 64 of O's), so every
+// scheduler has four softmax warps of the SM's two CTAs to interleave (with four per CTA the exponentials, FMAs and
+// TMEM traffic of one warp per scheduler ran back to back: XU and tensor pipe both ~50 % busy).  The two warps of a
+// row exchange their partial row maxima through shared memory once per block; partial row sums meet at the end.
+constexpr int FBC = 128;
+constexpr int kFwd128Threads = 320;
+struct Fwd128Smem {
+  static constexpr int kQ = BQ * 128 * 2;
+  static constexpr int kKV = FBC * 128 * 2;
+  static constexpr int oQ = 0;
+  static constexpr int oK = oQ + kQ;
+  static constexpr int oV = oK + kKV;
+  static constexpr int oBar = oV + kKV;          // 96 KB + barriers: two CTAs per SM
+  static constexpr int oXch = oBar + 128;        // float [2][128]: partial row max / row sum of the two column halves
+  static constexpr int kTotal = oXch + 1024 + 1024;
+};
+
+template <int MC>
+__global__ void __launch_bounds__(kFwd128Threads, 2)
+attn_fwd128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                   const __grid_constant__ CUtensorMap tmV, const Params p) {
+  using L = Fwd128Smem;
+  constexpr int D = 128, NH = 2;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
+  uint64_t* q_full = bars + 0;
+  uint64_t* k_full = bars + 1;
+  uint64_t* v_full = bars + 2;
+  uint64_t* k_empty = bars + 3;   // QK^T of the block retired (every CTA of the cluster)
+  uint64_t* v_empty = bars + 4;   // O += P V of the block retired
+  uint64_t* s_full = bars + 5;
+  uint64_t* p_full = bars + 6;    // one arrival per row warp
+  uint64_t* o_done = bars + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int pack = p.pack > 1 ? p.pack : 1;
+  const int b = blockIdx.y;
+  const int hk = pack > 1 ? (int)blockIdx.x : (int)blockIdx.x / (p.Hq / p.Hk);
+  const int h = pack > 1 ? hk * pack : (int)blockIdx.x;
+  Win w;
+  int q_row0, q_pos0, q_rows, kv_len;
+  const int* pages = nullptr;
+  if (p.atoms != nullptr) {
+    const int* a = p.atoms + 6 * (int)blockIdx.z;
+    w.off = 0; w.len = 0; w.tb = 0;
+    q_row0 = a[1]; q_rows = a[2]; q_pos0 = a[3]; kv_len = a[5];
+    pages = p.block_tables + (long long)a[0] * p.max_blocks;
+  } else {
+    const int q0 = (gridDim.z - 1 - blockIdx.z) * BQ;
+    w = window(p, b);
+    if (q0 >= w.len) return;
+    q_row0 = w.off + q0; q_pos0 = q0; q_rows = min(BQ, w.len - q0);
+    kv_len = p.causal ? min(w.len, q0 + BQ) : w.len;
+  }
+  const int nblk = (kv_len + FBC - 1) / FBC;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(q_full, 1); mbar_init(k_full, 1); mbar_init(v_full, 1);
+      mbar_init(k_empty, MC); mbar_init(v_empty, MC);
+      mbar_init(s_full, 1); mbar_init(p_full, 8); mbar_init(o_done, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 256);
+  }
+  tc_fence_before();
+  if (MC > 1) cluster_sync_all();
+  else __syncthreads();
+  tc_fence_after();
+  const uint32_t crank = (MC > 1) ? cluster_ctarank() : 0;
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem;          // 128 columns: S, then P (bf16 pairs) over its first 64
+  const uint32_t tO = tmem + 128;    // D columns
+
+  if (warp == 0) {
+    const bool elected = elect_one();
+    if (elected) {
+      mbar_expect_tx(q_full, L::kQ);
+      for (int hh = 0; hh < NH; ++hh)
+        tma_load_4d(smem + L::oQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h, q_row0, w.tb);
+    }
+    __syncwarp();
+    auto load_kv = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* bar, int j) {
+      if (pages == nullptr) {
+        if (MC > 1) {
+          tma_load_4d_mc(dst + crank * (FBC * 128), tm, bar, crank * 64, hk, w.off + j * FBC, w.tb, 3);
+        } else {
+          for (int hh = 0; hh < NH; ++hh)
+            tma_load_4d(dst + hh * (FBC * 128), tm, bar, hh * 64, hk, w.off + j * FBC, w.tb);
+        }
+        return;
+      }
+      const int bs = p.block_size, sub = min(bs, FBC), last = (kv_len - 1) / bs;
+      for (int r = 0; r < FBC; r += sub) {
+        const int pos = j * FBC + r;
+        const int blk = min(pos / bs, last);
+        const int page = pages[blk], in_page = (blk == pos / bs) ? pos % bs : 0;
+        if (MC > 1) {
+          tma_load_4d_mc(dst + crank * (FBC * 128) + r * 128, tm, bar, crank * 64, hk, in_page, page, 3);
+        } else {
+          for (int hh = 0; hh < NH; ++hh)
+            tma_load_4d(dst + hh * (FBC * 128) + r * 128, tm, bar, hh * 64, hk, in_page, page);
+        }
+      }
+    };
+    for (int j = 0; j < nblk; ++j) {
+      if (!__all_sync(0xffffffffu, mbar_wait_to(k_empty, (j & 1) ^ 1, 50, j))) goto done;
+      if (elected) {
+        mbar_expect_tx(k_full, L::kKV);
+        load_kv(&tmK, smem + L::oK, k_full, j);
+      }
+      __syncwarp();
+      if (!__all_sync(0xffffffffu, mbar_wait_to(v_empty, (j & 1) ^ 1, 51, j))) goto done;
+      if (elected) {
+        mbar_expect_tx(v_full, L::kKV);
+        load_kv(&tmV, smem + L::oV, v_full, j);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    const bool elected = elect_one();
+    const uint32_t sbase = __shfl_sync(0xffffffffu, smem_u32(smem), 0);
+    const uint32_t tS_u = __shfl_sync(0xffffffffu, tS, 0);
+    const uint32_t tO_u = tS_u + 128;
+    const uint32_t idesc_s = make_idesc(BQ, FBC, 1, 1, 0, 0);
+    const uint32_t idesc_o = make_idesc(BQ, D, 1, 1, 0, 1);
+    const uint32_t sQ = sbase + L::oQ, sK = sbase + L::oK, sV = sbase + L::oV;
+    if (!__all_sync(0xffffffffu, mbar_wait_to(q_full, 0, 52))) goto done;
+    const bool prof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+    long long pr_t0 = prof ? clock64() : 0, pr_k = 0, pr_p = 0, pr_v = 0;
+    for (int j = 0; j < nblk; ++j) {
+      long long c0 = prof ? clock64() : 0;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(k_full, j & 1, 53, j))) goto done;
+      if (prof) pr_k += clock64() - c0;
+      tc_fence_after();
+      if (elected) {
+        // S(j) overwrites P(j-1): issued behind PV(j-1) in the same thread's MMA stream, which executes in order
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16(tS_u, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, FBC, kk), idesc_s, kk != 0);
+        umma_commit(s_full);
+        if (MC > 1) umma_commit_mc(k_empty, 3);
+        else umma_commit(k_empty);
+      }
+      __syncwarp();
+      c0 = prof ? clock64() : 0;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(p_full, j & 1, 54, j))) goto done;
+      if (prof) { pr_p += clock64() - c0; c0 = clock64(); }
+      if (!__all_sync(0xffffffffu, mbar_wait_to(v_full, j & 1, 55, j))) goto done;
+      if (prof) pr_v += clock64() - c0;
+      tc_fence_after();
+      if (elected) {
+#pragma unroll
+        for (int kk = 0; kk < FBC / 16; ++kk)
+          // P of keys [64 hf, 64 hf + 64) sits bf16-packed on the first 32 of that half's own S columns
+          umma_f16_ts(tO_u, tS_u + (kk >> 2) * 64 + (kk & 3) * 8, desc_mnmajor(sV, FBC, kk), idesc_o, (j | kk) != 0);
+        if (MC > 1) umma_commit_mc(v_empty, 3);
+        else umma_commit(v_empty);
+        if (j == nblk - 1) umma_commit(o_done);
+      }
+      __syncwarp();
+    }
+    if (prof && lane == 0) {
+      g_attn_prof[0] = clock64() - pr_t0; g_attn_prof[1] = pr_k; g_attn_prof[2] = pr_p; g_attn_prof[3] = nblk;
+      g_attn_prof[7] = pr_v;
+    }
+  } else {
+    const int quad = warp & 3;                 // TMEM lane quadrant (hardware: warp id mod 4)
+    const int hf = (warp - 2) >> 2;            // which 64 of the block's 128 key columns (and of O's 128)
+    const int row = quad * 32 + lane;
+    const uint32_t lane_off = uint32_t(quad * 32) << 16;
+    const int qtok = pack > 1 ? row / pack : row;
+    const int qhead = pack > 1 ? h + (row - qtok * pack) : h;
+    const int qpos = q_pos0 + qtok;
+    const float sc = p.scale * kLog2e;
+    float* xch = reinterpret_cast<float*>(smem + L::oXch);     // [2][128]
+    const uint32_t tSh = tS + hf * 64 + lane_off;               // this warp's 64 S columns
+    float m_run = -INFINITY, l_run = 0.f;                       // l_run: partial sum over this warp's columns
+    const bool rprof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 2;
+    long long rp_t0 = rprof ? clock64() : 0, rp_wait = 0, rp_work = 0;
+    for (int j = 0; j < nblk; ++j) {
+      // s_full(j) is a commit behind QK^T(j): every earlier MMA of this CTA, PV(j-1) included, has retired, so O may
+      // be rescaled and S may be overwritten with P without further waits
+      long long rc0 = rprof ? clock64() : 0;
+      if (!mbar_wait_to(s_full, j & 1, 56, j)) goto done;
+      long long rc1 = rprof ? clock64() : 0;
+      rp_wait += rc1 - rc0;
+      tc_fence_after();
+      const int kh = j * FBC + hf * 64;
+      const bool need_mask = (p.causal && (kh + 63 > q_pos0)) || (kh + 64 > kv_len);
+      // pass 1: maximum over this warp's 64 raw scores (scale > 0 commutes with max)
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int q4 = 0; q4 < 2; ++q4) {
+        uint32_t x[32];
+        tmem_ld_32x32(tSh + q4 * 32, x);
+        tmem_ld_wait();
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        if (need_mask) {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const int kp = kh + q4 * 32 + c;
+            const bool ok = (kp < kv_len) && (!p.causal || kp <= qpos);
+            mx4[c & 3] = fmaxf(mx4[c & 3], ok ? __uint_as_float(x[c]) : -INFINITY);
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(x[c]));
+        }
+        mx = fmaxf(mx, fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])));
+      }
+      // the row's other 64 columns belong to the partner warp (same quadrant): swap partial maxima
+      xch[hf * 128 + row] = mx;
+      named_bar_sync(1 + quad, 64);
+      mx = fmaxf(mx, xch[(hf ^ 1) * 128 + row]) * sc;
+      // lazy rescale: keep the running max stale unless it grew by more than 2^8 (both warps of a row see the same mx)
+      float m_new = m_run;
+      const bool grow = mx > m_run + 8.f;
+      const bool any_grow = __any_sync(0xffffffffu, grow) != 0;
+      if (any_grow) m_new = fmaxf(m_run, mx);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      if (j > 0 && any_grow) {
+        const float alpha = (m_run == -INFINITY) ? 0.f : fast_exp2(m_run - m_use);
+        l_run *= alpha;
+#pragma unroll 1
+        for (int c = hf * 2; c < hf * 2 + 2; ++c) {               // this warp's 64 of O's 128 columns
+          uint32_t o[32];
+          tmem_ld_32x32(tO + lane_off + c * 32, o);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tmem_st_32x32(tO + lane_off + c * 32, o);
+        }
+        tmem_st_wait();
+      }
+      m_run = m_new;
+      // pass 2: P = exp2(s * sc - m), bf16-packed over the first 32 of this warp's own 64 S columns.  The first 32
+      // scores are loaded before they are overwritten; the second 32 land on columns 16..31, already consumed.
+      float rs = 0.f;
+#pragma unroll 1
+      for (int q4 = 0; q4 < 2; ++q4) {
+        uint32_t x[32];
+        tmem_ld_32x32(tSh + q4 * 32, x);
+        tmem_ld_wait();
+        float e[32];
+        float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+        if (need_mask) {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const int kp = kh + q4 * 32 + c;
+            const bool ok = (kp < kv_len) && (!p.causal || kp <= qpos);
+            e[c] = ok ? fast_exp2(fmaf(__uint_as_float(x[c]), sc, -m_use)) : 0.f;
+            rs4[c & 3] += e[c];
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            e[c] = fast_exp2(fmaf(__uint_as_float(x[c]), sc, -m_use));
+            rs4[c & 3] += e[c];
+          }
+        }
+        rs += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
+        uint32_t pk[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) pk[c] = pack_bf16(e[2 * c], e[2 * c + 1]);
+        tmem_st_32x16(tSh + q4 * 16, pk);
+      }
+      tmem_st_wait();
+      l_run += rs;
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full);
+      if (rprof) rp_work += clock64() - rc1;
+    }
+    if (rprof && lane == 0) { g_attn_prof[4] = clock64() - rp_t0; g_attn_prof[5] = rp_wait; g_attn_prof[6] = rp_work; }
+    if (!mbar_wait_to(o_done, 0, 57)) goto done;
+    tc_fence_after();
+    xch[hf * 128 + row] = l_run;
+    named_bar_sync(1 + quad, 64);
+    l_run += xch[(hf ^ 1) * 128 + row];
+    const float inv_l = (l_run > 0.f) ? 1.f / l_run : 0.f;
+    {
+      const bool valid = qtok < q_rows;
+      const int grow = valid ? q_row0 + qtok : q_row0;
+      __nv_bfloat16* orow = out_row_ptr(p, false, w.tb, grow) + (long long)qhead * D;
+      __nv_bfloat16* orow_keep = (p.scatter_rows > 0 && p.out != nullptr)
+          ? reinterpret_cast<__nv_bfloat16*>(p.out) + ((long long)w.tb * p.S + grow) * p.out2_stride +
+                (long long)qhead * D
+          : nullptr;
+#pragma unroll 1
+      for (int c = hf * 2; c < hf * 2 + 2; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32(tO + lane_off + c * 32, o);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 w4;
+            w4.x = pack_bf16(__uint_as_float(o[i * 8 + 0]) * inv_l, __uint_as_float(o[i * 8 + 1]) * inv_l);
+            w4.y = pack_bf16(__uint_as_float(o[i * 8 + 2]) * inv_l, __uint_as_float(o[i * 8 + 3]) * inv_l);
+            w4.z = pack_bf16(__uint_as_float(o[i * 8 + 4]) * inv_l, __uint_as_float(o[i * 8 + 5]) * inv_l);
+            w4.w = pack_bf16(__uint_as_float(o[i * 8 + 6]) * inv_l, __uint_as_float(o[i * 8 + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = w4;
+            if (orow_keep) *reinterpret_cast<uint4*>(orow_keep + c * 32 + i * 8) = w4;
+          }
+        }
+      }
+      if (valid && p.lse && hf == 0)
+        p.lse[stat_base(p, w, b, qhead) - w.off + grow] =
+            (l_run > 0.f) ? (m_run + log2f(l_run)) * kLn2 : -INFINITY;
+    }
+  }
+done:
+  tc_fence_before();
+  if (MC > 1) cluster_sync_all();
+  else __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 256);
+  }
+}
+
+// ============================================================================ forward, two heads per CTA (D = 128)
+// Cycle accounting of attn_fwd128_kernel (SXB_ATTN_DEBUG=3) showed why two independent CTAs per SM do not give the
+// ping-pong one hopes for: per 128-key block a CTA's row warps work 2145 cycles and wait 1646, its MMA warp issues for
+// 1150 and waits 2500 — the two CTAs of an SM run in LOCKSTEP, both in their softmax phase (sharing the MUFU, 16
+// exp2/clk/SM: 2 x 128 x 128 / 16 = 2048 cycles) and then both in their MMA phase (2 x 1024 cycles).  This kernel puts
+// the two tiles into ONE CTA — two q heads of the same GQA group, same query rows, so they share every K/V tile — and
+// lets the single MMA warp order the work: QK_A, QK_B | PV_A, QK_A' | PV_B, QK_B' | ...  While the rows of tile A
+// turn S_A into P_A the tensor pipe does tile B's two MMAs, and vice versa: MUFU and tensor pipe each see 2048 cycles
+// of work per pair of blocks and run concurrently.  K/V tiles are fetched once for both heads.
+// TMEM: S_A 0..127, O_A 128..255, S_B 256..383, O_B 384..511 (a tile's row warps only touch its own two 128-column
+// groups, and only while no MMA writes them).  18 warps: TMA, MMA, 8 row warps per tile (two per lane quadrant, 64 of
+// the 128 key columns each).
+constexpr int kFwdPairThreads = 576;
+struct FwdPairSmem {
+  static constexpr int kQ = BQ * 128 * 2;
+  static constexpr int kKV = FBC * 128 * 2;
+  static constexpr int kStages = 2;
+  static constexpr int oQ = 0;                        // two Q tiles
+  static constexpr int oK = oQ + 2 * kQ;
+  static constexpr int oV = oK + kStages * kKV;
+  static constexpr int oBar = oV + kStages * kKV;     // 192 KB
+  static constexpr int oXch = oBar + 256;             // float [2 tiles][2 halves][128]
+  static constexpr int kTotal = oXch + 2048 + 1024;
+};
+
+__global__ void __launch_bounds__(kFwdPairThreads, 1)
+attn_fwd_pair_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                     const __grid_constant__ CUtensorMap tmV, const Params p) {
+  using L = FwdPairSmem;
+  constexpr int D = 128, NH = 2, NS = L::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
+  uint64_t* q_full = bars + 0;
+  uint64_t* k_full = bars + 1;    // [2]
+  uint64_t* v_full = bars + 3;    // [2]
+  uint64_t* k_empty = bars + 5;   // [2] both tiles' QK^T of the block retired
+  uint64_t* v_empty = bars + 7;   // [2] both tiles' PV of the block retired
+  uint64_t* s_full = bars + 9;    // [2 tiles]
+  uint64_t* p_full = bars + 11;   // [2 tiles] one arrival per row warp of the tile
+  uint64_t* o_done = bars + 13;   // [2 tiles]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+  // turn[t]: tile t's row warps may run their exponentials for their next block (8 arrivals: the other tile's warps).
+  // Left alone the two tiles' softmax phases drift into lockstep, share the MUFU (each taking twice as long) and leave
+  // the tensor pipe idle meanwhile; taking turns keeps one tile in its exponentials while the other's MMAs run.
+  uint64_t* turn = bars + 17;     // [2]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.y;
+  const int h0 = 2 * (int)blockIdx.x;              // heads h0 and h0 + 1: same K/V head (host checks the group is even)
+  const int hk = h0 / (p.Hq / p.Hk);
+  Win w;
+  int q_row0, q_pos0, q_rows, kv_len;
+  const int* pages = nullptr;
+  if (p.atoms != nullptr) {
+    const int* a = p.atoms + 6 * (int)blockIdx.z;
+    w.off = 0; w.len = 0; w.tb = 0;
+    q_row0 = a[1]; q_rows = a[2]; q_pos0 = a[3]; kv_len = a[5];
+    pages = p.block_tables + (long long)a[0] * p.max_blocks;
+  } else {
+    const int q0 = (gridDim.z - 1 - blockIdx.z) * BQ;
+    w = window(p, b);
+    if (q0 >= w.len) return;
+    q_row0 = w.off + q0; q_pos0 = q0; q_rows = min(BQ, w.len - q0);
+    kv_len = p.causal ? min(w.len, q0 + BQ) : w.len;
+  }
+  const int nblk = (kv_len + FBC - 1) / FBC;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(q_full, 1);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&k_full[i], 1); mbar_init(&v_full[i], 1); mbar_init(&k_empty[i], 1); mbar_init(&v_empty[i], 1);
+        mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 8); mbar_init(&o_done[i], 1);
+        mbar_init(&turn[i], 8);
+      }
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    const bool elected = elect_one();
+    if (elected) {
+      mbar_expect_tx(q_full, 2 * L::kQ);
+      for (int t = 0; t < 2; ++t)
+        for (int hh = 0; hh < NH; ++hh)
+          tma_load_4d(smem + L::oQ + t * L::kQ + hh * (BQ * 128), &tmQ, q_full, hh * 64, h0 + t, q_row0, w.tb);
+    }
+    __syncwarp();
+    auto load_kv = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* bar, int j) {
+      if (pages == nullptr) {
+        for (int hh = 0; hh < NH; ++hh)
+          tma_load_4d(dst + hh * (FBC * 128), tm, bar, hh * 64, hk, w.off + j * FBC, w.tb);
+        return;
+      }
+      const int bs = p.block_size, sub = min(bs, FBC), last = (kv_len - 1) / bs;
+      for (int r = 0; r < FBC; r += sub) {
+        const int pos = j * FBC + r;
+        const int blk = min(pos / bs, last);
+        const int page = pages[blk], in_page = (blk == pos / bs) ? pos % bs : 0;
+        for (int hh = 0; hh < NH; ++hh)
+          tma_load_4d(dst + hh * (FBC * 128) + r * 128, tm, bar, hh * 64, hk, in_page, page);
+      }
+    };
+    for (int j = 0; j < nblk; ++j) {
+      const int st = j % NS;
+      const uint32_t ph = ((j / NS) & 1) ^ 1;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&k_empty[st], ph, 60, j))) goto done;
+      if (elected) {
+        mbar_expect_tx(&k_full[st], L::kKV);
+        load_kv(&tmK, smem + L::oK + st * L::kKV, &k_full[st], j);
+      }
+      __syncwarp();
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&v_empty[st], ph, 61, j))) goto done;
+      if (elected) {
+        mbar_expect_tx(&v_full[st], L::kKV);
+        load_kv(&tmV, smem + L::oV + st * L::kKV, &v_full[st], j);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    const bool elected = elect_one();
+    const uint32_t sbase = __shfl_sync(0xffffffffu, smem_u32(smem), 0);
+    const uint32_t tm_u = __shfl_sync(0xffffffffu, tmem, 0);
+    const uint32_t idesc_s = make_idesc(BQ, FBC, 1, 1, 0, 0);
+    const uint32_t idesc_o = make_idesc(BQ, D, 1, 1, 0, 1);
+    // S(t, j) = Q_t K(j)^T into the tile's S columns; overwrites P(t, j-1), which PV(t, j-1) — issued earlier by this
+    // thread, MMAs execute in issue order — has consumed
+    auto issue_qk = [&](int t, int j) {
+      const uint32_t sQ = sbase + L::oQ + t * L::kQ, sK = sbase + L::oK + (j % NS) * L::kKV;
+      if (elected) {
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16(tm_u + t * 256, desc_kmajor_d(sQ, BQ, kk), desc_kmajor_d(sK, FBC, kk), idesc_s, kk != 0);
+        umma_commit(&s_full[t]);
+      }
+      __syncwarp();
+    };
+    auto issue_pv = [&](int t, int j) {
+      const uint32_t sV = sbase + L::oV + (j % NS) * L::kKV;
+      if (elected) {
+#pragma unroll
+        for (int kk = 0; kk < FBC / 16; ++kk)
+          umma_f16_ts(tm_u + t * 256 + 128, tm_u + t * 256 + (kk >> 2) * 64 + (kk & 3) * 8, desc_mnmajor(sV, FBC, kk),
+                      idesc_o, (j | kk) != 0);
+        if (j == nblk - 1) umma_commit(&o_done[t]);
+      }
+      __syncwarp();
+    };
+    if (!__all_sync(0xffffffffu, mbar_wait_to(q_full, 0, 62))) goto done;
+    if (!__all_sync(0xffffffffu, mbar_wait_to(&k_full[0], 0, 63, 0))) goto done;
+    tc_fence_after();
+    issue_qk(0, 0);
+    issue_qk(1, 0);
+    if (elected) umma_commit(&k_empty[0]);
+    __syncwarp();
+    const bool prof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+    long long pr_t0 = prof ? clock64() : 0, pr_kv = 0, pr_p0 = 0, pr_p1 = 0;
+    for (int j = 0; j < nblk; ++j) {
+      const int st = j % NS, stn = (j + 1) % NS;
+      const bool more = j + 1 < nblk;
+      long long c0 = prof ? clock64() : 0;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&v_full[st], (j / NS) & 1, 64, j))) goto done;
+      if (prof) { pr_kv += clock64() - c0; c0 = clock64(); }
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&p_full[0], j & 1, 65, j))) goto done;
+      if (prof) pr_p0 += clock64() - c0;
+      tc_fence_after();
+      issue_pv(0, j);
+      if (more) {
+        c0 = prof ? clock64() : 0;
+        if (!__all_sync(0xffffffffu, mbar_wait_to(&k_full[stn], ((j + 1) / NS) & 1, 63, j + 1))) goto done;
+        if (prof) pr_kv += clock64() - c0;
+        tc_fence_after();
+        issue_qk(0, j + 1);
+      }
+      c0 = prof ? clock64() : 0;
+      if (!__all_sync(0xffffffffu, mbar_wait_to(&p_full[1], j & 1, 66, j))) goto done;
+      if (prof) pr_p1 += clock64() - c0;
+      tc_fence_after();
+      issue_pv(1, j);
+      if (elected) umma_commit(&v_empty[st]);
+      __syncwarp();
+      if (more) {
+        issue_qk(1, j + 1);
+        if (elected) umma_commit(&k_empty[stn]);
+        __syncwarp();
+      }
+    }
+    if (prof && lane == 0) {
+      g_attn_prof[0] = clock64() - pr_t0; g_attn_prof[1] = pr_kv; g_attn_prof[2] = pr_p0; g_attn_prof[3] = nblk;
+      g_attn_prof[7] = pr_p1;
+    }
+  } else {
+    const int t = (warp - 2) >> 3;               // tile (head h0 + t)
+    const int quad = warp & 3;                   // TMEM lane quadrant (hardware: warp id mod 4)
+    const int hf = ((warp - 2) & 7) >> 2;        // which 64 of the block's 128 key columns (and of O's 128)
+    const int row = quad * 32 + lane;
+    const uint32_t lane_off = uint32_t(quad * 32) << 16;
+    const int qhead = h0 + t;
+    const int qpos = q_pos0 + row;
+    const float sc = p.scale * kLog2e;
+    float* xch = reinterpret_cast<float*>(smem + L::oXch) + t * 256;     // [2][128]
+    const uint32_t tS = tmem + t * 256, tO = tS + 128;
+    const uint32_t tSh = tS + hf * 64 + lane_off;
+    const int bar_id = 1 + t * 4 + quad;
+    float m_run = -INFINITY, l_run = 0.f;
+    const bool rprof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 2;
+    long long rp_t0 = rprof ? clock64() : 0, rp_wait = 0, rp_work = 0;
+    for (int j = 0; j < nblk; ++j) {
+      // s_full[t](j) is a commit behind QK(t, j): PV(t, j-1) has retired, so O_t may be rescaled and S_t overwritten
+      long long rc0 = rprof ? clock64() : 0;
+      if (!mbar_wait_to(&s_full[t], j & 1, 67, j)) goto done;
+      long long rc1 = rprof ? clock64() : 0;
+      rp_wait += rc1 - rc0;
+      tc_fence_after();
+      const int kh = j * FBC + hf * 64;
+      const bool need_mask = (p.causal && (kh + 63 > q_pos0)) || (kh + 64 > kv_len);
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int q4 = 0; q4 < 2; ++q4) {
+        uint32_t x[32];
+        tmem_ld_32x32(tSh + q4 * 32, x);
+        tmem_ld_wait();
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        if (need_mask) {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const int kp = kh + q4 * 32 + c;
+            const bool ok = (kp < kv_len) && (!p.causal || kp <= qpos);
+            mx4[c & 3] = fmaxf(mx4[c & 3], ok ? __uint_as_float(x[c]) : -INFINITY);
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(x[c]));
+        }
+        mx = fmaxf(mx, fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])));
+      }
+      xch[hf * 128 + row] = mx;
+      named_bar_sync8(bar_id, 64);
+      mx = fmaxf(mx, xch[(hf ^ 1) * 128 + row]) * sc;
+      float m_new = m_run;
+      const bool grow = mx > m_run + 8.f;
+      const bool any_grow = __any_sync(0xffffffffu, grow) != 0;
+      if (any_grow) m_new = fmaxf(m_run, mx);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      if (j > 0 && any_grow) {
+        const float alpha = (m_run == -INFINITY) ? 0.f : fast_exp2(m_run - m_use);
+        l_run *= alpha;
+#pragma unroll 1
+        for (int c = hf * 2; c < hf * 2 + 2; ++c) {
+          uint32_t o[32];
+          tmem_ld_32x32(tO + lane_off + c * 32, o);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tmem_st_32x32(tO + lane_off + c * 32, o);
+        }
+        tmem_st_wait();
+      }
+      m_run = m_new;
+      // my turn at the MUFU: tile 0 goes first; tile t's block j follows the other tile's block j - (t == 0)
+      if (p.debug != 4 && (t == 1 || j > 0)) {
+        if (!mbar_wait_to(&turn[t], (t == 1 ? j : j - 1) & 1, 69, j)) goto done;
+      }
+      float rs = 0.f;
+#pragma unroll 1
+      for (int q4 = 0; q4 < 2; ++q4) {
+        uint32_t x[32];
+        tmem_ld_32x32(tSh + q4 * 32, x);
+        tmem_ld_wait();
+        float e[32];
+        float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+        if (need_mask) {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const int kp = kh + q4 * 32 + c;
+            const bool ok = (kp < kv_len) && (!p.causal || kp <= qpos);
+            e[c] = ok ? fast_exp2(fmaf(__uint_as_float(x[c]), sc, -m_use)) : 0.f;
+            rs4[c & 3] += e[c];
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            e[c] = fast_exp2(fmaf(__uint_as_float(x[c]), sc, -m_use));
+            rs4[c & 3] += e[c];
+          }
+        }
+        rs += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
+        uint32_t pk[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) pk[c] = pack_bf16(e[2 * c], e[2 * c + 1]);
+        tmem_st_32x16(tSh + q4 * 16, pk);
+      }
+      if (lane == 0) mbar_arrive(&turn[t ^ 1]);      // exponentials issued: the other tile may start its own
+      tmem_st_wait();
+      l_run += rs;
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[t]);
+      if (rprof) rp_work += clock64() - rc1;
+    }
+    if (rprof && lane == 0) { g_attn_prof[4] = clock64() - rp_t0; g_attn_prof[5] = rp_wait; g_attn_prof[6] = rp_work; }
+    if (!mbar_wait_to(&o_done[t], 0, 68)) goto done;
+    tc_fence_after();
+    xch[hf * 128 + row] = l_run;
+    named_bar_sync8(bar_id, 64);
+    l_run += xch[(hf ^ 1) * 128 + row];
+    const float inv_l = (l_run > 0.f) ? 1.f / l_run : 0.f;
+    {
+      const bool valid = row < q_rows;
+      const int grow = valid ? q_row0 + row : q_row0;
+      __nv_bfloat16* orow = out_row_ptr(p, false, w.tb, grow) + (long long)qhead * D;
+      __nv_bfloat16* orow_keep = (p.scatter_rows > 0 && p.out != nullptr)
+          ? reinterpret_cast<__nv_bfloat16*>(p.out) + ((long long)w.tb * p.S + grow) * p.out2_stride +
+                (long long)qhead * D
+          : nullptr;
+#pragma unroll 1
+      for (int c = hf * 2; c < hf * 2 + 2; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32(tO + lane_off + c * 32, o);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 w4;
+            w4.x = pack_bf16(__uint_as_float(o[i * 8 + 0]) * inv_l, __uint_as_float(o[i * 8 + 1]) * inv_l);
+            w4.y = pack_bf16(__uint_as_float(o[i * 8 + 2]) * inv_l, __uint_as_float(o[i * 8 + 3]) * inv_l);
+            w4.z = pack_bf16(__uint_as_float(o[i * 8 + 4]) * inv_l, __uint_as_float(o[i * 8 + 5]) * inv_l);
+            w4.w = pack_bf16(__uint_as_float(o[i * 8 + 6]) * inv_l, __uint_as_float(o[i * 8 + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(orow + c * 32 + i * 8) = w4;
+            if (orow_keep) *reinterpret_cast<uint4*>(orow_keep + c * 32 + i * 8) = w4;
+          }
+        }
+      }
+      if (valid && p.lse && hf == 0)
+        p.lse[stat_base(p, w, b, qhead) - w.off + grow] =
+            (l_run > 0.f) ? (m_run + log2f(l_run)) * kLn2 : -INFINITY;
+    }
+  }
+done:
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
 // ===================================================================== backward: dQ
 // One CTA per (128-query tile, head, batch); loops over 64-key blocks.  S / dP accumulators are
 // double-buffered in TMEM so the tensor core computes block j+1 while the row threads turn block j
@@ -1213,6 +1907,17 @@ SXB_API int sxb_attn_would_multicast(const void* k, const void* v, int B, int S,
   return use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride)) ? 1 : 0;
 }
 
+// SXB_ATTN_FWD128: forward kernel family for head_dim 128 — 0: 64-key blocks (attn_fwd_kernel), 1: 128-key blocks,
+// one head per CTA (attn_fwd128_kernel), 2: 128-key blocks, two heads of a GQA group per CTA (attn_fwd_pair_kernel).
+static int fwd_mode() {
+  static const int env = [] { const char* e = getenv("SXB_ATTN_FWD128"); return e ? atoi(e) : 0; }();
+  return env;
+}
+static bool use_fwd128(int D) { return fwd_mode() != 0 && D == 128; }
+static bool use_fwd_pair(int D, int Hq, int Hk) {
+  return fwd_mode() == 2 && D == 128 && Hk > 0 && (Hq % 2) == 0 && ((Hq / Hk) % 2) == 0;
+}
+
 static bool attn_args_ok(int B, int S, int Hq, int Hk, int D, long long qs, long long ks,
                          long long vs) {
   if (B <= 0 || S <= 0 || Hq <= 0 || Hk <= 0 || Hq % Hk) return false;
@@ -1262,17 +1967,41 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
     return SXB_ERR_UNSUPPORTED;
   CUtensorMap tq, tk, tv;
   int rc;
+  const bool wide = use_fwd128(D);       // 128-key blocks (attn_fwd128_kernel)
+  const int kv_rows = wide ? FBC : BC;
   if ((rc = make_qkv_map(&tq, q, B, S, Hq, D, q_stride, BQ))) return rc;
-  if ((rc = make_qkv_map(&tk, k, B, S, Hk, D, k_stride, BC))) return rc;
-  if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, BC))) return rc;
+  if ((rc = make_qkv_map(&tk, k, B, S, Hk, D, k_stride, kv_rows))) return rc;
+  if ((rc = make_qkv_map(&tv, v, B, S, Hk, D, v_stride, kv_rows))) return rc;
   Params p{};
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
   p.cu_seqlens = g_varlen.cu;
+  {
+    static const int dbg = [] { const char* e = getenv("SXB_ATTN_DEBUG"); return e ? atoi(e) : 0; }();
+    p.debug = dbg;
+  }
   apply_scatter(p, false);
   if (p.scatter_rows > 0) { p.out = g_keep; p.out2_stride = g_keep_stride; }
   dim3 grid = attn_grid(Hq, B, S);
   cudaStream_t s = (cudaStream_t)stream;
+  if (wide && use_fwd_pair(D, Hq, Hk)) {
+    grid.x = Hq / 2;
+    if ((rc = set_smem(attn_fwd_pair_kernel, FwdPairSmem::kTotal))) return rc;
+    attn_fwd_pair_kernel<<<grid, kFwdPairThreads, FwdPairSmem::kTotal, s>>>(tq, tk, tv, p);
+    SXB_CHECK_LAUNCH();
+    return SXB_OK;
+  }
+  if (wide) {
+    if (use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride))) {
+      if ((rc = set_smem(attn_fwd128_kernel<2>, Fwd128Smem::kTotal))) return rc;
+      if ((rc = launch_cluster2(attn_fwd128_kernel<2>, grid, kFwd128Threads, Fwd128Smem::kTotal, s, tq, tk, tv, p))) return rc;
+    } else {
+      if ((rc = set_smem(attn_fwd128_kernel<1>, Fwd128Smem::kTotal))) return rc;
+      attn_fwd128_kernel<1><<<grid, kFwd128Threads, Fwd128Smem::kTotal, s>>>(tq, tk, tv, p);
+    }
+    SXB_CHECK_LAUNCH();
+    return SXB_OK;
+  }
   if (use_multicast(Hq, Hk, D, k, span_bytes(B, S, Hk, D, k_stride), v, span_bytes(B, S, Hk, D, v_stride))) {
     if ((rc = set_smem(attn_fwd_kernel<128, 2>, FwdSmem<128>::kTotal))) return rc;
     if ((rc = launch_cluster2(attn_fwd_kernel<128, 2>, grid, kThreads, FwdSmem<128>::kTotal, s, tq, tk, tv, p)))
@@ -1472,7 +2201,10 @@ SXB_API int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, cons
   int rc;
   if ((rc = make_qkv_map(&tq, q, 1, T, Hq, D, q_stride, BQ))) return rc;
   const long long slot = 2LL * Hk * D;   // elements per cached token: K heads then V heads
-  const int box_rows = block_size < BC ? block_size : BC;
+  // 128-key tiles need pages that tile them exactly; other page sizes keep the 64-key kernel
+  const bool wide = use_fwd128(D) && (block_size <= FBC ? (FBC % block_size) == 0 : (block_size % FBC) == 0);
+  const int tile_rows = wide ? FBC : BC;
+  const int box_rows = block_size < tile_rows ? block_size : tile_rows;
   const __nv_bfloat16* kbase = static_cast<const __nv_bfloat16*>(cache);
   if ((rc = make_qkv_map(&tk, kbase, n_blocks, block_size, Hk, D, slot, box_rows))) return rc;
   if ((rc = make_qkv_map(&tv, kbase + (long long)Hk * D, n_blocks, block_size, Hk, D, slot, box_rows))) return rc;
@@ -1491,7 +2223,10 @@ SXB_API int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, cons
     pp.pack = group;
     pp.atoms = p.atoms + 6LL * (n_atoms - n_packed);
     dim3 gridp(Hk, 1, n_packed);
-    if (D == 128) {
+    if (wide) {
+      if ((rc = set_smem(attn_fwd128_kernel<1>, Fwd128Smem::kTotal))) return rc;
+      attn_fwd128_kernel<1><<<gridp, kFwd128Threads, Fwd128Smem::kTotal, s>>>(tqp, tk, tv, pp);
+    } else if (D == 128) {
       if ((rc = set_smem(attn_fwd_kernel<128, 1>, FwdSmem<128>::kTotal))) return rc;
       attn_fwd_kernel<128, 1><<<gridp, kThreads, FwdSmem<128>::kTotal, s>>>(tqp, tk, tv, pp);
     } else {
@@ -1504,6 +2239,24 @@ SXB_API int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, cons
   }
   dim3 grid(Hq, 1, n_atoms);
   const long long cache_bytes = (long long)n_blocks * block_size * slot * 2;
+  if (wide && use_fwd_pair(D, Hq, Hk)) {
+    grid.x = Hq / 2;
+    if ((rc = set_smem(attn_fwd_pair_kernel, FwdPairSmem::kTotal))) return rc;
+    attn_fwd_pair_kernel<<<grid, kFwdPairThreads, FwdPairSmem::kTotal, s>>>(tq, tk, tv, p);
+    SXB_CHECK_LAUNCH();
+    return SXB_OK;
+  }
+  if (wide) {
+    if (use_multicast(Hq, Hk, D, cache, cache_bytes, cache, cache_bytes)) {
+      if ((rc = set_smem(attn_fwd128_kernel<2>, Fwd128Smem::kTotal))) return rc;
+      if ((rc = launch_cluster2(attn_fwd128_kernel<2>, grid, kFwd128Threads, Fwd128Smem::kTotal, s, tq, tk, tv, p))) return rc;
+    } else {
+      if ((rc = set_smem(attn_fwd128_kernel<1>, Fwd128Smem::kTotal))) return rc;
+      attn_fwd128_kernel<1><<<grid, kFwd128Threads, Fwd128Smem::kTotal, s>>>(tq, tk, tv, p);
+    }
+    SXB_CHECK_LAUNCH();
+    return SXB_OK;
+  }
   if (use_multicast(Hq, Hk, D, cache, cache_bytes, cache, cache_bytes)) {
     if ((rc = set_smem(attn_fwd_kernel<128, 2>, FwdSmem<128>::kTotal))) return rc;
     if ((rc = launch_cluster2(attn_fwd_kernel<128, 2>, grid, kThreads, FwdSmem<128>::kTotal, s, tq, tk, tv, p)))

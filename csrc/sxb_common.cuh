@@ -319,6 +319,31 @@ __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&v
       "r"(v[30]), "r"(v[31])
       : "memory");
 }
+// Named barrier among `nthreads` threads of the CTA (ids 1..15; 0 is __syncthreads).
+template <int ID>
+__device__ __forceinline__ void named_bar_sync_id(int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"n"(ID), "r"(nthreads) : "memory");
+}
+// ids 1..4 chosen at run time but encoded as immediates, so the kernel reserves 5 barriers, not all 16
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  if (id == 1) named_bar_sync_id<1>(nthreads);
+  else if (id == 2) named_bar_sync_id<2>(nthreads);
+  else if (id == 3) named_bar_sync_id<3>(nthreads);
+  else named_bar_sync_id<4>(nthreads);
+}
+// ids 1..8 as immediates
+__device__ __forceinline__ void named_bar_sync8(int id, int nthreads) {
+  switch (id) {
+    case 1: named_bar_sync_id<1>(nthreads); break;
+    case 2: named_bar_sync_id<2>(nthreads); break;
+    case 3: named_bar_sync_id<3>(nthreads); break;
+    case 4: named_bar_sync_id<4>(nthreads); break;
+    case 5: named_bar_sync_id<5>(nthreads); break;
+    case 6: named_bar_sync_id<6>(nthreads); break;
+    case 7: named_bar_sync_id<7>(nthreads); break;
+    default: named_bar_sync_id<8>(nthreads); break;
+  }
+}
 __device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&v)[16]) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "

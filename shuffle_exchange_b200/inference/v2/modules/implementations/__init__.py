@@ -232,7 +232,7 @@ class DSMultiGemmMoE(DSMoEBase):
         c = self._config
         logits = torch.nn.functional.linear(hidden_states, gate_w)
         scores, assign, offsets, counts = moe_ops.top_k_gating(logits, c.top_k, renormalize=c.normalize_scores)
-        from ....moe import fused_ep
+        from .....moe import fused_ep
         if fused_ep.grouped_inference_ok(hidden_states, mlp_1_w, mlp_2_w, mlp_1_b, mlp_2_b):
             # one grouped tcgen05 GEMM per projection over expert-contiguous rows, no host synchronisation
             self._output = fused_ep.grouped_experts_inference(

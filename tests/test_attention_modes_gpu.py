@@ -153,3 +153,43 @@ def test_atom_attention_on_fused_qkv_view():
     got = R.ragged_attention(q, cache, w, scale=1.0 / math.sqrt(D))
     want = R.paged_attention(q.contiguous(), cache, w.token_to_seq(), w.token_positions(), w.block_tables())
     assert _rel_err(got, want) < 1e-2
+
+
+_VARIANT_SCRIPT = r"""
+import torch, sys
+from shuffle_exchange_b200.ops import functional as F
+from shuffle_exchange_b200.native import lib
+torch.manual_seed(0)
+worst = 0.0
+for (B, S, Hq, Hk, causal) in [(1, 512, 4, 2, True), (2, 300, 4, 1, True), (1, 1024, 2, 1, False), (1, 129, 8, 2, True)]:
+    q = torch.randn(B, S, Hq, 128, device="cuda", dtype=torch.bfloat16)
+    k = torch.randn(B, S, Hk, 128, device="cuda", dtype=torch.bfloat16)
+    v = torch.randn(B, S, Hk, 128, device="cuda", dtype=torch.bfloat16)
+    out, lse = F.attention_fwd_lse(q, k, v, causal, 128 ** -0.5)
+    ref = F.attention_ref(q.float(), k.float(), v.float(), causal)
+    worst = max(worst, ((out.float() - ref).norm() / ref.norm()).item())
+    qf = q.float().permute(0, 2, 1, 3); kf = k.float().permute(0, 2, 1, 3).repeat_interleave(Hq // Hk, 1)
+    s = qf @ kf.transpose(-1, -2) * 128 ** -0.5
+    if causal:
+        s = s.masked_fill(~torch.ones(S, S, dtype=torch.bool, device="cuda").tril(), float("-inf"))
+    worst = max(worst, (lse - torch.logsumexp(s, -1)).abs().max().item())
+assert lib.hang_info("attn") is None
+print("WORST", worst)
+"""
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["1", "2"])
+def test_forward_kernel_variants(mode):
+    """SXB_ATTN_FWD128=1 (128-key blocks) and =2 (two heads of a GQA group per CTA) compute the same attention as the
+    default kernel; the switch is read once per process, hence the subprocess."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, SXB_ATTN_FWD128=mode)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", _VARIANT_SCRIPT], capture_output=True, text=True, env=env, cwd=root,
+                       timeout=200)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    worst = float(r.stdout.strip().split("WORST")[-1])
+    assert worst < 1e-2, worst
