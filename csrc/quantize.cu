@@ -420,6 +420,79 @@ fp_dequantize_kernel(const uint8_t* __restrict__ in, T* __restrict__ out, int gr
   }
 }
 
+// ============================================================================ weight-only mini-float GEMV
+// y[M, N] = x[M, K] W^T with W [N, K] stored group-quantised (FP6 e3m2 / FP8 e4m3 / FP4 e2m1 payload + fp32 scale per
+// `group_size` consecutive elements, K % group_size == 0), for decode-sized M (<= 8): the product is bound by reading
+// W once, so the weights stay packed until they are in registers.  One warp owns R = 4 consecutive rows of W and walks
+// K 256 elements at a time (lane l: elements 8 l .. 8 l + 7 of the step): 8 codes = kBits bytes per row and lane, the
+// matching 8 activations of every batch row are loaded once and used for all R rows.  Decode is a bit trick, not the
+// exp2f of the offline dequantiser: the code's exponent|mantissa bits are moved to fp32 position, the exponent rebased
+// by an integer add, subnormals (exponent field 0) scaled from the integer mantissa.
+// (reference: inference/v2/kernels/core_ops/cuda_linear/fp6_linear.cu — W6A16 on mma.sync; here the
+// bandwidth-bound decode case, prefill sizes dequantise into scratch and use the tcgen05 GEMM.)
+template <int E, int M>
+__device__ __forceinline__ float minifloat_to_f32(uint32_t c) {
+  constexpr int kBias = (1 << (E - 1)) - 1;
+  const uint32_t sign = (c >> (E + M)) & 1u;
+  const uint32_t ef = (c >> M) & ((1u << E) - 1);
+  const uint32_t mant = c & ((1u << M) - 1);
+  const float normal = __uint_as_float(((ef + 127u - kBias) << 23) | (mant << (23 - M)));
+  const float sub = float(mant) * __uint_as_float((uint32_t)(127 + 1 - kBias - M) << 23);
+  const float v = ef ? normal : sub;
+  return sign ? -v : v;
+}
+
+template <int E, int M, int MB>
+__global__ void __launch_bounds__(256)
+fp_gemv_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict__ wq, __nv_bfloat16* __restrict__ y,
+               int N, int K, int group_size, long long x_stride, long long y_stride) {
+  using F = MiniFloat<E, M>;
+  constexpr int R = 4;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = (blockIdx.x * 8 + warp) * R;
+  if (n0 >= N) return;
+  const long long gbytes = (long long)group_size * F::kBits / 8 + 4;
+  float acc[R][MB];
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int m = 0; m < MB; ++m) acc[r][m] = 0.f;
+  for (int k = lane * 8; k < K; k += 256) {
+    float xv[MB][8];
+#pragma unroll
+    for (int m = 0; m < MB; ++m) load8<__nv_bfloat16>(x + m * x_stride + k, xv[m]);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (n0 + r >= N) break;
+      const long long e0 = (long long)(n0 + r) * K + k;            // element index in the flattened weight
+      const long long g = e0 / group_size;
+      const int o = (int)(e0 - g * group_size);                     // multiple of 8
+      const uint8_t* gp = wq + g * gbytes;
+      const uint8_t* sp = gp + gbytes - 4;
+      const float scale = __uint_as_float((uint32_t)sp[0] | ((uint32_t)sp[1] << 8) | ((uint32_t)sp[2] << 16) |
+                                          ((uint32_t)sp[3] << 24));
+      uint32_t c[8];
+      unpack8<F::kBits>(gp + (o / 8) * F::kBits, c);
+      float wv[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) wv[i] = minifloat_to_f32<E, M>(c[i]) * scale;
+#pragma unroll
+      for (int m = 0; m < MB; ++m)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[r][m] = fmaf(wv[i], xv[m][i], acc[r][m]);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int m = 0; m < MB; ++m) {
+      float v = acc[r][m];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+      if (lane == 0 && n0 + r < N) y[m * y_stride + n0 + r] = __float2bfloat16_rn(v);
+    }
+}
+
 // ================================================================================== sign packing
 // 1-bit optimizers: byte i holds the signs of elements 8i..8i+7, most significant bit first (numpy /
 // cupy packbits order, which the reference relies on).  unpack writes +1 / -1.
@@ -771,4 +844,43 @@ SXB_API int sxb_fp8_rowwise_quant(const void* in, void* out, void* scales, long 
       (const __nv_bfloat16*)in, (uint8_t*)out, (float*)scales, rows, cols, ld_in, ld_out);
   SXB_CHECK_LAUNCH();
   return SXB_OK;
+}
+
+namespace {
+template <int E, int M>
+int launch_fp_gemv(const void* x, const void* wq, void* y, int Mrows, int N, int K, int gs, long long xs, long long ys,
+                   cudaStream_t s) {
+  const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
+  const uint8_t* wp = static_cast<const uint8_t*>(wq);
+  __nv_bfloat16* yp = static_cast<__nv_bfloat16*>(y);
+  const unsigned blocks = (unsigned)((N + 31) / 32);      // 8 warps x 4 rows per block
+  for (int m0 = 0; m0 < Mrows; m0 += 8) {                 // batch rows in chunks of at most 8
+    const int mb = Mrows - m0 >= 8 ? 8 : (Mrows - m0 >= 4 ? 4 : (Mrows - m0 >= 2 ? 2 : 1));
+    const __nv_bfloat16* xc = xp + m0 * xs;
+    __nv_bfloat16* yc = yp + m0 * ys;
+    if (mb == 8) fp_gemv_kernel<E, M, 8><<<blocks, 256, 0, s>>>(xc, wp, yc, N, K, gs, xs, ys);
+    else if (mb == 4) fp_gemv_kernel<E, M, 4><<<blocks, 256, 0, s>>>(xc, wp, yc, N, K, gs, xs, ys);
+    else if (mb == 2) fp_gemv_kernel<E, M, 2><<<blocks, 256, 0, s>>>(xc, wp, yc, N, K, gs, xs, ys);
+    else fp_gemv_kernel<E, M, 1><<<blocks, 256, 0, s>>>(xc, wp, yc, N, K, gs, xs, ys);
+    if (mb < 8) m0 -= 8 - mb;                             // advance by mb, not 8
+  }
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+}  // namespace
+
+// Weight-only quantised linear for small batches: y[M, N] (bf16) = x[M, K] (bf16) W^T, W [N, K] in the layout written
+// by sxb_fp_quantize (q_bits 4 / 6 / 8, groups of `group_size` along the flattened weight, K % group_size == 0,
+// K % 256 == 0).  Intended for M <= 16 (decode); larger M should dequantise and use the tcgen05 GEMM.
+SXB_API int sxb_fp_gemv(const void* x, const void* wq, void* y, int M, int N, int K, int q_bits, int group_size,
+                        long long x_stride, long long y_stride, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return SXB_ERR_BAD_ARG;
+  if (group_size <= 0 || group_size % 8 || K % group_size || K % 256 || x_stride % 8) return SXB_ERR_UNSUPPORTED;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  switch (q_bits) {
+    case 8: return launch_fp_gemv<4, 3>(x, wq, y, M, N, K, group_size, x_stride, y_stride, s);
+    case 6: return launch_fp_gemv<3, 2>(x, wq, y, M, N, K, group_size, x_stride, y_stride, s);
+    case 4: return launch_fp_gemv<2, 1>(x, wq, y, M, N, K, group_size, x_stride, y_stride, s);
+  }
+  return SXB_ERR_UNSUPPORTED;
 }

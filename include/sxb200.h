@@ -389,6 +389,13 @@ int sxb_symm_subset_wsum2(const void* const* bufs, const void* const* sigs, int 
 /* SXB_ATTN_DEBUG=3 cycle accounting of the last dQ launch (8 x uint64, host pointer); see g_attn_prof. */
 int sxb_attn_prof(unsigned long long* out_host);
 
+/* ---- csrc/quantize.cu */
+/* Weight-only quantised linear for small batches: y[M, N] (bf16) = x[M, K] (bf16) W^T, W [N, K] in the layout written
+ * by sxb_fp_quantize (q_bits 4 / 6 / 8, groups of `group_size` along the flattened weight, K % group_size == 0,
+ * K % 256 == 0).  Intended for M <= 16 (decode); larger M should dequantise and use the tcgen05 GEMM. */
+int sxb_fp_gemv(const void* x, const void* wq, void* y, int M, int N, int K, int q_bits, int group_size,
+                long long x_stride, long long y_stride, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -110,8 +110,8 @@ class BlasLibLinear:
 
 class CUDAWf6Af16Linear:
     """W6A16 linear (reference ``cuda_linear/cuda_linear.py``: FP6-LLM kernel with 2+4-bit weight fragments).
-    Weights arrive FP6-quantised by ``ops.fp_quantizer`` (6 bits + group scales); they are expanded to bf16 and fed to
-    the tcgen05 GEMM."""
+    Weights arrive FP6-quantised by ``ops.fp_quantizer`` (6 bits + group scales).  Decode-sized inputs run the fused
+    weight-only GEMV (codes decoded in registers); larger inputs expand the weight to bf16 and use the tcgen05 GEMM."""
 
     def __init__(self, group_size: int = 512):
         from ....ops.fp_quantizer import FP_Quantize
@@ -121,6 +121,13 @@ class CUDAWf6Af16Linear:
         return self._q.quantize(weight.to(torch.bfloat16).contiguous(), q_bits=6, q_mantisa_bits=2)
 
     def __call__(self, output, hidden_states, weights_q, shape):
-        w = self._q.dequantize(weights_q, q_bits=6, q_mantisa_bits=2).view(shape).to(hidden_states.dtype)
-        y = F.linear(hidden_states, w)
+        from ....ops.fp_quantizer import fp_gemv, fp_gemv_ok
+        out_f, in_f = int(shape[0]), int(shape[1])
+        if fp_gemv_ok(hidden_states, out_f, in_f, self._q.group_size, 6):
+            # decode: the 6-bit codes are read once and decoded in registers (weight-bandwidth bound)
+            y = fp_gemv(hidden_states, weights_q, out_f, in_f, q_bits=6, group_size=self._q.group_size)
+        else:
+            # prefill: compute bound — expand to bf16 scratch, tcgen05 GEMM
+            w = self._q.dequantize(weights_q, q_bits=6, q_mantisa_bits=2).view(shape).to(hidden_states.dtype)
+            y = F.linear(hidden_states, w)
         return y if output is None else output.copy_(y)

@@ -14,6 +14,7 @@ from ...native import lib as _lib
 
 _lib.register({
     "sxb_fp_quantize": "pp" "l" "iii" "i" "i" "p",
+    "sxb_fp_gemv": "ppp" "iiiii" "ll" "p",
     "sxb_fp_dequantize": "pp" "l" "ii" "p" "l" "i" "p",
 })
 
@@ -88,6 +89,31 @@ def _unpack_cpu(raw: torch.Tensor, bits: int, gs: int) -> torch.Tensor:
             if s < e_:
                 code[:, :, i] |= ((r[:, :, b] >> (s - 8 * b)) & ((1 << (e_ - s)) - 1)) << (s - lo)
     return code.reshape(g, gs)
+
+
+GEMV_MAX_ROWS = 16
+
+
+def fp_gemv_ok(x: torch.Tensor, out_features: int, in_features: int, group_size: int, q_bits: int) -> bool:
+    """Whether :func:`fp_gemv` takes this problem (decode-sized batch, bf16 CUDA activations, aligned K)."""
+    rows = x.numel() // max(1, x.shape[-1])
+    return (x.is_cuda and x.dtype == torch.bfloat16 and rows <= GEMV_MAX_ROWS and q_bits in (4, 6, 8)
+            and in_features % 256 == 0 and in_features % group_size == 0 and x.shape[-1] == in_features)
+
+
+def fp_gemv(x: torch.Tensor, wq: torch.Tensor, out_features: int, in_features: int, q_bits: int = 6,
+            group_size: int = 512) -> torch.Tensor:
+    """``x @ W^T`` for a weight kept in :func:`fp_quantize`'s packed layout (``W`` is ``[out, in]``, quantised flat):
+    the packed codes are read once and decoded in registers (``csrc/quantize.cu: fp_gemv_kernel``).  For decode-sized
+    ``x`` (at most :data:`GEMV_MAX_ROWS` rows) this is bound by the packed weight bytes — 0.75 B per weight at 6 bits
+    instead of the 4.75 B of dequantise-to-scratch + GEMM."""
+    x2 = x.reshape(-1, in_features)
+    if not x2.is_contiguous():
+        x2 = x2.contiguous()
+    y = torch.empty(x2.shape[0], out_features, dtype=torch.bfloat16, device=x.device)
+    _lib.call("sxb_fp_gemv", x2.data_ptr(), wq.data_ptr(), y.data_ptr(), x2.shape[0], out_features, in_features,
+              int(q_bits), int(group_size), x2.stride(0), y.stride(0), _lib.stream_ptr())
+    return y.view(*x.shape[:-1], out_features)
 
 
 def fp_quantize(x: torch.Tensor, group_size: int = 512, q_bits: int = 8, stochastic: bool = False, seed: int = 0):

@@ -144,3 +144,38 @@ def test_ragged_ops_and_engine_match_cpu():
     for got, ref in ((out[0], ref_a), (out[1], ref_b)):
         assert torch.nn.functional.cosine_similarity(got, ref, dim=0) > 0.995
         assert got.argmax() == ref.argmax() or (got - ref).abs().max() < 0.1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("q_bits", [4, 6, 8])
+@pytest.mark.parametrize("rows", [1, 3, 8, 13])
+def test_weight_only_minifloat_gemv_matches_dequantised_matmul(q_bits, rows):
+    """Fused weight-only GEMV (codes decoded in registers) vs dequantise + fp32 matmul of the SAME quantised weight."""
+    import torch
+    from shuffle_exchange_b200.ops.fp_quantizer import fp_dequantize, fp_gemv, fp_gemv_ok, fp_quantize
+    torch.manual_seed(0)
+    N, K, gs = 1000, 1024, 512                      # N not a multiple of the rows-per-block
+    w = (torch.randn(N, K, device="cuda") * 0.1).to(torch.bfloat16)
+    x = torch.randn(rows, K, device="cuda", dtype=torch.bfloat16)
+    wq = fp_quantize(w, gs, q_bits)
+    assert fp_gemv_ok(x, N, K, gs, q_bits)
+    y = fp_gemv(x, wq, N, K, q_bits, gs)
+    wd = fp_dequantize(wq, gs, q_bits, dtype=torch.float32).view(N, K)
+    ref = x.float() @ wd.t()
+    err = ((y.float() - ref).norm() / ref.norm()).item()
+    assert err < 5e-3, err                          # bf16 rounding of the output only
+
+
+@pytest.mark.gpu
+def test_w6a16_linear_uses_gemv_for_decode_and_gemm_for_prefill():
+    import torch
+    from shuffle_exchange_b200.inference.v2.kernels.core_ops import CUDAWf6Af16Linear
+    torch.manual_seed(1)
+    lin = CUDAWf6Af16Linear(group_size=512)
+    w = (torch.randn(512, 1024, device="cuda") * 0.05).to(torch.bfloat16)
+    wq = lin.quantize(w)
+    for rows in (2, 64):
+        x = torch.randn(rows, 1024, device="cuda", dtype=torch.bfloat16)
+        y = lin(None, x, wq, (512, 1024))
+        ref = x.float() @ w.float().t()
+        assert ((y.float() - ref).norm() / ref.norm()).item() < 8e-2     # FP6 quantisation error of the weight
