@@ -49,6 +49,9 @@ def parse():
     ap.add_argument("--moe-fused", action="store_true",
                     help="Mixtral: symmetric-memory dispatch/combine + grouped expert GEMM (moe/fused_ep.py)")
     ap.add_argument("--fp8-experts", action="store_true", help="Mixtral: e4m3 expert GEMMs in forward")
+    ap.add_argument("--ep-capacity-factor", type=float, default=2.0,
+                    help="Mixtral fused exchange: receive-buffer rows per rank as a multiple of the balanced share (a "
+                         "random-init router is unbalanced: 1.25 overflowed at 8 GPUs; overflow raises, nothing is dropped)")
     ap.add_argument("--no-extras", action="store_true",
                     help="skip the secondary measurements (exposed communication, fused-path rooflines, the line at "
                          "the reference's recompute setting)")
@@ -198,7 +201,8 @@ def run_ours(args):
         # runtime/engine.py:1760).  The full 8x7B model needs >= 8 GPUs of 180 GB for training state.
         from shuffle_exchange_b200.models.mixtral import MixtralForCausalLM, mixtral_config
         cfg = mixtral_config(args.model, max_position_embeddings=max(args.seq, 8192), ep_size=world,
-                             fused_exchange=(False if args.moe_nccl else None), fp8_experts=args.fp8_experts)
+                             fused_exchange=(False if args.moe_nccl else None), fp8_experts=args.fp8_experts,
+                             ep_capacity_factor=args.ep_capacity_factor)
         if args.layers:
             cfg.num_hidden_layers = args.layers
         per_rank = cfg.num_parameters() - cfg.num_hidden_layers * (cfg.num_local_experts - cfg.num_local_experts // world) * 3 * cfg.hidden_size * cfg.intermediate_size

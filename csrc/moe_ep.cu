@@ -77,7 +77,7 @@ __device__ __forceinline__ bool wait_all(const Peers& P, int channel, uint32_t e
 // tables (device, int32): [0, E)            send_base: row in the owner's receive buffer where my tokens of expert e start
 //                         [E, E+L+1)        group_offsets of my local experts (aligned to 256)
 //                         [E+L+1, E+2L+1)   group_counts (real rows per local expert)
-//                         [E+2L+1]          overflow flag (1 = some receive buffer would exceed cap_rows)
+//                         [E+2L+1]          0, or the rows the fullest receive buffer would need (> cap_rows)
 struct PlanArgs {
   Peers P;
   const int* my_counts;   // [E] tokens of this rank per global expert (from the gating kernel)
@@ -127,7 +127,7 @@ __device__ __forceinline__ void plan_body(const PlanArgs& A) {
         goff[e] = off;
         off += (tot[e] + kAlign - 1) / kAlign * kAlign;
       }
-      if (off > A.cap_rows) overflow = 1;
+      if (off > A.cap_rows && off > overflow) overflow = off;   // rows the fullest rank would need
       if (d == P.rank) {
         for (int le = 0; le < L; ++le) {
           A.tables[E + le] = goff[d * L + le];

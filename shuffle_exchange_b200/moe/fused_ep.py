@@ -95,6 +95,7 @@ class FusedEP:
         self.sg = _LocalGroup(dev) if local else symm.SymmGroup.get(group)
         self.rank, self.world = self.sg.rank, self.sg.world
         self.E, self.L = num_experts, num_experts // self.world
+        self.capacity_factor = 1.0 if group is None else capacity_factor
         self.H, self.K = hidden, top_k
         rows = int(max_tokens * top_k * (1.0 if local else capacity_factor)) + self.L * GROUP_ALIGN_M
         self.cap_rows = (rows + GROUP_ALIGN_M - 1) // GROUP_ALIGN_M * GROUP_ALIGN_M
@@ -166,10 +167,12 @@ class FusedEP:
         if self.group is not None:
             # every rank must reach the same verdict, or the ranks that did not overflow wait forever for the one that raised
             torch.distributed.all_reduce(flags, op=torch.distributed.ReduceOp.MAX, group=self.group)
-        if int(flags.item()) != 0:
+        need = int(flags.item())
+        if need != 0:
             raise RuntimeError(
-                f"expert-parallel receive buffer overflow: routing sent more than {self.cap_rows} rows to one rank; "
-                "raise the MoE layer's ep_capacity_factor")
+                f"expert-parallel receive buffer overflow: routing sent {need} rows (with alignment) to one rank, the "
+                f"buffers hold {self.cap_rows}; raise the MoE layer's ep_capacity_factor to at least "
+                f"{need / max(1, self.cap_rows - self.L * GROUP_ALIGN_M) * self.capacity_factor:.2f}")
 
 
 class _Dispatch(torch.autograd.Function):

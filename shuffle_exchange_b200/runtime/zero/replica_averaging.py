@@ -193,8 +193,10 @@ class ReplicaAverager:
             return self._gossip_push(shards)
         for shard in shards:
             if self.method == "RR":
-                # on symmetric memory: the same one-shot kernel with every replica as a member
-                if not self._try_fused(shard, list(range(self.n_replicas))):
+                # A mean over ALL replicas of the fixed column group is a plain all-reduce: NCCL's in-switch (NVLS)
+                # algorithm beat the peer-load kernel on it (8 GPUs, 4 replicas x 512 MB: 1.47 vs 2.04 ms,
+                # profiles/replica_avg_bench_8gpu_r2.json), so the kernel serves RR only when asked for (fused=True).
+                if not (self.fused is True and self._try_fused(shard, list(range(self.n_replicas)))):
                     shard.div_(self.n_replicas)
                     dist.all_reduce(shard, group=self.column_pg)
             elif self.method == "H-RR":
