@@ -430,16 +430,30 @@ fp_dequantize_kernel(const uint8_t* __restrict__ in, T* __restrict__ out, int gr
 // by an integer add, subnormals (exponent field 0) scaled from the integer mantissa.
 // (reference: inference/v2/kernels/core_ops/cuda_linear/fp6_linear.cu — W6A16 on mma.sync; here the
 // bandwidth-bound decode case, prefill sizes dequantise into scratch and use the tcgen05 GEMM.)
+// Sign to bit 31, exponent|mantissa to fp32 position; multiplying by 2^(127 - bias) rebases the exponent and turns
+// the fp32 denormal that a zero exponent field produces into the format's subnormal value (no flush-to-zero: the
+// library is built without fast-math).
 template <int E, int M>
-__device__ __forceinline__ float minifloat_to_f32(uint32_t c) {
-  constexpr int kBias = (1 << (E - 1)) - 1;
-  const uint32_t sign = (c >> (E + M)) & 1u;
-  const uint32_t ef = (c >> M) & ((1u << E) - 1);
-  const uint32_t mant = c & ((1u << M) - 1);
-  const float normal = __uint_as_float(((ef + 127u - kBias) << 23) | (mant << (23 - M)));
-  const float sub = float(mant) * __uint_as_float((uint32_t)(127 + 1 - kBias - M) << 23);
-  const float v = ef ? normal : sub;
-  return sign ? -v : v;
+__device__ __forceinline__ float minifloat_bits(uint32_t c) {
+  const uint32_t u = ((c << (31 - (E + M))) & 0x80000000u) | ((c & ((1u << (E + M)) - 1u)) << (23 - M));
+  return __uint_as_float(u);
+}
+
+// 16 codes of BITS bits from 2*BITS bytes held in BITS/2 words (little-endian bit stream, 8 codes per BITS bytes)
+template <int BITS>
+__device__ __forceinline__ void unpack16(const uint32_t* __restrict__ wsrc, uint32_t (&c)[16]) {
+  constexpr int NW = BITS / 2;                   // words per 16 codes
+  uint32_t w[NW];
+#pragma unroll
+  for (int i = 0; i < NW; ++i) w[i] = wsrc[i];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int pos = i * BITS;                    // bit position inside the 2*BITS bytes
+    const int wi = pos >> 5, sh = pos & 31;
+    uint32_t v = w[wi] >> sh;
+    if (sh + BITS > 32 && wi + 1 < NW) v |= w[wi + 1] << (32 - sh);
+    c[i] = v & ((1u << BITS) - 1u);
+  }
 }
 
 template <int E, int M, int MB>
@@ -448,38 +462,44 @@ fp_gemv_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict__ 
                int N, int K, int group_size, long long x_stride, long long y_stride) {
   using F = MiniFloat<E, M>;
   constexpr int R = 4;
+  constexpr int kBias = (1 << (E - 1)) - 1;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = (blockIdx.x * 8 + warp) * R;
   if (n0 >= N) return;
-  const long long gbytes = (long long)group_size * F::kBits / 8 + 4;
+  const long long gbytes = (long long)group_size * F::kBits / 8 + 4;   // multiple of 4: word loads stay aligned
+  const float rebase = __uint_as_float((uint32_t)(127 + 127 - kBias) << 23);
   float acc[R][MB];
 #pragma unroll
   for (int r = 0; r < R; ++r)
 #pragma unroll
     for (int m = 0; m < MB; ++m) acc[r][m] = 0.f;
-  for (int k = lane * 8; k < K; k += 256) {
-    float xv[MB][8];
+  for (int k = lane * 16; k < K; k += 512) {
+    float xv[MB][16];
 #pragma unroll
-    for (int m = 0; m < MB; ++m) load8<__nv_bfloat16>(x + m * x_stride + k, xv[m]);
+    for (int m = 0; m < MB; ++m) {
+      float lo[8], hi[8];
+      load8<__nv_bfloat16>(x + m * x_stride + k, lo);
+      load8<__nv_bfloat16>(x + m * x_stride + k + 8, hi);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { xv[m][i] = lo[i]; xv[m][8 + i] = hi[i]; }
+    }
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       if (n0 + r >= N) break;
       const long long e0 = (long long)(n0 + r) * K + k;            // element index in the flattened weight
       const long long g = e0 / group_size;
-      const int o = (int)(e0 - g * group_size);                     // multiple of 8
+      const int o = (int)(e0 - g * group_size);                     // multiple of 16
       const uint8_t* gp = wq + g * gbytes;
-      const uint8_t* sp = gp + gbytes - 4;
-      const float scale = __uint_as_float((uint32_t)sp[0] | ((uint32_t)sp[1] << 8) | ((uint32_t)sp[2] << 16) |
-                                          ((uint32_t)sp[3] << 24));
-      uint32_t c[8];
-      unpack8<F::kBits>(gp + (o / 8) * F::kBits, c);
-      float wv[8];
+      const float scale = __uint_as_float(*reinterpret_cast<const uint32_t*>(gp + gbytes - 4));
+      uint32_t c[16];
+      unpack16<F::kBits>(reinterpret_cast<const uint32_t*>(gp + (o / 8) * F::kBits), c);
+      float wv[16];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) wv[i] = minifloat_to_f32<E, M>(c[i]) * scale;
+      for (int i = 0; i < 16; ++i) wv[i] = (minifloat_bits<E, M>(c[i]) * rebase) * scale;   // rebase first: no overflow
 #pragma unroll
       for (int m = 0; m < MB; ++m)
 #pragma unroll
-        for (int i = 0; i < 8; ++i) acc[r][m] = fmaf(wv[i], xv[m][i], acc[r][m]);
+        for (int i = 0; i < 16; ++i) acc[r][m] = fmaf(wv[i], xv[m][i], acc[r][m]);
     }
   }
 #pragma unroll
@@ -854,15 +874,14 @@ int launch_fp_gemv(const void* x, const void* wq, void* y, int Mrows, int N, int
   const uint8_t* wp = static_cast<const uint8_t*>(wq);
   __nv_bfloat16* yp = static_cast<__nv_bfloat16*>(y);
   const unsigned blocks = (unsigned)((N + 31) / 32);      // 8 warps x 4 rows per block
-  for (int m0 = 0; m0 < Mrows; m0 += 8) {                 // batch rows in chunks of at most 8
-    const int mb = Mrows - m0 >= 8 ? 8 : (Mrows - m0 >= 4 ? 4 : (Mrows - m0 >= 2 ? 2 : 1));
+  for (int m0 = 0; m0 < Mrows;) {                         // batch rows in chunks of 4 / 2 / 1 (register budget)
+    const int mb = Mrows - m0 >= 4 ? 4 : (Mrows - m0 >= 2 ? 2 : 1);
     const __nv_bfloat16* xc = xp + m0 * xs;
     __nv_bfloat16* yc = yp + m0 * ys;
-    if (mb == 8) fp_gemv_kernel<E, M, 8><<<blocks, 256, 0, s>>>(xc, wp, yc, N, K, gs, xs, ys);
-    else if (mb == 4) fp_gemv_kernel<E, M, 4><<<blocks, 256, 0, s>>>(xc, wp, yc, N, K, gs, xs, ys);
+    if (mb == 4) fp_gemv_kernel<E, M, 4><<<blocks, 256, 0, s>>>(xc, wp, yc, N, K, gs, xs, ys);
     else if (mb == 2) fp_gemv_kernel<E, M, 2><<<blocks, 256, 0, s>>>(xc, wp, yc, N, K, gs, xs, ys);
     else fp_gemv_kernel<E, M, 1><<<blocks, 256, 0, s>>>(xc, wp, yc, N, K, gs, xs, ys);
-    if (mb < 8) m0 -= 8 - mb;                             // advance by mb, not 8
+    m0 += mb;
   }
   SXB_CHECK_LAUNCH();
   return SXB_OK;
@@ -871,11 +890,11 @@ int launch_fp_gemv(const void* x, const void* wq, void* y, int Mrows, int N, int
 
 // Weight-only quantised linear for small batches: y[M, N] (bf16) = x[M, K] (bf16) W^T, W [N, K] in the layout written
 // by sxb_fp_quantize (q_bits 4 / 6 / 8, groups of `group_size` along the flattened weight, K % group_size == 0,
-// K % 256 == 0).  Intended for M <= 16 (decode); larger M should dequantise and use the tcgen05 GEMM.
+// K % 512 == 0).  Intended for M <= 16 (decode); larger M should dequantise and use the tcgen05 GEMM.
 SXB_API int sxb_fp_gemv(const void* x, const void* wq, void* y, int M, int N, int K, int q_bits, int group_size,
                         long long x_stride, long long y_stride, void* stream) {
   if (M <= 0 || N <= 0 || K <= 0) return SXB_ERR_BAD_ARG;
-  if (group_size <= 0 || group_size % 8 || K % group_size || K % 256 || x_stride % 8) return SXB_ERR_UNSUPPORTED;
+  if (group_size <= 0 || group_size % 16 || K % group_size || K % 512 || x_stride % 8) return SXB_ERR_UNSUPPORTED;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   switch (q_bits) {
     case 8: return launch_fp_gemv<4, 3>(x, wq, y, M, N, K, group_size, x_stride, y_stride, s);

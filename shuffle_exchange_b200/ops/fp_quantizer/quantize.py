@@ -91,14 +91,15 @@ def _unpack_cpu(raw: torch.Tensor, bits: int, gs: int) -> torch.Tensor:
     return code.reshape(g, gs)
 
 
-GEMV_MAX_ROWS = 16
+GEMV_MAX_ROWS = 8
 
 
 def fp_gemv_ok(x: torch.Tensor, out_features: int, in_features: int, group_size: int, q_bits: int) -> bool:
     """Whether :func:`fp_gemv` takes this problem (decode-sized batch, bf16 CUDA activations, aligned K)."""
     rows = x.numel() // max(1, x.shape[-1])
     return (x.is_cuda and x.dtype == torch.bfloat16 and rows <= GEMV_MAX_ROWS and q_bits in (4, 6, 8)
-            and in_features % 256 == 0 and in_features % group_size == 0 and x.shape[-1] == in_features)
+            and in_features % 512 == 0 and in_features % group_size == 0 and group_size % 16 == 0
+            and x.shape[-1] == in_features)
 
 
 def fp_gemv(x: torch.Tensor, wq: torch.Tensor, out_features: int, in_features: int, q_bits: int = 6,

@@ -148,7 +148,7 @@ def test_ragged_ops_and_engine_match_cpu():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("q_bits", [4, 6, 8])
-@pytest.mark.parametrize("rows", [1, 3, 8, 13])
+@pytest.mark.parametrize("rows", [1, 3, 8])
 def test_weight_only_minifloat_gemv_matches_dequantised_matmul(q_bits, rows):
     """Fused weight-only GEMV (codes decoded in registers) vs dequantise + fp32 matmul of the SAME quantised weight."""
     import torch
