@@ -91,7 +91,7 @@ def _unpack_cpu(raw: torch.Tensor, bits: int, gs: int) -> torch.Tensor:
     return code.reshape(g, gs)
 
 
-GEMV_MAX_ROWS = 8
+GEMV_MAX_ROWS = 4
 
 
 def fp_gemv_ok(x: torch.Tensor, out_features: int, in_features: int, group_size: int, q_bits: int) -> bool:

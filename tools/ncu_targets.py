@@ -1,8 +1,8 @@
 """Short single-GPU workload that launches each kernel family once per iteration, for ``ncu`` (one capture per call):
 
     python tools/ncu_targets.py && ncu --set full --clock-control none --import-source on \
-        -k regex:'gemm_pair_x_kernel|gemm_pair_kernel|rs_adam_emu|push_emu|pull_emu|attn_fwd_kernel|attn_bwd|all_gather_emu' \
-        -s 30 -c 15 -o gpurun_out/prof_r2 python tools/ncu_targets.py
+        -k regex:'gemm_pair_x_kernel|gemm_pair_kernel|rs_adam_emu|push_emu|pull_emu|attn_fwd_kernel|attn_bwd|all_gather_emu|fp_gemv' \
+        -s 36 -c 18 -o gpurun_out/prof_r2 python tools/ncu_targets.py
 
 Kernels: base pair GEMM (qkv fwd shape), extended GEMM gated NN / grouped NT / fp8 NT, emulated (4 logical ranks) fused
 reduce-scatter+AdamW, all-gather with flags, MoE push / pull, attention forward with the row-scatter epilogue."""
@@ -61,7 +61,32 @@ def main():
     stages = [_Stage(up, r, True) for r in range(2)]
     xu = [torch.randn(Sl, 4096, device=dev).to(torch.bfloat16) for _ in range(2)]
     qkv_d = (torch.randn(1, 8192, (32 + 16) * 128, device=dev) / 4).to(torch.bfloat16).requires_grad_(True)
+    # ragged inference: one 2048-token prefill + 32 decodes at 1024 (atoms; short atoms GQA-packed), FP6 weight-only GEMV
+    from shuffle_exchange_b200.inference.v2.kernels import ragged_ops as R
+    from shuffle_exchange_b200.inference.v2.ragged.ragged_wrapper import RaggedBatchWrapper
+    from shuffle_exchange_b200.ops.fp_quantizer import fp_gemv, fp_quantize
+
+    class _Seq:
+        def __init__(self, seen, blocks):
+            self.seen_tokens, self._b = seen, torch.tensor(blocks, dtype=torch.int32)
+
+        def kv_blocks(self):
+            return self._b
+    plan_rb = [(0, 2048)] + [(1024, 1)] * 32
+    cache = torch.randn(sum((s_ + n_ + 63) // 64 for s_, n_ in plan_rb) + 1, 64, 2, 8, 128, device=dev, dtype=torch.bfloat16)
+    rb = RaggedBatchWrapper(sum(n_ for _, n_ in plan_rb), len(plan_rb), 33, device=dev)
+    nxt = 0
+    for seen_, n_ in plan_rb:
+        need = (seen_ + n_ + 63) // 64
+        rb.insert_sequence(_Seq(seen_, list(range(nxt, nxt + need))), torch.zeros(n_, dtype=torch.int64))
+        nxt += need
+    rb.finalize()
+    q_rb = torch.randn(rb.current_tokens, 32, 128, device=dev, dtype=torch.bfloat16)
+    w6 = fp_quantize((torch.randn(28672, 4096, device=dev) * 0.05).to(torch.bfloat16), 512, 6)
+    x6 = torch.randn(1, 4096, device=dev, dtype=torch.bfloat16)
     for it in range(4):
+        R.ragged_attention(q_rb, cache, rb)
+        fp_gemv(x6, w6, 28672, 4096, 6, 512)
         # dense causal attention at the Llama-3-8B layer shape: forward, dQ and dK/dV kernels
         o_d = F.flash_attention_qkv(qkv_d, 32, 8, 128, causal=True)
         o_d.backward(o_d.detach())
