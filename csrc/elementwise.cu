@@ -101,74 +101,52 @@ __device__ __forceinline__ float act_bwd(float x, int act) {
 }
 
 // out[T,F] = act(in[:, :F] (+bias)) * (in[:, F:] (+bias))       (concatenated gate|up layout)
-// Grid: x over 8-element column vectors, y over row groups; a thread keeps its column and walks rows two at a time
-// (four / six independent 16-byte loads in flight).  The earlier flat grid-stride form spent a 64-bit division and
-// modulo per vector and ran at 57 % of HBM bandwidth (0.18 / 0.29 ms for the 8192 x 14336 SwiGLU of Llama-3-8B).
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
 gated_fwd_kernel(const T* __restrict__ in, const T* __restrict__ bias, T* __restrict__ out,
                  long long rows, int F, int act) {
-  const int c = (blockIdx.x * kThreads + threadIdx.x) * 8;
-  if (c >= F) return;
-  float bg[8], bu[8];
-  if (bias) { ld8<T>(bias + c, bg); ld8<T>(bias + F + c, bu); }
-  const long long step = gridDim.y;
-  for (long long r = blockIdx.y; r < rows; r += 2 * step) {
-    const long long r1 = r + step;
-    const bool two = r1 < rows;
-    float g0[8], u0[8], g1[8], u1[8], o[8];
-    ld8<T>(in + r * 2 * F + c, g0);
-    ld8<T>(in + r * 2 * F + F + c, u0);
-    if (two) { ld8<T>(in + r1 * 2 * F + c, g1); ld8<T>(in + r1 * 2 * F + F + c, u1); }
+  const int vpr = F >> 3;
+  const long long total = rows * vpr;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / vpr;
+    const int c = (int)(i % vpr) * 8;
+    float g[8], u[8], o[8];
+    ld8<T>(in + r * 2 * F + c, g);
+    ld8<T>(in + r * 2 * F + F + c, u);
     if (bias) {
+      float bg[8], bu[8];
+      ld8<T>(bias + c, bg);
+      ld8<T>(bias + F + c, bu);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) { g0[k] += bg[k]; u0[k] += bu[k]; g1[k] += bg[k]; u1[k] += bu[k]; }
+      for (int k = 0; k < 8; ++k) { g[k] += bg[k]; u[k] += bu[k]; }
     }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) o[k] = act_fwd(g0[k], act) * u0[k];
+    for (int k = 0; k < 8; ++k) o[k] = act_fwd(g[k], act) * u[k];
     st8<T>(out + r * F + c, o);
-    if (two) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) o[k] = act_fwd(g1[k], act) * u1[k];
-      st8<T>(out + r1 * F + c, o);
-    }
   }
 }
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
 gated_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ in, T* __restrict__ din,
                  long long rows, int F, int act) {
-  const int c = (blockIdx.x * kThreads + threadIdx.x) * 8;
-  if (c >= F) return;
-  const long long step = gridDim.y;
-  for (long long r = blockIdx.y; r < rows; r += 2 * step) {
-    const long long r1 = r + step;
-    const bool two = r1 < rows;
-    float g0[8], u0[8], d0[8], g1[8], u1[8], d1[8], dg[8], du[8];
-    ld8<T>(in + r * 2 * F + c, g0);
-    ld8<T>(in + r * 2 * F + F + c, u0);
-    ld8<T>(dy + r * F + c, d0);
-    if (two) {
-      ld8<T>(in + r1 * 2 * F + c, g1);
-      ld8<T>(in + r1 * 2 * F + F + c, u1);
-      ld8<T>(dy + r1 * F + c, d1);
-    }
+  const int vpr = F >> 3;
+  const long long total = rows * vpr;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / vpr;
+    const int c = (int)(i % vpr) * 8;
+    float g[8], u[8], d[8], dg[8], du[8];
+    ld8<T>(in + r * 2 * F + c, g);
+    ld8<T>(in + r * 2 * F + F + c, u);
+    ld8<T>(dy + r * F + c, d);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      dg[k] = d0[k] * u0[k] * act_bwd(g0[k], act);
-      du[k] = d0[k] * act_fwd(g0[k], act);
+      dg[k] = d[k] * u[k] * act_bwd(g[k], act);
+      du[k] = d[k] * act_fwd(g[k], act);
     }
     st8<T>(din + r * 2 * F + c, dg);
     st8<T>(din + r * 2 * F + F + c, du);
-    if (two) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        dg[k] = d1[k] * u1[k] * act_bwd(g1[k], act);
-        du[k] = d1[k] * act_fwd(g1[k], act);
-      }
-      st8<T>(din + r1 * 2 * F + c, dg);
-      st8<T>(din + r1 * 2 * F + F + c, du);
-    }
   }
 }
 // y = act(x + bias)  (in place allowed)
@@ -338,15 +316,6 @@ scale_cast_kernel(const TS* __restrict__ src, TD* __restrict__ dst, long long n,
   }
 }
 
-// columns x row groups for the gated kernels: ~16 CTAs per SM in total, never more row groups than half the rows
-static inline dim3 gated_grid(long long rows, int F) {
-  const unsigned gx = (unsigned)((F / 8 + kThreads - 1) / kThreads);
-  long long gy = (148LL * 16 + gx - 1) / gx;
-  if (gy > (rows + 1) / 2) gy = (rows + 1) / 2;
-  if (gy < 1) gy = 1;
-  if (gy > 65535) gy = 65535;
-  return dim3(gx, (unsigned)gy, 1);
-}
 static inline int grid_for(long long work) {
   long long b = (work + kThreads - 1) / kThreads;
   if (b < 1) b = 1;
@@ -388,8 +357,7 @@ SXB_API int sxb_gated_act_fwd(const void* in, const void* bias, void* out, long 
   if (rows <= 0) return SXB_OK;
   if (F % 8) return SXB_ERR_UNSUPPORTED;
   cudaStream_t s = (cudaStream_t)stream;
-  const dim3 grid = gated_grid(rows, F);
-  DISPATCH_16(dtype, (gated_fwd_kernel<T><<<grid, kThreads, 0, s>>>(
+  DISPATCH_16(dtype, (gated_fwd_kernel<T><<<grid_for(rows * (F / 8)), kThreads, 0, s>>>(
                          (const T*)in, (const T*)bias, (T*)out, rows, F, act)));
   SXB_CHECK_LAUNCH();
   return SXB_OK;
@@ -399,8 +367,7 @@ SXB_API int sxb_gated_act_bwd(const void* dy, const void* in, void* din, long lo
   if (rows <= 0) return SXB_OK;
   if (F % 8) return SXB_ERR_UNSUPPORTED;
   cudaStream_t s = (cudaStream_t)stream;
-  const dim3 grid = gated_grid(rows, F);
-  DISPATCH_16(dtype, (gated_bwd_kernel<T><<<grid, kThreads, 0, s>>>(
+  DISPATCH_16(dtype, (gated_bwd_kernel<T><<<grid_for(rows * (F / 8)), kThreads, 0, s>>>(
                          (const T*)dy, (const T*)in, (T*)din, rows, F, act)));
   SXB_CHECK_LAUNCH();
   return SXB_OK;
