@@ -54,6 +54,10 @@ struct Params {
   const int* atoms;
   const int* block_tables;   // [n_seqs, max_blocks]
   int max_blocks, block_size;
+  // Additive bias per (batch, key) in RAW-score units (the host divides the caller's bias by the softmax scale), e.g.
+  // a key-padding mask with -inf on padded keys: fp32 [B, S] (dense batches only).  Added to S before the maximum, so
+  // softmax, lse and the backward recomputation all see score * scale + bias.
+  const float* kbias;
   // pack > 1 (atoms of at most 128 / pack queries, e.g. decode): the `pack` q heads that share one KV head are packed
   // into the tile's rows (row r = query r / pack, head hk * pack + r % pack), one CTA per KV head: K/V are read once
   // per KV head instead of once per q head.
@@ -389,6 +393,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       float s[64];
       ld_row64(tS + (j & 1) * BC + lane_off, s);
       const int k0 = j * BC;
+      if (p.kbias != nullptr) {
+        const float4* kb = reinterpret_cast<const float4*>(p.kbias + (long long)b * p.S + k0);   // warp-uniform
+        const int nv = min(16, (p.S - k0 + 3) >> 2);
+#pragma unroll
+        for (int c4 = 0; c4 < 16; ++c4) {
+          if (c4 < nv) {
+            const float4 t = __ldg(kb + c4);
+            s[c4 * 4 + 0] += t.x; s[c4 * 4 + 1] += t.y; s[c4 * 4 + 2] += t.z; s[c4 * 4 + 3] += t.w;
+          }
+        }
+      }
       const bool need_mask = (p.causal && (k0 + BC - 1 > q_pos0)) || (k0 + BC > kv_len);
       // row max on raw scores (scale > 0 commutes with max); 4 independent chains
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -1433,6 +1448,17 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         for (int c = 0; c < 32; ++c) { s[c] = 0.f; dp[c] = 0.f; }
       }
       const int k0 = j * BC + half * 32;
+      if (p.kbias != nullptr) {
+        const float4* kb = reinterpret_cast<const float4*>(p.kbias + (long long)b * p.S + k0);
+        const int nv = min(8, (S_ - k0 + 3) >> 2);
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) {
+          if (c4 < nv) {
+            const float4 t = __ldg(kb + c4);
+            s[c4 * 4 + 0] += t.x; s[c4 * 4 + 1] += t.y; s[c4 * 4 + 2] += t.z; s[c4 * 4 + 3] += t.w;
+          }
+        }
+      }
       const bool need_mask = (p.causal && (k0 + 31 > q0)) || (k0 + 32 > S_) || (q0 + BQ > S_);
       if (p.debug == 1 || p.debug == 2) {
         // profiling aid (SXB_ATTN_DEBUG): no exponentials, results are meaningless
@@ -1699,6 +1725,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
     const int kpos = n0 + row;
     const float sc = p.scale * kLog2e;
+    // additive key bias of this thread's key (raw-score units -> log2 domain); 0 without one
+    const float kb2 = (p.kbias != nullptr && kpos < S_) ? p.kbias[(long long)b * p.S + kpos] * sc : 0.f;
     const uint32_t stat_u = smem_u32(smem + L::oStat) + half * 128;   // this warp's 32 of the 64 queries
     int st = 0, qrel = 0;
     uint32_t ph = 0;
@@ -1721,10 +1749,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
         for (int c4 = 0; c4 < 8; ++c4) {
           const float4 nl = lds128(sstat + c4 * 16);          // -lse * log2e, warp-broadcast
-          s[c4 * 4 + 0] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 0]), sc, nl.x));
-          s[c4 * 4 + 1] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 1]), sc, nl.y));
-          s[c4 * 4 + 2] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 2]), sc, nl.z));
-          s[c4 * 4 + 3] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 3]), sc, nl.w));
+          s[c4 * 4 + 0] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 0]), sc, nl.x + kb2));
+          s[c4 * 4 + 1] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 1]), sc, nl.y + kb2));
+          s[c4 * 4 + 2] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 2]), sc, nl.z + kb2));
+          s[c4 * 4 + 3] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 3]), sc, nl.w + kb2));
         }
       }
       if (need_mask) {
@@ -1943,6 +1971,7 @@ struct VarlenCfg {
   int nseq = 0, max_len = 0;
 };
 thread_local VarlenCfg g_varlen;
+thread_local const float* g_kbias = nullptr;   // set by the *_kbias entry points for the launches they make
 // grid over (heads, sequences, tiles of the longest sequence)
 dim3 attn_grid(int heads, int B, int S) {
   if (g_varlen.cu != nullptr) return dim3(heads, g_varlen.nseq, (g_varlen.max_len + sxb::attn::BQ - 1) / sxb::attn::BQ);
@@ -1967,7 +1996,7 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
     return SXB_ERR_UNSUPPORTED;
   CUtensorMap tq, tk, tv;
   int rc;
-  const bool wide = use_fwd128(D);       // 128-key blocks (attn_fwd128_kernel)
+  const bool wide = use_fwd128(D) && g_kbias == nullptr;       // 128-key blocks (attn_fwd128_kernel); no key bias there
   const int kv_rows = wide ? FBC : BC;
   if ((rc = make_qkv_map(&tq, q, B, S, Hq, D, q_stride, BQ))) return rc;
   if ((rc = make_qkv_map(&tk, k, B, S, Hk, D, k_stride, kv_rows))) return rc;
@@ -1976,6 +2005,7 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
   p.cu_seqlens = g_varlen.cu;
+  p.kbias = g_kbias;
   {
     static const int dbg = [] { const char* e = getenv("SXB_ATTN_DEBUG"); return e ? atoi(e) : 0; }();
     p.debug = dbg;
@@ -2041,6 +2071,7 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.lse = (float*)const_cast<void*>(lse); p.delta = (const float*)delta;
   p.cu_seqlens = g_varlen.cu;
+  p.kbias = g_kbias;
   {
     static int dbg = -1;
     if (dbg < 0) { const char* e = getenv("SXB_ATTN_DEBUG"); dbg = e ? atoi(e) : 0; }
@@ -2270,4 +2301,32 @@ SXB_API int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, cons
   }
   SXB_CHECK_LAUNCH();
   return SXB_OK;
+}
+
+// Dense attention with an additive per-key bias (key-padding masks of BERT-style encoders and the v1 inference path;
+// reference: the attn_mask argument of the fused softmax in csrc/transformer/softmax_kernels.cu and
+// ops/transformer/inference softmax_context).  key_bias: fp32 [B, S] in RAW-score units, i.e. the caller's additive
+// bias divided by `scale`; -inf masks a key.  S must be a multiple of 4 (16-byte loads of the bias).
+SXB_API int sxb_attn_fwd_kbias(const void* q, const void* k, const void* v, void* out, void* lse, const void* key_bias,
+                               int B, int S, int Hq, int Hk, int D, long long q_stride, long long k_stride,
+                               long long v_stride, long long o_stride, int causal, float scale, void* stream) {
+  if (key_bias == nullptr || (S % 4) || (reinterpret_cast<uintptr_t>(key_bias) & 15)) return SXB_ERR_UNSUPPORTED;
+  g_kbias = static_cast<const float*>(key_bias);
+  const int rc = sxb_attn_fwd(q, k, v, out, lse, B, S, Hq, Hk, D, q_stride, k_stride, v_stride, o_stride, causal, scale,
+                              stream);
+  g_kbias = nullptr;
+  return rc;
+}
+
+SXB_API int sxb_attn_bwd_kbias(const void* q, const void* k, const void* v, const void* out, const void* d_out,
+                               const void* lse, void* delta, void* dq, void* dk, void* dv, const void* key_bias, int B,
+                               int S, int Hq, int Hk, int D, long long q_stride, long long k_stride, long long v_stride,
+                               long long o_stride, long long do_stride, long long dq_stride, long long dk_stride,
+                               long long dv_stride, int causal, float scale, void* stream) {
+  if (key_bias == nullptr || (S % 4) || (reinterpret_cast<uintptr_t>(key_bias) & 15)) return SXB_ERR_UNSUPPORTED;
+  g_kbias = static_cast<const float*>(key_bias);
+  const int rc = sxb_attn_bwd(q, k, v, out, d_out, lse, delta, dq, dk, dv, B, S, Hq, Hk, D, q_stride, k_stride,
+                              v_stride, o_stride, do_stride, dq_stride, dk_stride, dv_stride, causal, scale, stream);
+  g_kbias = nullptr;
+  return rc;
 }

@@ -218,8 +218,14 @@ class SoftmaxContextOp(BaseOp):
         causal = c.triangular_masking and not no_masking
         plain = attn_mask is None and alibi is None and past == 0 and q.is_cuda and q.dtype == torch.bfloat16 \
             and D in (64, 128)
+        key_mask = None
+        if attn_mask is not None and alibi is None and past == 0 and attn_mask.numel() == B * S \
+                and attn_mask.shape[0] == B and attn_mask.shape[-1] == S and F.key_bias_supported(q, attn_mask.reshape(B, S)):
+            key_mask = attn_mask.reshape(B, S)        # additive key-padding mask: handled inside the flash kernels
         if plain:
             ctx = F.flash_attention(q, k, v, causal=causal, scale=scale)
+        elif key_mask is not None:
+            ctx = F.flash_attention_key_bias(q, k, v, key_mask, causal=causal, scale=scale)
         else:
             qh = q.permute(0, 2, 1, 3)
             kh = k.permute(0, 2, 1, 3).repeat_interleave(heads // Hkv, dim=1)

@@ -96,6 +96,10 @@ def _attention(layer: "DeepSpeedTransformerLayer", qkv: torch.Tensor, mask: Opti
     flash_ok = (mask is None and p_attn <= 0 and qkv.is_cuda and qkv.dtype == torch.bfloat16 and Dh in (64, 128))
     if flash_ok:
         return F.flash_attention(q, k, v, causal=False).reshape(B, S, H * Dh)
+    # additive key-padding mask ([B, S], [B, 1, S] or [B, 1, 1, S]): the flash kernels add it to the scores
+    if mask is not None and p_attn <= 0 and mask.numel() == B * S and mask.shape[0] == B and mask.shape[-1] == S \
+            and F.key_bias_supported(q, mask.reshape(B, S)):
+        return F.flash_attention_key_bias(q, k, v, mask.reshape(B, S), causal=False).reshape(B, S, H * Dh)
     # scores materialised: batched GEMM (library) + one fused mask/scale/softmax pass (+ fused dropout)
     qh, kh, vh = (t.permute(0, 2, 1, 3) for t in (q, k, v))
     scores = torch.matmul(qh, kh.transpose(-1, -2))

@@ -193,3 +193,60 @@ def test_forward_kernel_variants(mode):
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     worst = float(r.stdout.strip().split("WORST")[-1])
     assert worst < 1e-2, worst
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,S,Hq,Hk,D,causal", [(2, 256, 4, 2, 128, False), (3, 300, 2, 2, 64, False), (2, 512, 4, 1, 128, True)])
+def test_key_bias_attention_forward_backward(B, S, Hq, Hk, D, causal):
+    """Additive per-key bias (key-padding mask with -inf / -1e4 entries) inside the flash kernels vs fp32 softmax."""
+    from shuffle_exchange_b200.ops import functional as F
+    torch.manual_seed(5)
+    dev = "cuda"
+    q, k, v = (torch.randn(B, S, h, D, device=dev, dtype=torch.bfloat16, requires_grad=True) for h in (Hq, Hk, Hk))
+    bias = torch.zeros(B, S, device=dev)
+    for b_ in range(B):                                   # a different padded tail per sample, never the whole row
+        bias[b_, S - 17 * (b_ + 1):] = float("-inf") if b_ % 2 == 0 else -1e4
+    bias[:, 5] = 0.7                                       # and a finite bias somewhere
+    assert F.key_bias_supported(q, bias)
+    out = F.flash_attention_key_bias(q, k, v, bias, causal=causal)
+    g = torch.randn_like(out)
+    out.backward(g)
+    ref_in = [t.detach().float().requires_grad_(True) for t in (q, k, v)]
+    qf = ref_in[0].permute(0, 2, 1, 3)
+    kf = ref_in[1].permute(0, 2, 1, 3).repeat_interleave(Hq // Hk, dim=1)
+    vf = ref_in[2].permute(0, 2, 1, 3).repeat_interleave(Hq // Hk, dim=1)
+    sc = qf @ kf.transpose(-1, -2) * D ** -0.5 + bias[:, None, None, :]
+    if causal:
+        sc = sc.masked_fill(~torch.ones(S, S, dtype=torch.bool, device=dev).tril(), float("-inf"))
+    ref = (sc.softmax(-1) @ vf).permute(0, 2, 1, 3)
+    ref.backward(g.float())
+    assert _rel_err(out, ref) < 1e-2
+    for got, want in zip((q, k, v), ref_in):
+        assert torch.isfinite(got.grad).all()
+        assert _rel_err(got.grad, want.grad) < 3e-2
+    # masked keys receive no gradient through the scores: dK of a -inf key is exactly zero
+    assert float(k.grad[0, S - 1].abs().max()) == 0.0
+
+
+@pytest.mark.gpu
+def test_training_transformer_layer_uses_flash_kernels_for_padding_masks():
+    from shuffle_exchange_b200.native import lib
+    from shuffle_exchange_b200.ops import functional as F
+    from shuffle_exchange_b200.ops.transformer import transformer as T
+    torch.manual_seed(6)
+    B, S, H, Dh = 2, 128, 4, 64
+
+    class _Cfg:
+        heads, hidden_size, attn_dropout_ratio = H, H * Dh, 0.0
+
+    class _Layer:
+        config, training = _Cfg, False
+    qkv = torch.randn(B, S, 3 * H * Dh, device="cuda", dtype=torch.bfloat16)
+    mask = torch.zeros(B, 1, 1, S, device="cuda")
+    mask[1, ..., 100:] = -1e4
+    before = lib.launch_count
+    got = T._attention(_Layer, qkv, mask)
+    assert lib.launch_count > before                      # went through the native library, not torch.matmul
+    q, k, v = qkv.view(B, S, 3, H, Dh).unbind(2)
+    want = F.flash_attention_key_bias(q.float().cpu(), k.float().cpu(), v.float().cpu(), mask.reshape(B, S).cpu())
+    assert _rel_err(got.cpu().view(B, S, H, Dh), want) < 1e-2
