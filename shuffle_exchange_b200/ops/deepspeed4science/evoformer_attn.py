@@ -4,8 +4,9 @@ Reference: ``deepspeed/ops/deepspeed4science/evoformer_attn.py:15-106`` — ``DS
 with ``Q/K/V [B, N, L, H, D]``, ``bias1 [B, N, 1, 1, L]`` (sequence mask) and ``bias2 [B, 1, H, L, L]`` (pair bias), both
 optional, gradients for both biases.  The reference calls a CUTLASS kernel that is not in its tree.
 
-B200 path: without biases the rows go straight through the tcgen05 flash-attention kernel (``[B*N]`` as batch); with
-biases the ``L x L`` scores of the (short, L <= a few thousand) MSA rows are produced by one batched tensor-core GEMM and
+B200 path: without biases the rows go straight through the tcgen05 flash-attention kernel (``[B*N]`` as batch); a
+sequence mask alone (``bias1`` that needs no gradient) rides along as the kernels' additive per-key bias; with a pair
+bias the ``L x L`` scores of the (short, L <= a few thousand) MSA rows are produced by one batched tensor-core GEMM and
 the bias add + scale + softmax (forward) / softmax gradient + bias gradients (backward) run in a single fused kernel each
 (``csrc/softmax_dropout.cu``), both biases read through broadcast strides — never expanded in memory.
 """
@@ -27,6 +28,13 @@ def _evoformer_core(q, k, v, bias1, bias2):
     if bias1 is None and bias2 is None and q.is_cuda and q.dtype == torch.bfloat16 and D in (64, 128):
         out = F.flash_attention(q.reshape(B * N, L, H, D), k.reshape(B * N, L, H, D), v.reshape(B * N, L, H, D),
                                 causal=False, scale=scale)
+        return out.view(B, N, L, H, D)
+    # mask only (no pair bias) and no gradient wanted for the mask: it is a per-key bias of the [B*N] rows, which the
+    # flash kernels add to the scores themselves (forward and backward)
+    if bias2 is None and bias1 is not None and not bias1.requires_grad \
+            and F.key_bias_supported(q.reshape(B * N, L, H, D), bias1.reshape(B * N, L)):
+        out = F.flash_attention_key_bias(q.reshape(B * N, L, H, D), k.reshape(B * N, L, H, D),
+                                         v.reshape(B * N, L, H, D), bias1.reshape(B * N, L), causal=False, scale=scale)
         return out.view(B, N, L, H, D)
     outs = []
     for b in range(B):   # the pair bias is shared by the N rows of one batch element: one fused call per element

@@ -140,6 +140,22 @@ def test_evoformer_gpu_matches_cpu():
     out2 = DS4Sci_EvoformerAttention(q2.to(dev, torch.bfloat16), k2.to(dev, torch.bfloat16),
                                      v2.to(dev, torch.bfloat16), [])
     assert (out2.float().cpu() - ref2).abs().max() < 3e-2
+    # sequence mask only (no gradient wanted for it), D = 64: rides along as the flash kernels' per-key bias
+    from shuffle_exchange_b200.native import lib
+    m = torch.zeros(1, 2, 1, 1, 128)
+    m[0, 1, 0, 0, 100:] = -1e9
+    qc, kc, vc = (t.clone().requires_grad_(True) for t in (q2, k2, v2))
+    ref3 = DS4Sci_EvoformerAttention(qc, kc, vc, [m])
+    g3 = torch.randn_like(ref3)
+    ref3.backward(g3)
+    qg, kg, vg = (t.to(dev, torch.bfloat16).requires_grad_(True) for t in (q2, k2, v2))
+    before = lib.launch_count
+    out3 = DS4Sci_EvoformerAttention(qg, kg, vg, [m.to(dev)])
+    out3.backward(g3.to(dev, torch.bfloat16))
+    assert lib.launch_count >= before + 3
+    assert (out3.float().cpu() - ref3).abs().max() < 3e-2
+    for a, b in ((qg, qc), (kg, kc), (vg, vc)):
+        assert (a.grad.float().cpu() - b.grad).abs().max() < 0.05 * b.grad.abs().max().item() + 0.02
 
 
 @pytest.mark.parametrize("masked", [False, True])
