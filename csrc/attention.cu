@@ -58,6 +58,7 @@ struct Params {
   // a key-padding mask with -inf on padded keys: fp32 [B, S] (dense batches only).  Added to S before the maximum, so
   // softmax, lse and the backward recomputation all see score * scale + bias.
   const float* kbias;
+  long long kbias_bstride, kbias_hstride;   // element strides over batch and q head (0: the same bias for every head)
   // pack > 1 (atoms of at most 128 / pack queries, e.g. decode): the `pack` q heads that share one KV head are packed
   // into the tile's rows (row r = query r / pack, head hk * pack + r % pack), one CTA per KV head: K/V are read once
   // per KV head instead of once per q head.
@@ -394,7 +395,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       ld_row64(tS + (j & 1) * BC + lane_off, s);
       const int k0 = j * BC;
       if (p.kbias != nullptr) {
-        const float4* kb = reinterpret_cast<const float4*>(p.kbias + (long long)b * p.S + k0);   // warp-uniform
+        const float4* kb = reinterpret_cast<const float4*>(p.kbias + b * p.kbias_bstride + h * p.kbias_hstride + k0);   // warp-uniform
         const int nv = min(16, (p.S - k0 + 3) >> 2);
 #pragma unroll
         for (int c4 = 0; c4 < 16; ++c4) {
@@ -1449,7 +1450,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
       const int k0 = j * BC + half * 32;
       if (p.kbias != nullptr) {
-        const float4* kb = reinterpret_cast<const float4*>(p.kbias + (long long)b * p.S + k0);
+        const float4* kb = reinterpret_cast<const float4*>(p.kbias + b * p.kbias_bstride + h * p.kbias_hstride + k0);
         const int nv = min(8, (S_ - k0 + 3) >> 2);
 #pragma unroll
         for (int c4 = 0; c4 < 8; ++c4) {
@@ -1725,8 +1726,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
     const int kpos = n0 + row;
     const float sc = p.scale * kLog2e;
-    // additive key bias of this thread's key (raw-score units -> log2 domain); 0 without one
-    const float kb2 = (p.kbias != nullptr && kpos < S_) ? p.kbias[(long long)b * p.S + kpos] * sc : 0.f;
+    // additive key bias of this thread's key for the q head being processed (raw-score units -> log2 domain)
+    const float* kb_row = (p.kbias != nullptr && kpos < S_) ? p.kbias + b * p.kbias_bstride + kpos : nullptr;
+    int hrel_r = 0;
+    float kb2 = kb_row ? kb_row[(long long)(hk * group) * p.kbias_hstride] * sc : 0.f;
     const uint32_t stat_u = smem_u32(smem + L::oStat) + half * 128;   // this warp's 32 of the 64 queries
     int st = 0, qrel = 0;
     uint32_t ph = 0;
@@ -1795,7 +1798,12 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&ds_full[it & 1]);
-      if (++qrel == per_head) qrel = 0;
+      if (++qrel == per_head) {
+        qrel = 0;
+        ++hrel_r;                                         // next q head of the group: its own bias row
+        if (kb_row && p.kbias_hstride != 0 && hrel_r < group)
+          kb2 = kb_row[(long long)(hk * group + hrel_r) * p.kbias_hstride] * sc;
+      }
       if (++st == NS) { st = 0; ph ^= 1; }
     }
     if (niter > 0) {
@@ -1972,6 +1980,7 @@ struct VarlenCfg {
 };
 thread_local VarlenCfg g_varlen;
 thread_local const float* g_kbias = nullptr;   // set by the *_kbias entry points for the launches they make
+thread_local long long g_kbias_bstride = 0, g_kbias_hstride = 0;
 // grid over (heads, sequences, tiles of the longest sequence)
 dim3 attn_grid(int heads, int B, int S) {
   if (g_varlen.cu != nullptr) return dim3(heads, g_varlen.nseq, (g_varlen.max_len + sxb::attn::BQ - 1) / sxb::attn::BQ);
@@ -2005,7 +2014,7 @@ SXB_API int sxb_attn_fwd(const void* q, const void* k, const void* v, void* out,
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.out = out; p.out_stride = o_stride; p.lse = (float*)lse;
   p.cu_seqlens = g_varlen.cu;
-  p.kbias = g_kbias;
+  p.kbias = g_kbias; p.kbias_bstride = g_kbias_bstride; p.kbias_hstride = g_kbias_hstride;
   {
     static const int dbg = [] { const char* e = getenv("SXB_ATTN_DEBUG"); return e ? atoi(e) : 0; }();
     p.debug = dbg;
@@ -2071,7 +2080,7 @@ SXB_API int sxb_attn_bwd(const void* q, const void* k, const void* v, const void
   p.B = B; p.S = S; p.Hq = Hq; p.Hk = Hk; p.D = D; p.causal = causal; p.scale = scale;
   p.lse = (float*)const_cast<void*>(lse); p.delta = (const float*)delta;
   p.cu_seqlens = g_varlen.cu;
-  p.kbias = g_kbias;
+  p.kbias = g_kbias; p.kbias_bstride = g_kbias_bstride; p.kbias_hstride = g_kbias_hstride;
   {
     static int dbg = -1;
     if (dbg < 0) { const char* e = getenv("SXB_ATTN_DEBUG"); dbg = e ? atoi(e) : 0; }
@@ -2307,11 +2316,15 @@ SXB_API int sxb_attn_fwd_atoms(const void* q, const void* cache, void* out, cons
 // reference: the attn_mask argument of the fused softmax in csrc/transformer/softmax_kernels.cu and
 // ops/transformer/inference softmax_context).  key_bias: fp32 [B, S] in RAW-score units, i.e. the caller's additive
 // bias divided by `scale`; -inf masks a key.  S must be a multiple of 4 (16-byte loads of the bias).
+// per_head != 0: key_bias is [B, Hq, S] (ALiBi-style slopes x key position); else [B, S].
 SXB_API int sxb_attn_fwd_kbias(const void* q, const void* k, const void* v, void* out, void* lse, const void* key_bias,
-                               int B, int S, int Hq, int Hk, int D, long long q_stride, long long k_stride,
-                               long long v_stride, long long o_stride, int causal, float scale, void* stream) {
+                               int per_head, int B, int S, int Hq, int Hk, int D, long long q_stride,
+                               long long k_stride, long long v_stride, long long o_stride, int causal, float scale,
+                               void* stream) {
   if (key_bias == nullptr || (S % 4) || (reinterpret_cast<uintptr_t>(key_bias) & 15)) return SXB_ERR_UNSUPPORTED;
   g_kbias = static_cast<const float*>(key_bias);
+  g_kbias_hstride = per_head ? S : 0;
+  g_kbias_bstride = per_head ? (long long)Hq * S : S;
   const int rc = sxb_attn_fwd(q, k, v, out, lse, B, S, Hq, Hk, D, q_stride, k_stride, v_stride, o_stride, causal, scale,
                               stream);
   g_kbias = nullptr;
@@ -2319,12 +2332,15 @@ SXB_API int sxb_attn_fwd_kbias(const void* q, const void* k, const void* v, void
 }
 
 SXB_API int sxb_attn_bwd_kbias(const void* q, const void* k, const void* v, const void* out, const void* d_out,
-                               const void* lse, void* delta, void* dq, void* dk, void* dv, const void* key_bias, int B,
-                               int S, int Hq, int Hk, int D, long long q_stride, long long k_stride, long long v_stride,
-                               long long o_stride, long long do_stride, long long dq_stride, long long dk_stride,
-                               long long dv_stride, int causal, float scale, void* stream) {
+                               const void* lse, void* delta, void* dq, void* dk, void* dv, const void* key_bias,
+                               int per_head, int B, int S, int Hq, int Hk, int D, long long q_stride,
+                               long long k_stride, long long v_stride, long long o_stride, long long do_stride,
+                               long long dq_stride, long long dk_stride, long long dv_stride, int causal, float scale,
+                               void* stream) {
   if (key_bias == nullptr || (S % 4) || (reinterpret_cast<uintptr_t>(key_bias) & 15)) return SXB_ERR_UNSUPPORTED;
   g_kbias = static_cast<const float*>(key_bias);
+  g_kbias_hstride = per_head ? S : 0;
+  g_kbias_bstride = per_head ? (long long)Hq * S : S;
   const int rc = sxb_attn_bwd(q, k, v, out, d_out, lse, delta, dq, dk, dv, B, S, Hq, Hk, D, q_stride, k_stride,
                               v_stride, o_stride, do_stride, dq_stride, dk_stride, dv_stride, causal, scale, stream);
   g_kbias = nullptr;

@@ -402,13 +402,13 @@ int sxb_fp_gemv(const void* x, const void* wq, void* y, int M, int N, int K, int
  * ops/transformer/inference softmax_context).  key_bias: fp32 [B, S] in RAW-score units, i.e. the caller's additive
  * bias divided by `scale`; -inf masks a key.  S must be a multiple of 4 (16-byte loads of the bias). */
 int sxb_attn_fwd_kbias(const void* q, const void* k, const void* v, void* out, void* lse, const void* key_bias,
-                       int B, int S, int Hq, int Hk, int D, long long q_stride, long long k_stride,
+                       int per_head, int B, int S, int Hq, int Hk, int D, long long q_stride, long long k_stride,
                        long long v_stride, long long o_stride, int causal, float scale, void* stream);
 int sxb_attn_bwd_kbias(const void* q, const void* k, const void* v, const void* out, const void* d_out,
-                       const void* lse, void* delta, void* dq, void* dk, void* dv, const void* key_bias, int B,
-                       int S, int Hq, int Hk, int D, long long q_stride, long long k_stride, long long v_stride,
-                       long long o_stride, long long do_stride, long long dq_stride, long long dk_stride,
-                       long long dv_stride, int causal, float scale, void* stream);
+                       const void* lse, void* delta, void* dq, void* dk, void* dv, const void* key_bias,
+                       int per_head, int B, int S, int Hq, int Hk, int D, long long q_stride, long long k_stride,
+                       long long v_stride, long long o_stride, long long do_stride, long long dq_stride,
+                       long long dk_stride, long long dv_stride, int causal, float scale, void* stream);
 
 #ifdef __cplusplus
 }

@@ -768,8 +768,8 @@ def attention_bwd_raw(q, k, v, out, dout, lse, causal: bool, scale: float):
 
 # ------------------------------------------------------------------- attention with an additive per-key bias
 _n.register({
-    "sxb_attn_fwd_kbias": "ppppp" "p" "iiiii" "llll" "i" "f" "p",
-    "sxb_attn_bwd_kbias": "pppppppppp" "p" "iiiii" "llllllll" "i" "f" "p",
+    "sxb_attn_fwd_kbias": "ppppp" "pi" "iiiii" "llll" "i" "f" "p",
+    "sxb_attn_bwd_kbias": "pppppppppp" "pi" "iiiii" "llllllll" "i" "f" "p",
 })
 
 
@@ -784,8 +784,8 @@ class _FlashAttnKeyBias(torch.autograd.Function):
         out = torch.empty((B, S, Hq, D), dtype=q.dtype, device=q.device)
         lse = torch.empty((B, Hq, S), dtype=torch.float32, device=q.device)
         _n.call("sxb_attn_fwd_kbias", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), lse.data_ptr(),
-                kb_raw.data_ptr(), B, S, Hq, Hk, D, q.stride(1), k.stride(1), v.stride(1), out.stride(1), int(causal),
-                float(scale), _n.stream_ptr())
+                kb_raw.data_ptr(), int(kb_raw.dim() == 3), B, S, Hq, Hk, D, q.stride(1), k.stride(1), v.stride(1),
+                out.stride(1), int(causal), float(scale), _n.stream_ptr())
         ctx.save_for_backward(q, k, v, out, lse, kb_raw)
         ctx.causal, ctx.scale = causal, scale
         return out
@@ -801,21 +801,23 @@ class _FlashAttnKeyBias(torch.autograd.Function):
         delta = torch.empty((B, Hq, S), dtype=torch.float32, device=q.device)
         _n.call("sxb_attn_bwd_kbias", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), dout.data_ptr(),
                 lse.data_ptr(), delta.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), kb_raw.data_ptr(),
-                B, S, Hq, Hk, D, q.stride(1), k.stride(1), v.stride(1), out.stride(1), dout.stride(1),
+                int(kb_raw.dim() == 3), B, S, Hq, Hk, D, q.stride(1), k.stride(1), v.stride(1), out.stride(1), dout.stride(1),
                 dq.stride(1), dk.stride(1), dv.stride(1), int(ctx.causal), float(ctx.scale), _n.stream_ptr())
         return dq, dk, dv, None, None, None
 
 
 def key_bias_supported(q: torch.Tensor, key_bias: torch.Tensor) -> bool:
     """Whether :func:`flash_attention_key_bias` runs this on the flash kernels (else: materialised scores)."""
-    return (q.is_cuda and q.dtype == torch.bfloat16 and q.shape[-1] in (64, 128) and q.shape[1] % 4 == 0
-            and key_bias.shape == (q.shape[0], q.shape[1]))
+    B, S, Hq = q.shape[0], q.shape[1], q.shape[2]
+    return (q.is_cuda and q.dtype == torch.bfloat16 and q.shape[-1] in (64, 128) and S % 4 == 0
+            and tuple(key_bias.shape) in ((B, S), (B, Hq, S)))
 
 
 def flash_attention_key_bias(q, k, v, key_bias, causal: bool = False, scale: Optional[float] = None):
     """``softmax(q k^T * scale + key_bias[:, None, None, :]) v`` — q ``[B, S, Hq, D]``, k/v ``[B, S, Hk, D]``,
-    ``key_bias`` ``[B, S]`` additive (``-inf`` / large negative on padded keys).  BERT-style encoders and the v1
-    inference path pass their attention mask this way (reference: the additive ``attn_mask`` of the fused softmax)."""
+    ``key_bias`` ``[B, S]`` additive (``-inf`` / large negative on padded keys) or ``[B, Hq, S]`` (a bias per head and
+    key: ALiBi in its BLOOM form, slope x key position).  BERT-style encoders and the v1 inference path pass their
+    attention mask this way (reference: the additive ``attn_mask`` / ``alibi`` of the fused softmax)."""
     D = q.shape[-1]
     scale = scale if scale is not None else 1.0 / math.sqrt(D)
     if q.is_cuda and key_bias_supported(q, key_bias):
@@ -827,7 +829,8 @@ def flash_attention_key_bias(q, k, v, key_bias, causal: bool = False, scale: Opt
     qf = q.float().permute(0, 2, 1, 3)
     kf = k.float().permute(0, 2, 1, 3).repeat_interleave(Hq // Hk, dim=1)
     vf = v.float().permute(0, 2, 1, 3).repeat_interleave(Hq // Hk, dim=1)
-    sc = qf @ kf.transpose(-1, -2) * scale + key_bias.float()[:, None, None, :]
+    kb = key_bias.float()
+    sc = qf @ kf.transpose(-1, -2) * scale + (kb[:, None, None, :] if kb.dim() == 2 else kb[:, :, None, :])
     if causal:
         sc = sc.masked_fill(~torch.ones(S, S, dtype=torch.bool, device=q.device).tril(), float("-inf"))
     return (sc.softmax(-1) @ vf).permute(0, 2, 1, 3).to(q.dtype)

@@ -218,10 +218,17 @@ class SoftmaxContextOp(BaseOp):
         causal = c.triangular_masking and not no_masking
         plain = attn_mask is None and alibi is None and past == 0 and q.is_cuda and q.dtype == torch.bfloat16 \
             and D in (64, 128)
+        # additive key-padding mask and / or ALiBi (one bias per head and key): handled inside the flash kernels
         key_mask = None
-        if attn_mask is not None and alibi is None and past == 0 and attn_mask.numel() == B * S \
-                and attn_mask.shape[0] == B and attn_mask.shape[-1] == S and F.key_bias_supported(q, attn_mask.reshape(B, S)):
-            key_mask = attn_mask.reshape(B, S)        # additive key-padding mask: handled inside the flash kernels
+        mask_ok = attn_mask is None or (attn_mask.numel() == B * S and attn_mask.shape[0] == B and attn_mask.shape[-1] == S)
+        if past == 0 and mask_ok and (attn_mask is not None or alibi is not None) and q.is_cuda and S % 4 == 0:
+            kb = None if attn_mask is None else attn_mask.reshape(B, 1, S).float()
+            if alibi is not None:
+                al = alibi.reshape(B, heads, -1)[..., :S].float()
+                kb = al if kb is None else kb + al
+            kb = kb.reshape(B, S) if kb.shape[1] == 1 else kb.contiguous()
+            if F.key_bias_supported(q, kb):
+                key_mask = kb
         if plain:
             ctx = F.flash_attention(q, k, v, causal=causal, scale=scale)
         elif key_mask is not None:

@@ -250,3 +250,32 @@ def test_training_transformer_layer_uses_flash_kernels_for_padding_masks():
     q, k, v = qkv.view(B, S, 3, H, Dh).unbind(2)
     want = F.flash_attention_key_bias(q.float().cpu(), k.float().cpu(), v.float().cpu(), mask.reshape(B, S).cpu())
     assert _rel_err(got.cpu().view(B, S, H, Dh), want) < 1e-2
+
+
+@pytest.mark.gpu
+def test_per_head_key_bias_alibi_style():
+    """[B, Hq, S] bias (slope_h x key position, as BLOOM's alibi tensor) with GQA: every q head reads its own row in the
+    forward, the dQ and the dK/dV kernels."""
+    from shuffle_exchange_b200.ops import functional as F
+    torch.manual_seed(7)
+    B, S, Hq, Hk, D = 2, 384, 8, 2, 128
+    dev = "cuda"
+    q, k, v = (torch.randn(B, S, h, D, device=dev, dtype=torch.bfloat16, requires_grad=True) for h in (Hq, Hk, Hk))
+    slopes = torch.tensor([2.0 ** (-(i + 1)) for i in range(Hq)], device=dev)
+    bias = (slopes[None, :, None] * torch.arange(S, device=dev)[None, None, :] * 0.05).expand(B, Hq, S).contiguous()
+    bias[1, :, S - 40:] = float("-inf")
+    out = F.flash_attention_key_bias(q, k, v, bias, causal=True)
+    g = torch.randn_like(out)
+    out.backward(g)
+    ref_in = [t.detach().float().requires_grad_(True) for t in (q, k, v)]
+    qf = ref_in[0].permute(0, 2, 1, 3)
+    kf = ref_in[1].permute(0, 2, 1, 3).repeat_interleave(Hq // Hk, dim=1)
+    vf = ref_in[2].permute(0, 2, 1, 3).repeat_interleave(Hq // Hk, dim=1)
+    sc = qf @ kf.transpose(-1, -2) * D ** -0.5 + bias[:, :, None, :]
+    sc = sc.masked_fill(~torch.ones(S, S, dtype=torch.bool, device=dev).tril(), float("-inf"))
+    ref = (sc.softmax(-1) @ vf).permute(0, 2, 1, 3)
+    ref.backward(g.float())
+    assert _rel_err(out, ref) < 1e-2
+    for got, want in zip((q, k, v), ref_in):
+        assert torch.isfinite(got.grad).all()
+        assert _rel_err(got.grad, want.grad) < 3e-2
