@@ -525,7 +525,10 @@ class TLinear(torch.nn.Linear):
         self._fwd_func = self._fwd_bias_add if self.bias is not None else self._fwd
 
     def _fwd(self, input):
-        return torch.matmul(input, self.weight)
+        if torch.is_grad_enabled() and (input.requires_grad or self.weight.requires_grad):
+            return torch.matmul(input, self.weight)      # autograd path (the front end below records no graph)
+        from ..ops import functional as _F
+        return _F.matmul_nn(input, self.weight)          # inference: tcgen05 GEMM for bf16 CUDA operands
 
     def _fwd_bias_add(self, input):
         return self._fwd(input) + self.bias
