@@ -920,8 +920,16 @@ def flash_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: b
     D = q.shape[-1]
     scale = scale if scale is not None else 1.0 / math.sqrt(D)
     if q.is_cuda:
-        if q.dtype != torch.bfloat16 or D not in (64, 128):
-            raise _n.NativeError(f"sxb flash_attention: bf16 and head_dim 64/128 only (got {q.dtype}, {D})")
+        if q.dtype != torch.bfloat16 or D > 128 or D % 8:
+            raise _n.NativeError(f"sxb flash_attention: bf16 and head_dim <= 128, multiple of 8 (got {q.dtype}, {D})")
+        if D not in (64, 128):
+            # Other head sizes (32, 80, 96, ...) run on the 64 / 128 kernels with zero-padded channels: zeros add
+            # nothing to q . k, the padded channels of v give zero output columns that are sliced off again, and the
+            # softmax scale stays that of the true head size.  Exact; costs the padding copies.
+            Dp = 64 if D < 64 else 128
+            pad = (0, Dp - D)
+            out = flash_attention(F.pad(q, pad), F.pad(k, pad), F.pad(v, pad), causal, scale)
+            return out[..., :D]
         q = q if _attn_layout_ok(q) else q.contiguous()
         k = k if _attn_layout_ok(k) else k.contiguous()
         v = v if _attn_layout_ok(v) else v.contiguous()

@@ -279,3 +279,22 @@ def test_per_head_key_bias_alibi_style():
     for got, want in zip((q, k, v), ref_in):
         assert torch.isfinite(got.grad).all()
         assert _rel_err(got.grad, want.grad) < 3e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D", [32, 80, 96])
+def test_other_head_sizes_run_zero_padded(D):
+    from shuffle_exchange_b200.ops import functional as F
+    torch.manual_seed(8)
+    B, S, Hq, Hk = 2, 200, 4, 2
+    q, k, v = (torch.randn(B, S, h, D, device="cuda", dtype=torch.bfloat16, requires_grad=True) for h in (Hq, Hk, Hk))
+    out = F.flash_attention(q, k, v, causal=True)
+    assert out.shape == (B, S, Hq, D)
+    g = torch.randn_like(out)
+    out.backward(g)
+    ref_in = [t.detach().float().requires_grad_(True) for t in (q, k, v)]
+    ref = F.attention_ref(*ref_in, True)
+    ref.backward(g.float())
+    assert _rel_err(out, ref) < 1e-2
+    for got, want in zip((q, k, v), ref_in):
+        assert got.grad.shape == want.grad.shape and _rel_err(got.grad, want.grad) < 3e-2
