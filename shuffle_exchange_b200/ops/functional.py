@@ -225,6 +225,16 @@ class _Linear(torch.autograd.Function):
         return dx, dw, db
 
 
+_warned = set()
+
+
+def _warn_once(key: str, message: str) -> None:
+    if key not in _warned:
+        _warned.add(key)
+        import warnings
+        warnings.warn(message, stacklevel=3)
+
+
 def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``x @ weight.T + bias`` — tcgen05 GEMM for bf16 CUDA tensors (fwd, dgrad and wgrad)."""
     if x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 \
@@ -233,7 +243,10 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
             x = x.contiguous()
         return _Linear.apply(x, weight, bias)
     if x.is_cuda:
-        raise _n.NativeError(f"sxb linear: unsupported dtype/shape {x.dtype} {tuple(x.shape)} x {tuple(weight.shape)}")
+        # fp16 / fp32 operands or rows that are not 16-byte multiples: the tcgen05 GEMM takes bf16 only, the library
+        # GEMM serves the rest (the reference's fp16 + loss-scaling mode keeps working; said once, not silently)
+        _warn_once("linear", f"sxb linear: {x.dtype} {tuple(x.shape)} x {tuple(weight.shape)} runs on the library GEMM "
+                             "(the tcgen05 path takes bf16 operands with 8-element-aligned sizes)")
     return F.linear(x, weight, bias)
 
 
@@ -921,7 +934,12 @@ def flash_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: b
     scale = scale if scale is not None else 1.0 / math.sqrt(D)
     if q.is_cuda:
         if q.dtype != torch.bfloat16 or D > 128 or D % 8:
-            raise _n.NativeError(f"sxb flash_attention: bf16 and head_dim <= 128, multiple of 8 (got {q.dtype}, {D})")
+            # fp16 / fp32 or head sizes beyond the kernels': PyTorch's attention, said once
+            _warn_once("attn", f"sxb flash_attention: {q.dtype}, head_dim {D} runs on torch SDPA (the tcgen05 kernels "
+                               "take bf16 with head_dim <= 128, multiple of 8)")
+            o = F.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2), is_causal=causal,
+                                               scale=scale, enable_gqa=q.shape[2] != k.shape[2])
+            return o.transpose(1, 2).contiguous()
         if D not in (64, 128):
             # Other head sizes (32, 80, 96, ...) run on the 64 / 128 kernels with zero-padded channels: zeros add
             # nothing to q . k, the padded channels of v give zero output columns that are sliced off again, and the

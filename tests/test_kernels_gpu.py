@@ -54,5 +54,14 @@ def test_native_library_is_loaded_and_counted():
     assert lib.launch_count >= 1 and y.shape == (256, 1024)
     with open("/proc/self/maps") as f:
         assert "libsxb200.so" in f.read()
+    # dtypes the tcgen05 GEMM does not take run on the library GEMM — announced once, never silently
+    import warnings
+    F._warned.discard("linear")
+    with warnings.catch_warnings(record=True) as seen:
+        warnings.simplefilter("always")
+        y32 = F.linear(x.float(), w.float())
+    assert any("library GEMM" in str(w_.message) for w_ in seen)
+    assert (y32 - x.float() @ w.float().t()).abs().max() < 1e-2
+    # the kernels themselves still refuse what they cannot do
     with pytest.raises(lib.NativeError):
-        F.linear(x.float(), w.float())          # no silent fallback on a CUDA tensor
+        F.gemm(x.float(), w.float(), 0)
