@@ -101,3 +101,34 @@ def test_tied_embedding_gradients_match_fp32_oracle(stage):
         err = (got[n] - ref).abs()
         tol = 0.06 * ref.abs().max() + 0.06 * ref.abs()
         assert bool((err <= tol).all()), (stage, n, err.max().item(), ref.abs().max().item())
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("stage", [0, 2])
+def test_llama_trains_in_fp16_with_dynamic_loss_scale(stage):
+    """The reference's fp16 mode (dynamic loss scaling, overflow skips) on a GPU: the model's GEMMs and attention take
+    the library path for fp16 (the tcgen05 kernels are bf16), everything else stays on the native kernels."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(29570 + stage), RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    import warnings
+    import shuffle_exchange_b200 as sxb
+    from shuffle_exchange_b200.models.llama import LlamaForCausalLM, llama_config
+    torch.manual_seed(0)
+    cfg = llama_config("llama-tiny", hidden_size=256, num_attention_heads=4, num_key_value_heads=2)
+    model = LlamaForCausalLM(cfg, device="cuda", dtype=torch.float16)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        engine, _, _, _ = sxb.initialize(model=model, model_parameters=model.parameters(), config={
+            "train_micro_batch_size_per_gpu": 2, "steps_per_print": 1 << 30,
+            "fp16": {"enabled": True, "initial_scale_power": 12, "loss_scale_window": 4, "hysteresis": 1},
+            "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}}, "zero_optimization": {"stage": stage}})
+        ids = torch.randint(0, cfg.vocab_size, (2, 128), device="cuda")
+        losses = []
+        for _ in range(10):
+            loss = engine(ids, labels=ids)
+            engine.backward(loss)
+            engine.step()
+            losses.append(float(loss))
+    assert all(l == l for l in losses), losses
+    assert losses[-1] < losses[0] - 0.3, losses
+    assert engine.optimizer.loss_scaler.dynamic and engine.optimizer.loss_scaler.cur_scale >= 1
