@@ -709,7 +709,9 @@ def flash_attention_qkv(qkv: torch.Tensor, n_q: int, n_kv: int, head_dim: int, c
     scale = scale if scale is not None else 1.0 / math.sqrt(head_dim)
     if qkv.is_cuda:
         if qkv.dtype != torch.bfloat16 or head_dim not in (64, 128):
-            raise _n.NativeError(f"sxb flash_attention: bf16 and head_dim 64/128 only (got {qkv.dtype}, {head_dim})")
+            # fp16 / fp32 or another head size: the general entry point pads or takes the library path (see there)
+            q, k, v = _split_qkv(qkv, n_q, n_kv, head_dim)
+            return flash_attention(q, k, v, causal, scale)
         if qkv.dim() != 3 or qkv.shape[-1] != (n_q + 2 * n_kv) * head_dim:
             raise ValueError(f"fused qkv shape {tuple(qkv.shape)} != [B, S, {(n_q + 2 * n_kv) * head_dim}]")
         return _FlashAttnQKV.apply(qkv.contiguous(), n_q, n_kv, head_dim, causal, scale)
