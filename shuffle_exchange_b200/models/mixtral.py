@@ -29,7 +29,7 @@ class MixtralConfig(LlamaConfig):
     ep_size: int = 1
     fused_exchange: object = None        # None: symmetric-memory dispatch/combine when available; False: NCCL
     fp8_experts: bool = False            # e4m3 expert GEMMs in forward (tcgen05 kind::f8f6f4), bf16 backward
-    ep_capacity_factor: float = 1.25
+    ep_capacity_factor: float = 2.0          # 1.25 overflowed at 8 GPUs with a random-init router (overflow raises)
 
     def num_parameters(self) -> int:
         h, f, v, d = self.hidden_size, self.intermediate_size, self.vocab_size, self.head_dim

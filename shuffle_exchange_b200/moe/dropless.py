@@ -88,7 +88,7 @@ class SwiGLUExpert(nn.Module):
 class DroplessMoE(MoE):
     def __init__(self, hidden_size: int, intermediate_size: int, num_experts: int, ep_size: int = 1, k: int = 2,
                  aux_loss_coef: float = 0.0, device=None, dtype=None, fused_exchange: Optional[bool] = None,
-                 fp8_experts: bool = False, ep_capacity_factor: float = 1.5):
+                 fp8_experts: bool = False, ep_capacity_factor: float = 2.0):
         nn.Module.__init__(self)
         assert num_experts % ep_size == 0, f"Number of experts ({num_experts}) should be divisible by expert parallel size ({ep_size})"
         self.hidden_size, self.num_experts, self.ep_size, self.k = hidden_size, num_experts, ep_size, k
