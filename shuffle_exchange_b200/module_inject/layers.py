@@ -98,7 +98,9 @@ def _symm_reducer(x: torch.Tensor, group):
         sg.wait_readers(buf, symm.CH_AVG_READ)
         buf.tensor[:n].copy_(t.view(-1))
         out = torch.empty_like(t)
-        sg.subset_mean(buf, list(range(sg.world)), out.view(-1), n)
+        # large activations (prefill): two-phase form, 2 (w-1)/w instead of (w-1) tensor sizes over NVLink; small ones
+        # (decode) stay on the single-pass kernel, which has one handshake less
+        sg.subset_mean(buf, list(range(sg.world)), out.view(-1), n, shared=n * t.element_size() >= (8 << 20))
         return out.mul_(sg.world)               # kernel returns the mean
     return run
 
