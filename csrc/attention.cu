@@ -28,6 +28,14 @@ constexpr float kLn2 = 0.6931471805599453f;
 // K/V tiles, [2] its wait for dS, [3] iterations, [4] row warp total, [5] its wait for S/dP, [6] its TMEM load +
 // math, [7] its TMEM store + fence
 __device__ unsigned long long g_attn_prof[8];
+// The counters are compiled in only with -DSXB_ATTN_PROF (build an alternative library and load it through
+// SXB_LIB_PATH): even as never-taken branches they sit in the MMA warp's issue loop, which is what bounds the dQ
+// kernel (0.74 -> 0.79 ms with them compiled in).
+#ifdef SXB_ATTN_PROF
+constexpr bool kAttnProf = true;
+#else
+constexpr bool kAttnProf = false;
+#endif
 
 struct Params {
   int B, S, Hq, Hk, D;
@@ -662,7 +670,7 @@ attn_fwd128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const uint32_t idesc_o = make_idesc(BQ, D, 1, 1, 0, 1);
     const uint32_t sQ = sbase + L::oQ, sK = sbase + L::oK, sV = sbase + L::oV;
     if (!__all_sync(0xffffffffu, mbar_wait_to(q_full, 0, 52))) goto done;
-    const bool prof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+    const bool prof = kAttnProf && p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
     long long pr_t0 = prof ? clock64() : 0, pr_k = 0, pr_p = 0, pr_v = 0;
     for (int j = 0; j < nblk; ++j) {
       long long c0 = prof ? clock64() : 0;
@@ -712,7 +720,7 @@ attn_fwd128_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     float* xch = reinterpret_cast<float*>(smem + L::oXch);     // [2][128]
     const uint32_t tSh = tS + hf * 64 + lane_off;               // this warp's 64 S columns
     float m_run = -INFINITY, l_run = 0.f;                       // l_run: partial sum over this warp's columns
-    const bool rprof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 2;
+    const bool rprof = kAttnProf && p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 2;
     long long rp_t0 = rprof ? clock64() : 0, rp_wait = 0, rp_work = 0;
     for (int j = 0; j < nblk; ++j) {
       // s_full(j) is a commit behind QK^T(j): every earlier MMA of this CTA, PV(j-1) included, has retired, so O may
@@ -1021,7 +1029,7 @@ attn_fwd_pair_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     issue_qk(1, 0);
     if (elected) umma_commit(&k_empty[0]);
     __syncwarp();
-    const bool prof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+    const bool prof = kAttnProf && p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
     long long pr_t0 = prof ? clock64() : 0, pr_kv = 0, pr_p0 = 0, pr_p1 = 0;
     for (int j = 0; j < nblk; ++j) {
       const int st = j % NS, stn = (j + 1) % NS;
@@ -1071,7 +1079,7 @@ attn_fwd_pair_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     const uint32_t tSh = tS + hf * 64 + lane_off;
     const int bar_id = 1 + t * 4 + quad;
     float m_run = -INFINITY, l_run = 0.f;
-    const bool rprof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 2;
+    const bool rprof = kAttnProf && p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 2;
     long long rp_t0 = rprof ? clock64() : 0, rp_wait = 0, rp_work = 0;
     for (int j = 0; j < nblk; ++j) {
       // s_full[t](j) is a commit behind QK(t, j): PV(t, j-1) has retired, so O_t may be rescaled and S_t overwritten
@@ -1375,7 +1383,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     }
     __syncwarp();
     if (!issue_sdp(0)) goto done;
-    const bool prof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+    const bool prof = kAttnProf && p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
     long long pr_t0 = prof ? clock64() : 0, pr_kv = 0, pr_ds = 0;
     for (int j = 0; j < nblk; ++j) {
       const int st = j % NS;
@@ -1432,7 +1440,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       __syncwarp();
       if (lane == 0) mbar_arrive(qa_full);
     }
-    const bool rprof = p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 2;
+    const bool rprof = kAttnProf && p.debug == 3 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 2;
     long long rp_t0 = rprof ? clock64() : 0, rp_wait = 0, rp_math = 0, rp_st = 0;
     for (int j = 0; j < nblk; ++j) {
       long long rc0 = rprof ? clock64() : 0;
@@ -1749,13 +1757,24 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         uint32_t x[32];
         tmem_ld_32x32(tST, x);
         tmem_ld_wait();
+        if (p.kbias == nullptr) {
 #pragma unroll
-        for (int c4 = 0; c4 < 8; ++c4) {
-          const float4 nl = lds128(sstat + c4 * 16);          // -lse * log2e, warp-broadcast
-          s[c4 * 4 + 0] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 0]), sc, nl.x + kb2));
-          s[c4 * 4 + 1] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 1]), sc, nl.y + kb2));
-          s[c4 * 4 + 2] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 2]), sc, nl.z + kb2));
-          s[c4 * 4 + 3] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 3]), sc, nl.w + kb2));
+          for (int c4 = 0; c4 < 8; ++c4) {
+            const float4 nl = lds128(sstat + c4 * 16);          // -lse * log2e, warp-broadcast
+            s[c4 * 4 + 0] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 0]), sc, nl.x));
+            s[c4 * 4 + 1] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 1]), sc, nl.y));
+            s[c4 * 4 + 2] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 2]), sc, nl.z));
+            s[c4 * 4 + 3] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 3]), sc, nl.w));
+          }
+        } else {
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {                      // key bias: one more add per element
+            const float4 nl = lds128(sstat + c4 * 16);
+            s[c4 * 4 + 0] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 0]), sc, nl.x + kb2));
+            s[c4 * 4 + 1] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 1]), sc, nl.y + kb2));
+            s[c4 * 4 + 2] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 2]), sc, nl.z + kb2));
+            s[c4 * 4 + 3] = fast_exp2(fmaf(__uint_as_float(x[c4 * 4 + 3]), sc, nl.w + kb2));
+          }
         }
       }
       if (need_mask) {

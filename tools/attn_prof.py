@@ -1,4 +1,5 @@
-"""Cycle accounting of the heaviest dQ tile (SXB_ATTN_DEBUG=3; diagnostic only): where the MMA warp and a row warp of
+"""Cycle accounting of the heaviest dQ tile (SXB_ATTN_DEBUG=3; diagnostic only).  Needs a library whose csrc/attention.cu was compiled with -DSXB_ATTN_PROF
+(build it next to the default one and point SXB_LIB_PATH at it): where the MMA warp and a row warp of
 one CTA spend their time.  S=8192, 32q/8kv, d=128, causal."""
 import ctypes
 import json
