@@ -8,8 +8,9 @@ File layout kept byte-compatible so existing ``.bin/.idx`` pairs load:
            | int32 sizes[n_items] | int64 byte pointers[n_items] | int64 doc_idx[n_docs]
     .bin : the items back to back
 
-The legacy (non-mmap) ``IndexedDataset`` variants of the reference are not reproduced; ``make_dataset`` accepts only
-``mmap`` (``infer_dataset_impl`` reports other files as unsupported).
+The legacy (non-mmap, ``TNTIDX``) format is kept as ``IndexedDataset`` / ``IndexedCachedDataset`` /
+``IndexedDatasetBuilder`` further down for files written that way; ``make_dataset`` / ``make_builder`` produce the
+``mmap`` form (``infer_dataset_impl`` reports anything else as unsupported).
 """
 from __future__ import annotations
 
