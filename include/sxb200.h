@@ -12,6 +12,7 @@
  */
 #ifndef SXB200_H
 #define SXB200_H
+#include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -409,6 +410,34 @@ int sxb_attn_bwd_kbias(const void* q, const void* k, const void* v, const void* 
                        int per_head, int B, int S, int Hq, int Hk, int D, long long q_stride, long long k_stride,
                        long long v_stride, long long o_stride, long long do_stride, long long dq_stride,
                        long long dk_stride, long long dv_stride, int causal, float scale, void* stream);
+
+/* ---- csrc/host/aio.cpp */
+int sxbh_aio_create(long long block_size, int queue_depth, int single_submit, int overlap_events,
+                    int intra_op_parallelism);
+int sxbh_aio_destroy(int id);
+/* async = 0: returns when the bytes are transferred (0 or -errno).  async = 1: returns immediately; sxbh_aio_wait
+ * completes it. */
+int sxbh_aio_pread(int id, void* buffer, long long nbytes, const char* path, long long file_offset, int async);
+int sxbh_aio_pwrite(int id, const void* buffer, long long nbytes, const char* path, long long file_offset,
+                    int async);
+int sxbh_aio_wait(int id);
+long long sxbh_aio_info(int id, int what);
+long long sxbh_file_size(const char* path);
+
+/* ---- csrc/host/cpu_optim.cpp */
+/* bf16 <-> fp32 bulk converters used by the offload paths (gradients arrive from the GPU in bf16). */
+int sxbh_bf16_to_f32(const uint16_t* src, float* dst, long long n, float scale, int accumulate);
+int sxbh_num_threads();
+int sxbh_simd_width();
+
+/* ---- csrc/host/ragged_host.cpp */
+/* atoms: int32 [max_atoms, 6] = (seq_index, q_start_idx, q_len, global_q_idx, kv_blocks, total_extent)
+ * returns the number of atoms written, or -1 when max_atoms is too small. */
+int sxbh_build_atoms(int32_t* atoms, int max_atoms, const int32_t* seq_start, const int32_t* seq_tokens,
+                     const int32_t* seq_seen, int n_seqs, int q_block, int kv_block);
+/* tok_seq / tok_pos: int32 [total tokens]; last_tok: int32 [n_seqs]; returns total tokens. */
+int sxbh_fill_ragged_batch(int32_t* tok_seq, int32_t* tok_pos, int32_t* last_tok, const int32_t* seq_tokens,
+                           const int32_t* seq_seen, int n_seqs);
 
 #ifdef __cplusplus
 }

@@ -13,16 +13,16 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "sxb200.h")
 MARK = "/* ==== declarations below are kept in step with csrc/ by tools/gen_header.py ==== */"
-SIG = re.compile(r"^SXB_API\s+([^;{()]*?\b(sxb_\w+)\s*\([^;{]*?\))\s*\{", re.S | re.M)
+SIG = re.compile(r"^SXBH?_API\s+([^;{()]*?\b(sxbh?_\w+)\s*\([^;{]*?\))\s*\{", re.S | re.M)
 
 
 def entry_points():
     """[(source file, name, signature text, comment text)] in source order."""
     out = []
     csrc = os.path.join(ROOT, "csrc")
-    for fn in sorted(os.listdir(csrc)):
-        if not fn.endswith(".cu"):
-            continue
+    sources = [f for f in sorted(os.listdir(csrc)) if f.endswith(".cu")]
+    sources += [os.path.join("host", f) for f in sorted(os.listdir(os.path.join(csrc, "host"))) if f.endswith(".cpp")]
+    for fn in sources:
         text = open(os.path.join(csrc, fn)).read()
         for m in SIG.finditer(text):
             sig, name = " ".join(m.group(1).split()), m.group(2)
@@ -56,7 +56,7 @@ def wrap(sig, width=116):
 
 
 def _norm(sig):
-    return " ".join(sig.replace("SXB_API ", "").replace("(", " ( ").replace(")", " ) ").replace(",", " , ").split())
+    return " ".join(sig.replace("SXBH_API ", "").replace("SXB_API ", "").replace("(", " ( ").replace(")", " ) ").replace(",", " , ").split())
 
 
 def stale(text, entries):
@@ -87,7 +87,7 @@ def main():
     for fn, name, sig, comment, m, generated in sorted(old, key=lambda e: -e[4].start()):
         if not generated:
             raise SystemExit(f"{name}: hand-written declaration is stale; edit include/sxb200.h")
-        text = text[: m.start()] + wrap(sig.replace("SXB_API ", "")) + text[m.end():]
+        text = text[: m.start()] + wrap(sig.replace("SXBH_API ", "").replace("SXB_API ", "")) + text[m.end():]
     if old:
         open(HEADER, "w").write(text)
         print(f"refreshed {len(old)} declarations")
@@ -112,7 +112,7 @@ def main():
             cur_file = fn
         if comment:
             body += "/* " + "\n * ".join(c.replace("*/", "* /") for c in comment) + " */\n"
-        body += wrap(sig.replace("SXB_API ", "")) + "\n"
+        body += wrap(sig.replace("SXBH_API ", "").replace("SXB_API ", "")) + "\n"
     open(HEADER, "w").write(body + tail)
     print(f"declared {len(missing)} entry points")
 
