@@ -107,3 +107,40 @@ def test_header_parameter_types_match_the_sources():
         if name in header and header[name] != kinds(args):
             bad.append((fn, name, "".join(header[name]), "".join(kinds(args))))
     assert not bad, bad
+
+
+def test_host_library_signatures_match_the_header():
+    """Same check for libsxb200_host.so: its ctypes tables list argument types as ``[c_i, c_p, ...]``."""
+    import ast
+    import re
+    text = re.sub(r"/\*.*?\*/", " ", open(os.path.join(ROOT, "include", "sxb200.h")).read(), flags=re.S)
+    header = {}
+    for m in re.finditer(r"\b(?:int|long long)\s+(sxbh_\w+)\s*\(([^;{]*?)\)\s*;", text, flags=re.S):
+        args = " ".join(m.group(2).split())
+        kinds = []
+        if args not in ("", "void"):
+            for a in args.split(","):
+                kinds.append("p" if "*" in a else "l" if "long long" in a else "d" if "double" in a
+                             else "f" if "float" in a else "i")
+        header[m.group(1)] = "".join(kinds)
+    letter = {"c_i": "i", "c_p": "p", "c_l": "l", "c_f": "f", "c_d": "d", "c_int": "i", "c_void_p": "p",
+              "c_longlong": "l", "c_float": "f", "c_double": "d", "c_char_p": "p", "_P": "p"}
+    bad, seen = [], 0
+    pkg = os.path.join(ROOT, "shuffle_exchange_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if not f.endswith(".py"):
+                continue
+            for node in ast.walk(ast.parse(open(os.path.join(dirpath, f)).read())):
+                if not isinstance(node, ast.Dict):
+                    continue
+                for k, v in zip(node.keys, node.values):
+                    if not (isinstance(k, ast.Constant) and isinstance(k.value, str) and k.value.startswith("sxbh_")
+                            and isinstance(v, ast.List)):
+                        continue
+                    names = [e.id if isinstance(e, ast.Name) else getattr(e, "attr", "?") for e in v.elts]
+                    sig = "".join(letter.get(n, "?") for n in names)
+                    seen += 1
+                    if k.value in header and sig != header[k.value]:
+                        bad.append((f, k.value, sig, header[k.value]))
+    assert seen >= 20 and not bad, (seen, bad)
