@@ -46,7 +46,10 @@ class FlatGroup:
     def __init__(self, params: List[torch.nn.Parameter], names: List[str], world: int, rank: int, process_group,
                  device: torch.device, lp_dtype: torch.dtype, grad_dtype: Optional[torch.dtype] = None,
                  group_index: int = 0, param_group: Optional[dict] = None, keep_full_params: bool = True,
-                 hp_on_cpu: bool = False, pin: bool = False, allocator=None, lp_on_cpu: bool = False):
+                 hp_on_cpu: bool = False, pin: bool = False, allocator=None, lp_on_cpu: bool = False,
+                 lp_store=None):
+        self._lp_store, self._lp_shard = None, None       # see the ``lp_shard`` property
+        self._lp_key = f"group{group_index:04d}"
         self.params = list(params)
         self.names = list(names)
         self.world, self.rank, self.pg = world, rank, process_group
@@ -86,6 +89,10 @@ class FlatGroup:
             # offload_param = cpu: the low-precision shard lives in (pinned) host memory between uses
             host = self.lp_shard.to("cpu")
             self.lp_shard = host.pin_memory() if (pin and torch.cuda.is_available()) else host
+            if lp_store is not None:
+                # offload_param = nvme: the shard's home is a file; it passes through the store's host buffers
+                lp_store.put(self._lp_key, host)
+                self._lp_shard, self._lp_store = None, lp_store
         self._bind_params()
 
         # ---- fp32 master ---------------------------------------------------------------------
@@ -105,6 +112,25 @@ class FlatGroup:
             self.release_params()
 
     # ------------------------------------------------------------------------------ parameters
+    @property
+    def lp_shard(self) -> Optional[torch.Tensor]:
+        """This rank's low-precision shard.  With an NVMe store (``offload_param.device = nvme``) every access goes
+        through the store's resident buffers; whoever modifies the returned tensor calls :meth:`lp_shard_written`."""
+        if self._lp_store is not None:
+            return self._lp_store.get(self._lp_key)
+        return self._lp_shard
+
+    @lp_shard.setter
+    def lp_shard(self, t: Optional[torch.Tensor]):
+        if self._lp_store is not None and t is not None:
+            self._lp_store.put(self._lp_key, t)
+        else:
+            self._lp_shard = t
+
+    def lp_shard_written(self):
+        if self._lp_store is not None:
+            self._lp_store.written(self._lp_key)
+
     def _bind_params(self):
         for p, off, n, shp in zip(self.params, self.offsets, self.numels, self.shapes):
             p.data = self.flat_lp[off: off + n].view(shp)

@@ -239,6 +239,8 @@ class ShardedOptimizerBase:
             hp.grad = None
             if lp_out is not None:
                 lp_out.copy_(hp.data)
+        if lp_out is not None:
+            fg.lp_shard_written()         # NVMe-resident shards: the store writes the buffer back before reusing it
 
     def _update_scale(self, overflow: bool):
         if not self.custom_loss_scaler:

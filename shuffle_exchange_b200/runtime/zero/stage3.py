@@ -150,10 +150,22 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                 raise ValueError("offload_optimizer.device = nvme needs offload_optimizer.nvme_path")
         self._offload_optimizer_config, self._aio_config = offload_optimizer_config, aio_config
         self.offload_ratio = float(getattr(offload_optimizer_config, "ratio", 1.0)) if self.offload_optimizer else 0.0
+        self._param_store = None
         if offload_param_config is not None and str(getattr(offload_param_config, "device", "none")).endswith("nvme"):
-            raise NotImplementedError(
-                "offload_param.device = nvme is not supported: parameter shards stay in device or (offload_param.device "
-                "= cpu) pinned host memory; NVMe offload is available for optimizer state (offload_optimizer.device = nvme)")
+            # ZeRO-Infinity parameter offload: shards live in files, at most buffer_count of them resident in host memory
+            nvme_path = getattr(offload_param_config, "nvme_path", None)
+            if nvme_path is None:
+                raise ValueError("offload_param.device = nvme needs offload_param.nvme_path")
+            from .nvme_shards import NvmeShardStore
+            aio = dict(aio_config) if isinstance(aio_config, dict) else {
+                k: getattr(aio_config, k) for k in ("block_size", "queue_depth", "single_submit", "overlap_events",
+                                                    "intra_op_parallelism") if hasattr(aio_config, k)}
+            self.offload_param = True
+            self.offload_param_pin = bool(getattr(offload_param_config, "pin_memory", False))
+            self._param_store = NvmeShardStore(
+                os.path.join(str(nvme_path), "zero_stage_3", f"{str(self.dtype).split('.')[-1]}params", f"rank{self.rank}"),
+                self.dtype, buffer_count=int(getattr(offload_param_config, "buffer_count", 5) or 5), aio_config=aio,
+                pin_memory=self.offload_param_pin)
         self.hpz_size = int(zero_hpz_partition_size or 1)
         self.quantized_weights = bool(zero_quantized_weights)
         self.quantized_gradients = bool(zero_quantized_gradients)
@@ -229,7 +241,8 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                 fg = FlatGroup(params, names, self.world, self.rank, self.dp_process_group, self.device, self.dtype,
                                grad_dtype=self.dtype, group_index=len(self.groups), keep_full_params=keep_full,
                                hp_on_cpu=on_cpu, pin=self.offload_optimizer_pin or self.offload_param_pin,
-                               lp_on_cpu=self.offload_param and not keep_full)
+                               lp_on_cpu=self.offload_param and not keep_full,
+                               lp_store=None if keep_full else self._param_store)
                 self._configure_zeropp(fg)
                 fg.lazy_grad_zero = os.environ.get("SXB_LAZY_GRAD_ZERO", "1") != "0"
                 src_pg = self.optimizer.param_groups[gi]
@@ -783,6 +796,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
         for i, fg in enumerate(self.groups):
             fg.hp_param.data.copy_(mine[FP32_FLAT_GROUPS][i].to(fg.hp_param.device))
             fg.lp_shard.copy_(fg.hp_param.data.to(fg.lp_shard.device))
+            fg.lp_shard_written()
             if load_optimizer_states:
                 st = self.optimizer.state[fg.hp_param]
                 for k, v in mine[OPTIMIZER_STATE_DICT]["state"].get(i, {}).items():
@@ -804,6 +818,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
                 return out
             fg.hp_param.data.copy_(cut([sd[FP32_FLAT_GROUPS][i] for sd in sds]).to(fg.hp_param.device))
             fg.lp_shard.copy_(fg.hp_param.data.to(fg.lp_shard.device))
+            fg.lp_shard_written()
             if load_optimizer_states:
                 st = self.optimizer.state[fg.hp_param]
                 for k, v0 in sds[0][OPTIMIZER_STATE_DICT]["state"].get(i, {}).items():

@@ -34,6 +34,8 @@ def _worker(rank, world, extra, tmp):
     z.update(copy.deepcopy(extra))
     if z.get("offload_optimizer", {}).get("device") == "nvme":
         z["offload_optimizer"]["nvme_path"] = tmp
+    if z.get("offload_param", {}).get("device") == "nvme":
+        z["offload_param"]["nvme_path"] = tmp
     cfg = {"train_micro_batch_size_per_gpu": 4, "steps_per_print": 10 ** 9, "bf16": {"enabled": True},
            "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}}, "zero_optimization": z}
     engine, opt, _, _ = ds.initialize(model=model, config=cfg, model_parameters=model.parameters())
@@ -46,6 +48,11 @@ def _worker(rank, world, extra, tmp):
         assert all(fg.quantized_gradients is not None for fg in opt.groups)
     if "offload_param" in extra:
         assert all(fg.lp_shard.device.type == "cpu" for fg in opt.groups)
+    if extra.get("offload_param", {}).get("device") == "nvme":
+        import os
+        store = opt._param_store
+        assert store is not None and all(os.path.exists(store.path(fg._lp_key)) for fg in opt.groups)
+        assert all(fg._lp_shard is None for fg in opt.groups), "shards must live in the store, not in the group"
     if extra.get("offload_optimizer", {}).get("ratio", 1.0) < 1.0:
         on_cpu = [fg.hp_on_cpu for fg in opt.groups]
         assert any(on_cpu) and not all(on_cpu), on_cpu
@@ -60,6 +67,10 @@ def _worker(rank, world, extra, tmp):
         for x in xs:
             (oracle(x.to(torch.bfloat16).float()) / world).backward()
         o.step()
+    if extra.get("offload_param", {}).get("device") == "nvme":
+        store = opt._param_store
+        assert store.resident_count <= 2, store.resident_count         # buffer_count of the config
+        assert store.reads > len(opt.groups) and store.writes > len(opt.groups)   # shards really went to disk and back
     if extra.get("offload_optimizer", {}).get("device") == "nvme":
         assert opt.optimizer_swapper is not None and len(opt._swapped) == len(opt.groups)
         assert all(fg.hp_param.data.numel() == 0 for fg in opt.groups), "masters must be on NVMe between steps"
@@ -83,6 +94,7 @@ CASES = [
     (2, {"offload_optimizer": {"device": "cpu", "ratio": 0.5}}),
     (2, {"offload_param": {"device": "cpu"}}),
     (2, {"offload_optimizer": {"device": "nvme", "buffer_count": 16}}),
+    (2, {"offload_param": {"device": "nvme", "buffer_count": 2}}),
 ]
 
 
@@ -98,12 +110,12 @@ def test_unsupported_switches_raise():
 
     class _Cfg:
         device = "nvme"
-        nvme_path = "/tmp"
+        nvme_path = None
         pin_memory = False
 
     m = _Net().to(torch.bfloat16)
     base = torch.optim.AdamW(m.parameters(), lr=1e-3)
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(ValueError):                       # NVMe parameter offload without a path
         DeepSpeedZeroOptimizer_Stage3(m, base, offload_param_config=_Cfg())
     with pytest.raises(NotImplementedError):
         DeepSpeedZeroOptimizer_Stage3(m, base, zero_quantized_nontrainable_weights=True)
