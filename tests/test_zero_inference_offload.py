@@ -21,7 +21,7 @@ class _Net(nn.Module):
         return self.head(x)
 
 
-def _worker(rank, world, offload):
+def _worker(rank, world, offload, nvme_dir=None):
     import shuffle_exchange_b200 as ds  # noqa: F401  (initialises the comm layer)
     from shuffle_exchange_b200 import comm as dist
     from shuffle_exchange_b200.runtime.zero.offload_config import DeepSpeedZeroOffloadParamConfig
@@ -32,13 +32,19 @@ def _worker(rank, world, offload):
     for p in model.layers[1].parameters():
         p.requires_grad_(False)                               # a frozen block, as in ZeRO-Inference
     dense = copy.deepcopy(model)
-    cfg = DeepSpeedZeroOffloadParamConfig(device="cpu", pin_memory=False) if offload else None
+    cfg = None
+    if offload == "nvme":
+        cfg = DeepSpeedZeroOffloadParamConfig(device="nvme", nvme_path=nvme_dir, buffer_count=2, pin_memory=False)
+    elif offload:
+        cfg = DeepSpeedZeroOffloadParamConfig(device="cpu", pin_memory=False)
     z = DeepSpeedZeRoOffload(model, param_persistence_threshold=0, offload_param_config=cfg)
     eng = z._engine
     # sharded: every unit's flat buffer is split over the two ranks and released outside its forward
     assert all(fg.lp_shard.numel() * world == fg.total for fg in eng.groups)
     if offload:
         assert all(fg.lp_shard.device.type == "cpu" for fg in eng.groups)
+    if offload == "nvme":
+        assert eng._param_store is not None and eng._param_store.resident_count <= 2
     assert all(p.numel() == 0 for u in eng.units if not u.persistent for fg in u.groups for p in fg.params)
     x = torch.randn(5, 32)
     with torch.no_grad():
@@ -58,3 +64,7 @@ def test_optimizerless_zero3_matches_dense():
 
 def test_optimizerless_zero3_with_host_resident_shards():
     run_dist(_worker, 2, (True,))
+
+
+def test_optimizerless_zero3_with_nvme_resident_shards(tmp_path):
+    run_dist(_worker, 2, ("nvme", str(tmp_path)))
