@@ -94,7 +94,7 @@ def test_two_stage_training_matches_sequential():
     run_dist(_pipe_worker, 2)
 
 
-def _pipe_zero_worker(rank, world, zero_stage):
+def _pipe_zero_worker(rank, world, zero_stage, offload=False):
     """PP=2 x DP=2 with the stage's data-parallel pair running ZeRO-``zero_stage`` (the reference asserts stage < 2 under
     pipeline parallelism, pipe/engine.py:77-78): two batches must match unsharded AdamW on the same data."""
     import shuffle_exchange_b200 as ds
@@ -110,7 +110,11 @@ def _pipe_zero_worker(rank, world, zero_stage):
     engine, _, _, _ = ds.initialize(model=net, model_parameters=[p for p in net.parameters()], config={
         "train_micro_batch_size_per_gpu": micro, "gradient_accumulation_steps": gas, "steps_per_print": 10 ** 9,
         "bf16": {"enabled": True}, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}},
-        "zero_optimization": {"stage": zero_stage, "stage3_param_persistence_threshold": 0}})
+        "zero_optimization": dict({"stage": zero_stage, "stage3_param_persistence_threshold": 0},
+                                  **({"offload_optimizer": {"device": "cpu"}, "offload_param": {"device": "cpu"}}
+                                     if offload else {}))})
+    if offload:
+        assert all(fg.hp_on_cpu and fg.lp_shard.device.type == "cpu" for fg in engine.optimizer.groups)
     assert engine.zero_optimization_stage() == zero_stage
     dp_rank = engine.grid.data_parallel_id
     g = torch.Generator().manual_seed(11)
@@ -146,3 +150,9 @@ def _pipe_zero_worker(rank, world, zero_stage):
 @pytest.mark.parametrize("zero_stage", [2, 3])
 def test_zero_sharding_inside_pipeline_stages(zero_stage):
     run_dist(_pipe_zero_worker, 4, (zero_stage,))
+
+
+def test_zero3_with_host_offload_inside_pipeline_stages():
+    """BASELINE config 5 in miniature: ZeRO-3 + pipeline (PP=2) with optimizer state and parameter shards in host
+    memory, DP=2 per stage."""
+    run_dist(_pipe_zero_worker, 4, (3, True))
