@@ -513,6 +513,77 @@ fp_gemv_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict__ 
     }
 }
 
+// ============================================================================ weight-only integer GEMV
+// y[M, N] = x[M, K] W^T for a weight kept as group-wise ASYMMETRIC integer codes in the layout of
+// inference/quantization (reference deepspeed/inference/quantization/utils.py): codes uint8 [N, K] (8 bits) or
+// [N, K/2] (4 bits, even index in the HIGH nibble), groups of `group_size` along K, scale / min bf16 [N, K/group_size]
+// with w = code / scale + min.  Same decomposition as fp_gemv_kernel (one warp: 4 rows of W, 256 columns per step);
+// per row and step the code sum-product and the activation sum are accumulated separately inside a group so the
+// affine map costs two FMAs per 8 codes instead of one per code:  sum (c/s + m) x = (1/s) sum c x + m sum x.
+template <int BITS, int MB>
+__global__ void __launch_bounds__(256)
+int_gemv_kernel(const __nv_bfloat16* __restrict__ x, const uint8_t* __restrict__ codes,
+                const __nv_bfloat16* __restrict__ scale, const __nv_bfloat16* __restrict__ minv,
+                __nv_bfloat16* __restrict__ y, int N, int K, int group_size, long long x_stride, long long y_stride) {
+  constexpr int R = 4;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = (blockIdx.x * 8 + warp) * R;
+  if (n0 >= N) return;
+  const int gpr = K / group_size;                       // groups per row
+  const long long row_bytes = (long long)K * BITS / 8;
+  float acc[R][MB];
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int m = 0; m < MB; ++m) acc[r][m] = 0.f;
+  for (int k = lane * 8; k < K; k += 256) {
+    float xv[MB][8], xs[MB];
+#pragma unroll
+    for (int m = 0; m < MB; ++m) {
+      load8<__nv_bfloat16>(x + m * x_stride + k, xv[m]);
+      xs[m] = ((xv[m][0] + xv[m][1]) + (xv[m][2] + xv[m][3])) + ((xv[m][4] + xv[m][5]) + (xv[m][6] + xv[m][7]));
+    }
+    const int g = k / group_size;                        // the 8 codes of a lane never straddle a group (gs % 8 == 0)
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (n0 + r >= N) break;
+      const uint8_t* src = codes + (long long)(n0 + r) * row_bytes + (long long)k * BITS / 8;
+      float c[8];
+      if (BITS == 8) {
+        const uint2 u = *reinterpret_cast<const uint2*>(src);
+        const uint32_t w[2] = {u.x, u.y};
+#pragma unroll
+        for (int i = 0; i < 8; ++i) c[i] = float((w[i >> 2] >> (8 * (i & 3))) & 0xFF);
+      } else {
+        const uint32_t u = *reinterpret_cast<const uint32_t*>(src);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t byte = (u >> (8 * (i >> 1))) & 0xFF;          // byte i/2: value 2j in the high nibble
+          c[i] = float((i & 1) ? (byte & 0xF) : (byte >> 4));
+        }
+      }
+      const float inv_s = 1.f / __bfloat162float(scale[(long long)(n0 + r) * gpr + g]);
+      const float mn = __bfloat162float(minv[(long long)(n0 + r) * gpr + g]);
+#pragma unroll
+      for (int m = 0; m < MB; ++m) {
+        float dot = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dot = fmaf(c[i], xv[m][i], dot);
+        acc[r][m] += fmaf(dot, inv_s, mn * xs[m]);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int m = 0; m < MB; ++m) {
+      float v = acc[r][m];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+      if (lane == 0 && n0 + r < N) y[m * y_stride + n0 + r] = __float2bfloat16_rn(v);
+    }
+}
+
 // ================================================================================== sign packing
 // 1-bit optimizers: byte i holds the signs of elements 8i..8i+7, most significant bit first (numpy /
 // cupy packbits order, which the reference relies on).  unpack writes +1 / -1.
@@ -901,5 +972,41 @@ SXB_API int sxb_fp_gemv(const void* x, const void* wq, void* y, int M, int N, in
     case 6: return launch_fp_gemv<3, 2>(x, wq, y, M, N, K, group_size, x_stride, y_stride, s);
     case 4: return launch_fp_gemv<2, 1>(x, wq, y, M, N, K, group_size, x_stride, y_stride, s);
   }
+  return SXB_ERR_UNSUPPORTED;
+}
+
+namespace {
+template <int BITS>
+int launch_int_gemv(const void* x, const void* codes, const void* scale, const void* minv, void* y, int Mrows, int N,
+                    int K, int gs, long long xs, long long ys, cudaStream_t s) {
+  const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
+  const uint8_t* cp = static_cast<const uint8_t*>(codes);
+  const __nv_bfloat16* sp = static_cast<const __nv_bfloat16*>(scale);
+  const __nv_bfloat16* mp = static_cast<const __nv_bfloat16*>(minv);
+  __nv_bfloat16* yp = static_cast<__nv_bfloat16*>(y);
+  const unsigned blocks = (unsigned)((N + 31) / 32);
+  for (int m0 = 0; m0 < Mrows;) {
+    const int mb = Mrows - m0 >= 4 ? 4 : (Mrows - m0 >= 2 ? 2 : 1);
+    if (mb == 4) int_gemv_kernel<BITS, 4><<<blocks, 256, 0, s>>>(xp + m0 * xs, cp, sp, mp, yp + m0 * ys, N, K, gs, xs, ys);
+    else if (mb == 2) int_gemv_kernel<BITS, 2><<<blocks, 256, 0, s>>>(xp + m0 * xs, cp, sp, mp, yp + m0 * ys, N, K, gs, xs, ys);
+    else int_gemv_kernel<BITS, 1><<<blocks, 256, 0, s>>>(xp + m0 * xs, cp, sp, mp, yp + m0 * ys, N, K, gs, xs, ys);
+    m0 += mb;
+  }
+  SXB_CHECK_LAUNCH();
+  return SXB_OK;
+}
+}  // namespace
+
+// W8A16 / W4A16 linear for small batches on the inference/quantization layout (see int_gemv_kernel): x bf16 [M, K],
+// codes uint8, scale / min bf16 [N, K / group_size], y bf16 [M, N].  K % 256 == 0, group_size % 8 == 0,
+// K % group_size == 0.  (reference: inference/quantization dequantises and calls F.linear for every batch size.)
+SXB_API int sxb_int_gemv(const void* x, const void* codes, const void* scale, const void* minv, void* y, int M, int N,
+                         int K, int bits, int group_size, long long x_stride, long long y_stride, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return SXB_ERR_BAD_ARG;
+  if (group_size <= 0 || group_size % 8 || K % group_size || K % 256 || x_stride % 8) return SXB_ERR_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(codes) & 7) != 0) return SXB_ERR_UNSUPPORTED;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (bits == 8) return launch_int_gemv<8>(x, codes, scale, minv, y, M, N, K, group_size, x_stride, y_stride, s);
+  if (bits == 4) return launch_int_gemv<4>(x, codes, scale, minv, y, M, N, K, group_size, x_stride, y_stride, s);
   return SXB_ERR_UNSUPPORTED;
 }

@@ -439,6 +439,13 @@ int sxbh_build_atoms(int32_t* atoms, int max_atoms, const int32_t* seq_start, co
 int sxbh_fill_ragged_batch(int32_t* tok_seq, int32_t* tok_pos, int32_t* last_tok, const int32_t* seq_tokens,
                            const int32_t* seq_seen, int n_seqs);
 
+/* ---- csrc/quantize.cu */
+/* W8A16 / W4A16 linear for small batches on the inference/quantization layout (see int_gemv_kernel): x bf16 [M, K],
+ * codes uint8, scale / min bf16 [N, K / group_size], y bf16 [M, N].  K % 256 == 0, group_size % 8 == 0,
+ * K % group_size == 0.  (reference: inference/quantization dequantises and calls F.linear for every batch size.) */
+int sxb_int_gemv(const void* x, const void* codes, const void* scale, const void* minv, void* y, int M, int N,
+                 int K, int bits, int group_size, long long x_stride, long long y_stride, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

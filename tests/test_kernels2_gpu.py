@@ -179,3 +179,26 @@ def test_w6a16_linear_uses_gemv_for_decode_and_gemm_for_prefill():
         y = lin(None, x, wq, (512, 1024))
         ref = x.float() @ w.float().t()
         assert ((y.float() - ref).norm() / ref.norm()).item() < 8e-2     # FP6 quantisation error of the weight
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("num_bits", [4, 8])
+@pytest.mark.parametrize("rows", [1, 3, 16])
+def test_quantized_linear_decode_gemv_matches_dequantised_matmul(num_bits, rows):
+    """inference/quantization: at decode sizes the layer multiplies straight from the codes; the result must equal the
+    fp32 matmul with the layer's own dequantised weight (larger batches take the dequantise + GEMM path)."""
+    import torch
+    from shuffle_exchange_b200.inference.quantization import layers as ql
+    torch.manual_seed(3)
+    ql.quantized_weight_registry.clear()            # keyed by storage address: entries of freed layers must not be hit
+    lin = torch.nn.Linear(1024, 1000, bias=True, device="cuda", dtype=torch.bfloat16)
+    cfg = {"num_bits": num_bits, "group_size": 64, "group_dim": 1, "symmetric": False}
+    q = ql.QuantizedLinear(cfg, lin)
+    x = torch.randn(rows, 1024, device="cuda", dtype=torch.bfloat16)
+    codes, scale, mn = q._deconcat(q.weight.data)
+    assert ql.int_gemv_ok(x, codes, scale, cfg, 1024) == (rows <= ql.GEMV_MAX_ROWS)
+    y = q(x)
+    ref = x.float() @ q.dequantized_weight().float().t() + lin.bias.float()
+    err = ((y.float() - ref).norm() / ref.norm()).item()
+    # the layer's dequantised weight is rounded to bf16, the GEMV keeps code / scale + min in fp32
+    assert err < 1e-2, err
