@@ -25,6 +25,11 @@ LLAMA3_8B = dict(vocab_size=128256, hidden_size=4096, intermediate_size=14336, n
 
 
 def run(args, ClockSampler, ds_config_fn):
+    if not str(args.model).startswith("llama3-8b") or getattr(args, "sp", 1) > 1:
+        # the arm drives Llama-3-8B under ZeRO-3 data parallelism only; a run of another model or of sequence
+        # parallelism labelled with that name would be a wrong number, so say so instead
+        raise NotImplementedError(f"reference arm covers llama3-8b ZeRO-3 DP only (asked: model={args.model}, "
+                                  f"sp={getattr(args, 'sp', 1)})")
     from baseline import make_ref
     if not make_ref.is_staged():
         make_ref.main()          # raises with the staging instructions when /root/reference is not mounted
