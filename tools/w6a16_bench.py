@@ -23,7 +23,34 @@ def timed(fn, n=20):
     return a.elapsed_time(b) / n
 
 
+def int_layers():
+    """INT4 / INT8 layers of inference/quantization at decode sizes: GEMV on the codes vs the layer's dequantise +
+    F.linear path (the reference's only path)."""
+    import torch.nn.functional as tF
+    from shuffle_exchange_b200.inference.quantization import layers as ql
+    out = []
+    for (N, K) in [(14336 * 2, 4096), (4096, 14336)]:
+        lin = torch.nn.Linear(K, N, bias=False, device="cuda", dtype=torch.bfloat16)
+        for bits in (4, 8):
+            ql.quantized_weight_registry.clear()
+            cfg = {"num_bits": bits, "group_size": 64, "group_dim": 1, "symmetric": False}
+            q = ql.QuantizedLinear(cfg, lin)
+            for rows in (1, 4):
+                x = torch.randn(rows, K, device="cuda", dtype=torch.bfloat16)
+                t_fused = timed(lambda: q(x))
+                t_deq = timed(lambda: tF.linear(x, q.dequantized_weight()))
+                packed = N * K * bits / 8 + 2 * (N * K // 64) * 2
+                out.append({"N": N, "K": K, "bits": bits, "rows": rows, "gemv_ms": t_fused, "dequant_linear_ms": t_deq,
+                            "speedup": t_deq / t_fused, "gemv_weight_TBps": packed / t_fused / 1e9})
+                print(json.dumps(out[-1]))
+            del q
+    os.makedirs("gpurun_out", exist_ok=True)
+    json.dump(out, open("gpurun_out/int_gemv_bench.json", "w"), indent=1)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "int":
+        return int_layers()
     out = []
     for (N, K) in [(14336 * 2, 4096), (4096, 14336), (6144, 4096)]:
         w = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
