@@ -249,24 +249,7 @@ class TimersConfig(DeepSpeedConfigModel):
 
 
 # scalar top-level keys: attribute name -> (json key, default)
-_SCALARS = {
-    "steps_per_print": ("steps_per_print", 10),
-    "dump_state": ("dump_state", False),
-    "disable_allgather": ("disable_allgather", False),
-    "prescale_gradients": ("prescale_gradients", False),
-    "gradient_predivide_factor": ("gradient_predivide_factor", 1.0),
-    "sparse_gradients_enabled": ("sparse_gradients", False),
-    "gradient_clipping": ("gradient_clipping", 0.0),
-    "graph_harvesting": ("graph_harvesting", False),
-    "zero_allow_untested_optimizer": ("zero_allow_untested_optimizer", False),
-    "zero_force_ds_cpu_optimizer": ("zero_force_ds_cpu_optimizer", True),
-    "wall_clock_breakdown": ("wall_clock_breakdown", False),
-    "memory_breakdown": ("memory_breakdown", False),
-    "use_data_before_expert_parallel_": ("use_data_before_expert_parallelism", False),
-    "dataloader_drop_last": ("dataloader_drop_last", False),
-    "vocabulary_size": ("vocabulary_size", 1201),
-    "seq_parallel_communication_data_type": ("seq_parallel_communication_data_type", "fp32"),
-}
+_SCALARS = C.SCALAR_KEYS          # attribute -> (key, default), declared next to the key names
 
 _COMM_DTYPES = {None: None, "fp32": torch.float32, "fp16": torch.float16, "bf16": torch.bfloat16,
                 "float32": torch.float32, "float16": torch.float16, "bfloat16": torch.bfloat16}
@@ -352,7 +335,7 @@ class DeepSpeedConfig:
         for attr, (key, default) in _SCALARS.items():
             setattr(self, attr, get_scalar_param(pd, key, default))
 
-        cdt = pd.get("communication_data_type")
+        cdt = pd.get(C.COMMUNICATION_DATA_TYPE, C.COMMUNICATION_DATA_TYPE_DEFAULT)
         if cdt not in _COMM_DTYPES:
             raise ValueError(f"Invalid communication_data_type. Supported data types: ['fp16', 'bf16', 'fp32']. Got: {cdt}")
         self.communication_data_type = _COMM_DTYPES[cdt]
@@ -370,8 +353,8 @@ class DeepSpeedConfig:
         mon = {k: pd[k] for k in ("tensorboard", "wandb", "csv_monitor", "comet") if k in pd}
         self.monitor_config = MonitorConfig(**mon)
 
-        self.fp16_config = FP16Config(**pd.get("fp16", {}))
-        bf = pd.get("bf16", pd.get("bfloat16", {}))
+        self.fp16_config = FP16Config(**pd.get(C.FP16, {}))
+        bf = pd.get(C.BFLOAT16, pd.get(C.BFLOAT16_OLD, {}))
         self.bf16_config = BF16Config(**bf)
         assert not (self.fp16_config.enabled and self.bf16_config.enabled), "bfloat16 and fp16 modes cannot be simultaneously enabled"
         self.fp16_enabled = self.fp16_config.enabled
@@ -383,9 +366,9 @@ class DeepSpeedConfig:
         self.loss_scale = self.fp16_config.loss_scale
         self.initial_dynamic_scale = self.fp16_config.initial_dynamic_scale()
         self.dynamic_loss_scale_args = self.fp16_config.dynamic_loss_scale_args()
-        self.amp_enabled = pd.get("amp", {}).get("enabled", False)
-        self.amp_params = {k: v for k, v in pd.get("amp", {}).items() if k != "enabled"}
-        self.torch_autocast_config = TorchAutocastConfig(**pd.get("torch_autocast", {}))
+        self.amp_enabled = pd.get(C.AMP, {}).get(C.AMP_ENABLED, C.AMP_ENABLED_DEFAULT)
+        self.amp_params = {k: v for k, v in pd.get(C.AMP, {}).items() if k != C.AMP_ENABLED}
+        self.torch_autocast_config = TorchAutocastConfig(**pd.get(C.TORCH_AUTOCAST, {}))
         self.torch_autocast_enabled = self.torch_autocast_config.enabled
         self.torch_autocast_dtype = getattr(torch, self.torch_autocast_config.dtype, torch.bfloat16)
         self.torch_autocast_lower_precision_safe_modules = self.torch_autocast_config.lower_precision_safe_modules
@@ -393,46 +376,47 @@ class DeepSpeedConfig:
         self.compression_config = pd.get("compression_training", {})
         self.weight_quantization_config = pd.get("weight_quantization")
 
-        opt = pd.get("optimizer")
-        self.optimizer_name = opt.get("type") if opt else None
+        opt = pd.get(C.OPTIMIZER)
+        self.optimizer_name = opt.get(C.TYPE) if opt else C.OPTIMIZER_TYPE_DEFAULT
         if self.optimizer_name is not None and self.optimizer_name.lower() in DEEPSPEED_OPTIMIZERS:
             self.optimizer_name = self.optimizer_name.lower()
-        self.optimizer_params = (opt or {}).get("params")
-        self.optimizer_legacy_fusion = (opt or {}).get("legacy_fusion", False)
-        sched = pd.get("scheduler")
-        self.scheduler_name = sched.get("type") if sched else None
-        self.scheduler_params = (sched or {}).get("params")
+        self.optimizer_params = (opt or {}).get(C.OPTIMIZER_PARAMS)
+        self.optimizer_legacy_fusion = (opt or {}).get(C.LEGACY_FUSION, C.LEGACY_FUSION_DEFAULT)
+        sched = pd.get(C.SCHEDULER)
+        self.scheduler_name = sched.get(C.TYPE) if sched else C.SCHEDULER_TYPE_DEFAULT
+        self.scheduler_params = (sched or {}).get(C.SCHEDULER_PARAMS)
 
         self.flops_profiler_config = FlopsProfilerConfig(**pd.get("flops_profiler", {}))
         self.timers_config = TimersConfig(**pd.get("timers", {}))
         self.autotuning_config = pd.get("autotuning", {})
-        self.eigenvalue_config = EigenvalueConfig(**pd.get("eigenvalue", {}))
+        self.eigenvalue_config = EigenvalueConfig(**pd.get(C.EIGENVALUE, {}))
         for k in ("enabled", "verbose", "max_iter", "tol", "stability", "gas_boundary_resolution", "layer_name",
                   "layer_num"):
             setattr(self, f"eigenvalue_{k}", getattr(self.eigenvalue_config, k))
         self.hybrid_engine = HybridEngineConfig(**pd.get("hybrid_engine", {}))
-        self.sparse_attention = pd.get("sparse_attention")
+        self.sparse_attention = pd.get(C.SPARSE_ATTENTION)
         self.pipeline = PipelineConfig(**pd.get("pipeline", {})).model_dump()
-        self.pld_config = PLDConfig(**pd.get("progressive_layer_drop", {}))
+        self.pld_config = PLDConfig(**pd.get(C.PROGRESSIVE_LAYER_DROP, {}))
         self.pld_enabled = self.pld_config.enabled
-        self.pld_params = {"theta": self.pld_config.theta, "gamma": self.pld_config.gamma} if self.pld_enabled else False
+        self.pld_params = {C.PLD_THETA: self.pld_config.theta, C.PLD_GAMMA: self.pld_config.gamma} if self.pld_enabled else False
         self.curriculum_enabled_legacy = pd.get("curriculum_learning", {}).get("enabled", False)
         self.curriculum_params_legacy = pd.get("curriculum_learning", {}) if self.curriculum_enabled_legacy else False
         self.data_efficiency_config = pd.get("data_efficiency", {})
         self.data_efficiency_enabled = self.data_efficiency_config.get("enabled", False)
 
-        self.checkpoint_config = CheckpointConfig(**pd.get("checkpoint", {}))
+        self.checkpoint_config = CheckpointConfig(**pd.get(C.CHECKPOINT, {}))
         tv = self.checkpoint_config.tag_validation.upper()
-        if tv not in ("IGNORE", "WARN", "FAIL"):
+        if tv not in C.CHECKPOINT_TAG_VALIDATION_MODES:
             raise DeepSpeedConfigError(f"Checkpoint config contains invalid tag_validation value of {tv}, expecting one of ['IGNORE', 'WARN', 'FAIL']")
-        self.checkpoint_tag_validation_enabled = tv != "IGNORE"
-        self.checkpoint_tag_validation_fail = tv == "FAIL"
+        self.checkpoint_tag_validation_enabled = tv != C.ValidationMode.IGNORE
+        self.checkpoint_tag_validation_fail = tv == C.ValidationMode.FAIL
         self.load_universal_checkpoint = self.checkpoint_config.load_universal
         self.use_node_local_storage = self.checkpoint_config.use_node_local_storage
-        self.checkpoint_parallel_write_pipeline = bool(self.checkpoint_config.parallel_write.get("pipeline_stage", False))
+        self.checkpoint_parallel_write_pipeline = bool(self.checkpoint_config.parallel_write.get(C.CHECKPOINT_PARALLEL_WRITE_PIPELINE_STAGE,
+                                                                                     C.CHECKPOINT_PARALLEL_WRITE_PIPELINE_STAGE_DEFAULT))
         self.checkpoint_writer_config = self.checkpoint_config.writer
 
-        self.data_types_config = DataTypesConfig(**pd.get("data_types", {}))
+        self.data_types_config = DataTypesConfig(**pd.get(C.DATA_TYPES, {}))
         self.grad_accum_dtype = self.data_types_config.grad_accum_dtype
         self.aio_config = AioConfig(**pd.get("aio", {})).model_dump()
         self.nebula_config = pd.get("nebula", {})
@@ -482,7 +466,7 @@ class DeepSpeedConfig:
         if vs and vs % C.TENSOR_CORE_ALIGN_SIZE != 0:
             logger.debug(f"DeepSpeedConfig: vocabulary size {vs} is not aligned to {C.TENSOR_CORE_ALIGN_SIZE}, "
                          "may impact tensor core utilization.")
-        if self.optimizer_params is not None and "max_grad_norm" in self.optimizer_params:
+        if self.optimizer_params is not None and C.MAX_GRAD_NORM in self.optimizer_params:
             if self.fp16_enabled or self.bfloat16_enabled:
                 logger.warning("DeepSpeedConfig: In mixed-precision mode, max_grad_norm in the optimizer params is "
                                "superseded by the top-level gradient_clipping key; setting it to 0")

@@ -56,3 +56,26 @@ def test_precision_and_misc_sections():
     assert c.checkpoint_tag_validation_fail and c.wall_clock_breakdown
     with pytest.raises(AssertionError):
         DeepSpeedConfig({"train_batch_size": 1, "fp16": {"enabled": True}, "bf16": {"enabled": True}})
+
+
+def test_every_declared_scalar_key_is_read_with_its_default():
+    """runtime/constants.py declares key names next to their defaults; the config object must read exactly those."""
+    from shuffle_exchange_b200.runtime import constants as C
+    base = {C.TRAIN_BATCH_SIZE: 4}
+    c = DeepSpeedConfig(base)
+    probe = {bool: lambda d: not d, int: lambda d: d + 7, float: lambda d: d + 0.5, str: lambda d: "bf16"}
+    for attr, (key, default) in C.SCALAR_KEYS.items():
+        if attr != "seq_parallel_communication_data_type":          # converted to a torch dtype after reading
+            assert getattr(c, attr) == default, (attr, getattr(c, attr), default)
+        value = probe[type(default)](default)
+        c2 = DeepSpeedConfig({**base, key: value})
+        got = getattr(c2, attr)
+        assert got == (torch.bfloat16 if attr == "seq_parallel_communication_data_type" else value), (attr, got)
+    # section names: old and new spelling of the bf16 block, optimizer / scheduler sub-keys
+    c3 = DeepSpeedConfig({**base, C.BFLOAT16_OLD: {C.BFLOAT16_ENABLED: True},
+                          C.OPTIMIZER: {C.TYPE: "AdamW", C.OPTIMIZER_PARAMS: {"lr": 1e-3}, C.LEGACY_FUSION: True},
+                          C.SCHEDULER: {C.TYPE: "WarmupLR", C.SCHEDULER_PARAMS: {"warmup_num_steps": 3}},
+                          C.CHECKPOINT: {C.CHECKPOINT_TAG_VALIDATION: "fail", C.LOAD_UNIVERSAL_CHECKPOINT: True}})
+    assert c3.bfloat16_enabled and c3.optimizer_name == "adamw" and c3.optimizer_legacy_fusion
+    assert c3.scheduler_name == "WarmupLR" and c3.scheduler_params == {"warmup_num_steps": 3}
+    assert c3.checkpoint_tag_validation_fail and c3.load_universal_checkpoint
