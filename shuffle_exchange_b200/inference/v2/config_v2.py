@@ -3,7 +3,7 @@ from __future__ import annotations
 
 from dataclasses import dataclass, field
 
-from .ragged.manager import DSStateManagerConfig
+from .ragged.ragged_manager import DSStateManagerConfig
 
 
 @dataclass

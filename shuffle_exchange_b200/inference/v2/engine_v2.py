@@ -12,7 +12,7 @@ from typing import Iterable, List, Tuple
 import torch
 
 from .config_v2 import RaggedInferenceEngineConfig
-from .ragged.manager import DSStateManager
+from .ragged.ragged_manager import DSStateManager
 from .ragged.ragged_wrapper import RaggedBatchWrapper
 
 
@@ -90,8 +90,8 @@ class InferenceEngineV2:
         if seq is None:
             if self._state_manager.n_tracked_sequences >= self._config.state_manager.max_tracked_sequences:
                 return 0, 0
-            from .ragged.sequence_descriptor import DSSequenceDescriptor
-            seq = DSSequenceDescriptor(uid, self._state_manager.max_blocks_per_seq)
+            from .ragged.sequence_descriptor import PlaceholderSequenceDescriptor
+            seq = PlaceholderSequenceDescriptor()
         return self._model.get_kv_requirements(seq, max_request_tokens, max_request_blocks)
 
     def can_schedule(self, uids: Iterable[int], lengths: Iterable[int]) -> int:

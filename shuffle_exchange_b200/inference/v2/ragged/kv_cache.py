@@ -20,6 +20,14 @@ class KVCacheConfig:
     max_blocks_per_allocation_group: int = 64
 
 
+def split_kv(kv_cache: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Key and value views ``[n_blocks, block_size, n_kv_heads, head_dim]`` of one layer's cache
+    ``[n_blocks, block_size, 2, n_kv_heads, head_dim]`` (reference ``kv_cache.py:22-37``)."""
+    if kv_cache.ndim != 5 or kv_cache.shape[2] != 2:
+        raise ValueError(f"expected a [blocks, block_size, 2, heads, head_dim] cache, got {tuple(kv_cache.shape)}")
+    return kv_cache.select(2, 0), kv_cache.select(2, 1)
+
+
 class BlockedKVCache:
     def __init__(self, config: KVCacheConfig, num_blocks: Optional[int] = None, memory_fraction: float = 0.8,
                  device=None, reserve_bytes: Optional[int] = None, mp_group=None) -> None:

@@ -1,7 +1,7 @@
 """Configuration objects of the ragged state manager (reference: ``inference/v2/ragged/manager_configs.py:15-183``).
 
 ``KVCacheConfig`` and ``DSStateManagerConfig`` are defined next to the classes they configure (``kv_cache.py``,
-``manager.py``) and re-exported here under the reference's module name; ``MemoryConfig`` adds the reference's two
+``ragged_manager.py``) and re-exported here under the reference's module name; ``MemoryConfig`` adds the reference's two
 allocation modes on top of them.
 """
 from __future__ import annotations
@@ -41,4 +41,4 @@ class MemoryConfig:
             raise ValueError("MemoryConfig.size must be positive")
 
 
-from .manager import DSStateManagerConfig  # noqa: E402,F401
+from .ragged_manager import DSStateManagerConfig  # noqa: E402,F401

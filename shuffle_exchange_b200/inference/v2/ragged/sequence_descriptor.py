@@ -7,7 +7,39 @@ from typing import List
 import torch
 
 
-class DSSequenceDescriptor:
+class BaseSequenceDescriptor:
+    """What the scheduler-side checks read from a sequence (reference ``sequence_descriptor.py:15-33``)."""
+
+    @property
+    def seen_tokens(self) -> int:
+        raise NotImplementedError
+
+    @property
+    def cur_allocated_blocks(self) -> int:
+        raise NotImplementedError
+
+
+class PlaceholderSequenceDescriptor(BaseSequenceDescriptor):
+    """Stand-in for a sequence that is not tracked yet: lets ``query`` / ``can_schedule`` ask the model for the KV
+    requirement of a new request without allocating a block table (reference ``sequence_descriptor.py:35-56``)."""
+
+    def __init__(self, seen_tokens: int = 0, cur_allocated_blocks: int = 0, kv_blocks_ptr: int = 0) -> None:
+        self._seen_tokens, self._cur_allocated_blocks, self._kv_blocks_ptr = seen_tokens, cur_allocated_blocks, kv_blocks_ptr
+
+    @property
+    def seen_tokens(self) -> int:
+        return self._seen_tokens
+
+    @property
+    def cur_allocated_blocks(self) -> int:
+        return self._cur_allocated_blocks
+
+    @property
+    def kv_blocks_ptr(self) -> int:
+        return self._kv_blocks_ptr
+
+
+class DSSequenceDescriptor(BaseSequenceDescriptor):
     def __init__(self, tracking_id: int, max_blocks: int) -> None:
         self._tracking_id = tracking_id
         self._seen_tokens = 0
