@@ -432,3 +432,14 @@ def get_tensor_model_parallel_src_rank():
 
 def get_data_parallel_rank():
     return _get_data_parallel_rank()
+
+
+def get_data_parallel_group():
+    """Data-parallel group of the TP mesh set up by :func:`_init_tp_mesh_device` (AutoTP training); unlike
+    :func:`_get_data_parallel_group` this accessor does not fall back to the world group."""
+    assert _DATA_PARALLEL_GROUP is not None, "data parallel group is not initialized"
+    return _DATA_PARALLEL_GROUP
+
+
+def get_data_parallel_world_size():
+    return dist.get_world_size(group=get_data_parallel_group())

@@ -23,7 +23,28 @@ def _create_logger(name="sxb200", level=logging.INFO):
     return lg
 
 
+class LoggerFactory:
+    """Reference spelling of the logger constructor (``LoggerFactory.create_logger(name, level)``): a named,
+    non-propagating stdout logger with this package's line format; asking twice for a name returns the same logger."""
+
+    @staticmethod
+    def create_logger(name=None, level=logging.INFO):
+        if name is None:
+            raise ValueError("name for logger cannot be None")
+        return _create_logger(name, level)
+
+
+log_levels = {"debug": logging.DEBUG, "info": logging.INFO, "warning": logging.WARNING, "error": logging.ERROR,
+              "critical": logging.CRITICAL}
+
 logger = _create_logger()
+
+
+def print_configuration(args, name):
+    """Log every attribute of an argparse-style namespace, one aligned ``key ..... value`` line each."""
+    logger.info(f"{name}:")
+    for key in sorted(vars(args)):
+        logger.info(f"  {key} {'.' * max(1, 29 - len(key))} {getattr(args, key)}")
 
 
 def _my_rank() -> int:

@@ -21,9 +21,73 @@ from ..comm import comm as dist
 
 @dataclass
 class _Link:
+    """What ``param._hp_mapping`` is here.  It answers the questions the reference's ``tensor_fragment`` record answers
+    (:19-70) — where this rank's piece of the parameter sits in the fp32 master shard, in the parameter itself and in
+    every optimizer-state tensor — by computing views over the flat group instead of storing narrowed tensors."""
     group: object        # FlatGroup
     index: int           # position of the parameter inside the group
     optimizer: object    # owning sharded optimizer
+
+    def _range(self):
+        r = self.group.shard_range_of_param(self.index)
+        return (0, 0, 0) if r is None else r          # (offset in the parameter, offset in the shard, count)
+
+    # addresses
+    @property
+    def lp_fragment_address(self) -> "fragment_address":
+        p_off, _, cnt = self._range()
+        return fragment_address(numel=cnt, start=p_off)
+
+    @property
+    def hp_fragment_address(self) -> "fragment_address":
+        _, s_off, cnt = self._range()
+        return fragment_address(numel=cnt, start=s_off)
+
+    def get_hp_fragment_address(self) -> "fragment_address":
+        return self.hp_fragment_address
+
+    # tensors (views; empty when this rank holds no element of the parameter)
+    @property
+    def hp_fragment(self) -> torch.Tensor:
+        _, s_off, cnt = self._range()
+        return self.group.hp_param.data[s_off: s_off + cnt]
+
+    @property
+    def lp_fragment(self) -> torch.Tensor:
+        _, s_off, cnt = self._range()
+        return self.group.lp_shard[s_off: s_off + cnt]
+
+    def get_optim_state_keys(self):
+        st = self.optimizer._optimizer_state_for(self.group)
+        n = self.group.hp_param.numel()
+        return [k for k, v in st.items() if torch.is_tensor(v) and v.numel() == n]
+
+    def get_optim_state_fragment(self, key) -> torch.Tensor:
+        st = self.optimizer._optimizer_state_for(self.group)
+        if key not in st or not torch.is_tensor(st[key]):
+            raise ValueError(f"{key} not found in optimizer state fragment")
+        _, s_off, cnt = self._range()
+        return st[key][s_off: s_off + cnt]
+
+    def get_hp_fragment(self, optim_state_key=None) -> torch.Tensor:
+        return self.hp_fragment if optim_state_key is None else self.get_optim_state_fragment(optim_state_key)
+
+    def update_hp(self) -> None:
+        self.hp_fragment.copy_(self.lp_fragment)
+
+    def update_lp(self) -> None:
+        self.lp_fragment.copy_(self.hp_fragment)
+        self.group.lp_shard_written()
+
+    def get_lp_grad_fragment(self, index_in_param_group=None) -> torch.Tensor:
+        gs = self.group.grad_shard
+        if gs is None:
+            raise ValueError("Gradients are only available immediately after backward and before engine step")
+        _, s_off, cnt = self._range()
+        return gs[s_off: s_off + cnt]
+
+
+tensor_fragment = _Link      # reference name of the record type
 
 
 def link_group_params(fg, optimizer):

@@ -30,6 +30,17 @@ except ImportError:  # pragma: no cover
     _PSUTIL = False
 
 
+class CudaEventTimer:
+    """One (start, end) event pair; the elapsed time is resolved when asked for (reference ``timer.py:32-41``)."""
+
+    def __init__(self, start_event, end_event):
+        self.start_event, self.end_event = start_event, end_event
+
+    def get_elapsed_msec(self) -> float:
+        self.end_event.synchronize()
+        return self.start_event.elapsed_time(self.end_event)
+
+
 class _EventTimer:
     def __init__(self, name):
         self.name_ = name
@@ -54,7 +65,7 @@ class _EventTimer:
         if self._use_events:
             ev1 = get_accelerator().Event(enable_timing=True)
             ev1.record()
-            self.pairs.append((self._ev0, ev1))
+            self.pairs.append(CudaEventTimer(self._ev0, ev1))
         else:
             self.elapsed_ms += (time.perf_counter() - self._t0) * 1e3
         self.started_ = False
@@ -63,8 +74,7 @@ class _EventTimer:
 
     def _resolve(self) -> float:
         if self.pairs:
-            self.pairs[-1][1].synchronize()
-            self.elapsed_ms += sum(a.elapsed_time(b) for a, b in self.pairs)
+            self.elapsed_ms += sum(pair.get_elapsed_msec() for pair in reversed(self.pairs))
             self.pairs = []
         return self.elapsed_ms
 

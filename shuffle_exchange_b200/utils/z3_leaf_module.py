@@ -18,6 +18,13 @@ def get_z3_leaf_modules(model: torch.nn.Module) -> List[torch.nn.Module]:
     return [m for m in model.modules() if z3_leaf_module(m)]
 
 
+def set_z3_leaf_module(model: torch.nn.Module, flag: bool):
+    """Flag (or unflag) this one module; its parameters remember which unit they belong to."""
+    model._z3_leaf = flag
+    for p in model.parameters():
+        p.ds_z3_leaf_module = model if flag else None
+
+
 def _do_set_z3_leaf_modules(model, leaf_module_classes, flag: bool):
     assert all(isinstance(c, (type, str)) for c in leaf_module_classes), \
         f"leaf_module_classes must be a list of types or names, got {leaf_module_classes}"
@@ -26,9 +33,7 @@ def _do_set_z3_leaf_modules(model, leaf_module_classes, flag: bool):
     def _set(m: torch.nn.Module):
         for c in leaf_module_classes:
             if (isinstance(c, type) and m.__class__ == c) or (isinstance(c, str) and m.__class__.__name__ == c):
-                m._z3_leaf = flag
-                for p in m.parameters():
-                    p.ds_z3_leaf_module = m if flag else None
+                set_z3_leaf_module(m, flag)
                 leaf_modules.append(m)
 
     model.apply(_set)

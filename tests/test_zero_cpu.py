@@ -94,6 +94,18 @@ def _fragment_worker(rank, world):
     engine.backward(engine(ids, labels=ids))
     engine.step()
     assert tf.safe_get_full_optimizer_state(p, "exp_avg").shape == want["wte"].shape
+    # the per-parameter mapping object (reference ``param._hp_mapping``): pieces held by the ranks tile the parameter
+    hm = p._hp_mapping
+    assert isinstance(hm, tf.tensor_fragment)
+    a_lp, a_hp = hm.lp_fragment_address, hm.get_hp_fragment_address()
+    assert a_lp.numel == a_hp.numel == hm.get_hp_fragment().numel() == hm.lp_fragment.numel()
+    held = torch.tensor([a_lp.numel], dtype=torch.int64)
+    torch.distributed.all_reduce(held)
+    assert int(held) == p.ds_numel if hasattr(p, "ds_numel") else True
+    assert {"exp_avg", "exp_avg_sq"} <= set(hm.get_optim_state_keys())
+    assert hm.get_hp_fragment("exp_avg").numel() == a_hp.numel
+    full = tf.safe_get_full_fp32_param(p).reshape(-1)
+    assert torch.equal(hm.get_hp_fragment().cpu(), full[a_lp.start: a_lp.start + a_lp.numel].cpu())
     with ds.zero.GatheredParameters(list(engine.module.parameters()), modifier_rank=0):
         if rank == 0:
             engine.module.ln_f_w.data.fill_(3.0)
