@@ -25,6 +25,8 @@ class DtypeEnum(Enum):
                 return member
         raise ValueError(f"{v!r} is not a valid dtype")
 
+    from_str = from_any          # reference spelling (strings only there; torch dtypes are accepted too)
+
 
 class MoETypeEnum(str, Enum):
     residual = "residual"
@@ -123,13 +125,26 @@ class DeepSpeedInferenceConfig(DeepSpeedConfigModel):
 
     @field_validator("dtype", mode="before")
     @classmethod
-    def _dtype(cls, v):
-        return DtypeEnum.from_any(v).value[0] if not isinstance(v, DtypeEnum) else v.value[0]
+    def validate_dtype(cls, v):
+        if isinstance(v, DtypeEnum):
+            return v.value[0]
+        if not isinstance(v, (str, torch.dtype)):
+            raise TypeError(f"Invalid type for dtype: {type(v)}")
+        return DtypeEnum.from_any(v).value[0]
 
     @field_validator("moe", mode="before")
     @classmethod
-    def _moe_bool(cls, v):
-        return DeepSpeedMoEConfig(moe=v) if isinstance(v, bool) and False else ({} if isinstance(v, bool) else v)
+    def moe_backward_compat(cls, v):
+        """Old configs say ``moe: true/false``; that is the ``enabled`` switch of the MoE block."""
+        return {"enabled": v} if isinstance(v, bool) else v
+
+    @field_validator("use_triton")
+    @classmethod
+    def has_triton(cls, v):
+        if v:
+            raise ValueError("use_triton: this framework has no Triton kernel path (its inference kernels are the "
+                             "sm_100a CUDA kernels of csrc/); leave the switch off")
+        return v
 
     @model_validator(mode="after")
     def _legacy(self):

@@ -21,6 +21,12 @@ _grid = None
 _side_stream = None
 
 
+def can_send_recv() -> bool:
+    """Point-to-point send / recv is always available on the torch this package requires (the reference keeps a
+    broadcast fallback for torch < 1.8)."""
+    return True
+
+
 def init_process_groups(grid):
     global _groups, _grid
     _grid = grid

@@ -263,6 +263,9 @@ class PartitionedTensor:
     def local_size(self):
         return self.local_data.size()
 
+    def full_size(self):
+        return self.orig_size
+
 
 def see_memory_usage(message, force=False):
     if not force:

@@ -105,3 +105,22 @@ def reload_optimizer_states(zero_optimizer, non_blocking=False):
     zero_optimizer._offloaded_states = set()
     if not non_blocking and torch.cuda.is_available():
         torch.cuda.synchronize()
+
+
+def get_state_devices(model, state: OffloadStateTypeEnum) -> Set[torch.device]:
+    """Devices currently holding one kind of state of ``model`` (a training engine): what tests and users check after
+    ``engine.offload_states`` / ``reload_states`` (reference ``offload_states.py:49-72``).  States live per flat group
+    here, so the answer is one device per group rather than one per parameter."""
+    opt = model.optimizer
+    groups = getattr(opt, "groups", [])
+    state = OffloadStateTypeEnum(getattr(state, "value", state))
+    if state == OffloadStateTypeEnum.hp_params:
+        return {fg.hp_param.device for fg in groups}
+    if state == OffloadStateTypeEnum.lp_params:
+        return {fg.lp_shard.device for fg in groups}
+    if state == OffloadStateTypeEnum.lp_grads:
+        return {fg.grad_shard.device for fg in groups if getattr(fg, "grad_shard", None) is not None}
+    if state == OffloadStateTypeEnum.contiguous_grad_buffer:
+        return {fg.flat_grad.device for fg in groups if getattr(fg, "flat_grad", None) is not None}
+    inner = getattr(opt, "optimizer", opt)
+    return {v.device for st in inner.state.values() for v in st.values() if torch.is_tensor(v) and v.numel() > 1}

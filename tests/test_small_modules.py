@@ -256,3 +256,21 @@ def test_reference_named_helpers_lr_overrides_groups_debug_comm_switches(capsys)
     assert not comm._off("ALL_REDUCE") and not comm.in_aml() and comm.init_deepspeed_backend("hccl") is None
     with pytest.raises(ValueError):
         comm.init_deepspeed_backend("carrier-pigeon")
+
+
+def test_numa_core_lists_and_memory_policy():
+    import pytest
+    from shuffle_exchange_b200.utils import numa
+    assert numa.parse_range_list("0,2-4,6") == [0, 2, 3, 4, 6]
+    assert list(numa.parse_range("7")) == [7] and list(numa.parse_range("2-3")) == [2, 3]
+    for bad in ("3-1", "1-2-3", "a"):
+        with pytest.raises(ValueError):
+            numa.parse_range(bad)
+    with pytest.raises(ValueError):
+        numa.parse_range_list("0-3,2")                                   # overlap
+    assert numa._format_cores([0, 1, 2, 5, 7, 8]) == "0-2,5,7-8"
+    two = [[0, 1, 2, 3], [4, 5, 6, 7]]
+    assert numa._memory_policy([4, 5], two) == ["-m", "1"]
+    assert numa._memory_policy([3, 4], two) == []                        # spans both domains
+    assert numa._memory_policy([4, 5], two + [[], []]) == ["-p", "3"]    # flat HBM: node 1 pairs with node 3
+    assert numa._memory_policy([0], [[0, 1], [0, 1], [2, 3]]) == ["-m", "0,1"]   # fake NUMA

@@ -198,3 +198,55 @@ def _bf16_optimizer_methods(rank, world):
 
 def test_bf16_optimizer_reference_named_methods():
     run_dist(_bf16_optimizer_methods, world=2)
+
+
+def _offload_states_worker(rank, world, stage):
+    """engine.offload_states / reload_states between steps must not change training: every state tensor is replaced by
+    a moved copy (on this CPU box the "move" is forced to reallocate, which is what exposes stale references)."""
+    import shuffle_exchange_b200 as ds
+    from shuffle_exchange_b200.models import GPT2LMHeadModel, gpt2_config
+    from shuffle_exchange_b200.runtime.zero import offload_states as osm
+    from shuffle_exchange_b200.runtime.zero.offload_states import OffloadStateTypeEnum as K
+
+    moved = []
+
+    def relocating_to(t, device, pin_memory, non_blocking):
+        if t is None:
+            return t
+        moved.append(t.data_ptr())
+        return t.clone()
+
+    def run(offload):
+        torch.manual_seed(0)
+        model = GPT2LMHeadModel(gpt2_config("gpt2-tiny"))
+        engine, _, _, _ = ds.initialize(model=model, config=_cfg(stage), model_parameters=model.parameters())
+        g = torch.Generator().manual_seed(7 + rank)
+        losses = []
+        for step in range(4):
+            ids = torch.randint(0, 512, (2, 16), generator=g)
+            loss = engine(ids, labels=ids)
+            engine.backward(loss)
+            engine.step()
+            losses.append(float(loss))
+            if offload and step in (0, 2):
+                include = None if step == 0 else [K.optim_states, K.hp_params]
+                engine.offload_states(include=include, device="cpu", pin_memory=False)
+                assert osm.get_state_devices(engine, K.hp_params) == {torch.device("cpu")}
+                assert osm.get_state_devices(engine, K.optim_states) == {torch.device("cpu")}
+                engine.reload_states()
+        return losses
+
+    base = run(False)
+    orig = osm._to
+    osm._to = relocating_to
+    try:
+        got = run(True)
+    finally:
+        osm._to = orig
+    assert moved, "nothing was offloaded"
+    assert got == base, (got, base)
+
+
+@pytest.mark.parametrize("stage", [2, 3])
+def test_offload_and_reload_states_keep_training_identical(stage):
+    run_dist(_offload_states_worker, 2, (stage,))
