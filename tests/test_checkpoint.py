@@ -220,3 +220,62 @@ def test_2d_and_3d_layout_reshape_and_zero_checkpoint_merge(tmp_path):
     ea = st["optimizer_state_dict"]["base_optimizer_state"]["state"][0]["exp_avg"]
     assert ea.tolist() == [2.0] * 4 + [3.0] * 4
     assert st["optimizer_state_dict"]["partition_count"] == [2] and st["optimizer_state_dict"]["group_paddings"] == [0]
+
+
+def test_deepspeed_checkpoint_inspector_maps_and_merges(tmp_path, capsys):
+    """A Megatron-DeepSpeed style folder (tp=2, pp=2, dp=2; embedding + 4 blocks + final norm) read under its own
+    layout and under tp=1 / pp=1: file tables, TP merges along the right dimension, mp_rank and ZeRO file selection."""
+    import torch
+    from shuffle_exchange_b200.checkpoint import DeepSpeedCheckpoint
+    H = 4
+    for layer in range(6):                                  # 00 embedding, 01-04 blocks, 05 final norm
+        for tp in range(2):
+            if layer == 0:
+                sd = {"word_embeddings.weight": torch.full((3, H), float(tp))}
+            elif layer == 5:
+                sd = {"weight": torch.full((H,), 7.0)}
+            else:
+                sd = {"input_layernorm.weight": torch.full((H,), float(layer)),
+                      "self_attention.dense.weight": torch.full((H, 2), float(10 * layer + tp)),
+                      "mlp.dense_h_to_4h.weight": torch.full((2, H), float(10 * layer + tp))}
+            torch.save(sd, tmp_path / f"layer_{layer:02d}-model_{tp:02d}-model_states.pt")
+    for mp in range(4):
+        torch.save({"iteration": 11, "args": {"hidden": H}, "checkpoint_info": {"mp": mp},
+                    "module": None}, tmp_path / f"mp_rank_{mp:02d}_model_states.pt")
+        for dp in range(2):
+            torch.save({"optimizer_state_dict": {"base_optimizer_state": {"state": {}}, "group_paddings": [0],
+                                                 "partition_count": [2]}},
+                       tmp_path / f"zero_pp_rank_{dp}_mp_rank_{mp:02d}_optim_states.pt")
+
+    c = DeepSpeedCheckpoint(str(tmp_path))
+    assert (c.original_tp_degree, c.original_pp_degree, c.original_dp_degree) == (2, 2, 2)
+    assert not (c.is_change_tp_degree() or c.is_change_pp_degree() or c.is_change_dp_degree())
+    assert c.get_iteration() == 11 and c.get_args() == {"hidden": H} and c.get_checkpoint_info() == {"mp": 0}
+    assert c.get_embedding_layer_id() == "00" and c.get_final_norm_layer_id() == "05"
+    assert c.get_pp_transformer_map(0) == ["01", "02"] and c.get_pp_transformer_map(1) == ["03", "04"]
+    assert [len(v) for v in c.tp_to_embedding_map.values()] == [1, 1]
+    blocks = c.get_transformer_state(tp_index=1, pp_index=1)
+    assert len(blocks) == 2 and float(blocks[0]["self_attention.dense.weight"][0, 0]) == 31.0
+    assert [os.path.basename(f) for f in c.get_2d_parallel_files(tp_index=1, pp_index=1)] == ["mp_rank_03_model_states.pt"]
+    assert len(c.get_zero_files(pp_index=1, tp_index=0, dp_index=1)) == 1 and len(c.get_zero_files()) == 8
+
+    m = DeepSpeedCheckpoint(str(tmp_path), tp_degree=1, pp_degree=1, dp_degree=1)
+    assert m.is_change_tp_degree() and m.is_change_pp_degree() and m.is_change_dp_degree() and m.world_size == 1
+    assert len(m.get_embedding_files(0)) == 2 and m.get_embedding_state(0)["word_embeddings.weight"].shape == (6, H)
+    blocks = m.get_transformer_state(0, 0)
+    assert len(blocks) == 4
+    b = blocks[2]                                                        # layer 03, both TP slices merged
+    assert b["input_layernorm.weight"].shape == (H,)                     # sequential: taken once
+    assert b["self_attention.dense.weight"].shape == (H, 4)             # row-parallel weight: concatenated on dim 1
+    assert b["self_attention.dense.weight"][0].tolist() == [30.0, 30.0, 31.0, 31.0]
+    assert b["mlp.dense_h_to_4h.weight"].shape == (4, H)                # column-parallel weight: dim 0
+    assert m.get_final_norm_state(0)["weight"].tolist() == [7.0] * H
+    assert len(m.get_2d_parallel_files(0, 0)) == 4 and len(m.get_zero_files(0, 0, 0)) == 8
+    assert m.get_zero_checkpoint_state(0, 0, 0)["optimizer_state_dict"]["partition_count"] == [1]
+    m.show_2d_mapping(); m.show_tp_embedding_map(); m.show_pp_transformer_map(); m.show_transformer_file_map()
+    m.show_tp_final_norm_map(); m.validate_files()
+    out = capsys.readouterr().out
+    assert "[0, 0] = [0, 1, 2, 3]" in out and "pp_to_transformer_layers" in out
+    import pytest
+    with pytest.raises(AssertionError):
+        DeepSpeedCheckpoint(str(tmp_path), tp_degree=4)                  # growing a degree is not a reshape
