@@ -75,6 +75,8 @@ class InferenceEngineV2:
         seqs = []
         for uid, tokens in zip(batch_uids, batch_tokens):
             seq = self._state_manager.get_or_create_sequence(uid)
+            if seq.is_offloaded:
+                self._state_manager.restore_sequence(uid)
             self._model.maybe_allocate_kv(seq, tokens.numel())
             seq.pre_forward(tokens.numel())
             self._batch.insert_sequence(seq, tokens.reshape(-1).cpu(), do_checks=do_checks)
@@ -126,6 +128,14 @@ class InferenceEngineV2:
 
     def flush(self, uid: int) -> None:
         self._state_manager.flush_sequence(uid)
+
+    def offload(self, uid: int) -> int:
+        """Suspend an idle sequence: its KV blocks go to host memory and become free for other sequences; returns the
+        number of blocks released.  ``put`` restores the sequence by itself when it is scheduled again."""
+        return self._state_manager.offload_sequence(uid)
+
+    def restore(self, uid: int) -> int:
+        return self._state_manager.restore_sequence(uid)
 
     def serialize(self, save_path: str) -> None:
         """Write this rank's (sharded, fused, possibly quantised) parameters as one flat buffer plus its table of

@@ -62,6 +62,36 @@ class BlockedKVCache:
     def get_cache(self, layer: int) -> torch.Tensor:
         return self._cache[layer]
 
+    # ----------------------------------------------------------------------- host offload of blocks
+    def offload(self, blocks) -> torch.Tensor:
+        """Copy ``blocks`` (all layers) to host memory and return their block ids to the free list.  Returns the host
+        tensor ``[n_layers, len(blocks), block_size, 2, n_kv_heads, head_dim]`` (pinned when the cache is on a GPU) —
+        the caller keeps it and hands it back to :meth:`restore`.  (The reference declares both methods and raises
+        ``NotImplementedError``, ``kv_cache.py:166-184``.)"""
+        ids = torch.as_tensor(blocks, dtype=torch.long).reshape(-1)
+        picked = self._cache.index_select(1, ids.to(self._cache.device))
+        if self._cache.is_cuda:
+            host = torch.empty(picked.shape, dtype=picked.dtype, device="cpu", pin_memory=True)
+            host.copy_(picked, non_blocking=True)
+            torch.cuda.current_stream(self._cache.device).synchronize()   # blocks are reusable once this returns
+        else:
+            host = picked.clone()
+        self._allocator.free(ids.to(torch.int32))
+        return host
+
+    def restore(self, host: torch.Tensor) -> torch.Tensor:
+        """Allocate as many blocks as ``host`` holds, copy it back and return the new block ids (they differ from the
+        ids the data was offloaded from; the sequence's block table is what gives them meaning)."""
+        n = host.shape[1]
+        ids = self._allocator.allocate(n)
+        self._cache.index_copy_(1, ids.to(device=self._cache.device, dtype=torch.long),
+                                host.to(self._cache.device, non_blocking=True))
+        return ids
+
+    @property
+    def num_caches(self) -> int:
+        return self._cache.shape[0]
+
     @property
     def free_blocks(self) -> int:
         return self._allocator.free_blocks

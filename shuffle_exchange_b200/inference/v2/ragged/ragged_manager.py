@@ -62,7 +62,36 @@ class DSStateManager:
         seq = self._seqs.pop(uid, None)
         if seq is None:
             return
-        self._kv_cache.free(seq.kv_blocks())
+        if not seq.is_offloaded:
+            self._kv_cache.free(seq.kv_blocks())
+
+    # ------------------------------------------------------------------ suspending sequences to host
+    def offload_sequence(self, uid: int) -> int:
+        """Move the KV blocks of a tracked, idle sequence to host memory; returns the number of blocks released.  The
+        sequence stays tracked (its token count is kept) and must be restored before its next forward."""
+        seq = self._seqs[uid]
+        if seq.is_offloaded or seq.cur_allocated_blocks == 0:
+            return 0
+        if seq.in_flight_tokens:
+            raise RuntimeError(f"sequence {uid} has tokens in flight")
+        n = seq.cur_allocated_blocks
+        seq.detach_kv(self._kv_cache.offload(seq.kv_blocks()))
+        return n
+
+    def restore_sequence(self, uid: int) -> int:
+        """Bring an offloaded sequence's KV blocks back (into whichever blocks are free now)."""
+        seq = self._seqs[uid]
+        if not seq.is_offloaded:
+            return 0
+        n = seq._host_kv.shape[1]
+        if n > self.free_blocks:
+            raise ValueError(f"restoring sequence {uid} needs {n} KV blocks, {self.free_blocks} are free")
+        seq.attach_kv(self._kv_cache.restore(seq._host_kv))
+        return n
+
+    @property
+    def n_kv_cache_groups(self) -> int:
+        return 1
 
     def allocate_blocks(self, n_blocks: int) -> torch.Tensor:
         return self._kv_cache.reserve(n_blocks)

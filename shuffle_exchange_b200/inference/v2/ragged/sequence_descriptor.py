@@ -46,6 +46,7 @@ class DSSequenceDescriptor(BaseSequenceDescriptor):
         self._in_flight_tokens = 0
         self._blocks = torch.zeros(max_blocks, dtype=torch.int32)
         self._n_blocks = 0
+        self._host_kv = None          # host copy of the KV blocks while the sequence is offloaded
 
     @property
     def tracking_id(self) -> int:
@@ -69,6 +70,36 @@ class DSSequenceDescriptor(BaseSequenceDescriptor):
 
     def kv_blocks(self) -> torch.Tensor:
         return self._blocks[: self._n_blocks]
+
+    def kv_cache_ids(self, cache_group: int = 0, on_device: bool = False) -> torch.Tensor:
+        """The whole block table of the sequence (its first ``cur_allocated_blocks`` entries are valid).  The table
+        lives on the host; the batch wrapper copies the valid part into its staging buffer per forward, so there is
+        no per-sequence device copy to return."""
+        if on_device:
+            raise ValueError("block tables are staged per batch (RaggedBatchWrapper), not kept per sequence on device")
+        return self._blocks
+
+    @property
+    def kv_blocks_ptr(self) -> int:
+        return self._blocks.data_ptr()
+
+    @property
+    def is_offloaded(self) -> bool:
+        return self._host_kv is not None
+
+    def detach_kv(self, host_kv: torch.Tensor) -> None:
+        """The sequence's KV blocks now live in ``host_kv`` (see ``BlockedKVCache.offload``); it owns no device block."""
+        self._host_kv, self._n_blocks = host_kv, 0
+
+    def attach_kv(self, new_ids: torch.Tensor) -> torch.Tensor:
+        host, self._host_kv = self._host_kv, None
+        self._n_blocks = 0
+        self.extend_kv_cache(new_ids)
+        return host
+
+    def free_kv_cache(self, free_ids, cache_group: int = 0) -> None:
+        raise NotImplementedError("Partial KV-cache freeing is not supported: dense causal attention reads every "
+                                  "block of the sequence; use DSStateManager.offload_sequence to release memory")
 
     def all_block_ids(self) -> torch.Tensor:
         return self.kv_blocks()

@@ -52,3 +52,28 @@ def test_scheduling_and_flush_cpu():
     assert eng.get_remaining_block_capacity(5) == 2
     eng.flush(5)
     assert eng.free_blocks == free0
+
+
+def test_offloaded_sequence_resumes_with_identical_logits_cpu():
+    """Suspend a sequence to host memory, let another sequence take (and overwrite) its KV blocks, then continue the
+    first one: the next-token logits must equal an uninterrupted run's."""
+    lm, eng = _engine()
+    a = torch.randint(0, 1000, (13,))
+    b = torch.randint(0, 1000, (30,))
+    free0 = eng.free_blocks
+    out = eng.put([1], [a])
+    nxt = out[0].argmax().view(1)
+    released = eng.offload(1)
+    assert released == 4 and eng.free_blocks == free0                      # ceil(13 / 4) blocks back on the free list
+    assert eng.offload(1) == 0                                              # already on the host
+    eng.put([2], [b])                                                       # reuses the released block ids
+    tokens, blocks = eng.query(1, 1, eng.free_blocks)
+    assert (tokens, blocks) == (1, 4)                                       # resuming needs its 4 blocks again (14 tokens)
+    got = eng.put([1], [nxt])                                               # restores by itself
+    with torch.no_grad():
+        ref = lm(torch.cat([a, nxt])[None])[0, -1]
+    assert torch.allclose(got[0], ref, atol=2e-4, rtol=1e-3)
+    eng.offload(2)
+    eng.flush(2)                                                            # flushing a suspended sequence frees nothing twice
+    eng.flush(1)
+    assert eng.free_blocks == free0
