@@ -48,3 +48,39 @@ class DominoAsyncColumnParallelLinear(nn.Module):
 
     def forward(self, inp, handle_dic=None, h_id=None):
         return DominoAsyncColumnParallelLinearImpl.apply(inp, self.weight, self.bias, handle_dic, h_id, self.tp_group)
+
+
+class RowParallelLinearNoComm(nn.Module):
+    """Row-parallel linear that does NOT reduce its output: ``forward`` returns ``(partial_output, bias)`` and the caller
+    (the Domino schedule) all-reduces the partial result asynchronously and adds the bias after the wait (reference
+    ``async_linear.py:95-140``).  Weight ``[output_size, input_size / tp]``; the bias is replicated."""
+
+    def __init__(self, input_size: int, output_size: int, _tp_group=None, config=None,
+                 init_method=nn.init.xavier_normal_, bias: bool = True, skip_bias_add: bool = True):
+        super().__init__()
+        tp = dist.get_world_size(group=_tp_group) if (_tp_group is not None and dist.is_initialized()) else 1
+        assert input_size % tp == 0
+        self.weight = nn.Parameter(torch.empty(output_size, input_size // tp))
+        init_method(self.weight)
+        self.bias = nn.Parameter(torch.zeros(output_size)) if bias else None
+        self.skip_bias_add = skip_bias_add
+
+    def forward(self, input_):
+        out = _PartialLinear.apply(input_, self.weight)
+        if self.skip_bias_add or self.bias is None:
+            return out, self.bias
+        return out + self.bias, None
+
+
+class _PartialLinear(torch.autograd.Function):
+    """``x W^T`` on this framework's GEMM with explicit dgrad / wgrad."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        ctx.save_for_backward(x, weight)
+        return F.matmul_nt(x, weight)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        return F.matmul_nn(g, w), F.matmul_tn(g, x)

@@ -141,14 +141,68 @@ class DominoTransformerLayer(nn.Module):
 
 
 class DominoTransformer(nn.Module):
+    """Stack of Domino layers with the reference's two schedules (``transformer.py:467-605``):
+
+    * ``intra_layer_overlap=True`` — every layer ping-pongs its two half-batches and joins them at its end;
+    * inter-layer overlap (the default, as in the reference) — the half-batches are never joined between layers, so the
+      last all-reduce of layer ``i`` for one half overlaps the first GEMMs of layer ``i + 1`` for the other half.
+
+    The inter-layer schedule is written as one generator per half-batch that runs through the WHOLE stack and yields
+    each time it has issued an asynchronous all-reduce; :meth:`_interleave` resumes the halves round-robin, so a half
+    waits for its reduction only after the other half has been given the device.  The order of operations this
+    produces is the reference's hand-unrolled one; the layer count and the number of halves are free."""
+
     def __init__(self, num_layers: int, hidden_size: int, num_heads: int, ffn_hidden_size: Optional[int] = None,
-                 tp_group=None, post_layer_norm: bool = True, **kw):
+                 tp_group=None, post_layer_norm: bool = True, intra_layer_overlap: bool = False, **kw):
         super().__init__()
         self.layers = nn.ModuleList([DominoTransformerLayer(hidden_size, num_heads, ffn_hidden_size, tp_group, **kw)
                                      for _ in range(num_layers)])
         self.final_layernorm = nn.LayerNorm(hidden_size) if post_layer_norm else None
+        self.tp_group = tp_group
+        self.intra_layer_overlap = intra_layer_overlap
 
     def forward(self, hidden_states, attention_mask=None, rotary_pos_emb=None):
+        if self.intra_layer_overlap or hidden_states.shape[0] < 2:
+            return self.intra_layer_overlap_forward(hidden_states, attention_mask, rotary_pos_emb)
+        return self.inter_layer_overlap_forward(hidden_states, attention_mask, rotary_pos_emb)
+
+    def intra_layer_overlap_forward(self, hidden_states, attention_mask=None, rotary_pos_emb=None):
         for layer in self.layers:
             hidden_states = layer(hidden_states, attention_mask, rotary_pos_emb)
         return self.final_layernorm(hidden_states) if self.final_layernorm is not None else hidden_states
+
+    def _half_batch_stream(self, h, mb: int):
+        """One half-batch through every layer; yields after each issued all-reduce, returns the final hidden state."""
+        D = DominoUtil.HANDLE_DIC
+        k_attn, k_mlp = str(mb), str(2 + mb)
+        for layer in self.layers:
+            x = _WaitInputGrad.apply(layer.input_layernorm(h), D, k_attn)
+            pending = _AsyncReduce(layer._attn_partial(x, k_attn), layer.tp_group)
+            yield
+            h = h + TF.dropout(pending.wait() + layer.dense_bias, layer.hidden_p, layer.training)
+            x = _WaitInputGrad.apply(layer.post_attention_layernorm(h), D, k_mlp)
+            pending = _AsyncReduce(layer._mlp_partial(x, k_mlp), layer.tp_group)
+            yield
+            h = h + TF.dropout(pending.wait() + layer.mlp_bias, layer.hidden_p, layer.training)
+        return self.final_layernorm(h) if self.final_layernorm is not None else h
+
+    @staticmethod
+    def _interleave(streams):
+        """Resume the generators in turn until all have returned; -> their return values in order."""
+        results = [None] * len(streams)
+        live = list(enumerate(streams))
+        while live:
+            still = []
+            for i, g in live:
+                try:
+                    next(g)
+                    still.append((i, g))
+                except StopIteration as done:
+                    results[i] = done.value
+            live = still
+        return results
+
+    def inter_layer_overlap_forward(self, hidden_states, attention_mask=None, rotary_pos_emb=None):
+        halves = hidden_states.chunk(2, dim=0)
+        outs = self._interleave([self._half_batch_stream(h, mb) for mb, h in enumerate(halves)])
+        return torch.cat(outs, dim=0)
