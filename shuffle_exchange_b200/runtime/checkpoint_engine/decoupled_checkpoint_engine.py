@@ -1,6 +1,8 @@
 """Checkpointing decoupled from the training loop: ``save`` snapshots the state dict into host memory (pinned, async D2H)
-and returns; a background writer drains the queue to storage; ``commit`` of checkpoint *k* only waits for the snapshot,
-durability is awaited at the NEXT ``create``/``cleanup`` (reference:
+and returns; a background writer drains the queue to storage while training continues.  ``save_checkpoint`` leaves a
+:class:`CheckpointCommitInfo` with the engine instead of committing; the training engine commits at its next optimizer
+step (or at ``destroy``): ``commit`` waits until every queued file is on storage, and only then does the caller move
+the ``latest`` marker — a crash in between leaves ``latest`` on the previous, complete checkpoint (reference:
 ``runtime/checkpoint_engine/decoupled_checkpoint_engine.py:30-260``, which uses a separate process fed through a
 multiprocessing queue; a daemon thread suffices here because the writer spends its time in IO syscalls and native
 serialisation, both of which release the GIL)."""
@@ -38,6 +40,7 @@ class DecoupledCheckpointEngine(FastCheckpointEngine):
         self._thread = threading.Thread(target=self._drain, name="sxb-ckpt-writer", daemon=True)
         self._thread.start()
         self._pending_tag = None
+        self.commit_info = None
 
     def is_decoupled(self):
         return True
@@ -68,8 +71,19 @@ class DecoupledCheckpointEngine(FastCheckpointEngine):
             torch.cuda.current_stream().synchronize()       # D2H copies of the snapshot are complete
         self._q.put((snap, path))
 
+    def set_commit_info(self, info):
+        assert self.commit_info is None, f"checkpoint {self.commit_info} has not been committed yet"
+        self.commit_info = info
+
+    def get_commit_info(self):
+        return self.commit_info
+
     def commit(self, info):
-        log_dist(f"[Decoupled] Checkpoint {info} handed to the background writer", ranks=[0])
+        """Blocks until every file handed to the writer is on storage; raises if a write failed."""
+        assert self.commit_info is None or info == self.commit_info, (info, self.commit_info)
+        self._wait_durable()
+        self.commit_info = None
+        log_dist(f"[Decoupled] Checkpoint {info} is durable", ranks=[0])
         return True
 
     def _wait_durable(self):

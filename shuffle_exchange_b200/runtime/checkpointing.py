@@ -110,6 +110,8 @@ def save_checkpoint(self, save_dir, tag=None, client_state={}, save_latest=True,
     if tag is None:
         tag = f"global_step{self.global_steps}"
     tag = str(tag)
+    if self.checkpoint_engine.is_decoupled():
+        self._commit_decoupled_checkpoint()          # two saves with no optimizer step in between
     self.checkpoint_engine.create(tag)
     self._checkpoint_tag_validation(tag)
     os.makedirs(os.path.join(save_dir, tag), exist_ok=True)
@@ -126,26 +128,31 @@ def save_checkpoint(self, save_dir, tag=None, client_state={}, save_latest=True,
     if self.zero_has_nvme_offload():
         from .swap_tensor.utils import copy_swap_folder
         copy_swap_folder(self, os.path.join(save_dir, tag, "offloaded_tensors"))
-    commit_now = not getattr(self.checkpoint_engine, "is_decoupled", lambda: False)()
-    if commit_now:
+    if not self.checkpoint_engine.is_decoupled():
         self.checkpoint_engine.commit(tag)
         if save_latest and self.global_rank == 0:
             with open(os.path.join(save_dir, CKPT_LATEST), "w") as fd:
                 fd.write(tag)
     else:
-        self._decoupled_commit_pending = (save_dir, tag, save_latest)
+        from .checkpoint_engine.checkpoint_engine import CheckpointCommitInfo
+        self.checkpoint_engine.set_commit_info(CheckpointCommitInfo(tag=tag, save_dir=save_dir, save_latest=save_latest))
     if dist.is_initialized():
         dist.barrier()
     return True
 
 
 def _commit_decoupled_checkpoint(self):
-    save_dir, tag, save_latest = self._decoupled_commit_pending
-    self._decoupled_commit_pending = False
-    self.checkpoint_engine.commit(tag)
-    if save_latest and self.global_rank == 0:
-        with open(os.path.join(save_dir, CKPT_LATEST), "w") as fd:
-            fd.write(tag)
+    """Finish the checkpoint a decoupled engine has been writing in the background: wait until it is durable, then move
+    ``latest``.  Called at the next optimizer step and from ``destroy`` (reference ``engine.py:3437-3452``)."""
+    info = self.checkpoint_engine.get_commit_info()
+    if info is None:
+        return
+    self.checkpoint_engine.commit(info)
+    if info.save_latest and self.global_rank == 0:
+        with open(os.path.join(info.save_dir, CKPT_LATEST), "w") as fd:
+            fd.write(info.tag)
+    if dist.is_initialized():
+        dist.barrier()
 
 
 def _model_state_payload(self, client_state, exclude_frozen_parameters, module_sd):

@@ -701,7 +701,7 @@ class DeepSpeedEngine(nn.Module):
                 hook()
             self._take_model_step(lr_kwargs)
             report = True
-            if getattr(self, "_decoupled_commit_pending", False):
+            if self.checkpoint_engine is not None and self.checkpoint_engine.is_decoupled():
                 self._commit_decoupled_checkpoint()
         self.tput_timer.stop(global_step=self.is_gradient_accumulation_boundary(), report_speed=report)
         self._stop_timers(self.engine_timers.step_timers)
@@ -1179,7 +1179,9 @@ class DeepSpeedEngine(nn.Module):
     def destroy(self):
         if self.optimizer is not None and hasattr(self.optimizer, "destroy"):
             self.optimizer.destroy()
-        if self.checkpoint_engine is not None and hasattr(self.checkpoint_engine, "cleanup"):
+        if self.checkpoint_engine is not None:
+            if self.checkpoint_engine.is_decoupled():
+                self._commit_decoupled_checkpoint()        # a checkpoint saved after the last step still gets its marker
             self.checkpoint_engine.cleanup()
 
     def empty_partition_cache(self):

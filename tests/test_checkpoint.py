@@ -279,3 +279,71 @@ def test_deepspeed_checkpoint_inspector_maps_and_merges(tmp_path, capsys):
     import pytest
     with pytest.raises(AssertionError):
         DeepSpeedCheckpoint(str(tmp_path), tp_degree=4)                  # growing a degree is not a reshape
+
+
+def _decoupled_worker(rank, world, root):
+    """Decoupled checkpointing: save_checkpoint returns while files are still being written; the ``latest`` marker moves
+    only at the next optimizer step (after the files are durable), or at destroy(); a slow writer must not let it move
+    early; the result loads back."""
+    import threading
+    import time
+    import shuffle_exchange_b200 as ds
+    from shuffle_exchange_b200.models import GPT2LMHeadModel, gpt2_config
+    from shuffle_exchange_b200.runtime.checkpoint_engine import fast_checkpoint_engine as fce
+    from shuffle_exchange_b200.runtime.checkpoint_engine.decoupled_checkpoint_engine import DecoupledCheckpointEngine
+
+    gate = threading.Event()
+    slow_save = fce.FastCheckpointEngine.save
+
+    def held_back(self, state, path):
+        gate.wait(timeout=60)                           # the background writer is stuck until the test lets it go
+        return slow_save(self, state, path)
+
+    cfg = {"train_micro_batch_size_per_gpu": 2, "steps_per_print": 10 ** 9, "bf16": {"enabled": True},
+           "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}}, "zero_optimization": {"stage": 2},
+           "checkpoint": {"writer": {"type": "python", "decoupled": True}}}
+    torch.manual_seed(0)
+    model = GPT2LMHeadModel(gpt2_config("gpt2-tiny"))
+    engine, _, _, _ = ds.initialize(model=model, config=cfg, model_parameters=model.parameters())
+    assert isinstance(engine.checkpoint_engine, DecoupledCheckpointEngine) and engine.checkpoint_engine.is_decoupled()
+    ids = torch.randint(0, 512, (2, 16))
+
+    def step():
+        engine.backward(engine(ids, labels=ids))
+        engine.step()
+
+    step()
+    fce.FastCheckpointEngine.save = held_back
+    try:
+        t0 = time.time()
+        engine.save_checkpoint(root, tag="a")
+        assert time.time() - t0 < 30                    # did not wait for the (blocked) writer
+        info = engine.checkpoint_engine.get_commit_info()
+        assert info is not None and (info.tag, info.save_dir, info.save_latest) == ("a", root, True)
+        assert not os.path.exists(os.path.join(root, "latest"))
+        threading.Timer(1.0, gate.set).start()
+        step()                                          # commits: blocks until the writer has finished
+    finally:
+        fce.FastCheckpointEngine.save = slow_save
+    assert gate.is_set() and engine.checkpoint_engine.get_commit_info() is None
+    td = torch.distributed
+    td.barrier()
+    assert open(os.path.join(root, "latest")).read() == "a"
+    files = os.listdir(os.path.join(root, "a"))
+    assert "mp_rank_00_model_states.pt" in files and sum("optim_states" in f for f in files) == world
+    # a save right before destroy still gets its marker
+    engine.save_checkpoint(root, tag="b")
+    engine.destroy()
+    td.barrier()
+    assert open(os.path.join(root, "latest")).read() == "b"
+    # and loads
+    torch.manual_seed(0)
+    e2, _, _, _ = ds.initialize(model=GPT2LMHeadModel(gpt2_config("gpt2-tiny")), config=cfg)
+    path, _ = e2.load_checkpoint(root)
+    assert path is not None and e2.global_steps == 2
+    e2.destroy()
+
+
+def test_decoupled_checkpoint_engine_commits_only_when_durable(tmp_path):
+    from conftest import run_dist
+    run_dist(_decoupled_worker, 2, (str(tmp_path),))
