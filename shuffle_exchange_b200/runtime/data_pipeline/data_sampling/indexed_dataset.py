@@ -42,34 +42,48 @@ def data_file_path(prefix_path: str) -> str:
 
 
 def get_available_dataset_impl():
-    return ["mmap"]
+    return ["lazy", "cached", "mmap"]
 
 
 def infer_dataset_impl(path):
-    if not MMapIndexedDataset.exists(path):
+    """Which reader the files at ``path`` (+ ``.idx`` / ``.bin``) need: the index magic tells the two formats apart."""
+    if not IndexedDataset.exists(path):
+        print(f"Dataset does not exist: {path}")
+        print("Path should be a basename that both .idx and .bin can be appended to get full filenames.")
         return None
     with open(index_file_path(path), "rb") as f:
-        return "mmap" if f.read(9) == _MAGIC else None
+        magic = f.read(9)
+    if magic[:8] == _LEGACY_MAGIC:
+        return "cached"
+    return "mmap" if magic == _MAGIC else None
 
 
 def dataset_exists(path, impl="mmap"):
-    return MMapIndexedDataset.exists(path)
+    return MMapIndexedDataset.exists(path) if impl == "mmap" else IndexedDataset.exists(path)
 
 
 def make_builder(out_file, impl="mmap", vocab_size=None):
-    dtype = np.uint16 if vocab_size is not None and vocab_size < 65500 else np.int32
-    return MMapIndexedDatasetBuilder(out_file, dtype=dtype)
+    if impl == "mmap":
+        dtype = np.uint16 if vocab_size is not None and vocab_size < 65500 else np.int32
+        return MMapIndexedDatasetBuilder(out_file, dtype=dtype)
+    return IndexedDatasetBuilder(out_file)
 
 
 def make_dataset(path, impl="mmap", skip_warmup=False):
-    if not MMapIndexedDataset.exists(path):
+    if not IndexedDataset.exists(path):
         print(f"Dataset does not exist: {path}")
+        print("Path should be a basename that both .idx and .bin can be appended to get full filenames.")
         return None
     if impl == "infer":
         impl = infer_dataset_impl(path)
-    if impl != "mmap":
-        raise ValueError(f"dataset implementation '{impl}' is not supported (mmap only)")
-    return MMapIndexedDataset(path, skip_warmup)
+    if impl == "lazy":
+        return IndexedDataset(path)
+    if impl == "cached":
+        return IndexedCachedDataset(path)
+    if impl == "mmap":
+        return MMapIndexedDataset(path, skip_warmup)
+    print(f"Unknown dataset implementation: {impl}")
+    return None
 
 
 class _Index:
