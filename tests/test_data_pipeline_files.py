@@ -72,3 +72,109 @@ def test_legacy_indexed_dataset_round_trip(tmp_path):
     assert np.array_equal(np.asarray(cached[3]), docs[3])
     with pytest.raises(IndexError):
         ds[len(docs)]
+
+
+class _SeqDataset(torch.utils.data.Dataset):
+    """Sample i is a vector of length 1 + (7 i mod 13): its 'difficulty' is its length."""
+
+    def __init__(self, n):
+        self.n = n
+
+    def __len__(self):
+        return self.n
+
+    def __getitem__(self, i):
+        return torch.full((1 + (7 * i) % 13,), i, dtype=torch.int64)
+
+
+def _len_metric(batch):
+    return torch.tensor([len(x) for x in batch])
+
+
+def _token_histogram(batch):
+    return torch.tensor([sum(len(x) for x in batch), len(batch)])
+
+
+def _check_analyzer_output(root, n):
+    ds = _SeqDataset(n)
+    lens = np.array([len(ds[i]) for i in range(n)])
+    folder = f"{root}/seqlen"
+    s2m = ids.MMapIndexedDataset(f"{folder}/seqlen_sample_to_metric", skip_warmup=True)
+    assert [int(s2m[i][0]) for i in range(n)] == lens.tolist()
+    i2m = ids.MMapIndexedDataset(f"{folder}/seqlen_index_to_metric", skip_warmup=True)
+    i2s = ids.MMapIndexedDataset(f"{folder}/seqlen_index_to_sample", skip_warmup=True)
+    values = [int(i2m[k][0]) for k in range(len(i2m))]
+    assert values == sorted(set(lens.tolist()))
+    for k, v in enumerate(values):
+        assert sorted(np.asarray(i2s[k]).tolist()) == np.nonzero(lens == v)[0].tolist()
+    pct = ids.MMapIndexedDataset(f"{folder}/seqlen_index_to_sample_percentile_merged", skip_warmup=True)
+    merged = np.concatenate([np.asarray(pct[k]) for k in range(len(pct))])
+    assert len(pct) == 100 and sorted(merged.tolist()) == list(range(n))
+    assert (np.diff(lens[merged]) >= 0).all()                      # percentiles are ordered by difficulty
+
+
+def test_data_analyzer_two_workers_map_then_reduce(tmp_path):
+    from shuffle_exchange_b200.runtime.data_pipeline.data_sampling.data_analyzer import ACCUMULATE, SINGLE, DataAnalyzer
+    n, root = 103, str(tmp_path)
+    common = dict(batch_size=8, metric_names=["seqlen", "totals"], metric_functions=[_len_metric, _token_histogram],
+                  metric_types=[SINGLE, ACCUMULATE], metric_dtypes=[np.int64, np.int64], save_path=root,
+                  collate_fn=lambda xs: xs, num_workers=2)
+    for w in range(2):
+        DataAnalyzer(_SeqDataset(n), worker_id=w, **common).run_map()
+    DataAnalyzer(_SeqDataset(n), worker_id=0, **common).run_reduce()
+    _check_analyzer_output(root, n)
+    tot = ids.MMapIndexedDataset(f"{root}/totals/totals_metric_value", skip_warmup=True)
+    assert np.asarray(tot[0]).tolist() == [sum(1 + (7 * i) % 13 for i in range(n)), n]
+    pcts = DataAnalyzer.get_metric_value_percentiles("seqlen", {1: 10, 5: 40, 9: 50}, 100)
+    assert pcts == {10: 1, 50: 5, 100: 9}
+
+
+def _dist_analyzer_worker(rank, world, root):
+    from shuffle_exchange_b200.runtime.data_pipeline.data_sampling.data_analyzer import SINGLE, DistributedDataAnalyzer
+    DistributedDataAnalyzer(_SeqDataset(57), batch_size=4, metric_names=["seqlen"], metric_functions=[_len_metric],
+                            metric_types=[SINGLE], save_path=root, collate_fn=lambda xs: xs).run_map_reduce()
+    if rank == 0:
+        _check_analyzer_output(root, 57)
+
+
+def test_distributed_data_analyzer_three_ranks(tmp_path):
+    from conftest import run_dist
+    run_dist(_dist_analyzer_worker, 3, (str(tmp_path),))
+
+
+def test_variable_batch_size_packing_and_lr_scaling():
+    from shuffle_exchange_b200.runtime.data_pipeline.data_sampling import variable_batch_size_and_lr as vb
+    seqlens = [5, 9, 3, 12, 7, 2, 8, 4, 6, 30, 1, 10]
+    mb_ids, batch_sizes, max_seqlens = vb.batch_by_seqlens(seqlens, max_tokens=16, effective_batch_size=2)
+    flat = [i for _, mb in mb_ids for i in mb]
+    assert 9 not in flat                                              # 30 tokens can never fit
+    assert len(flat) == len(set(flat))                                # nobody is used twice
+    for bid, mb in mb_ids:
+        assert sum(seqlens[i] for i in mb) <= 16
+    assert len(mb_ids) == 2 * len(batch_sizes)                        # two micro-batches per optimizer step
+    for b, (size, mx) in enumerate(zip(batch_sizes, max_seqlens)):
+        members = [i for bid, mb in mb_ids if bid == b for i in mb]
+        assert size == len(members) and mx == max(seqlens[i] for i in members)
+    # same-size micro-batches for pipelines
+    mb2, _, _ = vb.batch_by_seqlens(seqlens, max_tokens=16, effective_batch_size=2, required_microbatches_of_same_size=True,
+                                    sequence_picking_order="seqlen")
+    for b in range(len(mb2) // 2):
+        assert len(mb2[2 * b][1]) == len(mb2[2 * b + 1][1])
+    assert vb.scale_lr(8, 16, 1.0, "linear") == 2.0 and abs(vb.scale_lr(8, 32, 1.0, "sqrt") - 2.0) < 1e-12
+    assert vb.scale_lr(8, 16, 0.5, None) == 0.5
+
+    ds = _SeqDataset(len(seqlens))
+    w = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.SGD([w], lr=0.1)
+    loader, sched = vb.get_dataloader_and_lr_scheduler_for_variable_batch_size(
+        dataset=ds, dataset_seqlens=seqlens, max_tokens=16, effective_batch_size=2, base_batch_size=4,
+        lr_scheduler_or_optimizer=opt, dataloader_num_workers=0)
+    batches = list(loader)
+    assert [len(b) for b in batches] == [len(mb) for _, mb in mb_ids]
+    assert abs(opt.param_groups[0]["lr"] - 0.1 * batch_sizes[0] / 4) < 1e-12       # scaled for the first batch
+    sched.step()
+    assert abs(opt.param_groups[0]["lr"] - 0.1 * batch_sizes[1 % len(batch_sizes)] / 4) < 1e-12
+    sd = sched.state_dict()
+    sched.step()
+    sched.load_state_dict(sd)
+    assert sched.last_epoch == 1
