@@ -5,28 +5,44 @@ the same DeepSpeed variables) and which restarts the worker group on membership 
 from __future__ import annotations
 
 import os
-import time
 from typing import Any, Dict
 
 from torch.distributed.elastic.agent.server.api import RunResult, WorkerGroup, WorkerSpec, WorkerState
 from torch.distributed.elastic.agent.server.local_elastic_agent import LocalElasticAgent
-from torch.distributed.elastic.metrics import put_metric
-from torch.distributed.elastic.multiprocessing import Std
 
 from ..utils.logging import logger
 
 
+def _participants(rdzv_handler) -> int:
+    """Number of nodes in the current rendezvous round (dynamic / c10d rendezvous keeps it in its state holder)."""
+    holder = getattr(rdzv_handler, "_state_holder", None)
+    state = getattr(holder, "state", None)
+    return len(getattr(state, "participants", ()) or ())
+
+
 class DSElasticAgent(LocalElasticAgent):
+    """``LocalElasticAgent`` with two additions:
+
+    * workers start with the launcher's environment ``env`` on top of the agent's own, so every restart sees the same
+      launcher variables;
+    * a node LEAVING the rendezvous makes the group unhealthy.  torch's agent loop restarts the group when workers
+      fail or when nodes are waiting to join; the reference's copy of that loop (``elastic_agent.py:127-191``) adds the
+      scale-down case by comparing the participant count with the one at the last (re)start.  Here the same rule sits in
+      ``_monitor_workers``, so the stock loop does the restarting (and counts it against ``max_restarts``)."""
+
     def __init__(self, spec: WorkerSpec, env: Dict, start_method="spawn", exit_barrier_timeout: float = 300,
                  log_dir=None):
         try:
-            super().__init__(spec, start_method=start_method, exit_barrier_timeout=exit_barrier_timeout, log_dir=log_dir)
-        except TypeError:      # newer torch: log_dir replaced by logs_specs
-            super().__init__(spec, start_method=start_method, exit_barrier_timeout=exit_barrier_timeout)
+            from torch.distributed.elastic.multiprocessing import DefaultLogsSpecs
+            super().__init__(spec, logs_specs=DefaultLogsSpecs(log_dir=log_dir), start_method=start_method,
+                             exit_barrier_timeout=exit_barrier_timeout)
+        except (ImportError, TypeError):       # torch < 2.2: the agent takes log_dir itself
+            super().__init__(spec, start_method=start_method, exit_barrier_timeout=exit_barrier_timeout,
+                             log_dir=log_dir)
         self.ds_env = env
+        self._participants_at_start = 0
 
     def _start_workers(self, worker_group: WorkerGroup) -> Dict[int, Any]:
-        # inject the launcher environment into the entrypoint's environment before delegating
         saved = {}
         for k, v in (self.ds_env or {}).items():
             saved[k] = os.environ.get(k)
@@ -40,53 +56,25 @@ class DSElasticAgent(LocalElasticAgent):
                 else:
                     os.environ[k] = v
 
-    def _invoke_run(self, role: str = "default") -> RunResult:
-        spec = self._worker_group.spec
-        role = spec.role
-        logger.info(f"[{role}] starting workers for entrypoint: {spec.get_entrypoint_name()}")
-        self._initialize_workers(self._worker_group)
-        monitor_interval = spec.monitor_interval
-        rdzv_handler = spec.rdzv_handler
-        participants = rdzv_handler._state_holder.state.participants if hasattr(rdzv_handler, "_state_holder") else None
-        while True:
-            assert self._worker_group.state != WorkerState.INIT
-            time.sleep(monitor_interval)
-            run_result = self._monitor_workers(self._worker_group)
-            state = run_result.state
-            self._worker_group.state = state
-            expire = getattr(getattr(rdzv_handler, "_settings", None), "keep_alive_interval", None)
-            put_metric(f"workers.{role}.remaining_restarts", self._remaining_restarts)
-            put_metric(f"workers.{role}.{state.name.lower()}", 1)
-            if state == WorkerState.SUCCEEDED:
-                logger.info(f"[{role}] worker group successfully finished. Waiting {self._exit_barrier_timeout} seconds for other agents to finish.")
-                self._exit_barrier()
-                return run_result
-            if state in {WorkerState.UNHEALTHY, WorkerState.FAILED}:
-                if self._remaining_restarts > 0:
-                    logger.info(f"[{role}] Worker group {state.name}. {self._remaining_restarts}/{spec.max_restarts} attempts left; will restart worker group")
-                    self._remaining_restarts -= 1
-                    self._restart_workers(self._worker_group)
-                else:
-                    self._stop_workers(self._worker_group)
-                    self._worker_group.state = WorkerState.FAILED
-                    return run_result
-            elif state == WorkerState.HEALTHY:
-                # membership change (nodes joined / left): restart on the new world
-                changed = False
-                try:
-                    changed = rdzv_handler.num_nodes_waiting() > 0
-                except Exception:
-                    pass
-                if changed:
-                    logger.info(f"[{role}] Detected membership change, will restart worker group")
-                    self._restart_workers(self._worker_group)
-            else:
-                raise Exception(f"[{role}] Worker group in {state.name} state")
+    def _initialize_workers(self, worker_group: WorkerGroup) -> None:
+        super()._initialize_workers(worker_group)
+        self._participants_at_start = _participants(worker_group.spec.rdzv_handler)
+
+    def _monitor_workers(self, worker_group: WorkerGroup) -> RunResult:
+        result = super()._monitor_workers(worker_group)
+        if result.state == WorkerState.HEALTHY:
+            now = _participants(worker_group.spec.rdzv_handler)
+            if 0 < now < self._participants_at_start:
+                logger.info(f"[{worker_group.spec.role}] {self._participants_at_start - now} node(s) left the "
+                            "rendezvous; the worker group will be restarted on the smaller world")
+                return RunResult(state=WorkerState.UNHEALTHY)
+        return result
 
 
 def run_elastic(args, env, local_gpus, world_size):
     """Entry used by ``launcher.launch --enable_elastic_training``: run the training script under a
     :class:`DSElasticAgent` with a c10d rendezvous on ``MASTER_ADDR:MASTER_PORT``."""
+    import inspect
     import sys
     import torch.distributed.elastic.rendezvous.registry as rdzv_registry
     from torch.distributed.elastic.rendezvous import RendezvousParameters
@@ -96,9 +84,13 @@ def run_elastic(args, env, local_gpus, world_size):
     params = RendezvousParameters(backend="c10d", endpoint=f"{args.master_addr}:{args.master_port}",
                                   run_id=os.environ.get("ELASTIC_RUN_ID", "sxb200_elastic"), min_nodes=min_nodes,
                                   max_nodes=max_nodes)
-    spec = WorkerSpec(role="trainer", local_world_size=len(local_gpus), entrypoint=cmd[0], args=tuple(cmd[1:]),
-                      rdzv_handler=rdzv_registry.get_rendezvous_handler(params), max_restarts=100, monitor_interval=5,
-                      redirects=Std.from_str("0"), tee=Std.from_str("0"), master_addr=None, master_port=None)
-    agent = DSElasticAgent(spec, env)
+    kw = dict(role="trainer", local_world_size=len(local_gpus), entrypoint=cmd[0], args=tuple(cmd[1:]),
+              rdzv_handler=rdzv_registry.get_rendezvous_handler(params),
+              max_restarts=int(getattr(args, "max_elastic_restarts", 100)),
+              monitor_interval=float(getattr(args, "elastic_monitor_interval", 5)), master_addr=None, master_port=None)
+    if "redirects" in inspect.signature(WorkerSpec.__init__).parameters:      # torch < 2.2 kept log routing here
+        from torch.distributed.elastic.multiprocessing import Std
+        kw.update(redirects=Std.from_str("0"), tee=Std.from_str("0"))
+    agent = DSElasticAgent(WorkerSpec(**kw), env)
     result = agent.run()
     return 0 if not result.is_failed() else 1
