@@ -36,9 +36,7 @@ class BaseTuner:
     def _run_round(self, batch):
         self.rm.schedule_experiments(write_experiments(batch, self.rm.exps_dir))
         self.rm.run()
-        result = self.rm.parse_results(self.metric)
-        self.rm.clear()
-        return result
+        return self.rm.parse_results(self.metric)       # finished experiments stay with the manager until update() ran
 
     def _improves(self, value) -> bool:
         if self.best_exp is None:
@@ -53,12 +51,14 @@ class BaseTuner:
                 exp, value = self._run_round(batch)
             except Exception as err:            # a failing experiment ends the search but keeps the incumbent
                 logger.info(f"tuner stopped by {type(err).__name__}: {err}")
+                self.rm.clear()
                 break
             self.history.append((done, exp, value))
             if self._improves(value):
                 self.best_exp, self.best_metric_val, self.best_iter = exp, value, done
             done += len(batch)
-            self.update()
+            self.update()                       # model-based tuners read the round's measurements here ...
+            self.rm.clear()                     # ... so the manager forgets them only afterwards
             if early_stopping and done - self.best_iter >= early_stopping:
                 logger.info(f"tuner: no improvement for {done - self.best_iter} trial(s) (limit {early_stopping}); "
                             f"best was found at trial {self.best_iter}")
