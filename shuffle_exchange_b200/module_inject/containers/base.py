@@ -280,13 +280,32 @@ class BaseTransformerContainer:
             assert tuple(param.shape) == tuple(v.shape), (tuple(param.shape), tuple(v.shape))
             param.data.copy_(v.to(dt))
 
-        put(mod.attention.attn_qkvw, a.qkvw, True)
+        quantizer = None
+        if self.dtype == torch.int8:
+            from ..replace_module import GroupQuantizer
+            q = getattr(self.config, "quant", None)
+            wq = getattr(q, "weight", None)
+            n_groups = int(getattr(wq, "q_groups", 1) or 1)
+            # default (q_groups = 1 in the config): one step size per row of the stored [in, out] weight, as the
+            # reference's GroupQuantizer() does; q_groups > 1 asks for exactly that many groups
+            quantizer = GroupQuantizer(q_int8=True, num_bits=int(getattr(wq, "num_bits", 8) or 8), group_size=1,
+                                       num_groups=n_groups if n_groups > 1 else 0)
+
+        def put_gemm(owner, name, value):
+            """The four GEMM weights: kept in the compute dtype, or as int8 + per-group step sizes."""
+            param = getattr(owner, name)
+            if quantizer is None:
+                return put(param, value, True)
+            assert tuple(param.shape) == tuple(value.t().shape), (tuple(param.shape), tuple(value.t().shape))
+            setattr(owner, name, quantizer.quantize(value.t().contiguous().to(param.device)))
+
+        put_gemm(mod.attention, "attn_qkvw", a.qkvw)
         put(mod.attention.attn_qkvb, a.qkvb)
-        put(mod.attention.attn_ow, a.ow, True)
+        put_gemm(mod.attention, "attn_ow", a.ow)
         put(mod.attention.attn_ob, a.ob)
-        put(mod.mlp.inter_w, m.inter_w, True)
+        put_gemm(mod.mlp, "inter_w", m.inter_w)
         put(mod.mlp.inter_b, m.inter_b)
-        put(mod.mlp.output_w, m.out_w, True)
+        put_gemm(mod.mlp, "output_w", m.out_w)
         put(mod.mlp.output_b, m.out_b)
         if nm.attn_nw is None:       # single-norm parallel block (GPT-J): MLP reads the attention's normed input
             mod.mlp.attn_nw = mod.mlp.attn_nb = None

@@ -15,6 +15,38 @@ from .auto_tp import AutoTP, Loading, ReplaceWithTensorSlicing
 from .tp_shard import set_n_embd, set_num_attention_heads, set_num_kv_heads
 
 
+class GroupQuantizer:
+    """Symmetric group-wise integer quantiser of injected GEMM weights (reference ``replace_module.py:44-77``): the
+    rows of a weight are cut into ``num_groups`` (or ``rows / group_size``) consecutive groups, each with one step size
+    ``2 * absmax / 2**bits``; the result is an int8 ``Parameter`` carrying ``.scale`` (fp32, one entry per group) that
+    ``ops.transformer.inference.op_binding.dequantize_int8`` expands at use.  With ``q_int8=False`` (or a tensor that is
+    not to be quantised) the weight is returned as a frozen ``Parameter`` with an empty ``.scale``, as the callers of
+    the reference class expect."""
+
+    def __init__(self, q_int8: bool = True, group_size: int = 1, num_bits: int = 8, num_groups: int = 0):
+        self.q_int8, self.group_size, self.num_bits, self.num_groups = q_int8, group_size, num_bits, num_groups
+
+    def groups_for(self, rows: int) -> int:
+        g = self.num_groups if self.num_groups > 0 else max(1, rows // max(1, self.group_size))
+        while rows % g:                     # the groups must tile the rows
+            g -= 1
+        return g
+
+    def quantize(self, inputs: torch.Tensor, qkv: bool = True, count: int = 1, parallel_dim: int = 0):
+        if not self.q_int8 or not qkv or inputs.dim() != 2:
+            out = nn.Parameter(inputs, requires_grad=False)
+            out.scale = torch.empty(1)
+            return out
+        levels = 1 << self.num_bits
+        g = self.groups_for(inputs.shape[0])
+        flat = inputs.detach().float().reshape(g, -1)
+        scale = flat.abs().amax(dim=1, keepdim=True).clamp_min(1e-12) * 2.0 / levels
+        q = (flat / scale).round_().clamp_(-(levels // 2), levels // 2 - 1)
+        out = nn.Parameter(q.reshape(inputs.shape).to(torch.int8).contiguous(), requires_grad=False)
+        out.scale = scale.reshape(-1).contiguous()
+        return out
+
+
 def _module_match(module):
     from .replace_policy import generic_policies
     for policy in generic_policies:

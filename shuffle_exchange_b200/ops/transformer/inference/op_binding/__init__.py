@@ -18,8 +18,19 @@ from ....fused_softmax import biased_softmax
 from .....utils.types import ActivationFuncType, NormType
 
 
-def _w(weight: torch.Tensor, transposed_mode: bool) -> torch.Tensor:
-    """v1 stores linear weights as [in, out]; ``F.linear`` wants [out, in]."""
+def dequantize_int8(weight: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """An int8 weight written by ``module_inject.replace_module.GroupQuantizer`` (symmetric, ``weight.scale`` holds one
+    step size per group of consecutive rows) back in ``dtype``."""
+    scale = weight.scale.to(device=weight.device, dtype=torch.float32).reshape(-1)
+    w = weight.float().reshape(scale.numel(), -1) * scale[:, None]
+    return w.reshape(weight.shape).to(dtype)
+
+
+def _w(weight: torch.Tensor, transposed_mode: bool, like: torch.Tensor = None) -> torch.Tensor:
+    """v1 stores linear weights as [in, out]; ``F.linear`` wants [out, in].  int8 weights (``dtype=torch.int8``
+    injection) are expanded to the activation dtype here, per call: the resident copy stays one byte per element."""
+    if weight.dtype == torch.int8:
+        weight = dequantize_int8(weight, like.dtype if like is not None else torch.float16)
     return weight if transposed_mode else weight.t()
 
 
@@ -63,12 +74,12 @@ class PreRMSNormOp(BaseOp):
 class LinearOp(BaseOp):
     def forward(self, input, weight, bias=None, add_bias=True, do_flash_attn=False, num_heads=1, external_cache=None,
                 num_layers=None):
-        return F.linear(input, _w(weight, self.tm), bias if add_bias else None)
+        return F.linear(input, _w(weight, self.tm, input), bias if add_bias else None)
 
 
 class VectorMatMulOp(BaseOp):
     def forward(self, input, weight, async_op=False):
-        return F.linear(input, _w(weight, self.tm))
+        return F.linear(input, _w(weight, self.tm, input))
 
 
 class QKVGemmOp(BaseOp):
@@ -82,7 +93,7 @@ class QKVGemmOp(BaseOp):
             n = F.layer_norm(input, gamma, beta, c.epsilon)[0]
         else:
             n = input
-        return F.linear(n, _w(weight, self.tm), bias), n
+        return F.linear(n, _w(weight, self.tm, n), bias), n
 
 
 class GatedActivationOp(BaseOp):
@@ -115,8 +126,8 @@ class MLPGemmOp(BaseOp):
             normed, pre = F.rms_norm(x, gamma, c.epsilon, residual=residual)
         else:
             normed, pre = F.layer_norm(x, gamma, beta, c.epsilon, residual=residual)
-        inter = _activate(F.linear(normed, _w(weight_interm, self.tm)), bias, c.mlp_act_func_type)
-        out = F.linear(inter, _w(weight_out, self.tm))
+        inter = _activate(F.linear(normed, _w(weight_interm, self.tm, normed)), bias, c.mlp_act_func_type)
+        out = F.linear(inter, _w(weight_out, self.tm, inter))
         if not c.mlp_after_attn:
             return out, None
         # the value the final residual adds to: the pre-norm sum for pre-LN blocks, the normed sum for post-LN blocks
@@ -125,8 +136,8 @@ class MLPGemmOp(BaseOp):
 
 class GELUGemmOp(BaseOp):
     def forward(self, input, weight, bias, weight_out):
-        inter = F.bias_act(F.linear(input, _w(weight, self.tm)), bias, "gelu")
-        return F.linear(inter, _w(weight_out, self.tm))
+        inter = F.bias_act(F.linear(input, _w(weight, self.tm, input)), bias, "gelu")
+        return F.linear(inter, _w(weight_out, self.tm, inter))
 
 
 class ResidualAddOp(BaseOp):

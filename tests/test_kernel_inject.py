@@ -156,3 +156,39 @@ def _inject_tp(rank, world, name):
 def test_kernel_injection_with_two_way_tensor_parallelism(name):
     from conftest import run_dist
     run_dist(_inject_tp, world=2, args=(name,))
+
+
+@pytest.mark.parametrize("name", ["gpt2", "llama", "gpt_neox"])
+def test_int8_injection_keeps_one_byte_weights_and_close_logits(name):
+    """``dtype=torch.int8``: the four GEMM weights of every injected layer are resident as int8 with one step size per
+    row, expanded per call; logits stay within the int8 quantisation error of the fp32 model."""
+    from shuffle_exchange_b200.module_inject.replace_module import GroupQuantizer
+    from shuffle_exchange_b200.ops.transformer.inference.op_binding import dequantize_int8
+    torch.manual_seed(0)
+    m = AutoModelForCausalLM.from_config(AutoConfig.for_model(**CAUSAL[name])).float().eval()
+    _randomize_biases(m)
+    ids = torch.randint(0, 96, (2, 11), generator=torch.Generator().manual_seed(1))
+    with torch.no_grad():
+        ref = m(ids, use_cache=False).logits.clone()
+        eng = sxb.init_inference(m, dtype=torch.int8, replace_with_kernel_inject=True)
+        out = eng.module(ids, use_cache=False).logits
+    layers = [mod for mod in eng.module.modules() if hasattr(mod, "attn_qkvw")]
+    assert len(layers) == 2
+    for att in layers:
+        for w in (att.attn_qkvw, att.attn_ow):
+            assert w.dtype == torch.int8 and w.scale.numel() == w.shape[0] and not w.requires_grad
+    mlps = [mod for mod in eng.module.modules() if hasattr(mod, "output_w") and hasattr(mod, "inter_w")]
+    assert all(mod.inter_w.dtype == torch.int8 and mod.output_w.dtype == torch.int8 for mod in mlps)
+    assert (out.float() - ref).abs().max() < 0.03 * ref.abs().max()
+    # the quantiser itself: round trip within half a step per element; non-GEMM tensors pass through
+    q = GroupQuantizer(q_int8=True, num_groups=4)
+    w = torch.randn(16, 24)
+    qw = q.quantize(w)
+    assert qw.dtype == torch.int8 and qw.scale.shape == (4,)
+    back = dequantize_int8(qw, torch.float32)
+    step = qw.scale.repeat_interleave(4)[:, None]
+    err = (back - w).abs()
+    assert (err <= step + 1e-6).all() and (err <= step * 0.5 + 1e-6).float().mean() > 0.98   # only +absmax clamps (127)
+    passthrough = q.quantize(torch.randn(8))
+    assert passthrough.dtype == torch.float32 and passthrough.scale.numel() == 1
+    assert GroupQuantizer(q_int8=False).quantize(w).dtype == torch.float32
