@@ -126,3 +126,74 @@ def test_int8_layer_quantisation_in_place():
     assert (got - want).abs().max() < 0.05 * want.abs().max()           # int8, 4 groups: ~1 % weight error
     w = blk.fc.dequantized_weight()
     assert w.shape == (32, 16) and (w.reshape(4, -1).abs().amax(1) > 0).all()
+
+
+def test_random_ltd_end_to_end_on_cpu():
+    """Random layer-token drop: convert layers, schedule the kept length, run a step where the wrapped layers see only
+    the kept tokens (others pass through unchanged), gradients flow to both; checkpoints load into the plain model."""
+    from shuffle_exchange_b200.runtime.data_pipeline.constants import (
+        RANDOM_LTD_GLOBAL_BATCH_SIZE, RANDOM_LTD_HIDDEN_STATE_ORDER, RANDOM_LTD_INCREASE_STEP, RANDOM_LTD_LAYER_NUM,
+        RANDOM_LTD_MAX_VALUE, RANDOM_LTD_MICRO_BATCH_SIZE, RANDOM_LTD_MIN_VALUE, RANDOM_LTD_MODEL_MASK_NAME,
+        RANDOM_LTD_MODEL_TYPE, RANDOM_LTD_REQUIRE_STEP, RANDOM_LTD_SCHEDULE_CONFIG, RANDOM_LTD_SCHEDULER,
+        RANDOM_LTD_SCHEDULER_TYPE, RANDOM_LTD_TOTAL_LAYER_NUM)
+    from shuffle_exchange_b200.runtime.data_pipeline.data_routing.basic_layer import RandomLayerTokenDrop
+    from shuffle_exchange_b200.runtime.data_pipeline.data_routing.helper import (convert_to_random_ltd,
+                                                                               remove_random_ltd_state_dict)
+    from shuffle_exchange_b200.runtime.data_pipeline.data_routing.scheduler import RandomLTDScheduler
+
+    class Layer(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.fc = torch.nn.Linear(8, 8)
+            self.seen = None
+
+        def forward(self, x, attention_mask=None):
+            self.seen = x.shape
+            return x + self.fc(x)
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.layers = torch.nn.ModuleList([Layer() for _ in range(3)])
+            self.head = torch.nn.Linear(8, 1)
+
+        def forward(self, x):
+            for l in self.layers:
+                x = l(x)
+            return self.head(x).sum()
+
+    torch.manual_seed(0)
+    net = Net()
+    plain_keys = set(net.state_dict())
+    convert_to_random_ltd(net, Layer)
+    wrapped = [m for m in net.modules() if isinstance(m, RandomLayerTokenDrop)]
+    assert len(wrapped) == 3 and set(remove_random_ltd_state_dict(net.state_dict())) == plain_keys
+    cfg = {RANDOM_LTD_TOTAL_LAYER_NUM: 3, RANDOM_LTD_LAYER_NUM: 3, RANDOM_LTD_GLOBAL_BATCH_SIZE: 2,
+           RANDOM_LTD_MICRO_BATCH_SIZE: 2, RANDOM_LTD_MODEL_MASK_NAME: None, RANDOM_LTD_MODEL_TYPE: "decoder",
+           RANDOM_LTD_HIDDEN_STATE_ORDER: "batch_seq_dim",
+           RANDOM_LTD_SCHEDULER: {RANDOM_LTD_MIN_VALUE: 4, RANDOM_LTD_MAX_VALUE: 16, RANDOM_LTD_SCHEDULER_TYPE: "fixed_linear",
+                                  RANDOM_LTD_SCHEDULE_CONFIG: {RANDOM_LTD_REQUIRE_STEP: 10, RANDOM_LTD_INCREASE_STEP: 4}}}
+    sched = RandomLTDScheduler(cfg)
+    for i, w in enumerate(wrapped):
+        w.init_config(cfg, sched, i)
+    assert sched.get_current_seq() == 4
+    sched.update_seq(5)                                   # halfway: 4 + 0.5 * 12 = 10 -> multiple of 4 -> 8
+    assert sched.get_current_seq() == 8
+    assert sched.state_dict()["consumed_layer_tokens"] == 2 * 8 * 3
+    net.train()
+    x = torch.randn(2, 16, 8, requires_grad=True)
+    net(x).backward()
+    assert all(tuple(w.random_ltd_layer.seen) == (2, 8, 8) for w in wrapped)      # layers ran on the 8 kept tokens
+    assert x.grad is not None and x.grad.abs().sum() > 0
+    assert all(w.random_ltd_layer.fc.weight.grad is not None for w in wrapped)
+    sched.update_seq(10)
+    assert sched.get_current_seq() == 16
+    net(torch.randn(2, 16, 8))
+    assert tuple(wrapped[0].random_ltd_layer.seen) == (2, 16, 8)                    # schedule complete: nothing dropped
+    net.eval()
+    sched.set_current_seq(4)
+    net(torch.randn(2, 16, 8))
+    assert tuple(wrapped[0].random_ltd_layer.seen) == (2, 16, 8)                    # never drops in eval
+    s2 = RandomLTDScheduler(cfg)
+    s2.load_state_dict(sched.state_dict())
+    assert s2.get_current_seq() == 4 and s2.state_dict() == sched.state_dict()
