@@ -32,3 +32,6 @@ def obj_serialization_details(obj):
         elif isinstance(o, (list, tuple)):
             stack.extend(o)
     return count, size
+
+
+serialize_details = obj_serialization_details      # older name used by callers of the reference module

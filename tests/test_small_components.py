@@ -197,3 +197,57 @@ def test_random_ltd_end_to_end_on_cpu():
     s2 = RandomLTDScheduler(cfg)
     s2.load_state_dict(sched.state_dict())
     assert s2.get_current_seq() == 4 and s2.state_dict() == sched.state_dict()
+
+
+def test_zero_and_checkpoint_helpers():
+    import collections
+    from shuffle_exchange_b200.checkpoint.utils import (clone_tensors_for_torch_save, get_layer_ckpt_name_for_rank,
+                                                        get_model_ckpt_name_for_rank, get_zero_ckpt_name_for_rank)
+    from shuffle_exchange_b200.io.utils import bytes_to_tensor, obj_serialization_details, serialize_details, tensor_to_bytes
+    from shuffle_exchange_b200.runtime.zero import utils as zu
+    from shuffle_exchange_b200.runtime.zero.mics_utils import _generate_mics_config
+    P = collections.namedtuple("P", "a b")
+    nested = {"x": [torch.ones(2), (torch.zeros(1), 3)], "y": P(torch.ones(1), "s")}
+    doubled = zu.apply_to_tensors_only(lambda t: t * 2, nested)
+    assert doubled["x"][0].tolist() == [2.0, 2.0] and doubled["x"][1][1] == 3
+    assert isinstance(doubled["y"], P) and doubled["y"].a.item() == 2.0 and doubled["y"].b == "s"
+    ts = [torch.zeros(3), torch.zeros(2, 2)]
+    assert [(o, n) for _, o, n in zu.get_mapping_to_flat_buffer(ts)] == [(0, 3), (3, 4)]
+    assert zu.is_zero_supported_optimizer(torch.optim.AdamW([torch.nn.Parameter(torch.zeros(1))]))
+    assert not zu.is_zero_supported_optimizer(torch.optim.LBFGS([torch.nn.Parameter(torch.zeros(1))]))
+
+    cfg = _generate_mics_config(world_size=16, ndev_per_node=4, shard_size=8)
+    assert cfg["shard_groups"] == [list(range(8)), list(range(8, 16))]
+    assert cfg["replicate_groups"] == [[i, i + 8] for i in range(8)] and cfg["span_nodes"] == 2
+    with pytest.raises(AssertionError):
+        _generate_mics_config(world_size=12, ndev_per_node=4, shard_size=8)
+
+    flat = torch.arange(1000.0)
+    view = {"w": flat[10:20], "l": [flat[:3]], "n": 5}
+    cloned = clone_tensors_for_torch_save(view)
+    assert cloned["w"].untyped_storage().nbytes() == 40 and torch.equal(cloned["w"], flat[10:20]) and cloned["n"] == 5
+    assert get_model_ckpt_name_for_rank("/c", "03").endswith("mp_rank_03_model_states.pt")
+    assert get_zero_ckpt_name_for_rank("/c", 2, 1).endswith("zero_pp_rank_2_mp_rank_01_optim_states.pt")
+    # (sic) the reference's helper joins with "_" although PipelineModule writes "layer_XX-model_YY-model_states.pt"
+    assert get_layer_ckpt_name_for_rank("/c", "layer_04", 1).endswith("layer_04-model_01_model_states.pt")
+    t = torch.randn(7).to(torch.bfloat16)
+    assert torch.equal(bytes_to_tensor(tensor_to_bytes(t)).view(torch.bfloat16), t)
+    assert obj_serialization_details({"a": [torch.zeros(4), torch.zeros(2, dtype=torch.float64)], "b": 1}) == (2, 32)
+    assert serialize_details is obj_serialization_details
+
+
+def _ints_worker(rank, world):
+    from shuffle_exchange_b200.runtime.zero.utils import assert_ints_same_as_other_ranks, get_lst_from_rank0
+    assert get_lst_from_rank0([rank + 5, 9]) == [5, 9]
+    assert_ints_same_as_other_ranks([1, 2, 3])
+    try:
+        assert_ints_same_as_other_ranks([1, 2, 3 + rank])
+        raised = False
+    except RuntimeError:
+        raised = True
+    assert raised == (rank != 0)
+
+
+def test_ranks_disagreeing_on_a_fetch_order_are_caught():
+    from conftest import run_dist
+    run_dist(_ints_worker, 2)
