@@ -63,6 +63,8 @@ class InferenceEngine(nn.Module):
             self._apply_injection_policy(config)
         if config.checkpoint is not None:
             self._load_checkpoint(config.checkpoint)
+        if config.save_mp_checkpoint_path is not None:
+            self._save_mp_checkpoint(config.save_mp_checkpoint_path)
         post_q = getattr(getattr(config.quant, "weight", None), "post_init_quant", None)
         if post_q:
             # group-wise INT4/INT8 weights, converted layer by layer before the move to the device
@@ -182,6 +184,13 @@ class InferenceEngine(nn.Module):
         import glob
         import json
         files = []
+        desc = load_dir if isinstance(load_dir, dict) else None
+        if desc is None and os.path.isfile(load_dir) and load_dir.endswith(".json"):
+            with open(load_dir) as f:
+                desc = json.load(f)
+            desc.setdefault("base_dir", os.path.dirname(load_dir))
+        if desc is not None and isinstance(desc.get("checkpoints"), dict):
+            return self._load_mp_checkpoint(desc)
         if isinstance(load_dir, dict):
             files = load_dir.get("checkpoints", [])
             base = load_dir.get("base_dir", self._config.base_dir)
@@ -224,6 +233,77 @@ class InferenceEngine(nn.Module):
         missing = self.module.load_state_dict(fixed, strict=False)
         if load_module_strict and missing.missing_keys:
             logger.warning(f"checkpoint is missing {len(missing.missing_keys)} keys, e.g. {missing.missing_keys[:3]}")
+
+    # ------------------------------------------------------------- tensor-parallel sharded checkpoints
+    _TP_PARTITIONS = 8       # files per rank, so that no single file holds all layers (reference: 8)
+
+    def _injected_prefixes(self):
+        from ..model_implementations.transformers.ds_transformer import DeepSpeedTransformerInference
+        return tuple(n + "." for n, m in self.module.named_modules() if isinstance(m, DeepSpeedTransformerInference))
+
+    def _save_mp_checkpoint(self, path: str) -> None:
+        """Write the model AS IT IS NOW — injected, tensor-parallel sliced, possibly int8 — so that the next start
+        loads each rank's slice directly instead of re-reading and re-slicing the full checkpoint (reference
+        ``replace_module.py:482-545``): ``non-tp.pt`` (everything outside the injected layers, written once),
+        ``tp_<rank>_<part>.pt`` (this rank's injected-layer tensors; an int8 weight is stored as ``[codes, scale]``) and
+        the descriptor ``ds_inference_config.json`` that ``init_inference(checkpoint=...)`` takes."""
+        import json
+        from collections import OrderedDict
+        os.makedirs(path, exist_ok=True)
+        tp = self._config.tensor_parallel.tp_size
+        rank = dist.get_rank(group=self.mp_group) if (self.mp_group is not None and tp > 1) else 0
+        writer = (not dist.is_initialized()) or dist.get_rank() == 0
+        prefixes = self._injected_prefixes()
+        sd = self.module.state_dict()
+        for name, p in self.module.named_parameters():
+            if hasattr(p, "scale") and p.dtype == torch.int8:
+                sd[name] = [p.data, p.scale]
+        sliced = [k for k in sd if k.startswith(prefixes)] if prefixes else []
+        if writer:
+            torch.save(OrderedDict((k, v) for k, v in sd.items() if k not in set(sliced)), os.path.join(path, "non-tp.pt"))
+            kind = type(self.module).__name__
+            reprs = {torch.float32: "float32", torch.float16: "float16", torch.bfloat16: "bfloat16", torch.int8: "int8"}
+            with open(os.path.join(path, "ds_inference_config.json"), "w") as f:
+                json.dump({"type": "bloom" if "bloom" in kind.lower() else "ds_model", "base_dir": path,
+                           "checkpoints": {"non_tp": ["non-tp.pt"],
+                                           "tp": [f"tp_{r:0>2d}_{m:0>2d}.pt" for m in range(self._TP_PARTITIONS)
+                                                  for r in range(tp)]},
+                           "version": 1.0, "parallelization": "tp", "tp_size": tp,
+                           "dtype": reprs.get(self._config.dtype, str(self._config.dtype))}, f)
+        per = len(sliced) // self._TP_PARTITIONS + 1
+        for m in range(self._TP_PARTITIONS):
+            part = OrderedDict((k, sd[k]) for k in sliced[m * per:(m + 1) * per])
+            torch.save(part, os.path.join(path, f"tp_{rank:0>2d}_{m:0>2d}.pt"))
+        if dist.is_initialized():
+            dist.barrier()
+
+    def _load_mp_checkpoint(self, desc: dict) -> None:
+        """Inverse of :meth:`_save_mp_checkpoint`: tensors already have this rank's shapes."""
+        tp = self._config.tensor_parallel.tp_size
+        if int(desc.get("tp_size", 1)) != tp:
+            raise ValueError(f"the sharded checkpoint was written for tp_size={desc.get('tp_size')}, "
+                             f"this engine runs tp_size={tp}; load the original checkpoint instead")
+        base = desc.get("base_dir", self._config.base_dir)
+        rank = dist.get_rank(group=self.mp_group) if (self.mp_group is not None and tp > 1) else 0
+        files = list(desc["checkpoints"]["non_tp"]) + [f for f in desc["checkpoints"]["tp"]
+                                                       if f.startswith(f"tp_{rank:0>2d}_")]
+        params = dict(self.module.named_parameters())
+        plain = {}
+        for f in files:
+            for k, v in torch.load(os.path.join(base, f), map_location="cpu", weights_only=False).items():
+                if isinstance(v, (list, tuple)):                      # int8 codes + per-group step sizes
+                    codes, scale = v
+                    owner, _, leaf = k.rpartition(".")
+                    mod = self.module.get_submodule(owner) if owner else self.module
+                    new = nn.Parameter(codes.to(params[k].device) if k in params else codes, requires_grad=False)
+                    new.scale = scale
+                    setattr(mod, leaf, new)
+                else:
+                    plain[k] = v
+        missing = self.module.load_state_dict(plain, strict=False)
+        left = [k for k in missing.missing_keys if not (k in params and params[k].dtype == torch.int8)]
+        if left:
+            logger.warning(f"sharded checkpoint is missing {len(left)} keys, e.g. {left[:3]}")
 
     # ------------------------------------------------------------------------------ CUDA graphs
     def _create_cuda_graph(self, *inputs, **kwargs):

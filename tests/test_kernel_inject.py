@@ -192,3 +192,53 @@ def test_int8_injection_keeps_one_byte_weights_and_close_logits(name):
     passthrough = q.quantize(torch.randn(8))
     assert passthrough.dtype == torch.float32 and passthrough.scale.numel() == 1
     assert GroupQuantizer(q_int8=False).quantize(w).dtype == torch.float32
+
+
+def _mp_checkpoint_worker(rank, world, name, root, dtype):
+    """save_mp_checkpoint_path writes this rank's slices; a second engine built from a DIFFERENT random model and the
+    descriptor reproduces the first engine's logits without seeing the original weights."""
+    import json
+    import os
+    torch.manual_seed(0)
+    cfg = AutoConfig.for_model(**CAUSAL[name])
+    m = AutoModelForCausalLM.from_config(cfg).float().eval()
+    _randomize_biases(m)
+    ids = torch.randint(0, 96, (2, 9), generator=torch.Generator().manual_seed(1))
+    tp = {"tp_size": world} if world > 1 else {}
+    with torch.no_grad():
+        eng = sxb.init_inference(m, dtype=dtype, replace_with_kernel_inject=True, tensor_parallel=tp,
+                                 save_mp_checkpoint_path=root)
+        want = eng.module(ids, use_cache=False).logits.clone()
+    desc = json.load(open(os.path.join(root, "ds_inference_config.json")))
+    assert desc["tp_size"] == world and desc["parallelization"] == "tp" and desc["checkpoints"]["non_tp"] == ["non-tp.pt"]
+    assert len(desc["checkpoints"]["tp"]) == 8 * world and all(os.path.exists(os.path.join(root, f)) for f in desc["checkpoints"]["tp"])
+    eng.destroy()
+    torch.manual_seed(123)                                   # other weights: everything must come from the files
+    m2 = AutoModelForCausalLM.from_config(cfg).float().eval()
+    with torch.no_grad():
+        eng2 = sxb.init_inference(m2, dtype=dtype, replace_with_kernel_inject=True, tensor_parallel=tp,
+                                  checkpoint=os.path.join(root, "ds_inference_config.json"))
+        got = eng2.module(ids, use_cache=False).logits
+    assert torch.equal(got, want), float((got - want).abs().max())
+    if dtype == torch.int8:
+        att = [mod for mod in eng2.module.modules() if hasattr(mod, "attn_qkvw")][0]
+        assert att.attn_qkvw.dtype == torch.int8 and att.attn_qkvw.scale.numel() == att.attn_qkvw.shape[0]
+    if world > 1:
+        try:
+            sxb.init_inference(AutoModelForCausalLM.from_config(cfg).float().eval(), dtype=dtype,
+                               replace_with_kernel_inject=True,
+                               checkpoint=os.path.join(root, "ds_inference_config.json"))
+            raised = False
+        except ValueError:
+            raised = True
+        assert raised, "a tp_size=2 checkpoint must not load into a tp_size=1 engine"
+
+
+def test_sharded_inference_checkpoint_round_trip_tp2(tmp_path):
+    from conftest import run_dist
+    run_dist(_mp_checkpoint_worker, world=2, args=("llama", str(tmp_path), torch.float32))
+
+
+def test_sharded_inference_checkpoint_round_trip_int8(tmp_path):
+    from conftest import run_dist
+    run_dist(_mp_checkpoint_worker, world=1, args=("gpt2", str(tmp_path), torch.int8))
