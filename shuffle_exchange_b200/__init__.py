@@ -127,8 +127,10 @@ def initialize(args=None, model: torch.nn.Module = None,
         config_class = DeepSpeedConfig(config, mpu, mesh_device=mesh_device)
         tp_size = config_class.tensor_parallel_config.autotp_size
         if tp_size and tp_size > 1 and mpu is None:
+            from .module_inject.layers import configure_tensor_parallel_runtime
             from .runtime.tensor_parallel import TpTrainingManager
             groups._init_tp_mesh_device(tp_size)
+            configure_tensor_parallel_runtime(config_class.tensor_parallel_config)
             TpTrainingManager(model=model, tp_size=tp_size, dtype=torch.bfloat16 if config_class.bfloat16_enabled else torch.float16)
         if config_class.hybrid_engine.enabled:
             from .runtime.hybrid_engine import DeepSpeedHybridEngine

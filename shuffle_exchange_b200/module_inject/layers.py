@@ -159,8 +159,8 @@ class AsyncColumnParallel(torch.autograd.Function):
     @staticmethod
     def backward(ctx: Any, grad_output: torch.Tensor):
         input, weight = ctx.saved_tensors
-        grad_input = F.matmul_nn(grad_output, weight)
-        handle = dist.all_reduce(grad_input.contiguous(), group=ctx.group, async_op=True) if _tp_world(ctx.group) > 1 else None
+        grad_input = F.matmul_nn(grad_output, weight).contiguous()       # reduced in place while the wgrad GEMM runs
+        handle = dist.all_reduce(grad_input, group=ctx.group, async_op=True) if _tp_world(ctx.group) > 1 else None
         g2 = grad_output.reshape(-1, grad_output.shape[-1])
         grad_weight = F.matmul_tn(g2, input).to(weight.dtype)
         grad_bias = g2.sum(0) if ctx.use_bias else None
@@ -173,6 +173,7 @@ class TensorParallel_Layer(nn.Module, ABC):
     """Base of the TP linears: knows its group, how to cut (``_tp_partition``) and re-assemble (``gather_params``) its
     parameters, and tags them (``tensor_model_parallel``, ``ds_is_replaced_module``) for checkpointing / optimizers."""
     keep_module_on_host: bool = False
+    tp_overlap_comm: bool = False      # runtime switch (config ``tensor_parallel.tp_overlap_comm``), set for all layers
 
     def __init__(self, mp_group, **kwargs: Any):
         super().__init__()
@@ -242,9 +243,13 @@ class TensorParallel_Layer(nn.Module, ABC):
 
 
 def configure_tensor_parallel_runtime(config):
+    """Apply the runtime part of the ``tensor_parallel`` config block to every TP layer: the grain size of uneven
+    splits and ``tp_overlap_comm`` (column-parallel layers overlap the input-gradient all-reduce with the
+    weight-gradient GEMM; reference :319-323)."""
     set_autotp_mode(training=True)
     from .tp_shard import set_tp_grain_size
     set_tp_grain_size(getattr(getattr(config, "tp", config), "tp_grain_size", 1))
+    TensorParallel_Layer.tp_overlap_comm = bool(getattr(config, "tp_overlap_comm", False))
 
 
 class GatherReplacedLayerParams:
@@ -321,7 +326,7 @@ class LinearLayer(TensorParallel_Layer):
             self.config_tp_params(self.bias)
 
     def forward(self, input):
-        if getattr(self, "__async_tp", False) and self.is_training_mode():
+        if type(self).tp_overlap_comm and self.is_training_mode():
             return AsyncColumnParallel.apply(self.mp_group, input, self.weight, self.bias)
         input = ColumnParallel.apply(self.mp_group, input)
         out = _project(input, self.weight)

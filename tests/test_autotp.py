@@ -58,10 +58,19 @@ def test_tp_parser_finds_row_parallel_linears():
     assert cls is Block and set(gem) == {"o_proj", "down_proj"}
 
 
-def _worker(rank, world):
+def _worker(rank, world, overlap=False):
     import copy
+    import types
     from shuffle_exchange_b200.module_inject import tp_model_init
+    from shuffle_exchange_b200.module_inject import layers as L
     from shuffle_exchange_b200.module_inject.layers import LinearAllreduce, LinearLayer
+    # ``tensor_parallel.tp_overlap_comm``: column-parallel layers take the asynchronous-all-reduce backward
+    L.configure_tensor_parallel_runtime(types.SimpleNamespace(tp_grain_size=1, tp_overlap_comm=overlap))
+    assert L.TensorParallel_Layer.tp_overlap_comm is overlap
+    taken = []
+    if overlap:
+        orig = L.AsyncColumnParallel.forward
+        L.AsyncColumnParallel.forward = staticmethod(lambda ctx, *a: (taken.append(1), orig(ctx, *a))[1])
     torch.manual_seed(0)
     full = Tiny()
     x = torch.randn(2, 6, 32)
@@ -81,7 +90,14 @@ def _worker(rank, world):
     g_full = full.layers[0].self_attn.o_proj.weight.grad
     g_tp = tp.layers[0].self_attn.o_proj.weight.grad
     assert torch.allclose(g_tp, g_full.chunk(2, 1)[rank], atol=1e-5)
+    if overlap:
+        assert len(taken) >= 4, "tp_overlap_comm did not route the column-parallel layers through AsyncColumnParallel"
+        L.configure_tensor_parallel_runtime(types.SimpleNamespace(tp_grain_size=1, tp_overlap_comm=False))
 
 
 def test_autotp_matches_unsharded():
     run_dist(_worker, 2)
+
+
+def test_autotp_with_overlapped_input_gradient_all_reduce():
+    run_dist(_worker, 2, (True,))
