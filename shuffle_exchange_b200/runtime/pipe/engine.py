@@ -24,6 +24,7 @@ import torch
 from ... import comm as dist
 from ...device import get_accelerator
 from ...ops import functional as _F
+from ...utils.logging import logger
 from ...utils.timer import ThroughputTimer
 from ..engine import MEMORY_OPT_ALLREDUCE_SIZE, DeepSpeedEngine
 from . import p2p, schedule
@@ -148,6 +149,13 @@ class PipelineEngine(DeepSpeedEngine):
         self.dynamic_shape = self.module.dynamic_shape
         if pc["activation_checkpoint_interval"]:
             self.module.activation_checkpoint_interval = pc["activation_checkpoint_interval"]
+            if pc.get("use_reentrant", True) is False:
+                # ``pipeline.use_reentrant: false``: recompute through saved-tensor hooks instead of a re-entrant
+                # autograd function (no dummy requires_grad inputs, works with keyword tensors)
+                from ..activation_checkpointing import checkpointing as ds_checkpointing
+                self.module.activation_checkpoint_func = ds_checkpointing.non_reentrant_checkpoint
+                if self.grid.get_global_rank() == 0:
+                    logger.info("CONFIG: activation_checkpoint_func=non_reentrant_checkpoint")
         self.module.checkpoint_parallel_write_pipeline = self._config.checkpoint_parallel_write_pipeline
         self.has_attention_mask = type(self.module).__name__ == "GPT2ModelPipe"
         self.batch_timer = ThroughputTimer(self._config.timers_config.throughput, batch_size=self.train_batch_size(),

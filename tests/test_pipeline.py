@@ -52,7 +52,7 @@ class _Block(nn.Module):
         return torch.tanh(self.lin(x))
 
 
-def _pipe_worker(rank, world):
+def _pipe_worker(rank, world, pipeline_cfg=None):
     import shuffle_exchange_b200 as ds
     from shuffle_exchange_b200.runtime.pipe.module import LayerSpec, PipelineModule
     torch.manual_seed(0)
@@ -68,9 +68,18 @@ def _pipe_worker(rank, world):
     net.load_state_dict(own, strict=True)
     engine, _, _, _ = ds.initialize(model=net, model_parameters=[p for p in net.parameters()], config={
         "train_micro_batch_size_per_gpu": micro, "gradient_accumulation_steps": gas, "steps_per_print": 10 ** 9,
-        "optimizer": {"type": "SGD", "params": {"lr": 0.1}}})
+        "optimizer": {"type": "SGD", "params": {"lr": 0.1}}, **({"pipeline": pipeline_cfg} if pipeline_cfg else {})})
+    if pipeline_cfg:
+        from shuffle_exchange_b200.runtime.activation_checkpointing import checkpointing as ck
+        assert net.activation_checkpoint_interval == pipeline_cfg["activation_checkpoint_interval"]
+        want_fn = ck.checkpoint if pipeline_cfg.get("use_reentrant", True) else ck.non_reentrant_checkpoint
+        assert net.activation_checkpoint_func is want_fn
+        calls = []
+        net.activation_checkpoint_func = lambda f, *a: (calls.append(1), want_fn(f, *a))[1]
     it = iter(data)
     losses = [float(engine.train_batch(data_iter=it)) for _ in range(3)]
+    if pipeline_cfg:
+        assert len(calls) >= 3 * gas, "activation checkpointing was configured but never used"
     # reference: plain SGD with gradient accumulation
     opt = torch.optim.SGD(ref.parameters(), lr=0.1)
     it = iter(data)
@@ -92,6 +101,13 @@ def _pipe_worker(rank, world):
 
 def test_two_stage_training_matches_sequential():
     run_dist(_pipe_worker, 2)
+
+
+@pytest.mark.parametrize("use_reentrant", [True, False])
+def test_two_stage_training_with_activation_checkpointing(use_reentrant):
+    """``pipeline.activation_checkpoint_interval`` recomputes every layer in backward (re-entrant or hook-based per
+    ``pipeline.use_reentrant``); training must be bit-for-bit the run without recomputation."""
+    run_dist(_pipe_worker, 2, ({"activation_checkpoint_interval": 1, "use_reentrant": use_reentrant},))
 
 
 def _pipe_zero_worker(rank, world, zero_stage, offload=False):
