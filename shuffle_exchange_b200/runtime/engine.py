@@ -1201,6 +1201,14 @@ class DeepSpeedEngine(nn.Module):
         if self.is_deepcompile_enabled():
             stage = self.zero_optimization_stage()
             cfg = self._config.compile_config
+            # knobs of the reference's FX-graph passes that have no counterpart in a schedule over ZeRO units: say so
+            # once instead of letting a migrated config believe they act
+            graph_only = [k for k in ("free_activation", "sync_before_reduce", "sync_after_reduce",
+                                      "sync_before_allgather", "sync_after_allgather", "keep_all_input_tensors")
+                          if getattr(cfg, k)] + ([] if cfg.keep_int_input_tensors else ["keep_int_input_tensors"])
+            if graph_only:
+                logger.warning(f"compile: {graph_only} apply to traced FX graphs only; the schedule compiler of this "
+                               "framework has no such graph and ignores them")
             if stage == 3:
                 from ..compile.init_z3 import init_z3
                 self._compile_backend = init_z3(self, backend, cfg, compile_kwargs, schedule)

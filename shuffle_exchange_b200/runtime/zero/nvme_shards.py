@@ -2,8 +2,9 @@
 
 Reference: ``runtime/swap_tensor/partitioned_param_swapper.py`` — every rank's ``ds_tensor`` partitions live in swap
 files and pass through a fixed pool of pinned buffers.  Here the unit of swapping is the unit of everything else in
-this engine: the flat group's shard (one file per group and rank).  :class:`NvmeShardStore` keeps at most
-``buffer_count`` shards resident in (pinned) host memory, reads a shard with the asynchronous file engine
+this engine: the flat group's shard (one file per group and rank).  :class:`NvmeShardStore` keeps ``buffer_count``
+shards resident in (pinned) host memory — more while the resident elements stay within ``max_in_cpu``
+(``offload_param.max_in_cpu``: how much of the model may stay in host memory) — reads a shard with the asynchronous file engine
 (``csrc/host/aio.cpp``) when someone asks for it and writes it back on eviction if it was modified since it was read.
 The flat group sees an ordinary host tensor (``FlatGroup.lp_shard`` becomes a property over the store), so gathers,
 optimizer write-back and checkpointing need no NVMe-specific code; they only say when they have written
@@ -24,11 +25,12 @@ _IO_ALIGN = 4096          # bytes: files are padded to whole blocks so O_DIRECT 
 
 class NvmeShardStore:
     def __init__(self, folder: str, dtype: torch.dtype, buffer_count: int = 5, aio_config: dict = None,
-                 pin_memory: bool = False):
+                 pin_memory: bool = False, max_in_cpu: int = 0):
         self.folder = folder
         os.makedirs(folder, exist_ok=True)
         self.dtype = dtype
         self.capacity = max(1, int(buffer_count))
+        self.max_in_cpu = max(0, int(max_in_cpu))       # elements that may be resident beyond the first `capacity` shards
         self.pin = bool(pin_memory) and torch.cuda.is_available()
         a = aio_config or {}
         self.handle = aio_handle(int(a.get("block_size", 1 << 20)), int(a.get("queue_depth", 8)),
@@ -64,7 +66,7 @@ class NvmeShardStore:
         """The shard as a host tensor (a view of its resident buffer); most recently used last."""
         hit = self._resident.get(key)
         if hit is None:
-            while len(self._resident) >= self.capacity:
+            while self._resident and not self._room_for(self._numel[key]):
                 self._evict_one()
             buf = self._buffer(self._numel[key])
             rc = self.handle.sync_pread(buf, self.path(key))
@@ -97,7 +99,16 @@ class NvmeShardStore:
     def resident_count(self) -> int:
         return len(self._resident)
 
+    @property
+    def resident_numel(self) -> int:
+        return sum(self._numel[k] for k in self._resident)
+
     # ---------------------------------------------------------------------------------- internal
+    def _room_for(self, numel: int) -> bool:
+        if len(self._resident) < self.capacity:
+            return True
+        return self.max_in_cpu > 0 and self.resident_numel + numel <= self.max_in_cpu
+
     def _evict_one(self) -> None:
         key, (buf, dirty) = self._resident.popitem(last=False)
         if dirty:

@@ -165,7 +165,7 @@ class DeepSpeedZeroOptimizer_Stage3(ShardedOptimizerBase):
             self._param_store = NvmeShardStore(
                 os.path.join(str(nvme_path), "zero_stage_3", f"{str(self.dtype).split('.')[-1]}params", f"rank{self.rank}"),
                 self.dtype, buffer_count=int(getattr(offload_param_config, "buffer_count", 5) or 5), aio_config=aio,
-                pin_memory=self.offload_param_pin)
+                pin_memory=self.offload_param_pin, max_in_cpu=int(getattr(offload_param_config, "max_in_cpu", 0) or 0))
         self.hpz_size = int(zero_hpz_partition_size or 1)
         self.quantized_weights = bool(zero_quantized_weights)
         self.quantized_gradients = bool(zero_quantized_gradients)

@@ -94,7 +94,7 @@ CASES = [
     (2, {"offload_optimizer": {"device": "cpu", "ratio": 0.5}}),
     (2, {"offload_param": {"device": "cpu"}}),
     (2, {"offload_optimizer": {"device": "nvme", "buffer_count": 16}}),
-    (2, {"offload_param": {"device": "nvme", "buffer_count": 2}}),
+    (2, {"offload_param": {"device": "nvme", "buffer_count": 2, "max_in_cpu": 0}}),   # nothing resident beyond 2 shards
 ]
 
 

@@ -34,7 +34,7 @@ def _worker(rank, world, offload, nvme_dir=None):
     dense = copy.deepcopy(model)
     cfg = None
     if offload == "nvme":
-        cfg = DeepSpeedZeroOffloadParamConfig(device="nvme", nvme_path=nvme_dir, buffer_count=2, pin_memory=False)
+        cfg = DeepSpeedZeroOffloadParamConfig(device="nvme", nvme_path=nvme_dir, buffer_count=2, max_in_cpu=0, pin_memory=False)
     elif offload:
         cfg = DeepSpeedZeroOffloadParamConfig(device="cpu", pin_memory=False)
     z = DeepSpeedZeRoOffload(model, param_persistence_threshold=0, offload_param_config=cfg)
