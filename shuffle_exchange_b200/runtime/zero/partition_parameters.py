@@ -16,6 +16,7 @@ memory is max(largest module, largest unit) — never the whole model.
 from __future__ import annotations
 
 import functools
+import os
 import itertools
 from enum import Enum
 from typing import Iterable, List, Optional
@@ -60,7 +61,21 @@ def _shard_of(t: torch.Tensor, world: int, rank: int) -> torch.Tensor:
 
 
 class Init:
-    """Context manager: modules built inside have their parameters sharded at construction."""
+    """Context manager: modules built inside have their parameters sharded at construction.
+
+    Two granularities (``Init.granularity`` / env ``SXB_ZERO_INIT_GRANULARITY``):
+
+    * ``"model"`` (default): the model is sharded when its OUTERMOST constructor returns.  Any initialisation code
+      inside constructors (loops over ``self.parameters()``, ``self.apply(...)``, weight tying) sees ordinary tensors;
+      the price is that one rank holds the whole model (on the construction device, normally the host) for a moment.
+    * ``"module"``: every sub-module's own parameters are sharded as soon as ITS constructor returns, as the reference
+      does (``partition_parameters.py:1066-1100``), so no rank ever holds more than one sub-module whole — this is what
+      builds models larger than one device / one host.  Code that runs later in a parent constructor then sees empty
+      tensors; the one common pattern, ``module.apply(init_fn)`` (Hugging Face ``post_init``), is kept working by
+      gathering each visited module's own parameters around ``init_fn`` and re-sharding rank 0's result
+      (``override_module_apply`` of the reference); anything else needs ``GatheredParameters``.
+    """
+    granularity = os.environ.get("SXB_ZERO_INIT_GRANULARITY", "model")
 
     def __init__(self, module=None, data_parallel_group=None, mem_efficient_linear=True, remote_device=None,
                  pin_memory=False, config_dict_or_path=None, config=None, enabled=True, dtype=None, mpu=None,
@@ -142,7 +157,9 @@ class Init:
                     orig(module, *a, **k)
                 finally:
                     outer.depth -= 1
-                if outer.depth == 0:
+                if outer.granularity == "module":
+                    outer._convert_module(module, recurse=False)       # children sharded theirs when they returned
+                elif outer.depth == 0:
                     outer._convert_module(module)
 
             cls.__init__ = wrapped
@@ -160,11 +177,81 @@ class Init:
             wrap(cls)
 
         nn.Module.__init_subclass__ = classmethod(init_subclass)
+        self._orig_apply = None
+        if self.granularity == "module":
+            self._orig_apply = nn.Module.apply
+
+            def sharded_apply(module, fn):
+                """``module.apply(fn)`` over sharded parameters: children first (as torch does), then this module with
+                its OWN parameters made whole; rank 0's result is what every rank keeps."""
+                for child in module.children():
+                    child.apply(fn)
+                own = [p for p in module.parameters(recurse=False)
+                       if is_zero_param(p) and getattr(p, "ds_tensor", None) is not None and p.numel() == 0]
+                if own:
+                    with GatheredParameters(own, modifier_rank=0):
+                        fn(module)
+                else:
+                    fn(module)
+                return module
+
+            nn.Module.apply = sharded_apply
+            self._patch_init_functions()
+
+    _INIT_FUNCTIONS = ("uniform_", "normal_", "trunc_normal_", "constant_", "ones_", "zeros_", "eye_", "dirac_",
+                       "xavier_uniform_", "xavier_normal_", "kaiming_uniform_", "kaiming_normal_", "orthogonal_",
+                       "sparse_")
+
+    def _patch_init_functions(self):
+        """``torch.nn.init.<fn>(param, ...)`` on a sharded parameter: make it whole, initialise, keep rank 0's values.
+        Libraries that captured the functions in a table before this context was entered (``transformers >= 5``:
+        ``initialization.TORCH_INIT_FUNCTIONS``, which its ``_init_weights`` goes through) get the table patched too.
+        In-place methods on ``param.data`` cannot be seen from here — such code needs ``GatheredParameters``."""
+        def wrap(orig):
+            @functools.wraps(orig)
+            def init_fn(tensor, *a, **k):
+                if is_zero_param(tensor) and getattr(tensor, "ds_tensor", None) is not None and tensor.numel() == 0:
+                    with GatheredParameters([tensor], modifier_rank=0):
+                        orig(tensor, *a, **k)
+                    return tensor
+                return orig(tensor, *a, **k)
+            return init_fn
+
+        self._init_patches = []
+        tables = [vars(torch.nn.init)]
+        try:
+            import sys
+            hf = sys.modules.get("transformers.initialization")
+            if hf is not None and isinstance(getattr(hf, "TORCH_INIT_FUNCTIONS", None), dict):
+                tables.append(hf.TORCH_INIT_FUNCTIONS)
+        except Exception:
+            pass
+        for table in tables:
+            for name in self._INIT_FUNCTIONS:
+                orig = table.get(name)
+                if callable(orig):
+                    self._init_patches.append((table, name, orig))
+                    if table is vars(torch.nn.init):
+                        setattr(torch.nn.init, name, wrap(orig))
+                    else:
+                        table[name] = wrap(orig)
+
+    def _unpatch_init_functions(self):
+        for table, name, orig in getattr(self, "_init_patches", []):
+            if table is vars(torch.nn.init):
+                setattr(torch.nn.init, name, orig)
+            else:
+                table[name] = orig
+        self._init_patches = []
 
     def _unpatch(self):
+        self._unpatch_init_functions()
         for cls, orig in self._orig_subclass_inits.items():
             cls.__init__ = orig
         self._orig_subclass_inits = {}
+        if getattr(self, "_orig_apply", None) is not None:
+            nn.Module.apply = self._orig_apply
+            self._orig_apply = None
         if self._orig_init_subclass is None:
             try:
                 del nn.Module.__init_subclass__
@@ -179,11 +266,11 @@ class Init:
             return 1, 0
         return dist.get_world_size(self.group), dist.get_rank(self.group)
 
-    def _convert_module(self, module: nn.Module):
+    def _convert_module(self, module: nn.Module, recurse: bool = True):
         world, rank = self._world()
         dev = torch.device(self.remote_device) if self.remote_device in ("cpu",) else \
             torch.device(get_accelerator().current_device_name())
-        for name, p in module.named_parameters(recurse=True):
+        for name, p in module.named_parameters(recurse=recurse):
             if is_zero_param(p) or id(p) in self._seen:
                 continue
             self._seen.add(id(p))

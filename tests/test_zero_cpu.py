@@ -250,3 +250,59 @@ def _offload_states_worker(rank, world, stage):
 @pytest.mark.parametrize("stage", [2, 3])
 def test_offload_and_reload_states_keep_training_identical(stage):
     run_dist(_offload_states_worker, 2, (stage,))
+
+
+def _zero_init_module_granularity_worker(rank, world):
+    """``Init.granularity = "module"``: a Hugging Face model (whose post_init runs ``self.apply(self._init_weights)``) is
+    built without any rank ever holding it whole — every sub-module is sharded when its constructor returns — the HF
+    initialiser still takes effect (through the gathered ``apply``), every rank ends up with rank 0's values, and the
+    model trains."""
+    import pytest as _pt
+    transformers = _pt.importorskip("transformers")
+    import shuffle_exchange_b200 as ds
+    from shuffle_exchange_b200.runtime.zero import partition_parameters as pp
+    cfg = transformers.AutoConfig.for_model(model_type="llama", vocab_size=128, hidden_size=32, intermediate_size=64,
+                                            num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
+                                            max_position_embeddings=64, initializer_range=0.5)
+    held = []                      # elements still whole under the module being sharded, at each sharding event
+    orig_convert = pp.Init._convert_module
+
+    def tracking(self, module, recurse=True):
+        held.append(sum(p.numel() for p in module.parameters(recurse=True)))
+        orig_convert(self, module, recurse)
+
+    pp.Init._convert_module = tracking
+    pp.Init.granularity = "module"
+    try:
+        torch.manual_seed(100 + rank)               # ranks would initialise differently ...
+        with ds.zero.Init(dtype=torch.float32):
+            model = transformers.AutoModelForCausalLM.from_config(cfg)
+    finally:
+        pp.Init._convert_module = orig_convert
+        pp.Init.granularity = "model"
+    assert max(held) <= 128 * 32, max(held)         # never more than one sub-module (the embedding) whole at a time
+    params = list(model.parameters())
+    assert all(p.numel() == 0 and p.ds_tensor is not None for p in params)
+    total = sum(p.ds_numel for p in params)
+    w = model.model.layers[0].mlp.down_proj.weight
+    with ds.zero.GatheredParameters([w]):
+        full = w.data.clone()
+    assert abs(float(full.std()) - 0.5) < 0.1, float(full.std())      # HF's normal_(std=initializer_range) was applied
+    ref = full.clone()
+    torch.distributed.broadcast(ref, 0)
+    assert torch.equal(ref, full)                                      # ... but all hold rank 0's initial values
+    assert torch.nn.Module.apply.__name__ == "apply"                  # the patch is lifted on exit
+    engine, _, _, _ = ds.initialize(model=model, config=_cfg(3), model_parameters=model.parameters())
+    ids = torch.randint(0, 128, (2, 16))
+    first = None
+    for _ in range(4):
+        loss = engine(input_ids=ids, labels=ids).loss
+        engine.backward(loss)
+        engine.step()
+        first = first if first is not None else float(loss)
+    assert float(loss) < first
+    assert total == sum(p.ds_numel for p in model.parameters())
+
+
+def test_zero_init_shards_per_module_with_hf_post_init():
+    run_dist(_zero_init_module_granularity_worker, 2)
