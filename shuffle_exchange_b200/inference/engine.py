@@ -215,24 +215,88 @@ class InferenceEngine(nn.Module):
                 sd.update(part.get("module", part.get("model", part)) if isinstance(part, dict) else part)
         if not sd:
             raise ValueError(f"no checkpoint files found for {load_dir}")
+        # ---- a skeleton built on the meta device (``OnDevice(device="meta")``): tensor-parallel layers could not slice
+        # anything when they were created, so each one is materialised from the checkpoint and sliced by its own rule
+        # right away (one layer whole at a time), then everything else is assigned
+        from ..module_inject.layers import TensorParallel_Layer
+        done = set()
+        for name, mod in self.module.named_modules():
+            w = getattr(mod, "weight", None)
+            if not isinstance(mod, TensorParallel_Layer) or w is None or not w.is_meta:
+                continue
+            wk, bk = f"{name}.weight", f"{name}.bias"
+            if wk not in sd:
+                continue
+            mod.weight = nn.Parameter(sd[wk].to(w.dtype), requires_grad=False)
+            b = getattr(mod, "bias", None)
+            if b is not None and bk in sd:
+                mod.bias = nn.Parameter(sd[bk].to(b.dtype), requires_grad=False)
+            mod._tp_partition([mod.weight, getattr(mod, "bias", None)])
+            done |= {wk, bk}
         own = self.module.state_dict()
         tp_rank = dist.get_rank(group=self.mp_group) if self.mp_group is not None else 0
         tp = self._config.tensor_parallel.tp_size
-        fixed = {}
+        fixed, on_meta = {}, False
         for k, v in sd.items():
-            if k not in own:
+            if k not in own or k in done:
                 continue
             tgt = own[k]
+            on_meta = on_meta or tgt.is_meta
             if v.shape == tgt.shape:
-                fixed[k] = v
+                fixed[k] = v.to(tgt.dtype) if tgt.is_meta else v
                 continue
             for dim in range(v.dim()):          # full tensor -> this rank's TP slice
                 if v.shape[dim] == tgt.shape[dim] * tp:
                     fixed[k] = v.chunk(tp, dim=dim)[tp_rank]
                     break
-        missing = self.module.load_state_dict(fixed, strict=False)
-        if load_module_strict and missing.missing_keys:
-            logger.warning(f"checkpoint is missing {len(missing.missing_keys)} keys, e.g. {missing.missing_keys[:3]}")
+        missing = self.module.load_state_dict(fixed, strict=False, assign=on_meta)
+        left = [k for k in missing.missing_keys if k not in done]
+        if load_module_strict and left:
+            logger.warning(f"checkpoint is missing {len(left)} keys, e.g. {left[:3]}")
+        still_meta = [n for n, p in self.module.named_parameters() if p.is_meta]
+        if still_meta:
+            tied = getattr(self.module, "tie_weights", None)
+            if callable(tied):
+                tied()                           # e.g. lm_head sharing the embedding: re-tie to the loaded tensor
+                still_meta = [n for n, p in self.module.named_parameters() if p.is_meta]
+        if still_meta:
+            raise RuntimeError(f"{len(still_meta)} parameters have no data after loading the checkpoint "
+                               f"(e.g. {still_meta[:3]}): the checkpoint does not cover the model")
+        self._materialise_meta_buffers(sd)
+
+    @staticmethod
+    def _rebuilt_on_cpu(mod):
+        """A parameter-free module whose buffers are computed in its constructor from a config object (rotary tables):
+        build a second instance on the host to obtain them."""
+        if any(True for _ in mod.parameters(recurse=False)) or not hasattr(mod, "config"):
+            return None
+        try:
+            with torch.device("cpu"):
+                return type(mod)(mod.config)
+        except Exception:
+            return None
+
+    def _materialise_meta_buffers(self, sd) -> None:
+        """Buffers of a meta-device skeleton: persistent ones come from the checkpoint; the usual non-persistent one —
+        the rotary ``inv_freq`` table — is recomputed by constructing the (parameter-free) module again on the host; anything else is an error here
+        rather than a failure inside ``.to(device)`` later."""
+        lost = []
+        for name, mod in self.module.named_modules():
+            for bname, buf in list(mod._buffers.items()):
+                if buf is None or not buf.is_meta:
+                    continue
+                key = f"{name}.{bname}" if name else bname
+                if key in sd:
+                    mod._buffers[bname] = sd[key].to(buf.dtype)
+                else:
+                    fresh = self._rebuilt_on_cpu(mod)
+                    if fresh is not None and isinstance(fresh._buffers.get(bname), torch.Tensor):
+                        mod._buffers[bname] = fresh._buffers[bname].to(buf.dtype)
+                    else:
+                        lost.append(key)
+        if lost:
+            raise RuntimeError(f"buffers without data after loading the checkpoint: {lost[:5]} — build the skeleton "
+                               "with these buffers on a real device or add them to the checkpoint")
 
     # ------------------------------------------------------------- tensor-parallel sharded checkpoints
     _TP_PARTITIONS = 8       # files per rank, so that no single file holds all layers (reference: 8)

@@ -101,3 +101,53 @@ def test_autotp_matches_unsharded():
 
 def test_autotp_with_overlapped_input_gradient_all_reduce():
     run_dist(_worker, 2, (True,))
+
+
+def _meta_skeleton_worker(rank, world, root):
+    """The large-model flow of the reference: skeleton on the meta device + checkpoint folder + tensor parallelism.
+    Every TP layer is filled from the checkpoint and sliced by its own rule, replicated tensors and tied / recomputed
+    buffers are materialised, and the logits equal the unsharded model's."""
+    import os
+    import pytest as _pt
+    transformers = _pt.importorskip("transformers")
+    import shuffle_exchange_b200 as sxb
+    cfg = transformers.AutoConfig.for_model(model_type="llama", vocab_size=96, hidden_size=32, intermediate_size=48,
+                                            num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
+                                            max_position_embeddings=64)
+    torch.manual_seed(0)
+    full = transformers.AutoModelForCausalLM.from_config(cfg).float().eval()
+    ids = torch.randint(0, 96, (2, 9), generator=torch.Generator().manual_seed(1))
+    with torch.no_grad():
+        ref = full(ids, use_cache=False).logits.clone()
+    if rank == 0:
+        torch.save(full.state_dict(), os.path.join(root, "pytorch_model.bin"))
+    torch.distributed.barrier()
+    with sxb.OnDevice(dtype=torch.float32, device="meta"):
+        skeleton = transformers.AutoModelForCausalLM.from_config(cfg).eval()
+    assert all(p.is_meta for p in skeleton.parameters())
+    eng = sxb.init_inference(skeleton, dtype=torch.float32, tensor_parallel={"tp_size": world}, checkpoint=root)
+    assert not any(p.is_meta for p in eng.module.parameters()) and not any(b.is_meta for b in eng.module.buffers())
+    assert tuple(eng.module.model.layers[0].mlp.down_proj.weight.shape) == (32, 48 // world)      # row-parallel slice
+    assert tuple(eng.module.model.layers[0].self_attn.q_proj.weight.shape) == (32 // world, 32)   # column-parallel
+    with torch.no_grad():
+        out = eng.module(ids, use_cache=False).logits
+    assert torch.allclose(out, ref, atol=1e-5), float((out - ref).abs().max())
+    # a checkpoint that does not cover the model is an error, not a crash inside .to(device)
+    if rank == 0:
+        sd = {k: v for k, v in full.state_dict().items() if "layers.1.mlp" not in k}
+        os.makedirs(os.path.join(root, "partial"), exist_ok=True)
+        torch.save(sd, os.path.join(root, "partial", "pytorch_model.bin"))
+    torch.distributed.barrier()
+    with sxb.OnDevice(dtype=torch.float32, device="meta"):
+        skeleton = transformers.AutoModelForCausalLM.from_config(cfg).eval()
+    try:
+        sxb.init_inference(skeleton, dtype=torch.float32, tensor_parallel={"tp_size": world},
+                           checkpoint=os.path.join(root, "partial"))
+        raised = False
+    except RuntimeError as e:
+        raised = "no data" in str(e)
+    assert raised
+
+
+def test_meta_skeleton_plus_checkpoint_with_tensor_parallelism(tmp_path):
+    run_dist(_meta_skeleton_worker, 2, (str(tmp_path),))
