@@ -172,3 +172,95 @@ def test_zero3_with_host_offload_inside_pipeline_stages():
     """BASELINE config 5 in miniature: ZeRO-3 + pipeline (PP=2) with optimizer state and parameter shards in host
     memory, DP=2 per stage."""
     run_dist(_pipe_zero_worker, 4, (3, True))
+
+
+class _Embed(nn.Module):
+    def __init__(self, vocab, d):
+        super().__init__()
+        self.weight = nn.Parameter(torch.randn(vocab, d) * 0.1)
+
+    def forward(self, ids):
+        return nn.functional.embedding(ids, self.weight)
+
+
+def _unembed(module, x):
+    return x @ module.weight.t()
+
+
+def _ce(logits, labels):
+    return nn.functional.cross_entropy(logits.reshape(-1, logits.shape[-1]), labels.reshape(-1))
+
+
+def _tied_pipe_worker(rank, world, root):
+    """Embedding on the first stage tied to the LM head on the last: both copies start equal, their gradients are
+    summed every step, training equals a single-process model that really shares the tensor; eval_batch returns the
+    same loss everywhere; a checkpoint written by the two stages restores a fresh engine bit for bit."""
+    import shuffle_exchange_b200 as ds
+    from shuffle_exchange_b200.runtime.pipe.module import LayerSpec, PipelineModule, TiedLayerSpec
+    V, d, micro, gas = 32, 8, 4, 2
+
+    def build():
+        torch.manual_seed(0)
+        return PipelineModule([TiedLayerSpec("embed", _Embed, V, d), LayerSpec(_Block, d), LayerSpec(_Block, d),
+                               TiedLayerSpec("embed", _Embed, V, d, forward_fn=_unembed)],
+                              num_stages=2, loss_fn=_ce, partition_method="uniform")
+
+    cfg = {"train_micro_batch_size_per_gpu": micro, "gradient_accumulation_steps": gas, "steps_per_print": 10 ** 9,
+           "optimizer": {"type": "SGD", "params": {"lr": 0.5}}}
+    # single-process oracle with ONE shared embedding
+    torch.manual_seed(0)
+    emb = _Embed(V, d)
+    blocks = nn.Sequential(_Block(d), _Block(d))
+    net = build()
+    tied = net.tied_modules["embed"] if hasattr(net, "tied_modules") else None
+    assert tied is not None
+    with torch.no_grad():                            # identical starting point on both sides
+        tied.weight.copy_(emb.weight)
+        for i, blk in enumerate(blocks):
+            idx = i + 1
+            if net._local_start <= idx < net._local_stop:
+                net.forward_funcs[idx - net._local_start].load_state_dict(blk.state_dict())
+    engine, _, _, _ = ds.initialize(model=net, model_parameters=[p for p in net.parameters()], config=cfg)
+    g = torch.Generator().manual_seed(3)
+    data = [(torch.randint(0, V, (micro, 6), generator=g),) * 2 for _ in range(gas * 4)]
+    it = iter(data)
+    losses = [float(engine.train_batch(data_iter=it)) for _ in range(3)]
+    opt = torch.optim.SGD(list(emb.parameters()) + list(blocks.parameters()), lr=0.5)
+    it2 = iter(data)
+    want = []
+    for _ in range(3):
+        opt.zero_grad()
+        tot = 0.0
+        for _ in range(gas):
+            ids, labels = next(it2)
+            l = _ce(blocks(emb(ids)) @ emb.weight.t(), labels) / gas
+            l.backward()
+            tot += float(l)
+        opt.step()
+        want.append(tot)
+    assert all(abs(a - b) < 1e-5 for a, b in zip(losses, want)), (losses, want)
+    assert torch.allclose(tied.weight, emb.weight, atol=1e-5)                 # both stages hold the SAME updated tensor
+    # evaluation: forward only, loss known on every stage
+    ev = float(engine.eval_batch(iter(data[-gas:])))
+    with torch.no_grad():
+        want_ev = sum(float(_ce(blocks(emb(i)) @ emb.weight.t(), l)) for i, l in data[-gas:]) / gas
+    assert abs(ev - want_ev) < 1e-5, (ev, want_ev)
+    assert engine.is_first_stage() == (rank == 0) and engine.is_last_stage() == (rank == world - 1)
+    # checkpoint: per-layer files from both stages, restored into a fresh engine that continues identically
+    engine.save_checkpoint(root, tag="t")
+    import os
+    files = os.listdir(os.path.join(root, "t"))
+    assert sum(f.startswith("layer_") for f in files) == 4, files
+    net2 = build()
+    e2, _, _, _ = ds.initialize(model=net2, model_parameters=[p for p in net2.parameters()], config=cfg)
+    e2.load_checkpoint(root, tag="t")
+    assert e2.global_steps == 3
+    nxt = iter(data[-gas:])
+    nxt2 = iter(data[-gas:])
+    assert abs(float(engine.train_batch(data_iter=nxt)) - float(e2.train_batch(data_iter=nxt2))) < 1e-6
+    for (n, p), (_, q) in zip(net.named_parameters(), net2.named_parameters()):
+        assert torch.allclose(p, q, atol=1e-6), n
+
+
+def test_tied_embedding_eval_and_checkpoint_across_two_stages(tmp_path):
+    run_dist(_tied_pipe_worker, 2, (str(tmp_path),))
