@@ -361,15 +361,40 @@ class IndexedDataset(torch.utils.data.Dataset):
     def __len__(self):
         return self._len
 
-    def __getitem__(self, i):
+    def check_index(self, i):
         if not 0 <= i < self._len:
             raise IndexError("index out of range")
+
+    def read_data(self, path=None):
+        """Open the data file (kept lazy so that the object pickles into DataLoader workers)."""
+        self._open()
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):                        # contiguous items: one read, then cut (reference :205-217)
+            start, stop, step = i.indices(self._len)
+            if step != 1:
+                raise ValueError("Slices into indexed_dataset must be contiguous")
+            if stop <= start:
+                return []
+            self._open()
+            counts = [int(self.data_offsets[k + 1] - self.data_offsets[k]) for k in range(start, stop)]
+            flat = np.empty(sum(counts), dtype=self.dtype)
+            self.data_file.seek(int(self.data_offsets[start]) * self.element_size)
+            self.data_file.readinto(flat)
+            return np.split(flat, np.cumsum(counts)[:-1])
+        self.check_index(i)
         self._open()
         shape = tuple(int(s) for s in self.sizes[self.dim_offsets[i]:self.dim_offsets[i + 1]])
         a = np.empty(shape, dtype=self.dtype)
         self.data_file.seek(int(self.data_offsets[i]) * self.element_size)
         self.data_file.readinto(a)
         return a
+
+    def num_tokens(self, index):
+        return int(self.sizes[index])
+
+    def size(self, index):
+        return int(self.sizes[index])
 
     def __del__(self):
         if getattr(self, "data_file", None):

@@ -67,6 +67,11 @@ def test_legacy_indexed_dataset_round_trip(tmp_path):
     assert len(ds) == len(docs)
     for i, d in enumerate(docs):
         assert np.array_equal(np.asarray(ds[i]), d)
+    sl = ds[1:4]
+    assert len(sl) == 3 and all(np.array_equal(a, d) for a, d in zip(sl, docs[1:4])) and ds[3:3] == []
+    assert ds.num_tokens(2) == ds.size(2) == len(docs[2])
+    with pytest.raises(ValueError):
+        ds[0:4:2]
     cached = ids.IndexedCachedDataset(prefix)
     cached.prefetch([1, 3])
     assert np.array_equal(np.asarray(cached[3]), docs[3])
