@@ -183,3 +183,53 @@ def test_variable_batch_size_packing_and_lr_scaling():
     sched.step()
     sched.load_state_dict(sd)
     assert sched.last_epoch == 1
+
+
+def test_curriculum_sampler_consumes_the_analyzer_output(tmp_path):
+    """Analyzer -> sampler: with a value-based ``seqlen`` curriculum rising from 3 to 13, early batches hold only short
+    samples, the eligible pool grows cluster by cluster, ranks get disjoint slices of each global batch, and a resumed
+    sampler continues exactly where the saved one would."""
+    from shuffle_exchange_b200.runtime.data_pipeline.data_sampling.data_analyzer import SINGLE, DataAnalyzer
+    from shuffle_exchange_b200.runtime.data_pipeline.data_sampling.data_sampler import DeepSpeedDataSampler
+    n, root = 130, str(tmp_path)
+    ds = _SeqDataset(n)
+    DataAnalyzer(ds, batch_size=8, metric_names=["seqlen"], metric_functions=[_len_metric], metric_types=[SINGLE],
+                 metric_dtypes=[np.int64], save_path=root, collate_fn=lambda xs: xs).run_map_reduce()
+    lens = np.array([len(ds[i]) for i in range(n)])
+    cfg = {"seed": 7, "data_sampling": {"num_epochs": 50, "curriculum_learning": {
+        "enabled": True, "data_cluster_path": f"{root}/clusters", "curriculum_metrics": {"seqlen": {
+            "index_to_sample_path": f"{root}/seqlen/seqlen_index_to_sample",
+            "index_to_metric_path": f"{root}/seqlen/seqlen_index_to_metric",
+            "difficulty_type": "value", "clustering_type": "schedule_based", "min_difficulty": 3, "max_difficulty": 13,
+            "schedule_type": "fixed_linear", "schedule_config": {"total_curriculum_step": 10, "difficulty_step": 2}}}}}}
+
+    def sampler(rank):
+        return DeepSpeedDataSampler(cfg, n, micro_batch_size=4, data_parallel_rank=rank, data_parallel_size=2,
+                                    data_parallel_group=None, gradient_accumulation_steps=1, global_rank=0)
+
+    s0 = sampler(0)
+    it = iter(s0)
+    seen_max = []
+    for step in range(14):
+        mine = next(it)
+        assert len(mine) == 4 and all(0 <= i < n for i in mine)
+        limit = s0.current_difficulties["seqlen"]
+        assert lens[mine].max() <= limit, (step, lens[mine].max(), limit)     # nothing harder than the schedule allows
+        seen_max.append(int(limit))
+    assert seen_max[0] == 3 or seen_max[0] == 4 and seen_max[-1] == 13 and seen_max == sorted(seen_max)
+    assert len(s0.clusters) >= 4 and sum(len(c) for c in s0.clusters) == int((lens <= 13).sum())
+    union = np.concatenate([c.ids for c in s0.clusters])
+    assert len(np.unique(union)) == len(union)                                  # clusters never overlap
+    # the two data-parallel ranks split every global batch without overlap
+    a, b = sampler(0), sampler(1)
+    assert a.get_start_end_idx() == (0, 4) and b.get_start_end_idx() == (4, 8)
+    # resume: the restored sampler yields what the original yields next
+    sd = s0.state_dict()
+    import copy
+    sd = copy.deepcopy(sd)
+    want = [next(it) for _ in range(3)]
+    s1 = sampler(0)
+    s1.load_state_dict(sd)
+    it1 = iter(s1)
+    got = [next(it1) for _ in range(3)]
+    assert got == want
