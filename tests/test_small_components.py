@@ -251,3 +251,54 @@ def _ints_worker(rank, world):
 def test_ranks_disagreeing_on_a_fetch_order_are_caught():
     from conftest import run_dist
     run_dist(_ints_worker, 2)
+
+
+def _curriculum_pld_worker(rank, world):
+    """Legacy sequence-length curriculum and progressive layer drop reach the model's forward as keyword arguments, step
+    by step, and only while training."""
+    import math
+    import shuffle_exchange_b200 as ds
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.emb = torch.nn.Embedding(32, 8)
+            self.head = torch.nn.Linear(8, 32)
+            self.calls = []
+
+        def forward(self, ids, curriculum_seqlen=None, progressive_layer_drop=None, pld_theta=None):
+            self.calls.append((curriculum_seqlen, progressive_layer_drop, pld_theta))
+            if curriculum_seqlen is not None:
+                ids = ids[:, :curriculum_seqlen]
+            logits = self.head(self.emb(ids))
+            return torch.nn.functional.cross_entropy(logits.reshape(-1, 32), ids.reshape(-1))
+
+    net = Net()
+    engine, _, _, _ = ds.initialize(model=net, model_parameters=net.parameters(), config={
+        "train_micro_batch_size_per_gpu": 2, "steps_per_print": 10 ** 9,
+        "optimizer": {"type": "SGD", "params": {"lr": 0.1}},
+        "progressive_layer_drop": {"enabled": True, "theta": 0.5, "gamma": 0.1},
+        "curriculum_learning": {"enabled": True, "curriculum_type": "seqlen", "min_difficulty": 4, "max_difficulty": 16,
+                                "schedule_type": "fixed_linear",
+                                "schedule_config": {"total_curriculum_step": 4, "difficulty_step": 4}}})
+    ids = torch.randint(0, 32, (2, 16))
+    for _ in range(6):
+        engine.backward(engine(ids))
+        engine.step()
+    seqlens = [c[0] for c in net.calls]
+    assert seqlens == [4, 8, 12, 16, 16, 16], seqlens                       # multiples of difficulty_step, capped
+    assert all(c[1] is True for c in net.calls)
+    thetas = [c[2] for c in net.calls]
+    assert thetas[0] == 1.0 and all(a >= b for a, b in zip(thetas, thetas[1:]))
+    # the schedule is advanced with the step count BEFORE it is incremented (as in the reference): 6th forward sees t = 4
+    assert abs(thetas[-1] - (0.5 * math.exp(-0.1 * 4) + 0.5)) < 1e-9
+    net.calls.clear()
+    engine.eval()
+    with torch.no_grad():
+        engine(ids)
+    assert net.calls == [(None, None, None)]                                 # evaluation sees the plain signature
+
+
+def test_legacy_curriculum_and_pld_reach_the_forward():
+    from conftest import run_dist
+    run_dist(_curriculum_pld_worker, 1)
