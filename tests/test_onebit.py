@@ -1,4 +1,5 @@
 """1-bit communication: packbits round trip, compressed all-reduce accuracy and 1-bit Adam convergence (gloo, 2 ranks)."""
+import pytest
 import torch
 
 from conftest import run_dist
@@ -65,3 +66,46 @@ def _onebit_adam_worker(rank, world):
 
 def test_onebit_adam_converges():
     run_dist(_onebit_adam_worker, 2)
+
+
+def _other_onebit_worker(rank, world, which):
+    """1-bit LAMB and 0/1 Adam on the same noisy quadratic: pass their warm-up / variance-freeze point, converge, and
+    keep the replicas identical under compressed communication."""
+    import torch.distributed as td
+    from shuffle_exchange_b200.runtime.fp16.onebit import OnebitLamb, ZeroOneAdam
+    torch.manual_seed(0)
+    ws_ = [torch.nn.Parameter(torch.zeros(64)), torch.nn.Parameter(torch.zeros(8, 16))]
+    target = [torch.where(torch.arange(64) % 2 == 0, 1.0, -1.0), torch.full((8, 16), 0.5)]
+    if which == "lamb":
+        opt = OnebitLamb(ws_, lr=0.05, freeze_step=20, comm_backend_name="compressed", max_coeff=2.0, min_coeff=0.1)
+        frozen = lambda: opt.lamb_freeze_key            # noqa: E731
+    else:
+        opt = ZeroOneAdam(ws_, lr=0.02, var_freeze_step=20, var_update_scaler=4, local_step_scaler=40,
+                          local_step_clipper=4, comm_backend_name="compressed")
+        frozen = lambda: opt.freeze_key                 # noqa: E731
+    g = torch.Generator().manual_seed(100 + rank)
+    first = None
+    for it in range(300):
+        loss = sum(((w - t + torch.randn(w.shape, generator=g) * 0.1) ** 2).sum() for w, t in zip(ws_, target))
+        first = first if first is not None else float(loss)
+        opt.zero_grad()
+        loss.backward()
+        if which == "lamb" and not frozen():           # warm-up of 1-bit LAMB: the "engine" averages gradients
+            for w in ws_:
+                td.all_reduce(w.grad)
+                w.grad /= world
+        opt.step()
+    assert frozen()
+    errs = [float((w.detach() - t).abs().max()) for w, t in zip(ws_, target)]
+    assert max(errs) < 0.3, errs
+    for w in ws_:
+        parts = [torch.zeros_like(w.data) for _ in range(world)]
+        td.all_gather(parts, w.data)
+        assert torch.allclose(parts[0], parts[1], atol=1e-5)
+    sd = opt.state_dict()
+    assert len(sd["state"]) == 2 and "exp_avg" in sd["state"][0]
+
+
+@pytest.mark.parametrize("which", ["lamb", "zoadam"])
+def test_onebit_lamb_and_zero_one_adam_converge(which):
+    run_dist(_other_onebit_worker, 2, (which,))
