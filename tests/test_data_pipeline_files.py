@@ -233,3 +233,54 @@ def test_curriculum_sampler_consumes_the_analyzer_output(tmp_path):
     it1 = iter(s1)
     got = [next(it1) for _ in range(3)]
     assert got == want
+
+
+def _engine_curriculum_worker(rank, world, root):
+    """``initialize(training_data=..., config={"data_efficiency": ...})`` on two ranks: rank 0 draws every global batch
+    from the curriculum clusters and broadcasts it, each rank receives its own slice, difficulty grows with the steps,
+    the post-process hook sees every batch."""
+    import shuffle_exchange_b200 as ds
+    from shuffle_exchange_b200.runtime.data_pipeline.data_sampling.data_analyzer import SINGLE, DataAnalyzer
+    n = 96
+    data = _SeqDataset(n)
+    if rank == 0:
+        DataAnalyzer(data, batch_size=8, metric_names=["seqlen"], metric_functions=[_len_metric], metric_types=[SINGLE],
+                     metric_dtypes=[np.int64], save_path=root, collate_fn=lambda xs: xs).run_map()
+        DataAnalyzer(data, batch_size=8, metric_names=["seqlen"], metric_functions=[_len_metric], metric_types=[SINGLE],
+                     metric_dtypes=[np.int64], save_path=root, collate_fn=lambda xs: xs).run_reduce()
+    torch.distributed.barrier()
+    net = torch.nn.Linear(4, 4)
+    cfg = {"train_micro_batch_size_per_gpu": 3, "steps_per_print": 10 ** 9,
+           "optimizer": {"type": "SGD", "params": {"lr": 0.1}},
+           "data_efficiency": {"enabled": True, "seed": 5, "data_sampling": {"enabled": True, "num_epochs": 100,
+               "curriculum_learning": {"enabled": True, "data_cluster_path": f"{root}/clusters", "curriculum_metrics": {
+                   "seqlen": {"index_to_sample_path": f"{root}/seqlen/seqlen_index_to_sample",
+                              "index_to_metric_path": f"{root}/seqlen/seqlen_index_to_metric",
+                              "difficulty_type": "value", "clustering_type": "schedule_based", "min_difficulty": 2,
+                              "max_difficulty": 13, "schedule_type": "fixed_linear",
+                              "schedule_config": {"total_curriculum_step": 6, "difficulty_step": 1}}}}}}}
+    engine, _, loader, _ = ds.initialize(model=net, model_parameters=net.parameters(), training_data=data, config=cfg,
+                                         collate_fn=lambda xs: xs)
+    assert engine.curriculum_learning_enabled() and loader.curriculum_learning_enabled
+    hooked = []
+    engine.set_data_post_process_func(lambda batch, state: (hooked.append(len(batch)), batch)[1])
+    it = iter(loader)
+    longest = []
+    for step in range(8):
+        batch = next(it)
+        assert len(batch) == 3                                           # this rank's micro-batch
+        ids = torch.tensor([int(x[0]) for x in batch])                   # sample i is filled with the value i
+        gathered = [torch.zeros_like(ids) for _ in range(world)]
+        torch.distributed.all_gather(gathered, ids)
+        assert len(set(torch.cat(gathered).tolist())) == 3 * world      # ranks hold disjoint slices of one global batch
+        longest.append(max(len(x) for x in batch))
+    bounds = [min(13, int(2 + 11 * k / 6)) for k in range(1, 9)]        # fixed_linear: 3, 5, 7, 9, 11, 13, 13, 13
+    assert all(l <= b for l, b in zip(longest, bounds)), (longest, bounds)   # short samples first
+    assert len(hooked) == 8
+    sampler = loader.data_sampler
+    assert sampler.curriculum_step == 8 and sampler.current_difficulties["seqlen"] == 13
+
+
+def test_engine_level_curriculum_data_loading_two_ranks(tmp_path):
+    from conftest import run_dist
+    run_dist(_engine_curriculum_worker, 2, (str(tmp_path),))
