@@ -127,3 +127,37 @@ def _moe_worker(rank, world):
 def test_moe_layer_capacity_path_matches_dense_evaluation():
     from conftest import run_dist
     run_dist(_moe_worker, 1)
+
+
+def _moe_ep_worker(rank, world):
+    """Expert parallelism of the capacity path: 4 experts over 2 ranks, each rank routes ITS tokens; the all-to-alls
+    carry them to the owning rank and back.  Every rank's output equals the dense evaluation with all four experts."""
+    from shuffle_exchange_b200.moe.layer import MoE
+    d, E = 8, 4
+    torch.manual_seed(0)
+    all_experts = [_Expert(d) for _ in range(E)]                       # same on both ranks (same seed)
+    gate_w = torch.randn(E, d) * 0.5
+    moe = MoE(hidden_size=d, expert=_Expert(d), num_experts=E, ep_size=2, k=1, capacity_factor=16.0, min_capacity=1,
+              use_rts=False)
+    moe.set_deepspeed_parallelism()
+    with torch.no_grad():
+        moe.deepspeed_moe.gate.wg.weight.copy_(gate_w)
+        for local, ex in enumerate(moe.deepspeed_moe.experts.deepspeed_experts):
+            ex.load_state_dict(all_experts[rank * 2 + local].state_dict())   # rank r owns experts 2r, 2r+1
+    g = torch.Generator().manual_seed(10 + rank)
+    x = torch.randn(2, 6, d, generator=g, requires_grad=True)
+    y, l_aux, counts = moe(x)
+    flat = x.detach().reshape(-1, d)
+    gates = F.softmax(F.linear(flat, gate_w), 1)
+    want = torch.stack([gates[t].max() * all_experts[int(gates[t].argmax())](flat[t]) for t in range(flat.shape[0])])
+    assert torch.allclose(y.reshape(-1, d), want, atol=1e-5), float((y.reshape(-1, d) - want).abs().max())
+    y.sum().backward()
+    assert x.grad is not None and x.grad.abs().sum() > 0
+    # an expert's gradient contains the tokens the OTHER rank sent to it
+    g0 = moe.deepspeed_moe.experts.deepspeed_experts[0].fc.weight.grad
+    assert g0 is not None
+
+
+def test_moe_capacity_path_with_expert_parallelism_two_ranks():
+    from conftest import run_dist
+    run_dist(_moe_ep_worker, 2)
